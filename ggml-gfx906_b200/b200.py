@@ -1,0 +1,202 @@
+"""ctypes binding of libggml_b200_kernels.so (the C ABI in include/ggml_b200.h).
+
+This is the host-side mirror of the reference's kernel launchers for the quantized hot path
+(src/ggml-cuda/{convert,quantize,getrows,mmvq,mmq}.cu host functions): same operations, same
+argument meaning (ggml ne/nb conventions), errors raised instead of GGML_ABORT.  PyTorch is used
+only as plumbing: device buffers (uint8 / float32 tensors), streams and torch.distributed.  Nothing
+here computes on the CPU; if the library or a device is missing the calls raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libggml_b200_kernels.so")
+
+TYPE_ID = {"f32": 0, "f16": 1, "q4_0": 2, "q8_0": 8, "q8_1": 9, "q4_K": 12, "q5_K": 13, "q6_K": 14, "i32": 26, "bf16": 30}
+BLOCK_ELEMS = {"q4_0": 32, "q8_0": 32, "q8_1": 32, "q4_K": 256, "q5_K": 256, "q6_K": 256}
+BLOCK_BYTES = {"q4_0": 18, "q8_0": 34, "q8_1": 36, "q4_K": 144, "q5_K": 176, "q6_K": 210}
+QUANT_TYPES = ("q4_0", "q8_0", "q4_K", "q5_K", "q6_K")
+MMVQ_MAX_N = 8
+
+
+class B200Error(RuntimeError):
+    pass
+
+
+def row_bytes(t: str, k: int) -> int:
+    if k % BLOCK_ELEMS[t] != 0:
+        raise ValueError(f"k={k} is not a multiple of the {t} block size")
+    return k // BLOCK_ELEMS[t] * BLOCK_BYTES[t]
+
+
+def load_library(path: Optional[str] = None) -> C.CDLL:
+    path = path or LIB_PATH
+    if not os.path.exists(path):
+        raise B200Error(f"{path} not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                        f"(there is no CPU fallback for these ops)")
+    lib = C.CDLL(path)
+    vp, i64, sz, i32 = C.c_void_p, C.c_int64, C.c_size_t, C.c_int
+    A4i, A4s = C.POINTER(i64), C.POINTER(sz)
+    lib.b200_abi_version.restype = i32
+    lib.b200_error_string.restype = C.c_char_p;  lib.b200_error_string.argtypes = [i32]
+    lib.b200_device_count.restype = i32
+    lib.b200_device_info.restype = i32
+    lib.b200_device_info.argtypes = [i32, C.c_char_p, sz, C.POINTER(sz), C.POINTER(sz), C.POINTER(i32), C.POINTER(i32)]
+    lib.b200_block_elems.restype = i32;          lib.b200_block_elems.argtypes = [i32]
+    lib.b200_block_bytes.restype = sz;           lib.b200_block_bytes.argtypes = [i32]
+    lib.b200_row_bytes.restype = sz;             lib.b200_row_bytes.argtypes = [i32, i64]
+    lib.b200_dequantize_row.restype = i32;       lib.b200_dequantize_row.argtypes = [i32, vp, vp, i64, i32, vp]
+    lib.b200_dequantize_4d.restype = i32
+    lib.b200_dequantize_4d.argtypes = [i32, vp, A4i, A4s, vp, i32, A4i, A4s, vp]
+    lib.b200_quantize_row_q8_1.restype = i32;    lib.b200_quantize_row_q8_1.argtypes = [vp, sz, i64, i64, vp, vp]
+    lib.b200_get_rows.restype = i32
+    lib.b200_get_rows.argtypes = [i32, vp, sz, i64, i64, vp, sz, i64, vp, i32, sz, vp]
+    lib.b200_mul_mat_workspace_size.restype = sz
+    lib.b200_mul_mat_workspace_size.argtypes = [i32, A4i, A4i]
+    lib.b200_mul_mat.restype = i32
+    lib.b200_mul_mat.argtypes = [i32, vp, A4i, A4s, vp, A4i, A4s, vp, vp, sz, vp]
+    lib.b200_acts_scratch_bytes.restype = sz;    lib.b200_acts_scratch_bytes.argtypes = [i64, i64]
+    lib.b200_quantize_acts.restype = i32;        lib.b200_quantize_acts.argtypes = [vp, sz, i64, i64, vp, vp]
+    lib.b200_mul_mat_vec_q.restype = i32
+    lib.b200_mul_mat_vec_q.argtypes = [i32, vp, sz, i64, i64, vp, i64, vp, sz, vp]
+    lib.b200_mul_mat_q_workspace_size.restype = sz
+    lib.b200_mul_mat_q_workspace_size.argtypes = [i64, i64, i64]
+    lib.b200_mul_mat_q.restype = i32
+    lib.b200_mul_mat_q.argtypes = [i32, vp, sz, i64, i64, vp, sz, i64, vp, sz, vp, sz, vp]
+    lib.b200_launch_count.restype = C.c_uint64
+    return lib
+
+
+def _a4i(v):
+    return (C.c_int64 * 4)(*[int(x) for x in v])
+
+
+def _a4s(v):
+    return (C.c_size_t * 4)(*[int(x) for x in v])
+
+
+class Kernels:
+    """The kernel library bound to torch device buffers.  All methods enqueue on torch's current stream."""
+
+    def __init__(self, path: Optional[str] = None, device: int = 0):
+        import torch
+        self.torch = torch
+        self.lib = load_library(path)
+        if not torch.cuda.is_available() or self.lib.b200_device_count() <= device:
+            raise B200Error("no sm_100 CUDA device visible: the B200 kernels have no CPU fallback")
+        self.device = torch.device("cuda", device)
+        torch.cuda.set_device(self.device)
+        self._ws = None
+
+    # ------------------------------------------------------------------ helpers
+    def _check(self, rc: int, what: str):
+        if rc != 0:
+            raise B200Error(f"{what}: {self.lib.b200_error_string(rc).decode()} (code {rc})")
+
+    def _stream(self):
+        return C.c_void_p(self.torch.cuda.current_stream().cuda_stream)
+
+    def launch_count(self) -> int:
+        return int(self.lib.b200_launch_count())
+
+    def to_device(self, arr):
+        """numpy array (any dtype) -> device tensor of the same dtype/shape."""
+        return self.torch.from_numpy(arr).to(self.device)
+
+    def workspace(self, nbytes: int):
+        if self._ws is None or self._ws.numel() < nbytes:
+            self._ws = self.torch.empty(max(nbytes, 1 << 20), dtype=self.torch.uint8, device=self.device)
+        return self._ws
+
+    # ------------------------------------------------------------------ dequantize_row_*
+    def dequantize_row(self, t: str, blocks, n_elems: int, out_dtype: str = "f32"):
+        torch = self.torch
+        out = torch.empty(n_elems, dtype=torch.float32 if out_dtype == "f32" else torch.float16, device=self.device)
+        self._check(self.lib.b200_dequantize_row(TYPE_ID[t], blocks.data_ptr(), out.data_ptr(), n_elems,
+                                                 TYPE_ID[out_dtype], self._stream()), "dequantize_row")
+        return out
+
+    def dequantize_4d(self, t: str, blocks, ne_src, nb_src, out, ne_dst, nb_dst):
+        out_type = TYPE_ID["f32"] if out.dtype == self.torch.float32 else TYPE_ID["f16"]
+        self._check(self.lib.b200_dequantize_4d(TYPE_ID[t], blocks.data_ptr(), _a4i(ne_src), _a4s(nb_src), out.data_ptr(),
+                                                out_type, _a4i(ne_dst), _a4s(nb_dst), self._stream()), "dequantize_4d")
+        return out
+
+    # ------------------------------------------------------------------ quantize_row_q8_1
+    def quantize_row_q8_1(self, x):
+        """x: f32 [n, k] (row stride may exceed k) -> uint8 [n, k/32*36] block_q8_1."""
+        torch = self.torch
+        assert x.dtype == torch.float32 and x.dim() == 2 and x.stride(1) == 1
+        n, k = x.shape
+        out = torch.empty((n, k // 32 * 36), dtype=torch.uint8, device=self.device)
+        self._check(self.lib.b200_quantize_row_q8_1(x.data_ptr(), x.stride(0) * 4, k, n, out.data_ptr(), self._stream()),
+                    "quantize_row_q8_1")
+        return out
+
+    # ------------------------------------------------------------------ GET_ROWS
+    def get_rows(self, t: str, table, k: int, rows, out_dtype: str = "f32", table_row_stride: Optional[int] = None):
+        torch = self.torch
+        assert rows.dtype == torch.int32
+        rb = table_row_stride or row_bytes(t, k)
+        n_table = table.numel() // rb
+        out = torch.empty((rows.numel(), k), dtype=torch.float32 if out_dtype == "f32" else torch.float16, device=self.device)
+        self._check(self.lib.b200_get_rows(TYPE_ID[t], table.data_ptr(), rb, k, n_table, rows.data_ptr(), 4, rows.numel(),
+                                           out.data_ptr(), TYPE_ID[out_dtype], out.stride(0) * out.element_size(),
+                                           self._stream()), "get_rows")
+        return out
+
+    # ------------------------------------------------------------------ MUL_MAT
+    def quantize_acts(self, x, scratch=None):
+        torch = self.torch
+        n, k = x.shape
+        nbytes = int(self.lib.b200_acts_scratch_bytes(k, n))
+        if scratch is None:
+            scratch = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=self.device)
+        self._check(self.lib.b200_quantize_acts(x.data_ptr(), x.stride(0) * 4, k, n, scratch.data_ptr(), self._stream()),
+                    "quantize_acts")
+        return scratch
+
+    def mul_mat_vec_q(self, t: str, w, m: int, k: int, scratch, n: int, out=None, w_row_stride: Optional[int] = None):
+        torch = self.torch
+        if out is None:
+            out = torch.empty((n, m), dtype=torch.float32, device=self.device)
+        self._check(self.lib.b200_mul_mat_vec_q(TYPE_ID[t], w.data_ptr(), w_row_stride or row_bytes(t, k), m, k,
+                                                scratch.data_ptr(), n, out.data_ptr(), out.stride(0) * 4, self._stream()),
+                    "mul_mat_vec_q")
+        return out
+
+    def mul_mat_q(self, t: str, w, m: int, k: int, x, out=None, w_row_stride: Optional[int] = None):
+        torch = self.torch
+        n = x.shape[0]
+        if out is None:
+            out = torch.empty((n, m), dtype=torch.float32, device=self.device)
+        nbytes = int(self.lib.b200_mul_mat_q_workspace_size(m, k, n))
+        ws = self.workspace(nbytes)
+        self._check(self.lib.b200_mul_mat_q(TYPE_ID[t], w.data_ptr(), w_row_stride or row_bytes(t, k), m, k,
+                                            x.data_ptr(), x.stride(0) * 4, n, out.data_ptr(), out.stride(0) * 4,
+                                            ws.data_ptr(), ws.numel(), self._stream()), "mul_mat_q")
+        return out
+
+    def mul_mat(self, t: str, w, m: int, k: int, x, out=None):
+        """ggml_mul_mat(W[k,m] quantized, X[k,n] f32) -> [m,n] stored as an (n, m) row-major tensor."""
+        n = x.shape[0]
+        ne_a = [k, m, 1, 1]
+        rb = row_bytes(t, k)
+        nb_a = [BLOCK_BYTES[t], rb, rb * m, rb * m]
+        ne_b = [k, n, 1, 1]
+        sb = x.stride(0) * 4
+        nb_b = [4, sb, sb * n, sb * n]
+        return self.mul_mat_4d(t, w, ne_a, nb_a, x, ne_b, nb_b, out)
+
+    def mul_mat_4d(self, t: str, a, ne_a, nb_a, b, ne_b, nb_b, out=None):
+        torch = self.torch
+        if out is None:
+            out = torch.empty((ne_b[3], ne_b[2], ne_b[1], ne_a[1]), dtype=torch.float32, device=self.device)
+        nbytes = int(self.lib.b200_mul_mat_workspace_size(TYPE_ID[t], _a4i(ne_a), _a4i(ne_b)))
+        ws = self.workspace(nbytes)
+        self._check(self.lib.b200_mul_mat(TYPE_ID[t], a.data_ptr(), _a4i(ne_a), _a4s(nb_a), b.data_ptr(), _a4i(ne_b),
+                                          _a4s(nb_b), out.data_ptr(), ws.data_ptr(), ws.numel(), self._stream()), "mul_mat")
+        return out

@@ -1,0 +1,676 @@
+// plugin.cpp — libggml-b200.so: the ggml backend plugin around the B200 kernel library.
+//
+// An unmodified ggml loads this with ggml_backend_load() / GGML_BACKEND_PATH
+// (reference src/ggml-backend-reg.cpp:239-283, 595-599).  It fills the reference's own vtables
+// (src/ggml-backend-impl.h:17-207) and plays the role of src/ggml-cuda/ggml-cuda.cu for the ops it
+// claims: MUL_MAT with Q4_0/Q8_0/Q4_K/Q5_K/Q6_K weights and f32 activations, GET_ROWS on those
+// formats, CPY/DUP/CONT from those formats to f32/f16.  Everything else is answered with
+// supports_op = false so ggml_backend_sched keeps it on another backend; nothing claimed here ever
+// falls back to the CPU.
+//
+// Host-side design (not a port of ggml-cuda.cu): one stream per backend instance, one grow-only
+// workspace per backend, every kernel reached through the C ABI of include/ggml_b200.h, and whole
+// graph_compute() calls replayed as CUDA graphs (see graph_cache below) because decode graphs are
+// hundreds of 1-5 us kernels.
+#include "ggml.h"
+#include "ggml-backend.h"
+#include "ggml-backend-impl.h"
+
+#include "../../include/ggml_b200.h"
+#include "../../include/ggml_b200_plugin.h"
+
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#define B200_MAX_DEVICES 16
+
+static void b200_log(const char * fmt, ...) __attribute__((format(printf, 1, 2)));
+static void b200_log(const char * fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    fprintf(stderr, "ggml-b200: ");
+    vfprintf(stderr, fmt, ap);
+    va_end(ap);
+}
+
+// Device errors are fatal, as in the reference (CUDA_CHECK -> GGML_ABORT, src/ggml-cuda/common.cuh:145-156)
+#define CUDA_OK(expr)                                                                                  \
+    do {                                                                                               \
+        cudaError_t e_ = (expr);                                                                       \
+        if (e_ != cudaSuccess) {                                                                       \
+            b200_log("%s failed: %s (%s:%d)\n", #expr, cudaGetErrorString(e_), __FILE__, __LINE__);    \
+            GGML_ABORT("ggml-b200: CUDA error");                                                       \
+        }                                                                                              \
+    } while (0)
+#define B200_OK_OR_ABORT(expr)                                                                         \
+    do {                                                                                               \
+        int rc_ = (expr);                                                                              \
+        if (rc_ != 0) {                                                                                \
+            b200_log("%s failed: %s (%s:%d)\n", #expr, b200_error_string(rc_), __FILE__, __LINE__);    \
+            GGML_ABORT("ggml-b200: kernel library error");                                             \
+        }                                                                                              \
+    } while (0)
+
+static bool is_hot_quant(enum ggml_type t) {
+    return t == GGML_TYPE_Q4_0 || t == GGML_TYPE_Q8_0 || t == GGML_TYPE_Q4_K || t == GGML_TYPE_Q5_K || t == GGML_TYPE_Q6_K;
+}
+
+// ================================================================= contexts
+struct b200_device_ctx {
+    int         device;
+    std::string name;         // "B200_0"
+    std::string description;  // cudaDeviceProp::name
+};
+
+struct b200_buffer_ctx {
+    int    device;
+    void * base;
+};
+
+struct b200_backend_ctx;
+static ggml_backend_buffer_type_t b200_buffer_type(int device);
+static bool buft_is_b200(ggml_backend_buffer_type_t buft);
+static bool buft_is_b200_split(ggml_backend_buffer_type_t buft);
+
+// ================================================================= device buffer
+// mirrors the role of ggml_backend_cuda_buffer_* (src/ggml-cuda/ggml-cuda.cu:571-669)
+static void b200_buffer_free(ggml_backend_buffer_t buffer) {
+    b200_buffer_ctx * ctx = (b200_buffer_ctx *) buffer->context;
+    cudaSetDevice(ctx->device);
+    cudaFree(ctx->base);
+    delete ctx;
+}
+static void * b200_buffer_get_base(ggml_backend_buffer_t buffer) {
+    return ((b200_buffer_ctx *) buffer->context)->base;
+}
+static enum ggml_status b200_buffer_init_tensor(ggml_backend_buffer_t, struct ggml_tensor *) {
+    return GGML_STATUS_SUCCESS;   // no padding contract: the kernels never read past a row's 16-byte ceiling
+}
+static void b200_buffer_memset_tensor(ggml_backend_buffer_t buffer, struct ggml_tensor * tensor, uint8_t value, size_t offset, size_t size) {
+    b200_buffer_ctx * ctx = (b200_buffer_ctx *) buffer->context;
+    CUDA_OK(cudaSetDevice(ctx->device));
+    CUDA_OK(cudaMemsetAsync((char *) tensor->data + offset, value, size, cudaStreamPerThread));
+    CUDA_OK(cudaStreamSynchronize(cudaStreamPerThread));
+}
+static void b200_buffer_set_tensor(ggml_backend_buffer_t buffer, struct ggml_tensor * tensor, const void * data, size_t offset, size_t size) {
+    b200_buffer_ctx * ctx = (b200_buffer_ctx *) buffer->context;
+    CUDA_OK(cudaSetDevice(ctx->device));
+    CUDA_OK(cudaMemcpyAsync((char *) tensor->data + offset, data, size, cudaMemcpyHostToDevice, cudaStreamPerThread));
+    CUDA_OK(cudaStreamSynchronize(cudaStreamPerThread));
+}
+static void b200_buffer_get_tensor(ggml_backend_buffer_t buffer, const struct ggml_tensor * tensor, void * data, size_t offset, size_t size) {
+    b200_buffer_ctx * ctx = (b200_buffer_ctx *) buffer->context;
+    CUDA_OK(cudaSetDevice(ctx->device));
+    CUDA_OK(cudaMemcpyAsync(data, (const char *) tensor->data + offset, size, cudaMemcpyDeviceToHost, cudaStreamPerThread));
+    CUDA_OK(cudaStreamSynchronize(cudaStreamPerThread));
+}
+static bool b200_buffer_cpy_tensor(ggml_backend_buffer_t buffer, const struct ggml_tensor * src, struct ggml_tensor * dst) {
+    if (!src->buffer || !buft_is_b200(src->buffer->buft)) return false;
+    b200_buffer_ctx * sctx = (b200_buffer_ctx *) src->buffer->context;
+    b200_buffer_ctx * dctx = (b200_buffer_ctx *) buffer->context;
+    CUDA_OK(cudaSetDevice(dctx->device));
+    if (sctx->device == dctx->device) {
+        CUDA_OK(cudaMemcpyAsync(dst->data, src->data, ggml_nbytes(src), cudaMemcpyDeviceToDevice, cudaStreamPerThread));
+    } else {
+        CUDA_OK(cudaMemcpyPeerAsync(dst->data, dctx->device, src->data, sctx->device, ggml_nbytes(src), cudaStreamPerThread));
+    }
+    CUDA_OK(cudaStreamSynchronize(cudaStreamPerThread));
+    return true;
+}
+static void b200_buffer_clear(ggml_backend_buffer_t buffer, uint8_t value) {
+    b200_buffer_ctx * ctx = (b200_buffer_ctx *) buffer->context;
+    CUDA_OK(cudaSetDevice(ctx->device));
+    CUDA_OK(cudaMemset(ctx->base, value, buffer->size));
+}
+static const struct ggml_backend_buffer_i b200_buffer_iface = {
+    /* .free_buffer   = */ b200_buffer_free,
+    /* .get_base      = */ b200_buffer_get_base,
+    /* .init_tensor   = */ b200_buffer_init_tensor,
+    /* .memset_tensor = */ b200_buffer_memset_tensor,
+    /* .set_tensor    = */ b200_buffer_set_tensor,
+    /* .get_tensor    = */ b200_buffer_get_tensor,
+    /* .cpy_tensor    = */ b200_buffer_cpy_tensor,
+    /* .clear         = */ b200_buffer_clear,
+    /* .reset         = */ NULL,
+};
+
+// ================================================================= device buffer type
+// mirrors ggml_backend_cuda_buffer_type_* (src/ggml-cuda/ggml-cuda.cu:677-761)
+struct b200_buft_ctx {
+    int         device;
+    std::string name;
+};
+static const char * b200_buft_get_name(ggml_backend_buffer_type_t buft) {
+    return ((b200_buft_ctx *) buft->context)->name.c_str();
+}
+static ggml_backend_buffer_t b200_buft_alloc_buffer(ggml_backend_buffer_type_t buft, size_t size) {
+    b200_buft_ctx * bctx = (b200_buft_ctx *) buft->context;
+    if (cudaSetDevice(bctx->device) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    void * base = nullptr;
+    // +256: bulk copies of a row may read up to the next 16-byte boundary past the last tensor
+    cudaError_t e = cudaMalloc(&base, size + 256);
+    if (e != cudaSuccess) {
+        cudaGetLastError();   // recoverable, like the reference (ggml-cuda.cu:693-699)
+        b200_log("allocating %.2f MiB on device %d failed: %s\n", size / 1048576.0, bctx->device, cudaGetErrorString(e));
+        return nullptr;
+    }
+    b200_buffer_ctx * ctx = new b200_buffer_ctx{ bctx->device, base };
+    return ggml_backend_buffer_init(buft, b200_buffer_iface, ctx, size);
+}
+static size_t b200_buft_get_alignment(ggml_backend_buffer_type_t) { return 128; }
+static const struct ggml_backend_buffer_type_i b200_buft_iface = {
+    /* .get_name       = */ b200_buft_get_name,
+    /* .alloc_buffer   = */ b200_buft_alloc_buffer,
+    /* .get_alignment  = */ b200_buft_get_alignment,
+    /* .get_max_size   = */ NULL,
+    /* .get_alloc_size = */ NULL,
+    /* .is_host        = */ NULL,
+};
+static bool buft_is_b200(ggml_backend_buffer_type_t buft) { return buft && buft->iface.get_name == b200_buft_get_name; }
+
+// ================================================================= pinned host buffer type
+// same construction as ggml_backend_cuda_host_buffer_type (src/ggml-cuda/ggml-cuda.cu:1096-1160):
+// a CPU buffer whose memory is page-locked, so set/get_tensor and the scheduler's copies run at
+// full PCIe rate and can be asynchronous.
+static const char * b200_host_buft_get_name(ggml_backend_buffer_type_t) { return "B200_Host"; }
+static void b200_host_buffer_free(ggml_backend_buffer_t buffer) { cudaFreeHost(buffer->context); }
+static ggml_backend_buffer_t b200_host_buft_alloc_buffer(ggml_backend_buffer_type_t buft, size_t size) {
+    void * ptr = nullptr;
+    if (cudaMallocHost(&ptr, size) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    ggml_backend_buffer_t buffer = ggml_backend_cpu_buffer_from_ptr(ptr, size);
+    buffer->buft = buft;
+    buffer->iface.free_buffer = b200_host_buffer_free;
+    return buffer;
+}
+
+// ================================================================= backend (one stream)
+struct graph_key_entry {
+    int op; int type; const void * data;
+    const void * src_data[3]; int src_type[3];
+    int64_t ne[4]; size_t nb[4];
+    int64_t sne[3][4]; size_t snb[3][4];
+    bool operator==(const graph_key_entry & o) const { return memcmp(this, &o, sizeof(*this)) == 0; }
+};
+
+struct b200_backend_ctx {
+    int          device;
+    std::string  name;
+    cudaStream_t stream    = nullptr;
+    void *       ws        = nullptr;
+    size_t       ws_size   = 0;
+    // CUDA-graph replay of repeated graph_compute() calls
+    std::vector<graph_key_entry> last_key;
+    cudaGraphExec_t              exec = nullptr;
+    bool                         exec_valid = false;
+    bool                         graphs_enabled = true;
+    uint64_t                     n_replays = 0, n_captures = 0, n_eager = 0;
+};
+
+static const char * b200_backend_get_name(ggml_backend_t backend) {
+    return ((b200_backend_ctx *) backend->context)->name.c_str();
+}
+static void b200_backend_free(ggml_backend_t backend) {
+    b200_backend_ctx * ctx = (b200_backend_ctx *) backend->context;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    if (ctx->exec) cudaGraphExecDestroy(ctx->exec);
+    if (ctx->ws) cudaFree(ctx->ws);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    delete backend;
+}
+static void b200_backend_set_tensor_async(ggml_backend_t backend, struct ggml_tensor * tensor, const void * data, size_t offset, size_t size) {
+    b200_backend_ctx * ctx = (b200_backend_ctx *) backend->context;
+    CUDA_OK(cudaSetDevice(ctx->device));
+    CUDA_OK(cudaMemcpyAsync((char *) tensor->data + offset, data, size, cudaMemcpyHostToDevice, ctx->stream));
+}
+static void b200_backend_get_tensor_async(ggml_backend_t backend, const struct ggml_tensor * tensor, void * data, size_t offset, size_t size) {
+    b200_backend_ctx * ctx = (b200_backend_ctx *) backend->context;
+    CUDA_OK(cudaSetDevice(ctx->device));
+    CUDA_OK(cudaMemcpyAsync(data, (const char *) tensor->data + offset, size, cudaMemcpyDeviceToHost, ctx->stream));
+}
+static void b200_backend_synchronize(ggml_backend_t backend) {
+    b200_backend_ctx * ctx = (b200_backend_ctx *) backend->context;
+    CUDA_OK(cudaSetDevice(ctx->device));
+    CUDA_OK(cudaStreamSynchronize(ctx->stream));
+}
+
+static bool op_is_noop(const struct ggml_tensor * t) {
+    return ggml_is_empty(t) || t->op == GGML_OP_NONE || t->op == GGML_OP_RESHAPE || t->op == GGML_OP_VIEW ||
+           t->op == GGML_OP_PERMUTE || t->op == GGML_OP_TRANSPOSE;
+}
+
+static size_t node_workspace(const struct ggml_tensor * node) {
+    if (node->op != GGML_OP_MUL_MAT) return 0;
+    return b200_mul_mat_workspace_size((int) node->src[0]->type, node->src[0]->ne, node->src[1]->ne);
+}
+
+// one node -> kernel-library calls on ctx->stream
+static void b200_compute_node(b200_backend_ctx * ctx, struct ggml_tensor * node) {
+    const struct ggml_tensor * s0 = node->src[0];
+    const struct ggml_tensor * s1 = node->src[1];
+    switch (node->op) {
+        case GGML_OP_MUL_MAT:
+            B200_OK_OR_ABORT(b200_mul_mat((int) s0->type, s0->data, s0->ne, s0->nb, (const float *) s1->data, s1->ne, s1->nb,
+                                          (float *) node->data, ctx->ws, ctx->ws_size, ctx->stream));
+            break;
+        case GGML_OP_GET_ROWS: {
+            // dst[:, i10, i11, i12] = dequant(src0[:, rows[i10, i11, i12], i11, i12])  (src/ggml-cpu/ops.cpp:5121-5165)
+            const int out_type = node->type == GGML_TYPE_F32 ? B200_TYPE_F32 : B200_TYPE_F16;
+            for (int64_t i12 = 0; i12 < s1->ne[2]; i12++) for (int64_t i11 = 0; i11 < s1->ne[1]; i11++) {
+                const char * table = (const char *) s0->data + i11 * s0->nb[2] + i12 * s0->nb[3];
+                const char * rows  = (const char *) s1->data + i11 * s1->nb[1] + i12 * s1->nb[2];
+                char * dst = (char *) node->data + i11 * node->nb[2] + i12 * node->nb[3];
+                B200_OK_OR_ABORT(b200_get_rows((int) s0->type, table, s0->nb[1], s0->ne[0], s0->ne[1], (const int32_t *) rows, s1->nb[0],
+                                               s1->ne[0], dst, out_type, node->nb[1], ctx->stream));
+            }
+        } break;
+        case GGML_OP_CPY:
+        case GGML_OP_DUP:
+        case GGML_OP_CONT: {
+            const struct ggml_tensor * dst = node->op == GGML_OP_CPY ? node->src[1] : node;
+            const int out_type = dst->type == GGML_TYPE_F32 ? B200_TYPE_F32 : B200_TYPE_F16;
+            B200_OK_OR_ABORT(b200_dequantize_4d((int) s0->type, s0->data, s0->ne, s0->nb, dst->data, out_type, dst->ne, dst->nb, ctx->stream));
+        } break;
+        default:
+            b200_log("graph_compute: op %s was never claimed by supports_op\n", ggml_op_name(node->op));
+            GGML_ABORT("ggml-b200: unsupported op");
+    }
+}
+
+static void make_key(struct ggml_cgraph * cgraph, std::vector<graph_key_entry> & key) {
+    const int n = ggml_graph_n_nodes(cgraph);
+    key.clear();
+    key.reserve(n);
+    for (int i = 0; i < n; i++) {
+        const struct ggml_tensor * t = ggml_graph_node(cgraph, i);
+        graph_key_entry e;
+        memset(&e, 0, sizeof(e));
+        e.op = (int) t->op; e.type = (int) t->type; e.data = t->data;
+        for (int d = 0; d < 4; d++) { e.ne[d] = t->ne[d]; e.nb[d] = t->nb[d]; }
+        for (int s = 0; s < 3; s++) {
+            const struct ggml_tensor * src = t->src[s];
+            if (!src) continue;
+            e.src_data[s] = src->data; e.src_type[s] = (int) src->type;
+            for (int d = 0; d < 4; d++) { e.sne[s][d] = src->ne[d]; e.snb[s][d] = src->nb[d]; }
+        }
+        key.push_back(e);
+    }
+}
+
+static enum ggml_status b200_backend_graph_compute(ggml_backend_t backend, struct ggml_cgraph * cgraph) {
+    b200_backend_ctx * ctx = (b200_backend_ctx *) backend->context;
+    CUDA_OK(cudaSetDevice(ctx->device));
+    const int n = ggml_graph_n_nodes(cgraph);
+
+    // size the workspace before anything is launched (no allocation inside a capture)
+    size_t need = 0;
+    int n_work = 0;
+    for (int i = 0; i < n; i++) {
+        struct ggml_tensor * node = ggml_graph_node(cgraph, i);
+        if (op_is_noop(node)) continue;
+        n_work++;
+        const size_t w = node_workspace(node);
+        if (w > need) need = w;
+    }
+    if (need > ctx->ws_size) {
+        CUDA_OK(cudaStreamSynchronize(ctx->stream));
+        if (ctx->ws) CUDA_OK(cudaFree(ctx->ws));
+        ctx->ws_size = need + (need >> 2) + (1u << 20);
+        CUDA_OK(cudaMalloc(&ctx->ws, ctx->ws_size));
+        ctx->exec_valid = false;     // captured launches hold the old pointer
+        ctx->last_key.clear();
+    }
+
+    // Replay policy: a graph seen twice in a row (same ops, shapes, strides, data pointers) is captured
+    // on its second appearance and replayed from the third on.  Single-node graphs (test-backend-ops)
+    // never pay for a capture.
+    bool use_graph = false, capture = false;
+    if (ctx->graphs_enabled && n_work >= 4) {
+        std::vector<graph_key_entry> key;
+        make_key(cgraph, key);
+        if (key == ctx->last_key) {
+            use_graph = true;
+            capture = !ctx->exec_valid;
+        } else {
+            ctx->last_key.swap(key);
+            ctx->exec_valid = false;
+        }
+    }
+    if (use_graph && !capture) {
+        CUDA_OK(cudaGraphLaunch(ctx->exec, ctx->stream));
+        ctx->n_replays++;
+        return GGML_STATUS_SUCCESS;
+    }
+    if (capture) CUDA_OK(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeRelaxed));
+    for (int i = 0; i < n; i++) {
+        struct ggml_tensor * node = ggml_graph_node(cgraph, i);
+        if (op_is_noop(node)) continue;
+        b200_compute_node(ctx, node);
+    }
+    if (capture) {
+        cudaGraph_t graph = nullptr;
+        CUDA_OK(cudaStreamEndCapture(ctx->stream, &graph));
+        if (ctx->exec) { cudaGraphExecDestroy(ctx->exec); ctx->exec = nullptr; }
+        CUDA_OK(cudaGraphInstantiate(&ctx->exec, graph, 0));
+        CUDA_OK(cudaGraphDestroy(graph));
+        ctx->exec_valid = true;
+        ctx->n_captures++;
+        CUDA_OK(cudaGraphLaunch(ctx->exec, ctx->stream));
+    } else {
+        ctx->n_eager++;
+    }
+    return GGML_STATUS_SUCCESS;
+}
+
+static void b200_backend_event_record(ggml_backend_t backend, ggml_backend_event_t event) {
+    b200_backend_ctx * ctx = (b200_backend_ctx *) backend->context;
+    CUDA_OK(cudaEventRecord((cudaEvent_t) event->context, ctx->stream));
+}
+static void b200_backend_event_wait(ggml_backend_t backend, ggml_backend_event_t event) {
+    b200_backend_ctx * ctx = (b200_backend_ctx *) backend->context;
+    CUDA_OK(cudaStreamWaitEvent(ctx->stream, (cudaEvent_t) event->context, 0));
+}
+
+static bool b200_backend_cpy_tensor_async(ggml_backend_t backend_src, ggml_backend_t backend_dst, const struct ggml_tensor * src, struct ggml_tensor * dst);
+
+static const struct ggml_backend_i b200_backend_iface = {
+    /* .get_name           = */ b200_backend_get_name,
+    /* .free               = */ b200_backend_free,
+    /* .set_tensor_async   = */ b200_backend_set_tensor_async,
+    /* .get_tensor_async   = */ b200_backend_get_tensor_async,
+    /* .cpy_tensor_async   = */ b200_backend_cpy_tensor_async,
+    /* .synchronize        = */ b200_backend_synchronize,
+    /* .graph_plan_create  = */ NULL,
+    /* .graph_plan_free    = */ NULL,
+    /* .graph_plan_update  = */ NULL,
+    /* .graph_plan_compute = */ NULL,
+    /* .graph_compute      = */ b200_backend_graph_compute,
+    /* .event_record       = */ b200_backend_event_record,
+    /* .event_wait         = */ b200_backend_event_wait,
+};
+
+static ggml_guid_t b200_guid(void) {
+    static ggml_guid guid = { 0xb2, 0x00, 0x51, 0x00, 0xa1, 0x7c, 0x4d, 0x05, 0x9e, 0x11, 0x67, 0x67, 0x6d, 0x6c, 0xb2, 0x00 };
+    return &guid;
+}
+
+static bool b200_backend_cpy_tensor_async(ggml_backend_t backend_src, ggml_backend_t backend_dst, const struct ggml_tensor * src, struct ggml_tensor * dst) {
+    // same-device copies between two b200 backends only; anything else goes through the generic path
+    if (!ggml_guid_matches(backend_src->guid, b200_guid()) || !ggml_guid_matches(backend_dst->guid, b200_guid())) return false;
+    if (!src->buffer || !dst->buffer || !buft_is_b200(src->buffer->buft) || !buft_is_b200(dst->buffer->buft)) return false;
+    b200_backend_ctx * sctx = (b200_backend_ctx *) backend_src->context;
+    b200_backend_ctx * dctx = (b200_backend_ctx *) backend_dst->context;
+    if (sctx->device != dctx->device || backend_src != backend_dst) return false;
+    CUDA_OK(cudaMemcpyAsync(dst->data, src->data, ggml_nbytes(dst), cudaMemcpyDeviceToDevice, sctx->stream));
+    return true;
+}
+
+// ================================================================= device
+// mirrors ggml_backend_cuda_device_* (src/ggml-cuda/ggml-cuda.cu:3153-3652)
+static const char * b200_dev_get_name(ggml_backend_dev_t dev) { return ((b200_device_ctx *) dev->context)->name.c_str(); }
+static const char * b200_dev_get_description(ggml_backend_dev_t dev) { return ((b200_device_ctx *) dev->context)->description.c_str(); }
+static void b200_dev_get_memory(ggml_backend_dev_t dev, size_t * free, size_t * total) {
+    b200_device_ctx * ctx = (b200_device_ctx *) dev->context;
+    if (b200_device_info(ctx->device, nullptr, 0, free, total, nullptr, nullptr) != 0) { *free = 0; *total = 0; }
+}
+static enum ggml_backend_dev_type b200_dev_get_type(ggml_backend_dev_t) { return GGML_BACKEND_DEVICE_TYPE_GPU; }
+
+static ggml_backend_buffer_type_t b200_host_buffer_type(void);
+
+static void b200_dev_get_props(ggml_backend_dev_t dev, struct ggml_backend_dev_props * props) {
+    props->name        = b200_dev_get_name(dev);
+    props->description = b200_dev_get_description(dev);
+    props->type        = GGML_BACKEND_DEVICE_TYPE_GPU;
+    b200_dev_get_memory(dev, &props->memory_free, &props->memory_total);
+    props->caps.async                = true;
+    props->caps.host_buffer          = true;
+    props->caps.buffer_from_host_ptr = false;
+    props->caps.events               = true;
+}
+
+static ggml_backend_t b200_dev_init_backend(ggml_backend_dev_t dev, const char *) {
+    b200_device_ctx * dctx = (b200_device_ctx *) dev->context;
+    if (cudaSetDevice(dctx->device) != cudaSuccess) {
+        cudaGetLastError();
+        b200_log("cannot select device %d\n", dctx->device);
+        return nullptr;
+    }
+    b200_backend_ctx * ctx = new b200_backend_ctx();
+    ctx->device = dctx->device;
+    ctx->name   = dctx->name;
+    const char * g = getenv("GGML_B200_DISABLE_GRAPHS");
+    ctx->graphs_enabled = !(g && *g && *g != '0');
+    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        cudaGetLastError();
+        delete ctx;
+        return nullptr;
+    }
+    ggml_backend_t backend = new ggml_backend{
+        /* .guid    = */ b200_guid(),
+        /* .iface   = */ b200_backend_iface,
+        /* .device  = */ dev,
+        /* .context = */ ctx,
+    };
+    return backend;
+}
+
+static ggml_backend_buffer_type_t b200_dev_get_buffer_type(ggml_backend_dev_t dev) {
+    return b200_buffer_type(((b200_device_ctx *) dev->context)->device);
+}
+static ggml_backend_buffer_type_t b200_dev_get_host_buffer_type(ggml_backend_dev_t) { return b200_host_buffer_type(); }
+
+static bool tensor_on_other_device(const struct ggml_tensor * t, int device) {
+    if (!t || !t->buffer || !buft_is_b200(t->buffer->buft)) return false;
+    return ((b200_buffer_ctx *) t->buffer->context)->device != device;
+}
+
+// The claim list.  Cheap, pure and thread-safe: it is called for every tensor (leafs included) by
+// test-backend-ops (tests/test-backend-ops.cpp:1106-1115) and per node x backend by the scheduler.
+static bool b200_dev_supports_op(ggml_backend_dev_t dev, const struct ggml_tensor * op) {
+    const int device = ((b200_device_ctx *) dev->context)->device;
+    for (int i = 0; i < GGML_MAX_SRC; i++) {
+        if (tensor_on_other_device(op->src[i], device)) return false;
+    }
+    const struct ggml_tensor * s0 = op->src[0];
+    const struct ggml_tensor * s1 = op->src[1];
+    switch (op->op) {
+        case GGML_OP_NONE:
+        case GGML_OP_RESHAPE:
+        case GGML_OP_VIEW:
+        case GGML_OP_PERMUTE:
+        case GGML_OP_TRANSPOSE:
+            return true;
+        case GGML_OP_MUL_MAT:
+            return s0 && s1 && is_hot_quant(s0->type) && s1->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 &&
+                   s0->nb[0] == ggml_type_size(s0->type) && s1->nb[0] == sizeof(float) && ggml_is_contiguous(op) &&
+                   s0->ne[2] > 0 && s0->ne[3] > 0 && s1->ne[2] % s0->ne[2] == 0 && s1->ne[3] % s0->ne[3] == 0 &&
+                   s1->ne[2] <= 65535 && s1->ne[3] <= 65535;
+        case GGML_OP_GET_ROWS:
+            return s0 && s1 && is_hot_quant(s0->type) && s1->type == GGML_TYPE_I32 && op->type == GGML_TYPE_F32 &&
+                   s0->nb[0] == ggml_type_size(s0->type) && op->nb[0] == sizeof(float) && s1->ne[3] == 1;
+        case GGML_OP_CPY:
+        case GGML_OP_DUP:
+        case GGML_OP_CONT: {
+            const struct ggml_tensor * dst = op->op == GGML_OP_CPY ? s1 : op;
+            return s0 && dst && is_hot_quant(s0->type) && (dst->type == GGML_TYPE_F32 || dst->type == GGML_TYPE_F16) &&
+                   s0->nb[0] == ggml_type_size(s0->type) && ggml_nelements(s0) == ggml_nelements(dst);
+        }
+        default:
+            return false;
+    }
+}
+
+static bool b200_dev_supports_buft(ggml_backend_dev_t dev, ggml_backend_buffer_type_t buft) {
+    if (!buft_is_b200(buft)) return false;
+    return ((b200_buft_ctx *) buft->context)->device == ((b200_device_ctx *) dev->context)->device;
+}
+
+// offload weights that live in host memory when the batch is large enough to amortise the copy
+// (the reference's rule: batch >= 32, src/ggml-cuda/ggml-cuda.cu:3583-3604)
+static bool b200_dev_offload_op(ggml_backend_dev_t, const struct ggml_tensor * op) {
+    return op->op == GGML_OP_MUL_MAT && op->ne[1] >= 32;
+}
+
+static ggml_backend_event_t b200_dev_event_new(ggml_backend_dev_t dev) {
+    b200_device_ctx * ctx = (b200_device_ctx *) dev->context;
+    CUDA_OK(cudaSetDevice(ctx->device));
+    cudaEvent_t ev;
+    CUDA_OK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    return new ggml_backend_event{ /* .device = */ dev, /* .context = */ ev };
+}
+static void b200_dev_event_free(ggml_backend_dev_t, ggml_backend_event_t event) {
+    cudaEventDestroy((cudaEvent_t) event->context);
+    delete event;
+}
+static void b200_dev_event_synchronize(ggml_backend_dev_t, ggml_backend_event_t event) {
+    CUDA_OK(cudaEventSynchronize((cudaEvent_t) event->context));
+}
+
+static const struct ggml_backend_device_i b200_device_iface = {
+    /* .get_name             = */ b200_dev_get_name,
+    /* .get_description      = */ b200_dev_get_description,
+    /* .get_memory           = */ b200_dev_get_memory,
+    /* .get_type             = */ b200_dev_get_type,
+    /* .get_props            = */ b200_dev_get_props,
+    /* .init_backend         = */ b200_dev_init_backend,
+    /* .get_buffer_type      = */ b200_dev_get_buffer_type,
+    /* .get_host_buffer_type = */ b200_dev_get_host_buffer_type,
+    /* .buffer_from_host_ptr = */ NULL,
+    /* .supports_op          = */ b200_dev_supports_op,
+    /* .supports_buft        = */ b200_dev_supports_buft,
+    /* .offload_op           = */ b200_dev_offload_op,
+    /* .event_new            = */ b200_dev_event_new,
+    /* .event_free           = */ b200_dev_event_free,
+    /* .event_synchronize    = */ b200_dev_event_synchronize,
+};
+
+// ================================================================= registry + singletons
+struct b200_reg_ctx {
+    std::vector<ggml_backend_dev_t> devices;
+};
+
+static const char * b200_reg_get_name(ggml_backend_reg_t) { return "B200"; }
+static size_t b200_reg_get_device_count(ggml_backend_reg_t reg) { return ((b200_reg_ctx *) reg->context)->devices.size(); }
+static ggml_backend_dev_t b200_reg_get_device(ggml_backend_reg_t reg, size_t index) {
+    b200_reg_ctx * ctx = (b200_reg_ctx *) reg->context;
+    GGML_ASSERT(index < ctx->devices.size());
+    return ctx->devices[index];
+}
+
+static struct ggml_backend_feature * b200_get_features(ggml_backend_reg_t) {
+    static struct ggml_backend_feature features[] = {
+        { "ARCH", "sm_100a" }, { "TMA_MMVQ", "1" }, { "TCGEN05_MMQ", "1" }, { "CUDA_GRAPHS", "1" }, { nullptr, nullptr },
+    };
+    return features;
+}
+
+static void * b200_reg_get_proc_address(ggml_backend_reg_t, const char * name) {
+    if (strcmp(name, "ggml_backend_split_buffer_type") == 0) return (void *) ggml_backend_b200_split_buffer_type;
+    if (strcmp(name, "ggml_backend_get_features") == 0) return (void *) b200_get_features;
+    return nullptr;
+}
+
+static const struct ggml_backend_reg_i b200_reg_iface = {
+    /* .get_name         = */ b200_reg_get_name,
+    /* .get_device_count = */ b200_reg_get_device_count,
+    /* .get_device       = */ b200_reg_get_device,
+    /* .get_proc_address = */ b200_reg_get_proc_address,
+};
+
+ggml_backend_reg_t ggml_backend_b200_reg(void) {
+    static ggml_backend_reg reg;
+    static bool initialized = false;
+    static std::mutex mutex;
+    std::lock_guard<std::mutex> lock(mutex);
+    if (!initialized) {
+        b200_reg_ctx * ctx = new b200_reg_ctx;
+        const int n = b200_device_count();
+        for (int i = 0; i < n && i < B200_MAX_DEVICES; i++) {
+            char name[256] = { 0 };
+            b200_device_info(i, name, sizeof(name), nullptr, nullptr, nullptr, nullptr);
+            b200_device_ctx * dctx = new b200_device_ctx{ i, "B200_" + std::to_string(i), name };
+            ctx->devices.push_back(new ggml_backend_device{ /* .iface = */ b200_device_iface, /* .reg = */ &reg, /* .context = */ dctx });
+        }
+        reg = ggml_backend_reg{ /* .api_version = */ GGML_BACKEND_API_VERSION, /* .iface = */ b200_reg_iface, /* .context = */ ctx };
+        initialized = true;
+    }
+    return &reg;
+}
+
+static ggml_backend_buffer_type_t b200_buffer_type(int device) {
+    static struct ggml_backend_buffer_type bufts[B200_MAX_DEVICES];
+    static bool initialized = false;
+    static std::mutex mutex;
+    std::lock_guard<std::mutex> lock(mutex);
+    if (device < 0 || device >= B200_MAX_DEVICES) return nullptr;
+    if (!initialized) {
+        ggml_backend_reg_t reg = ggml_backend_b200_reg();
+        const int n = (int) b200_reg_get_device_count(reg);
+        for (int i = 0; i < B200_MAX_DEVICES; i++) {
+            bufts[i] = ggml_backend_buffer_type{
+                /* .iface   = */ b200_buft_iface,
+                /* .device  = */ i < n ? b200_reg_get_device(reg, i) : nullptr,
+                /* .context = */ new b200_buft_ctx{ i, "B200_" + std::to_string(i) },
+            };
+        }
+        initialized = true;
+    }
+    return &bufts[device];
+}
+
+static ggml_backend_buffer_type_t b200_host_buffer_type(void) {
+    static struct ggml_backend_buffer_type buft;
+    static bool initialized = false;
+    static std::mutex mutex;
+    std::lock_guard<std::mutex> lock(mutex);
+    if (!initialized) {
+        ggml_backend_reg_t reg = ggml_backend_b200_reg();
+        buft.iface = ggml_backend_cpu_buffer_type()->iface;     // is_host = true, alignment, alloc size as CPU
+        buft.iface.get_name     = b200_host_buft_get_name;
+        buft.iface.alloc_buffer = b200_host_buft_alloc_buffer;
+        buft.device  = b200_reg_get_device_count(reg) > 0 ? b200_reg_get_device(reg, 0) : nullptr;
+        buft.context = nullptr;
+        initialized = true;
+    }
+    return &buft;
+}
+
+// ================================================================= exported C surface
+extern "C" {
+
+ggml_backend_reg_t ggml_backend_init(void) { return ggml_backend_b200_reg(); }
+int ggml_backend_score(void) { return b200_device_count() > 0 ? 100 : 0; }
+
+ggml_backend_t ggml_backend_b200_init(int device) {
+    ggml_backend_reg_t reg = ggml_backend_b200_reg();
+    if (device < 0 || (size_t) device >= b200_reg_get_device_count(reg)) {
+        b200_log("invalid device %d\n", device);
+        return nullptr;
+    }
+    return b200_dev_init_backend(b200_reg_get_device(reg, device), nullptr);
+}
+int ggml_backend_is_b200(ggml_backend_t backend) { return backend != nullptr && ggml_guid_matches(backend->guid, b200_guid()); }
+ggml_backend_buffer_type_t ggml_backend_b200_buffer_type(int device) { return b200_buffer_type(device); }
+ggml_backend_buffer_type_t ggml_backend_b200_host_buffer_type(void) { return b200_host_buffer_type(); }
+int  ggml_backend_b200_get_device_count(void) { return b200_device_count(); }
+void ggml_backend_b200_get_device_description(int device, char * description, size_t description_size) {
+    if (b200_device_info(device, description, description_size, nullptr, nullptr, nullptr, nullptr) != 0 && description_size) description[0] = 0;
+}
+void ggml_backend_b200_get_device_memory(int device, size_t * free_bytes, size_t * total_bytes) {
+    if (b200_device_info(device, nullptr, 0, free_bytes, total_bytes, nullptr, nullptr) != 0) { *free_bytes = 0; *total_bytes = 0; }
+}
+
+} // extern "C"
+
+#include "plugin_split.inc"

@@ -1,0 +1,109 @@
+// quantize.cu — f32 activations -> q8_1 (32 values: d = amax/127, q = round(x/d), s = d*sum(q)).
+//
+// Value contract: quantize_row_q8_1_ref (reference src/ggml-quants.c:225-258), bit-exact:
+//   d  = amax / 127.0f            (IEEE division)
+//   id = d ? 1.0f / d : 0.0f      (IEEE division)
+//   q  = roundf(x * id)           (half away from zero)
+//   block.d = fp16(d), block.s = fp16((float)sum(q) * d)     (d unrounded f32)
+// Two output forms share the arithmetic:
+//   * block_q8_1 (36 B) — the public, checkable form (b200_quantize_row_q8_1);
+//   * planar scratch for the matvec: int8 plane [n][k] (16-byte loadable) + f32 plane of the
+//     fp16-rounded d per 32 (b200_quantize_acts).  s is not stored: the matvec takes integer sums.
+//
+// One warp per 32-value block (lane = element): max by shuffle, sum by shuffle.  Activation
+// quantization is latency-, not bandwidth-bound (k=4096: 16 KiB in, 4.6 KiB out).
+#include "common.cuh"
+
+namespace b200 {
+
+struct q8_result { int q; float d; int sum; };
+
+__device__ __forceinline__ q8_result quantize32(float x) {
+    const float amax = warp_max(fabsf(x));
+    const float d  = __fdiv_rn(amax, 127.0f);
+    const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+    const int   q  = (int) roundf(__fmul_rn(x, id));
+    int sum = q;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xFFFFFFFFu, sum, o);
+    return { q, d, sum };
+}
+
+// grid (ceil(k/32 / 8), n), block 256 = 8 warps = 8 blocks of 32
+__global__ void __launch_bounds__(256) k_quantize_q8_1(const uint8_t * __restrict__ x, int64_t x_row_stride, int64_t k,
+                                                       uint8_t * __restrict__ y) {
+    const int64_t kb = (int64_t) blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (kb * 32 >= k) return;
+    const int64_t row = blockIdx.y;
+    const float v = reinterpret_cast<const float *>(x + row * x_row_stride)[kb * 32 + lane];
+    const q8_result r = quantize32(v);
+    uint8_t * b = y + (row * (k / 32) + kb) * 36;
+    b[4 + lane] = (uint8_t) (int8_t) r.q;
+    if (lane == 0) {
+        const __half hd = __float2half_rn(r.d);
+        const __half hs = __float2half_rn(__fmul_rn((float) r.sum, r.d));
+        *reinterpret_cast<__half2 *>(b) = __halves2half2(hd, hs);   // blocks are 4-byte aligned (36 B)
+    }
+}
+
+__global__ void __launch_bounds__(256) k_quantize_acts(const uint8_t * __restrict__ x, int64_t x_row_stride, int64_t k, int64_t n,
+                                                       int8_t * __restrict__ q, float * __restrict__ dd) {
+    const int64_t kb = (int64_t) blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (kb * 32 >= k) return;
+    const int64_t row = blockIdx.y;
+    const float v = reinterpret_cast<const float *>(x + row * x_row_stride)[kb * 32 + lane];
+    const q8_result r = quantize32(v);
+    q[row * k + kb * 32 + lane] = (int8_t) r.q;
+    if (lane == 0) dd[row * (k / 32) + kb] = __half2float(__float2half_rn(r.d));
+}
+
+} // namespace b200
+
+using namespace b200;
+
+int b200::b200_quantize_acts_planes(const float * x_dev, size_t x_row_stride_bytes, int64_t k, int64_t n,
+                                    int8_t * q, float * dd, cudaStream_t st) {
+    for (int64_t r0 = 0; r0 < n; r0 += 65535) {
+        const int64_t nr = n - r0 < 65535 ? n - r0 : 65535;
+        const dim3 grid((unsigned) ceil_div(k / 32, 8), (unsigned) nr);
+        k_quantize_acts<<<grid, 256, 0, st>>>((const uint8_t *) x_dev + r0 * x_row_stride_bytes, (int64_t) x_row_stride_bytes, k, n,
+                                              q + r0 * k, dd + r0 * (k / 32));
+        b200_count_launch(1);
+    }
+    B200_RETURN_IF_LAUNCH_FAILED();
+    return B200_OK;
+}
+
+extern "C" int b200_quantize_row_q8_1(const float * x_dev, size_t x_row_stride_bytes, int64_t k, int64_t n, void * y_dev, void * stream) {
+    if (k < 0 || n < 0 || k % 32 != 0) return B200_ERR_SHAPE;
+    if (x_row_stride_bytes % 4 != 0) return B200_ERR_STRIDE;
+    if (k == 0 || n == 0) return B200_OK;
+    for (int64_t r0 = 0; r0 < n; r0 += 65535) {
+        const int64_t nr = n - r0 < 65535 ? n - r0 : 65535;
+        const dim3 grid((unsigned) ceil_div(k / 32, 8), (unsigned) nr);
+        k_quantize_q8_1<<<grid, 256, 0, (cudaStream_t) stream>>>((const uint8_t *) x_dev + r0 * x_row_stride_bytes, (int64_t) x_row_stride_bytes, k,
+                                                                (uint8_t *) y_dev + r0 * (k / 32) * 36);
+        b200_count_launch(1);
+    }
+    B200_RETURN_IF_LAUNCH_FAILED();
+    return B200_OK;
+}
+
+extern "C" size_t b200_acts_scratch_bytes(int64_t k, int64_t n) {
+    if (k <= 0 || n <= 0) return 0;
+    const size_t qbytes = ((size_t) n * (size_t) k + 255) / 256 * 256;
+    return qbytes + (size_t) n * (size_t) (k / 32) * sizeof(float);
+}
+
+extern "C" int b200_quantize_acts(const float * x_dev, size_t x_row_stride_bytes, int64_t k, int64_t n, void * scratch_dev, void * stream) {
+    if (k < 0 || n < 0 || k % 32 != 0) return B200_ERR_SHAPE;
+    if (x_row_stride_bytes % 4 != 0) return B200_ERR_STRIDE;
+    if (k == 0 || n == 0) return B200_OK;
+    if (!scratch_dev) return B200_ERR_WORKSPACE;
+    const size_t qbytes = ((size_t) n * (size_t) k + 255) / 256 * 256;
+    int8_t * q  = (int8_t *) scratch_dev;
+    float  * dd = (float *) ((uint8_t *) scratch_dev + qbytes);
+    return b200_quantize_acts_planes(x_dev, x_row_stride_bytes, k, n, q, dd, (cudaStream_t) stream);
+}

@@ -1,0 +1,146 @@
+/*
+ * ggml_b200.h — the C ABI of libggml_b200_kernels.so: hand-written sm_100a CUDA for ggml's
+ * quantized hot path (Q4_0 / Q8_0 / Q4_K / Q5_K / Q6_K dequantization, q8_1 activation
+ * quantization, GET_ROWS, MUL_MAT).  Plain pointers and sizes only; every pointer named *_dev is a
+ * device pointer on the current CUDA device; `stream` is a cudaStream_t passed as void* (NULL =
+ * default stream).  All calls are asynchronous on `stream` unless stated otherwise.
+ *
+ * Return value: 0 on success, B200_ERR_* (> 0) for argument errors, -(cudaError_t) for CUDA errors.
+ * There is no CPU fallback anywhere behind this ABI: without a usable device the calls fail.
+ *
+ * Each entry point names the reference interface it replaces (paths relative to the reference
+ * tree skyne98/ggml-gfx906).  Tensor conventions are ggml's (include/ggml.h:614-646): ne[] are
+ * extents in elements, nb[] are strides in BYTES, dimension 0 is the contiguous one.
+ */
+#ifndef GGML_B200_H
+#define GGML_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define B200_API __declspec(dllexport)
+#else
+#define B200_API __attribute__((visibility("default")))
+#endif
+
+/* type ids = the numeric values of enum ggml_type (include/ggml.h:376-410) */
+enum b200_type {
+    B200_TYPE_F32  = 0,
+    B200_TYPE_F16  = 1,
+    B200_TYPE_Q4_0 = 2,
+    B200_TYPE_Q8_0 = 8,
+    B200_TYPE_Q8_1 = 9,
+    B200_TYPE_Q4_K = 12,
+    B200_TYPE_Q5_K = 13,
+    B200_TYPE_Q6_K = 14,
+    B200_TYPE_I32  = 26,
+    B200_TYPE_BF16 = 30,
+};
+
+enum b200_error {
+    B200_OK              = 0,
+    B200_ERR_TYPE        = 1, /* type not one of the five weight formats / unsupported output type */
+    B200_ERR_SHAPE       = 2, /* k not a multiple of the block size, negative extents, bad broadcast */
+    B200_ERR_STRIDE      = 3, /* dimension 0 not contiguous, or misaligned strides */
+    B200_ERR_WORKSPACE   = 4, /* workspace too small / NULL */
+    B200_ERR_NO_DEVICE   = 5, /* no sm_100 device visible */
+};
+
+/* ---- library / device ---------------------------------------------------------------------
+ * replaces ggml_backend_cuda_get_device_count / _get_device_description / _get_device_memory
+ * (include/ggml-cuda.h:36-40) and the arch probe in ggml_cuda_init (src/ggml-cuda/ggml-cuda.cu:196-306). */
+B200_API int          b200_abi_version(void);
+B200_API const char * b200_error_string(int code);
+B200_API int          b200_device_count(void);                 /* devices with compute capability 10.x */
+B200_API int          b200_device_info(int device, char * name, size_t name_len,
+                                       size_t * free_bytes, size_t * total_bytes, int * sm_count, int * cc);
+
+/* ---- format table -------------------------------------------------------------------------
+ * replaces ggml_blck_size / ggml_type_size / ggml_row_size for the hot-path types (include/ggml.h:716-721) */
+B200_API int    b200_block_elems(int type);
+B200_API size_t b200_block_bytes(int type);
+B200_API size_t b200_row_bytes(int type, int64_t k);
+
+/* ---- dequantize_row_* ----------------------------------------------------------------------
+ * replaces to_fp32_cuda_t / to_fp16_cuda_t from ggml_get_to_fp32_cuda / ggml_get_to_fp16_cuda
+ * (src/ggml-cuda/convert.cu:661-764); values bit-exact with dequantize_row_<type>
+ * (src/ggml-quants.c:307-325, 401-415, 1352-1374, 1554-1579, 1762-1791) and, for f16 output,
+ * with the RN-even narrowing of those f32 values.
+ * x_dev: n_elems/QK contiguous blocks.  out_type: B200_TYPE_F32 or B200_TYPE_F16. */
+B200_API int b200_dequantize_row(int type, const void * x_dev, void * y_dev, int64_t n_elems,
+                                 int out_type, void * stream);
+
+/* Strided 4-D form: CPY / DUP / CONT of a quantized tensor into an f32/f16 tensor.
+ * replaces ggml_cuda_cpy for q -> f32 (src/ggml-cuda/cpy.cu:53-64, 94-121, 185-196) and the _nc_
+ * converters (src/ggml-cuda/convert.cu:766-827).  src rows (dim 0) must be contiguous blocks;
+ * dst element (i0,i1,i2,i3) is written at byte offset i0*nb_dst[0]+..+i3*nb_dst[3]; the logical
+ * element order of src and dst is the same (ggml CPY semantics, shapes may differ as long as the
+ * element counts match and ne_dst[0] % 8 == 0 or ne_src == ne_dst). */
+B200_API int b200_dequantize_4d(int type, const void * x_dev, const int64_t ne_src[4], const size_t nb_src[4],
+                                void * y_dev, int out_type, const int64_t ne_dst[4], const size_t nb_dst[4],
+                                void * stream);
+
+/* ---- quantize_row_q8_1 ---------------------------------------------------------------------
+ * replaces quantize_row_q8_1_cuda (src/ggml-cuda/quantize.cu:145-157) with the value contract of
+ * quantize_row_q8_1_ref (src/ggml-quants.c:225-258): bit-exact block_q8_1 output.
+ * x_dev: n rows of k floats, row stride x_row_stride_bytes; y_dev: n * k/32 block_q8_1, rows packed. */
+B200_API int b200_quantize_row_q8_1(const float * x_dev, size_t x_row_stride_bytes, int64_t k, int64_t n,
+                                    void * y_dev, void * stream);
+
+/* ---- GET_ROWS ------------------------------------------------------------------------------
+ * replaces ggml_cuda_op_get_rows / get_rows_cuda_q (src/ggml-cuda/getrows.cu:93-124, 236-253) and
+ * extends it to the K-quants, which the reference serves only on the CPU
+ * (src/ggml-cpu/ops.cpp:5121-5165).  dst[i, :] = dequant(table[rows[i], :]).
+ * rows_dev: n_rows int32 indices, consecutive indices rows_stride_bytes apart. */
+B200_API int b200_get_rows(int type, const void * table_dev, size_t table_row_stride_bytes, int64_t k,
+                           int64_t table_rows, const int32_t * rows_dev, size_t rows_stride_bytes, int64_t n_rows,
+                           void * dst_dev, int out_type, size_t dst_row_stride_bytes, void * stream);
+
+/* ---- MUL_MAT -------------------------------------------------------------------------------
+ * dst[m, n] = W[m, k] (quantized rows) x X[n, k]^T (f32), ggml_mul_mat semantics
+ * (include/ggml.h:1287-1293): dst column j (token j) is contiguous over m.
+ *
+ * b200_mul_mat replaces the dispatcher ggml_cuda_mul_mat (src/ggml-cuda/ggml-cuda.cu:2007-2090):
+ *   n <= B200_MMVQ_MAX_N  -> quantize activations to q8_1 + dp4a matvec
+ *                            (ggml_cuda_mul_mat_vec_q, src/ggml-cuda/mmvq.cu:500-570)
+ *   larger n              -> tensor-core tile kernel (ggml_cuda_mul_mat_q, src/ggml-cuda/mmq.cu:71-143)
+ * with ggml's 4-D broadcast rules: ne_b[2] % ne_a[2] == 0, ne_b[3] % ne_a[3] == 0; dims 1..3 of
+ * a and b may be permuted/strided (nb arbitrary), dim 0 contiguous; dst is contiguous
+ * [ne_a[1], ne_b[1], ne_b[2], ne_b[3]] f32.
+ * workspace_dev: at least b200_mul_mat_workspace_size(...) bytes, 256-byte aligned. */
+#define B200_MMVQ_MAX_N 8
+
+B200_API size_t b200_mul_mat_workspace_size(int type_a, const int64_t ne_a[4], const int64_t ne_b[4]);
+B200_API int    b200_mul_mat(int type_a, const void * a_dev, const int64_t ne_a[4], const size_t nb_a[4],
+                             const float * b_dev, const int64_t ne_b[4], const size_t nb_b[4],
+                             float * dst_dev, void * workspace_dev, size_t workspace_bytes, void * stream);
+
+/* The two legs separately (2-D, for tests and benches).
+ * b200_quantize_acts: f32 [n, k] -> the planar q8 scratch the matvec consumes (same values as
+ *   quantize_row_q8_1: int8 plane [n][k] followed by the per-32 scales d as f32 [n][k/32]).
+ * b200_mul_mat_vec_q: the matvec proper on that scratch, n <= B200_MMVQ_MAX_N.
+ * b200_mul_mat_q: the batched path, any n >= 1 (activations f32, converted inside). */
+B200_API size_t b200_acts_scratch_bytes(int64_t k, int64_t n);
+B200_API int    b200_quantize_acts(const float * x_dev, size_t x_row_stride_bytes, int64_t k, int64_t n,
+                                   void * scratch_dev, void * stream);
+B200_API int    b200_mul_mat_vec_q(int type, const void * w_dev, size_t w_row_stride_bytes, int64_t m, int64_t k,
+                                   const void * acts_scratch_dev, int64_t n,
+                                   float * dst_dev, size_t dst_col_stride_bytes, void * stream);
+B200_API size_t b200_mul_mat_q_workspace_size(int64_t m, int64_t k, int64_t n);
+B200_API int    b200_mul_mat_q(int type, const void * w_dev, size_t w_row_stride_bytes, int64_t m, int64_t k,
+                               const float * x_dev, size_t x_row_stride_bytes, int64_t n,
+                               float * dst_dev, size_t dst_col_stride_bytes,
+                               void * workspace_dev, size_t workspace_bytes, void * stream);
+
+/* Number of kernels this library has launched since load (bench.py's gpu_launches). */
+B200_API uint64_t b200_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GGML_B200_H */
