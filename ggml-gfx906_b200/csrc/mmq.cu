@@ -1,8 +1,141 @@
+// mmq.cu — host side of the batched tensor-core MUL_MAT (kernel: mmq_tc.cuh).
+// Replaces ggml_cuda_mul_mat_q / mul_mat_q_case / launch_mul_mat_q (reference src/ggml-cuda/mmq.cu:71-143,
+// mmq.cuh:3542-3712): converts the activations to bf16 once (instead of quantize_mmq_q8_1), encodes a
+// TMA descriptor over them and launches one CTA per 128 x BN output tile.
 #include "common.cuh"
 #include "mmq_tc.cuh"
+
+#include <mutex>
+
 using namespace b200;
-extern "C" size_t b200_mul_mat_q_workspace_size(int64_t m, int64_t k, int64_t n) { return 256; }
+
+namespace {
+
+typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                    const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+encode_tiled_fn get_encode_tiled() {
+    static encode_tiled_fn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void * p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess) {
+            fn = (encode_tiled_fn) p;
+        } else {
+            cudaGetLastError();
+        }
+    });
+    return fn;
+}
+
+template <int T, int BN, bool ALIGNED>
+int launch_mmq(const mmq_args & a, const CUtensorMap & tmap, cudaStream_t st) {
+    auto kern = k_mmq_tc<T, BN, ALIGNED>;
+    const size_t smem = mmq_smem<BN>::total(a.raw_pitch);
+    static size_t smem_set[64];
+    int dev = 0; cudaGetDevice(&dev); if (dev < 0 || dev >= 64) dev = 0;
+    if (smem > smem_set[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+        if (e != cudaSuccess) return -(int) e;
+        smem_set[dev] = smem;
+    }
+    const dim3 grid((unsigned) ceil_div(a.m, MMQ_BM), (unsigned) ceil_div(a.n, BN));
+    kern<<<grid, MMQ_THREADS, smem, st>>>(a, tmap);
+    b200_count_launch(1);
+    B200_RETURN_IF_LAUNCH_FAILED();
+    return B200_OK;
+}
+
+template <int T, int BN>
+int launch_mmq_al(mmq_args a, const CUtensorMap & tmap, bool aligned, cudaStream_t st) {
+    if (aligned) { a.raw_pitch = slab<T>::pitch; return launch_mmq<T, BN, true>(a, tmap, st); }
+    a.raw_pitch = slab<T>::pitch_unaligned;
+    return launch_mmq<T, BN, false>(a, tmap, st);
+}
+
+template <int T>
+int launch_mmq_bn(const mmq_args & a, const CUtensorMap & tmap, int bn, bool aligned, cudaStream_t st) {
+    switch (bn) {
+        case 32:  return launch_mmq_al<T, 32>(a, tmap, aligned, st);
+        case 64:  return launch_mmq_al<T, 64>(a, tmap, aligned, st);
+        case 128: return launch_mmq_al<T, 128>(a, tmap, aligned, st);
+        default:  return launch_mmq_al<T, 256>(a, tmap, aligned, st);
+    }
+}
+
+int pick_bn(int64_t m, int64_t n, int sm_count) {
+    const int forced = env_int("GGML_B200_MMQ_BN", 0);
+    if (forced == 32 || forced == 64 || forced == 128 || forced == 256) return forced;
+    if (n <= 32) return 32;
+    if (n <= 64) return 64;
+    if (n <= 128) return 128;
+    // larger n: whichever of 128 / 256 needs less tensor time including the wave tail
+    const int64_t tm = ceil_div(m, MMQ_BM);
+    const int64_t w128 = ceil_div(tm * ceil_div(n, 128), sm_count) * 128;
+    const int64_t w256 = ceil_div(tm * ceil_div(n, 256), sm_count) * 256;
+    return w256 <= w128 ? 256 : 128;
+}
+
+} // namespace
+
+extern "C" size_t b200_mul_mat_q_workspace_size(int64_t m, int64_t k, int64_t n) {
+    (void) m;
+    if (k <= 0 || n <= 0) return 256;
+    return (size_t) n * (size_t) k * sizeof(__nv_bfloat16) + 512;
+}
+
 extern "C" int b200_mul_mat_q(int type, const void * w_dev, size_t w_row_stride_bytes, int64_t m, int64_t k,
-                               const float * x_dev, size_t x_row_stride_bytes, int64_t n,
-                               float * dst_dev, size_t dst_col_stride_bytes,
-                               void * workspace_dev, size_t workspace_bytes, void * stream) { return B200_ERR_TYPE; }
+                              const float * x_dev, size_t x_row_stride_bytes, int64_t n,
+                              float * dst_dev, size_t dst_col_stride_bytes,
+                              void * workspace_dev, size_t workspace_bytes, void * stream) {
+    if (!type_is_quant(type)) return B200_ERR_TYPE;
+    if (m < 0 || k < 0 || n < 0 || k % type_qk(type) != 0) return B200_ERR_SHAPE;
+    if (dst_col_stride_bytes % 4 != 0 || w_row_stride_bytes % 2 != 0 || x_row_stride_bytes % 4 != 0) return B200_ERR_STRIDE;
+    if (m == 0 || n == 0) return B200_OK;
+    cudaStream_t st = (cudaStream_t) stream;
+    if (k == 0) return -(int) cudaMemset2DAsync(dst_dev, dst_col_stride_bytes, 0, (size_t) m * 4, (size_t) n, st);
+    if (!workspace_dev || workspace_bytes < b200_mul_mat_q_workspace_size(m, k, n)) return B200_ERR_WORKSPACE;
+    if (k > 0x7FFFFFFF || n > 0x7FFFFFFF) return B200_ERR_SHAPE;
+
+    // 1. activations -> bf16 [n][k]
+    __nv_bfloat16 * xb = (__nv_bfloat16 *) (((uintptr_t) workspace_dev + 255) & ~(uintptr_t) 255);
+    for (int64_t r0 = 0; r0 < n; r0 += 65535) {
+        const int64_t nr = n - r0 < 65535 ? n - r0 : 65535;
+        const dim3 grid((unsigned) ceil_div(k, 1024), (unsigned) nr);
+        k_f32_to_bf16<<<grid, 256, 0, st>>>((const uint8_t *) x_dev + r0 * x_row_stride_bytes, (int64_t) x_row_stride_bytes, k, xb + r0 * k);
+        b200_count_launch(1);
+    }
+    B200_RETURN_IF_LAUNCH_FAILED();
+
+    // 2. TMA descriptor over the bf16 activations: dims {k, n}, box {64, BN}, 128-byte swizzle, zero fill
+    const dev_caps & caps = current_caps();
+    const int bn = pick_bn(m, n, caps.sm_count);
+    encode_tiled_fn encode = get_encode_tiled();
+    if (!encode) return B200_ERR_NO_DEVICE;
+    CUtensorMap tmap;
+    const cuuint64_t gdim[2]    = { (cuuint64_t) k, (cuuint64_t) n };
+    const cuuint64_t gstride[1] = { (cuuint64_t) k * sizeof(__nv_bfloat16) };
+    const cuuint32_t box[2]     = { (cuuint32_t) MMQ_BK, (cuuint32_t) bn };
+    const cuuint32_t estr[2]    = { 1, 1 };
+    const CUresult cr = encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, xb, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (cr != CUDA_SUCCESS) return B200_ERR_STRIDE;
+
+    // 3. the tile kernel
+    mmq_args a;
+    a.w = (const uint8_t *) w_dev; a.w_row_stride = (int64_t) w_row_stride_bytes; a.m = m; a.k = k; a.n = n;
+    a.dst = dst_dev; a.dst_col_stride = (int64_t) (dst_col_stride_bytes / 4);
+    a.nblk = (int) (k / type_qk(type)); a.raw_pitch = 0;
+    const bool aligned = type != T_Q6_K && ((uintptr_t) w_dev % 16 == 0) && (w_row_stride_bytes % 16 == 0) &&
+                         !env_int("GGML_B200_MMQ_FORCE_UNALIGNED", 0);
+    switch (type) {
+        case T_Q4_0: return launch_mmq_bn<T_Q4_0>(a, tmap, bn, aligned, st);
+        case T_Q8_0: return launch_mmq_bn<T_Q8_0>(a, tmap, bn, aligned, st);
+        case T_Q4_K: return launch_mmq_bn<T_Q4_K>(a, tmap, bn, aligned, st);
+        case T_Q5_K: return launch_mmq_bn<T_Q5_K>(a, tmap, bn, aligned, st);
+        case T_Q6_K: return launch_mmq_bn<T_Q6_K>(a, tmap, bn, false, st);
+        default: return B200_ERR_TYPE;
+    }
+}

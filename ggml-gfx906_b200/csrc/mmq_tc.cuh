@@ -1,1 +1,497 @@
+// mmq_tc.cuh — batched quantized MUL_MAT on the 5th-gen tensor cores (tcgen05 + TMEM).
+//
+//   dst[m, n] = W[m, k] (ggml quant blocks)  x  X[n, k]^T (f32)        for n > 8 (prefill)
+//
+// Replaces mul_mat_q / load_tiles_* / vec_dot_*_mma (reference src/ggml-cuda/mmq.cuh:277-3522,
+// mmq.cu:71-143), which unpack weights to int8 and issue one mma.sync m16n8k32 per 32-wide block,
+// rescaling in registers after every block.
+//
+// Design.  A per-32 (or per-16) block scale cannot ride through an integer TMEM accumulator: with
+// kind::i8 every 32-deep slice would need its own accumulator drained and FMA-scaled on the CUDA
+// cores — 128xN f32 FMAs per 128xNx32 MACs caps the tensor pipe below ~40 % of its i8 rate.  So the
+// scale is folded into the WEIGHT operand instead: producer warps dequantize the quant blocks to
+// fp16 (exact integer -> fp16 via the 0x6400 magic, one HFMA2 per two weights) straight into the
+// UMMA canonical K-major SWIZZLE_128B shared-memory layout, activations are converted once to bf16
+// and fetched by TMA with the same swizzle, and a single tcgen05.mma.kind::f16 chain accumulates
+// the whole K extent in f32 in TMEM.  Accuracy is better than the q8_1 route (activations keep 8
+// mantissa bits instead of <= 7 bits per 32-block; weights keep 11) and there is no per-block drain.
+//
+// CTA = one 128 x BN output tile, 6 warps:
+//   warps 0-3  weight producers, then the epilogue (TMEM lane quarter = warp id)
+//   warp  4    activation loader (TMA 2-D tiles, zero-filled past n and k)
+//   warp  5    TMEM allocation + the single MMA-issuing thread
+// Raw quant bytes are prefetched two 256-deep slabs ahead by 128 per-row bulk async copies
+// (cp.async.bulk, one per producer thread), re-aligned in shared memory when rows are not 16-byte
+// aligned (Q6_K, odd block counts), then expanded 64 K-elements at a time into a ring of A stages.
 #pragma once
+#include "common.cuh"
+#include "mmvq_stream.cuh"   // mbarrier / bulk-copy PTX helpers
+
+#include <cuda.h>
+
+namespace b200 {
+
+// ---------------------------------------------------------------- tcgen05 PTX
+__device__ __forceinline__ void tmem_alloc(uint32_t * dst_smem, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_u32(dst_smem)), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after()  { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// D[tmem] (+)= A[smem] * B[smem], 128 x N x 16, f16/bf16 inputs, f32 accumulate
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" :: "r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+// arrive on an mbarrier when all previously issued MMAs of this thread have completed
+__device__ __forceinline__ void umma_commit(uint64_t * bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&v)[8]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+                 : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+__device__ __forceinline__ void mbar_arrive(uint64_t * bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(bar)) : "memory");
+}
+// TMA 2-D tile load (global -> swizzled shared), completion on an mbarrier
+__device__ __forceinline__ void tma_load_2d(void * dst, const CUtensorMap * tmap, int c0, int c1, uint64_t * bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 :: "r"(smem_u32(dst)), "l"(tmap), "r"(c0), "r"(c1), "r"(smem_u32(bar)) : "memory");
+}
+
+// UMMA shared-memory descriptor, K-major, SWIZZLE_128B, 8-row groups 1024 B apart
+__device__ __forceinline__ uint64_t umma_desc_sw128(const void * smem_ptr) {
+    const uint64_t addr = (uint64_t) (smem_u32(smem_ptr) >> 4) & 0x3FFFull;
+    return addr | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+
+// ---------------------------------------------------------------- exact small-int -> fp16 helpers
+// (x & mask) | 0x6400 in each 16-bit lane is the fp16 value 1024 + x for 0 <= x < 1024
+__device__ __forceinline__ __half2 u32_as_h2(uint32_t v) { return *reinterpret_cast<__half2 *>(&v); }
+__device__ __forceinline__ uint32_t h2_as_u32(__half2 v) { return *reinterpret_cast<uint32_t *>(&v); }
+// bytes (b0,b1) or (b2,b3) of w spread to the low byte of each 16-bit lane
+__device__ __forceinline__ uint32_t spread01(uint32_t w) { return __byte_perm(w, 0, 0x4140); }
+__device__ __forceinline__ uint32_t spread23(uint32_t w) { return __byte_perm(w, 0, 0x4342); }
+__device__ __forceinline__ __half2 magic_to_h2(uint32_t lanes, float bias) {
+    // lanes hold integers < 1024 in each 16-bit half; returns (int - bias) exactly
+    return __hsub2(u32_as_h2(lanes | 0x64006400u), __float2half2_rn(1024.0f + bias));
+}
+
+} // namespace b200
+
+namespace b200 {
+
+// ================================================================= weight expansion (quant -> fp16)
+// A producer thread owns one weight row.  Its 256-element slab sits 16-byte aligned in shared
+// memory (SLAB bytes, PITCH apart); expand64<T>(SUB) turns elements [64*SUB, 64*SUB+64) into eight
+// 16-byte chunks of fp16 and stores them into the row of the SWIZZLE_128B A tile.
+template <int T> struct slab;
+template <> struct slab<T_Q4_0> { static constexpr int bytes = 144, pitch = 144, pitch_unaligned = 176; };
+template <> struct slab<T_Q8_0> { static constexpr int bytes = 272, pitch = 272, pitch_unaligned = 304; };
+template <> struct slab<T_Q4_K> { static constexpr int bytes = 144, pitch = 144, pitch_unaligned = 176; };
+template <> struct slab<T_Q5_K> { static constexpr int bytes = 176, pitch = 176, pitch_unaligned = 208; };
+template <> struct slab<T_Q6_K> { static constexpr int bytes = 210, pitch = 240, pitch_unaligned = 240; };
+
+// words [W0, W0+N) of the slab via 16-byte shared loads (conflict-free: PITCH/16 is odd)
+template <int W0, int N>
+__device__ __forceinline__ void slab_words(const uint8_t * s, uint32_t (&w)[N]) {
+    constexpr int C0 = W0 / 4, C1 = (W0 + N + 3) / 4;
+    uint32_t t[(C1 - C0) * 4];
+#pragma unroll
+    for (int c = C0; c < C1; c++) {
+        const uint4 v = lds128(s + 16 * c);
+        t[(c - C0) * 4 + 0] = v.x; t[(c - C0) * 4 + 1] = v.y; t[(c - C0) * 4 + 2] = v.z; t[(c - C0) * 4 + 3] = v.w;
+    }
+#pragma unroll
+    for (int i = 0; i < N; i++) w[i] = t[W0 - 4 * C0 + i];
+}
+
+__device__ __forceinline__ void store_chunk(uint8_t * a_row, int row7, int c, __half2 v0, __half2 v1, __half2 v2, __half2 v3) {
+    uint4 o;
+    o.x = h2_as_u32(v0); o.y = h2_as_u32(v1); o.z = h2_as_u32(v2); o.w = h2_as_u32(v3);
+    *reinterpret_cast<uint4 *>(a_row + ((c ^ row7) << 4)) = o;
+}
+__device__ __forceinline__ void store_zero_chunk(uint8_t * a_row, int row7, int c) {
+    *reinterpret_cast<uint4 *>(a_row + ((c ^ row7) << 4)) = make_uint4(0, 0, 0, 0);
+}
+
+template <int T> struct expander;
+
+// ---- Q4_K / Q5_K
+template <bool HAS_QH> struct expander_k45 {
+    uint32_t hdr[4];      // d|dmin, scales[12]
+    uint32_t qh[8];       // Q5_K only
+    __device__ __forceinline__ void begin_slab(const uint8_t * s, int /*nvalid*/) {
+        slab_words<0, 4>(s, hdr);
+        if (HAS_QH) slab_words<4, 8>(s, qh);
+    }
+    template <int SUB> __device__ __forceinline__ void expand64(const uint8_t * s, uint8_t * a_row, int row7) {
+        const float d = f16_bits_to_f32(hdr[0]), dmin = f16_bits_to_f32(hdr[0] >> 16);
+        uint32_t q[8];
+        slab_words<(HAS_QH ? 12 : 4) + 8 * SUB, 8>(s, q);
+#pragma unroll
+        for (int hi = 0; hi < 2; hi++) {
+            int sc, mn;
+            k4_scale_min(hdr[1], hdr[2], hdr[3], 2 * SUB + hi, sc, mn);
+            const __half2 d1 = __float2half2_rn(d * (float) sc);
+            const __half2 m1 = __float2half2_rn(-(dmin * (float) mn));
+#pragma unroll
+            for (int cc = 0; cc < 4; cc++) {
+                __half2 v[4];
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const uint32_t w  = q[2 * cc + (j >> 1)];
+                    uint32_t lanes = (((j & 1) ? spread23(w) : spread01(w)) >> (4 * hi)) & 0x000F000Fu;
+                    if (HAS_QH) {
+                        const uint32_t h = qh[2 * cc + (j >> 1)];
+                        lanes |= ((((j & 1) ? spread23(h) : spread01(h)) >> (2 * SUB + hi)) & 0x00010001u) << 4;
+                    }
+                    v[j] = __hfma2(magic_to_h2(lanes, 0.0f), d1, m1);
+                }
+                store_chunk(a_row, row7, 4 * hi + cc, v[0], v[1], v[2], v[3]);
+            }
+        }
+    }
+};
+template <> struct expander<T_Q4_K> : expander_k45<false> {};
+template <> struct expander<T_Q5_K> : expander_k45<true> {};
+
+// ---- Q6_K
+template <> struct expander<T_Q6_K> {
+    uint32_t sc[4];       // 16 int8 scales
+    float d;
+    __device__ __forceinline__ void begin_slab(const uint8_t * s, int /*nvalid*/) {
+        uint32_t t[5];
+        slab_words<48, 5>(s, t);          // bytes 192..211: scales[16], d
+        sc[0] = t[0]; sc[1] = t[1]; sc[2] = t[2]; sc[3] = t[3];
+        d = f16_bits_to_f32(t[4]);
+    }
+    template <int SUB> __device__ __forceinline__ void expand64(const uint8_t * s, uint8_t * a_row, int row7) {
+        constexpr int h = SUB >> 1, p = SUB & 1;
+        uint32_t ql[16], qh[8];
+        slab_words<16 * h, 16>(s, ql);            // ql[64h .. 64h+64)
+        slab_words<32 + 8 * h, 8>(s, qh);         // qh[32h .. 32h+32)
+#pragma unroll
+        for (int c = 0; c < 8; c++) {
+            constexpr int dummy = 0; (void) dummy;
+            const int st = 2 * p + (c >> 2);      // stream
+            const int l0 = 8 * (c & 3);
+            const int sidx = 8 * h + 2 * st + (l0 >> 4);
+            const int scv = (int) (int8_t) ((sc[sidx >> 2] >> (8 * (sidx & 3))) & 0xFFu);
+            const __half2 ds = __float2half2_rn(d * (float) scv);
+            __half2 v[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const uint32_t wl = ql[8 * (c >> 2) + 2 * (c & 3) + (j >> 1)];
+                const uint32_t wh = qh[2 * (c & 3) + (j >> 1)];
+                const uint32_t lo = (((j & 1) ? spread23(wl) : spread01(wl)) >> (4 * p)) & 0x000F000Fu;
+                const uint32_t hi = ((((j & 1) ? spread23(wh) : spread01(wh)) >> (2 * st)) & 0x00030003u) << 4;
+                v[j] = __hmul2(magic_to_h2(lo | hi, 32.0f), ds);
+            }
+            store_chunk(a_row, row7, c, v[0], v[1], v[2], v[3]);
+        }
+    }
+};
+
+// ---- Q4_0: two 18-byte blocks per 64 elements, words 9*SUB .. 9*SUB+8 of the slab
+template <> struct expander<T_Q4_0> {
+    int nvalid;   // valid blocks in this slab (k tail)
+    __device__ __forceinline__ void begin_slab(const uint8_t *, int nv) { nvalid = nv; }
+    template <int SUB> __device__ __forceinline__ void expand64(const uint8_t * s, uint8_t * a_row, int row7) {
+        uint32_t w[9];
+        slab_words<9 * SUB, 9>(s, w);
+#pragma unroll
+        for (int b = 0; b < 2; b++) {
+            if (2 * SUB + b >= nvalid) {
+#pragma unroll
+                for (int cc = 0; cc < 4; cc++) store_zero_chunk(a_row, row7, 4 * b + cc);
+                continue;
+            }
+            uint32_t qs[4];
+#pragma unroll
+            for (int i = 0; i < 4; i++) qs[i] = b == 0 ? __funnelshift_r(w[i], w[i + 1], 16) : w[5 + i];
+            const __half2 d = __float2half2_rn(f16_bits_to_f32(b == 0 ? w[0] : (w[4] >> 16)));
+#pragma unroll
+            for (int cc = 0; cc < 4; cc++) {
+                __half2 v[4];
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const uint32_t x = qs[2 * (cc & 1) + (j >> 1)];
+                    const uint32_t lanes = (((j & 1) ? spread23(x) : spread01(x)) >> (4 * (cc >> 1))) & 0x000F000Fu;
+                    v[j] = __hmul2(magic_to_h2(lanes, 8.0f), d);
+                }
+                store_chunk(a_row, row7, 4 * b + cc, v[0], v[1], v[2], v[3]);
+            }
+        }
+    }
+};
+
+// ---- Q8_0: two 34-byte blocks per 64 elements, words 17*SUB .. 17*SUB+16
+template <> struct expander<T_Q8_0> {
+    int nvalid;
+    __device__ __forceinline__ void begin_slab(const uint8_t *, int nv) { nvalid = nv; }
+    template <int SUB> __device__ __forceinline__ void expand64(const uint8_t * s, uint8_t * a_row, int row7) {
+        uint32_t w[17];
+        slab_words<17 * SUB, 17>(s, w);
+#pragma unroll
+        for (int b = 0; b < 2; b++) {
+            if (2 * SUB + b >= nvalid) {
+#pragma unroll
+                for (int cc = 0; cc < 4; cc++) store_zero_chunk(a_row, row7, 4 * b + cc);
+                continue;
+            }
+            const __half2 d = __float2half2_rn(f16_bits_to_f32(b == 0 ? w[0] : (w[8] >> 16)));
+#pragma unroll
+            for (int cc = 0; cc < 4; cc++) {
+                __half2 v[4];
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const int wi = 2 * cc + (j >> 1);
+                    const uint32_t x = b == 0 ? __funnelshift_r(w[wi], w[wi + 1], 16) : w[9 + wi];
+                    const uint32_t lanes = (((j & 1) ? spread23(x) : spread01(x)) ^ 0x00800080u) & 0x00FF00FFu;
+                    v[j] = __hmul2(magic_to_h2(lanes, 128.0f), d);
+                }
+                store_chunk(a_row, row7, 4 * b + cc, v[0], v[1], v[2], v[3]);
+            }
+        }
+    }
+};
+
+} // namespace b200
+
+namespace b200 {
+
+// ================================================================= the kernel
+struct mmq_args {
+    const uint8_t * w;         // weight rows
+    int64_t w_row_stride;      // bytes
+    int64_t m, k, n;
+    float * dst;               // dst[j * dst_col_stride + i]
+    int64_t dst_col_stride;    // floats
+    int     nblk;              // blocks per row (k / qk)
+    int     raw_pitch;         // bytes per row slot in the raw ring
+};
+
+constexpr int MMQ_BM = 128;
+constexpr int MMQ_BK = 64;           // K elements per MMA stage (one 128-byte swizzle row)
+constexpr int MMQ_RS = 2;            // raw slab ring depth
+constexpr int MMQ_THREADS = 192;
+
+template <int BN> struct mmq_cfg {
+    static constexpr int stages   = BN <= 128 ? 4 : 3;
+    static constexpr int a_bytes  = MMQ_BM * 128;
+    static constexpr int b_bytes  = BN * 128;
+    static constexpr int tmem_cols = BN < 32 ? 32 : BN;
+};
+
+// dynamic shared memory map (offsets from a 1024-byte aligned base)
+template <int BN> struct mmq_smem {
+    static constexpr int a_off    = 0;
+    static constexpr int b_off    = a_off + mmq_cfg<BN>::stages * mmq_cfg<BN>::a_bytes;
+    static constexpr int raw_off  = b_off + mmq_cfg<BN>::stages * mmq_cfg<BN>::b_bytes;
+    static size_t total(int raw_pitch) { return (size_t) raw_off + (size_t) MMQ_RS * MMQ_BM * raw_pitch + 256 + 1024; }
+};
+
+template <int T, int BN, bool ALIGNED>
+__global__ void __launch_bounds__(MMQ_THREADS, 1)
+k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b) {
+    using CFG = mmq_cfg<BN>;
+    using SM  = mmq_smem<BN>;
+    constexpr int ST = CFG::stages;
+    constexpr int SLAB_ELEMS = 256;
+    constexpr int BLK_PER_SLAB = SLAB_ELEMS / fmt<T>::qk;       // 1 or 8
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t * smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t) 1023);
+    uint8_t * a_tiles = smem + SM::a_off;
+    uint8_t * b_tiles = smem + SM::b_off;
+    uint8_t * raw     = smem + SM::raw_off;
+    uint8_t * ctl     = raw + (size_t) MMQ_RS * MMQ_BM * a.raw_pitch;
+    uint64_t * full      = reinterpret_cast<uint64_t *>(ctl);            // [ST]   A written + B landed
+    uint64_t * empty     = full + ST;                                    // [ST]   MMAs of the stage retired
+    uint64_t * raw_full  = empty + ST;                                   // [RS][4] raw slab landed, per producer warp
+    uint64_t * tmem_full = raw_full + MMQ_RS * 4;                        // accumulator complete
+    uint32_t * tmem_slot = reinterpret_cast<uint32_t *>(tmem_full + 1);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int64_t m0 = (int64_t) blockIdx.x * MMQ_BM;
+    const int64_t n0 = (int64_t) blockIdx.y * BN;
+    const int nkt   = (int) ((a.k + MMQ_BK - 1) / MMQ_BK);               // 64-deep MMA stages
+    const int nslab = (int) ((a.k + SLAB_ELEMS - 1) / SLAB_ELEMS);
+
+    if (tid == 0) {
+        for (int s = 0; s < ST; s++) { mbar_init(&full[s], 128 + 1); mbar_init(&empty[s], 1); }
+        for (int s = 0; s < MMQ_RS * 4; s++) mbar_init(&raw_full[s], 32);
+        mbar_init(tmem_full, 1);
+        mbar_fence_init();
+    }
+    if (warp == 5) tmem_alloc(tmem_slot, CFG::tmem_cols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp < 4) {
+        // ===================================================== weight producers
+        const int64_t row = (m0 + tid < a.m) ? (m0 + tid) : (a.m - 1);     // rows past m recompute the last row, never stored
+        const uint8_t * wrow = a.w + row * a.w_row_stride;
+        const int row7 = tid & 7;
+        uint8_t * my_raw[MMQ_RS];
+#pragma unroll
+        for (int r = 0; r < MMQ_RS; r++) my_raw[r] = raw + ((size_t) r * MMQ_BM + tid) * a.raw_pitch;
+
+        auto slab_valid_blocks = [&](int s) {
+            const int left = a.nblk - s * BLK_PER_SLAB;
+            return left < BLK_PER_SLAB ? left : BLK_PER_SLAB;
+        };
+        auto issue_raw = [&](int s) {
+            const int r = s % MMQ_RS;
+            const uint8_t * src = wrow + (size_t) s * BLK_PER_SLAB * fmt<T>::bytes;
+            const uint32_t nbytes = (uint32_t) slab_valid_blocks(s) * fmt<T>::bytes;
+            const uint32_t off = ALIGNED ? 0u : (uint32_t) (reinterpret_cast<uintptr_t>(src) & 15);
+            const uint32_t cp = (off + nbytes + 15u) & ~15u;
+            uint64_t * bar = &raw_full[r * 4 + warp];
+            mbar_arrive_expect_tx(bar, cp);
+            bulk_g2s(my_raw[r], src - off, cp, bar);
+        };
+
+        issue_raw(0);
+        if (nslab > 1) issue_raw(1);
+
+        expander<T> ex;
+        for (int s = 0; s < nslab; s++) {
+            const int r = s % MMQ_RS;
+            mbar_wait(&raw_full[r * 4 + warp], (uint32_t) ((s / MMQ_RS) & 1));
+            uint8_t * slab_ptr = my_raw[r];
+            if (!ALIGNED) {
+                // shift every row of this warp down to its 16-byte aligned slot start (2-byte granules,
+                // lanes side by side: conflict-free), in place
+                const uint8_t * src = wrow + (size_t) s * BLK_PER_SLAB * fmt<T>::bytes;
+                const int my_off = (int) (reinterpret_cast<uintptr_t>(src) & 15);
+                constexpr int NU16 = (slab<T>::bytes + 1) / 2;
+                for (int rr = 0; rr < 32; rr++) {
+                    const int off = __shfl_sync(0xFFFFFFFFu, my_off, rr);
+                    if (off == 0) continue;
+                    uint8_t * rp = raw + ((size_t) r * MMQ_BM + warp * 32 + rr) * a.raw_pitch;
+#pragma unroll
+                    for (int i0 = 0; i0 < NU16; i0 += 32) {
+                        const int i = i0 + lane;
+                        uint16_t v = 0;
+                        if (i < NU16) v = *reinterpret_cast<const uint16_t *>(rp + off + 2 * i);
+                        __syncwarp();
+                        if (i < NU16) *reinterpret_cast<uint16_t *>(rp + 2 * i) = v;
+                        __syncwarp();
+                    }
+                }
+                __syncwarp();
+            }
+            ex.begin_slab(slab_ptr, slab_valid_blocks(s));
+#pragma unroll
+            for (int sub = 0; sub < 4; sub++) {
+                const int kt = s * 4 + sub;
+                if (kt < nkt) {
+                    const int st = kt % ST;
+                    if (kt >= ST) mbar_wait(&empty[st], (uint32_t) (((kt / ST) - 1) & 1));
+                    uint8_t * a_row = a_tiles + (size_t) st * CFG::a_bytes + tid * 128;
+                    if      (sub == 0) ex.template expand64<0>(slab_ptr, a_row, row7);
+                    else if (sub == 1) ex.template expand64<1>(slab_ptr, a_row, row7);
+                    else if (sub == 2) ex.template expand64<2>(slab_ptr, a_row, row7);
+                    else               ex.template expand64<3>(slab_ptr, a_row, row7);
+                    fence_proxy_async_smem();       // generic-proxy stores -> visible to the tensor core's async proxy
+                    mbar_arrive(&full[st]);
+                }
+            }
+            __syncwarp();                            // the whole warp is done with the raw slot (realign reads neighbours)
+            if (s + MMQ_RS < nslab) issue_raw(s + MMQ_RS);
+        }
+
+        // ===================================================== epilogue: TMEM -> registers -> global
+        mbar_wait(tmem_full, 0);
+        tc_fence_after();
+        const int64_t out_row = m0 + tid;
+        const uint32_t taddr = tmem_base + ((uint32_t) (warp * 32) << 16);
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += 8) {
+            if (n0 + c0 >= a.n) break;               // warp-uniform
+            uint32_t v[8];
+            tmem_ld8(taddr + (uint32_t) c0, v);
+            tmem_ld_wait();
+            if (out_row < a.m) {
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    if (n0 + c0 + j < a.n) a.dst[(n0 + c0 + j) * a.dst_col_stride + out_row] = __uint_as_float(v[j]);
+                }
+            }
+        }
+        tc_fence_before();
+    } else if (warp == 4) {
+        // ===================================================== activation loader (TMA)
+        if (lane == 0) {
+            for (int kt = 0; kt < nkt; kt++) {
+                const int st = kt % ST;
+                if (kt >= ST) mbar_wait(&empty[st], (uint32_t) (((kt / ST) - 1) & 1));
+                mbar_arrive_expect_tx(&full[st], (uint32_t) CFG::b_bytes);
+                tma_load_2d(b_tiles + (size_t) st * CFG::b_bytes, &tmap_b, kt * MMQ_BK, (int) n0, &full[st]);
+            }
+        }
+    } else {
+        // ===================================================== MMA issuer
+        if (lane == 0) {
+            // instruction descriptor: D=f32, A=f16, B=bf16, both K-major, N=BN, M=128
+            constexpr uint32_t idesc = (1u << 4) | (0u << 7) | (1u << 10) | ((uint32_t) (BN >> 3) << 17) | ((uint32_t) (MMQ_BM >> 4) << 24);
+            for (int kt = 0; kt < nkt; kt++) {
+                const int st = kt % ST;
+                mbar_wait(&full[st], (uint32_t) ((kt / ST) & 1));
+                tc_fence_after();
+                const uint64_t da = umma_desc_sw128(a_tiles + (size_t) st * CFG::a_bytes);
+                const uint64_t db = umma_desc_sw128(b_tiles + (size_t) st * CFG::b_bytes);
+#pragma unroll
+                for (int k4 = 0; k4 < MMQ_BK / 16; k4++) {
+                    // +32 bytes (2 x 16-byte units) along K inside the 128-byte swizzle row
+                    umma_f16(tmem_base, da + (uint64_t) (2 * k4), db + (uint64_t) (2 * k4), idesc, (kt > 0 || k4 > 0) ? 1u : 0u);
+                }
+                umma_commit(&empty[st]);             // frees the stage when these MMAs retire
+            }
+            umma_commit(tmem_full);
+        }
+    }
+
+    __syncthreads();
+    if (warp == 5) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, CFG::tmem_cols);
+    }
+}
+
+// f32 [n, k] (row stride in bytes) -> bf16 [n, k] packed, RN
+__global__ void __launch_bounds__(256) k_f32_to_bf16(const uint8_t * __restrict__ x, int64_t x_row_stride, int64_t k, __nv_bfloat16 * __restrict__ y) {
+    const int64_t row = blockIdx.y;
+    const int64_t i = ((int64_t) blockIdx.x * 256 + threadIdx.x) * 4;
+    if (i >= k) return;
+    const float * xr = reinterpret_cast<const float *>(x + row * x_row_stride);
+    __nv_bfloat16 * yr = y + row * k;
+    if (i + 3 < k && (reinterpret_cast<uintptr_t>(xr + i) & 15) == 0) {
+        const float4 v = *reinterpret_cast<const float4 *>(xr + i);
+        __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+        uint2 o;
+        o.x = *reinterpret_cast<uint32_t *>(&lo); o.y = *reinterpret_cast<uint32_t *>(&hi);
+        *reinterpret_cast<uint2 *>(yr + i) = o;
+    } else {
+        for (int j = 0; j < 4 && i + j < k; j++) yr[i + j] = __float2bfloat16_rn(xr[i + j]);
+    }
+}
+
+} // namespace b200

@@ -22,7 +22,12 @@ __device__ __forceinline__ q8_result quantize32(float x) {
     const float amax = warp_max(fabsf(x));
     const float d  = __fdiv_rn(amax, 127.0f);
     const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
-    const int   q  = (int) roundf(__fmul_rn(x, id));
+    // float -> int8 as the reference's x86 build does it (cvttss2si, then the low byte): NaN and
+    // |v| >= 2^31 give INT_MIN, whose low byte is 0; in-range values wrap.  Only reachable when
+    // 1/d overflows (f32-denormal inputs) — the golden vectors from the reference pin it.
+    const float v  = roundf(__fmul_rn(x, id));
+    const int   qi = fabsf(v) < 2147483648.0f ? (int) v : (int) 0x80000000;
+    const int   q  = (int) (int8_t) (qi & 0xFF);
     int sum = q;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xFFFFFFFFu, sum, o);

@@ -36,6 +36,7 @@ def run_harness(args, timeout=900):
 
 
 def check_harness_output(rc, out, min_supported):
+    out = re.sub(r"\x1b\[[0-9;]*m", "", out)
     tail = out[-3000:]
     assert rc == 0, tail
     assert "Backend B200_0: OK" in out or re.search(r"Backend B200_0.*OK", out), tail
