@@ -1,6 +1,6 @@
 // mmq.cu — host side of the batched tensor-core MUL_MAT (kernel: mmq_tc.cuh).
 // Replaces ggml_cuda_mul_mat_q / mul_mat_q_case / launch_mul_mat_q (reference src/ggml-cuda/mmq.cu:71-143,
-// mmq.cuh:3542-3712): converts the activations to bf16 once (instead of quantize_mmq_q8_1), encodes a
+// mmq.cuh:3542-3712): converts the activations to fp16 once (instead of quantize_mmq_q8_1), encodes a
 // TMA descriptor over them and launches one CTA per 128 x BN output tile.
 #include "common.cuh"
 #include "mmq_tc.cuh"
@@ -83,7 +83,7 @@ int pick_bn(int64_t m, int64_t n, int sm_count) {
 extern "C" size_t b200_mul_mat_q_workspace_size(int64_t m, int64_t k, int64_t n) {
     (void) m;
     if (k <= 0 || n <= 0) return 256;
-    return (size_t) n * (size_t) k * sizeof(__nv_bfloat16) + 512;
+    return (size_t) n * (size_t) k * sizeof(__half) + 512;
 }
 
 extern "C" int b200_mul_mat_q(int type, const void * w_dev, size_t w_row_stride_bytes, int64_t m, int64_t k,
@@ -99,27 +99,27 @@ extern "C" int b200_mul_mat_q(int type, const void * w_dev, size_t w_row_stride_
     if (!workspace_dev || workspace_bytes < b200_mul_mat_q_workspace_size(m, k, n)) return B200_ERR_WORKSPACE;
     if (k > 0x7FFFFFFF || n > 0x7FFFFFFF) return B200_ERR_SHAPE;
 
-    // 1. activations -> bf16 [n][k]
-    __nv_bfloat16 * xb = (__nv_bfloat16 *) (((uintptr_t) workspace_dev + 255) & ~(uintptr_t) 255);
+    // 1. activations -> fp16 [n][k]
+    uint16_t * xb = (uint16_t *) (((uintptr_t) workspace_dev + 255) & ~(uintptr_t) 255);
     for (int64_t r0 = 0; r0 < n; r0 += 65535) {
         const int64_t nr = n - r0 < 65535 ? n - r0 : 65535;
         const dim3 grid((unsigned) ceil_div(k, 1024), (unsigned) nr);
-        k_f32_to_bf16<<<grid, 256, 0, st>>>((const uint8_t *) x_dev + r0 * x_row_stride_bytes, (int64_t) x_row_stride_bytes, k, xb + r0 * k);
+        k_f32_to_f16<<<grid, 256, 0, st>>>((const uint8_t *) x_dev + r0 * x_row_stride_bytes, (int64_t) x_row_stride_bytes, k, xb + r0 * k);
         b200_count_launch(1);
     }
     B200_RETURN_IF_LAUNCH_FAILED();
 
-    // 2. TMA descriptor over the bf16 activations: dims {k, n}, box {64, BN}, 128-byte swizzle, zero fill
+    // 2. TMA descriptor over the fp16 activations: dims {k, n}, box {64, BN}, 128-byte swizzle, zero fill
     const dev_caps & caps = current_caps();
     const int bn = pick_bn(m, n, caps.sm_count);
     encode_tiled_fn encode = get_encode_tiled();
     if (!encode) return B200_ERR_NO_DEVICE;
     CUtensorMap tmap;
     const cuuint64_t gdim[2]    = { (cuuint64_t) k, (cuuint64_t) n };
-    const cuuint64_t gstride[1] = { (cuuint64_t) k * sizeof(__nv_bfloat16) };
+    const cuuint64_t gstride[1] = { (cuuint64_t) k * sizeof(__half) };
     const cuuint32_t box[2]     = { (cuuint32_t) MMQ_BK, (cuuint32_t) bn };
     const cuuint32_t estr[2]    = { 1, 1 };
-    const CUresult cr = encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, xb, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+    const CUresult cr = encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, xb, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (cr != CUDA_SUCCESS) return B200_ERR_STRIDE;
 
