@@ -32,6 +32,25 @@ def row_bytes(t: str, k: int) -> int:
     return k // BLOCK_ELEMS[t] * BLOCK_BYTES[t]
 
 
+class MulMatNode(C.Structure):
+    """struct b200_mul_mat_node (include/ggml_b200.h)."""
+    _fields_ = [("type_a", C.c_int32), ("reserved", C.c_int32), ("a_dev", C.c_void_p),
+                ("ne_a", C.c_int64 * 4), ("nb_a", C.c_size_t * 4), ("b_dev", C.c_void_p),
+                ("ne_b", C.c_int64 * 4), ("nb_b", C.c_size_t * 4), ("dst_dev", C.c_void_p)]
+
+
+def mul_mat_node(t: str, a_ptr: int, m: int, k: int, b_ptr: int, n: int, dst_ptr: int,
+                 a_row_stride: Optional[int] = None, b_row_stride: Optional[int] = None) -> MulMatNode:
+    """A plain 2-D node: W[m rows of k] x X[n rows of k] -> dst[n][m]."""
+    rb = a_row_stride or row_bytes(t, k)
+    sb = b_row_stride or 4 * k
+    nd = MulMatNode()
+    nd.type_a = TYPE_ID[t]; nd.a_dev = a_ptr; nd.b_dev = b_ptr; nd.dst_dev = dst_ptr
+    nd.ne_a[:] = [k, m, 1, 1]; nd.nb_a[:] = [BLOCK_BYTES[t], rb, rb * m, rb * m]
+    nd.ne_b[:] = [k, n, 1, 1]; nd.nb_b[:] = [4, sb, sb * n, sb * n]
+    return nd
+
+
 def load_library(path: Optional[str] = None) -> C.CDLL:
     path = path or LIB_PATH
     if not os.path.exists(path):
@@ -66,6 +85,10 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
     lib.b200_mul_mat_q_workspace_size.argtypes = [i64, i64, i64]
     lib.b200_mul_mat_q.restype = i32
     lib.b200_mul_mat_q.argtypes = [i32, vp, sz, i64, i64, vp, sz, i64, vp, sz, vp, sz, vp]
+    lib.b200_mul_mat_batch_workspace_size.restype = sz
+    lib.b200_mul_mat_batch_workspace_size.argtypes = [C.POINTER(MulMatNode), i64]
+    lib.b200_mul_mat_batch.restype = i32
+    lib.b200_mul_mat_batch.argtypes = [C.POINTER(MulMatNode), i64, vp, sz, vp]
     lib.b200_launch_count.restype = C.c_uint64
     return lib
 
@@ -200,3 +223,10 @@ class Kernels:
         self._check(self.lib.b200_mul_mat(TYPE_ID[t], a.data_ptr(), _a4i(ne_a), _a4s(nb_a), b.data_ptr(), _a4i(ne_b),
                                           _a4s(nb_b), out.data_ptr(), ws.data_ptr(), ws.numel(), self._stream()), "mul_mat")
         return out
+
+    def mul_mat_batch(self, nodes, count: Optional[int] = None, ws=None):
+        """nodes: a ctypes array of MulMatNode (see mul_mat_node); one host call for the whole list."""
+        count = len(nodes) if count is None else count
+        if ws is None:
+            ws = self.workspace(int(self.lib.b200_mul_mat_batch_workspace_size(nodes, count)))
+        self._check(self.lib.b200_mul_mat_batch(nodes, count, ws.data_ptr(), ws.numel(), self._stream()), "mul_mat_batch")

@@ -185,3 +185,25 @@ extern "C" int b200_mul_mat(int type_a, const void * a_dev, const int64_t ne_a[4
     }
     return B200_OK;
 }
+
+// ---------------------------------------------------------------- a list of MUL_MAT nodes
+extern "C" size_t b200_mul_mat_batch_workspace_size(const b200_mul_mat_node * nodes, int64_t count) {
+    size_t need = 256;
+    for (int64_t i = 0; i < count; i++) {
+        const size_t s = b200_mul_mat_workspace_size(nodes[i].type_a, nodes[i].ne_a, nodes[i].ne_b);
+        if (s > need) need = s;
+    }
+    return need;
+}
+
+extern "C" int b200_mul_mat_batch(const b200_mul_mat_node * nodes, int64_t count,
+                                  void * workspace_dev, size_t workspace_bytes, void * stream) {
+    if (count < 0 || (count > 0 && !nodes)) return B200_ERR_SHAPE;
+    for (int64_t i = 0; i < count; i++) {
+        const b200_mul_mat_node & nd = nodes[i];
+        const int rc = b200_mul_mat(nd.type_a, nd.a_dev, nd.ne_a, nd.nb_a, nd.b_dev, nd.ne_b, nd.nb_b, nd.dst_dev,
+                                    workspace_dev, workspace_bytes, stream);
+        if (rc) return rc;
+    }
+    return B200_OK;
+}

@@ -239,3 +239,46 @@ class GgmlHost:
                 b.ggml_backend_buffer_free(buf)
         finally:
             b.ggml_free(ctx)
+
+
+class MulMatGraph:
+    """A ggml graph of independent MUL_MAT nodes (one per (type, m, k) entry, f32 activations [k, n])
+    allocated once on `backend`: weights / activations are set with ggml_backend_tensor_set, compute()
+    is ggml_backend_graph_compute — the calls an unmodified ggml program makes per step."""
+
+    def __init__(self, host: GgmlHost, backend, mats: Sequence, n: int):
+        self.host, self.backend, self.mats, self.n = host, backend, list(mats), n
+        b = host.base
+        self.ctx = host.new_context(n_tensors=3 * len(self.mats) + 8, graph_nodes=2 * len(self.mats) + 64)
+        self.w, self.x, self.y = [], [], []
+        for mt in self.mats:
+            a = b.ggml_new_tensor_2d(self.ctx, GGML_TYPE[mt.type], mt.k, mt.m)
+            x = b.ggml_new_tensor_2d(self.ctx, GGML_TYPE["f32"], mt.k, n)
+            self.w.append(a); self.x.append(x); self.y.append(b.ggml_mul_mat(self.ctx, a, x))
+        self.graph = b.ggml_new_graph_custom(self.ctx, max(2048, 2 * len(self.mats) + 64), False)
+        for y in self.y:
+            b.ggml_build_forward_expand(self.graph, y)
+        self.buf = b.ggml_backend_alloc_ctx_tensors(self.ctx, backend)
+        if not self.buf:
+            b.ggml_free(self.ctx)
+            raise MemoryError("ggml_backend_alloc_ctx_tensors")
+
+    def set_weight(self, i: int, blocks: np.ndarray):
+        self.host.tensor_set(self.w[i], np.ascontiguousarray(blocks, dtype=np.uint8))
+
+    def set_input(self, i: int, x: np.ndarray):
+        self.host.tensor_set(self.x[i], np.ascontiguousarray(x, dtype=np.float32))
+
+    def get_output(self, i: int) -> np.ndarray:
+        return self.host.tensor_get(self.y[i]).reshape(self.n, self.mats[i].m)
+
+    def compute(self):
+        st = self.host.base.ggml_backend_graph_compute(self.backend, self.graph)
+        if st != GGML_STATUS_SUCCESS:
+            raise RuntimeError(f"graph_compute status {st}")
+
+    def close(self):
+        if self.buf:
+            self.host.base.ggml_backend_buffer_free(self.buf)
+            self.host.base.ggml_free(self.ctx)
+            self.buf = None

@@ -120,6 +120,28 @@ B200_API int    b200_mul_mat(int type_a, const void * a_dev, const int64_t ne_a[
                              const float * b_dev, const int64_t ne_b[4], const size_t nb_b[4],
                              float * dst_dev, void * workspace_dev, size_t workspace_bytes, void * stream);
 
+/* A whole list of MUL_MAT nodes in one call, issued back to back on `stream` in list order.
+ * replaces the node loop of ggml_backend_cuda_graph_compute -> evaluate_and_capture_cuda_graph ->
+ * ggml_cuda_compute_forward (src/ggml-cuda/ggml-cuda.cu:2226-2520, 2870-2960) for graphs made of
+ * MUL_MAT nodes: one host call per graph instead of one per node.  workspace_dev is shared by the
+ * nodes (stream order makes that safe) and must hold b200_mul_mat_batch_workspace_size() bytes.
+ * Returns the first error; nodes before it have been enqueued. */
+typedef struct b200_mul_mat_node {
+    int32_t       type_a;
+    int32_t       reserved;
+    const void  * a_dev;
+    int64_t       ne_a[4];
+    size_t        nb_a[4];
+    const float * b_dev;
+    int64_t       ne_b[4];
+    size_t        nb_b[4];
+    float       * dst_dev;
+} b200_mul_mat_node;
+
+B200_API size_t b200_mul_mat_batch_workspace_size(const b200_mul_mat_node * nodes, int64_t count);
+B200_API int    b200_mul_mat_batch(const b200_mul_mat_node * nodes, int64_t count,
+                                   void * workspace_dev, size_t workspace_bytes, void * stream);
+
 /* The two legs separately (2-D, for tests and benches).
  * b200_quantize_acts: f32 [n, k] -> the planar q8 scratch the matvec consumes (same values as
  *   quantize_row_q8_1: int8 plane [n][k] followed by the per-32 scales d as f32 [n][k/32]).
