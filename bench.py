@@ -151,7 +151,7 @@ class DecodeStack:
         Nodes = b200.MulMatNode * len(mats)
         self.nodes = Nodes(*[
             b200.mul_mat_node(mt.type, w.data_ptr(), hi - lo, mt.k, self.x_dev.data_ptr() + 4 * x_off[i], n,
-                              self.y_dev.data_ptr() + 4 * (y_off[i] + lo))
+                              self.y_dev.data_ptr() + 4 * (y_off[i] + lo), const_weights=True)
             for i, (mt, w, (lo, hi)) in enumerate(zip(mats, self.weights, self.rows))])
         # output column stride: b200_mul_mat writes dst as [n][m_local]; with n == 1 that is the slice itself
         self.ws = torch.empty(int(kern.lib.b200_mul_mat_batch_workspace_size(self.nodes, len(mats))) + 256,

@@ -34,18 +34,18 @@ def row_bytes(t: str, k: int) -> int:
 
 class MulMatNode(C.Structure):
     """struct b200_mul_mat_node (include/ggml_b200.h)."""
-    _fields_ = [("type_a", C.c_int32), ("reserved", C.c_int32), ("a_dev", C.c_void_p),
+    _fields_ = [("type_a", C.c_int32), ("flags", C.c_uint32), ("a_dev", C.c_void_p),
                 ("ne_a", C.c_int64 * 4), ("nb_a", C.c_size_t * 4), ("b_dev", C.c_void_p),
                 ("ne_b", C.c_int64 * 4), ("nb_b", C.c_size_t * 4), ("dst_dev", C.c_void_p)]
 
 
 def mul_mat_node(t: str, a_ptr: int, m: int, k: int, b_ptr: int, n: int, dst_ptr: int,
-                 a_row_stride: Optional[int] = None, b_row_stride: Optional[int] = None) -> MulMatNode:
+                 a_row_stride: Optional[int] = None, b_row_stride: Optional[int] = None, const_weights: bool = False) -> MulMatNode:
     """A plain 2-D node: W[m rows of k] x X[n rows of k] -> dst[n][m]."""
     rb = a_row_stride or row_bytes(t, k)
     sb = b_row_stride or 4 * k
     nd = MulMatNode()
-    nd.type_a = TYPE_ID[t]; nd.a_dev = a_ptr; nd.b_dev = b_ptr; nd.dst_dev = dst_ptr
+    nd.type_a = TYPE_ID[t]; nd.flags = 1 if const_weights else 0; nd.a_dev = a_ptr; nd.b_dev = b_ptr; nd.dst_dev = dst_ptr
     nd.ne_a[:] = [k, m, 1, 1]; nd.nb_a[:] = [BLOCK_BYTES[t], rb, rb * m, rb * m]
     nd.ne_b[:] = [k, n, 1, 1]; nd.nb_b[:] = [4, sb, sb * n, sb * n]
     return nd
@@ -77,6 +77,8 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
     lib.b200_mul_mat_workspace_size.argtypes = [i32, A4i, A4i]
     lib.b200_mul_mat.restype = i32
     lib.b200_mul_mat.argtypes = [i32, vp, A4i, A4s, vp, A4i, A4s, vp, vp, sz, vp]
+    lib.b200_mul_mat_ex.restype = i32
+    lib.b200_mul_mat_ex.argtypes = [i32, vp, A4i, A4s, vp, A4i, A4s, vp, vp, sz, C.c_uint32, vp]
     lib.b200_acts_scratch_bytes.restype = sz;    lib.b200_acts_scratch_bytes.argtypes = [i64, i64]
     lib.b200_quantize_acts.restype = i32;        lib.b200_quantize_acts.argtypes = [vp, sz, i64, i64, vp, vp]
     lib.b200_mul_mat_vec_q.restype = i32
@@ -203,25 +205,26 @@ class Kernels:
                                             ws.data_ptr(), ws.numel(), self._stream()), "mul_mat_q")
         return out
 
-    def mul_mat(self, t: str, w, m: int, k: int, x, out=None):
+    def mul_mat(self, t: str, w, m: int, k: int, x, out=None, const_weights: bool = False, w_row_stride: Optional[int] = None):
         """ggml_mul_mat(W[k,m] quantized, X[k,n] f32) -> [m,n] stored as an (n, m) row-major tensor."""
         n = x.shape[0]
         ne_a = [k, m, 1, 1]
-        rb = row_bytes(t, k)
+        rb = w_row_stride or row_bytes(t, k)
         nb_a = [BLOCK_BYTES[t], rb, rb * m, rb * m]
         ne_b = [k, n, 1, 1]
         sb = x.stride(0) * 4
         nb_b = [4, sb, sb * n, sb * n]
-        return self.mul_mat_4d(t, w, ne_a, nb_a, x, ne_b, nb_b, out)
+        return self.mul_mat_4d(t, w, ne_a, nb_a, x, ne_b, nb_b, out, flags=1 if const_weights else 0)
 
-    def mul_mat_4d(self, t: str, a, ne_a, nb_a, b, ne_b, nb_b, out=None):
+    def mul_mat_4d(self, t: str, a, ne_a, nb_a, b, ne_b, nb_b, out=None, flags: int = 0):
         torch = self.torch
         if out is None:
             out = torch.empty((ne_b[3], ne_b[2], ne_b[1], ne_a[1]), dtype=torch.float32, device=self.device)
         nbytes = int(self.lib.b200_mul_mat_workspace_size(TYPE_ID[t], _a4i(ne_a), _a4i(ne_b)))
         ws = self.workspace(nbytes)
-        self._check(self.lib.b200_mul_mat(TYPE_ID[t], a.data_ptr(), _a4i(ne_a), _a4s(nb_a), b.data_ptr(), _a4i(ne_b),
-                                          _a4s(nb_b), out.data_ptr(), ws.data_ptr(), ws.numel(), self._stream()), "mul_mat")
+        self._check(self.lib.b200_mul_mat_ex(TYPE_ID[t], a.data_ptr(), _a4i(ne_a), _a4s(nb_a), b.data_ptr(), _a4i(ne_b),
+                                             _a4s(nb_b), out.data_ptr(), ws.data_ptr(), ws.numel(), flags, self._stream()),
+                    "mul_mat")
         return out
 
     def mul_mat_batch(self, nodes, count: Optional[int] = None, ws=None):

@@ -9,6 +9,7 @@
 #include "common.cuh"
 #include "unpack.cuh"
 #include "mmvq_stream.cuh"
+#include "mmvq_fused.cuh"
 
 namespace b200 {
 
@@ -140,6 +141,12 @@ extern "C" size_t b200_mul_mat_workspace_size(int type_a, const int64_t ne_a[4],
 extern "C" int b200_mul_mat(int type_a, const void * a_dev, const int64_t ne_a[4], const size_t nb_a[4],
                             const float * b_dev, const int64_t ne_b[4], const size_t nb_b[4],
                             float * dst_dev, void * workspace_dev, size_t workspace_bytes, void * stream) {
+    return b200_mul_mat_ex(type_a, a_dev, ne_a, nb_a, b_dev, ne_b, nb_b, dst_dev, workspace_dev, workspace_bytes, 0, stream);
+}
+
+extern "C" int b200_mul_mat_ex(int type_a, const void * a_dev, const int64_t ne_a[4], const size_t nb_a[4],
+                               const float * b_dev, const int64_t ne_b[4], const size_t nb_b[4],
+                               float * dst_dev, void * workspace_dev, size_t workspace_bytes, uint32_t flags, void * stream) {
     if (!type_is_quant(type_a)) return B200_ERR_TYPE;
     const int64_t k = ne_a[0], m = ne_a[1], n = ne_b[1];
     for (int i = 0; i < 4; i++) if (ne_a[i] < 0 || ne_b[i] < 0) return B200_ERR_SHAPE;
@@ -155,6 +162,12 @@ extern "C" int b200_mul_mat(int type_a, const void * a_dev, const int64_t ne_a[4
     if (workspace_bytes < b200_mul_mat_workspace_size(type_a, ne_a, ne_b) || !workspace_dev) return B200_ERR_WORKSPACE;
     uint8_t * ws = (uint8_t *) (((uintptr_t) workspace_dev + 255) & ~(uintptr_t) 255);
 
+    if (n == 1 && ne12 == 1 && ne13 == 1) {
+        // decode fast path: activation quantization fused into the mat-vec, one launch
+        const int rc = mmvq_fused_try(type_a, (const uint8_t *) a_dev, (int64_t) nb_a[1], m, k, b_dev, dst_dev,
+                                      (flags & B200_MUL_MAT_CONST_WEIGHTS) != 0, st);
+        if (rc != B200_STREAM_NOT_APPLICABLE) return rc;
+    }
     if (n <= B200_MMVQ_MAX_N) {
         // quantize every activation column once: scratch column index = (i13*ne12 + i12)*n + j
         const int64_t cols = n * ne12 * ne13;
@@ -201,9 +214,12 @@ extern "C" int b200_mul_mat_batch(const b200_mul_mat_node * nodes, int64_t count
     if (count < 0 || (count > 0 && !nodes)) return B200_ERR_SHAPE;
     for (int64_t i = 0; i < count; i++) {
         const b200_mul_mat_node & nd = nodes[i];
-        const int rc = b200_mul_mat(nd.type_a, nd.a_dev, nd.ne_a, nd.nb_a, nd.b_dev, nd.ne_b, nd.nb_b, nd.dst_dev,
-                                    workspace_dev, workspace_bytes, stream);
+        const int rc = b200_mul_mat_ex(nd.type_a, nd.a_dev, nd.ne_a, nd.nb_a, nd.b_dev, nd.ne_b, nd.nb_b, nd.dst_dev,
+                                       workspace_dev, workspace_bytes, nd.flags, stream);
         if (rc) return rc;
     }
     return B200_OK;
 }
+
+// tuning aid used by tools/: every fused decode launch writes 8 globaltimer stamps per CTA into buf
+extern "C" __attribute__((visibility("default"))) void b200_debug_timestamps(void * buf) { g_fused_dbg = (unsigned long long *) buf; }

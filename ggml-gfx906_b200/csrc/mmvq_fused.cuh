@@ -38,6 +38,11 @@ __device__ __forceinline__ int dp4a_us(uint32_t a, int b, int c) {
     return d;
 }
 
+__device__ __forceinline__ unsigned long long gtime() {
+    unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t;
+}
+#define FUSED_STAMP(slot) do { if (a.dbg && lane == 0) a.dbg[(size_t) blockIdx.x * 8 + (slot)] = gtime(); } while (0)
+
 constexpr int FUSED_RB = 2;          // rows a warp carries at once (one shuffle tree per pair)
 
 // ---------------------------------------------------------------- q8 activations of one item
@@ -132,5 +137,342 @@ template <> struct hitem<T_Q5_K> {
         return d * fd - dmin * fm;
     }
 };
+
+// ================================================================= the kernel
+struct fused_args {
+    const uint8_t * w;        // weight rows
+    int64_t row_stride;       // bytes between rows
+    int64_t m;                // rows
+    const float * x;          // activations, k floats, 16-byte aligned
+    float * dst;              // m floats
+    int     k;
+    int     row_bytes;        // bytes of one row
+    int     items;            // 128-weight items per row (k / 128)
+    int     rows_per_cta;
+    int     R, S;             // rows per stage, stages
+    int     W, G;             // warps per row group, row groups per CTA (consumer warps = W * G)
+    int     slot_stride;      // bytes per stage slot (multiple of 128)
+    int     off_part, off_yq, off_yd, off_ys, off_slots;   // shared-memory byte offsets
+    int     contiguous;       // rows back to back in memory -> one bulk copy per stage
+    int     row_pitch;        // non-contiguous: bytes between rows inside a slot (multiple of 16)
+    int     early_weights;    // weights are constant: request them before the grid dependency resolves
+    int     dbg_mode;         // tuning aid: 1 = skip the dot products, 2 = skip the quantization
+    unsigned long long * dbg; // tuning aid: per-CTA globaltimer stamps (NULL in normal use)
+};
+
+constexpr int FUSED_MAX_WARPS = 10;   // up to 9 consumer warps + the producer
+constexpr int FUSED_MAX_STAGES = 16;
+
+template <int T, int IPL>
+__global__ void __launch_bounds__(FUSED_MAX_WARPS * 32)
+k_mmvq_fused(const fused_args a) {
+    using IT = hitem<T>;
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint64_t * full  = reinterpret_cast<uint64_t *>(smem);
+    uint64_t * empty = full + FUSED_MAX_STAGES;
+    float    * part  = reinterpret_cast<float *>(smem + a.off_part);
+    int8_t   * yq    = reinterpret_cast<int8_t *>(smem + a.off_yq);
+    float    * yd    = reinterpret_cast<float *>(smem + a.off_yd);
+    int      * ys    = reinterpret_cast<int *>(smem + a.off_ys);
+    uint8_t  * slots = smem + a.off_slots;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int W = a.W, G = a.G, NWC = W * G;
+    const int R = a.R, S = a.S;
+    const int64_t r_begin = (int64_t) blockIdx.x * a.rows_per_cta;
+    const int nrows = (int) ((a.m - r_begin < a.rows_per_cta) ? (a.m - r_begin) : a.rows_per_cta);
+    const int nbatch = (nrows + R - 1) / R;
+
+    if (tid == 0) {
+        for (int s = 0; s < S; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], (uint32_t) NWC); }
+        mbar_fence_init();
+    }
+    __syncthreads();
+    pdl_launch();
+
+    if (warp == NWC) {
+        // ===================================================== producer: weight rows -> stage ring
+        // The WHOLE warp waits on the empty barrier and lane 0 issues: an mbarrier wait executed by a
+        // single lane is only released when its suspend time limit runs out (~0.4 us measured with
+        // tools/stream_probe.cu), which throttles the ring to one slot per time-out.
+        if (lane == 0) FUSED_STAMP(0);
+        if (!a.early_weights) pdl_wait();
+        for (int b = 0; b < nbatch; b++) {
+            const int s = b % S;
+            if (b >= S) mbar_wait(&empty[s], (uint32_t) (((b / S) - 1) & 1));
+            if (lane == 0) {
+                const int rows_here = (nrows - b * R < R) ? (nrows - b * R) : R;
+                const uint8_t * src = a.w + (r_begin + (int64_t) b * R) * a.row_stride;
+                uint8_t * slot = slots + (size_t) s * a.slot_stride;
+                if (a.dbg && blockIdx.x == 0 && b < 120) a.dbg[2048 + b] = gtime();
+                if (a.contiguous) {
+                    const uint32_t off = (uint32_t) (reinterpret_cast<uintptr_t>(src) & 15);
+                    const uint32_t bytes = (off + (uint32_t) rows_here * (uint32_t) a.row_bytes + 15u) & ~15u;
+                    mbar_arrive_expect_tx(&full[s], bytes);
+                    bulk_g2s(slot, src - off, bytes, &full[s]);
+                } else {
+                    uint32_t total = 0;
+                    for (int r = 0; r < rows_here; r++) {
+                        const uint32_t off = (uint32_t) (reinterpret_cast<uintptr_t>(src + r * a.row_stride) & 15);
+                        total += (off + (uint32_t) a.row_bytes + 15u) & ~15u;
+                    }
+                    mbar_arrive_expect_tx(&full[s], total);
+                    for (int r = 0; r < rows_here; r++) {
+                        const uint8_t * p = src + r * a.row_stride;
+                        const uint32_t off = (uint32_t) (reinterpret_cast<uintptr_t>(p) & 15);
+                        bulk_g2s(slot + r * a.row_pitch, p - off, (off + (uint32_t) a.row_bytes + 15u) & ~15u, &full[s]);
+                    }
+                }
+            }
+            __syncwarp();
+        }
+        return;
+    }
+
+    // ========================================================= consumers
+    // 1. quantize x (bit-exact quantize_row_q8_1_ref values) into shared memory: 8 lanes per q8 block
+    pdl_wait();
+    if (warp == 0) FUSED_STAMP(1);
+    if (!(a.dbg_mode & 2)) {
+        const int nblk32 = a.k >> 5;
+        const int sub = lane >> 3, l8 = lane & 7;
+        constexpr int U = 4;                                  // loads in flight per lane
+        for (int blk0 = warp * 4 + sub; blk0 < nblk32; blk0 += NWC * 4 * U) {
+            float4 vv[U];
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                const int blk = blk0 + u * NWC * 4;
+                if (blk < nblk32) vv[u] = __ldg(reinterpret_cast<const float4 *>(a.x + blk * 32 + l8 * 4));
+            }
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                const int blk = blk0 + u * NWC * 4;
+                if (blk >= nblk32) break;                     // warp-uniform: k % 128 == 0
+                const float4 v = vv[u];
+                float amax = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
+#pragma unroll
+                for (int o = 1; o < 8; o <<= 1) amax = fmaxf(amax, __shfl_xor_sync(0xFFFFFFFFu, amax, o));
+                const float d  = __fdiv_rn(amax, 127.0f);
+                const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+                const float xs[4] = { v.x, v.y, v.z, v.w };
+                uint32_t packed = 0;
+                int sum = 0;
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    // float -> int8 as quantize.cu does it (cvttss2si semantics of the reference's x86 build)
+                    const float r  = roundf(__fmul_rn(xs[j], id));
+                    const int   qi = fabsf(r) < 2147483648.0f ? (int) r : (int) 0x80000000;
+                    const int   q  = (int) (int8_t) (qi & 0xFF);
+                    packed |= (uint32_t) (q & 0xFF) << (8 * j);
+                    sum += q;
+                }
+#pragma unroll
+                for (int o = 1; o < 8; o <<= 1) sum += __shfl_xor_sync(0xFFFFFFFFu, sum, o);
+                *reinterpret_cast<uint32_t *>(yq + blk * 32 + l8 * 4) = packed;
+                if (l8 == 0) { yd[blk] = __half2float(__float2half_rn(d)); ys[blk] = sum; }
+            }
+        }
+    }
+    named_bar_sync(1, NWC * 32);
+    if (warp == 0) FUSED_STAMP(2);
+
+    // 2. the slice of K this lane owns, in registers
+    const int g = warp / W, wg = warp - g * W;
+    acts128 acts[IPL];
+#pragma unroll
+    for (int i = 0; i < IPL; i++) {
+        const int idx = (i * W + wg) * 32 + lane;
+        if (idx < a.items) {
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int4 lo = *reinterpret_cast<const int4 *>(yq + idx * 128 + 32 * j);
+                const int4 hi = *reinterpret_cast<const int4 *>(yq + idx * 128 + 32 * j + 16);
+                acts[i].q[j][0] = lo.x; acts[i].q[j][1] = lo.y; acts[i].q[j][2] = lo.z; acts[i].q[j][3] = lo.w;
+                acts[i].q[j][4] = hi.x; acts[i].q[j][5] = hi.y; acts[i].q[j][6] = hi.z; acts[i].q[j][7] = hi.w;
+                const float d = yd[idx * 4 + j];
+                acts[i].sd[j] = d * (float) ys[idx * 4 + j];
+                acts[i].d[j]  = (IT::hi_div16 && (j & 1)) ? d * 0.0625f : d;
+            }
+        }
+    }
+
+    // 3. stream the rows
+    int work_it = 0;                  // stages in which this group had rows: parity selects the partials buffer
+    for (int b = 0; b < nbatch; b++) {
+        const int s = b % S;
+        mbar_wait(&full[s], (uint32_t) ((b / S) & 1));      // every lane waits (see the producer's note)
+        if (warp == 0 && b == 0) FUSED_STAMP(3);
+        if (a.dbg && blockIdx.x == 0 && warp == 0 && lane == 0 && b < 120) a.dbg[2048 + 128 + b] = gtime();
+        if (warp == 0 && b == nbatch - 1) FUSED_STAMP(4);
+        const int rows_here = (nrows - b * R < R) ? (nrows - b * R) : R;
+        const uint8_t * slot = slots + (size_t) s * a.slot_stride;
+        const uint8_t * src0 = a.w + (r_begin + (int64_t) b * R) * a.row_stride;
+        const int nchunks = (rows_here + FUSED_RB - 1) / FUSED_RB;
+        float * pb = part + (size_t) (g * 2 + (work_it & 1)) * R * W;      // per group: groups work on different slots at once
+        // chunks (row pairs) are dealt to the groups round-robin over the CTA's whole slab, not per slot
+        const int c_first = (g - (b * (R / FUSED_RB)) % G + G) % G;
+
+        for (int c = c_first; c < nchunks && !(a.dbg_mode & 1); c += G) {
+            const int r0 = c * FUSED_RB;
+            float acc[FUSED_RB];
+#pragma unroll
+            for (int rr = 0; rr < FUSED_RB; rr++) acc[rr] = 0.0f;
+#pragma unroll
+            for (int i = 0; i < IPL; i++) {
+                const int idx = (i * W + wg) * 32 + lane;
+                if (idx < a.items) {
+                    typename IT::wts w[FUSED_RB];
+#pragma unroll
+                    for (int rr = 0; rr < FUSED_RB; rr++) {
+                        const int r = (r0 + rr < rows_here) ? (r0 + rr) : (rows_here - 1);   // odd tail: recompute, never stored
+                        const uint8_t * row = a.contiguous
+                            ? slot + (reinterpret_cast<uintptr_t>(src0) & 15) + (size_t) r * a.row_bytes
+                            : slot + (size_t) r * a.row_pitch + (reinterpret_cast<uintptr_t>(src0 + r * a.row_stride) & 15);
+                        IT::load(w[rr], row, idx);
+                    }
+#pragma unroll
+                    for (int rr = 0; rr < FUSED_RB; rr++) acc[rr] += IT::dot(w[rr], idx & 1, acts[i]);
+                }
+            }
+            // one shuffle tree for the row pair: lanes 0-15 end with row r0, lanes 16-31 with row r0 + 1
+            float v = (lane & 16) ? acc[1] : acc[0];
+            const float o = (lane & 16) ? acc[0] : acc[1];
+            v += __shfl_xor_sync(0xFFFFFFFFu, o, 16);
+#pragma unroll
+            for (int off = 8; off > 0; off >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, off);
+            const int r = r0 + (lane >> 4);
+            if ((lane & 15) == 0 && r < rows_here) {
+                if (W == 1) a.dst[r_begin + (int64_t) b * R + r] = v;
+                else        pb[r * W + wg] = v;
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cta(&empty[s]);          // this warp is done with the slot
+        if (a.dbg && blockIdx.x == 0 && warp == NWC - 1 && lane == 0 && b < 120) a.dbg[2048 + 256 + b] = gtime();
+        if (c_first < nchunks) work_it++;
+        if (W > 1 && c_first < nchunks) {
+            // the W warps of the group meet; warp 0 of the group adds the partials in fixed order.  The
+            // buffer written two working stages later is only touched after the barrier in between,
+            // which warp 0 reaches after these reads.
+            named_bar_sync(2 + g, W * 32);
+            if (wg == 0) {
+                for (int j = lane; ; j += 32) {
+                    const int c = c_first + (j / FUSED_RB) * G;
+                    const int r = c * FUSED_RB + (j % FUSED_RB);
+                    if (c >= nchunks) break;
+                    if (r < rows_here) {
+                        float v = 0.0f;
+                        for (int u = 0; u < W; u++) v += pb[r * W + u];
+                        a.dst[r_begin + (int64_t) b * R + r] = v;
+                    }
+                }
+            }
+        }
+    }
+    if (warp == 0) FUSED_STAMP(5);
+}
+
+} // namespace b200
+
+namespace b200 {
+
+// ================================================================= host side
+static unsigned long long * g_fused_dbg = nullptr;   // set through b200_debug_timestamps (tools/ only)
+
+template <int T, int IPL>
+static int launch_fused(fused_args a, cudaStream_t st) {
+    const dev_caps & caps = current_caps();
+    const int ring_env = env_int("GGML_B200_FUSED_RING_BYTES", 98304);   // two kernels' CTAs share an SM
+    const int slot_env = env_int("GGML_B200_FUSED_SLOT_BYTES", 9216);
+    const int cps_env  = env_int("GGML_B200_FUSED_CTAS_PER_SM", 1);
+    const int pdl      = env_int("GGML_B200_FUSED_PDL", 1);
+
+    int mult = slot_env / (FUSED_RB * a.row_bytes);
+    if (mult < 1) mult = 1;
+    a.R = FUSED_RB * mult;
+    a.row_pitch = (a.row_bytes + 15 + 15 + 16) & ~15;
+    const int slot_bytes = a.contiguous ? (15 + a.R * a.row_bytes + 15 + 16) : a.R * a.row_pitch;
+    a.slot_stride = (slot_bytes + 127) & ~127;
+    a.off_part  = 2 * FUSED_MAX_STAGES * 8;
+    a.off_yq    = (a.off_part + a.G * 2 * a.R * a.W * (int) sizeof(float) + 15) & ~15;
+    a.off_yd    = a.off_yq + a.k;
+    a.off_ys    = a.off_yd + (a.k / 32) * 4;
+    a.off_slots = (a.off_ys + (a.k / 32) * 4 + 127) & ~127;
+    a.S = ring_env / a.slot_stride;
+    if (a.S < 2) a.S = 2;
+    if (a.S > FUSED_MAX_STAGES) a.S = FUSED_MAX_STAGES;
+    const int cps = cps_env < 1 ? 1 : cps_env;
+    const size_t smem = (size_t) a.off_slots + (size_t) a.S * a.slot_stride;
+    if (smem > (size_t) caps.smem_optin) return B200_STREAM_NOT_APPLICABLE;
+
+    auto kern = k_mmvq_fused<T, IPL>;
+    static size_t smem_set[64];
+    int dev = 0; cudaGetDevice(&dev); if (dev < 0 || dev >= 64) dev = 0;
+    if (smem > smem_set[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+        if (e != cudaSuccess) return -(int) e;
+        smem_set[dev] = smem;
+    }
+    int64_t grid = (int64_t) caps.sm_count * cps;
+    const int64_t max_grid = ceil_div(a.m, FUSED_RB);
+    if (grid > max_grid) grid = max_grid;
+    a.rows_per_cta = (int) ceil_div(a.m, grid);
+    grid = ceil_div(a.m, a.rows_per_cta);
+
+    static bool carve_set[64];
+    if (!carve_set[dev]) {
+        // two kernels' CTAs must fit an SM at once (the next mat-vec prefetches while this one computes)
+        cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        carve_set[dev] = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned) grid); cfg.blockDim = dim3((unsigned) ((a.W * a.G + 1) * 32));
+    cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, a);
+    if (e != cudaSuccess) return -(int) e;
+    b200_count_launch(1);
+    return B200_OK;
+}
+
+template <int T>
+static int launch_fused_t(fused_args a, cudaStream_t st) {
+    if (!hitem<T>::ok(a.k, a.row_stride, reinterpret_cast<uintptr_t>(a.w))) return B200_STREAM_NOT_APPLICABLE;
+    a.items = a.k / 128;
+    const int passes = (int) ceil_div(a.items, 32);             // warp-passes one row needs
+    if (passes <= 8) {
+        a.W = passes; a.G = 9 / passes;                         // up to 9 consumer warps
+        return launch_fused<T, 1>(a, st);
+    }
+    if (passes <= 16) {
+        a.W = (passes + 1) / 2; a.G = 1;
+        return launch_fused<T, 2>(a, st);
+    }
+    return B200_STREAM_NOT_APPLICABLE;
+}
+
+// dst[m] = W[m, k] . x[k]; returns B200_OK, B200_STREAM_NOT_APPLICABLE (caller falls back) or an error.
+static int mmvq_fused_try(int type, const uint8_t * w, int64_t row_stride, int64_t m, int64_t k,
+                          const float * x, float * dst, bool const_weights, cudaStream_t st) {
+    if (env_int("GGML_B200_MMVQ_NO_FUSED", 0)) return B200_STREAM_NOT_APPLICABLE;
+    if (m < 1 || k < 1024 || k % 256 != 0 || k > 131072) return B200_STREAM_NOT_APPLICABLE;
+    if (reinterpret_cast<uintptr_t>(x) % 16 != 0) return B200_STREAM_NOT_APPLICABLE;
+    const int64_t row_bytes = k / type_qk(type) * type_bytes(type);
+    if (row_stride < row_bytes) return B200_STREAM_NOT_APPLICABLE;
+    fused_args a = {};
+    a.w = w; a.row_stride = row_stride; a.m = m; a.x = x; a.dst = dst; a.k = (int) k; a.row_bytes = (int) row_bytes;
+    a.contiguous = row_stride == row_bytes ? 1 : 0;
+    a.early_weights = const_weights ? 1 : 0;
+    a.dbg = g_fused_dbg;
+    a.dbg_mode = env_int("GGML_B200_FUSED_DBG_MODE", 0);
+    switch (type) {
+        case T_Q4_K: return launch_fused_t<T_Q4_K>(a, st);
+        case T_Q5_K: return launch_fused_t<T_Q5_K>(a, st);
+        default: return B200_STREAM_NOT_APPLICABLE;
+    }
+}
 
 } // namespace b200

@@ -120,6 +120,16 @@ B200_API int    b200_mul_mat(int type_a, const void * a_dev, const int64_t ne_a[
                              const float * b_dev, const int64_t ne_b[4], const size_t nb_b[4],
                              float * dst_dev, void * workspace_dev, size_t workspace_bytes, void * stream);
 
+/* b200_mul_mat with flags.  B200_MUL_MAT_CONST_WEIGHTS: a_dev is not written by any work queued
+ * before this call on `stream` (model weights; ggml marks such buffers
+ * GGML_BACKEND_BUFFER_USAGE_WEIGHTS, include/ggml-backend.h:38-42) — the decode kernel may then
+ * request weight rows before the preceding kernel has finished (programmatic dependent launch). */
+#define B200_MUL_MAT_CONST_WEIGHTS 1u
+B200_API int    b200_mul_mat_ex(int type_a, const void * a_dev, const int64_t ne_a[4], const size_t nb_a[4],
+                                const float * b_dev, const int64_t ne_b[4], const size_t nb_b[4],
+                                float * dst_dev, void * workspace_dev, size_t workspace_bytes,
+                                uint32_t flags, void * stream);
+
 /* A whole list of MUL_MAT nodes in one call, issued back to back on `stream` in list order.
  * replaces the node loop of ggml_backend_cuda_graph_compute -> evaluate_and_capture_cuda_graph ->
  * ggml_cuda_compute_forward (src/ggml-cuda/ggml-cuda.cu:2226-2520, 2870-2960) for graphs made of
@@ -128,7 +138,7 @@ B200_API int    b200_mul_mat(int type_a, const void * a_dev, const int64_t ne_a[
  * Returns the first error; nodes before it have been enqueued. */
 typedef struct b200_mul_mat_node {
     int32_t       type_a;
-    int32_t       reserved;
+    uint32_t      flags;      /* B200_MUL_MAT_* */
     const void  * a_dev;
     int64_t       ne_a[4];
     size_t        nb_a[4];

@@ -276,6 +276,86 @@ def test_mul_mat_4d_permuted_b(kern, oracle, t):
         assert oracle.nmse(want, got[0, i12]) <= NMSE_ORACLE, i12
 
 
+# ---------------------------------------------------------------------------- MUL_MAT n = 1: the fused decode kernel
+FUSED_TYPES = ["q4_K", "q5_K"]
+FUSED_SHAPES = [(1, 1024), (2, 1024), (3, 4096), (37, 1280), (600, 4096), (1000, 2048), (129, 8192), (300, 11008),
+                (77, 14336), (40, 28672), (20, 32768), (5000, 4096)]
+
+
+@pytest.mark.parametrize("t", FUSED_TYPES)
+@pytest.mark.parametrize("m,k", FUSED_SHAPES)
+def test_mul_mat_fused_decode_vs_oracle(kern, oracle, monkeypatch, t, m, k):
+    """b200_mul_mat with n = 1 takes the fused quantize + mat-vec kernel (mmvq_fused.cuh): same q8_1
+    arithmetic as the two-kernel path -> NMSE 1e-9 to oracle mode 1, and row r is bit-identical to the
+    two-kernel path's partial-order-independent value only up to f32 summation order, so the cross
+    check between the two paths is NMSE as well."""
+    w = random_blocks(t, m, k, seed=3 * m + k)
+    x = np.random.default_rng(m + k).uniform(-1, 1, size=(1, k)).astype(np.float32)
+    wd, xd = dev_blocks(kern, w), kern.to_device(x)
+    want = oracle.mul_mat(t, w, m, k, x, mode=1)
+    for const in (False, True):
+        got = kern.mul_mat(t, wd, m, k, xd, const_weights=const).cpu().numpy().reshape(1, m)
+        assert np.isfinite(got).all()
+        assert oracle.nmse(want, got) <= NMSE_ORACLE, (const, oracle.nmse(want, got))
+    monkeypatch.setenv("GGML_B200_MMVQ_NO_FUSED", "1")
+    two = kern.mul_mat(t, wd, m, k, xd).cpu().numpy().reshape(1, m)
+    monkeypatch.delenv("GGML_B200_MMVQ_NO_FUSED")
+    assert oracle.nmse(two, got) <= NMSE_ORACLE
+
+
+@pytest.mark.parametrize("t", FUSED_TYPES)
+def test_mul_mat_fused_decode_adversarial_scales_and_activations(kern, oracle, t):
+    """edge scale fields (0, subnormal, max, sc = m = 63) and activations with zero blocks, a single
+    outlier and +-x.5 ties (the q8_1 rounding contract)."""
+    m, k = 64, 4096
+    w = adversarial_blocks(t, m, k, seed=11)
+    x = np.random.default_rng(12).standard_normal(size=(1, k)).astype(np.float32)
+    x[0, :64] = 0.0
+    x[0, 100] = 1000.0
+    x[0, 128:160] = (np.arange(32) - 16 + 0.5) * (127.0 / 15.5) / 127.0
+    got = kern.mul_mat(t, dev_blocks(kern, w), m, k, kern.to_device(x)).cpu().numpy().reshape(1, m)
+    want = oracle.mul_mat(t, w, m, k, x, mode=1)
+    fin = np.isfinite(want)
+    assert np.array_equal(np.isfinite(got), fin)
+    assert oracle.nmse(want[fin], got[fin]) <= NMSE_ORACLE
+
+
+@pytest.mark.parametrize("t", FUSED_TYPES)
+def test_mul_mat_fused_decode_row_stride_and_row_independence(kern, oracle, t):
+    """strided weight view (row stride 2x) and the row-split property: a row's value does not depend
+    on which other rows the launch covers (bit-identical sub-matrix results)."""
+    m, k = 211, 4096
+    rb = k // BLOCK_ELEMS[t] * BLOCK_BYTES[t]
+    w = random_blocks(t, m, k, seed=5)
+    x = np.random.default_rng(6).uniform(-1, 1, size=(1, k)).astype(np.float32)
+    xd = kern.to_device(x)
+    full = kern.mul_mat(t, dev_blocks(kern, w), m, k, xd).cpu().numpy().reshape(m)
+    buf = np.zeros(m * 2 * rb + 64, dtype=np.uint8)
+    for r in range(m):
+        buf[r * 2 * rb: r * 2 * rb + rb] = w[r]
+    strided = kern.mul_mat(t, kern.to_device(buf), m, k, xd, w_row_stride=2 * rb).cpu().numpy().reshape(m)
+    assert np.array_equal(u32(full), u32(strided))
+    lo, hi = 64, 173
+    part = kern.mul_mat(t, dev_blocks(kern, w[lo:hi]), hi - lo, k, xd).cpu().numpy().reshape(hi - lo)
+    assert np.array_equal(u32(part), u32(full[lo:hi]))
+
+
+def test_mul_mat_batch_matches_single_calls(kern, oracle):
+    import b200
+    import torch
+    mats = [("q4_K", 300, 4096), ("q5_K", 128, 2048), ("q6_K", 64, 1024), ("q4_0", 96, 512), ("q4_K", 17, 11008)]
+    ws = [dev_blocks(kern, random_blocks(t, m, k, seed=i)) for i, (t, m, k) in enumerate(mats)]
+    xs = [kern.to_device(np.random.default_rng(i).uniform(-1, 1, size=(1, k)).astype(np.float32)) for i, (t, m, k) in enumerate(mats)]
+    ys = [torch.zeros((1, m), dtype=torch.float32, device=kern.device) for (t, m, k) in mats]
+    nodes = (b200.MulMatNode * len(mats))(*[
+        b200.mul_mat_node(t, w.data_ptr(), m, k, x.data_ptr(), 1, y.data_ptr(), const_weights=True)
+        for (t, m, k), w, x, y in zip(mats, ws, xs, ys)])
+    kern.mul_mat_batch(nodes)
+    for (t, m, k), w, x, y in zip(mats, ws, xs, ys):
+        single = kern.mul_mat(t, w, m, k, x)
+        assert np.array_equal(u32(single.cpu().numpy().reshape(-1)), u32(y.cpu().numpy().reshape(-1))), (t, m, k)
+
+
 # ---------------------------------------------------------------------------- full-size (BASELINE.json configs)
 FULL = [("q4_0", 4096, 4096), ("q4_K", 4096, 4096), ("q4_K", 11008, 4096), ("q4_K", 4096, 11008),
         ("q5_K", 4096, 11008), ("q6_K", 4096, 11008), ("q6_K", 32000, 4096), ("q8_0", 11008, 4096)]
