@@ -10,6 +10,9 @@
 #include "unpack.cuh"
 #include "mmvq_stream.cuh"
 #include "mmvq_fused.cuh"
+#include "mmvq_batch.cuh"
+
+#include <vector>
 
 namespace b200 {
 
@@ -201,24 +204,91 @@ extern "C" int b200_mul_mat_ex(int type_a, const void * a_dev, const int64_t ne_
 
 // ---------------------------------------------------------------- a list of MUL_MAT nodes
 extern "C" size_t b200_mul_mat_batch_workspace_size(const b200_mul_mat_node * nodes, int64_t count) {
-    size_t need = 256;
+    // the largest single-node need + one q8 activation record per decode node (persistent launches)
+    size_t need = 256, acts = 0;
     for (int64_t i = 0; i < count; i++) {
         const size_t s = b200_mul_mat_workspace_size(nodes[i].type_a, nodes[i].ne_a, nodes[i].ne_b);
         if (s > need) need = s;
+        if (nodes[i].ne_b[1] == 1 && nodes[i].ne_a[0] > 0) acts += batch_acts_record_bytes(nodes[i].ne_a[0]);
     }
-    return need;
+    return need + acts + 256;
+}
+
+// Pointer ranges a pending persistent launch reads (x) and writes (dst): a node joins the launch only if
+// it neither reads nor writes what an earlier node of the launch writes, nor writes what one reads.
+namespace {
+struct range_set {
+    struct iv { uintptr_t lo, hi; };
+    std::vector<iv> v;
+    uintptr_t lo = ~(uintptr_t) 0, hi = 0;
+    void clear() { v.clear(); lo = ~(uintptr_t) 0; hi = 0; }
+    void add(uintptr_t a, uintptr_t b) { v.push_back({a, b}); if (a < lo) lo = a; if (b > hi) hi = b; }
+    bool hits(uintptr_t a, uintptr_t b) const {
+        if (a >= hi || b <= lo) return false;                 // outside the hull: the common case
+        for (const iv & i : v) if (a < i.hi && i.lo < b) return true;
+        return false;
+    }
+};
 }
 
 extern "C" int b200_mul_mat_batch(const b200_mul_mat_node * nodes, int64_t count,
                                   void * workspace_dev, size_t workspace_bytes, void * stream) {
     if (count < 0 || (count > 0 && !nodes)) return B200_ERR_SHAPE;
+    cudaStream_t st = (cudaStream_t) stream;
+    static const bool persistent = !env_int("GGML_B200_NO_BATCH_KERNEL", 0);
+    static thread_local batch_builder * bb = nullptr;         // 28 KB parameter block, reused
+    static thread_local range_set reads, writes;
+    if (!bb) bb = new batch_builder();
+    bb->reset((uint8_t *) workspace_dev, workspace_dev ? workspace_bytes : 0);
+    reads.clear(); writes.clear();
+    const int grid = current_caps().sm_count;
+    auto flush = [&]() -> int {
+        if (bb->empty()) return B200_OK;
+        reads.clear(); writes.clear();
+        int rc;
+        if (bb->args.count == 1 && !env_int("GGML_B200_BATCH_SINGLE", 0)) {
+            // one node: the per-node decode kernel (same per-row arithmetic, one launch instead of two)
+            const batch_node nd = bb->args.nodes[0];
+            rc = mmvq_fused_try(nd.type, nd.w, nd.row_stride, nd.m, nd.k, nd.x, nd.dst, bb->all_const, st);
+            if (rc == B200_STREAM_NOT_APPLICABLE) rc = batch_launch(*bb, st);
+        } else {
+            rc = batch_launch(*bb, st);
+        }
+        // stream order: the next launch's quantizer starts after this launch has finished with the workspace
+        bb->reset((uint8_t *) workspace_dev, workspace_dev ? workspace_bytes : 0);
+        return rc;
+    };
     for (int64_t i = 0; i < count; i++) {
         const b200_mul_mat_node & nd = nodes[i];
-        const int rc = b200_mul_mat_ex(nd.type_a, nd.a_dev, nd.ne_a, nd.nb_a, nd.b_dev, nd.ne_b, nd.nb_b, nd.dst_dev,
-                                       workspace_dev, workspace_bytes, nd.flags, stream);
+        const int64_t k = nd.ne_a[0], m = nd.ne_a[1];
+        const bool plain = persistent && type_is_quant(nd.type_a) && nd.ne_b[0] == k && nd.ne_b[1] == 1 &&
+                           nd.ne_a[2] == 1 && nd.ne_a[3] == 1 && nd.ne_b[2] == 1 && nd.ne_b[3] == 1 &&
+                           nd.nb_a[0] == (size_t) type_bytes(nd.type_a) && nd.nb_b[0] == sizeof(float) &&
+                           batch_node_ok(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, nd.b_dev);
+        if (plain) {
+            const uintptr_t x0 = (uintptr_t) nd.b_dev, x1 = x0 + (size_t) k * 4;
+            const uintptr_t d0 = (uintptr_t) nd.dst_dev, d1 = d0 + (size_t) m * 4;
+            if (bb->full() || writes.hits(x0, x1) || writes.hits(d0, d1) || reads.hits(d0, d1)) {
+                const int rc = flush();
+                if (rc) return rc;
+            }
+            const bool cw = (nd.flags & B200_MUL_MAT_CONST_WEIGHTS) != 0;
+            bool ok = bb->add(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, nd.b_dev, nd.dst_dev, cw, grid);
+            if (!ok && !bb->empty()) {                         // workspace full: launch what is pending, start over
+                const int rc = flush();
+                if (rc) return rc;
+                ok = bb->add(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, nd.b_dev, nd.dst_dev, cw, grid);
+            }
+            if (ok) { reads.add(x0, x1); writes.add(d0, d1); continue; }
+            // no room even for one record: the per-node path below reports the workspace error
+        }
+        int rc = flush();
+        if (rc) return rc;
+        rc = b200_mul_mat_ex(nd.type_a, nd.a_dev, nd.ne_a, nd.nb_a, nd.b_dev, nd.ne_b, nd.nb_b, nd.dst_dev,
+                             workspace_dev, workspace_bytes, nd.flags, stream);
         if (rc) return rc;
     }
-    return B200_OK;
+    return flush();
 }
 
 // tuning aid used by tools/: every fused decode launch writes 8 globaltimer stamps per CTA into buf

@@ -1,0 +1,429 @@
+// mmvq_batch.cuh — the persistent decode mat-vec: a whole LIST of independent n = 1 MUL_MATs in ONE launch.
+//
+//   for every node i:   dst_i[m_i] = W_i[m_i, k_i] (ggml quant blocks) . x_i[k_i] (f32)
+//
+// Why: a decode mat-vec is tiny next to a B200 (4096 x 4096 Q4_K = 9.4 MB = 1.3 us of HBM time, one
+// DRAM round trip of bytes per SM), so one launch per MUL_MAT (what the reference's graph loop does,
+// src/ggml-cuda/ggml-cuda.cu:2870-2960 -> mmvq.cu:500-570, plus a quantize_q8_1 launch each) spends most
+// of its time filling and draining the machine: measured 8 us per 4096^2 mat-vec = 1.2 TB/s
+// (profiles/r01b_mmvq_probe_per_launch.txt) against a 7.2 TB/s read ceiling for a TMA ring
+// (profiles/r01b_stream_probe.txt).  Here the machine is filled once per list:
+//
+//   * k_quantize_batch: ONE small launch turns every node's x into q8_1 values (bit-exact
+//     quantize_row_q8_1_ref, src/ggml-quants.c:225-258) in the caller's workspace: int8 plane [k] followed
+//     by the fp16-rounded scales as f32 [k/32] — 1.125 bytes per activation, nodes sharing x share it;
+//   * k_mmvq_batch: one CTA per SM, resident for the whole list; every node's rows are dealt to the CTAs as
+//     contiguous slabs (rotated per node so that short last slabs do not always hit the same SM);
+//       warp 0 (weight producer) streams the CTA's slabs of ALL nodes, back to back, through one ring of
+//         shared-memory stages with bulk async copies (cp.async.bulk, SASS UBLKCP) on full/empty
+//         mbarriers: the weights of node i+1.. are in flight while node i is reduced, HBM never idles;
+//       warp 1 (activation producer) bulk-copies the quantized activations of the next nodes into a small
+//         ring of activation buffers (ready/free mbarriers);
+//       9 consumer warps: a lane owns 128 consecutive weights of a row (hitem<T>, mmvq_fused.cuh) and keeps
+//         the matching q8 activations in registers for the node; W consecutive warps cover a row, the
+//         G = 9 / W groups take the row pairs of the stages round-robin; partials of a row meet in shared
+//         memory in fixed order, so a row's value never depends on the grid, the list or the GPU that
+//         computes it (row-split results stay bit-identical).  Every consumer warp observes every stage
+//         (mbarrier phases are parity bits: a waiter that skipped stages could mistake phase n-2 for n).
+//
+// Nodes of one launch must be independent (no node reads what another writes): b200_mul_mat_batch checks
+// the pointer ranges and cuts the list where they are not.
+#pragma once
+#include "mmvq_fused.cuh"
+
+namespace b200 {
+
+constexpr int BATCH_MAX_NODES  = 448;
+constexpr int BATCH_NWC        = 9;      // consumer warps
+constexpr int BATCH_THREADS    = (2 + BATCH_NWC) * 32;
+constexpr int BATCH_MAX_STAGES = 16;
+constexpr int BATCH_MAX_ABUF   = 4;      // activation buffers
+constexpr int BATCH_RMAX       = 16;     // rows per stage, at most
+constexpr int BATCH_ROT        = 61;     // slab rotation per node (coprime with the SM count)
+
+struct batch_node {                      // 64 bytes
+    const uint8_t * w;                   // first weight row
+    const float   * x;                   // k floats, 16-byte aligned
+    float         * dst;                 // m floats
+    const uint8_t * acts;                // quantized activations in the workspace: int8[k] | f32 d[k/32]
+    int64_t         row_stride;          // bytes between rows
+    int   m, k;
+    int   row_bytes;
+    int   rows_per_cta;                  // slab height (even)
+    unsigned char type, R, W, G, contiguous, quantize, pad[2];   // quantize: this node's x is not the previous node's
+};
+static_assert(sizeof(batch_node) == 64, "batch_node is part of the kernel parameter block");
+
+struct batch_args {
+    int count, S, slot_stride, acts_stride;
+    int off_part, off_acts, off_slots, const_weights;
+    int NB, kmax, pad[2];
+    batch_node nodes[BATCH_MAX_NODES];
+};
+
+__device__ __forceinline__ int batch_row_pitch(int row_bytes) { return (row_bytes + 15 + 15 + 16) & ~15; }
+__device__ __forceinline__ uint32_t batch_acts_bytes(int k) { return (uint32_t) (k + (k >> 5) * 4); }
+
+__device__ __forceinline__ void batch_slab(const batch_node & nd, int i, int & r_begin, int & nrows) {
+    const int v = (int) ((blockIdx.x + (unsigned) i * BATCH_ROT) % gridDim.x);
+    const int64_t rb = (int64_t) v * nd.rows_per_cta;
+    int64_t n = (int64_t) nd.m - rb;
+    if (n > nd.rows_per_cta) n = nd.rows_per_cta;
+    if (n < 0) n = 0;
+    r_begin = (int) (rb < nd.m ? rb : 0);
+    nrows = (int) n;
+}
+
+// ---------------------------------------------------------------- all activations of a list: f32 -> q8
+// grid (ceil(kmax / 32 / 8), count), block 256: one warp per 32 values (lane = element), as k_quantize_acts.
+__global__ void __launch_bounds__(256) k_quantize_batch(const __grid_constant__ batch_args a) {
+    const batch_node & nd = a.nodes[blockIdx.y];
+    const int kb = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (!nd.quantize || kb * 32 >= nd.k) return;
+    const float x = __ldg(nd.x + kb * 32 + lane);
+    const float amax = warp_max(fabsf(x));
+    const float d  = __fdiv_rn(amax, 127.0f);
+    const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+    // float -> int8 as quantize.cu does it (cvttss2si semantics of the reference's x86 build)
+    const float v  = roundf(__fmul_rn(x, id));
+    const int   qi = fabsf(v) < 2147483648.0f ? (int) v : (int) 0x80000000;
+    int8_t * q = reinterpret_cast<int8_t *>(const_cast<uint8_t *>(nd.acts));
+    q[kb * 32 + lane] = (int8_t) (qi & 0xFF);
+    if (lane == 0) reinterpret_cast<float *>(q + nd.k)[kb] = __half2float(__float2half_rn(d));
+}
+
+// ---------------------------------------------------------------- consumer: one node
+// cc: running count of row pairs ("chunks") this CTA has seen; chunk j belongs to group j % G.
+template <int T>
+__device__ __forceinline__ void batch_consume(const batch_args & a, const batch_node & nd, const int cw, const int lane,
+                                              const int r_begin, const int nrows, const int nbatch,
+                                              int & st_s, uint32_t & st_ph, int & cc,
+                                              const uint8_t * actbuf, uint64_t * acts_free, uint64_t * full, uint64_t * empty,
+                                              float * part, const uint8_t * slots) {
+    using IT = hitem<T>;
+    const int W = nd.W, G = nd.G, R = nd.R;
+    const int g = cw / W, wg = cw - g * W;
+    const int items = nd.k >> 7;
+    const int idx = wg * 32 + lane;                      // the 128-weight item of a row this lane owns
+    const bool active = g < G && idx < items;
+    const int row_pitch = batch_row_pitch(nd.row_bytes);
+
+    // the slice of K this lane owns, in registers for the node
+    acts128 acts;
+    if (active) {
+        const int8_t * yq = reinterpret_cast<const int8_t *>(actbuf);
+        const float  * yd = reinterpret_cast<const float *>(actbuf + nd.k);
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int4 lo = *reinterpret_cast<const int4 *>(yq + idx * 128 + 32 * j);
+            const int4 hi = *reinterpret_cast<const int4 *>(yq + idx * 128 + 32 * j + 16);
+            acts.q[j][0] = lo.x; acts.q[j][1] = lo.y; acts.q[j][2] = lo.z; acts.q[j][3] = lo.w;
+            acts.q[j][4] = hi.x; acts.q[j][5] = hi.y; acts.q[j][6] = hi.z; acts.q[j][7] = hi.w;
+            int sum = 0;
+#pragma unroll
+            for (int u = 0; u < 8; u++) sum = __dp4a(0x01010101, acts.q[j][u], sum);
+            const float d = yd[idx * 4 + j];
+            acts.sd[j] = d * (float) sum;
+            acts.d[j]  = (IT::hi_div16 && (j & 1)) ? d * 0.0625f : d;
+        }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive_cta(acts_free);            // this warp no longer reads the activation buffer
+
+    const int S = a.S;
+    int git = 0;                                          // stages in which this group had rows: selects the partials buffer
+    int cmod = cc % G;                                    // owner group of the next chunk
+    for (int lb = 0; lb < nbatch; lb++) {
+        const int s = st_s;
+        mbar_wait(&full[s], st_ph);                       // every lane polls (a single polling lane sleeps out its time slice)
+        if (++st_s == S) { st_s = 0; st_ph ^= 1u; }
+        const int rows_here = (nrows - lb * R < R) ? (nrows - lb * R) : R;
+        const int nchunks = (rows_here + FUSED_RB - 1) / FUSED_RB;
+        const int c_first = g >= cmod ? g - cmod : g - cmod + G;   // first chunk of this stage that belongs to group g
+        cc += nchunks;
+        cmod += nchunks;
+        while (cmod >= G) cmod -= G;
+        float * pb = part + (size_t) ((g * 2 + (git & 1)) * W) * BATCH_RMAX;
+        if (g < G && c_first < nchunks) {
+            const uint8_t * slot = slots + (size_t) s * a.slot_stride;
+            const uint8_t * src0 = nd.w + (int64_t) (r_begin + lb * R) * nd.row_stride;
+            for (int c = c_first; c < nchunks; c += G) {
+                const int r0 = c * FUSED_RB;
+                float acc[FUSED_RB];
+#pragma unroll
+                for (int rr = 0; rr < FUSED_RB; rr++) acc[rr] = 0.0f;
+                if (active) {
+                    typename IT::wts w[FUSED_RB];
+#pragma unroll
+                    for (int rr = 0; rr < FUSED_RB; rr++) {
+                        const int r = (r0 + rr < rows_here) ? (r0 + rr) : (rows_here - 1);   // odd tail: recomputed, never stored
+                        const uint8_t * row = nd.contiguous
+                            ? slot + (reinterpret_cast<uintptr_t>(src0) & 15) + (size_t) r * nd.row_bytes
+                            : slot + (size_t) r * row_pitch + (reinterpret_cast<uintptr_t>(src0 + r * nd.row_stride) & 15);
+                        IT::load(w[rr], row, idx);
+                    }
+#pragma unroll
+                    for (int rr = 0; rr < FUSED_RB; rr++) acc[rr] += IT::dot(w[rr], idx & 1, acts);
+                }
+                // one shuffle tree for the row pair: lanes 0-15 end with row r0, lanes 16-31 with row r0 + 1
+                float v = (lane & 16) ? acc[1] : acc[0];
+                const float o = (lane & 16) ? acc[0] : acc[1];
+                v += __shfl_xor_sync(0xFFFFFFFFu, o, 16);
+#pragma unroll
+                for (int off = 8; off > 0; off >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, off);
+                const int r = r0 + (lane >> 4);
+                if ((lane & 15) == 0 && r < rows_here) {
+                    if (W == 1) nd.dst[r_begin + lb * R + r] = v;
+                    else        pb[r * W + wg] = v;
+                }
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cta(&empty[s]);        // this warp is done with the stage
+        if (W > 1 && g < G && c_first < nchunks) {
+            // the W warps of the group meet; warp 0 of the group adds the partials in fixed order.  pb
+            // alternates per working stage of the group: the buffer written two working stages later is
+            // only touched after the barrier in between, which warp 0 reaches after these reads.
+            named_bar_sync(1 + g, W * 32);
+            if (wg == 0) {
+                for (int j = lane; ; j += 32) {
+                    const int c = c_first + (j / FUSED_RB) * G;
+                    const int r = c * FUSED_RB + (j % FUSED_RB);
+                    if (c >= nchunks) break;
+                    if (r < rows_here) {
+                        float v = 0.0f;
+                        for (int u = 0; u < W; u++) v += pb[r * W + u];
+                        nd.dst[r_begin + lb * R + r] = v;
+                    }
+                }
+            }
+            git++;
+        }
+    }
+}
+
+// ---------------------------------------------------------------- the persistent kernel
+__global__ void __launch_bounds__(BATCH_THREADS, 1)
+k_mmvq_batch(const __grid_constant__ batch_args a) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint64_t * full       = reinterpret_cast<uint64_t *>(smem);
+    uint64_t * empty      = full + BATCH_MAX_STAGES;
+    uint64_t * acts_ready = full + 2 * BATCH_MAX_STAGES;
+    uint64_t * acts_free  = acts_ready + BATCH_MAX_ABUF;
+    float    * part       = reinterpret_cast<float *>(smem + a.off_part);
+    uint8_t  * actbufs    = smem + a.off_acts;
+    uint8_t  * slots      = smem + a.off_slots;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int S = a.S, NB = a.NB;
+
+    if (tid == 0) {
+        for (int s = 0; s < S; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], BATCH_NWC); }
+        for (int u = 0; u < NB; u++) { mbar_init(&acts_ready[u], 1); mbar_init(&acts_free[u], BATCH_NWC); }
+        mbar_fence_init();
+    }
+    __syncthreads();
+    pdl_launch();
+
+    if (warp == 0) {
+        // ===================================================== weight producer: slabs of every node -> stage ring
+        if (!a.const_weights) pdl_wait();
+        int s = 0;
+        uint32_t ph = 1;                                          // parity of the phase before the one to wait for; first lap: no wait
+        bool lap0 = true;
+        for (int i = 0; i < a.count; i++) {
+            const batch_node & nd = a.nodes[i];
+            int r_begin, nrows;
+            batch_slab(nd, i, r_begin, nrows);
+            const int R = nd.R;
+            const int nbatch = (nrows + R - 1) / R;
+            const int row_pitch = batch_row_pitch(nd.row_bytes);
+            for (int lb = 0; lb < nbatch; lb++) {
+                if (!lap0) mbar_wait(&empty[s], ph);              // the whole warp polls
+                if (lane == 0) {
+                    const int rows_here = (nrows - lb * R < R) ? (nrows - lb * R) : R;
+                    const uint8_t * src = nd.w + (int64_t) (r_begin + lb * R) * nd.row_stride;
+                    uint8_t * slot = slots + (size_t) s * a.slot_stride;
+                    if (nd.contiguous) {
+                        const uint32_t off = (uint32_t) (reinterpret_cast<uintptr_t>(src) & 15);
+                        const uint32_t bytes = (off + (uint32_t) rows_here * (uint32_t) nd.row_bytes + 15u) & ~15u;
+                        mbar_arrive_expect_tx(&full[s], bytes);
+                        bulk_g2s(slot, src - off, bytes, &full[s]);
+                    } else {
+                        uint32_t total = 0;
+                        for (int r = 0; r < rows_here; r++) {
+                            const uint32_t off = (uint32_t) (reinterpret_cast<uintptr_t>(src + r * nd.row_stride) & 15);
+                            total += (off + (uint32_t) nd.row_bytes + 15u) & ~15u;
+                        }
+                        mbar_arrive_expect_tx(&full[s], total);
+                        for (int r = 0; r < rows_here; r++) {
+                            const uint8_t * p = src + r * nd.row_stride;
+                            const uint32_t off = (uint32_t) (reinterpret_cast<uintptr_t>(p) & 15);
+                            bulk_g2s(slot + r * row_pitch, p - off, (off + (uint32_t) nd.row_bytes + 15u) & ~15u, &full[s]);
+                        }
+                    }
+                }
+                __syncwarp();
+                if (++s == S) { s = 0; ph ^= 1u; lap0 = false; }
+            }
+        }
+        return;
+    }
+
+    if (warp == 1) {
+        // ===================================================== activation producer: q8 activations of node i -> buffer i % NB
+        pdl_wait();                                               // k_quantize_batch (and whatever made x) is done
+        for (int i = 0; i < a.count; i++) {
+            const batch_node & nd = a.nodes[i];
+            const int u = i % NB;
+            if (i >= NB) mbar_wait(&acts_free[u], (uint32_t) (((i / NB) - 1) & 1));
+            if (lane == 0) {
+                const uint32_t bytes = batch_acts_bytes(nd.k);    // k % 256 == 0: a multiple of 16
+                mbar_arrive_expect_tx(&acts_ready[u], bytes);
+                bulk_g2s(actbufs + (size_t) u * a.acts_stride, nd.acts, bytes, &acts_ready[u]);
+            }
+            __syncwarp();
+        }
+        return;
+    }
+
+    // ========================================================= consumers
+    const int cw = warp - 2;
+    int st_s = 0, cc = 0, prev_w = 1;
+    uint32_t st_ph = 0;
+    for (int i = 0; i < a.count; i++) {
+        const batch_node & nd = a.nodes[i];
+        // the partials area is laid out per (W, G): when either side of a node boundary uses it, every
+        // consumer warp must be past its last reduction before the new layout is written
+        if (nd.W > 1 || prev_w > 1) named_bar_sync(11, BATCH_NWC * 32);
+        prev_w = nd.W;
+        int r_begin, nrows;
+        batch_slab(nd, i, r_begin, nrows);
+        const int nbatch = (nrows + nd.R - 1) / nd.R;
+        const int u = i % NB;
+        const uint8_t * buf = actbufs + (size_t) u * a.acts_stride;
+        mbar_wait(&acts_ready[u], (uint32_t) ((i / NB) & 1));
+        if (nd.type == T_Q5_K) batch_consume<T_Q5_K>(a, nd, cw, lane, r_begin, nrows, nbatch, st_s, st_ph, cc, buf, &acts_free[u], full, empty, part, slots);
+        else                   batch_consume<T_Q4_K>(a, nd, cw, lane, r_begin, nrows, nbatch, st_s, st_ph, cc, buf, &acts_free[u], full, empty, part, slots);
+    }
+}
+
+// ================================================================= host side
+// Can this MUL_MAT ride in a persistent launch?  (n = 1, plain 2-D, a format with a 128-weight item.)
+static bool batch_node_ok(int type, const uint8_t * w, int64_t row_stride, int64_t m, int64_t k, const float * x) {
+    if (type != T_Q4_K && type != T_Q5_K) return false;
+    if (m < 1 || m > 0x7FFFFFFF || k < 1024 || k % 256 != 0) return false;
+    if (ceil_div(k / 128, 32) > 8) return false;                 // k <= 32768: one item per lane, same (W, lane) map as the per-node kernel
+    if (reinterpret_cast<uintptr_t>(x) % 16 != 0) return false;
+    if (!hitem<T_Q4_K>::ok(k, row_stride, reinterpret_cast<uintptr_t>(w))) return false;
+    const int64_t row_bytes = k / 256 * type_bytes(type);
+    if (row_stride < row_bytes) return false;
+    return true;
+}
+
+static inline size_t batch_acts_record_bytes(int64_t k) { return ((size_t) (k + k / 32 * 4) + 127) & ~(size_t) 127; }
+
+struct batch_builder {
+    batch_args args;
+    int max_slot = 0;
+    bool all_const = true;
+    uint8_t * ws = nullptr;            // workspace cursor for the activation records
+    size_t ws_left = 0;
+    batch_builder() { reset(nullptr, 0); }
+    void reset(uint8_t * w, size_t bytes) {
+        args.count = 0; args.kmax = 0; max_slot = 0; all_const = true;
+        ws = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(w) + 127) & ~(uintptr_t) 127);
+        const size_t skew = (size_t) (ws - w);
+        ws_left = bytes > skew ? bytes - skew : 0;
+    }
+    bool full() const { return args.count >= BATCH_MAX_NODES; }
+    bool empty() const { return args.count == 0; }
+
+    // false: the workspace cannot hold this node's activation record
+    bool add(int type, const uint8_t * w, int64_t row_stride, int64_t m, int64_t k, const float * x, float * dst, bool const_w, int grid) {
+        static const int slot_target = env_int("GGML_B200_BATCH_SLOT_BYTES", 9216);
+        batch_node & nd = args.nodes[args.count];
+        const batch_node * prev = args.count > 0 ? &args.nodes[args.count - 1] : nullptr;
+        if (prev && prev->x == x && prev->k == k) {
+            nd.acts = prev->acts; nd.quantize = 0;              // same activations as the previous node (gate/up, q/k/v)
+        } else {
+            const size_t need = batch_acts_record_bytes(k);
+            if (need > ws_left) return false;
+            nd.acts = ws; nd.quantize = 1; ws += need; ws_left -= need;
+        }
+        args.count++;
+        nd.w = w; nd.x = x; nd.dst = dst; nd.row_stride = row_stride; nd.m = (int) m; nd.k = (int) k;
+        nd.row_bytes = (int) (k / 256 * type_bytes(type));
+        nd.type = (unsigned char) type;
+        nd.W = (unsigned char) ceil_div(k / 128, 32);
+        nd.G = (unsigned char) (BATCH_NWC / nd.W);
+        int R = 2 * (slot_target / (2 * nd.row_bytes));
+        if (R < 2) R = 2;
+        if (R > BATCH_RMAX) R = BATCH_RMAX;
+        nd.R = (unsigned char) R;
+        nd.contiguous = row_stride == nd.row_bytes ? 1 : 0;
+        nd.pad[0] = nd.pad[1] = 0;
+        int rpc = (int) ceil_div(m, grid);
+        rpc += rpc & 1;
+        nd.rows_per_cta = rpc;
+        const int row_pitch = (nd.row_bytes + 15 + 15 + 16) & ~15;
+        const int slot_bytes = nd.contiguous ? (15 + R * nd.row_bytes + 15 + 16) : R * row_pitch;
+        if (slot_bytes > max_slot) max_slot = slot_bytes;
+        if (nd.k > args.kmax) args.kmax = nd.k;
+        all_const = all_const && const_w;
+        return true;
+    }
+};
+
+static int batch_launch(batch_builder & bb, cudaStream_t st) {
+    if (bb.empty()) return B200_OK;
+    const dev_caps & caps = current_caps();
+    batch_args & a = bb.args;
+    static const int s_env = env_int("GGML_B200_BATCH_STAGES", BATCH_MAX_STAGES);
+    static const int nb_env = env_int("GGML_B200_BATCH_ABUF", 3);
+    static const int pdl = env_int("GGML_B200_FUSED_PDL", 1);
+    a.const_weights = bb.all_const ? 1 : 0;
+    a.slot_stride = (bb.max_slot + 127) & ~127;
+    a.off_part    = (2 * BATCH_MAX_STAGES + 2 * BATCH_MAX_ABUF) * 8;
+    a.off_acts    = (a.off_part + 2 * BATCH_NWC * BATCH_RMAX * (int) sizeof(float) + 127) & ~127;
+    a.acts_stride = (int) batch_acts_record_bytes(a.kmax);
+    int NB = nb_env < 2 ? 2 : (nb_env > BATCH_MAX_ABUF ? BATCH_MAX_ABUF : nb_env);
+    while (NB > 2 && NB * a.acts_stride > 49152) NB--;           // keep the weight ring large
+    a.NB = NB;
+    a.off_slots   = a.off_acts + NB * a.acts_stride;
+    int S = (caps.smem_optin - a.off_slots) / a.slot_stride;
+    if (S > s_env) S = s_env;
+    if (S > BATCH_MAX_STAGES) S = BATCH_MAX_STAGES;
+    if (S < 2) return B200_STREAM_NOT_APPLICABLE;
+    a.S = S;
+    const size_t smem = (size_t) a.off_slots + (size_t) S * a.slot_stride;
+
+    static size_t smem_set[64];
+    int dev = 0; cudaGetDevice(&dev); if (dev < 0 || dev >= 64) dev = 0;
+    if (smem > smem_set[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(k_mmvq_batch, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+        if (e != cudaSuccess) return -(int) e;
+        smem_set[dev] = smem;
+    }
+    // 1. every activation vector of the list -> q8 (one launch)
+    {
+        const dim3 grid((unsigned) ceil_div(a.kmax / 32, 8), (unsigned) a.count);
+        k_quantize_batch<<<grid, 256, 0, st>>>(a);
+        b200_count_launch(1);
+    }
+    // 2. the persistent mat-vec; starts (and prefetches constant weights) while the quantizer drains
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned) caps.sm_count); cfg.blockDim = dim3(BATCH_THREADS);
+    cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, k_mmvq_batch, a);
+    if (e != cudaSuccess) return -(int) e;
+    b200_count_launch(1);
+    return B200_OK;
+}
+
+} // namespace b200

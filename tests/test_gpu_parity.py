@@ -356,6 +356,124 @@ def test_mul_mat_batch_matches_single_calls(kern, oracle):
         assert np.array_equal(u32(single.cpu().numpy().reshape(-1)), u32(y.cpu().numpy().reshape(-1))), (t, m, k)
 
 
+def _batch_nodes(kern, mats, seed0=0, shared_x=False):
+    import b200
+    import torch
+    ws_np = [random_blocks(t, m, k, seed=seed0 + i) for i, (t, m, k) in enumerate(mats)]
+    ws = [dev_blocks(kern, w) for w in ws_np]
+    xs_np, cache = [], {}
+    for i, (t, m, k) in enumerate(mats):
+        if shared_x and k in cache:
+            xs_np.append(cache[k])
+        else:
+            cache[k] = np.random.default_rng(seed0 + 100 + i).uniform(-1, 1, size=(1, k)).astype(np.float32)
+            xs_np.append(cache[k])
+    xdev = {}
+    xs = []
+    for x in xs_np:
+        if id(x) not in xdev:
+            xdev[id(x)] = kern.to_device(x)
+        xs.append(xdev[id(x)])
+    ys = [torch.zeros((1, m), dtype=torch.float32, device=kern.device) for (t, m, k) in mats]
+    nodes = (b200.MulMatNode * len(mats))(*[
+        b200.mul_mat_node(t, w.data_ptr(), m, k, x.data_ptr(), 1, y.data_ptr(), const_weights=True)
+        for (t, m, k), w, x, y in zip(mats, ws, xs, ys)])
+    return nodes, ws_np, ws, xs_np, xs, ys
+
+
+@pytest.mark.parametrize("shared_x", [False, True])
+def test_mul_mat_persistent_batch_vs_oracle(kern, oracle, shared_x):
+    """the persistent list kernel (mmvq_batch.cuh): mixed formats, K from 1024 to 32768 (W = 1..8 warps
+    per row), odd and tiny m, m below / far above the SM count, shared and distinct activations.  Every
+    node: NMSE 1e-9 to the oracle's q8_1 arithmetic and bit-identical to the single-node call."""
+    mats = [("q4_K", 300, 4096), ("q5_K", 128, 2048), ("q4_K", 17, 11008), ("q4_K", 1, 1024), ("q5_K", 3, 4096),
+            ("q4_K", 4096, 4096), ("q5_K", 1111, 11008), ("q4_K", 40, 28672), ("q5_K", 21, 32768), ("q4_K", 2, 1280),
+            ("q4_K", 999, 4096), ("q4_K", 5000, 1024), ("q5_K", 77, 14336), ("q4_K", 148 * 2 + 1, 8192)]
+    nodes, ws_np, ws, xs_np, xs, ys = _batch_nodes(kern, mats, seed0=40, shared_x=shared_x)
+    c0 = kern.launch_count()
+    kern.mul_mat_batch(nodes)
+    assert kern.launch_count() - c0 == 2, "independent decode nodes ride in one quantize + one persistent launch"
+    for (t, m, k), w_np, w, x_np, x, y in zip(mats, ws_np, ws, xs_np, xs, ys):
+        got = y.cpu().numpy().reshape(1, m)
+        want = oracle.mul_mat(t, w_np, m, k, x_np, mode=1)
+        assert oracle.nmse(want, got) <= NMSE_ORACLE, (t, m, k, oracle.nmse(want, got))
+        single = kern.mul_mat(t, w, m, k, x).cpu().numpy().reshape(-1)
+        assert np.array_equal(u32(single), u32(got.reshape(-1))), (t, m, k)
+
+
+def test_mul_mat_persistent_batch_many_nodes_and_strided_rows(kern, oracle):
+    """more nodes than one launch holds (448) and a strided weight view inside the list."""
+    import b200
+    import torch
+    t, m, k = "q4_K", 64, 1024
+    rb = k // BLOCK_ELEMS[t] * BLOCK_BYTES[t]
+    w_np = random_blocks(t, m, k, seed=9)
+    buf = np.zeros(m * 2 * rb + 64, dtype=np.uint8)
+    for r in range(m):
+        buf[r * 2 * rb: r * 2 * rb + rb] = w_np[r]
+    w, wstr = dev_blocks(kern, w_np), kern.to_device(buf)
+    count = 460
+    x_np = np.random.default_rng(3).uniform(-1, 1, size=(count, k)).astype(np.float32)
+    x = kern.to_device(x_np)
+    y = torch.zeros((count, m), dtype=torch.float32, device=kern.device)
+    nodes = (b200.MulMatNode * count)(*[
+        b200.mul_mat_node(t, (wstr if i % 3 == 1 else w).data_ptr(), m, k, x[i].data_ptr(), 1, y[i].data_ptr(),
+                          a_row_stride=2 * rb if i % 3 == 1 else None, const_weights=(i % 2 == 0))
+        for i in range(count)])
+    c0 = kern.launch_count()
+    kern.mul_mat_batch(nodes)
+    assert kern.launch_count() - c0 == 4        # 448 + 12 nodes: two (quantize, persistent) pairs
+    got = y.cpu().numpy()
+    want = oracle.mul_mat(t, w_np, m, k, x_np, mode=1)
+    assert oracle.nmse(want, got) <= NMSE_ORACLE
+
+
+def test_mul_mat_persistent_batch_cuts_at_dependencies(kern, oracle):
+    """a node that reads (or overwrites) what an earlier node of the list writes must not share its
+    launch: chain y1 = W1 x, y2 = W2 y1, then a node that overwrites y1."""
+    import b200
+    import torch
+    w1_np, w2_np, w3_np = random_blocks("q4_K", 4096, 1024, seed=1), random_blocks("q5_K", 200, 4096, seed=2), random_blocks("q4_K", 4096, 2048, seed=3)
+    w1, w2, w3 = dev_blocks(kern, w1_np), dev_blocks(kern, w2_np), dev_blocks(kern, w3_np)
+    x_np = np.random.default_rng(8).uniform(-1, 1, size=(1, 1024)).astype(np.float32)
+    x3_np = np.random.default_rng(9).uniform(-1, 1, size=(1, 2048)).astype(np.float32)
+    x, x3 = kern.to_device(x_np), kern.to_device(x3_np)
+    y1 = torch.zeros((1, 4096), dtype=torch.float32, device=kern.device)
+    y2 = torch.zeros((1, 200), dtype=torch.float32, device=kern.device)
+    nodes = (b200.MulMatNode * 3)(
+        b200.mul_mat_node("q4_K", w1.data_ptr(), 4096, 1024, x.data_ptr(), 1, y1.data_ptr()),
+        b200.mul_mat_node("q5_K", w2.data_ptr(), 200, 4096, y1.data_ptr(), 1, y2.data_ptr()),
+        b200.mul_mat_node("q4_K", w3.data_ptr(), 4096, 2048, x3.data_ptr(), 1, y1.data_ptr()))
+    c0 = kern.launch_count()
+    kern.mul_mat_batch(nodes)
+    assert kern.launch_count() - c0 == 3
+    r1 = kern.mul_mat("q4_K", w1, 4096, 1024, x)
+    r2 = kern.mul_mat("q5_K", w2, 200, 4096, r1)
+    r3 = kern.mul_mat("q4_K", w3, 4096, 2048, x3)
+    assert np.array_equal(u32(y2.cpu().numpy().reshape(-1)), u32(r2.cpu().numpy().reshape(-1)))
+    assert np.array_equal(u32(y1.cpu().numpy().reshape(-1)), u32(r3.cpu().numpy().reshape(-1)))
+    assert oracle.nmse(oracle.mul_mat("q5_K", w2_np, 200, 4096, r1.cpu().numpy().reshape(1, 4096), mode=1), y2.cpu().numpy()) <= NMSE_ORACLE
+
+
+@pytest.mark.parametrize("t", FUSED_TYPES)
+@pytest.mark.parametrize("m,k", FUSED_SHAPES)
+def test_mul_mat_persistent_single_node(kern, oracle, monkeypatch, t, m, k):
+    """one node through the persistent kernel (GGML_B200_BATCH_SINGLE=1): bit-identical to the per-node kernel."""
+    import b200
+    import torch
+    w_np = random_blocks(t, m, k, seed=3 * m + k)
+    x_np = np.random.default_rng(m + k).uniform(-1, 1, size=(1, k)).astype(np.float32)
+    w, x = dev_blocks(kern, w_np), kern.to_device(x_np)
+    y = torch.zeros((1, m), dtype=torch.float32, device=kern.device)
+    nodes = (b200.MulMatNode * 1)(b200.mul_mat_node(t, w.data_ptr(), m, k, x.data_ptr(), 1, y.data_ptr()))
+    monkeypatch.setenv("GGML_B200_BATCH_SINGLE", "1")
+    kern.mul_mat_batch(nodes)
+    monkeypatch.delenv("GGML_B200_BATCH_SINGLE")
+    single = kern.mul_mat(t, w, m, k, x).cpu().numpy().reshape(-1)
+    assert np.array_equal(u32(single), u32(y.cpu().numpy().reshape(-1)))
+    assert oracle.nmse(oracle.mul_mat(t, w_np, m, k, x_np, mode=1), y.cpu().numpy()) <= NMSE_ORACLE
+
+
 # ---------------------------------------------------------------------------- full-size (BASELINE.json configs)
 FULL = [("q4_0", 4096, 4096), ("q4_K", 4096, 4096), ("q4_K", 11008, 4096), ("q4_K", 4096, 11008),
         ("q5_K", 4096, 11008), ("q6_K", 4096, 11008), ("q6_K", 32000, 4096), ("q8_0", 11008, 4096)]
