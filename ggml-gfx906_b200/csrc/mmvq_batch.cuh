@@ -11,7 +11,8 @@
 //
 //   * k_quantize_batch: ONE small launch turns every node's x into q8_1 values (bit-exact
 //     quantize_row_q8_1_ref, src/ggml-quants.c:225-258) in the caller's workspace: int8 plane [k] followed
-//     by the fp16-rounded scales as f32 [k/32] — 1.125 bytes per activation, nodes sharing x share it;
+//     by the fp16-rounded scales as f32 [k/32] — 1.125 bytes per activation, nodes sharing x share it
+//     (the int8 plane is bank-swizzled per 128-value item for the consumers' register loads);
 //   * k_mmvq_batch: one CTA per SM, resident for the whole list; every node's rows are dealt to the CTAs as
 //     contiguous slabs (rotated per node so that short last slabs do not always hit the same SM);
 //       warp 0 (weight producer) streams the CTA's slabs of ALL nodes, back to back, through one ring of
@@ -38,7 +39,8 @@ constexpr int BATCH_NWC        = 9;      // consumer warps
 constexpr int BATCH_THREADS    = (2 + BATCH_NWC) * 32;
 constexpr int BATCH_MAX_STAGES = 16;
 constexpr int BATCH_MAX_ABUF   = 4;      // activation buffers
-constexpr int BATCH_RMAX       = 16;     // rows per stage, at most
+constexpr int BATCH_RMAX       = 16;     // rows per stage, at most, when a row needs several warps (partials buffer)
+constexpr int BATCH_RMAX_W1    = 96;     // rows per stage, at most, otherwise
 constexpr int BATCH_ROT        = 61;     // slab rotation per node (coprime with the SM count)
 
 struct batch_node {                      // 64 bytes
@@ -61,10 +63,65 @@ struct batch_args {
     batch_node nodes[BATCH_MAX_NODES];
 };
 
+// mbarrier ops on precomputed shared-window addresses (no generic -> shared conversion per call)
+__device__ __forceinline__ void mbar_wait_a(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "B200A_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra B200A_DONE;\n"
+        "bra B200A_WAIT;\n"
+        "B200A_DONE:\n"
+        "}\n" :: "r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_a(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(bar) : "memory");
+}
+
 __device__ __forceinline__ int batch_row_pitch(int row_bytes) { return (row_bytes + 15 + 15 + 16) & ~15; }
 __device__ __forceinline__ uint32_t batch_acts_bytes(int k) { return (uint32_t) (k + (k >> 5) * 4); }
 
-__device__ __forceinline__ void batch_slab(const batch_node & nd, int i, int & r_begin, int & nrows) {
+// A node descriptor in registers.  The parameter block (up to 28 KB) is far larger than the constant
+// cache: reading a descriptor where it is needed costs a chain of cache misses per node and per warp
+// (measured: 23 % of the kernel).  Instead every lane of a warp keeps ONE descriptor (node base + lane),
+// fetched 32 nodes at a time, and the warp broadcasts the current node's fields by shuffle.
+struct node_r {
+    const uint8_t * w; float * dst; const uint8_t * acts; int64_t row_stride;
+    int m, k, row_bytes, rows_per_cta, type, R, W, G, contiguous;
+};
+__device__ __forceinline__ uint64_t shfl_u64(uint64_t v, int src) {
+    const uint32_t lo = __shfl_sync(0xFFFFFFFFu, (uint32_t) v, src), hi = __shfl_sync(0xFFFFFFFFu, (uint32_t) (v >> 32), src);
+    return ((uint64_t) hi << 32) | lo;
+}
+struct node_cache {
+    node_r c;
+    int base;
+    __device__ __forceinline__ node_cache() : base(-64) {}
+    __device__ __forceinline__ node_r get(const batch_args & a, int i, int lane) {     // convergent: all 32 lanes call
+        if (i >= base + 32) {
+            base = i & ~31;
+            const int j = base + lane < a.count ? base + lane : a.count - 1;
+            const batch_node & nd = a.nodes[j];
+            c.w = nd.w; c.dst = nd.dst; c.acts = nd.acts; c.row_stride = nd.row_stride;
+            c.m = nd.m; c.k = nd.k; c.row_bytes = nd.row_bytes; c.rows_per_cta = nd.rows_per_cta;
+            c.type = nd.type; c.R = nd.R; c.W = nd.W; c.G = nd.G; c.contiguous = nd.contiguous;
+        }
+        const int src = i & 31;
+        node_r r;
+        r.w = reinterpret_cast<const uint8_t *>(shfl_u64(reinterpret_cast<uint64_t>(c.w), src));
+        r.dst = reinterpret_cast<float *>(shfl_u64(reinterpret_cast<uint64_t>(c.dst), src));
+        r.acts = reinterpret_cast<const uint8_t *>(shfl_u64(reinterpret_cast<uint64_t>(c.acts), src));
+        r.row_stride = (int64_t) shfl_u64((uint64_t) c.row_stride, src);
+        r.m = __shfl_sync(0xFFFFFFFFu, c.m, src); r.k = __shfl_sync(0xFFFFFFFFu, c.k, src);
+        r.row_bytes = __shfl_sync(0xFFFFFFFFu, c.row_bytes, src); r.rows_per_cta = __shfl_sync(0xFFFFFFFFu, c.rows_per_cta, src);
+        const int packed = __shfl_sync(0xFFFFFFFFu, c.type | (c.R << 8) | (c.W << 16) | (c.G << 20) | (c.contiguous << 24), src);
+        r.type = packed & 0xFF; r.R = (packed >> 8) & 0xFF; r.W = (packed >> 16) & 0xF; r.G = (packed >> 20) & 0xF; r.contiguous = (packed >> 24) & 1;
+        return r;
+    }
+};
+
+__device__ __forceinline__ void batch_slab(const node_r & nd, int i, int & r_begin, int & nrows) {
     const int v = (int) ((blockIdx.x + (unsigned) i * BATCH_ROT) % gridDim.x);
     const int64_t rb = (int64_t) v * nd.rows_per_cta;
     int64_t n = (int64_t) nd.m - rb;
@@ -89,18 +146,21 @@ __global__ void __launch_bounds__(256) k_quantize_batch(const __grid_constant__ 
     const float v  = roundf(__fmul_rn(x, id));
     const int   qi = fabsf(v) < 2147483648.0f ? (int) v : (int) 0x80000000;
     int8_t * q = reinterpret_cast<int8_t *>(const_cast<uint8_t *>(nd.acts));
-    q[kb * 32 + lane] = (int8_t) (qi & 0xFF);
+    // 16-byte piece p of 128-value item idx is stored at piece (p + idx) % 8 of the item: the consumer lanes
+    // (one item each, 128 B apart) then read piece p from eight different bank groups
+    const int e = kb * 32 + lane, idx = e >> 7, pc = (e >> 4) & 7;
+    q[idx * 128 + (((pc + idx) & 7) << 4) + (e & 15)] = (int8_t) (qi & 0xFF);
     if (lane == 0) reinterpret_cast<float *>(q + nd.k)[kb] = __half2float(__float2half_rn(d));
 }
 
 // ---------------------------------------------------------------- consumer: one node
 // cc: running count of row pairs ("chunks") this CTA has seen; chunk j belongs to group j % G.
 template <int T>
-__device__ __forceinline__ void batch_consume(const batch_args & a, const batch_node & nd, const int cw, const int lane,
+__device__ __forceinline__ void batch_consume(const node_r & nd, const int cw, const int lane,
                                               const int r_begin, const int nrows, const int nbatch,
                                               int & st_s, uint32_t & st_ph, int & cc,
-                                              const uint8_t * actbuf, uint64_t * acts_free, uint64_t * full, uint64_t * empty,
-                                              float * part, const uint8_t * slots) {
+                                              const uint8_t * actbuf, const uint32_t acts_free, const uint32_t full, const uint32_t empty,
+                                              float * part, const uint8_t * slots, const int S, const int slot_stride) {
     using IT = hitem<T>;
     const int W = nd.W, G = nd.G, R = nd.R;
     const int g = cw / W, wg = cw - g * W;
@@ -114,29 +174,30 @@ __device__ __forceinline__ void batch_consume(const batch_args & a, const batch_
     if (active) {
         const int8_t * yq = reinterpret_cast<const int8_t *>(actbuf);
         const float  * yd = reinterpret_cast<const float *>(actbuf + nd.k);
+        const float4 d4 = *reinterpret_cast<const float4 *>(yd + idx * 4);
+        const float dd[4] = { d4.x, d4.y, d4.z, d4.w };
 #pragma unroll
         for (int j = 0; j < 4; j++) {
-            const int4 lo = *reinterpret_cast<const int4 *>(yq + idx * 128 + 32 * j);
-            const int4 hi = *reinterpret_cast<const int4 *>(yq + idx * 128 + 32 * j + 16);
+            const int4 lo = *reinterpret_cast<const int4 *>(yq + idx * 128 + (((2 * j + idx) & 7) << 4));       // swizzled by k_quantize_batch
+            const int4 hi = *reinterpret_cast<const int4 *>(yq + idx * 128 + (((2 * j + 1 + idx) & 7) << 4));
             acts.q[j][0] = lo.x; acts.q[j][1] = lo.y; acts.q[j][2] = lo.z; acts.q[j][3] = lo.w;
             acts.q[j][4] = hi.x; acts.q[j][5] = hi.y; acts.q[j][6] = hi.z; acts.q[j][7] = hi.w;
             int sum = 0;
 #pragma unroll
             for (int u = 0; u < 8; u++) sum = __dp4a(0x01010101, acts.q[j][u], sum);
-            const float d = yd[idx * 4 + j];
+            const float d = dd[j];
             acts.sd[j] = d * (float) sum;
             acts.d[j]  = (IT::hi_div16 && (j & 1)) ? d * 0.0625f : d;
         }
     }
     __syncwarp();
-    if (lane == 0) mbar_arrive_cta(acts_free);            // this warp no longer reads the activation buffer
+    if (lane == 0) mbar_arrive_a(acts_free);              // this warp no longer reads the activation buffer
 
-    const int S = a.S;
     int git = 0;                                          // stages in which this group had rows: selects the partials buffer
     int cmod = cc % G;                                    // owner group of the next chunk
     for (int lb = 0; lb < nbatch; lb++) {
         const int s = st_s;
-        mbar_wait(&full[s], st_ph);                       // every lane polls (a single polling lane sleeps out its time slice)
+        mbar_wait_a(full + 8 * s, st_ph);                 // every lane polls (a single polling lane sleeps out its time slice)
         if (++st_s == S) { st_s = 0; st_ph ^= 1u; }
         const int rows_here = (nrows - lb * R < R) ? (nrows - lb * R) : R;
         const int nchunks = (rows_here + FUSED_RB - 1) / FUSED_RB;
@@ -146,7 +207,7 @@ __device__ __forceinline__ void batch_consume(const batch_args & a, const batch_
         while (cmod >= G) cmod -= G;
         float * pb = part + (size_t) ((g * 2 + (git & 1)) * W) * BATCH_RMAX;
         if (g < G && c_first < nchunks) {
-            const uint8_t * slot = slots + (size_t) s * a.slot_stride;
+            const uint8_t * slot = slots + s * slot_stride;
             const uint8_t * src0 = nd.w + (int64_t) (r_begin + lb * R) * nd.row_stride;
             for (int c = c_first; c < nchunks; c += G) {
                 const int r0 = c * FUSED_RB;
@@ -180,7 +241,7 @@ __device__ __forceinline__ void batch_consume(const batch_args & a, const batch_
             }
         }
         __syncwarp();
-        if (lane == 0) mbar_arrive_cta(&empty[s]);        // this warp is done with the stage
+        if (lane == 0) mbar_arrive_a(empty + 8 * s);      // this warp is done with the stage
         if (W > 1 && g < G && c_first < nchunks) {
             // the W warps of the group meet; warp 0 of the group adds the partials in fixed order.  pb
             // alternates per working stage of the group: the buffer written two working stages later is
@@ -232,8 +293,9 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
         int s = 0;
         uint32_t ph = 1;                                          // parity of the phase before the one to wait for; first lap: no wait
         bool lap0 = true;
+        node_cache cache;
         for (int i = 0; i < a.count; i++) {
-            const batch_node & nd = a.nodes[i];
+            const node_r nd = cache.get(a, i, lane);
             int r_begin, nrows;
             batch_slab(nd, i, r_begin, nrows);
             const int R = nd.R;
@@ -274,8 +336,9 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
     if (warp == 1) {
         // ===================================================== activation producer: q8 activations of node i -> buffer i % NB
         pdl_wait();                                               // k_quantize_batch (and whatever made x) is done
+        node_cache cache;
         for (int i = 0; i < a.count; i++) {
-            const batch_node & nd = a.nodes[i];
+            const node_r nd = cache.get(a, i, lane);
             const int u = i % NB;
             if (i >= NB) mbar_wait(&acts_free[u], (uint32_t) (((i / NB) - 1) & 1));
             if (lane == 0) {
@@ -292,8 +355,11 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
     const int cw = warp - 2;
     int st_s = 0, cc = 0, prev_w = 1;
     uint32_t st_ph = 0;
+    const uint32_t full_a = smem_u32(full), empty_a = smem_u32(empty), ready_a = smem_u32(acts_ready), free_a = smem_u32(acts_free);
+    const int slot_stride = a.slot_stride;
+    node_cache cache;
     for (int i = 0; i < a.count; i++) {
-        const batch_node & nd = a.nodes[i];
+        const node_r nd = cache.get(a, i, lane);
         // the partials area is laid out per (W, G): when either side of a node boundary uses it, every
         // consumer warp must be past its last reduction before the new layout is written
         if (nd.W > 1 || prev_w > 1) named_bar_sync(11, BATCH_NWC * 32);
@@ -303,9 +369,9 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
         const int nbatch = (nrows + nd.R - 1) / nd.R;
         const int u = i % NB;
         const uint8_t * buf = actbufs + (size_t) u * a.acts_stride;
-        mbar_wait(&acts_ready[u], (uint32_t) ((i / NB) & 1));
-        if (nd.type == T_Q5_K) batch_consume<T_Q5_K>(a, nd, cw, lane, r_begin, nrows, nbatch, st_s, st_ph, cc, buf, &acts_free[u], full, empty, part, slots);
-        else                   batch_consume<T_Q4_K>(a, nd, cw, lane, r_begin, nrows, nbatch, st_s, st_ph, cc, buf, &acts_free[u], full, empty, part, slots);
+        mbar_wait_a(ready_a + 8 * u, (uint32_t) ((i / NB) & 1));
+        if (nd.type == T_Q5_K) batch_consume<T_Q5_K>(nd, cw, lane, r_begin, nrows, nbatch, st_s, st_ph, cc, buf, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
+        else                   batch_consume<T_Q4_K>(nd, cw, lane, r_begin, nrows, nbatch, st_s, st_ph, cc, buf, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
     }
 }
 
@@ -342,7 +408,7 @@ struct batch_builder {
 
     // false: the workspace cannot hold this node's activation record
     bool add(int type, const uint8_t * w, int64_t row_stride, int64_t m, int64_t k, const float * x, float * dst, bool const_w, int grid) {
-        static const int slot_target = env_int("GGML_B200_BATCH_SLOT_BYTES", 9216);
+        static const int slot_target = env_int("GGML_B200_BATCH_SLOT_BYTES", 36864);
         batch_node & nd = args.nodes[args.count];
         const batch_node * prev = args.count > 0 ? &args.nodes[args.count - 1] : nullptr;
         if (prev && prev->x == x && prev->k == k) {
@@ -358,9 +424,11 @@ struct batch_builder {
         nd.type = (unsigned char) type;
         nd.W = (unsigned char) ceil_div(k / 128, 32);
         nd.G = (unsigned char) (BATCH_NWC / nd.W);
-        int R = 2 * (slot_target / (2 * nd.row_bytes));
+        // rows per stage: the nearest number of row pairs to the target; mat-vecs whose rows need several
+        // warps (W > 1) keep their partials in shared memory, sized for BATCH_RMAX rows
+        int R = 2 * ((slot_target + nd.row_bytes) / (2 * nd.row_bytes));
         if (R < 2) R = 2;
-        if (R > BATCH_RMAX) R = BATCH_RMAX;
+        if (R > (nd.W > 1 ? BATCH_RMAX : BATCH_RMAX_W1)) R = nd.W > 1 ? BATCH_RMAX : BATCH_RMAX_W1;
         nd.R = (unsigned char) R;
         nd.contiguous = row_stride == nd.row_bytes ? 1 : 0;
         nd.pad[0] = nd.pad[1] = 0;
