@@ -235,7 +235,7 @@ extern "C" int b200_mul_mat_batch(const b200_mul_mat_node * nodes, int64_t count
                                   void * workspace_dev, size_t workspace_bytes, void * stream) {
     if (count < 0 || (count > 0 && !nodes)) return B200_ERR_SHAPE;
     cudaStream_t st = (cudaStream_t) stream;
-    static const bool persistent = !env_int("GGML_B200_NO_BATCH_KERNEL", 0);
+    const bool persistent = !env_int("GGML_B200_NO_BATCH_KERNEL", 0);
     static thread_local batch_builder * bb = nullptr;         // 28 KB parameter block, reused
     static thread_local range_set reads, writes;
     if (!bb) bb = new batch_builder();

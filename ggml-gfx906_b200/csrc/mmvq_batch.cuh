@@ -20,9 +20,9 @@
 //         mbarriers: the weights of node i+1.. are in flight while node i is reduced, HBM never idles;
 //       warp 1 (activation producer) bulk-copies the quantized activations of the next nodes into a small
 //         ring of activation buffers (ready/free mbarriers);
-//       9 consumer warps: a lane owns 128 consecutive weights of a row (hitem<T>, mmvq_fused.cuh) and keeps
+//       12 consumer warps: a lane owns 128 consecutive weights of a row (hitem<T>, mmvq_fused.cuh) and keeps
 //         the matching q8 activations in registers for the node; W consecutive warps cover a row, the
-//         G = 9 / W groups take the row pairs of the stages round-robin; partials of a row meet in shared
+//         G = 12 / W groups take the row pairs of the stages round-robin; partials of a row meet in shared
 //         memory in fixed order, so a row's value never depends on the grid, the list or the GPU that
 //         computes it (row-split results stay bit-identical).  Every consumer warp observes every stage
 //         (mbarrier phases are parity bits: a waiter that skipped stages could mistake phase n-2 for n).
@@ -35,7 +35,8 @@
 namespace b200 {
 
 constexpr int BATCH_MAX_NODES  = 448;
-constexpr int BATCH_NWC        = 9;      // consumer warps
+constexpr int BATCH_NWC        = 12;     // consumer warps
+constexpr int BATCH_AHDR       = 128;    // bytes in front of each activation buffer: the node as the consumers need it
 constexpr int BATCH_THREADS    = (2 + BATCH_NWC) * 32;
 constexpr int BATCH_MAX_STAGES = 16;
 constexpr int BATCH_MAX_ABUF   = 4;      // activation buffers
@@ -121,14 +122,16 @@ struct node_cache {
     }
 };
 
-__device__ __forceinline__ void batch_slab(const node_r & nd, int i, int & r_begin, int & nrows) {
-    const int v = (int) ((blockIdx.x + (unsigned) i * BATCH_ROT) % gridDim.x);
+// v: this CTA's slab index for the node = (blockIdx.x + i * BATCH_ROT) % gridDim.x, kept incrementally
+__device__ __forceinline__ void batch_slab(const node_r & nd, int & v, int & r_begin, int & nrows) {
     const int64_t rb = (int64_t) v * nd.rows_per_cta;
     int64_t n = (int64_t) nd.m - rb;
     if (n > nd.rows_per_cta) n = nd.rows_per_cta;
     if (n < 0) n = 0;
     r_begin = (int) (rb < nd.m ? rb : 0);
     nrows = (int) n;
+    v += BATCH_ROT % (int) gridDim.x;
+    if (v >= (int) gridDim.x) v -= (int) gridDim.x;
 }
 
 // ---------------------------------------------------------------- all activations of a list: f32 -> q8
@@ -153,21 +156,32 @@ __global__ void __launch_bounds__(256) k_quantize_batch(const __grid_constant__ 
     if (lane == 0) reinterpret_cast<float *>(q + nd.k)[kb] = __half2float(__float2half_rn(d));
 }
 
+// What the consumers need of a node; written to the head of the activation buffer by the activation
+// producer (one thread, ahead of time), read from shared memory by every consumer warp.
+struct cnode {
+    float * dst;
+    int k, pitch;             // pitch: bytes between rows inside a stage
+    int r_begin, nrows;       // this CTA's slab
+    int type, R, W, G;
+};
+static_assert(sizeof(cnode) <= BATCH_AHDR, "consumer header");
+
 // ---------------------------------------------------------------- consumer: one node
 // cc: running count of row pairs ("chunks") this CTA has seen; chunk j belongs to group j % G.
 template <int T>
-__device__ __forceinline__ void batch_consume(const node_r & nd, const int cw, const int lane,
-                                              const int r_begin, const int nrows, const int nbatch,
-                                              int & st_s, uint32_t & st_ph, int & cc,
+__device__ __forceinline__ void batch_consume(const cnode & nd, const int cw, const int lane,
+                                              int & st_s, uint32_t & st_ph, int & cc, int & git,
                                               const uint8_t * actbuf, const uint32_t acts_free, const uint32_t full, const uint32_t empty,
                                               float * part, const uint8_t * slots, const int S, const int slot_stride) {
     using IT = hitem<T>;
     const int W = nd.W, G = nd.G, R = nd.R;
+    const int r_begin = nd.r_begin, nrows = nd.nrows, pitch = nd.pitch;
+    const int nbatch = (nrows + R - 1) / R;
+    float * const dst = nd.dst + r_begin;
     const int g = cw / W, wg = cw - g * W;
     const int items = nd.k >> 7;
     const int idx = wg * 32 + lane;                      // the 128-weight item of a row this lane owns
     const bool active = g < G && idx < items;
-    const int row_pitch = batch_row_pitch(nd.row_bytes);
 
     // the slice of K this lane owns, in registers for the node
     acts128 acts;
@@ -193,7 +207,7 @@ __device__ __forceinline__ void batch_consume(const node_r & nd, const int cw, c
     __syncwarp();
     if (lane == 0) mbar_arrive_a(acts_free);              // this warp no longer reads the activation buffer
 
-    int git = 0;                                          // stages in which this group had rows: selects the partials buffer
+    // git: stages in which this group had rows (W > 1): selects the partials buffer
     int cmod = cc % G;                                    // owner group of the next chunk
     for (int lb = 0; lb < nbatch; lb++) {
         const int s = st_s;
@@ -207,8 +221,7 @@ __device__ __forceinline__ void batch_consume(const node_r & nd, const int cw, c
         while (cmod >= G) cmod -= G;
         float * pb = part + (size_t) ((g * 2 + (git & 1)) * W) * BATCH_RMAX;
         if (g < G && c_first < nchunks) {
-            const uint8_t * slot = slots + s * slot_stride;
-            const uint8_t * src0 = nd.w + (int64_t) (r_begin + lb * R) * nd.row_stride;
+            const uint8_t * slot = slots + s * slot_stride;       // rows start 16-byte aligned (batch_node_ok): no skew inside a stage
             for (int c = c_first; c < nchunks; c += G) {
                 const int r0 = c * FUSED_RB;
                 float acc[FUSED_RB];
@@ -219,10 +232,7 @@ __device__ __forceinline__ void batch_consume(const node_r & nd, const int cw, c
 #pragma unroll
                     for (int rr = 0; rr < FUSED_RB; rr++) {
                         const int r = (r0 + rr < rows_here) ? (r0 + rr) : (rows_here - 1);   // odd tail: recomputed, never stored
-                        const uint8_t * row = nd.contiguous
-                            ? slot + (reinterpret_cast<uintptr_t>(src0) & 15) + (size_t) r * nd.row_bytes
-                            : slot + (size_t) r * row_pitch + (reinterpret_cast<uintptr_t>(src0 + r * nd.row_stride) & 15);
-                        IT::load(w[rr], row, idx);
+                        IT::load(w[rr], slot + r * pitch, idx);
                     }
 #pragma unroll
                     for (int rr = 0; rr < FUSED_RB; rr++) acc[rr] += IT::dot(w[rr], idx & 1, acts);
@@ -235,7 +245,7 @@ __device__ __forceinline__ void batch_consume(const node_r & nd, const int cw, c
                 for (int off = 8; off > 0; off >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, off);
                 const int r = r0 + (lane >> 4);
                 if ((lane & 15) == 0 && r < rows_here) {
-                    if (W == 1) nd.dst[r_begin + lb * R + r] = v;
+                    if (W == 1) dst[lb * R + r] = v;
                     else        pb[r * W + wg] = v;
                 }
             }
@@ -255,7 +265,7 @@ __device__ __forceinline__ void batch_consume(const node_r & nd, const int cw, c
                     if (r < rows_here) {
                         float v = 0.0f;
                         for (int u = 0; u < W; u++) v += pb[r * W + u];
-                        nd.dst[r_begin + lb * R + r] = v;
+                        dst[lb * R + r] = v;
                     }
                 }
             }
@@ -293,11 +303,12 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
         int s = 0;
         uint32_t ph = 1;                                          // parity of the phase before the one to wait for; first lap: no wait
         bool lap0 = true;
+        int slab_v = (int) blockIdx.x;
         node_cache cache;
         for (int i = 0; i < a.count; i++) {
             const node_r nd = cache.get(a, i, lane);
             int r_begin, nrows;
-            batch_slab(nd, i, r_begin, nrows);
+            batch_slab(nd, slab_v, r_begin, nrows);
             const int R = nd.R;
             const int nbatch = (nrows + R - 1) / R;
             const int row_pitch = batch_row_pitch(nd.row_bytes);
@@ -337,14 +348,21 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
         // ===================================================== activation producer: q8 activations of node i -> buffer i % NB
         pdl_wait();                                               // k_quantize_batch (and whatever made x) is done
         node_cache cache;
+        int slab_v = (int) blockIdx.x;
         for (int i = 0; i < a.count; i++) {
             const node_r nd = cache.get(a, i, lane);
+            int r_begin, nrows;
+            batch_slab(nd, slab_v, r_begin, nrows);
             const int u = i % NB;
             if (i >= NB) mbar_wait(&acts_free[u], (uint32_t) (((i / NB) - 1) & 1));
             if (lane == 0) {
+                uint8_t * buf = actbufs + (size_t) u * a.acts_stride;
+                cnode * hd = reinterpret_cast<cnode *>(buf);
+                hd->dst = nd.dst; hd->k = nd.k; hd->pitch = nd.contiguous ? nd.row_bytes : batch_row_pitch(nd.row_bytes);
+                hd->r_begin = r_begin; hd->nrows = nrows; hd->type = nd.type; hd->R = nd.R; hd->W = nd.W; hd->G = nd.G;
                 const uint32_t bytes = batch_acts_bytes(nd.k);    // k % 256 == 0: a multiple of 16
-                mbar_arrive_expect_tx(&acts_ready[u], bytes);
-                bulk_g2s(actbufs + (size_t) u * a.acts_stride, nd.acts, bytes, &acts_ready[u]);
+                mbar_arrive_expect_tx(&acts_ready[u], bytes);     // release: the header is visible to whoever sees the phase complete
+                bulk_g2s(buf + BATCH_AHDR, nd.acts, bytes, &acts_ready[u]);
             }
             __syncwarp();
         }
@@ -353,27 +371,31 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
 
     // ========================================================= consumers
     const int cw = warp - 2;
-    int st_s = 0, cc = 0, prev_w = 1;
+    int st_s = 0, cc = 0, layout_w = 0, git = 0;
     uint32_t st_ph = 0;
     const uint32_t full_a = smem_u32(full), empty_a = smem_u32(empty), ready_a = smem_u32(acts_ready), free_a = smem_u32(acts_free);
-    const int slot_stride = a.slot_stride;
-    node_cache cache;
-    for (int i = 0; i < a.count; i++) {
-        const node_r nd = cache.get(a, i, lane);
-        // the partials area is laid out per (W, G): when either side of a node boundary uses it, every
-        // consumer warp must be past its last reduction before the new layout is written
-        if (nd.W > 1 || prev_w > 1) named_bar_sync(11, BATCH_NWC * 32);
-        prev_w = nd.W;
-        int r_begin, nrows;
-        batch_slab(nd, i, r_begin, nrows);
-        const int nbatch = (nrows + nd.R - 1) / nd.R;
-        const int u = i % NB;
-        const uint8_t * buf = actbufs + (size_t) u * a.acts_stride;
-        mbar_wait_a(ready_a + 8 * u, (uint32_t) ((i / NB) & 1));
-        if (nd.type == T_Q5_K) batch_consume<T_Q5_K>(nd, cw, lane, r_begin, nrows, nbatch, st_s, st_ph, cc, buf, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
-        else                   batch_consume<T_Q4_K>(nd, cw, lane, r_begin, nrows, nbatch, st_s, st_ph, cc, buf, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
+    const int slot_stride = a.slot_stride, count = a.count, acts_stride = a.acts_stride;
+    for (int i = 0, u = 0, uph = 0; i < count; i++) {
+        const uint8_t * buf = actbufs + u * acts_stride;
+        mbar_wait_a(ready_a + 8 * u, (uint32_t) uph);
+        const cnode nd = *reinterpret_cast<const cnode *>(buf);
+        // the partials area is laid out per W and only rows that need several warps (W > 1) use it: as long
+        // as every such node of the list has the same W, the groups, their barriers and their buffer
+        // parity (git) simply carry on across nodes; a different W needs every consumer warp to be past its
+        // last reduction before the new layout is written
+        if (nd.W > 1) {
+            if (layout_w != 0 && layout_w != nd.W) { named_bar_sync(13, BATCH_NWC * 32); git = 0; }
+            layout_w = nd.W;
+        }
+        if (nd.type == T_Q5_K) batch_consume<T_Q5_K>(nd, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
+        else                   batch_consume<T_Q4_K>(nd, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
+        if (++u == NB) { u = 0; uph ^= 1; }
     }
 }
+
+} // namespace b200
+
+namespace b200 {
 
 // ================================================================= host side
 // Can this MUL_MAT ride in a persistent launch?  (n = 1, plain 2-D, a format with a 128-weight item.)
@@ -408,7 +430,7 @@ struct batch_builder {
 
     // false: the workspace cannot hold this node's activation record
     bool add(int type, const uint8_t * w, int64_t row_stride, int64_t m, int64_t k, const float * x, float * dst, bool const_w, int grid) {
-        static const int slot_target = env_int("GGML_B200_BATCH_SLOT_BYTES", 36864);
+        static const int slot_target = env_int("GGML_B200_BATCH_SLOT_BYTES", 46080);
         batch_node & nd = args.nodes[args.count];
         const batch_node * prev = args.count > 0 ? &args.nodes[args.count - 1] : nullptr;
         if (prev && prev->x == x && prev->k == k) {
@@ -449,13 +471,13 @@ static int batch_launch(batch_builder & bb, cudaStream_t st) {
     const dev_caps & caps = current_caps();
     batch_args & a = bb.args;
     static const int s_env = env_int("GGML_B200_BATCH_STAGES", BATCH_MAX_STAGES);
-    static const int nb_env = env_int("GGML_B200_BATCH_ABUF", 3);
+    static const int nb_env = env_int("GGML_B200_BATCH_ABUF", 2);
     static const int pdl = env_int("GGML_B200_FUSED_PDL", 1);
     a.const_weights = bb.all_const ? 1 : 0;
     a.slot_stride = (bb.max_slot + 127) & ~127;
     a.off_part    = (2 * BATCH_MAX_STAGES + 2 * BATCH_MAX_ABUF) * 8;
     a.off_acts    = (a.off_part + 2 * BATCH_NWC * BATCH_RMAX * (int) sizeof(float) + 127) & ~127;
-    a.acts_stride = (int) batch_acts_record_bytes(a.kmax);
+    a.acts_stride = BATCH_AHDR + (int) batch_acts_record_bytes(a.kmax);
     int NB = nb_env < 2 ? 2 : (nb_env > BATCH_MAX_ABUF ? BATCH_MAX_ABUF : nb_env);
     while (NB > 2 && NB * a.acts_stride > 49152) NB--;           // keep the weight ring large
     a.NB = NB;
