@@ -214,6 +214,7 @@ struct b200_backend_ctx {
     bool                         exec_valid = false;
     bool                         graphs_enabled = true;
     uint64_t                     n_replays = 0, n_captures = 0, n_eager = 0;
+    std::vector<b200_mul_mat_node> run;      // scratch: the current run of MUL_MAT nodes
 };
 
 static const char * b200_backend_get_name(ggml_backend_t backend) {
@@ -250,11 +251,6 @@ static bool op_is_noop(const struct ggml_tensor * t) {
            t->op == GGML_OP_PERMUTE || t->op == GGML_OP_TRANSPOSE;
 }
 
-static size_t node_workspace(const struct ggml_tensor * node) {
-    if (node->op != GGML_OP_MUL_MAT) return 0;
-    return b200_mul_mat_workspace_size((int) node->src[0]->type, node->src[0]->ne, node->src[1]->ne);
-}
-
 // one node -> kernel-library calls on ctx->stream
 static void b200_compute_node(b200_backend_ctx * ctx, struct ggml_tensor * node) {
     const struct ggml_tensor * s0 = node->src[0];
@@ -288,6 +284,38 @@ static void b200_compute_node(b200_backend_ctx * ctx, struct ggml_tensor * node)
     }
 }
 
+// A MUL_MAT node as the kernel library's list entry.  Weights living in a buffer that ggml marked
+// GGML_BACKEND_BUFFER_USAGE_WEIGHTS are constant for the life of the graph.
+static b200_mul_mat_node to_list_entry(const struct ggml_tensor * node) {
+    const struct ggml_tensor * s0 = node->src[0];
+    const struct ggml_tensor * s1 = node->src[1];
+    b200_mul_mat_node e;
+    memset(&e, 0, sizeof(e));
+    e.type_a = (int32_t) s0->type;
+    const struct ggml_tensor * base = s0->view_src ? s0->view_src : s0;
+    e.flags = (base->buffer && base->buffer->usage == GGML_BACKEND_BUFFER_USAGE_WEIGHTS) ? B200_MUL_MAT_CONST_WEIGHTS : 0u;
+    e.a_dev = s0->data; e.b_dev = (const float *) s1->data; e.dst_dev = (float *) node->data;
+    for (int d = 0; d < 4; d++) { e.ne_a[d] = s0->ne[d]; e.nb_a[d] = s0->nb[d]; e.ne_b[d] = s1->ne[d]; e.nb_b[d] = s1->nb[d]; }
+    return e;
+}
+
+// Runs of consecutive MUL_MAT nodes go to the library as ONE list (b200_mul_mat_batch): independent decode
+// mat-vecs of a run (q/k/v, gate/up, or a whole per-layer GEMM graph) then share a persistent launch; the
+// library cuts the list wherever a node depends on an earlier one.  fn_run(first, count) / fn_other(node).
+template <typename FR, typename FO>
+static void walk_graph(struct ggml_cgraph * cgraph, std::vector<b200_mul_mat_node> & run, FR fn_run, FO fn_other) {
+    const int n = ggml_graph_n_nodes(cgraph);
+    run.clear();
+    for (int i = 0; i < n; i++) {
+        struct ggml_tensor * node = ggml_graph_node(cgraph, i);
+        if (op_is_noop(node)) continue;
+        if (node->op == GGML_OP_MUL_MAT) { run.push_back(to_list_entry(node)); continue; }
+        if (!run.empty()) { fn_run(run); run.clear(); }
+        fn_other(node);
+    }
+    if (!run.empty()) { fn_run(run); run.clear(); }
+}
+
 static void make_key(struct ggml_cgraph * cgraph, std::vector<graph_key_entry> & key) {
     const int n = ggml_graph_n_nodes(cgraph);
     key.clear();
@@ -311,18 +339,18 @@ static void make_key(struct ggml_cgraph * cgraph, std::vector<graph_key_entry> &
 static enum ggml_status b200_backend_graph_compute(ggml_backend_t backend, struct ggml_cgraph * cgraph) {
     b200_backend_ctx * ctx = (b200_backend_ctx *) backend->context;
     CUDA_OK(cudaSetDevice(ctx->device));
-    const int n = ggml_graph_n_nodes(cgraph);
 
     // size the workspace before anything is launched (no allocation inside a capture)
     size_t need = 0;
     int n_work = 0;
-    for (int i = 0; i < n; i++) {
-        struct ggml_tensor * node = ggml_graph_node(cgraph, i);
-        if (op_is_noop(node)) continue;
-        n_work++;
-        const size_t w = node_workspace(node);
-        if (w > need) need = w;
-    }
+    std::vector<b200_mul_mat_node> & run = ctx->run;
+    walk_graph(cgraph, run,
+               [&](std::vector<b200_mul_mat_node> & r) {
+                   n_work += (int) r.size();
+                   const size_t w = b200_mul_mat_batch_workspace_size(r.data(), (int64_t) r.size());
+                   if (w > need) need = w;
+               },
+               [&](struct ggml_tensor *) { n_work++; });
     if (need > ctx->ws_size) {
         CUDA_OK(cudaStreamSynchronize(ctx->stream));
         if (ctx->ws) CUDA_OK(cudaFree(ctx->ws));
@@ -353,11 +381,11 @@ static enum ggml_status b200_backend_graph_compute(ggml_backend_t backend, struc
         return GGML_STATUS_SUCCESS;
     }
     if (capture) CUDA_OK(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeRelaxed));
-    for (int i = 0; i < n; i++) {
-        struct ggml_tensor * node = ggml_graph_node(cgraph, i);
-        if (op_is_noop(node)) continue;
-        b200_compute_node(ctx, node);
-    }
+    walk_graph(cgraph, run,
+               [&](std::vector<b200_mul_mat_node> & r) {
+                   B200_OK_OR_ABORT(b200_mul_mat_batch(r.data(), (int64_t) r.size(), ctx->ws, ctx->ws_size, ctx->stream));
+               },
+               [&](struct ggml_tensor * node) { b200_compute_node(ctx, node); });
     if (capture) {
         cudaGraph_t graph = nullptr;
         CUDA_OK(cudaStreamEndCapture(ctx->stream, &graph));
