@@ -126,61 +126,60 @@ def random_blocks_device(torch, dev, wtype, rows, k, seed):
 
 
 class DecodeStack:
-    """All matrices of the workload resident on one device + host/device activation and output arenas."""
+    """All matrices of the workload resident on one device + host/device activation and output arenas.
+
+    world > 1 (row split): rank r owns rows [b_r, b_{r+1}) of every matrix (row_split.split_bounds).  The
+    output arena is RANK-MAJOR: y[r] holds rank r's row blocks of all matrices back to back, so that after
+    the step's single persistent launch ONE all-gather of the arena leaves every rank with every output
+    (matrix i, rank r's rows at y[r, off_i : off_i + rows_r(i)])."""
 
     def __init__(self, kern, mats, n, rank=0, world=1):
         import torch
         import b200
+        import row_split
+        assert n == 1
         self.torch, self.kern, self.mats, self.n, self.rank, self.world = torch, kern, mats, n, rank, world
         dev = kern.device
-        self.rows = [workloads.split_rows(mt.m, world, rank) for mt in mats]       # my row block per matrix
+        self.bounds = [row_split.split_bounds(mt.m, world) for mt in mats]
+        self.rows = [(b[rank], b[rank + 1]) for b in self.bounds]                   # my row block per matrix
+        for b in self.bounds:
+            assert len({b[r + 1] - b[r] for r in range(world)}) == 1, "bench shapes split evenly"
         self.weights = [random_blocks_device(torch, dev, mt.type, hi - lo, mt.k, 0xB200 + 7919 * i + rank)
                         for i, (mt, (lo, hi)) in enumerate(zip(mats, self.rows))]
         x_off, y_off, xo, yo = [], [], 0, 0
-        for mt in mats:
+        for mt, (lo, hi) in zip(mats, self.rows):
             x_off.append(xo); xo += n * mt.k
-            y_off.append(yo); yo += n * mt.m                                        # full (gathered) output
-        self.x_off, self.y_off = x_off, y_off
+            y_off.append(yo); yo += n * (hi - lo)                                   # my block; same size on every rank
+        self.x_off, self.y_off, self.local_out = x_off, y_off, yo
         g = torch.Generator(device="cpu"); g.manual_seed(1234)
         self.x_host = (torch.rand(xo, generator=g) * 2 - 1).pin_memory()
-        self.y_host = torch.empty(yo, dtype=torch.float32).pin_memory()
+        self.y_host = torch.empty(world * yo, dtype=torch.float32).pin_memory()
         self.x_dev = self.x_host.to(dev)
-        self.y_dev = torch.zeros(yo, dtype=torch.float32, device=dev)
-        # node list: my row block of every matrix; dst = my slice of the full output (n == 1: contiguous)
-        assert n == 1 or world == 1
+        self.y_dev = torch.zeros((world, yo), dtype=torch.float32, device=dev)
         Nodes = b200.MulMatNode * len(mats)
         self.nodes = Nodes(*[
             b200.mul_mat_node(mt.type, w.data_ptr(), hi - lo, mt.k, self.x_dev.data_ptr() + 4 * x_off[i], n,
-                              self.y_dev.data_ptr() + 4 * (y_off[i] + lo), const_weights=True)
+                              self.y_dev[rank].data_ptr() + 4 * y_off[i], const_weights=True)
             for i, (mt, w, (lo, hi)) in enumerate(zip(mats, self.weights, self.rows))])
-        # output column stride: b200_mul_mat writes dst as [n][m_local]; with n == 1 that is the slice itself
         self.ws = torch.empty(int(kern.lib.b200_mul_mat_batch_workspace_size(self.nodes, len(mats))) + 256,
                               dtype=torch.uint8, device=dev)
         self.local_weight_bytes = sum(int(w.numel()) for w in self.weights)
         self.local_alg_bytes = sum((hi - lo) * (mt.k // workloads.BLOCK_ELEMS[mt.type]) * workloads.BLOCK_BYTES[mt.type]
                                    + n * mt.k * 4 + n * (hi - lo) * 4 for mt, (lo, hi) in zip(mats, self.rows))
-        self.x_bytes, self.y_bytes = 4 * xo, 4 * yo
+        self.x_bytes, self.y_bytes = 4 * xo, 4 * world * yo
 
     def compute(self):
-        """Every MUL_MAT of the step: one C-ABI call (world 1), or per matrix one call + one all-gather
-        of the f32 row blocks when the rows are split over ranks."""
-        if self.world == 1:
-            self.kern.mul_mat_batch(self.nodes, ws=self.ws)
-            return
-        import ctypes
-        import torch.distributed as dist
-        lib, kern = self.kern.lib, self.kern
-        for i, mt in enumerate(self.mats):
-            kern._check(lib.b200_mul_mat_batch(ctypes.byref(self.nodes[i]), 1, self.ws.data_ptr(), self.ws.numel(),
-                                               kern._stream()), "mul_mat_batch")
-            lo, hi = self.rows[i]
-            full = self.y_dev[self.y_off[i]: self.y_off[i] + mt.m]
-            dist.all_gather_into_tensor(full, full[lo:hi])
+        """Every MUL_MAT of the step in one C-ABI call (one quantize + one persistent launch); with the rows
+        split over ranks, one all-gather of the rank-major output arena follows."""
+        self.kern.mul_mat_batch(self.nodes, ws=self.ws)
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.all_gather_into_tensor(self.y_dev.view(-1), self.y_dev[self.rank])
 
     def step_e2e(self):
         self.x_dev.copy_(self.x_host, non_blocking=True)
         self.compute()
-        self.y_host.copy_(self.y_dev, non_blocking=True)
+        self.y_host.copy_(self.y_dev.view(-1), non_blocking=True)
 
 
 # ------------------------------------------------------------------------------------- timing
@@ -439,7 +438,7 @@ def main():
                    "algorithmic_bytes_per_step": alg_total,
                    "l2": "inputs larger than L2 (3.7 GB of weights per GPU streamed once per step; no flush)",
                    "launch": "CUDA graph replay" if graph is not None else "eager",
-                   "parallelism": "single GPU" if world == 1 else f"row-split x{world} + NCCL all-gather per MUL_MAT"},
+                   "parallelism": "single GPU" if world == 1 else f"row-split x{world}: one persistent launch per rank + one NCCL all-gather of the rank-major output arena per step"},
         "e2e": {"value": round(e2e, 1), "unit": UNIT, "h2d_bytes_per_step": stack.x_bytes,
                 "d2h_bytes_per_step": stack.y_bytes, "ms_per_step": round(sec_e2e / args.steps * 1e3, 4),
                 "path": "pinned host activations -> b200_mul_mat_batch (C ABI) -> pinned host outputs, sync per step"},
