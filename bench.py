@@ -41,6 +41,13 @@ UNIT = "GB/s"
 WORKLOAD = "llama2-7b all projections, Q4_K, decode mat-vec n=1 (BASELINE configs[2])"
 
 
+def dbg(msg):
+    """milestones to stderr when BENCH_DEBUG is set (multi-rank hangs are otherwise silent)"""
+    if os.environ.get("BENCH_DEBUG"):
+        sys.stderr.write(f"[bench r{os.environ.get('RANK', '0')} {time.perf_counter():.1f}] {msg}\n")
+        sys.stderr.flush()
+
+
 def env_int(name, dflt):
     try:
         return int(os.environ.get(name, dflt))
@@ -355,15 +362,18 @@ def main():
         import torch.distributed as dist
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dbg("process group up")
     kern = b200.Kernels(device=local_rank)
     mats = workloads.llama2_7b_stack(args.wtype, row_mult=world)
     stack = DecodeStack(kern, mats, 1, rank, world)
     lib = kern.lib
+    dbg("stack built")
 
     # ---- warm-up (eager), then capture the step into a CUDA graph
     for _ in range(args.warmup):
         stack.compute()
     torch.cuda.synchronize()
+    dbg("eager warm-up done")
     c0 = int(lib.b200_launch_count())
     graph, step = None, stack.compute
     try:
@@ -385,15 +395,18 @@ def main():
         c0 = int(lib.b200_launch_count())
         stack.compute()
     launches_per_step = int(lib.b200_launch_count()) - c0
+    dbg(f"capture done (graph={graph is not None})")
     for _ in range(3):
         step()
     torch.cuda.synchronize()
+    dbg("graph warm-up done")
 
     # ---- device-resident timed region
     clocks = ClockSampler(local_rank)
     if rank == 0:
         clocks.start()
     sec = timed_loop(torch, step, args.steps, dist)
+    dbg("device-resident region done")
     # keep the sampler running through the e2e region too (short regions give few samples)
     # ---- end-to-end: host activations in, host outputs out, every step
     def e2e_step():
@@ -402,6 +415,7 @@ def main():
     for _ in range(3):
         e2e_step()
     sec_e2e = timed_loop(torch, e2e_step, args.steps, dist)
+    dbg("e2e region done")
     clk = clocks.stop() if rank == 0 else None
 
     # parity guard: the host copy of the outputs is what the device computed, and it is finite
@@ -465,9 +479,18 @@ def main():
         line["cpu_baseline"] = {k: info[k] for k in ("value", "unit", "cores", "kind", "sample")}
     if rank == 0:
         print(json.dumps(line), flush=True)
+    dbg("line printed")
     if dist is not None:
+        # Tearing the process group down while a captured graph still holds NCCL work hung both ranks
+        # (measured, NCCL 2.28.9): drop the graph, drain, meet once more and leave without the teardown.
+        graph = None
+        step = None
+        torch.cuda.synchronize()
         dist.barrier()
-        dist.destroy_process_group()
+        torch.cuda.synchronize()
+        dbg("exit")
+        sys.stdout.flush(); sys.stderr.flush()
+        os._exit(0)
 
 
 if __name__ == "__main__":
