@@ -236,26 +236,34 @@ extern "C" int b200_mul_mat_batch(const b200_mul_mat_node * nodes, int64_t count
     if (count < 0 || (count > 0 && !nodes)) return B200_ERR_SHAPE;
     cudaStream_t st = (cudaStream_t) stream;
     const bool persistent = !env_int("GGML_B200_NO_BATCH_KERNEL", 0);
-    static thread_local batch_builder * bb = nullptr;         // 28 KB parameter block, reused
+    // one builder (28 KB parameter block, reused) per format family = kernel instantiation; the nodes of a
+    // pending set are independent, so sorting them into per-family launches keeps the semantics
+    static thread_local batch_builder * fam_bb[2] = { nullptr, nullptr };
     static thread_local range_set reads, writes;
-    if (!bb) bb = new batch_builder();
-    bb->reset((uint8_t *) workspace_dev, workspace_dev ? workspace_bytes : 0);
+    if (!fam_bb[0]) { fam_bb[0] = new batch_builder(0); fam_bb[1] = new batch_builder(1); }
+    ws_cursor cur;
+    cur.reset((uint8_t *) workspace_dev, workspace_bytes);
+    fam_bb[0]->reset(); fam_bb[1]->reset();
     reads.clear(); writes.clear();
     const int grid = current_caps().sm_count;
     auto flush = [&]() -> int {
-        if (bb->empty()) return B200_OK;
         reads.clear(); writes.clear();
-        int rc;
-        if (bb->args.count == 1 && !env_int("GGML_B200_BATCH_SINGLE", 0)) {
-            // one node: the per-node decode kernel (same per-row arithmetic, one launch instead of two)
-            const batch_node nd = bb->args.nodes[0];
-            rc = mmvq_fused_try(nd.type, nd.w, nd.row_stride, nd.m, nd.k, nd.x, nd.dst, bb->all_const, st);
-            if (rc == B200_STREAM_NOT_APPLICABLE) rc = batch_launch(*bb, st);
-        } else {
-            rc = batch_launch(*bb, st);
+        int rc = B200_OK;
+        for (int f = 0; f < 2 && rc == B200_OK; f++) {
+            batch_builder * bb = fam_bb[f];
+            if (bb->empty()) continue;
+            if (bb->args.count == 1 && !env_int("GGML_B200_BATCH_SINGLE", 0)) {
+                // one node: the per-node decode kernel (same per-row arithmetic, one launch instead of two)
+                const batch_node nd = bb->args.nodes[0];
+                rc = mmvq_fused_try(nd.type, nd.w, nd.row_stride, nd.m, nd.k, nd.x, nd.dst, bb->all_const, st);
+                if (rc == B200_STREAM_NOT_APPLICABLE) rc = batch_launch(*bb, st);
+            } else {
+                rc = batch_launch(*bb, st);
+            }
+            bb->reset();
         }
-        // stream order: the next launch's quantizer starts after this launch has finished with the workspace
-        bb->reset((uint8_t *) workspace_dev, workspace_dev ? workspace_bytes : 0);
+        // stream order: the next launch's quantizer starts after these launches have finished with the workspace
+        cur.reset((uint8_t *) workspace_dev, workspace_bytes);
         return rc;
     };
     for (int64_t i = 0; i < count; i++) {
@@ -268,16 +276,17 @@ extern "C" int b200_mul_mat_batch(const b200_mul_mat_node * nodes, int64_t count
         if (plain) {
             const uintptr_t x0 = (uintptr_t) nd.b_dev, x1 = x0 + (size_t) k * 4;
             const uintptr_t d0 = (uintptr_t) nd.dst_dev, d1 = d0 + (size_t) m * 4;
+            batch_builder * bb = fam_bb[nd.type_a == T_Q6_K ? 1 : 0];
             if (bb->full() || writes.hits(x0, x1) || writes.hits(d0, d1) || reads.hits(d0, d1)) {
                 const int rc = flush();
                 if (rc) return rc;
             }
             const bool cw = (nd.flags & B200_MUL_MAT_CONST_WEIGHTS) != 0;
-            bool ok = bb->add(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, nd.b_dev, nd.dst_dev, cw, grid);
-            if (!ok && !bb->empty()) {                         // workspace full: launch what is pending, start over
+            bool ok = bb->add(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, nd.b_dev, nd.dst_dev, cw, grid, cur);
+            if (!ok && !(fam_bb[0]->empty() && fam_bb[1]->empty())) {      // workspace full: launch what is pending, start over
                 const int rc = flush();
                 if (rc) return rc;
-                ok = bb->add(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, nd.b_dev, nd.dst_dev, cw, grid);
+                ok = bb->add(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, nd.b_dev, nd.dst_dev, cw, grid, cur);
             }
             if (ok) { reads.add(x0, x1); writes.add(d0, d1); continue; }
             // no room even for one record: the per-node path below reports the workspace error

@@ -163,6 +163,8 @@ struct cnode {
     int k, pitch;             // pitch: bytes between rows inside a stage
     int r_begin, nrows;       // this CTA's slab
     int type, R, W, G;
+    int skew0, rs16;          // formats whose rows are not 16-byte aligned: (address of slab row i) % 16 = (skew0 + i * rs16) % 16
+    int contiguous;
 };
 static_assert(sizeof(cnode) <= BATCH_AHDR, "consumer header");
 
@@ -196,9 +198,11 @@ __device__ __forceinline__ void batch_consume(const cnode & nd, const int cw, co
             const int4 hi = *reinterpret_cast<const int4 *>(yq + idx * 128 + (((2 * j + 1 + idx) & 7) << 4));
             acts.q[j][0] = lo.x; acts.q[j][1] = lo.y; acts.q[j][2] = lo.z; acts.q[j][3] = lo.w;
             acts.q[j][4] = hi.x; acts.q[j][5] = hi.y; acts.q[j][6] = hi.z; acts.q[j][7] = hi.w;
-            int sum = 0;
+            int sum = 0, sum_hi = 0;
 #pragma unroll
-            for (int u = 0; u < 8; u++) sum = __dp4a(0x01010101, acts.q[j][u], sum);
+            for (int u = 0; u < 4; u++) { sum = __dp4a(0x01010101, acts.q[j][u], sum); sum_hi = __dp4a(0x01010101, acts.q[j][u + 4], sum_hi); }
+            if (IT::need_ys16) { acts.ys16[2 * j] = sum; acts.ys16[2 * j + 1] = sum_hi; }
+            sum += sum_hi;
             const float d = dd[j];
             acts.sd[j] = d * (float) sum;
             acts.d[j]  = (IT::hi_div16 && (j & 1)) ? d * 0.0625f : d;
@@ -221,21 +225,36 @@ __device__ __forceinline__ void batch_consume(const cnode & nd, const int cw, co
         while (cmod >= G) cmod -= G;
         float * pb = part + (size_t) ((g * 2 + (git & 1)) * W) * BATCH_RMAX;
         if (g < G && c_first < nchunks) {
-            const uint8_t * slot = slots + s * slot_stride;       // rows start 16-byte aligned (batch_node_ok): no skew inside a stage
+            const uint8_t * slot = slots + s * slot_stride;       // 16-byte aligned formats: no skew inside a stage
             for (int c = c_first; c < nchunks; c += G) {
                 const int r0 = c * FUSED_RB;
                 float acc[FUSED_RB];
 #pragma unroll
                 for (int rr = 0; rr < FUSED_RB; rr++) acc[rr] = 0.0f;
                 if (active) {
-                    typename IT::wts w[FUSED_RB];
-#pragma unroll
-                    for (int rr = 0; rr < FUSED_RB; rr++) {
+                    auto row_off = [&](int rr) -> int {
                         const int r = (r0 + rr < rows_here) ? (r0 + rr) : (rows_here - 1);   // odd tail: recomputed, never stored
-                        IT::load(w[rr], slot + r * pitch, idx);
-                    }
+                        int off = r * pitch;
+                        if (!IT::aligned16) off += nd.contiguous ? ((nd.skew0 + lb * R * nd.rs16) & 15) : ((nd.skew0 + (lb * R + r) * nd.rs16) & 15);
+                        return off;
+                    };
+                    if (IT::aligned16) {
+                        // light items: both rows' words in flight before the first dot
+                        typename IT::wts w[FUSED_RB];
 #pragma unroll
-                    for (int rr = 0; rr < FUSED_RB; rr++) acc[rr] += IT::dot(w[rr], idx & 1, acts);
+                        for (int rr = 0; rr < FUSED_RB; rr++) IT::load(w[rr], slot + row_off(rr), idx);
+#pragma unroll
+                        for (int rr = 0; rr < FUSED_RB; rr++) acc[rr] += IT::dot(w[rr], idx & 1, acts);
+                    } else {
+                        // heavy items (27 words + realignment): one row at a time keeps the registers in bounds
+#pragma unroll 1
+                        for (int rr = 0; rr < FUSED_RB; rr++) {
+                            typename IT::wts w;
+                            IT::load(w, slot + row_off(rr), idx);
+                            const float v = IT::dot(w, idx & 1, acts);
+                            if (rr == 0) acc[0] += v; else acc[1] += v;
+                        }
+                    }
                 }
                 // one shuffle tree for the row pair: lanes 0-15 end with row r0, lanes 16-31 with row r0 + 1
                 float v = (lane & 16) ? acc[1] : acc[0];
@@ -275,6 +294,12 @@ __device__ __forceinline__ void batch_consume(const cnode & nd, const int cw, co
 }
 
 // ---------------------------------------------------------------- the persistent kernel
+// 14 warps = 4 + 4 + 3 + 3 per SM sub-partition: 4 warps share 16 K registers -> 128 per thread is the ceiling.
+// One instantiation per format family: FAM 0 = Q4_K / Q5_K (16-byte aligned 128-weight items), FAM 1 = Q6_K.
+// Mixed in one kernel, Q6_K's 27-word realigned items push the loop state of ALL formats into local memory
+// (measured: Q4_K falls from 5.8 to 2.8 TB/s); the nodes of a list are independent, so b200_mul_mat_batch
+// simply sorts them into one launch per family.
+template <int FAM>
 __global__ void __launch_bounds__(BATCH_THREADS, 1)
 k_mmvq_batch(const __grid_constant__ batch_args a) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -360,6 +385,8 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
                 cnode * hd = reinterpret_cast<cnode *>(buf);
                 hd->dst = nd.dst; hd->k = nd.k; hd->pitch = nd.contiguous ? nd.row_bytes : batch_row_pitch(nd.row_bytes);
                 hd->r_begin = r_begin; hd->nrows = nrows; hd->type = nd.type; hd->R = nd.R; hd->W = nd.W; hd->G = nd.G;
+                hd->skew0 = (int) (reinterpret_cast<uintptr_t>(nd.w + (int64_t) r_begin * nd.row_stride) & 15);
+                hd->rs16 = (int) (nd.row_stride & 15); hd->contiguous = nd.contiguous;
                 const uint32_t bytes = batch_acts_bytes(nd.k);    // k % 256 == 0: a multiple of 16
                 mbar_arrive_expect_tx(&acts_ready[u], bytes);     // release: the header is visible to whoever sees the phase complete
                 bulk_g2s(buf + BATCH_AHDR, nd.acts, bytes, &acts_ready[u]);
@@ -387,7 +414,8 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
             if (layout_w != 0 && layout_w != nd.W) { named_bar_sync(13, BATCH_NWC * 32); git = 0; }
             layout_w = nd.W;
         }
-        if (nd.type == T_Q5_K) batch_consume<T_Q5_K>(nd, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
+        if (FAM == 1)               batch_consume<T_Q6_K>(nd, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
+        else if (nd.type == T_Q5_K) batch_consume<T_Q5_K>(nd, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
         else                   batch_consume<T_Q4_K>(nd, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
         if (++u == NB) { u = 0; uph ^= 1; }
     }
@@ -400,11 +428,12 @@ namespace b200 {
 // ================================================================= host side
 // Can this MUL_MAT ride in a persistent launch?  (n = 1, plain 2-D, a format with a 128-weight item.)
 static bool batch_node_ok(int type, const uint8_t * w, int64_t row_stride, int64_t m, int64_t k, const float * x) {
-    if (type != T_Q4_K && type != T_Q5_K) return false;
+    if (type != T_Q4_K && type != T_Q5_K && type != T_Q6_K) return false;
     if (m < 1 || m > 0x7FFFFFFF || k < 1024 || k % 256 != 0) return false;
     if (ceil_div(k / 128, 32) > 8) return false;                 // k <= 32768: one item per lane, same (W, lane) map as the per-node kernel
     if (reinterpret_cast<uintptr_t>(x) % 16 != 0) return false;
-    if (!hitem<T_Q4_K>::ok(k, row_stride, reinterpret_cast<uintptr_t>(w))) return false;
+    if (type == T_Q6_K ? !hitem<T_Q6_K>::ok(k, row_stride, reinterpret_cast<uintptr_t>(w))
+                       : !hitem<T_Q4_K>::ok(k, row_stride, reinterpret_cast<uintptr_t>(w))) return false;
     const int64_t row_bytes = k / 256 * type_bytes(type);
     if (row_stride < row_bytes) return false;
     return true;
@@ -412,24 +441,29 @@ static bool batch_node_ok(int type, const uint8_t * w, int64_t row_stride, int64
 
 static inline size_t batch_acts_record_bytes(int64_t k) { return ((size_t) (k + k / 32 * 4) + 127) & ~(size_t) 127; }
 
+// where the next q8 activation record goes in the caller's workspace (shared by the families' builders)
+struct ws_cursor {
+    uint8_t * p = nullptr;
+    size_t left = 0;
+    void reset(uint8_t * w, size_t bytes) {
+        p = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(w) + 127) & ~(uintptr_t) 127);
+        const size_t skew = (size_t) (p - w);
+        left = (w && bytes > skew) ? bytes - skew : 0;
+    }
+};
+
 struct batch_builder {
     batch_args args;
     int max_slot = 0;
     bool all_const = true;
-    uint8_t * ws = nullptr;            // workspace cursor for the activation records
-    size_t ws_left = 0;
-    batch_builder() { reset(nullptr, 0); }
-    void reset(uint8_t * w, size_t bytes) {
-        args.count = 0; args.kmax = 0; max_slot = 0; all_const = true;
-        ws = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(w) + 127) & ~(uintptr_t) 127);
-        const size_t skew = (size_t) (ws - w);
-        ws_left = bytes > skew ? bytes - skew : 0;
-    }
+    int  fam = 0;                     // format family of this builder's nodes (kernel instantiation)
+    explicit batch_builder(int family) : fam(family) { reset(); }
+    void reset() { args.count = 0; args.kmax = 0; max_slot = 0; all_const = true; }
     bool full() const { return args.count >= BATCH_MAX_NODES; }
     bool empty() const { return args.count == 0; }
 
     // false: the workspace cannot hold this node's activation record
-    bool add(int type, const uint8_t * w, int64_t row_stride, int64_t m, int64_t k, const float * x, float * dst, bool const_w, int grid) {
+    bool add(int type, const uint8_t * w, int64_t row_stride, int64_t m, int64_t k, const float * x, float * dst, bool const_w, int grid, ws_cursor & cur) {
         static const int slot_target = env_int("GGML_B200_BATCH_SLOT_BYTES", 46080);
         batch_node & nd = args.nodes[args.count];
         const batch_node * prev = args.count > 0 ? &args.nodes[args.count - 1] : nullptr;
@@ -437,8 +471,8 @@ struct batch_builder {
             nd.acts = prev->acts; nd.quantize = 0;              // same activations as the previous node (gate/up, q/k/v)
         } else {
             const size_t need = batch_acts_record_bytes(k);
-            if (need > ws_left) return false;
-            nd.acts = ws; nd.quantize = 1; ws += need; ws_left -= need;
+            if (need > cur.left) return false;
+            nd.acts = cur.p; nd.quantize = 1; cur.p += need; cur.left -= need;
         }
         args.count++;
         nd.w = w; nd.x = x; nd.dst = dst; nd.row_stride = row_stride; nd.m = (int) m; nd.k = (int) k;
@@ -489,12 +523,13 @@ static int batch_launch(batch_builder & bb, cudaStream_t st) {
     a.S = S;
     const size_t smem = (size_t) a.off_slots + (size_t) S * a.slot_stride;
 
-    static size_t smem_set[64];
+    static size_t smem_set[2][64];
     int dev = 0; cudaGetDevice(&dev); if (dev < 0 || dev >= 64) dev = 0;
-    if (smem > smem_set[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(k_mmvq_batch, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+    auto kern = bb.fam == 1 ? k_mmvq_batch<1> : k_mmvq_batch<0>;
+    if (smem > smem_set[bb.fam][dev]) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
         if (e != cudaSuccess) return -(int) e;
-        smem_set[dev] = smem;
+        smem_set[bb.fam][dev] = smem;
     }
     // 1. every activation vector of the list -> q8 (one launch)
     {
@@ -510,7 +545,7 @@ static int batch_launch(batch_builder & bb, cudaStream_t st) {
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
-    const cudaError_t e = cudaLaunchKernelEx(&cfg, k_mmvq_batch, a);
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, a);
     if (e != cudaSuccess) return -(int) e;
     b200_count_launch(1);
     return B200_OK;

@@ -50,7 +50,8 @@ constexpr int FUSED_RB = 2;          // rows a warp carries at once (one shuffle
 struct acts128 {
     int   q[4][8];
     float d[4];       // d of block j (the odd blocks pre-divided by 16 where the format asks for it)
-    float sd[4];      // d * sum(q) of block j
+    float sd[4];      // d * sum(q) of block j                      (formats with a min / offset per 32)
+    int   ys16[8];    // sum(q) of each 16-value half of block j       (Q6_K: one scale per 16, offset 32)
 };
 
 // ================================================================= per-format half-block items
@@ -59,6 +60,8 @@ template <int T> struct hitem;
 // ---- Q4_K: block 144 B = d,dmin | scales[12] | qs[128]; item h of block b: sub-blocks 4h..4h+3,
 // quant bytes qs[64h, 64h+64): byte 32g+l holds element 64g+l (low nibble) and 64g+32+l (high nibble).
 template <> struct hitem<T_Q4_K> {
+    static constexpr bool aligned16 = true;    // rows and items are 16-byte aligned: no skew inside a stage
+    static constexpr bool need_ys16 = false;
     static constexpr bool hi_div16 = true;     // high nibbles are used in place (x16), folded into d
     static bool ok(int64_t k, int64_t row_stride, uintptr_t base) { return k % 256 == 0 && row_stride % 16 == 0 && base % 16 == 0; }
     struct wts { uint4 hdr; uint4 q[4]; };
@@ -93,11 +96,16 @@ template <> struct hitem<T_Q4_K> {
         }
         return d * fd - dmin * fm;
     }
+    static __device__ __forceinline__ float load_dot(const uint8_t * row, int idx, const acts128 & a) {
+        wts w; load(w, row, idx); return dot(w, idx & 1, a);
+    }
 };
 
 // ---- Q5_K: block 176 B = d,dmin | scales[12] | qh[32] | qs[128]; bit j of qh[l] is the 5th bit of
 // element l of sub-block j.
 template <> struct hitem<T_Q5_K> {
+    static constexpr bool aligned16 = true;
+    static constexpr bool need_ys16 = false;
     static constexpr bool hi_div16 = false;
     static bool ok(int64_t k, int64_t row_stride, uintptr_t base) { return k % 256 == 0 && row_stride % 16 == 0 && base % 16 == 0; }
     struct wts { uint4 hdr; uint4 qh[2]; uint4 q[4]; };
@@ -135,6 +143,92 @@ template <> struct hitem<T_Q5_K> {
             fm += a.sd[2 * g] * (float) m0 + a.sd[2 * g + 1] * (float) m1;
         }
         return d * fd - dmin * fm;
+    }
+    static __device__ __forceinline__ float load_dot(const uint8_t * row, int idx, const acts128 & a) {
+        wts w; load(w, row, idx); return dot(w, idx & 1, a);
+    }
+};
+
+// ---- Q6_K: block 210 B = ql[128] | qh[64] | int8 scales[16] | f16 d (src/ggml-common.h:330-336); item h of
+// block b = elements 128h .. 128h+127 = four streams of 32 (src/ggml-quants.c:1762-1791):
+//   stream 0: (ql[64h+l]    & 15) | ((qh[32h+l]     ) & 3) << 4      stream 2: (ql[64h+l]    >> 4) | ((qh[32h+l] >> 4) & 3) << 4
+//   stream 1: (ql[64h+32+l] & 15) | ((qh[32h+l] >> 2) & 3) << 4      stream 3: (ql[64h+32+l] >> 4) | ((qh[32h+l] >> 6) & 3) << 4
+// w = d * scales[8h + 2s + l/16] * (q - 32).  Blocks are only 2-byte aligned: every run of words is fetched as
+// aligned words + funnel shift.  The -32 is taken out of the dot product through the activation sums per 16.
+template <> struct hitem<T_Q6_K> {
+    static constexpr bool aligned16 = false;
+    static constexpr bool need_ys16 = true;
+    static constexpr bool hi_div16 = false;
+    static bool ok(int64_t k, int64_t row_stride, uintptr_t base) { return k % 256 == 0 && row_stride % 2 == 0 && base % 2 == 0; }
+    struct wts { uint32_t ql[16]; uint32_t qh[8]; uint32_t sc[2]; uint32_t d; };
+    template <int N>
+    static __device__ __forceinline__ void run(uint32_t (&out)[N], const uint8_t * p) {      // N words from a 2-byte aligned address
+        const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+        const uint32_t * A = reinterpret_cast<const uint32_t *>(a & ~(uintptr_t) 3);
+        const uint32_t sh = (uint32_t) (a & 2) * 8;
+        uint32_t x[N + 1];
+#pragma unroll
+        for (int i = 0; i <= N; i++) x[i] = A[i];
+#pragma unroll
+        for (int i = 0; i < N; i++) out[i] = __funnelshift_r(x[i], x[i + 1], sh);
+    }
+    static __device__ __forceinline__ void load(wts & w, const uint8_t * row, int idx) {
+        const uint8_t * bp = row + (idx >> 1) * 210;
+        const int h = idx & 1;
+        run<16>(w.ql, bp + 64 * h);
+        run<8>(w.qh, bp + 128 + 32 * h);
+        run<2>(w.sc, bp + 192 + 8 * h);
+        w.d = lds16(bp + 208);
+    }
+    static __device__ __forceinline__ float dot(const wts & w, int, const acts128 & a) {
+        float r = 0.0f;
+#pragma unroll
+        for (int s = 0; s < 4; s++) {
+            int sum[2] = { 0, 0 };
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                const uint32_t l = w.ql[8 * (s & 1) + i];
+                const uint32_t lo = ((s & 2) ? (l >> 4) : l) & 0x0F0F0F0Fu;
+                const uint32_t hb = s == 0 ? (w.qh[i] << 4) : (s == 1 ? (w.qh[i] << 2) : (s == 2 ? w.qh[i] : (w.qh[i] >> 2)));
+                sum[i >> 2] = __dp4a((int) (lo | (hb & 0x30303030u)), a.q[s][i], sum[i >> 2]);
+            }
+            // scales 2s, 2s+1 of this half: bytes of sc[s >> 1]
+            const uint32_t sw = w.sc[s >> 1] >> (16 * (s & 1));
+            const int sc0 = (int) (int8_t) (sw & 0xFFu), sc1 = (int) (int8_t) ((sw >> 8) & 0xFFu);
+            r += a.d[s] * (float) (sc0 * (sum[0] - 32 * a.ys16[2 * s]) + sc1 * (sum[1] - 32 * a.ys16[2 * s + 1]));
+        }
+        return f16_bits_to_f32(w.d) * r;
+    }
+    // load and reduce in one pass, 8 ql words at a time (streams s and s + 2 share them): half the live registers of
+    // load() + dot(), same arithmetic in the same order
+    static __device__ __forceinline__ float load_dot(const uint8_t * row, int idx, const acts128 & a) {
+        const uint8_t * bp = row + (idx >> 1) * 210;
+        const int h = idx & 1;
+        uint32_t qh[8], sc[2];
+        run<8>(qh, bp + 128 + 32 * h);
+        run<2>(sc, bp + 192 + 8 * h);
+        float part[4];
+#pragma unroll
+        for (int half = 0; half < 2; half++) {
+            uint32_t ql[8];
+            run<8>(ql, bp + 64 * h + 32 * half);
+#pragma unroll
+            for (int hi = 0; hi < 2; hi++) {
+                const int s = half + 2 * hi;
+                int sum[2] = { 0, 0 };
+#pragma unroll
+                for (int i = 0; i < 8; i++) {
+                    const uint32_t lo = (hi ? (ql[i] >> 4) : ql[i]) & 0x0F0F0F0Fu;
+                    const uint32_t hb = s == 0 ? (qh[i] << 4) : (s == 1 ? (qh[i] << 2) : (s == 2 ? qh[i] : (qh[i] >> 2)));
+                    sum[i >> 2] = __dp4a((int) (lo | (hb & 0x30303030u)), a.q[s][i], sum[i >> 2]);
+                }
+                const uint32_t sw = sc[s >> 1] >> (16 * (s & 1));
+                const int sc0 = (int) (int8_t) (sw & 0xFFu), sc1 = (int) (int8_t) ((sw >> 8) & 0xFFu);
+                part[s] = a.d[s] * (float) (sc0 * (sum[0] - 32 * a.ys16[2 * s]) + sc1 * (sum[1] - 32 * a.ys16[2 * s + 1]));
+            }
+        }
+        const float r = ((part[0] + part[1]) + part[2]) + part[3];      // the order dot() adds them in
+        return f16_bits_to_f32(lds16(bp + 208)) * r;
     }
 };
 

@@ -353,6 +353,9 @@ def test_mul_mat_batch_matches_single_calls(kern, oracle):
     kern.mul_mat_batch(nodes)
     for (t, m, k), w, x, y in zip(mats, ws, xs, ys):
         single = kern.mul_mat(t, w, m, k, x)
+        if t == "q6_K":      # list: persistent kernel; single call: stream kernel -- same q8_1 arithmetic, another f32 summation order
+            assert oracle.nmse(single.cpu().numpy().reshape(1, -1), y.cpu().numpy().reshape(1, -1)) <= NMSE_ORACLE
+            continue
         assert np.array_equal(u32(single.cpu().numpy().reshape(-1)), u32(y.cpu().numpy().reshape(-1))), (t, m, k)
 
 
@@ -388,17 +391,60 @@ def test_mul_mat_persistent_batch_vs_oracle(kern, oracle, shared_x):
     node: NMSE 1e-9 to the oracle's q8_1 arithmetic and bit-identical to the single-node call."""
     mats = [("q4_K", 300, 4096), ("q5_K", 128, 2048), ("q4_K", 17, 11008), ("q4_K", 1, 1024), ("q5_K", 3, 4096),
             ("q4_K", 4096, 4096), ("q5_K", 1111, 11008), ("q4_K", 40, 28672), ("q5_K", 21, 32768), ("q4_K", 2, 1280),
-            ("q4_K", 999, 4096), ("q4_K", 5000, 1024), ("q5_K", 77, 14336), ("q4_K", 148 * 2 + 1, 8192)]
+            ("q4_K", 999, 4096), ("q4_K", 5000, 1024), ("q5_K", 77, 14336), ("q4_K", 148 * 2 + 1, 8192),
+            ("q6_K", 4096, 4096), ("q6_K", 333, 11008), ("q6_K", 3, 1024), ("q6_K", 50, 14336), ("q6_K", 1000, 2304)]
     nodes, ws_np, ws, xs_np, xs, ys = _batch_nodes(kern, mats, seed0=40, shared_x=shared_x)
     c0 = kern.launch_count()
     kern.mul_mat_batch(nodes)
-    assert kern.launch_count() - c0 == 2, "independent decode nodes ride in one quantize + one persistent launch"
+    assert kern.launch_count() - c0 == 4, "independent decode nodes ride in one (quantize, persistent) launch pair per format family"
     for (t, m, k), w_np, w, x_np, x, y in zip(mats, ws_np, ws, xs_np, xs, ys):
         got = y.cpu().numpy().reshape(1, m)
         want = oracle.mul_mat(t, w_np, m, k, x_np, mode=1)
         assert oracle.nmse(want, got) <= NMSE_ORACLE, (t, m, k, oracle.nmse(want, got))
-        single = kern.mul_mat(t, w, m, k, x).cpu().numpy().reshape(-1)
+        if t in FUSED_TYPES:
+            single = kern.mul_mat(t, w, m, k, x).cpu().numpy().reshape(-1)
+        else:
+            # formats whose single-node call takes another kernel: the row values must still not depend on the
+            # list -- the same node alone in a persistent launch gives the same bits
+            import b200
+            import torch
+            y1 = torch.zeros((1, m), dtype=torch.float32, device=kern.device)
+            one = (b200.MulMatNode * 1)(b200.mul_mat_node(t, w.data_ptr(), m, k, x.data_ptr(), 1, y1.data_ptr()))
+            os.environ["GGML_B200_BATCH_SINGLE"] = "1"
+            try:
+                kern.mul_mat_batch(one)
+            finally:
+                del os.environ["GGML_B200_BATCH_SINGLE"]
+            single = y1.cpu().numpy().reshape(-1)
         assert np.array_equal(u32(single), u32(got.reshape(-1))), (t, m, k)
+
+
+def test_mul_mat_persistent_q6_K_adversarial_and_strided(kern, oracle):
+    """Q6_K through the persistent kernel: edge scales (0, subnormal, max d; scales +-127/-128), rows that are
+    not 16-byte aligned (k = 2304: 1890-byte rows), a strided weight view, zero / outlier / tie activations."""
+    import b200
+    import torch
+    t, m, k = "q6_K", 96, 2304
+    rb = k // BLOCK_ELEMS[t] * BLOCK_BYTES[t]
+    w_np = adversarial_blocks(t, m, k, seed=21)
+    buf = np.zeros(m * (rb + 6) + 64, dtype=np.uint8)
+    for r in range(m):
+        buf[r * (rb + 6): r * (rb + 6) + rb] = w_np[r]
+    x_np = np.random.default_rng(22).standard_normal(size=(1, k)).astype(np.float32)
+    x_np[0, :64] = 0.0
+    x_np[0, 100] = 1000.0
+    x_np[0, 128:160] = (np.arange(32) - 16 + 0.5) * (127.0 / 15.5) / 127.0
+    w, ws, x = dev_blocks(kern, w_np), kern.to_device(buf), kern.to_device(x_np)
+    y = torch.zeros((2, m), dtype=torch.float32, device=kern.device)
+    nodes = (b200.MulMatNode * 2)(b200.mul_mat_node(t, w.data_ptr(), m, k, x.data_ptr(), 1, y[0].data_ptr()),
+                                  b200.mul_mat_node(t, ws.data_ptr(), m, k, x.data_ptr(), 1, y[1].data_ptr(), a_row_stride=rb + 6))
+    kern.mul_mat_batch(nodes)
+    got = y.cpu().numpy()
+    want = oracle.mul_mat(t, w_np, m, k, x_np, mode=1)
+    fin = np.isfinite(want[0])
+    assert np.array_equal(np.isfinite(got[0]), fin)
+    assert oracle.nmse(want[0][fin], got[0][fin]) <= NMSE_ORACLE
+    assert np.array_equal(u32(got[0][fin]), u32(got[1][fin]))
 
 
 def test_mul_mat_persistent_batch_many_nodes_and_strided_rows(kern, oracle):
