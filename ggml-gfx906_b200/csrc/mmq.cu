@@ -71,10 +71,11 @@ int pick_bn(int64_t m, int64_t n, int sm_count) {
     if (n <= 32) return 32;
     if (n <= 64) return 64;
     if (n <= 128) return 128;
-    // larger n: whichever of 128 / 256 needs less tensor time including the wave tail
+    // larger n: fewer waves wins.  A tile's time is the weight expansion (independent of BN, measured ~ the MMA
+    // time of 600 columns) + its MMAs (~ BN): cost = waves x (600 + BN)   (profiles/r01g_prefill_probe.txt)
     const int64_t tm = ceil_div(m, MMQ_BM);
-    const int64_t w128 = ceil_div(tm * ceil_div(n, 128), sm_count) * 128;
-    const int64_t w256 = ceil_div(tm * ceil_div(n, 256), sm_count) * 256;
+    const int64_t w128 = ceil_div(tm * ceil_div(n, 128), sm_count) * (600 + 128);
+    const int64_t w256 = ceil_div(tm * ceil_div(n, 256), sm_count) * (600 + 256);
     return w256 <= w128 ? 256 : 128;
 }
 

@@ -289,9 +289,18 @@ constexpr int MMQ_BM = 128;
 constexpr int MMQ_BK = 64;           // K elements per MMA stage (one 128-byte swizzle row)
 constexpr int MMQ_RS = 2;            // raw slab ring depth
 constexpr int MMQ_THREADS = 192;
+#ifndef MMQ_STAGES_SMALL
+#define MMQ_STAGES_SMALL 4
+#endif
+#ifndef MMQ_CTAS_SMALL
+#define MMQ_CTAS_SMALL 1
+#endif
 
 template <int BN> struct mmq_cfg {
-    static constexpr int stages   = BN <= 128 ? 4 : 3;
+    // (tried: 2 stages + 2 CTAs per SM for BN <= 128 to double the weight-expansion producers per tensor pipe:
+    //  no gain at n = 512, profiles/r01g_prefill_probe.txt; -DMMQ_STAGES_SMALL=2 -DMMQ_CTAS_SMALL=2 rebuilds it)
+    static constexpr int stages   = BN <= 128 ? MMQ_STAGES_SMALL : 3;
+    static constexpr int ctas_per_sm = BN <= 128 ? MMQ_CTAS_SMALL : 1;
     static constexpr int a_bytes  = MMQ_BM * 128;
     static constexpr int b_bytes  = BN * 128;
     static constexpr int tmem_cols = BN < 32 ? 32 : BN;
@@ -306,7 +315,7 @@ template <int BN> struct mmq_smem {
 };
 
 template <int T, int BN, bool ALIGNED>
-__global__ void __launch_bounds__(MMQ_THREADS, 1)
+__global__ void __launch_bounds__(MMQ_THREADS, mmq_cfg<BN>::ctas_per_sm)
 k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b) {
     using CFG = mmq_cfg<BN>;
     using SM  = mmq_smem<BN>;
