@@ -238,18 +238,18 @@ extern "C" int b200_mul_mat_batch(const b200_mul_mat_node * nodes, int64_t count
     const bool persistent = !env_int("GGML_B200_NO_BATCH_KERNEL", 0);
     // one builder (28 KB parameter block, reused) per format family = kernel instantiation; the nodes of a
     // pending set are independent, so sorting them into per-family launches keeps the semantics
-    static thread_local batch_builder * fam_bb[2] = { nullptr, nullptr };
+    static thread_local batch_builder * fam_bb[3] = { nullptr, nullptr, nullptr };
     static thread_local range_set reads, writes;
-    if (!fam_bb[0]) { fam_bb[0] = new batch_builder(0); fam_bb[1] = new batch_builder(1); }
+    if (!fam_bb[0]) { for (int f = 0; f < 3; f++) fam_bb[f] = new batch_builder(f); }
     ws_cursor cur;
     cur.reset((uint8_t *) workspace_dev, workspace_bytes);
-    fam_bb[0]->reset(); fam_bb[1]->reset();
+    for (int f = 0; f < 3; f++) fam_bb[f]->reset();
     reads.clear(); writes.clear();
     const int grid = current_caps().sm_count;
     auto flush = [&]() -> int {
         reads.clear(); writes.clear();
         int rc = B200_OK;
-        for (int f = 0; f < 2 && rc == B200_OK; f++) {
+        for (int f = 0; f < 3 && rc == B200_OK; f++) {
             batch_builder * bb = fam_bb[f];
             if (bb->empty()) continue;
             if (bb->args.count == 1 && !env_int("GGML_B200_BATCH_SINGLE", 0)) {
@@ -276,14 +276,14 @@ extern "C" int b200_mul_mat_batch(const b200_mul_mat_node * nodes, int64_t count
         if (plain) {
             const uintptr_t x0 = (uintptr_t) nd.b_dev, x1 = x0 + (size_t) k * 4;
             const uintptr_t d0 = (uintptr_t) nd.dst_dev, d1 = d0 + (size_t) m * 4;
-            batch_builder * bb = fam_bb[nd.type_a == T_Q6_K ? 1 : 0];
+            batch_builder * bb = fam_bb[batch_family(nd.type_a)];
             if (bb->full() || writes.hits(x0, x1) || writes.hits(d0, d1) || reads.hits(d0, d1)) {
                 const int rc = flush();
                 if (rc) return rc;
             }
             const bool cw = (nd.flags & B200_MUL_MAT_CONST_WEIGHTS) != 0;
             bool ok = bb->add(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, nd.b_dev, nd.dst_dev, cw, grid, cur);
-            if (!ok && !(fam_bb[0]->empty() && fam_bb[1]->empty())) {      // workspace full: launch what is pending, start over
+            if (!ok && !(fam_bb[0]->empty() && fam_bb[1]->empty() && fam_bb[2]->empty())) {      // workspace full: launch what is pending, start over
                 const int rc = flush();
                 if (rc) return rc;
                 ok = bb->add(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, nd.b_dev, nd.dst_dev, cw, grid, cur);

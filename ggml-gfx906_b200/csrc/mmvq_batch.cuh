@@ -295,7 +295,8 @@ __device__ __forceinline__ void batch_consume(const cnode & nd, const int cw, co
 
 // ---------------------------------------------------------------- the persistent kernel
 // 14 warps = 4 + 4 + 3 + 3 per SM sub-partition: 4 warps share 16 K registers -> 128 per thread is the ceiling.
-// One instantiation per format family: FAM 0 = Q4_K / Q5_K (16-byte aligned 128-weight items), FAM 1 = Q6_K.
+// One instantiation per format family: FAM 0 = Q4_K / Q5_K (16-byte aligned 128-weight items), FAM 1 = Q6_K,
+// FAM 2 = Q4_0 / Q8_0 (four 32-weight blocks per item).
 // Mixed in one kernel, Q6_K's 27-word realigned items push the loop state of ALL formats into local memory
 // (measured: Q4_K falls from 5.8 to 2.8 TB/s); the nodes of a list are independent, so b200_mul_mat_batch
 // simply sorts them into one launch per family.
@@ -414,7 +415,11 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
             if (layout_w != 0 && layout_w != nd.W) { named_bar_sync(13, BATCH_NWC * 32); git = 0; }
             layout_w = nd.W;
         }
-        if (FAM == 1)               batch_consume<T_Q6_K>(nd, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
+        if (FAM == 2) {
+            if (nd.type == T_Q8_0) batch_consume<T_Q8_0>(nd, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
+            else                   batch_consume<T_Q4_0>(nd, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
+        }
+        else if (FAM == 1)          batch_consume<T_Q6_K>(nd, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
         else if (nd.type == T_Q5_K) batch_consume<T_Q5_K>(nd, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
         else                   batch_consume<T_Q4_K>(nd, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
         if (++u == NB) { u = 0; uph ^= 1; }
@@ -428,13 +433,13 @@ namespace b200 {
 // ================================================================= host side
 // Can this MUL_MAT ride in a persistent launch?  (n = 1, plain 2-D, a format with a 128-weight item.)
 static bool batch_node_ok(int type, const uint8_t * w, int64_t row_stride, int64_t m, int64_t k, const float * x) {
-    if (type != T_Q4_K && type != T_Q5_K && type != T_Q6_K) return false;
+    if (!type_is_quant(type)) return false;
     if (m < 1 || m > 0x7FFFFFFF || k < 1024 || k % 256 != 0) return false;
     if (ceil_div(k / 128, 32) > 8) return false;                 // k <= 32768: one item per lane, same (W, lane) map as the per-node kernel
     if (reinterpret_cast<uintptr_t>(x) % 16 != 0) return false;
-    if (type == T_Q6_K ? !hitem<T_Q6_K>::ok(k, row_stride, reinterpret_cast<uintptr_t>(w))
-                       : !hitem<T_Q4_K>::ok(k, row_stride, reinterpret_cast<uintptr_t>(w))) return false;
-    const int64_t row_bytes = k / 256 * type_bytes(type);
+    if ((type == T_Q4_K || type == T_Q5_K) ? !hitem<T_Q4_K>::ok(k, row_stride, reinterpret_cast<uintptr_t>(w))
+                                           : !hitem<T_Q6_K>::ok(k, row_stride, reinterpret_cast<uintptr_t>(w))) return false;
+    const int64_t row_bytes = k / type_qk(type) * type_bytes(type);
     if (row_stride < row_bytes) return false;
     return true;
 }
@@ -451,6 +456,8 @@ struct ws_cursor {
         left = (w && bytes > skew) ? bytes - skew : 0;
     }
 };
+
+static inline int batch_family(int type) { return type == T_Q6_K ? 1 : ((type == T_Q4_0 || type == T_Q8_0) ? 2 : 0); }
 
 struct batch_builder {
     batch_args args;
@@ -476,7 +483,7 @@ struct batch_builder {
         }
         args.count++;
         nd.w = w; nd.x = x; nd.dst = dst; nd.row_stride = row_stride; nd.m = (int) m; nd.k = (int) k;
-        nd.row_bytes = (int) (k / 256 * type_bytes(type));
+        nd.row_bytes = (int) (k / type_qk(type) * type_bytes(type));
         nd.type = (unsigned char) type;
         nd.W = (unsigned char) ceil_div(k / 128, 32);
         nd.G = (unsigned char) (BATCH_NWC / nd.W);
@@ -523,9 +530,9 @@ static int batch_launch(batch_builder & bb, cudaStream_t st) {
     a.S = S;
     const size_t smem = (size_t) a.off_slots + (size_t) S * a.slot_stride;
 
-    static size_t smem_set[2][64];
+    static size_t smem_set[3][64];
     int dev = 0; cudaGetDevice(&dev); if (dev < 0 || dev >= 64) dev = 0;
-    auto kern = bb.fam == 1 ? k_mmvq_batch<1> : k_mmvq_batch<0>;
+    auto kern = bb.fam == 2 ? k_mmvq_batch<2> : (bb.fam == 1 ? k_mmvq_batch<1> : k_mmvq_batch<0>);
     if (smem > smem_set[bb.fam][dev]) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
         if (e != cudaSuccess) return -(int) e;

@@ -232,6 +232,90 @@ template <> struct hitem<T_Q6_K> {
     }
 };
 
+// ---- Q4_0 / Q8_0: item = four 32-weight blocks (72 / 136 bytes).  Blocks are 18 / 34 bytes: block b of an item
+// starts at word 4.5 b / 8.5 b, so even blocks have their f16 d in the low half of a word and their quants across
+// word boundaries, odd blocks the other way round; the item itself is only 2-byte aligned (run<> realigns).
+// load() only notes the address; dot() streams block by block so that at most 10 words are live.
+template <> struct hitem<T_Q4_0> {
+    static constexpr bool aligned16 = false;
+    static constexpr bool need_ys16 = false;
+    static constexpr bool hi_div16 = false;
+    static bool ok(int64_t k, int64_t row_stride, uintptr_t base) { return k % 128 == 0 && row_stride % 2 == 0 && base % 2 == 0; }
+    struct wts { const uint8_t * p; };
+    static __device__ __forceinline__ void load(wts & w, const uint8_t * row, int idx) { w.p = row + idx * 72; }
+    static __device__ __forceinline__ float dot(const wts & w, int, const acts128 & a) {
+        // the item's 18 words: 8-byte loads when the item is 8-byte aligned (items are 72 bytes apart: true for every
+        // lane as soon as the row start is), else aligned words + funnel shift
+        uint32_t x[18];
+        if ((reinterpret_cast<uintptr_t>(w.p) & 7) == 0) {
+#pragma unroll
+            for (int i = 0; i < 9; i++) {
+                const uint2 v = *reinterpret_cast<const uint2 *>(w.p + 8 * i);
+                x[2 * i] = v.x; x[2 * i + 1] = v.y;
+            }
+        } else {
+            hitem<T_Q6_K>::run<18>(x, w.p);
+        }
+        float r = 0.0f;
+#pragma unroll
+        for (int b = 0; b < 4; b++) {
+            constexpr int B0[4] = { 0, 4, 9, 13 };
+            uint32_t d, q[4];
+            if ((b & 1) == 0) {
+                d = x[B0[b]] & 0xFFFFu;
+#pragma unroll
+                for (int i = 0; i < 4; i++) q[i] = __funnelshift_r(x[B0[b] + i], x[B0[b] + i + 1], 16);
+            } else {
+                d = x[B0[b]] >> 16;
+#pragma unroll
+                for (int i = 0; i < 4; i++) q[i] = x[B0[b] + 1 + i];
+            }
+            int lo = 0, hi16 = 0;                       // hi16 = 16 x the high-nibble dot (nibbles used in place)
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                lo   = __dp4a((int) (q[i] & 0x0F0F0F0Fu), a.q[b][i], lo);
+                hi16 = dp4a_us(q[i] & 0xF0F0F0F0u, a.q[b][4 + i], hi16);
+            }
+            const int sum = lo + (hi16 >> 4);           // exact: hi16 is a multiple of 16
+            r += f16_bits_to_f32(d) * (a.d[b] * (float) sum - 8.0f * a.sd[b]);
+        }
+        return r;
+    }
+};
+
+template <> struct hitem<T_Q8_0> {
+    static constexpr bool aligned16 = false;
+    static constexpr bool need_ys16 = false;
+    static constexpr bool hi_div16 = false;
+    static bool ok(int64_t k, int64_t row_stride, uintptr_t base) { return k % 128 == 0 && row_stride % 2 == 0 && base % 2 == 0; }
+    struct wts { const uint8_t * p; };
+    static __device__ __forceinline__ void load(wts & w, const uint8_t * row, int idx) { w.p = row + idx * 136; }
+    static __device__ __forceinline__ float dot(const wts & w, int, const acts128 & a) {
+        float r = 0.0f;
+#pragma unroll
+        for (int b = 0; b < 4; b++) {
+            constexpr int B0[4] = { 0, 8, 17, 25 };
+            uint32_t x[9];
+            hitem<T_Q6_K>::run<9>(x, w.p + 4 * B0[b]);
+            uint32_t d, q[8];
+            if ((b & 1) == 0) {
+                d = x[0] & 0xFFFFu;
+#pragma unroll
+                for (int i = 0; i < 8; i++) q[i] = __funnelshift_r(x[i], x[i + 1], 16);
+            } else {
+                d = x[0] >> 16;
+#pragma unroll
+                for (int i = 0; i < 8; i++) q[i] = x[1 + i];
+            }
+            int sum = 0;
+#pragma unroll
+            for (int i = 0; i < 8; i++) sum = __dp4a((int) q[i], a.q[b][i], sum);
+            r += f16_bits_to_f32(d) * (a.d[b] * (float) sum);
+        }
+        return r;
+    }
+};
+
 // ================================================================= the kernel
 struct fused_args {
     const uint8_t * w;        // weight rows

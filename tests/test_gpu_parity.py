@@ -353,7 +353,7 @@ def test_mul_mat_batch_matches_single_calls(kern, oracle):
     kern.mul_mat_batch(nodes)
     for (t, m, k), w, x, y in zip(mats, ws, xs, ys):
         single = kern.mul_mat(t, w, m, k, x)
-        if t == "q6_K":      # list: persistent kernel; single call: stream kernel -- same q8_1 arithmetic, another f32 summation order
+        if t not in FUSED_TYPES:      # list: persistent kernel; single call: stream kernel -- same q8_1 arithmetic, another f32 summation order
             assert oracle.nmse(single.cpu().numpy().reshape(1, -1), y.cpu().numpy().reshape(1, -1)) <= NMSE_ORACLE
             continue
         assert np.array_equal(u32(single.cpu().numpy().reshape(-1)), u32(y.cpu().numpy().reshape(-1))), (t, m, k)
@@ -392,11 +392,13 @@ def test_mul_mat_persistent_batch_vs_oracle(kern, oracle, shared_x):
     mats = [("q4_K", 300, 4096), ("q5_K", 128, 2048), ("q4_K", 17, 11008), ("q4_K", 1, 1024), ("q5_K", 3, 4096),
             ("q4_K", 4096, 4096), ("q5_K", 1111, 11008), ("q4_K", 40, 28672), ("q5_K", 21, 32768), ("q4_K", 2, 1280),
             ("q4_K", 999, 4096), ("q4_K", 5000, 1024), ("q5_K", 77, 14336), ("q4_K", 148 * 2 + 1, 8192),
-            ("q6_K", 4096, 4096), ("q6_K", 333, 11008), ("q6_K", 3, 1024), ("q6_K", 50, 14336), ("q6_K", 1000, 2304)]
+            ("q6_K", 4096, 4096), ("q6_K", 333, 11008), ("q6_K", 3, 1024), ("q6_K", 50, 14336), ("q6_K", 1000, 2304),
+            ("q4_0", 4096, 4096), ("q8_0", 300, 4096), ("q4_0", 77, 11008), ("q8_0", 50, 1024), ("q8_0", 1001, 2304),
+            ("q4_0", 5, 32768), ("q8_0", 33, 14336)]
     nodes, ws_np, ws, xs_np, xs, ys = _batch_nodes(kern, mats, seed0=40, shared_x=shared_x)
     c0 = kern.launch_count()
     kern.mul_mat_batch(nodes)
-    assert kern.launch_count() - c0 == 4, "independent decode nodes ride in one (quantize, persistent) launch pair per format family"
+    assert kern.launch_count() - c0 == 6, "independent decode nodes ride in one (quantize, persistent) launch pair per format family"
     for (t, m, k), w_np, w, x_np, x, y in zip(mats, ws_np, ws, xs_np, xs, ys):
         got = y.cpu().numpy().reshape(1, m)
         want = oracle.mul_mat(t, w_np, m, k, x_np, mode=1)
@@ -419,12 +421,14 @@ def test_mul_mat_persistent_batch_vs_oracle(kern, oracle, shared_x):
         assert np.array_equal(u32(single), u32(got.reshape(-1))), (t, m, k)
 
 
-def test_mul_mat_persistent_q6_K_adversarial_and_strided(kern, oracle):
-    """Q6_K through the persistent kernel: edge scales (0, subnormal, max d; scales +-127/-128), rows that are
-    not 16-byte aligned (k = 2304: 1890-byte rows), a strided weight view, zero / outlier / tie activations."""
+@pytest.mark.parametrize("t", ["q6_K", "q4_0", "q8_0"])
+def test_mul_mat_persistent_unaligned_formats_adversarial_and_strided(kern, oracle, t):
+    """the 2-byte-aligned formats through the persistent kernel: edge scales (0, subnormal, max d; Q6_K scales
+    +-127/-128), rows that are not 16-byte aligned (Q6_K k = 2304: 1890-byte rows; a strided view whose rows start
+    at every 2-byte phase), zero / outlier / tie activations."""
     import b200
     import torch
-    t, m, k = "q6_K", 96, 2304
+    m, k = 96, 2304
     rb = k // BLOCK_ELEMS[t] * BLOCK_BYTES[t]
     w_np = adversarial_blocks(t, m, k, seed=21)
     buf = np.zeros(m * (rb + 6) + 64, dtype=np.uint8)
