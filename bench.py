@@ -183,10 +183,58 @@ class DecodeStack:
             import torch.distributed as dist
             dist.all_gather_into_tensor(self.y_dev.view(-1), self.y_dev[self.rank])
 
+    def _e2e_setup(self, chunks):
+        """Split the node list into `chunks` consecutive sub-lists with their activation / output ranges, so
+        that the host->device copy of sub-list c+1 and the device->host copy of sub-list c-1 overlap the
+        persistent launch of sub-list c (three streams, events in between)."""
+        import ctypes
+        import b200
+        torch = self.torch
+        n = len(self.mats)
+        edges = [round(i * n / chunks) for i in range(chunks + 1)]
+        # balance by weight bytes rather than by node count
+        total = sum(int(w.numel()) for w in self.weights)
+        edges, acc, nxt = [0], 0, 1
+        for i, w in enumerate(self.weights):
+            acc += int(w.numel())
+            if nxt < chunks and acc >= total * nxt / chunks:
+                edges.append(i + 1); nxt += 1
+        edges.append(n)
+        edges = sorted(set(edges))
+        self.e2e_chunks = []
+        xo_end = self.x_off + [self.x_host.numel()]
+        yo_end = self.y_off + [self.local_out]
+        for a, b in zip(edges[:-1], edges[1:]):
+            sub = (b200.MulMatNode * (b - a))(*[self.nodes[i] for i in range(a, b)])
+            self.e2e_chunks.append((sub, b - a, xo_end[a], xo_end[b], yo_end[a], yo_end[b]))
+        self.s_h2d, self.s_d2h = torch.cuda.Stream(), torch.cuda.Stream()
+
     def step_e2e(self):
-        self.x_dev.copy_(self.x_host, non_blocking=True)
-        self.compute()
-        self.y_host.copy_(self.y_dev.view(-1), non_blocking=True)
+        """pinned host activations -> device, every MUL_MAT, outputs -> pinned host.  Single GPU: pipelined over
+        sub-lists; with the rows split over ranks the gather needs the whole arena, so the step is serial."""
+        torch = self.torch
+        if self.world > 1:
+            self.x_dev.copy_(self.x_host, non_blocking=True)
+            self.compute()
+            self.y_host.copy_(self.y_dev.view(-1), non_blocking=True)
+            return
+        if not hasattr(self, "e2e_chunks"):
+            self._e2e_setup(env_int("BENCH_E2E_CHUNKS", 4))
+        cur = torch.cuda.current_stream()
+        self.s_h2d.wait_stream(cur)                       # the previous step is done with x_dev
+        self.s_d2h.wait_stream(cur)
+        y_flat = self.y_dev.view(-1)
+        for sub, cnt, x0, x1, y0, y1 in self.e2e_chunks:
+            with torch.cuda.stream(self.s_h2d):
+                self.x_dev[x0:x1].copy_(self.x_host[x0:x1], non_blocking=True)
+                ev_in = torch.cuda.Event(); ev_in.record(self.s_h2d)
+            cur.wait_event(ev_in)
+            self.kern.mul_mat_batch(sub, count=cnt, ws=self.ws)
+            ev_out = torch.cuda.Event(); ev_out.record(cur)
+            with torch.cuda.stream(self.s_d2h):
+                self.s_d2h.wait_event(ev_out)
+                self.y_host[y0:y1].copy_(y_flat[y0:y1], non_blocking=True)
+        cur.wait_stream(self.s_d2h)                       # the step ends when its last output is on the host
 
 
 # ------------------------------------------------------------------------------------- timing
@@ -455,7 +503,8 @@ def main():
                    "parallelism": "single GPU" if world == 1 else f"row-split x{world}: one persistent launch per rank + one NCCL all-gather of the rank-major output arena per step"},
         "e2e": {"value": round(e2e, 1), "unit": UNIT, "h2d_bytes_per_step": stack.x_bytes,
                 "d2h_bytes_per_step": stack.y_bytes, "ms_per_step": round(sec_e2e / args.steps * 1e3, 4),
-                "path": "pinned host activations -> b200_mul_mat_batch (C ABI) -> pinned host outputs, sync per step"},
+                "path": "pinned host activations -> b200_mul_mat_batch (C ABI) -> pinned host outputs, sync per step"
+                        + ("; pipelined over 4 sub-lists (copies overlap the persistent launches)" if world == 1 else "")},
         "gpu_launches": launches_per_step * args.steps,
         "decode_tok_s": round(args.steps / sec, 1),
         "weight_GBps": round(weight_total * args.steps / sec / 1e9, 1),
