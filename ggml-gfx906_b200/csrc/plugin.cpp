@@ -78,6 +78,10 @@ struct b200_backend_ctx;
 static ggml_backend_buffer_type_t b200_buffer_type(int device);
 static bool buft_is_b200(ggml_backend_buffer_type_t buft);
 static bool buft_is_b200_split(ggml_backend_buffer_type_t buft);
+// row-split weights (plugin_split.inc)
+static bool split_mul_mat_supported(const struct ggml_tensor * op);
+static void split_mul_mat(b200_backend_ctx * ctx, struct ggml_tensor * node);
+static bool tensor_is_split(const struct ggml_tensor * t) { return t && t->buffer && buft_is_b200_split(t->buffer->buft); }
 
 // ================================================================= device buffer
 // mirrors the role of ggml_backend_cuda_buffer_* (src/ggml-cuda/ggml-cuda.cu:571-669)
@@ -257,6 +261,7 @@ static void b200_compute_node(b200_backend_ctx * ctx, struct ggml_tensor * node)
     const struct ggml_tensor * s1 = node->src[1];
     switch (node->op) {
         case GGML_OP_MUL_MAT:
+            if (tensor_is_split(s0)) { split_mul_mat(ctx, node); break; }
             B200_OK_OR_ABORT(b200_mul_mat((int) s0->type, s0->data, s0->ne, s0->nb, (const float *) s1->data, s1->ne, s1->nb,
                                           (float *) node->data, ctx->ws, ctx->ws_size, ctx->stream));
             break;
@@ -309,7 +314,7 @@ static void walk_graph(struct ggml_cgraph * cgraph, std::vector<b200_mul_mat_nod
     for (int i = 0; i < n; i++) {
         struct ggml_tensor * node = ggml_graph_node(cgraph, i);
         if (op_is_noop(node)) continue;
-        if (node->op == GGML_OP_MUL_MAT) { run.push_back(to_list_entry(node)); continue; }
+        if (node->op == GGML_OP_MUL_MAT && !tensor_is_split(node->src[0])) { run.push_back(to_list_entry(node)); continue; }
         if (!run.empty()) { fn_run(run); run.clear(); }
         fn_other(node);
     }
@@ -343,6 +348,7 @@ static enum ggml_status b200_backend_graph_compute(ggml_backend_t backend, struc
     // size the workspace before anything is launched (no allocation inside a capture)
     size_t need = 0;
     int n_work = 0;
+    bool has_split = false;          // multi-device nodes are not captured into a CUDA graph
     std::vector<b200_mul_mat_node> & run = ctx->run;
     walk_graph(cgraph, run,
                [&](std::vector<b200_mul_mat_node> & r) {
@@ -350,7 +356,7 @@ static enum ggml_status b200_backend_graph_compute(ggml_backend_t backend, struc
                    const size_t w = b200_mul_mat_batch_workspace_size(r.data(), (int64_t) r.size());
                    if (w > need) need = w;
                },
-               [&](struct ggml_tensor *) { n_work++; });
+               [&](struct ggml_tensor * node) { n_work++; has_split = has_split || tensor_is_split(node->src[0]); });
     if (need > ctx->ws_size) {
         CUDA_OK(cudaStreamSynchronize(ctx->stream));
         if (ctx->ws) CUDA_OK(cudaFree(ctx->ws));
@@ -364,7 +370,7 @@ static enum ggml_status b200_backend_graph_compute(ggml_backend_t backend, struc
     // on its second appearance and replayed from the third on.  Single-node graphs (test-backend-ops)
     // never pay for a capture.
     bool use_graph = false, capture = false;
-    if (ctx->graphs_enabled && n_work >= 4) {
+    if (ctx->graphs_enabled && n_work >= 4 && !has_split) {
         std::vector<graph_key_entry> key;
         make_key(cgraph, key);
         if (key == ctx->last_key) {
@@ -512,6 +518,10 @@ static bool b200_dev_supports_op(ggml_backend_dev_t dev, const struct ggml_tenso
     }
     const struct ggml_tensor * s0 = op->src[0];
     const struct ggml_tensor * s1 = op->src[1];
+    // row-split weights: only as src0 of a plain 2-D MUL_MAT (reference src/ggml-cuda/ggml-cuda.cu:3215-3222, 3276-3278)
+    for (int i = 0; i < GGML_MAX_SRC; i++) {
+        if (tensor_is_split(op->src[i])) return i == 0 && split_mul_mat_supported(op);
+    }
     switch (op->op) {
         case GGML_OP_NONE:
         case GGML_OP_RESHAPE:
@@ -540,6 +550,7 @@ static bool b200_dev_supports_op(ggml_backend_dev_t dev, const struct ggml_tenso
 }
 
 static bool b200_dev_supports_buft(ggml_backend_dev_t dev, ggml_backend_buffer_type_t buft) {
+    if (buft_is_b200_split(buft)) return true;       // any device of the box can be the main device of a split MUL_MAT
     if (!buft_is_b200(buft)) return false;
     return ((b200_buft_ctx *) buft->context)->device == ((b200_device_ctx *) dev->context)->device;
 }

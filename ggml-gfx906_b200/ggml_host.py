@@ -241,6 +241,52 @@ class GgmlHost:
             b.ggml_free(ctx)
 
 
+def split_buffer_type(host: "GgmlHost", backend, main_device: int, tensor_split: Sequence[float]):
+    """The backend registry's "ggml_backend_split_buffer_type" proc (include/ggml-backend.h:188), as llama.cpp
+    obtains it for --split-mode row."""
+    b = host.base
+    reg = b.ggml_backend_dev_backend_reg(b.ggml_backend_get_device(backend))
+    fn = b.ggml_backend_reg_get_proc_address(reg, b"ggml_backend_split_buffer_type")
+    if not fn:
+        return None
+    ts = (C.c_float * 16)(*([float(v) for v in tensor_split] + [0.0] * (16 - len(tensor_split))))
+    return C.CFUNCTYPE(C.c_void_p, C.c_int, C.POINTER(C.c_float))(fn)(int(main_device), ts)
+
+
+def mul_mat_split(host: "GgmlHost", backend, buft, tname: str, w_blocks: np.ndarray, m: int, k: int, x: np.ndarray) -> np.ndarray:
+    """ggml_mul_mat with the weight tensor allocated in the row-split buffer type `buft` and the activations /
+    output on `backend` (the main device): returns [n, m] f32, and the weight bytes read back through get_tensor."""
+    x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1, k)
+    n = x.shape[0]
+    b = host.base
+    ctx_w, ctx = host.new_context(), host.new_context()
+    buf_w = buf = None
+    try:
+        a = b.ggml_new_tensor_2d(ctx_w, GGML_TYPE[tname], k, m)
+        buf_w = b.ggml_backend_alloc_ctx_tensors_from_buft(ctx_w, buft)
+        if not buf_w:
+            raise MemoryError("ggml_backend_alloc_ctx_tensors_from_buft(split)")
+        bb = b.ggml_new_tensor_2d(ctx, GGML_TYPE["f32"], k, n)
+        c = b.ggml_mul_mat(ctx, a, bb)
+        gf = b.ggml_new_graph(ctx)
+        b.ggml_build_forward_expand(gf, c)
+        buf = b.ggml_backend_alloc_ctx_tensors(ctx, backend)
+        if not buf:
+            raise MemoryError("ggml_backend_alloc_ctx_tensors")
+        host.tensor_set(a, np.ascontiguousarray(w_blocks, dtype=np.uint8))
+        host.tensor_set(bb, x)
+        st = b.ggml_backend_graph_compute(backend, gf)
+        if st != GGML_STATUS_SUCCESS:
+            raise RuntimeError(f"graph_compute status {st}")
+        return host.tensor_get(c).reshape(n, m), host.tensor_get(a, dtype=np.uint8)
+    finally:
+        if buf:
+            b.ggml_backend_buffer_free(buf)
+        if buf_w:
+            b.ggml_backend_buffer_free(buf_w)
+        b.ggml_free(ctx); b.ggml_free(ctx_w)
+
+
 class MulMatGraph:
     """A ggml graph of independent MUL_MAT nodes (one per (type, m, k) entry, f32 activations [k, n])
     allocated once on `backend`: weights / activations are set with ggml_backend_tensor_set, compute()

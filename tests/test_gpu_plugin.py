@@ -128,3 +128,28 @@ def test_decode_graph_through_plugin_vs_ggml_cpu(host_and_backends):
                 assert nmse(gc.get_output(i), gg.get_output(i)) <= 5e-4, (rep, mt.name)
     finally:
         gc.close(); gg.close()
+
+
+@pytest.mark.parametrize("t,m,k,n,ts", [("q4_K", 1024, 4096, 1, [1, 1]), ("q4_K", 1000, 4096, 1, [3, 1]), ("q6_K", 512, 2048, 4, [1, 1]),
+                                        ("q8_0", 640, 1024, 64, [1, 1]), ("q4_0", 300, 512, 1, [1, 1])])
+def test_row_split_buffer_type_two_devices(host_and_backends, t, m, k, n, ts):
+    """weights in ggml_backend_split_buffer_type (rows on B200_0 and B200_1), MUL_MAT on B200_0: the result is
+    bit-identical to the single-device result (each row is computed by one device with the same kernel), within
+    the harness gate of ggml-cpu, and get_tensor reassembles the canonical weight bytes.  Needs 2 GPUs."""
+    import ggml_host
+    host, cpu, gpu = host_and_backends
+    reg = host.base.ggml_backend_dev_backend_reg(host.base.ggml_backend_get_device(gpu))
+    if host.base.ggml_backend_reg_dev_count(reg) < 2:
+        pytest.skip("one device visible")
+    buft = ggml_host.split_buffer_type(host, gpu, 0, ts)
+    assert buft, "ggml_backend_split_buffer_type proc missing"
+    w = random_blocks(t, m, k, seed=91)
+    x = np.random.default_rng(92).uniform(-1, 1, size=(n, k)).astype(np.float32)
+    got, w_back = ggml_host.mul_mat_split(host, gpu, buft, t, w, m, k, x)
+    assert np.array_equal(w_back, np.ascontiguousarray(w, dtype=np.uint8).reshape(-1))
+    single = host.mul_mat(gpu, t, w, m, k, x)
+    assert nmse(host.mul_mat(cpu, t, w, m, k, x), got) <= 5e-4
+    if n <= 8:
+        assert np.array_equal(got.view(np.uint32), single.view(np.uint32))
+    else:
+        assert nmse(single, got) <= 1e-6
