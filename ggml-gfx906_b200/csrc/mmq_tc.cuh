@@ -16,10 +16,11 @@
 // the whole K extent in f32 in TMEM.  Accuracy is better than the q8_1 route (activations keep 11
 // mantissa bits instead of <= 7 bits per 32-block; weights keep 11) and there is no per-block drain.
 //
-// CTA = one 128 x BN output tile, 6 warps:
-//   warps 0-3  weight producers, then the epilogue (TMEM lane quarter = warp id)
-//   warp  4    activation loader (TMA 2-D tiles, zero-filled past n and k)
-//   warp  5    TMEM allocation + the single MMA-issuing thread
+// CTA = one 128 x BN output tile, 10 warps:
+//   warps 0-7  weight producers (two threads per row: each expands 32 of every 64 elements), then the
+//              epilogue (TMEM lane quarter = warp id % 4, the pair splits the columns)
+//   warp  8    activation loader (TMA 2-D tiles, zero-filled past n and k)
+//   warp  9    TMEM allocation + the single MMA-issuing thread
 // Raw quant bytes are prefetched two 256-deep slabs ahead by 128 per-row bulk async copies
 // (cp.async.bulk, one per producer thread), re-aligned in shared memory when rows are not 16-byte
 // aligned (Q6_K, odd block counts), then expanded 64 K-elements at a time into a ring of A stages.
@@ -138,12 +139,14 @@ template <bool HAS_QH> struct expander_k45 {
         slab_words<0, 4>(s, hdr);
         if (HAS_QH) slab_words<4, 8>(s, qh);
     }
-    template <int SUB> __device__ __forceinline__ void expand64(const uint8_t * s, uint8_t * a_row, int row7) {
+    // half: which 32 of the 64 elements this thread expands (two producer threads per row)
+    template <int SUB> __device__ __forceinline__ void expand64(const uint8_t * s, uint8_t * a_row, int row7, int half) {
         const float d = f16_bits_to_f32(hdr[0]), dmin = f16_bits_to_f32(hdr[0] >> 16);
         uint32_t q[8];
         slab_words<(HAS_QH ? 12 : 4) + 8 * SUB, 8>(s, q);
 #pragma unroll
         for (int hi = 0; hi < 2; hi++) {
+            if (hi != half) continue;
             int sc, mn;
             k4_scale_min(hdr[1], hdr[2], hdr[3], 2 * SUB + hi, sc, mn);
             const __half2 d1 = __float2half2_rn(d * (float) sc);
@@ -179,14 +182,14 @@ template <> struct expander<T_Q6_K> {
         sc[0] = t[0]; sc[1] = t[1]; sc[2] = t[2]; sc[3] = t[3];
         d = f16_bits_to_f32(t[4]);
     }
-    template <int SUB> __device__ __forceinline__ void expand64(const uint8_t * s, uint8_t * a_row, int row7) {
+    template <int SUB> __device__ __forceinline__ void expand64(const uint8_t * s, uint8_t * a_row, int row7, int half) {
         constexpr int h = SUB >> 1, p = SUB & 1;
         uint32_t ql[16], qh[8];
         slab_words<16 * h, 16>(s, ql);            // ql[64h .. 64h+64)
         slab_words<32 + 8 * h, 8>(s, qh);         // qh[32h .. 32h+32)
 #pragma unroll
         for (int c = 0; c < 8; c++) {
-            constexpr int dummy = 0; (void) dummy;
+            if ((c >> 2) != half) continue;
             const int st = 2 * p + (c >> 2);      // stream
             const int l0 = 8 * (c & 3);
             const int sidx = 8 * h + 2 * st + (l0 >> 4);
@@ -210,11 +213,12 @@ template <> struct expander<T_Q6_K> {
 template <> struct expander<T_Q4_0> {
     int nvalid;   // valid blocks in this slab (k tail)
     __device__ __forceinline__ void begin_slab(const uint8_t *, int nv) { nvalid = nv; }
-    template <int SUB> __device__ __forceinline__ void expand64(const uint8_t * s, uint8_t * a_row, int row7) {
+    template <int SUB> __device__ __forceinline__ void expand64(const uint8_t * s, uint8_t * a_row, int row7, int half) {
         uint32_t w[9];
         slab_words<9 * SUB, 9>(s, w);
 #pragma unroll
         for (int b = 0; b < 2; b++) {
+            if (b != half) continue;
             if (2 * SUB + b >= nvalid) {
 #pragma unroll
                 for (int cc = 0; cc < 4; cc++) store_zero_chunk(a_row, row7, 4 * b + cc);
@@ -243,11 +247,12 @@ template <> struct expander<T_Q4_0> {
 template <> struct expander<T_Q8_0> {
     int nvalid;
     __device__ __forceinline__ void begin_slab(const uint8_t *, int nv) { nvalid = nv; }
-    template <int SUB> __device__ __forceinline__ void expand64(const uint8_t * s, uint8_t * a_row, int row7) {
+    template <int SUB> __device__ __forceinline__ void expand64(const uint8_t * s, uint8_t * a_row, int row7, int half) {
         uint32_t w[17];
         slab_words<17 * SUB, 17>(s, w);
 #pragma unroll
         for (int b = 0; b < 2; b++) {
+            if (b != half) continue;
             if (2 * SUB + b >= nvalid) {
 #pragma unroll
                 for (int cc = 0; cc < 4; cc++) store_zero_chunk(a_row, row7, 4 * b + cc);
@@ -288,7 +293,7 @@ struct mmq_args {
 constexpr int MMQ_BM = 128;
 constexpr int MMQ_BK = 64;           // K elements per MMA stage (one 128-byte swizzle row)
 constexpr int MMQ_RS = 2;            // raw slab ring depth
-constexpr int MMQ_THREADS = 192;
+constexpr int MMQ_THREADS = 320;      // 8 weight-producer warps (two threads per row) + activation loader + MMA issuer
 #ifndef MMQ_STAGES_SMALL
 #define MMQ_STAGES_SMALL 4
 #endif
@@ -342,25 +347,28 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b) {
     const int nslab = (int) ((a.k + SLAB_ELEMS - 1) / SLAB_ELEMS);
 
     if (tid == 0) {
-        for (int s = 0; s < ST; s++) { mbar_init(&full[s], 128 + 1); mbar_init(&empty[s], 1); }
+        for (int s = 0; s < ST; s++) { mbar_init(&full[s], 256 + 1); mbar_init(&empty[s], 1); }
         for (int s = 0; s < MMQ_RS * 4; s++) mbar_init(&raw_full[s], 32);
         mbar_init(tmem_full, 1);
         mbar_fence_init();
     }
-    if (warp == 5) tmem_alloc(tmem_slot, CFG::tmem_cols);
+    if (warp == 9) tmem_alloc(tmem_slot, CFG::tmem_cols);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    if (warp < 4) {
-        // ===================================================== weight producers
-        const int64_t row = (m0 + tid < a.m) ? (m0 + tid) : (a.m - 1);     // rows past m recompute the last row, never stored
+    if (warp < 8) {
+        // ===================================================== weight producers: thread pair (prow, half) per row.
+        // The quant -> fp16 expansion is the bound of this kernel (one warp per scheduler cannot hide its own
+        // latencies); warps w and w + 4 share rows 32 w .. 32 w + 31, each expanding 32 of every 64 elements.
+        const int prow = tid & 127, half = tid >> 7, pw = warp & 3;
+        const int64_t row = (m0 + prow < a.m) ? (m0 + prow) : (a.m - 1);   // rows past m recompute the last row, never stored
         const uint8_t * wrow = a.w + row * a.w_row_stride;
-        const int row7 = tid & 7;
+        const int row7 = prow & 7;
         uint8_t * my_raw[MMQ_RS];
 #pragma unroll
-        for (int r = 0; r < MMQ_RS; r++) my_raw[r] = raw + ((size_t) r * MMQ_BM + tid) * a.raw_pitch;
+        for (int r = 0; r < MMQ_RS; r++) my_raw[r] = raw + ((size_t) r * MMQ_BM + prow) * a.raw_pitch;
 
         auto slab_valid_blocks = [&](int s) {
             const int left = a.nblk - s * BLK_PER_SLAB;
@@ -372,20 +380,22 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b) {
             const uint32_t nbytes = (uint32_t) slab_valid_blocks(s) * fmt<T>::bytes;
             const uint32_t off = ALIGNED ? 0u : (uint32_t) (reinterpret_cast<uintptr_t>(src) & 15);
             const uint32_t cp = (off + nbytes + 15u) & ~15u;
-            uint64_t * bar = &raw_full[r * 4 + warp];
+            uint64_t * bar = &raw_full[r * 4 + pw];
             mbar_arrive_expect_tx(bar, cp);
             bulk_g2s(my_raw[r], src - off, cp, bar);
         };
 
-        issue_raw(0);
-        if (nslab > 1) issue_raw(1);
+        if (half == 0) {
+            issue_raw(0);
+            if (nslab > 1) issue_raw(1);
+        }
 
         expander<T> ex;
         for (int s = 0; s < nslab; s++) {
             const int r = s % MMQ_RS;
-            mbar_wait(&raw_full[r * 4 + warp], (uint32_t) ((s / MMQ_RS) & 1));
+            mbar_wait(&raw_full[r * 4 + pw], (uint32_t) ((s / MMQ_RS) & 1));
             uint8_t * slab_ptr = my_raw[r];
-            if (!ALIGNED) {
+            if (!ALIGNED && half == 0) {
                 // shift every row of this warp down to its 16-byte aligned slot start (2-byte granules,
                 // lanes side by side: conflict-free), in place
                 const uint8_t * src = wrow + (size_t) s * BLK_PER_SLAB * fmt<T>::bytes;
@@ -394,7 +404,7 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b) {
                 for (int rr = 0; rr < 32; rr++) {
                     const int off = __shfl_sync(0xFFFFFFFFu, my_off, rr);
                     if (off == 0) continue;
-                    uint8_t * rp = raw + ((size_t) r * MMQ_BM + warp * 32 + rr) * a.raw_pitch;
+                    uint8_t * rp = raw + ((size_t) r * MMQ_BM + pw * 32 + rr) * a.raw_pitch;
 #pragma unroll
                     for (int i0 = 0; i0 < NU16; i0 += 32) {
                         const int i = i0 + lane;
@@ -407,6 +417,7 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b) {
                 }
                 __syncwarp();
             }
+            if (!ALIGNED) named_bar_sync(1 + pw, 64);        // the pair's other warp reads the realigned rows
             ex.begin_slab(slab_ptr, slab_valid_blocks(s));
 #pragma unroll
             for (int sub = 0; sub < 4; sub++) {
@@ -414,26 +425,27 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b) {
                 if (kt < nkt) {
                     const int st = kt % ST;
                     if (kt >= ST) mbar_wait(&empty[st], (uint32_t) (((kt / ST) - 1) & 1));
-                    uint8_t * a_row = a_tiles + (size_t) st * CFG::a_bytes + tid * 128;
-                    if      (sub == 0) ex.template expand64<0>(slab_ptr, a_row, row7);
-                    else if (sub == 1) ex.template expand64<1>(slab_ptr, a_row, row7);
-                    else if (sub == 2) ex.template expand64<2>(slab_ptr, a_row, row7);
-                    else               ex.template expand64<3>(slab_ptr, a_row, row7);
+                    uint8_t * a_row = a_tiles + (size_t) st * CFG::a_bytes + prow * 128;
+                    if      (sub == 0) ex.template expand64<0>(slab_ptr, a_row, row7, half);
+                    else if (sub == 1) ex.template expand64<1>(slab_ptr, a_row, row7, half);
+                    else if (sub == 2) ex.template expand64<2>(slab_ptr, a_row, row7, half);
+                    else               ex.template expand64<3>(slab_ptr, a_row, row7, half);
                     fence_proxy_async_smem();       // generic-proxy stores -> visible to the tensor core's async proxy
                     mbar_arrive(&full[st]);
                 }
             }
-            __syncwarp();                            // the whole warp is done with the raw slot (realign reads neighbours)
-            if (s + MMQ_RS < nslab) issue_raw(s + MMQ_RS);
+            named_bar_sync(1 + pw, 64);              // both warps of the pair are done with the raw slot
+            if (half == 0 && s + MMQ_RS < nslab) issue_raw(s + MMQ_RS);
         }
 
         // ===================================================== epilogue: TMEM -> registers -> global
         mbar_wait(tmem_full, 0);
         tc_fence_after();
-        const int64_t out_row = m0 + tid;
-        const uint32_t taddr = tmem_base + ((uint32_t) (warp * 32) << 16);
+        const int64_t out_row = m0 + prow;
+        const uint32_t taddr = tmem_base + ((uint32_t) (pw * 32) << 16);      // a warp reaches TMEM lanes 32 (warp % 4) ..
+        constexpr int CH = BN >= 16 ? BN / 2 : BN;                             // .. the pair splits the columns
 #pragma unroll 1
-        for (int c0 = 0; c0 < BN; c0 += 8) {
+        for (int c0 = (BN >= 16 ? half * CH : 0); c0 < (BN >= 16 ? (half + 1) * CH : (half == 0 ? BN : 0)); c0 += 8) {
             if (n0 + c0 >= a.n) break;               // warp-uniform
             uint32_t v[8];
             tmem_ld8(taddr + (uint32_t) c0, v);
@@ -446,7 +458,7 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b) {
             }
         }
         tc_fence_before();
-    } else if (warp == 4) {
+    } else if (warp == 8) {
         // ===================================================== activation loader (TMA)
         if (lane == 0) {
             for (int kt = 0; kt < nkt; kt++) {
@@ -480,7 +492,7 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b) {
     }
 
     __syncthreads();
-    if (warp == 5) {
+    if (warp == 9) {
         tc_fence_after();
         tmem_dealloc(tmem_base, CFG::tmem_cols);
     }
