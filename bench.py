@@ -294,6 +294,26 @@ def measure_prefill(torch, kern, n=512, reps=5):
     return out
 
 
+def measure_support(torch, kern, peak):
+    """Secondary figures: the support kernels of the path (SURVEY §8a a7, a18, a19) against the HBM peak;
+    bytes = bytes read + bytes written.  tools/support_probe.py has the full format table."""
+    import b200
+    out = {}
+    m, k = 32000, 4096
+    w = random_blocks_device(torch, kern.device, "q4_K", m, k, 3)
+    rows = torch.randint(0, m, (8192,), dtype=torch.int32, device=kern.device)
+    x = torch.rand((4096, 8192), device=kern.device) * 2 - 1
+    legs = {"dequantize_row_q4_K->f32": (lambda: kern.dequantize_row("q4_K", w, m * k, "f32"), w.numel() + m * k * 4),
+            "get_rows_q4_K(8192 rows)": (lambda: kern.get_rows("q4_K", w, k, rows), 8192 * (b200.row_bytes("q4_K", k) + 4 * k)),
+            "quantize_row_q8_1": (lambda: kern.quantize_row_q8_1(x), x.numel() * 4 + x.numel() // 32 * 36)}
+    for name, (fn, byts) in legs.items():
+        for _ in range(3):
+            fn()
+        sec = timed_loop(torch, fn, 10) / 10
+        out[name] = {"GBps": round(byts / sec / 1e9, 1), "frac": round(byts / sec / 1e9 / peak, 3)}
+    return out
+
+
 # ------------------------------------------------------------------------------------- the CPU reference
 def cpu_reference(budget_s=12.0, sample_layers=4, steps=None, warmup=1):
     """The reference's own CPU implementation of the path (ggml-cpu, unmodified, compiled from
@@ -524,6 +544,10 @@ def main():
             line["prefill_n512_TFLOPs"] = measure_prefill(torch, kern)
         except Exception as e:                   # noqa: BLE001
             line["prefill_n512_TFLOPs"] = {"error": str(e)[:200]}
+        try:
+            line["support_kernels"] = measure_support(torch, kern, peak)
+        except Exception as e:                   # noqa: BLE001
+            line["support_kernels"] = {"error": str(e)[:200]}
         _, info = cpu_reference()
         line["cpu_baseline"] = {k: info[k] for k in ("value", "unit", "cores", "kind", "sample")}
     if rank == 0:

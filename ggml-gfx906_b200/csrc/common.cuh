@@ -67,6 +67,19 @@ __device__ __forceinline__ uint32_t ld_u32_a2(const uint8_t * p) {
 __device__ __forceinline__ uint32_t ld_u32_a4(const uint8_t * p) {
     return __ldg(reinterpret_cast<const uint32_t *>(p));
 }
+// 8 bytes from a 2-byte aligned address with at most three loads; may read up to p + 9 (callers keep that
+// inside the block), never before p
+__device__ __forceinline__ void ld_2x32_a2(const uint8_t * p, uint32_t & w0, uint32_t & w1) {
+    if ((reinterpret_cast<uintptr_t>(p) & 2) == 0) {
+        w0 = ld_u32_a4(p); w1 = ld_u32_a4(p + 4);
+    } else {
+        const uint32_t a = ld_u16(p), b = ld_u32_a4(p + 2), c = ld_u32_a4(p + 6);
+        w0 = a | (b << 16); w1 = (b >> 16) | (c << 16);
+    }
+}
+__device__ __forceinline__ uint2 ld_u64(const uint8_t * p) {
+    return __ldg(reinterpret_cast<const uint2 *>(p));
+}
 __device__ __forceinline__ uint4 ld_u128(const uint8_t * p) {
     return __ldg(reinterpret_cast<const uint4 *>(p));
 }

@@ -47,9 +47,15 @@ template <> __device__ __forceinline__ void dequant8<T_Q8_0>(const uint8_t * b, 
 // the group the first 32 are low nibbles (scale pair 2g), the next 32 high nibbles (pair 2g+1) of
 // qs[32g .. 32g+31].
 template <bool HAS_QH> __device__ __forceinline__ void dequant8_k45(const uint8_t * b, int c, float (&y)[8]) {
-    const float d    = f16_bits_to_f32(ld_u16(b));
-    const float dmin = f16_bits_to_f32(ld_u16(b + 2));
-    const uint32_t s0 = ld_u32_a2(b + 4), s1 = ld_u32_a2(b + 8), s2 = ld_u32_a2(b + 12);
+    // blocks are 144 / 176 bytes: every block of a 16-byte aligned tensor is 16-byte aligned -> one 16-byte load for
+    // the header, one 8-byte load per quant run (the 2-byte-load path costs 12-16 loads per 8 elements and is
+    // load-issue bound: 3.6 TB/s, profiles/r01i_support_probe.txt)
+    const bool al = (reinterpret_cast<uintptr_t>(b) & 15) == 0;
+    uint32_t dm, s0, s1, s2;
+    if (al) { const uint4 hd = ld_u128(b); dm = hd.x; s0 = hd.y; s1 = hd.z; s2 = hd.w; }
+    else    { dm = ld_u32_a2(b); s0 = ld_u32_a2(b + 4); s1 = ld_u32_a2(b + 8); s2 = ld_u32_a2(b + 12); }
+    const float d    = f16_bits_to_f32(dm);
+    const float dmin = f16_bits_to_f32(dm >> 16);
     const int g  = c >> 3;            // 64-element group
     const int hi = (c >> 2) & 1;      // 0: low nibbles, 1: high nibbles
     const int l0 = (c & 3) * 8;       // first byte inside the group's 32 bytes
@@ -58,11 +64,13 @@ template <bool HAS_QH> __device__ __forceinline__ void dequant8_k45(const uint8_
     const float d1 = __fmul_rn(d, (float) sc);
     const float m1 = __fmul_rn(dmin, (float) mn);
     const uint8_t * q = b + (HAS_QH ? 48 : 16) + 32 * g + l0;
-    const uint32_t w0 = ld_u32_a2(q), w1 = ld_u32_a2(q + 4);
-    uint32_t h0 = 0, h1 = 0;
-    if (HAS_QH) {
-        h0 = ld_u32_a2(b + 16 + l0);
-        h1 = ld_u32_a2(b + 16 + l0 + 4);
+    uint32_t w0, w1, h0 = 0, h1 = 0;
+    if (al) {
+        const uint2 w = ld_u64(q); w0 = w.x; w1 = w.y;
+        if (HAS_QH) { const uint2 h = ld_u64(b + 16 + l0); h0 = h.x; h1 = h.y; }
+    } else {
+        w0 = ld_u32_a2(q); w1 = ld_u32_a2(q + 4);            // (never past the block: the last run ends at its last byte)
+        if (HAS_QH) { h0 = ld_u32_a2(b + 16 + l0); h1 = ld_u32_a2(b + 16 + l0 + 4); }
     }
 #pragma unroll
     for (int i = 0; i < 8; i++) {
@@ -90,8 +98,9 @@ template <> __device__ __forceinline__ void dequant8<T_Q6_K>(const uint8_t * b, 
     const float a  = __fmul_rn(d, (float) sc);
     const uint8_t * ql = b + 64 * h + 32 * (s & 1) + l0;
     const uint8_t * qh = b + 128 + 32 * h + l0;
-    const uint32_t w0 = ld_u32_a2(ql), w1 = ld_u32_a2(ql + 4);
-    const uint32_t h0 = ld_u32_a2(qh), h1 = ld_u32_a2(qh + 4);
+    uint32_t w0, w1, h0, h1;
+    ld_2x32_a2(ql, w0, w1);           // a warp covers one block: the alignment branch is warp-uniform
+    ld_2x32_a2(qh, h0, h1);
 #pragma unroll
     for (int i = 0; i < 8; i++) {
         const uint32_t w = i < 4 ? w0 : w1;
