@@ -498,6 +498,15 @@ struct batch_builder {
         int rpc = (int) ceil_div(m, grid);
         rpc += rpc & 1;
         nd.rows_per_cta = rpc;
+        // equal stages: a 28-row slab as 14 + 14 rows instead of 20 + 8 (the short stage costs as much fixed work
+        // and leaves most consumer warps without a row pair)
+        {
+            const int ns = (rpc + R - 1) / R;
+            int Re = (rpc + ns - 1) / ns;
+            Re += Re & 1;
+            if (Re < R) R = Re;
+            nd.R = (unsigned char) R;
+        }
         const int row_pitch = (nd.row_bytes + 15 + 15 + 16) & ~15;
         const int slot_bytes = nd.contiguous ? (15 + R * nd.row_bytes + 15 + 16) : R * row_pitch;
         if (slot_bytes > max_slot) max_slot = slot_bytes;
