@@ -6,6 +6,7 @@
 #include "mmq_tc.cuh"
 
 #include <mutex>
+#include <cstring>
 
 using namespace b200;
 
@@ -31,9 +32,9 @@ encode_tiled_fn get_encode_tiled() {
 }
 
 template <int T, int BN, bool ALIGNED>
-int launch_mmq(const mmq_args & a, const CUtensorMap & tmap, cudaStream_t st) {
+int launch_mmq(const mmq_args & a, const CUtensorMap & tmap, const CUtensorMap & tmap_w, cudaStream_t st) {
     auto kern = k_mmq_tc<T, BN, ALIGNED>;
-    const size_t smem = mmq_smem<BN>::total(a.raw_pitch);
+    const size_t smem = mmq_smem<BN>::total(a.raw_pitch, mmq_rs<T>::value);
     static size_t smem_set[64];
     int dev = 0; cudaGetDevice(&dev); if (dev < 0 || dev >= 64) dev = 0;
     if (smem > smem_set[dev]) {
@@ -42,26 +43,26 @@ int launch_mmq(const mmq_args & a, const CUtensorMap & tmap, cudaStream_t st) {
         smem_set[dev] = smem;
     }
     const dim3 grid((unsigned) ceil_div(a.m, MMQ_BM), (unsigned) ceil_div(a.n, BN));
-    kern<<<grid, MMQ_THREADS, smem, st>>>(a, tmap);
+    kern<<<grid, MMQ_THREADS, smem, st>>>(a, tmap, tmap_w);
     b200_count_launch(1);
     B200_RETURN_IF_LAUNCH_FAILED();
     return B200_OK;
 }
 
 template <int T, int BN>
-int launch_mmq_al(mmq_args a, const CUtensorMap & tmap, bool aligned, cudaStream_t st) {
-    if (aligned) { a.raw_pitch = slab<T>::pitch; return launch_mmq<T, BN, true>(a, tmap, st); }
+int launch_mmq_al(mmq_args a, const CUtensorMap & tmap, const CUtensorMap & tmap_w, bool aligned, cudaStream_t st) {
+    if (aligned) { a.raw_pitch = slab<T>::pitch; return launch_mmq<T, BN, true>(a, tmap, tmap_w, st); }
     a.raw_pitch = slab<T>::pitch_unaligned;
-    return launch_mmq<T, BN, false>(a, tmap, st);
+    return launch_mmq<T, BN, false>(a, tmap, tmap_w, st);
 }
 
 template <int T>
-int launch_mmq_bn(const mmq_args & a, const CUtensorMap & tmap, int bn, bool aligned, cudaStream_t st) {
+int launch_mmq_bn(const mmq_args & a, const CUtensorMap & tmap, const CUtensorMap & tmap_w, int bn, bool aligned, cudaStream_t st) {
     switch (bn) {
-        case 32:  return launch_mmq_al<T, 32>(a, tmap, aligned, st);
-        case 64:  return launch_mmq_al<T, 64>(a, tmap, aligned, st);
-        case 128: return launch_mmq_al<T, 128>(a, tmap, aligned, st);
-        default:  return launch_mmq_al<T, 256>(a, tmap, aligned, st);
+        case 32:  return launch_mmq_al<T, 32>(a, tmap, tmap_w, aligned, st);
+        case 64:  return launch_mmq_al<T, 64>(a, tmap, tmap_w, aligned, st);
+        case 128: return launch_mmq_al<T, 128>(a, tmap, tmap_w, aligned, st);
+        default:  return launch_mmq_al<T, 256>(a, tmap, tmap_w, aligned, st);
     }
 }
 
@@ -129,14 +130,29 @@ extern "C" int b200_mul_mat_q(int type, const void * w_dev, size_t w_row_stride_
     a.w = (const uint8_t *) w_dev; a.w_row_stride = (int64_t) w_row_stride_bytes; a.m = m; a.k = k; a.n = n;
     a.dst = dst_dev; a.dst_col_stride = (int64_t) (dst_col_stride_bytes / 4);
     a.nblk = (int) (k / type_qk(type)); a.raw_pitch = 0;
-    const bool aligned = type != T_Q6_K && ((uintptr_t) w_dev % 16 == 0) && (w_row_stride_bytes % 16 == 0) &&
+    const bool aligned0 = type != T_Q6_K && ((uintptr_t) w_dev % 16 == 0) && (w_row_stride_bytes % 16 == 0) &&
                          !env_int("GGML_B200_MMQ_FORCE_UNALIGNED", 0);
+    // aligned rows: a second descriptor over the raw weight bytes as 32-bit words, dims {row words, m}, box {slab words, 128}
+    bool aligned = aligned0;
+    CUtensorMap tmap_w;
+    memset(&tmap_w, 0, sizeof(tmap_w));
+    if (aligned && b200_row_bytes(type, k) % 4 != 0) aligned = false;      // the descriptor counts the row in 32-bit words
+    if (aligned) {
+        const int slab_words = (type == T_Q8_0 ? 272 : (type == T_Q5_K ? 176 : 144)) / 4;
+        const cuuint64_t wdim[2]    = { (cuuint64_t) (b200_row_bytes(type, k) / 4), (cuuint64_t) m };
+        const cuuint64_t wstride[1] = { (cuuint64_t) w_row_stride_bytes };
+        const cuuint32_t wbox[2]    = { (cuuint32_t) slab_words, (cuuint32_t) MMQ_BM };
+        const CUresult wr = encode(&tmap_w, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<void *>(w_dev), wdim, wstride, wbox, estr,
+                                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (wr != CUDA_SUCCESS) aligned = false;          // odd geometry: per-row copies
+    }
     switch (type) {
-        case T_Q4_0: return launch_mmq_bn<T_Q4_0>(a, tmap, bn, aligned, st);
-        case T_Q8_0: return launch_mmq_bn<T_Q8_0>(a, tmap, bn, aligned, st);
-        case T_Q4_K: return launch_mmq_bn<T_Q4_K>(a, tmap, bn, aligned, st);
-        case T_Q5_K: return launch_mmq_bn<T_Q5_K>(a, tmap, bn, aligned, st);
-        case T_Q6_K: return launch_mmq_bn<T_Q6_K>(a, tmap, bn, false, st);
+        case T_Q4_0: return launch_mmq_bn<T_Q4_0>(a, tmap, tmap_w, bn, aligned, st);
+        case T_Q8_0: return launch_mmq_bn<T_Q8_0>(a, tmap, tmap_w, bn, aligned, st);
+        case T_Q4_K: return launch_mmq_bn<T_Q4_K>(a, tmap, tmap_w, bn, aligned, st);
+        case T_Q5_K: return launch_mmq_bn<T_Q5_K>(a, tmap, tmap_w, bn, aligned, st);
+        case T_Q6_K: return launch_mmq_bn<T_Q6_K>(a, tmap, tmap_w, bn, false, st);
         default: return B200_ERR_TYPE;
     }
 }

@@ -292,7 +292,8 @@ struct mmq_args {
 
 constexpr int MMQ_BM = 128;
 constexpr int MMQ_BK = 64;           // K elements per MMA stage (one 128-byte swizzle row)
-constexpr int MMQ_RS = 2;            // raw slab ring depth
+constexpr int MMQ_RS = 3;            // raw slab ring depth (2 for the formats with slabs > 200 bytes: shared memory)
+template <int T> struct mmq_rs { static constexpr int value = slab<T>::bytes > 200 ? 2 : MMQ_RS; };
 constexpr int MMQ_THREADS = 320;      // 8 weight-producer warps (two threads per row) + activation loader + MMA issuer
 #ifndef MMQ_STAGES_SMALL
 #define MMQ_STAGES_SMALL 4
@@ -316,28 +317,30 @@ template <int BN> struct mmq_smem {
     static constexpr int a_off    = 0;
     static constexpr int b_off    = a_off + mmq_cfg<BN>::stages * mmq_cfg<BN>::a_bytes;
     static constexpr int raw_off  = b_off + mmq_cfg<BN>::stages * mmq_cfg<BN>::b_bytes;
-    static size_t total(int raw_pitch) { return (size_t) raw_off + (size_t) MMQ_RS * MMQ_BM * raw_pitch + 256 + 1024; }
+    static size_t total(int raw_pitch, int rs) { return (size_t) raw_off + (size_t) rs * MMQ_BM * raw_pitch + 256 + 1024; }
 };
 
 template <int T, int BN, bool ALIGNED>
 __global__ void __launch_bounds__(MMQ_THREADS, mmq_cfg<BN>::ctas_per_sm)
-k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b) {
+k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b, const __grid_constant__ CUtensorMap tmap_w) {
     using CFG = mmq_cfg<BN>;
     using SM  = mmq_smem<BN>;
     constexpr int ST = CFG::stages;
     constexpr int SLAB_ELEMS = 256;
     constexpr int BLK_PER_SLAB = SLAB_ELEMS / fmt<T>::qk;       // 1 or 8
+    constexpr int RS = mmq_rs<T>::value;
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t * smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t) 1023);
     uint8_t * a_tiles = smem + SM::a_off;
     uint8_t * b_tiles = smem + SM::b_off;
     uint8_t * raw     = smem + SM::raw_off;
-    uint8_t * ctl     = raw + (size_t) MMQ_RS * MMQ_BM * a.raw_pitch;
+    uint8_t * ctl     = raw + (size_t) RS * MMQ_BM * a.raw_pitch;
     uint64_t * full      = reinterpret_cast<uint64_t *>(ctl);            // [ST]   A written + B landed
     uint64_t * empty     = full + ST;                                    // [ST]   MMAs of the stage retired
     uint64_t * raw_full  = empty + ST;                                   // [RS][4] raw slab landed, per producer warp
-    uint64_t * tmem_full = raw_full + MMQ_RS * 4;                        // accumulator complete
+    uint64_t * raw_empty = raw_full + MMQ_RS * 4;                        // [RS]   every producer is done with the raw slab (ALIGNED)
+    uint64_t * tmem_full = raw_empty + MMQ_RS;                           // accumulator complete
     uint32_t * tmem_slot = reinterpret_cast<uint32_t *>(tmem_full + 1);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -348,7 +351,10 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b) {
 
     if (tid == 0) {
         for (int s = 0; s < ST; s++) { mbar_init(&full[s], 256 + 1); mbar_init(&empty[s], 1); }
-        for (int s = 0; s < MMQ_RS * 4; s++) mbar_init(&raw_full[s], 32);
+        // ALIGNED: one 2-D TMA tile per raw slab (128 rows x slab bytes), issued by the loader thread;
+        // otherwise one bulk copy per row, issued by that row's producer thread
+        for (int s = 0; s < MMQ_RS * 4; s++) mbar_init(&raw_full[s], ALIGNED ? 1 : 32);
+        for (int s = 0; s < MMQ_RS; s++) mbar_init(&raw_empty[s], 256);
         mbar_init(tmem_full, 1);
         mbar_fence_init();
     }
@@ -366,16 +372,16 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b) {
         const int64_t row = (m0 + prow < a.m) ? (m0 + prow) : (a.m - 1);   // rows past m recompute the last row, never stored
         const uint8_t * wrow = a.w + row * a.w_row_stride;
         const int row7 = prow & 7;
-        uint8_t * my_raw[MMQ_RS];
+        uint8_t * my_raw[RS];
 #pragma unroll
-        for (int r = 0; r < MMQ_RS; r++) my_raw[r] = raw + ((size_t) r * MMQ_BM + prow) * a.raw_pitch;
+        for (int r = 0; r < RS; r++) my_raw[r] = raw + ((size_t) r * MMQ_BM + prow) * a.raw_pitch;
 
         auto slab_valid_blocks = [&](int s) {
             const int left = a.nblk - s * BLK_PER_SLAB;
             return left < BLK_PER_SLAB ? left : BLK_PER_SLAB;
         };
         auto issue_raw = [&](int s) {
-            const int r = s % MMQ_RS;
+            const int r = s % RS;
             const uint8_t * src = wrow + (size_t) s * BLK_PER_SLAB * fmt<T>::bytes;
             const uint32_t nbytes = (uint32_t) slab_valid_blocks(s) * fmt<T>::bytes;
             const uint32_t off = ALIGNED ? 0u : (uint32_t) (reinterpret_cast<uintptr_t>(src) & 15);
@@ -385,15 +391,14 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b) {
             bulk_g2s(my_raw[r], src - off, cp, bar);
         };
 
-        if (half == 0) {
-            issue_raw(0);
-            if (nslab > 1) issue_raw(1);
+        if (!ALIGNED && half == 0) {
+            for (int s = 0; s < RS && s < nslab; s++) issue_raw(s);
         }
 
         expander<T> ex;
         for (int s = 0; s < nslab; s++) {
-            const int r = s % MMQ_RS;
-            mbar_wait(&raw_full[r * 4 + pw], (uint32_t) ((s / MMQ_RS) & 1));
+            const int r = s % RS;
+            mbar_wait(&raw_full[r * 4 + (ALIGNED ? 0 : pw)], (uint32_t) ((s / RS) & 1));
             uint8_t * slab_ptr = my_raw[r];
             if (!ALIGNED && half == 0) {
                 // shift every row of this warp down to its 16-byte aligned slot start (2-byte granules,
@@ -434,8 +439,12 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b) {
                     mbar_arrive(&full[st]);
                 }
             }
-            named_bar_sync(1 + pw, 64);              // both warps of the pair are done with the raw slot
-            if (half == 0 && s + MMQ_RS < nslab) issue_raw(s + MMQ_RS);
+            if (ALIGNED) {
+                mbar_arrive(&raw_empty[r]);          // the loader refills the slot when all 256 producers have left it
+            } else {
+                named_bar_sync(1 + pw, 64);          // both warps of the pair are done with the raw slot
+                if (half == 0 && s + RS < nslab) issue_raw(s + RS);
+            }
         }
 
         // ===================================================== epilogue: TMEM -> registers -> global
@@ -461,7 +470,19 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b) {
     } else if (warp == 8) {
         // ===================================================== activation loader (TMA)
         if (lane == 0) {
+            int next_slab = 0;
             for (int kt = 0; kt < nkt; kt++) {
+                if (ALIGNED) {
+                    // raw weight slabs, MMQ_RS - 1 ahead of the slab the producers expand: one 2-D TMA tile each (rows
+                    // past m and words past the row end are zero-filled)
+                    while (next_slab < nslab && next_slab <= kt / 4 + RS - 1) {
+                        const int r = next_slab % RS;
+                        if (next_slab >= RS) mbar_wait(&raw_empty[r], (uint32_t) (((next_slab / RS) - 1) & 1));
+                        mbar_arrive_expect_tx(&raw_full[r * 4], (uint32_t) (MMQ_BM * slab<T>::bytes));
+                        tma_load_2d(raw + (size_t) r * MMQ_BM * a.raw_pitch, &tmap_w, next_slab * (slab<T>::bytes / 4), (int) m0, &raw_full[r * 4]);
+                        next_slab++;
+                    }
+                }
                 const int st = kt % ST;
                 if (kt >= ST) mbar_wait(&empty[st], (uint32_t) (((kt / ST) - 1) & 1));
                 mbar_arrive_expect_tx(&full[st], (uint32_t) CFG::b_bytes);
