@@ -13,7 +13,7 @@ import os
 from typing import Optional
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libggml_b200_kernels.so")
+LIB_PATH = os.environ.get("GGML_B200_KERNELS_LIB") or os.path.join(HERE, "libggml_b200_kernels.so")   # override: tuning builds
 
 TYPE_ID = {"f32": 0, "f16": 1, "q4_0": 2, "q8_0": 8, "q8_1": 9, "q4_K": 12, "q5_K": 13, "q6_K": 14, "i32": 26, "bf16": 30}
 BLOCK_ELEMS = {"q4_0": 32, "q8_0": 32, "q8_1": 32, "q4_K": 256, "q5_K": 256, "q6_K": 256}

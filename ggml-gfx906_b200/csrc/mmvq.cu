@@ -252,9 +252,15 @@ extern "C" int b200_mul_mat_batch(const b200_mul_mat_node * nodes, int64_t count
         for (int f = 0; f < 3 && rc == B200_OK; f++) {
             batch_builder * bb = fam_bb[f];
             if (bb->empty()) continue;
-            if (bb->args.count == 1 && !env_int("GGML_B200_BATCH_SINGLE", 0)) {
-                // one node: the per-node decode kernel (same per-row arithmetic, one launch instead of two)
-                const batch_node nd = bb->args.nodes[0];
+            // one node (a dependent chain's link): small ones take the per-node decode kernel (same per-row
+            // arithmetic, one launch instead of two); from ~4 MB of Q4_K/Q5_K weights the persistent pair is
+            // faster even alone (4096x11008: 11.2 us against 17.4 us, profiles/r01m_single_probe.txt).
+            // GGML_B200_BATCH_SINGLE=1 / 0 forces the persistent / the per-node kernel.
+            const int single_mode = env_int("GGML_B200_BATCH_SINGLE", -1);
+            const batch_node nd = bb->args.nodes[0];
+            const bool single_persistent = single_mode >= 0 ? single_mode != 0
+                                         : (f == 0 && (int64_t) nd.m * nd.row_bytes >= (int64_t) 4 << 20);
+            if (bb->args.count == 1 && !single_persistent) {
                 rc = mmvq_fused_try(nd.type, nd.w, nd.row_stride, nd.m, nd.k, nd.x, nd.dst, bb->all_const, st);
                 if (rc == B200_STREAM_NOT_APPLICABLE) rc = batch_launch(*bb, st);
             } else {

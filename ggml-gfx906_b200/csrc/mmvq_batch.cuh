@@ -20,9 +20,9 @@
 //         mbarriers: the weights of node i+1.. are in flight while node i is reduced, HBM never idles;
 //       warp 1 (activation producer) bulk-copies the quantized activations of the next nodes into a small
 //         ring of activation buffers (ready/free mbarriers);
-//       12 consumer warps: a lane owns 128 consecutive weights of a row (hitem<T>, mmvq_fused.cuh) and keeps
+//       14 consumer warps: a lane owns 128 consecutive weights of a row (hitem<T>, mmvq_fused.cuh) and keeps
 //         the matching q8 activations in registers for the node; W consecutive warps cover a row, the
-//         G = 12 / W groups take the row pairs of the stages round-robin; partials of a row meet in shared
+//         G = 14 / W groups (12 when W = 1) take the row pairs of the stages round-robin; partials of a row meet in shared
 //         memory in fixed order, so a row's value never depends on the grid, the list or the GPU that
 //         computes it (row-split results stay bit-identical).  Every consumer warp observes every stage
 //         (mbarrier phases are parity bits: a waiter that skipped stages could mistake phase n-2 for n).
@@ -35,7 +35,7 @@
 namespace b200 {
 
 constexpr int BATCH_MAX_NODES  = 448;
-constexpr int BATCH_NWC        = 12;     // consumer warps
+constexpr int BATCH_NWC        = 14;     // consumer warps at most; a launch runs 12 or 14 (batch_args::nwc)
 constexpr int BATCH_AHDR       = 128;    // bytes in front of each activation buffer: the node as the consumers need it
 constexpr int BATCH_THREADS    = (2 + BATCH_NWC) * 32;
 constexpr int BATCH_MAX_STAGES = 16;
@@ -60,7 +60,7 @@ static_assert(sizeof(batch_node) == 64, "batch_node is part of the kernel parame
 struct batch_args {
     int count, S, slot_stride, acts_stride;
     int off_part, off_acts, off_slots, const_weights;
-    int NB, kmax, pad[2];
+    int NB, kmax, nwc, pad;
     batch_node nodes[BATCH_MAX_NODES];
 };
 
@@ -294,7 +294,7 @@ __device__ __forceinline__ void batch_consume(const cnode & nd, const int cw, co
 }
 
 // ---------------------------------------------------------------- the persistent kernel
-// 14 warps = 4 + 4 + 3 + 3 per SM sub-partition: 4 warps share 16 K registers -> 128 per thread is the ceiling.
+// 16 warps = 4 per SM sub-partition: 4 warps share 16 K registers -> 128 per thread is the ceiling.
 // One instantiation per format family: FAM 0 = Q4_K / Q5_K (16-byte aligned 128-weight items), FAM 1 = Q6_K,
 // FAM 2 = Q4_0 / Q8_0 (four 32-weight blocks per item).
 // Mixed in one kernel, Q6_K's 27-word realigned items push the loop state of ALL formats into local memory
@@ -316,8 +316,8 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
     const int S = a.S, NB = a.NB;
 
     if (tid == 0) {
-        for (int s = 0; s < S; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], BATCH_NWC); }
-        for (int u = 0; u < NB; u++) { mbar_init(&acts_ready[u], 1); mbar_init(&acts_free[u], BATCH_NWC); }
+        for (int s = 0; s < S; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], a.nwc); }
+        for (int u = 0; u < NB; u++) { mbar_init(&acts_ready[u], 1); mbar_init(&acts_free[u], a.nwc); }
         mbar_fence_init();
     }
     __syncthreads();
@@ -412,7 +412,7 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
         // parity (git) simply carry on across nodes; a different W needs every consumer warp to be past its
         // last reduction before the new layout is written
         if (nd.W > 1) {
-            if (layout_w != 0 && layout_w != nd.W) { named_bar_sync(13, BATCH_NWC * 32); git = 0; }
+            if (layout_w != 0 && layout_w != nd.W) { named_bar_sync(BATCH_NWC + 1, a.nwc * 32); git = 0; }
             layout_w = nd.W;
         }
         if (FAM == 2) {
@@ -465,7 +465,8 @@ struct batch_builder {
     bool all_const = true;
     int  fam = 0;                     // format family of this builder's nodes (kernel instantiation)
     explicit batch_builder(int family) : fam(family) { reset(); }
-    void reset() { args.count = 0; args.kmax = 0; max_slot = 0; all_const = true; }
+    int64_t bytes_w14 = 0, bytes_w12 = 0;                       // weight bytes of nodes that gain / do not gain from 14 consumer warps
+    void reset() { args.count = 0; args.kmax = 0; max_slot = 0; all_const = true; bytes_w14 = bytes_w12 = 0; }
     bool full() const { return args.count >= BATCH_MAX_NODES; }
     bool empty() const { return args.count == 0; }
 
@@ -486,7 +487,8 @@ struct batch_builder {
         nd.row_bytes = (int) (k / type_qk(type) * type_bytes(type));
         nd.type = (unsigned char) type;
         nd.W = (unsigned char) ceil_div(k / 128, 32);
-        nd.G = (unsigned char) (BATCH_NWC / nd.W);
+        nd.G = 0;                                               // batch_launch: consumer warps of the launch / W
+        (nd.W == 7 || nd.W == 2 ? bytes_w14 : bytes_w12) += (int64_t) m * nd.row_bytes;
         // rows per stage: the nearest number of row pairs to the target; mat-vecs whose rows need several
         // warps (W > 1) keep their partials in shared memory, sized for BATCH_RMAX rows
         int R = 2 * ((slot_target + nd.row_bytes) / (2 * nd.row_bytes));
@@ -524,6 +526,15 @@ static int batch_launch(batch_builder & bb, cudaStream_t st) {
     static const int nb_env = env_int("GGML_B200_BATCH_ABUF", 2);
     static const int pdl = env_int("GGML_B200_FUSED_PDL", 1);
     a.const_weights = bb.all_const ? 1 : 0;
+    // consumer warps: 12 (14 warps = 448 threads) is 1-1.5 % faster on one-warp rows (k <= 4096) than 14; rows of
+    // 7 warps (k = 28672, the Llama-3-70B down projection) leave 5 of 12 idle but fill 14 (60 % -> 85 % of the
+    // measured HBM peak), rows of 2 warps gain 2 %.  Both are within the 128-register ceiling (<= 4 warps / SMSP).
+    static const int nwc_env = env_int("GGML_B200_BATCH_NWC", 0);
+    a.nwc = nwc_env == 12 || nwc_env == 14 ? nwc_env : (bb.bytes_w14 > bb.bytes_w12 ? 14 : 12);
+    for (int i = 0; i < a.count; i++) {
+        const int G = a.nwc / a.nodes[i].W;
+        a.nodes[i].G = (unsigned char) (a.nodes[i].W == 1 && G > 12 ? 12 : G);
+    }
     a.slot_stride = (bb.max_slot + 127) & ~127;
     a.off_part    = (2 * BATCH_MAX_STAGES + 2 * BATCH_MAX_ABUF) * 8;
     a.off_acts    = (a.off_part + 2 * BATCH_NWC * BATCH_RMAX * (int) sizeof(float) + 127) & ~127;
@@ -555,7 +566,7 @@ static int batch_launch(batch_builder & bb, cudaStream_t st) {
     }
     // 2. the persistent mat-vec; starts (and prefetches constant weights) while the quantizer drains
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned) caps.sm_count); cfg.blockDim = dim3(BATCH_THREADS);
+    cfg.gridDim = dim3((unsigned) caps.sm_count); cfg.blockDim = dim3((unsigned) (2 + a.nwc) * 32);
     cfg.dynamicSmemBytes = smem; cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
