@@ -413,6 +413,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--wtype", default="q4_K", help="weight format of the stack (default: the headline Q4_K)")
+    ap.add_argument("--stack", default="llama2-7b", choices=["llama2-7b", "llama3-70b-ffn"],
+                    help="llama2-7b: the headline stack, rows x N at N GPUs (weak scaling); llama3-70b-ffn: BASELINE "
+                         "configs[4], 16 layers of the 8192x28672 Q4_K FFN row-split over the N GPUs (strong scaling)")
     ap.add_argument("--no-extras", action="store_true", help="skip the prefill figure and the CPU baseline")
     args = ap.parse_args()
     rank = env_int("RANK", 0)
@@ -432,7 +435,8 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     dbg("process group up")
     kern = b200.Kernels(device=local_rank)
-    mats = workloads.llama2_7b_stack(args.wtype, row_mult=world)
+    strong = args.stack == "llama3-70b-ffn"
+    mats = workloads.llama3_70b_ffn(n_layers=16) if strong else workloads.llama2_7b_stack(args.wtype, row_mult=world)
     stack = DecodeStack(kern, mats, 1, rank, world)
     lib = kern.lib
     dbg("stack built")
@@ -512,13 +516,14 @@ def main():
     line = {
         "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": round(sec / args.steps * 1e3, 4), "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "int8 dot (q8_1 activations), f32 accumulate",
+        "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "int8 dot (q8_1 activations), f32 accumulate",
         "data": "synthetic",
-        "config": {"workload": WORKLOAD if args.wtype == "q4_K" else WORKLOAD.replace("Q4_K", args.wtype),
-                   "n": 1, "matrices": len(mats), "row_mult": world,
+        "config": {"workload": "llama3-70b FFN (gate, up 28672x8192; down 8192x28672) x 16 layers, Q4_K, decode mat-vec n=1, rows split over the GPUs (BASELINE configs[4])"
+                               if strong else (WORKLOAD if args.wtype == "q4_K" else WORKLOAD.replace("Q4_K", args.wtype)),
+                   "n": 1, "matrices": len(mats), "row_mult": 1 if strong else world,
                    "weight_bytes_per_gpu": stack.local_weight_bytes,
                    "algorithmic_bytes_per_step": alg_total,
-                   "l2": "inputs larger than L2 (3.7 GB of weights per GPU streamed once per step; no flush)",
+                   "l2": f"inputs larger than L2 ({stack.local_weight_bytes / 1e9:.1f} GB of weights per GPU streamed once per step; no flush)",
                    "launch": "CUDA graph replay" if graph is not None else "eager",
                    "parallelism": "single GPU" if world == 1 else f"row-split x{world}: one persistent launch per rank + one NCCL all-gather of the rank-major output arena per step"},
         "e2e": {"value": round(e2e, 1), "unit": UNIT, "h2d_bytes_per_step": stack.x_bytes,

@@ -11,6 +11,7 @@
 #include "mmvq_stream.cuh"
 #include "mmvq_fused.cuh"
 #include "mmvq_batch.cuh"
+#include "mmvq_cols.cuh"
 
 #include <vector>
 
@@ -209,7 +210,11 @@ extern "C" size_t b200_mul_mat_batch_workspace_size(const b200_mul_mat_node * no
     for (int64_t i = 0; i < count; i++) {
         const size_t s = b200_mul_mat_workspace_size(nodes[i].type_a, nodes[i].ne_a, nodes[i].ne_b);
         if (s > need) need = s;
-        if (nodes[i].ne_b[1] == 1 && nodes[i].ne_a[0] > 0) acts += batch_acts_record_bytes(nodes[i].ne_a[0]);
+        if (nodes[i].ne_b[1] >= 1 && nodes[i].ne_b[1] <= B200_MMVQ_MAX_N && nodes[i].ne_a[0] > 0) {
+            const size_t per_col = (size_t) nodes[i].ne_b[1] * batch_acts_record_bytes(nodes[i].ne_a[0]);
+            const size_t tile = cols_ws_bytes(nodes[i].ne_a[0], nodes[i].ne_b[1]);
+            acts += per_col > tile ? per_col : tile;
+        }
     }
     return need + acts + 256;
 }
@@ -240,6 +245,10 @@ extern "C" int b200_mul_mat_batch(const b200_mul_mat_node * nodes, int64_t count
     // pending set are independent, so sorting them into per-family launches keeps the semantics
     static thread_local batch_builder * fam_bb[3] = { nullptr, nullptr, nullptr };
     static thread_local range_set reads, writes;
+    static thread_local cols_builder * cols_bb = nullptr;       // nodes with 2..8 columns (Q4_K / Q5_K): the MMA list kernel
+    if (!cols_bb) cols_bb = new cols_builder();
+    cols_bb->reset();
+    static const int use_cols = env_int("GGML_B200_COLS_KERNEL", 1);
     if (!fam_bb[0]) { for (int f = 0; f < 3; f++) fam_bb[f] = new batch_builder(f); }
     ws_cursor cur;
     cur.reset((uint8_t *) workspace_dev, workspace_bytes);
@@ -268,6 +277,7 @@ extern "C" int b200_mul_mat_batch(const b200_mul_mat_node * nodes, int64_t count
             }
             bb->reset();
         }
+        if (rc == B200_OK && !cols_bb->empty()) { rc = cols_launch(*cols_bb, st); cols_bb->reset(); }
         // stream order: the next launch's quantizer starts after these launches have finished with the workspace
         cur.reset((uint8_t *) workspace_dev, workspace_bytes);
         return rc;
@@ -275,26 +285,63 @@ extern "C" int b200_mul_mat_batch(const b200_mul_mat_node * nodes, int64_t count
     for (int64_t i = 0; i < count; i++) {
         const b200_mul_mat_node & nd = nodes[i];
         const int64_t k = nd.ne_a[0], m = nd.ne_a[1];
-        const bool plain = persistent && type_is_quant(nd.type_a) && nd.ne_b[0] == k && nd.ne_b[1] == 1 &&
+        // a few columns (decode at batch 2..8) ride the persistent launch as one entry per column, back to back:
+        // the CTA streams its slab of W once from HBM and finds it in L2 for the other columns (a node's slab per
+        // CTA is 64-200 KB), which beats the per-node kernel's two launches per MUL_MAT up to GGML_B200_BATCH_COLS
+        static const int colmax = env_int("GGML_B200_BATCH_COLS", 8);
+        const int64_t ncols = nd.ne_b[1];
+        const bool plain = persistent && type_is_quant(nd.type_a) && nd.ne_b[0] == k && ncols >= 1 && (ncols == 1 || ncols <= colmax) &&
+                           (ncols == 1 || nd.nb_b[1] % 16 == 0) &&
                            nd.ne_a[2] == 1 && nd.ne_a[3] == 1 && nd.ne_b[2] == 1 && nd.ne_b[3] == 1 &&
                            nd.nb_a[0] == (size_t) type_bytes(nd.type_a) && nd.nb_b[0] == sizeof(float) &&
                            batch_node_ok(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, nd.b_dev);
+        if (persistent && use_cols && ncols >= 2 && nd.ne_b[0] == k && nd.ne_a[2] == 1 && nd.ne_a[3] == 1 && nd.ne_b[2] == 1 && nd.ne_b[3] == 1 &&
+            nd.nb_a[0] == (size_t) type_bytes(nd.type_a) && nd.nb_b[0] == sizeof(float) &&
+            cols_node_ok(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, nd.b_dev, (int64_t) nd.nb_b[1], ncols)) {
+            const uintptr_t x0 = (uintptr_t) nd.b_dev, x1 = x0 + (size_t) (ncols - 1) * nd.nb_b[1] + (size_t) k * 4;
+            const uintptr_t d0 = (uintptr_t) nd.dst_dev, d1 = d0 + (size_t) m * ncols * 4;
+            if (cols_bb->full() || writes.hits(x0, x1) || writes.hits(d0, d1) || reads.hits(d0, d1)) {
+                const int rc = flush();
+                if (rc) return rc;
+            }
+            bool ok = cols_bb->add(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, nd.b_dev, (int64_t) nd.nb_b[1], ncols, nd.dst_dev, cur);
+            if (!ok && !(fam_bb[0]->empty() && fam_bb[1]->empty() && fam_bb[2]->empty() && cols_bb->empty())) {
+                const int rc = flush();
+                if (rc) return rc;
+                ok = cols_bb->add(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, nd.b_dev, (int64_t) nd.nb_b[1], ncols, nd.dst_dev, cur);
+            }
+            if (ok) { reads.add(x0, x1); writes.add(d0, d1); continue; }
+        }
         if (plain) {
-            const uintptr_t x0 = (uintptr_t) nd.b_dev, x1 = x0 + (size_t) k * 4;
-            const uintptr_t d0 = (uintptr_t) nd.dst_dev, d1 = d0 + (size_t) m * 4;
+            const uintptr_t x0 = (uintptr_t) nd.b_dev, x1 = x0 + (size_t) (ncols - 1) * nd.nb_b[1] + (size_t) k * 4;
+            const uintptr_t d0 = (uintptr_t) nd.dst_dev, d1 = d0 + (size_t) m * ncols * 4;
             batch_builder * bb = fam_bb[batch_family(nd.type_a)];
-            if (bb->full() || writes.hits(x0, x1) || writes.hits(d0, d1) || reads.hits(d0, d1)) {
+            if (writes.hits(x0, x1) || writes.hits(d0, d1) || reads.hits(d0, d1)) {
                 const int rc = flush();
                 if (rc) return rc;
             }
             const bool cw = (nd.flags & B200_MUL_MAT_CONST_WEIGHTS) != 0;
-            bool ok = bb->add(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, nd.b_dev, nd.dst_dev, cw, grid, cur);
-            if (!ok && !(fam_bb[0]->empty() && fam_bb[1]->empty() && fam_bb[2]->empty())) {      // workspace full: launch what is pending, start over
-                const int rc = flush();
-                if (rc) return rc;
-                ok = bb->add(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, nd.b_dev, nd.dst_dev, cw, grid, cur);
+            int64_t c = 0;
+            for (; c < ncols; c++) {
+                const float * xc = (const float *) ((const uint8_t *) nd.b_dev + c * nd.nb_b[1]);
+                float * dc = nd.dst_dev + c * m;
+                if (bb->full()) {
+                    const int rc = flush();
+                    if (rc) return rc;
+                }
+                bool ok = bb->add(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, xc, dc, cw, grid, cur);
+                if (!ok && !(fam_bb[0]->empty() && fam_bb[1]->empty() && fam_bb[2]->empty() && cols_bb->empty())) {  // workspace full: launch what is pending, start over
+                    const int rc = flush();
+                    if (rc) return rc;
+                    ok = bb->add(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, xc, dc, cw, grid, cur);
+                }
+                if (!ok) break;
             }
-            if (ok) { reads.add(x0, x1); writes.add(d0, d1); continue; }
+            if (c == ncols) { reads.add(x0, x1); writes.add(d0, d1); continue; }
+            if (c > 0) {                              // some columns are pending and the rest has no room: not reachable with a
+                const int rc = flush();               // workspace of b200_mul_mat_batch_workspace_size; finish them, then recompute the node
+                if (rc) return rc;
+            }
             // no room even for one record: the per-node path below reports the workspace error
         }
         int rc = flush();

@@ -1,0 +1,293 @@
+// mmvq_cols.cuh — decode at batch 2..8 (MUL_MAT with a few activation columns), Q4_K / Q5_K weights:
+// ONE launch pair per list of independent nodes, int8 tensor-core MMA on the weight nibbles as they are.
+//
+// The reference sends n <= 8 through mul_mat_vec_q with ncols_dst template instances (src/ggml-cuda/mmvq.cu:139-226,
+// one dp4a chain per column) and larger n to the MMQ tiles (mmq.cuh).  On B200 the dp4a chains make the decode
+// list kernel issue-bound as soon as there is more than one column (measured: time = n x the one-column time even
+// with the weights in L2), so here a warp multiplies a 16-row x 32-weight sub-block by the 8 (padded) columns
+// with one mma.sync.m16n8k32.s8 and applies the block scales on the 16x8 int32 result:
+//   * the k4 nibble layout IS the A fragment: lane (g, t) needs bytes 4t..4t+3 and 16+4t..16+4t+3 of rows g and
+//     g + 8 of a 32-byte quant chunk -- two words per row, whose low / high nibbles are the sub-blocks 2j / 2j+1;
+//   * activations are quantized once per list to int8 columns + (d, d * sum) pairs per 32-block (q8_1 arithmetic),
+//     and read as B fragments straight from global memory (they stay in L1/L2: n x k bytes);
+//   * work unit = (node, 16-row tile), dealt round-robin to a grid of 3 CTAs per SM; the 8 warps of a CTA split K
+//     in 128-weight items (software-prefetched one item ahead), partial 16x8 tiles meet in shared memory and are
+//     added in fixed warp order: a row's value does not depend on the grid.
+// No shared-memory staging of the weights: a tile row's 128-weight item is 64 contiguous bytes (two full sectors),
+// and the CTA's warps walk the same 16 rows together.
+#pragma once
+#include "mmvq_batch.cuh"
+
+namespace b200 {
+
+constexpr int COLS_NW        = 8;      // warps per CTA
+constexpr int COLS_CTAS      = 3;      // CTAs per SM (register budget 85 per thread)
+constexpr int COLS_MAX_NODES = 384;    // 72 B each in the kernel parameter block (27 KB)
+constexpr int COLS_N         = 8;      // columns of the MMA tile
+
+struct cols_node {
+    const uint8_t * w;        // weights, rows of k4 super-blocks
+    const float   * x;        // activations [n][x_stride floats]
+    float         * dst;      // [n][m]
+    int8_t        * yq;       // workspace: int8 [n][k]
+    float2        * yds;      // workspace: (d, d * sum) [k / 32][8]
+    int64_t row_stride;
+    int   m, k, n, x_stride, unit0;     // unit0: index of this node's first 16-row tile in the launch
+    unsigned char type, quantize, pad[2];
+};
+static_assert(sizeof(cols_node) == 72, "cols_node is part of the kernel parameter block");
+
+struct cols_args {
+    int count, units, kmax, pad;
+    cols_node nodes[COLS_MAX_NODES];
+};
+
+// ---------------------------------------------------------------- activations of the list: f32 -> int8 columns
+// grid (ceil(kmax / 32 / 8), count, 8), block 256: one warp per 32 values of one column (q8_1 arithmetic as quantize.cu)
+__global__ void __launch_bounds__(256) k_quantize_cols(const __grid_constant__ cols_args a) {
+    const cols_node & nd = a.nodes[blockIdx.y];
+    const int kb = blockIdx.x * 8 + (threadIdx.x >> 5), c = blockIdx.z;
+    const int lane = threadIdx.x & 31;
+    if (!nd.quantize || kb * 32 >= nd.k) return;
+    if (c >= nd.n) {                                      // padding columns: zero scale pairs, q never read as non-zero
+        if (lane == 0) nd.yds[kb * COLS_N + c] = make_float2(0.0f, 0.0f);
+        return;
+    }
+    const float x = __ldg(nd.x + (size_t) c * nd.x_stride + kb * 32 + lane);
+    const float amax = warp_max(fabsf(x));
+    const float d  = __fdiv_rn(amax, 127.0f);
+    const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+    const float v  = roundf(__fmul_rn(x, id));
+    const int   qi = fabsf(v) < 2147483648.0f ? (int) v : (int) 0x80000000;
+    const int   q8 = (int) (int8_t) (qi & 0xFF);
+    nd.yq[(size_t) c * nd.k + kb * 32 + lane] = (int8_t) q8;
+    int sum = q8;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) sum += __shfl_xor_sync(0xFFFFFFFFu, sum, off);
+    if (lane == 0) {
+        const float dh = __half2float(__float2half_rn(d));
+        nd.yds[kb * COLS_N + c] = make_float2(dh, dh * (float) sum);
+    }
+}
+
+// ---------------------------------------------------------------- the MMA
+__device__ __forceinline__ void mma_s8_16x8x32(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+                 : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// streaming loads of the weights: read-only path, not kept in L1 (L1 is for the activation columns)
+__device__ __forceinline__ uint2 ldg_stream64(const void * p) {
+    uint2 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ uint4 ldg_stream128(const void * p) {
+    uint4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+}
+
+// The words of one 128-weight item (half a super-block) of one row that lane (g, t) needs.  The MMA's k order
+// inside a 32-block is free as long as A and B agree: lane t takes bytes 8t..8t+7 of the 32-byte quant chunk
+// (one 8-byte load) as its k slots 4t..4t+3 and 16+4t..16+4t+3, and the same bytes of the activation block.
+struct cols_item {
+    uint4 hdr;                // d, dmin (f16 x 2) + 12 scale bytes
+    uint2 q[2];               // [quant chunk of the item] bytes 8t..8t+7
+    uint2 h;                  // Q5_K: high-bit bytes 8t..8t+7
+};
+
+__device__ __forceinline__ void cols_load(cols_item & it, const uint8_t * row, int item, int t, bool q5) {
+    const uint8_t * blk = row + (size_t) (item >> 1) * (q5 ? 176 : 144);
+    it.hdr = ldg_stream128(blk);
+    const uint8_t * qs = blk + (q5 ? 48 : 16) + (item & 1) * 64 + 8 * t;
+    it.q[0] = ldg_stream64(qs);
+    it.q[1] = ldg_stream64(qs + 32);
+    if (q5) it.h = ldg_stream64(blk + 16 + 8 * t);
+}
+
+// d * sc and dmin * m of the item's four sub-blocks (get_scale_min_k4 on four bytes at a time)
+__device__ __forceinline__ void cols_scales(const uint4 & hdr, int half, float (&dsc)[4], float (&dmn)[4]) {
+    const float2 dm = __half22float2(*reinterpret_cast<const __half2 *>(&hdr.x));
+    uint32_t sc, mn;
+    if (half == 0) { sc = hdr.y & 0x3F3F3F3Fu; mn = hdr.z & 0x3F3F3F3Fu; }
+    else {
+        sc = (hdr.w & 0x0F0F0F0Fu) | ((hdr.y >> 2) & 0x30303030u);
+        mn = ((hdr.w >> 4) & 0x0F0F0F0Fu) | ((hdr.z >> 2) & 0x30303030u);
+    }
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        dsc[q] = dm.x * (float) ((sc >> (8 * q)) & 0xFFu);
+        dmn[q] = dm.y * (float) ((mn >> (8 * q)) & 0xFFu);
+    }
+}
+
+__device__ __forceinline__ void cols_item_mma(const cols_item & ia, const cols_item & ib, int item, int g, int t, bool q5,
+                                              const int8_t * yq_col, const float2 * yds, bool col_ok, float (&acc)[4]) {
+    const int half = item & 1;
+    float dscA[4], dmnA[4], dscB[4], dmnB[4];
+    cols_scales(ia.hdr, half, dscA, dmnA);
+    cols_scales(ib.hdr, half, dscB, dmnB);
+    const int blk0 = (item >> 1) * 8 + half * 4;                       // first 32-block of the item
+    const int8_t * yq = yq_col + (size_t) blk0 * 32 + 8 * t;
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        const int p = q >> 1, sh = (q & 1) * 4;
+        uint32_t a0 = (ia.q[p].x >> sh) & 0x0F0F0F0Fu, a1 = (ib.q[p].x >> sh) & 0x0F0F0F0Fu;
+        uint32_t a2 = (ia.q[p].y >> sh) & 0x0F0F0F0Fu, a3 = (ib.q[p].y >> sh) & 0x0F0F0F0Fu;
+        if (q5) {
+            const int s = half * 4 + q;                                  // bit s of qh belongs to sub-block s
+            a0 |= ((ia.h.x >> s) & 0x01010101u) << 4; a1 |= ((ib.h.x >> s) & 0x01010101u) << 4;
+            a2 |= ((ia.h.y >> s) & 0x01010101u) << 4; a3 |= ((ib.h.y >> s) & 0x01010101u) << 4;
+        }
+        uint2 b = make_uint2(0u, 0u);
+        if (col_ok) b = __ldg(reinterpret_cast<const uint2 *>(yq + q * 32));
+        int c[4] = { 0, 0, 0, 0 };
+        mma_s8_16x8x32(c, a0, a1, a2, a3, b.x, b.y);
+        // (d, d * sum) of columns 2t, 2t + 1 for this 32-block
+        const float4 ds = __ldg(reinterpret_cast<const float4 *>(yds + (size_t) (blk0 + q) * COLS_N + 2 * t));
+        acc[0] += dscA[q] * (ds.x * (float) c[0]) - dmnA[q] * ds.y;
+        acc[1] += dscA[q] * (ds.z * (float) c[1]) - dmnA[q] * ds.w;
+        acc[2] += dscB[q] * (ds.x * (float) c[2]) - dmnB[q] * ds.y;
+        acc[3] += dscB[q] * (ds.z * (float) c[3]) - dmnB[q] * ds.w;
+    }
+}
+
+__global__ void __launch_bounds__(COLS_NW * 32, COLS_CTAS) k_mmvq_cols(const __grid_constant__ cols_args a) {
+    __shared__ float red[2][COLS_NW][128];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    // the weights do not depend on the quantizer: the first item is in flight before the wait
+    int ni = 0, par = 0;
+    int u = blockIdx.x;
+    cols_item ia, ib, na, nb;
+    bool have = false;                   // ia / ib hold item `warp` of unit u
+    auto rows_of = [&](const cols_node & nd, int row0, const uint8_t * & pa, const uint8_t * & pb) {
+        const int ra = min(row0 + g, nd.m - 1), rb = min(row0 + g + 8, nd.m - 1);      // tail rows: recomputed, never stored
+        pa = nd.w + (size_t) ra * nd.row_stride; pb = nd.w + (size_t) rb * nd.row_stride;
+    };
+    if (u < a.units) {
+        while (ni + 1 < a.count && u >= a.nodes[ni + 1].unit0) ni++;
+        const cols_node & nd = a.nodes[ni];
+        if (warp < (nd.k >> 7)) {
+            const uint8_t * pa, * pb;
+            rows_of(nd, (u - nd.unit0) * 16, pa, pb);
+            const bool q5 = nd.type == T_Q5_K;
+            cols_load(ia, pa, warp, t, q5); cols_load(ib, pb, warp, t, q5);
+            have = true;
+        }
+    }
+    asm volatile("griddepcontrol.wait;" ::: "memory");        // the quantizer of this list has finished
+    for (; u < a.units; par ^= 1) {
+        const cols_node & nd = a.nodes[ni];
+        const int row0 = (u - nd.unit0) * 16, items = nd.k >> 7;
+        const bool q5 = nd.type == T_Q5_K;
+        const uint8_t * pa, * pb;
+        rows_of(nd, row0, pa, pb);
+        // the unit after this one (for the prefetch across the unit boundary)
+        const int u2 = u + (int) gridDim.x;
+        int ni2 = ni;
+        if (u2 < a.units) { while (ni2 + 1 < a.count && u2 >= a.nodes[ni2 + 1].unit0) ni2++; }
+        const int8_t * yq_col = nd.yq + (size_t) g * nd.k;
+        const bool col_ok = g < nd.n;
+        float acc[4] = { 0.0f, 0.0f, 0.0f, 0.0f };
+        if (!have && warp < items) { cols_load(ia, pa, warp, t, q5); cols_load(ib, pb, warp, t, q5); }
+        have = false;
+        for (int it = warp; it < items; it += COLS_NW) {
+            const int nx = it + COLS_NW;
+            if (nx < items) { cols_load(na, pa, nx, t, q5); cols_load(nb, pb, nx, t, q5); }
+            else if (u2 < a.units) {
+                const cols_node & n2 = a.nodes[ni2];
+                if (warp < (n2.k >> 7)) {
+                    const uint8_t * qa, * qb;
+                    rows_of(n2, (u2 - n2.unit0) * 16, qa, qb);
+                    const bool q52 = n2.type == T_Q5_K;
+                    cols_load(na, qa, warp, t, q52); cols_load(nb, qb, warp, t, q52);
+                    have = true;
+                }
+            }
+            cols_item_mma(ia, ib, it, g, t, q5, yq_col, nd.yds, col_ok, acc);
+            ia = na; ib = nb;
+        }
+        *reinterpret_cast<float4 *>(&red[par][warp][lane * 4]) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+        __syncthreads();
+        // red is double-buffered by unit parity: the buffer written two units later is only touched by threads
+        // that have passed the next unit's barrier, which these readers reach after their reads
+        if (threadIdx.x < 128) {
+            const int e = threadIdx.x, l = e >> 2, i = e & 3;
+            const int row = row0 + (l >> 2) + 8 * (i >> 1), col = 2 * (l & 3) + (i & 1);
+            float v = 0.0f;
+#pragma unroll
+            for (int w = 0; w < COLS_NW; w++) v += red[par][w][e];
+            if (row < nd.m && col < nd.n) nd.dst[(size_t) col * nd.m + row] = v;
+        }
+        u = u2; ni = ni2;
+    }
+}
+
+// ---------------------------------------------------------------- host side
+static inline bool cols_node_ok(int type, const uint8_t * w, int64_t row_stride, int64_t m, int64_t k, const float * x,
+                                int64_t x_stride_bytes, int64_t n) {
+    if (type != T_Q4_K && type != T_Q5_K) return false;
+    if (n < 2 || n > COLS_N || m < 1 || k < 256 || k % 256 != 0) return false;
+    if (m >= (int64_t) 1 << 31 || k >= (int64_t) 1 << 24) return false;
+    if ((reinterpret_cast<uintptr_t>(w) & 15) || (row_stride & 15) || (reinterpret_cast<uintptr_t>(x) & 3) || (x_stride_bytes & 3)) return false;
+    return row_stride >= k / 256 * (type == T_Q5_K ? 176 : 144);
+}
+static inline size_t cols_ws_bytes(int64_t k, int64_t n) {
+    return (((size_t) n * k + 127) & ~(size_t) 127) + (((size_t) (k / 32) * COLS_N * sizeof(float2) + 127) & ~(size_t) 127);
+}
+
+struct cols_builder {
+    cols_args args;
+    cols_builder() { reset(); }
+    void reset() { args.count = 0; args.units = 0; args.kmax = 0; args.pad = 0; }
+    bool full() const { return args.count >= COLS_MAX_NODES; }
+    bool empty() const { return args.count == 0; }
+    bool add(int type, const uint8_t * w, int64_t row_stride, int64_t m, int64_t k, const float * x, int64_t x_stride_bytes,
+             int64_t n, float * dst, ws_cursor & cur) {
+        cols_node & nd = args.nodes[args.count];
+        const cols_node * prev = args.count > 0 ? &args.nodes[args.count - 1] : nullptr;
+        if (prev && prev->x == x && prev->k == k && prev->n == n && prev->x_stride == (int) (x_stride_bytes / 4)) {
+            nd.yq = prev->yq; nd.yds = prev->yds; nd.quantize = 0;     // same activations as the previous node (gate/up, q/k/v)
+        } else {
+            const size_t need = cols_ws_bytes(k, n);
+            if (need > cur.left) return false;
+            nd.yq = reinterpret_cast<int8_t *>(cur.p);
+            nd.yds = reinterpret_cast<float2 *>(cur.p + (((size_t) n * k + 127) & ~(size_t) 127));
+            nd.quantize = 1; cur.p += need; cur.left -= need;
+        }
+        nd.w = w; nd.x = x; nd.dst = dst; nd.row_stride = row_stride; nd.m = (int) m; nd.k = (int) k; nd.n = (int) n;
+        nd.x_stride = (int) (x_stride_bytes / 4); nd.unit0 = args.units; nd.type = (unsigned char) type; nd.pad[0] = nd.pad[1] = 0;
+        args.units += (int) ((m + 15) / 16);
+        if (nd.k > args.kmax) args.kmax = nd.k;
+        args.count++;
+        return true;
+    }
+};
+
+static int cols_launch(cols_builder & cb, cudaStream_t st) {
+    if (cb.empty()) return B200_OK;
+    const dev_caps & caps = current_caps();
+    cols_args & a = cb.args;
+    static const int pdl = env_int("GGML_B200_FUSED_PDL", 1);
+    {
+        const dim3 grid((unsigned) ceil_div(a.kmax / 32, 8), (unsigned) a.count, COLS_N);
+        k_quantize_cols<<<grid, 256, 0, st>>>(a);
+        b200_count_launch(1);
+    }
+    int ctas = caps.sm_count * COLS_CTAS;
+    if (ctas > a.units) ctas = a.units;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned) ctas); cfg.blockDim = dim3(COLS_NW * 32);
+    cfg.dynamicSmemBytes = 0; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, k_mmvq_cols, a);
+    if (e != cudaSuccess) return -(int) e;
+    b200_count_launch(1);
+    return B200_OK;
+}
+
+} // namespace b200

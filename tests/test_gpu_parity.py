@@ -359,6 +359,53 @@ def test_mul_mat_batch_matches_single_calls(kern, oracle):
         assert np.array_equal(u32(single.cpu().numpy().reshape(-1)), u32(y.cpu().numpy().reshape(-1))), (t, m, k)
 
 
+@pytest.mark.parametrize("n", [2, 3, 4, 8])
+def test_mul_mat_batch_few_columns(kern, oracle, n):
+    """decode at batch n: Q4_K / Q5_K nodes with 2..8 columns go to the MMA list kernel (mmvq_cols.cuh); the other
+    formats ride the persistent launch as one entry per column (same weights, L2-resident for the later
+    columns), where each column equals the same column computed alone (n = 1 list) bit for bit.  All within
+    the NMSE bound of the oracle.  Column stride of x is padded (nb_b[1] > 4 k)."""
+    import b200
+    import torch
+    mats = [("q4_K", 300, 4096), ("q6_K", 130, 1024), ("q8_0", 96, 2048), ("q5_K", 4096, 1024), ("q4_0", 64, 4096),
+            ("q4_K", 17, 256), ("q5_K", 33, 11008), ("q4_K", 4096, 14336)]
+    c0 = kern.launch_count()
+    for i, (t, m, k) in enumerate(mats):
+        w_np = random_blocks(t, m, k, seed=40 + i)
+        w = dev_blocks(kern, w_np)
+        pad = 32
+        x_np = np.random.default_rng(50 + i).uniform(-1, 1, size=(n, k + pad)).astype(np.float32)
+        x = kern.to_device(x_np)
+        y = torch.zeros((n, m), dtype=torch.float32, device=kern.device)
+        nodes = (b200.MulMatNode * 1)(b200.mul_mat_node(t, w.data_ptr(), m, k, x.data_ptr(), n, y.data_ptr(), b_row_stride=4 * (k + pad)))
+        kern.mul_mat_batch(nodes)
+        got = y.cpu().numpy()
+        want = oracle.mul_mat(t, w_np, m, k, np.ascontiguousarray(x_np[:, :k]), mode=1)
+        assert oracle.nmse(want, got) <= NMSE_ORACLE, (t, m, k, n)
+        if t in ("q4_K", "q5_K"):
+            # the MMA list kernel (mmvq_cols.cuh): a column's value depends on that column alone -- the first two
+            # columns computed as an n = 2 node give the same bits; and the result is reproducible
+            y2 = torch.zeros((2, m), dtype=torch.float32, device=kern.device)
+            kern.mul_mat_batch((b200.MulMatNode * 1)(b200.mul_mat_node(t, w.data_ptr(), m, k, x.data_ptr(), 2, y2.data_ptr(), b_row_stride=4 * (k + pad))))
+            assert np.array_equal(u32(y2.cpu().numpy().reshape(-1)), u32(got[:2].reshape(-1))), (t, m, k, n)
+            y.zero_()
+            kern.mul_mat_batch(nodes)
+            assert np.array_equal(u32(y.cpu().numpy().reshape(-1)), u32(got.reshape(-1))), (t, m, k, n)
+        elif n <= 4:
+            for c in range(n):
+                y1 = torch.zeros((1, m), dtype=torch.float32, device=kern.device)
+                xc = kern.to_device(np.ascontiguousarray(x_np[c:c + 1, :k]))
+                one = (b200.MulMatNode * 2)(b200.mul_mat_node(t, w.data_ptr(), m, k, xc.data_ptr(), 1, y1.data_ptr()),
+                                            b200.mul_mat_node(t, w.data_ptr(), m, k, xc.data_ptr(), 1, y1.data_ptr()))
+                os.environ["GGML_B200_BATCH_SINGLE"] = "1"
+                try:
+                    kern.mul_mat_batch((b200.MulMatNode * 1)(one[0]))
+                finally:
+                    del os.environ["GGML_B200_BATCH_SINGLE"]
+                assert np.array_equal(u32(y1.cpu().numpy().reshape(-1)), u32(got[c])), (t, m, k, n, c)
+    assert kern.launch_count() > c0
+
+
 def _batch_nodes(kern, mats, seed0=0, shared_x=False):
     import b200
     import torch
