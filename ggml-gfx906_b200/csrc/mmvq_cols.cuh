@@ -10,18 +10,23 @@
 //     g + 8 of a 32-byte quant chunk -- two words per row, whose low / high nibbles are the sub-blocks 2j / 2j+1;
 //   * activations are quantized once per list to int8 columns + (d, d * sum) pairs per 32-block (q8_1 arithmetic),
 //     and read as B fragments straight from global memory (they stay in L1/L2: n x k bytes);
-//   * work unit = (node, 16-row tile), dealt round-robin to a grid of 3 CTAs per SM; the 8 warps of a CTA split K
-//     in 128-weight items (software-prefetched one item ahead), partial 16x8 tiles meet in shared memory and are
-//     added in fixed warp order: a row's value does not depend on the grid.
-// No shared-memory staging of the weights: a tile row's 128-weight item is 64 contiguous bytes (two full sectors),
-// and the CTA's warps walk the same 16 rows together.
+//   * work unit = (node, 16-row tile), dealt round-robin to two CTAs per SM; the 8 warps of a CTA split K in
+//     256-weight super-blocks (software-prefetched one ahead, across unit boundaries), partial 16x8 tiles meet in
+//     shared memory and are added in fixed warp order: a row's value does not depend on the grid.
+// No shared-memory staging of the weights yet: the warps' row-strided 8-byte loads cost ~80 L1 wavefronts per
+// 16-row super-block column, which (with the activation fragment loads) bounds this kernel at ~2 TB/s -- 3.7x the
+// tokens/s of the one-column kernel at batch 8; staging the tiles through the TMA ring of mmvq_batch.cuh is next.
 #pragma once
 #include "mmvq_batch.cuh"
 
 namespace b200 {
 
-constexpr int COLS_NW        = 8;      // warps per CTA
-constexpr int COLS_CTAS      = 3;      // CTAs per SM (register budget 85 per thread)
+#ifndef B200_COLS_NW
+#define B200_COLS_NW 8
+#define B200_COLS_CTAS 2
+#endif
+constexpr int COLS_NW        = B200_COLS_NW;     // warps per CTA
+constexpr int COLS_CTAS      = B200_COLS_CTAS;   // CTAs per SM (128 registers per thread: a super-block pair in use + one in flight)
 constexpr int COLS_MAX_NODES = 384;    // 72 B each in the kernel parameter block (27 KB)
 constexpr int COLS_N         = 8;      // columns of the MMA tile
 
@@ -29,7 +34,7 @@ struct cols_node {
     const uint8_t * w;        // weights, rows of k4 super-blocks
     const float   * x;        // activations [n][x_stride floats]
     float         * dst;      // [n][m]
-    int8_t        * yq;       // workspace: int8 [n][k]
+    int8_t        * yq;       // workspace: int8 [k / 32][8][32] (the 8 columns of a 32-block side by side: a B-fragment load touches 2 lines)
     float2        * yds;      // workspace: (d, d * sum) [k / 32][8]
     int64_t row_stride;
     int   m, k, n, x_stride, unit0;     // unit0: index of this node's first 16-row tile in the launch
@@ -60,7 +65,7 @@ __global__ void __launch_bounds__(256) k_quantize_cols(const __grid_constant__ c
     const float v  = roundf(__fmul_rn(x, id));
     const int   qi = fabsf(v) < 2147483648.0f ? (int) v : (int) 0x80000000;
     const int   q8 = (int) (int8_t) (qi & 0xFF);
-    nd.yq[(size_t) c * nd.k + kb * 32 + lane] = (int8_t) q8;
+    nd.yq[((size_t) kb * COLS_N + c) * 32 + lane] = (int8_t) q8;
     int sum = q8;
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) sum += __shfl_xor_sync(0xFFFFFFFFu, sum, off);
@@ -91,18 +96,18 @@ __device__ __forceinline__ uint4 ldg_stream128(const void * p) {
 // The words of one 128-weight item (half a super-block) of one row that lane (g, t) needs.  The MMA's k order
 // inside a 32-block is free as long as A and B agree: lane t takes bytes 8t..8t+7 of the 32-byte quant chunk
 // (one 8-byte load) as its k slots 4t..4t+3 and 16+4t..16+4t+3, and the same bytes of the activation block.
-struct cols_item {
+struct cols_item {            // one 256-weight super-block of one row, as lane (g, t) needs it
     uint4 hdr;                // d, dmin (f16 x 2) + 12 scale bytes
-    uint2 q[2];               // [quant chunk of the item] bytes 8t..8t+7
+    uint2 q[4];               // [32-byte quant chunk] bytes 8t..8t+7
     uint2 h;                  // Q5_K: high-bit bytes 8t..8t+7
 };
 
 __device__ __forceinline__ void cols_load(cols_item & it, const uint8_t * row, int item, int t, bool q5) {
-    const uint8_t * blk = row + (size_t) (item >> 1) * (q5 ? 176 : 144);
+    const uint8_t * blk = row + (size_t) item * (q5 ? 176 : 144);
     it.hdr = ldg_stream128(blk);
-    const uint8_t * qs = blk + (q5 ? 48 : 16) + (item & 1) * 64 + 8 * t;
-    it.q[0] = ldg_stream64(qs);
-    it.q[1] = ldg_stream64(qs + 32);
+    const uint8_t * qs = blk + (q5 ? 48 : 16) + 8 * t;
+#pragma unroll
+    for (int p = 0; p < 4; p++) it.q[p] = ldg_stream64(qs + 32 * p);
     if (q5) it.h = ldg_stream64(blk + 16 + 8 * t);
 }
 
@@ -122,17 +127,21 @@ __device__ __forceinline__ void cols_scales(const uint4 & hdr, int half, float (
     }
 }
 
+// One super-block of rows g and g + 8 against the 8 columns: 8 MMAs (one per 32-weight sub-block), block scales
+// applied to the 16x8 int32 result.  (Requesting the activation fragments of a whole block up front was measured
+// slower: the registers they hold cost more than the L1 latency they hide.)
 __device__ __forceinline__ void cols_item_mma(const cols_item & ia, const cols_item & ib, int item, int g, int t, bool q5,
                                               const int8_t * yq_col, const float2 * yds, bool col_ok, float (&acc)[4]) {
-    const int half = item & 1;
+#pragma unroll
+  for (int half = 0; half < 2; half++) {
     float dscA[4], dmnA[4], dscB[4], dmnB[4];
     cols_scales(ia.hdr, half, dscA, dmnA);
     cols_scales(ib.hdr, half, dscB, dmnB);
-    const int blk0 = (item >> 1) * 8 + half * 4;                       // first 32-block of the item
-    const int8_t * yq = yq_col + (size_t) blk0 * 32 + 8 * t;
+    const int blk0 = item * 8 + half * 4;                              // first 32-block of this half
+    const int8_t * yq = yq_col + (size_t) blk0 * (32 * COLS_N) + 8 * t;
 #pragma unroll
     for (int q = 0; q < 4; q++) {
-        const int p = q >> 1, sh = (q & 1) * 4;
+        const int p = half * 2 + (q >> 1), sh = (q & 1) * 4;
         uint32_t a0 = (ia.q[p].x >> sh) & 0x0F0F0F0Fu, a1 = (ib.q[p].x >> sh) & 0x0F0F0F0Fu;
         uint32_t a2 = (ia.q[p].y >> sh) & 0x0F0F0F0Fu, a3 = (ib.q[p].y >> sh) & 0x0F0F0F0Fu;
         if (q5) {
@@ -141,7 +150,7 @@ __device__ __forceinline__ void cols_item_mma(const cols_item & ia, const cols_i
             a2 |= ((ia.h.y >> s) & 0x01010101u) << 4; a3 |= ((ib.h.y >> s) & 0x01010101u) << 4;
         }
         uint2 b = make_uint2(0u, 0u);
-        if (col_ok) b = __ldg(reinterpret_cast<const uint2 *>(yq + q * 32));
+        if (col_ok) b = __ldg(reinterpret_cast<const uint2 *>(yq + q * (32 * COLS_N)));
         int c[4] = { 0, 0, 0, 0 };
         mma_s8_16x8x32(c, a0, a1, a2, a3, b.x, b.y);
         // (d, d * sum) of columns 2t, 2t + 1 for this 32-block
@@ -151,6 +160,7 @@ __device__ __forceinline__ void cols_item_mma(const cols_item & ia, const cols_i
         acc[2] += dscB[q] * (ds.x * (float) c[2]) - dmnB[q] * ds.y;
         acc[3] += dscB[q] * (ds.z * (float) c[3]) - dmnB[q] * ds.w;
     }
+  }
 }
 
 __global__ void __launch_bounds__(COLS_NW * 32, COLS_CTAS) k_mmvq_cols(const __grid_constant__ cols_args a) {
@@ -168,7 +178,7 @@ __global__ void __launch_bounds__(COLS_NW * 32, COLS_CTAS) k_mmvq_cols(const __g
     if (u < a.units) {
         while (ni + 1 < a.count && u >= a.nodes[ni + 1].unit0) ni++;
         const cols_node & nd = a.nodes[ni];
-        if (warp < (nd.k >> 7)) {
+        if (warp < (nd.k >> 8)) {
             const uint8_t * pa, * pb;
             rows_of(nd, (u - nd.unit0) * 16, pa, pb);
             const bool q5 = nd.type == T_Q5_K;
@@ -179,7 +189,7 @@ __global__ void __launch_bounds__(COLS_NW * 32, COLS_CTAS) k_mmvq_cols(const __g
     asm volatile("griddepcontrol.wait;" ::: "memory");        // the quantizer of this list has finished
     for (; u < a.units; par ^= 1) {
         const cols_node & nd = a.nodes[ni];
-        const int row0 = (u - nd.unit0) * 16, items = nd.k >> 7;
+        const int row0 = (u - nd.unit0) * 16, items = nd.k >> 8;
         const bool q5 = nd.type == T_Q5_K;
         const uint8_t * pa, * pb;
         rows_of(nd, row0, pa, pb);
@@ -187,7 +197,7 @@ __global__ void __launch_bounds__(COLS_NW * 32, COLS_CTAS) k_mmvq_cols(const __g
         const int u2 = u + (int) gridDim.x;
         int ni2 = ni;
         if (u2 < a.units) { while (ni2 + 1 < a.count && u2 >= a.nodes[ni2 + 1].unit0) ni2++; }
-        const int8_t * yq_col = nd.yq + (size_t) g * nd.k;
+        const int8_t * yq_col = nd.yq + g * 32;
         const bool col_ok = g < nd.n;
         float acc[4] = { 0.0f, 0.0f, 0.0f, 0.0f };
         if (!have && warp < items) { cols_load(ia, pa, warp, t, q5); cols_load(ib, pb, warp, t, q5); }
@@ -197,7 +207,7 @@ __global__ void __launch_bounds__(COLS_NW * 32, COLS_CTAS) k_mmvq_cols(const __g
             if (nx < items) { cols_load(na, pa, nx, t, q5); cols_load(nb, pb, nx, t, q5); }
             else if (u2 < a.units) {
                 const cols_node & n2 = a.nodes[ni2];
-                if (warp < (n2.k >> 7)) {
+                if (warp < (n2.k >> 8)) {
                     const uint8_t * qa, * qb;
                     rows_of(n2, (u2 - n2.unit0) * 16, qa, qb);
                     const bool q52 = n2.type == T_Q5_K;
@@ -234,7 +244,8 @@ static inline bool cols_node_ok(int type, const uint8_t * w, int64_t row_stride,
     return row_stride >= k / 256 * (type == T_Q5_K ? 176 : 144);
 }
 static inline size_t cols_ws_bytes(int64_t k, int64_t n) {
-    return (((size_t) n * k + 127) & ~(size_t) 127) + (((size_t) (k / 32) * COLS_N * sizeof(float2) + 127) & ~(size_t) 127);
+    (void) n;
+    return (((size_t) COLS_N * k + 127) & ~(size_t) 127) + (((size_t) (k / 32) * COLS_N * sizeof(float2) + 127) & ~(size_t) 127);
 }
 
 struct cols_builder {
@@ -253,7 +264,7 @@ struct cols_builder {
             const size_t need = cols_ws_bytes(k, n);
             if (need > cur.left) return false;
             nd.yq = reinterpret_cast<int8_t *>(cur.p);
-            nd.yds = reinterpret_cast<float2 *>(cur.p + (((size_t) n * k + 127) & ~(size_t) 127));
+            nd.yds = reinterpret_cast<float2 *>(cur.p + (((size_t) COLS_N * k + 127) & ~(size_t) 127));
             nd.quantize = 1; cur.p += need; cur.left -= need;
         }
         nd.w = w; nd.x = x; nd.dst = dst; nd.row_stride = row_stride; nd.m = (int) m; nd.k = (int) k; nd.n = (int) n;

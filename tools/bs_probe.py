@@ -8,7 +8,8 @@ import b200, bench, workloads
 
 kern = b200.Kernels()
 peak, _ = bench.hbm_peak()
-mats = workloads.llama3_8b_q4_k_m_stack()
+stack_name = os.environ.get("BS_STACK", "l3mix")
+mats = workloads.llama3_8b_q4_k_m_stack() if stack_name == "l3mix" else workloads.llama2_7b_stack(stack_name)
 ws = [bench.random_blocks_device(torch, kern.device, mt.type, mt.m, mt.k, i) for i, mt in enumerate(mats)]
 wbytes = sum(mt.weight_bytes for mt in mats)
 out = {}
@@ -27,6 +28,6 @@ for n in [int(a) for a in sys.argv[1:]] or [1, 2, 4, 8]:
     sec = bench.timed_loop(torch, g.replay, 10) / 10
     out[f"bs={n}"] = {"launches": launches, "ms_per_pass": round(sec * 1e3, 3), "weight_GBps": round(wbytes / sec / 1e9, 1),
                       "frac_of_measured_peak": round(wbytes / sec / 1e9 / peak, 3), "tok_per_s": round(n / sec, 1)}
-    print(f"bs={n}: {launches} launches/pass, {sec*1e3:.3f} ms/pass, {wbytes/sec/1e9:.0f} GB/s on weight bytes "
+    print(f"{stack_name} bs={n}: {launches} launches/pass, {sec*1e3:.3f} ms/pass, {wbytes/sec/1e9:.0f} GB/s on weight bytes "
           f"({wbytes/sec/1e9/peak*100:.1f}% of measured peak), {n/sec:.0f} tok/s", flush=True)
 json.dump(out, open(os.path.join(ROOT, "gpurun_out", "bs_probe.json"), "w"), indent=1)
