@@ -314,6 +314,38 @@ def measure_support(torch, kern, peak):
     return out
 
 
+def measure_decode_batches(torch, kern, stack, peak):
+    """Secondary figure: the same stack (same resident weights) with n = 2, 4, 8 activation columns per MUL_MAT
+    (decode at batch n, BASELINE configs[3]): one b200_mul_mat_batch list per pass (Q4_K / Q5_K: the MMA list
+    kernel of mmvq_cols.cuh), CUDA graph replay; GB/s on the weight bytes and tokens/s."""
+    import b200
+    out = {}
+    mats = stack.mats
+    wbytes = stack.local_weight_bytes
+    for n in (2, 4, 8):
+        xs = [torch.rand((n, mt.k), device=kern.device) * 2 - 1 for mt in mats]
+        ys = [torch.empty((n, hi - lo), dtype=torch.float32, device=kern.device) for (lo, hi) in stack.rows]
+        nodes = (b200.MulMatNode * len(mats))(*[
+            b200.mul_mat_node(mt.type, w.data_ptr(), hi - lo, mt.k, x.data_ptr(), n, y.data_ptr(), const_weights=True)
+            for mt, w, x, y, (lo, hi) in zip(mats, stack.weights, xs, ys, stack.rows)])
+        ws = torch.empty(int(kern.lib.b200_mul_mat_batch_workspace_size(nodes, len(mats))) + 256, dtype=torch.uint8, device=kern.device)
+        fn = lambda: kern.mul_mat_batch(nodes, ws=ws)    # noqa: E731
+        fn()
+        torch.cuda.synchronize()
+        c0 = kern.launch_count()
+        fn()
+        launches = kern.launch_count() - c0
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            fn()
+        g.replay()
+        sec = timed_loop(torch, g.replay, 10) / 10
+        out[f"n={n}"] = {"ms_per_pass": round(sec * 1e3, 4), "launches": launches, "weight_GBps": round(wbytes / sec / 1e9, 1),
+                         "frac": round(wbytes / sec / 1e9 / peak, 3), "tok_s": round(n / sec, 1)}
+        del g, xs, ys, ws
+    return out
+
+
 # ------------------------------------------------------------------------------------- the CPU reference
 def cpu_reference(budget_s=12.0, sample_layers=4, steps=None, warmup=1):
     """The reference's own CPU implementation of the path (ggml-cpu, unmodified, compiled from
@@ -553,6 +585,10 @@ def main():
             line["support_kernels"] = measure_support(torch, kern, peak)
         except Exception as e:                   # noqa: BLE001
             line["support_kernels"] = {"error": str(e)[:200]}
+        try:
+            line["decode_batches"] = measure_decode_batches(torch, kern, stack, peak)
+        except Exception as e:                   # noqa: BLE001
+            line["decode_batches"] = {"error": str(e)[:200]}
         _, info = cpu_reference()
         line["cpu_baseline"] = {k: info[k] for k in ("value", "unit", "cores", "kind", "sample")}
     if rank == 0:
