@@ -29,6 +29,10 @@ constexpr int COLS_NW        = B200_COLS_NW;     // warps per CTA
 constexpr int COLS_CTAS      = B200_COLS_CTAS;   // CTAs per SM (128 registers per thread: a super-block pair in use + one in flight)
 constexpr int COLS_MAX_NODES = 384;    // 72 B each in the kernel parameter block (27 KB)
 constexpr int COLS_N         = 8;      // columns of the MMA tile
+#ifndef B200_COLS_PREFETCH_UNITS
+#define B200_COLS_PREFETCH_UNITS 2
+#endif
+constexpr int COLS_PREFETCH_UNITS = B200_COLS_PREFETCH_UNITS;   // tiles ahead of the current one that are requested into L2
 
 struct cols_node {
     const uint8_t * w;        // weights, rows of k4 super-blocks
@@ -93,6 +97,11 @@ __device__ __forceinline__ uint4 ldg_stream128(const void * p) {
     return v;
 }
 
+// HBM -> L2 prefetch of a whole weight row (16-byte aligned, a multiple of 16 bytes): no registers, no completion
+__device__ __forceinline__ void l2_prefetch_bulk(const void * p, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(p), "r"(bytes) : "memory");
+}
+
 // The words of one 128-weight item (half a super-block) of one row that lane (g, t) needs.  The MMA's k order
 // inside a 32-block is free as long as A and B agree: lane t takes bytes 8t..8t+7 of the 32-byte quant chunk
 // (one 8-byte load) as its k slots 4t..4t+3 and 16+4t..16+4t+3, and the same bytes of the activation block.
@@ -127,18 +136,25 @@ __device__ __forceinline__ void cols_scales(const uint4 & hdr, int half, float (
     }
 }
 
-// One super-block of rows g and g + 8 against the 8 columns: 8 MMAs (one per 32-weight sub-block), block scales
-// applied to the 16x8 int32 result.  (Requesting the activation fragments of a whole block up front was measured
-// slower: the registers they hold cost more than the L1 latency they hide.)
-__device__ __forceinline__ void cols_item_mma(const cols_item & ia, const cols_item & ib, int item, int g, int t, bool q5,
-                                              const int8_t * yq_col, const float2 * yds, bool col_ok, float (&acc)[4]) {
+// B fragments and (d, d * sum) pairs of four consecutive 32-blocks (half a super-block), requested together
+struct cols_acts { uint2 b[4]; float4 ds[4]; };
+__device__ __forceinline__ void cols_load_acts(cols_acts & y, const int8_t * yq_col, const float2 * yds, int blk0, int t, bool col_ok) {
+    const int8_t * yq = yq_col + (size_t) blk0 * (32 * COLS_N) + 8 * t;
 #pragma unroll
-  for (int half = 0; half < 2; half++) {
+    for (int q = 0; q < 4; q++) {
+        y.b[q] = make_uint2(0u, 0u);
+        if (col_ok) y.b[q] = __ldg(reinterpret_cast<const uint2 *>(yq + q * (32 * COLS_N)));
+        y.ds[q] = __ldg(reinterpret_cast<const float4 *>(yds + (size_t) (blk0 + q) * COLS_N + 2 * t));   // columns 2t, 2t + 1
+    }
+}
+
+// Half a super-block of rows g and g + 8 against the 8 columns: 4 MMAs (one per 32-weight sub-block), block
+// scales applied to the 16x8 int32 result.
+__device__ __forceinline__ void cols_half_mma(const cols_item & ia, const cols_item & ib, const int half, bool q5,
+                                              const cols_acts & y, float (&acc)[4]) {
     float dscA[4], dmnA[4], dscB[4], dmnB[4];
     cols_scales(ia.hdr, half, dscA, dmnA);
     cols_scales(ib.hdr, half, dscB, dmnB);
-    const int blk0 = item * 8 + half * 4;                              // first 32-block of this half
-    const int8_t * yq = yq_col + (size_t) blk0 * (32 * COLS_N) + 8 * t;
 #pragma unroll
     for (int q = 0; q < 4; q++) {
         const int p = half * 2 + (q >> 1), sh = (q & 1) * 4;
@@ -149,74 +165,58 @@ __device__ __forceinline__ void cols_item_mma(const cols_item & ia, const cols_i
             a0 |= ((ia.h.x >> s) & 0x01010101u) << 4; a1 |= ((ib.h.x >> s) & 0x01010101u) << 4;
             a2 |= ((ia.h.y >> s) & 0x01010101u) << 4; a3 |= ((ib.h.y >> s) & 0x01010101u) << 4;
         }
-        uint2 b = make_uint2(0u, 0u);
-        if (col_ok) b = __ldg(reinterpret_cast<const uint2 *>(yq + q * (32 * COLS_N)));
         int c[4] = { 0, 0, 0, 0 };
-        mma_s8_16x8x32(c, a0, a1, a2, a3, b.x, b.y);
-        // (d, d * sum) of columns 2t, 2t + 1 for this 32-block
-        const float4 ds = __ldg(reinterpret_cast<const float4 *>(yds + (size_t) (blk0 + q) * COLS_N + 2 * t));
+        mma_s8_16x8x32(c, a0, a1, a2, a3, y.b[q].x, y.b[q].y);
+        const float4 ds = y.ds[q];
         acc[0] += dscA[q] * (ds.x * (float) c[0]) - dmnA[q] * ds.y;
         acc[1] += dscA[q] * (ds.z * (float) c[1]) - dmnA[q] * ds.w;
         acc[2] += dscB[q] * (ds.x * (float) c[2]) - dmnB[q] * ds.y;
         acc[3] += dscB[q] * (ds.z * (float) c[3]) - dmnB[q] * ds.w;
     }
-  }
 }
 
 __global__ void __launch_bounds__(COLS_NW * 32, COLS_CTAS) k_mmvq_cols(const __grid_constant__ cols_args a) {
     __shared__ float red[2][COLS_NW][128];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
-    // the weights do not depend on the quantizer: the first item is in flight before the wait
     int ni = 0, par = 0;
     int u = blockIdx.x;
-    cols_item ia, ib, na, nb;
-    bool have = false;                   // ia / ib hold item `warp` of unit u
-    auto rows_of = [&](const cols_node & nd, int row0, const uint8_t * & pa, const uint8_t * & pb) {
-        const int ra = min(row0 + g, nd.m - 1), rb = min(row0 + g + 8, nd.m - 1);      // tail rows: recomputed, never stored
-        pa = nd.w + (size_t) ra * nd.row_stride; pb = nd.w + (size_t) rb * nd.row_stride;
+    // Weights reach the SM in two steps: whole tiles are requested into L2 a few units ahead by bulk prefetches
+    // (one weight row per thread 0..15; no registers, ~150 KB in flight per SM), and a warp's loads of its
+    // super-block then hit L2.  The registers go to the activation fragments instead, which are requested half a
+    // super-block ahead of their MMAs (ncu: the long-scoreboard stalls sat on the MMAs' B operands).
+    auto prefetch_unit = [&](int up, int & nip) {
+        if (up >= a.units) return;
+        while (nip + 1 < a.count && up >= a.nodes[nip + 1].unit0) nip++;
+        const cols_node & np = a.nodes[nip];
+        const int row = (up - np.unit0) * 16 + (int) threadIdx.x;
+        if (threadIdx.x < 16 && row < np.m)
+            l2_prefetch_bulk(np.w + (size_t) row * np.row_stride, (uint32_t) ((np.k >> 8) * (np.type == T_Q5_K ? 176 : 144)));
     };
-    if (u < a.units) {
-        while (ni + 1 < a.count && u >= a.nodes[ni + 1].unit0) ni++;
-        const cols_node & nd = a.nodes[ni];
-        if (warp < (nd.k >> 8)) {
-            const uint8_t * pa, * pb;
-            rows_of(nd, (u - nd.unit0) * 16, pa, pb);
-            const bool q5 = nd.type == T_Q5_K;
-            cols_load(ia, pa, warp, t, q5); cols_load(ib, pb, warp, t, q5);
-            have = true;
-        }
-    }
+    const int PD = COLS_PREFETCH_UNITS;
+    int nip = 0;
+    for (int d = 0; d < PD; d++) prefetch_unit(u + d * (int) gridDim.x, nip);
     asm volatile("griddepcontrol.wait;" ::: "memory");        // the quantizer of this list has finished
-    for (; u < a.units; par ^= 1) {
+    for (; u < a.units; u += (int) gridDim.x, par ^= 1) {
+        while (ni + 1 < a.count && u >= a.nodes[ni + 1].unit0) ni++;
         const cols_node & nd = a.nodes[ni];
         const int row0 = (u - nd.unit0) * 16, items = nd.k >> 8;
         const bool q5 = nd.type == T_Q5_K;
-        const uint8_t * pa, * pb;
-        rows_of(nd, row0, pa, pb);
-        // the unit after this one (for the prefetch across the unit boundary)
-        const int u2 = u + (int) gridDim.x;
-        int ni2 = ni;
-        if (u2 < a.units) { while (ni2 + 1 < a.count && u2 >= a.nodes[ni2 + 1].unit0) ni2++; }
+        const int ra = min(row0 + g, nd.m - 1), rb = min(row0 + g + 8, nd.m - 1);      // tail rows: recomputed, never stored
+        const uint8_t * pa = nd.w + (size_t) ra * nd.row_stride;
+        const uint8_t * pb = nd.w + (size_t) rb * nd.row_stride;
+        prefetch_unit(u + PD * (int) gridDim.x, nip);
         const int8_t * yq_col = nd.yq + g * 32;
+        const float2 * yds = nd.yds;
         const bool col_ok = g < nd.n;
         float acc[4] = { 0.0f, 0.0f, 0.0f, 0.0f };
-        if (!have && warp < items) { cols_load(ia, pa, warp, t, q5); cols_load(ib, pb, warp, t, q5); }
-        have = false;
         for (int it = warp; it < items; it += COLS_NW) {
-            const int nx = it + COLS_NW;
-            if (nx < items) { cols_load(na, pa, nx, t, q5); cols_load(nb, pb, nx, t, q5); }
-            else if (u2 < a.units) {
-                const cols_node & n2 = a.nodes[ni2];
-                if (warp < (n2.k >> 8)) {
-                    const uint8_t * qa, * qb;
-                    rows_of(n2, (u2 - n2.unit0) * 16, qa, qb);
-                    const bool q52 = n2.type == T_Q5_K;
-                    cols_load(na, qa, warp, t, q52); cols_load(nb, qb, warp, t, q52);
-                    have = true;
-                }
-            }
-            cols_item_mma(ia, ib, it, g, t, q5, yq_col, nd.yds, col_ok, acc);
-            ia = na; ib = nb;
+            cols_item ia, ib;
+            cols_acts y0, y1;
+            cols_load(ia, pa, it, t, q5); cols_load(ib, pb, it, t, q5);
+            cols_load_acts(y0, yq_col, yds, it * 8, t, col_ok);
+            cols_load_acts(y1, yq_col, yds, it * 8 + 4, t, col_ok);
+            cols_half_mma(ia, ib, 0, q5, y0, acc);
+            cols_half_mma(ia, ib, 1, q5, y1, acc);
         }
         *reinterpret_cast<float4 *>(&red[par][warp][lane * 4]) = make_float4(acc[0], acc[1], acc[2], acc[3]);
         __syncthreads();
@@ -230,7 +230,6 @@ __global__ void __launch_bounds__(COLS_NW * 32, COLS_CTAS) k_mmvq_cols(const __g
             for (int w = 0; w < COLS_NW; w++) v += red[par][w][e];
             if (row < nd.m && col < nd.n) nd.dst[(size_t) col * nd.m + row] = v;
         }
-        u = u2; ni = ni2;
     }
 }
 
