@@ -45,6 +45,7 @@ struct cols_node {
     unsigned char type, quantize, pad[2];
 };
 static_assert(sizeof(cols_node) == 72, "cols_node is part of the kernel parameter block");
+static_assert(COLS_NW == 8, "k_mmvq_cols<8> splits K over the 8 warps of a CTA");
 
 struct cols_args {
     int count, units, kmax, pad;
@@ -175,11 +176,18 @@ __device__ __forceinline__ void cols_half_mma(const cols_item & ia, const cols_i
     }
 }
 
+// KS = 8 (default): the 8 warps of a CTA split K of one tile, partial tiles meet in shared memory;
+// KS = 1 (tuning variant): every warp owns whole tiles -- no barrier, no shared-memory reduction.
+// A row's value does not depend on the grid in either; the two differ in the f32 summation order over K.
+template <int KS>
 __global__ void __launch_bounds__(COLS_NW * 32, COLS_CTAS) k_mmvq_cols(const __grid_constant__ cols_args a) {
-    __shared__ float red[2][COLS_NW][128];
+    __shared__ float red[KS > 1 ? 2 : 1][KS > 1 ? COLS_NW : 1][KS > 1 ? 128 : 1];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
     int ni = 0, par = 0;
-    int u = blockIdx.x;
+    const int ustride = KS > 1 ? (int) gridDim.x : (int) gridDim.x * COLS_NW;
+    const int kw = KS > 1 ? warp : 0;                       // this warp's first super-block of a tile, and its stride
+    const int ptid = KS > 1 ? (int) threadIdx.x : lane;     // the thread's index among those that prefetch a tile
+    int u = KS > 1 ? (int) blockIdx.x : (int) blockIdx.x * COLS_NW + warp;
     // Weights reach the SM in two steps: whole tiles are requested into L2 a few units ahead by bulk prefetches
     // (one weight row per thread 0..15; no registers, ~150 KB in flight per SM), and a warp's loads of its
     // super-block then hit L2.  The registers go to the activation fragments instead, which are requested half a
@@ -188,15 +196,26 @@ __global__ void __launch_bounds__(COLS_NW * 32, COLS_CTAS) k_mmvq_cols(const __g
         if (up >= a.units) return;
         while (nip + 1 < a.count && up >= a.nodes[nip + 1].unit0) nip++;
         const cols_node & np = a.nodes[nip];
-        const int row = (up - np.unit0) * 16 + (int) threadIdx.x;
-        if (threadIdx.x < 16 && row < np.m)
+        const int row = (up - np.unit0) * 16 + ptid;
+        if (ptid < 16 && row < np.m)
             l2_prefetch_bulk(np.w + (size_t) row * np.row_stride, (uint32_t) ((np.k >> 8) * (np.type == T_Q5_K ? 176 : 144)));
+    };
+    // KS = 1: 16 warps x whole tiles ahead would not fit L2; a warp requests 8 super-blocks (1152 B of each of its 16
+    // rows) at a time, 8 ahead of the one it works on, across tile boundaries
+    auto prefetch_chunk = [&](const cols_node & np, int row0p, int b0) {
+        const int nb = min(8, (np.k >> 8) - b0), bs = np.type == T_Q5_K ? 176 : 144;
+        if (lane < 16 && row0p + lane < np.m && nb > 0)
+            l2_prefetch_bulk(np.w + (size_t) (row0p + lane) * np.row_stride + (size_t) b0 * bs, (uint32_t) (nb * bs));
     };
     const int PD = COLS_PREFETCH_UNITS;
     int nip = 0;
-    for (int d = 0; d < PD; d++) prefetch_unit(u + d * (int) gridDim.x, nip);
+    if (KS > 1) { for (int d = 0; d < PD; d++) prefetch_unit(u + d * ustride, nip); }
+    else if (u < a.units) {
+        while (nip + 1 < a.count && u >= a.nodes[nip + 1].unit0) nip++;
+        prefetch_chunk(a.nodes[nip], (u - a.nodes[nip].unit0) * 16, 0);
+    }
     asm volatile("griddepcontrol.wait;" ::: "memory");        // the quantizer of this list has finished
-    for (; u < a.units; u += (int) gridDim.x, par ^= 1) {
+    for (; u < a.units; u += ustride, par ^= 1) {
         while (ni + 1 < a.count && u >= a.nodes[ni + 1].unit0) ni++;
         const cols_node & nd = a.nodes[ni];
         const int row0 = (u - nd.unit0) * 16, items = nd.k >> 8;
@@ -204,12 +223,17 @@ __global__ void __launch_bounds__(COLS_NW * 32, COLS_CTAS) k_mmvq_cols(const __g
         const int ra = min(row0 + g, nd.m - 1), rb = min(row0 + g + 8, nd.m - 1);      // tail rows: recomputed, never stored
         const uint8_t * pa = nd.w + (size_t) ra * nd.row_stride;
         const uint8_t * pb = nd.w + (size_t) rb * nd.row_stride;
-        prefetch_unit(u + PD * (int) gridDim.x, nip);
+        if (KS > 1) prefetch_unit(u + PD * ustride, nip);
+        else if (u + ustride < a.units) { while (nip + 1 < a.count && u + ustride >= a.nodes[nip + 1].unit0) nip++; }   // nip: the next tile's node
         const int8_t * yq_col = nd.yq + g * 32;
         const float2 * yds = nd.yds;
         const bool col_ok = g < nd.n;
         float acc[4] = { 0.0f, 0.0f, 0.0f, 0.0f };
-        for (int it = warp; it < items; it += COLS_NW) {
+        for (int it = kw; it < items; it += KS) {
+            if (KS == 1 && (it & 7) == 0) {
+                if (it + 8 < items) prefetch_chunk(nd, row0, it + 8);
+                else if (u + ustride < a.units) prefetch_chunk(a.nodes[nip], (u + ustride - a.nodes[nip].unit0) * 16, 0);
+            }
             cols_item ia, ib;
             cols_acts y0, y1;
             cols_load(ia, pa, it, t, q5); cols_load(ib, pb, it, t, q5);
@@ -217,6 +241,15 @@ __global__ void __launch_bounds__(COLS_NW * 32, COLS_CTAS) k_mmvq_cols(const __g
             cols_load_acts(y1, yq_col, yds, it * 8 + 4, t, col_ok);
             cols_half_mma(ia, ib, 0, q5, y0, acc);
             cols_half_mma(ia, ib, 1, q5, y1, acc);
+        }
+        if (KS == 1) {
+            // c fragment layout: acc[0..1] = row g, columns 2t, 2t + 1; acc[2..3] = row g + 8
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const int row = row0 + g + 8 * (i >> 1), col = 2 * t + (i & 1);
+                if (row < nd.m && col < nd.n) nd.dst[(size_t) col * nd.m + row] = acc[i];
+            }
+            continue;
         }
         *reinterpret_cast<float4 *>(&red[par][warp][lane * 4]) = make_float4(acc[0], acc[1], acc[2], acc[3]);
         __syncthreads();
@@ -294,7 +327,12 @@ static int cols_launch(cols_builder & cb, cudaStream_t st) {
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
-    const cudaError_t e = cudaLaunchKernelEx(&cfg, k_mmvq_cols, a);
+    // whole tiles per warp (GGML_B200_COLS_KS=1) measured 7 % slower than the K split even on long lists
+    // (profiles/r01o_bs_probe.txt): the per-tile barrier is not what bounds the kernel
+    static const int ks_env = env_int("GGML_B200_COLS_KS", 8);
+    const bool ks1 = ks_env == 1;
+    if (ks1) cfg.gridDim = dim3((unsigned) (caps.sm_count * COLS_CTAS));
+    const cudaError_t e = ks1 ? cudaLaunchKernelEx(&cfg, k_mmvq_cols<1>, a) : cudaLaunchKernelEx(&cfg, k_mmvq_cols<8>, a);
     if (e != cudaSuccess) return -(int) e;
     b200_count_launch(1);
     return B200_OK;
