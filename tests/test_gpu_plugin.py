@@ -102,10 +102,13 @@ def test_device_properties(host_and_backends):
     assert b"B200" in host.base.ggml_backend_dev_description(dev)
 
 
-def test_decode_graph_through_plugin_vs_ggml_cpu(host_and_backends):
-    """a per-layer GEMM graph (independent n = 1 MUL_MATs, mixed formats and shapes) through
+@pytest.mark.parametrize("n", [1, 4, 8])
+def test_decode_graph_through_plugin_vs_ggml_cpu(host_and_backends, n):
+    """a per-layer GEMM graph (independent MUL_MATs with n = 1 / 4 / 8 columns: decode at batch n, BASELINE
+    configs[3]; mixed formats and shapes) through
     ggml_backend_graph_compute on B200_0: the plugin hands the run of MUL_MAT nodes to b200_mul_mat_batch
-    (persistent list kernel for the Q4_K/Q5_K nodes, per-node kernels for the rest).  Computed four times
+    (n = 1: persistent list kernel; n > 1: the MMA list kernel for the Q4_K/Q5_K nodes, one persistent-list
+    entry per column for the rest).  Computed four times
     (eager, eager, CUDA-graph capture, replay): every pass must match ggml-cpu under the harness's NMSE gate."""
     import ggml_host
     import workloads
@@ -113,7 +116,7 @@ def test_decode_graph_through_plugin_vs_ggml_cpu(host_and_backends):
     shapes = [("q4_K", 512, 4096), ("q4_K", 512, 4096), ("q5_K", 300, 4096), ("q4_K", 1376, 4096), ("q4_K", 1376, 4096),
               ("q4_K", 512, 11008), ("q6_K", 256, 4096), ("q8_0", 128, 2048), ("q4_K", 1000, 8192)]
     mats = [workloads.Mat(f"m{i}", t, m, k) for i, (t, m, k) in enumerate(shapes)]
-    gc, gg = ggml_host.MulMatGraph(host, cpu, mats, 1), ggml_host.MulMatGraph(host, gpu, mats, 1)
+    gc, gg = ggml_host.MulMatGraph(host, cpu, mats, n), ggml_host.MulMatGraph(host, gpu, mats, n)
     try:
         rng = np.random.default_rng(77)
         for i, mt in enumerate(mats):
@@ -121,7 +124,7 @@ def test_decode_graph_through_plugin_vs_ggml_cpu(host_and_backends):
             gc.set_weight(i, w); gg.set_weight(i, w)
         for rep in range(4):
             for i, mt in enumerate(mats):
-                x = rng.uniform(-1, 1, size=(1, mt.k)).astype(np.float32)
+                x = rng.uniform(-1, 1, size=(n, mt.k)).astype(np.float32)
                 gc.set_input(i, x); gg.set_input(i, x)
             gc.compute(); gg.compute()
             for i, mt in enumerate(mats):
