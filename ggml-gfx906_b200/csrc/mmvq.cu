@@ -212,7 +212,7 @@ extern "C" size_t b200_mul_mat_batch_workspace_size(const b200_mul_mat_node * no
         if (s > need) need = s;
         if (nodes[i].ne_b[1] >= 1 && nodes[i].ne_b[1] <= B200_MMVQ_MAX_N && nodes[i].ne_a[0] > 0) {
             const size_t per_col = (size_t) nodes[i].ne_b[1] * batch_acts_record_bytes(nodes[i].ne_a[0]);
-            const size_t tile = cols_ws_bytes(nodes[i].ne_a[0], nodes[i].ne_b[1]);
+            const size_t tile = nodes[i].ne_b[1] >= 2 ? cols_ws_bytes(nodes[i].ne_a[0], nodes[i].ne_b[1]) : 0;
             acts += per_col > tile ? per_col : tile;
         }
     }
