@@ -6,16 +6,19 @@
 // list kernel issue-bound as soon as there is more than one column (measured: time = n x the one-column time even
 // with the weights in L2), so here a warp multiplies a 16-row x 32-weight sub-block by the 8 (padded) columns
 // with one mma.sync.m16n8k32.s8 and applies the block scales on the 16x8 int32 result:
-//   * the k4 nibble layout IS the A fragment: lane (g, t) needs bytes 4t..4t+3 and 16+4t..16+4t+3 of rows g and
-//     g + 8 of a 32-byte quant chunk -- two words per row, whose low / high nibbles are the sub-blocks 2j / 2j+1;
-//   * activations are quantized once per list to int8 columns + (d, d * sum) pairs per 32-block (q8_1 arithmetic),
-//     and read as B fragments straight from global memory (they stay in L1/L2: n x k bytes);
+//   * the k4 nibble layout IS the A fragment: lane (g, t) takes bytes 8t..8t+7 of a 32-byte quant chunk of rows g
+//     and g + 8 (the k order inside a 32-block is free as long as A and B agree), whose low / high nibbles are the
+//     sub-blocks 2j / 2j+1;
+//   * activations are quantized once per list to int8, the 8 columns of a 32-block side by side, + (d, d * sum)
+//     pairs per 32-block (q8_1 arithmetic), and read as B fragments from global memory (L1-resident: 10 k bytes);
 //   * work unit = (node, 16-row tile), dealt round-robin to two CTAs per SM; the 8 warps of a CTA split K in
-//     256-weight super-blocks (software-prefetched one ahead, across unit boundaries), partial 16x8 tiles meet in
-//     shared memory and are added in fixed warp order: a row's value does not depend on the grid.
-// No shared-memory staging of the weights yet: the warps' row-strided 8-byte loads cost ~80 L1 wavefronts per
-// 16-row super-block column, which (with the activation fragment loads) bounds this kernel at ~2 TB/s -- 3.7x the
-// tokens/s of the one-column kernel at batch 8; staging the tiles through the TMA ring of mmvq_batch.cuh is next.
+//     256-weight super-blocks; whole tiles are requested into L2 two units ahead by bulk prefetches, the warps'
+//     own loads then hit L2, and the registers hold the activation fragments half a super-block ahead of their
+//     MMAs; partial 16x8 tiles meet in shared memory and are added in fixed warp order: a row's value does not
+//     depend on the grid.
+// Measured (profiles/r01o_bs_probe.txt, r01p_ncu_k_mmvq_cols_summary.txt): 2.85 TB/s on the weight bytes of the
+// Llama-2-7B Q4_K stack at 8 columns (44 % of the measured HBM peak, 6100 tok/s = 4x one-column decode); issue-bound
+// (441 instructions per 16-row super-block column, 61 % issue-active with 4 warps per scheduler).
 #pragma once
 #include "mmvq_batch.cuh"
 
@@ -26,7 +29,7 @@ namespace b200 {
 #define B200_COLS_CTAS 2
 #endif
 constexpr int COLS_NW        = B200_COLS_NW;     // warps per CTA
-constexpr int COLS_CTAS      = B200_COLS_CTAS;   // CTAs per SM (128 registers per thread: a super-block pair in use + one in flight)
+constexpr int COLS_CTAS      = B200_COLS_CTAS;   // CTAs per SM (122 registers per thread; 3 or 4 CTAs measured 9 / 24 % slower)
 constexpr int COLS_MAX_NODES = 384;    // 72 B each in the kernel parameter block (27 KB)
 constexpr int COLS_N         = 8;      // columns of the MMA tile
 #ifndef B200_COLS_PREFETCH_UNITS
