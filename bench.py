@@ -194,10 +194,18 @@ class DecodeStack:
         edges = [round(i * n / chunks) for i in range(chunks + 1)]
         # balance by weight bytes rather than by node count
         total = sum(int(w.numel()) for w in self.weights)
-        edges, acc, nxt = [0], 0, 1
+        # cut points as fractions of the weight bytes: a short first and last sub-list (BENCH_E2E_EDGE of the bytes
+        # each) keep the two copies that nothing can overlap -- the first sub-list's activations in, the last
+        # sub-list's outputs out -- small
+        edge = float(os.environ.get("BENCH_E2E_EDGE", "0.1"))
+        if chunks >= 4 and 0.0 < edge < 0.25:
+            cuts = [edge + (1.0 - 2.0 * edge) * j / (chunks - 2) for j in range(chunks - 1)]
+        else:
+            cuts = [j / chunks for j in range(1, chunks)]
+        edges, acc, nxt = [0], 0, 0
         for i, w in enumerate(self.weights):
             acc += int(w.numel())
-            if nxt < chunks and acc >= total * nxt / chunks:
+            while nxt < len(cuts) and acc >= total * cuts[nxt]:
                 edges.append(i + 1); nxt += 1
         edges.append(n)
         edges = sorted(set(edges))
