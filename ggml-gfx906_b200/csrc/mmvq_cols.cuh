@@ -55,6 +55,9 @@ struct cols_args {
     cols_node nodes[COLS_MAX_NODES];
 };
 
+// third activation plane, behind yds: int32 [k / 16][8] = -32 * (sum of the 16 int8 activations)
+__device__ __host__ __forceinline__ int * cols_yns(const cols_node & nd) { return reinterpret_cast<int *>(nd.yds + (size_t) (nd.k / 32) * COLS_N); }
+
 // ---------------------------------------------------------------- activations of the list: f32 -> int8 columns
 // grid (ceil(kmax / 32 / 8), count, 8), block 256: one warp per 32 values of one column (q8_1 arithmetic as quantize.cu)
 __global__ void __launch_bounds__(256) k_quantize_cols(const __grid_constant__ cols_args a) {
@@ -64,6 +67,7 @@ __global__ void __launch_bounds__(256) k_quantize_cols(const __grid_constant__ c
     if (!nd.quantize || kb * 32 >= nd.k) return;
     if (c >= nd.n) {                                      // padding columns: zero scale pairs, q never read as non-zero
         if (lane == 0) nd.yds[kb * COLS_N + c] = make_float2(0.0f, 0.0f);
+        if (lane < 2) cols_yns(nd)[(2 * kb + lane) * COLS_N + c] = 0;
         return;
     }
     const float x = __ldg(nd.x + (size_t) c * nd.x_stride + kb * 32 + lane);
@@ -76,7 +80,10 @@ __global__ void __launch_bounds__(256) k_quantize_cols(const __grid_constant__ c
     nd.yq[((size_t) kb * COLS_N + c) * 32 + lane] = (int8_t) q8;
     int sum = q8;
 #pragma unroll
-    for (int off = 16; off > 0; off >>= 1) sum += __shfl_xor_sync(0xFFFFFFFFu, sum, off);
+    for (int off = 8; off > 0; off >>= 1) sum += __shfl_xor_sync(0xFFFFFFFFu, sum, off);
+    // Q6_K weights are (q - 32) * scale per 16 weights: -32 * (sum of the 16 activations) is the C input of that MMA
+    if ((lane & 15) == 0) cols_yns(nd)[(2 * kb + (lane >> 4)) * COLS_N + c] = -32 * sum;
+    sum += __shfl_xor_sync(0xFFFFFFFFu, sum, 16);
     if (lane == 0) {
         const float dh = __half2float(__float2half_rn(d));
         nd.yds[kb * COLS_N + c] = make_float2(dh, dh * (float) sum);
@@ -100,6 +107,8 @@ __device__ __forceinline__ uint4 ldg_stream128(const void * p) {
     asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
     return v;
 }
+
+__device__ __forceinline__ int cols_block_bytes(int type) { return type == T_Q6_K ? 210 : (type == T_Q5_K ? 176 : 144); }
 
 // HBM -> L2 prefetch of a whole weight row (16-byte aligned, a multiple of 16 bytes): no registers, no completion
 __device__ __forceinline__ void l2_prefetch_bulk(const void * p, uint32_t bytes) {
@@ -179,6 +188,88 @@ __device__ __forceinline__ void cols_half_mma(const cols_item & ia, const cols_i
     }
 }
 
+// ---------------------------------------------------------------- Q6_K: one m16n8k16 MMA per 16-weight scale group
+// block = ql[128] qh[64] sc[16] (int8) d (f16) = 210 bytes: blocks sit at 2-byte alignment.  With w and the row
+// stride multiples of 4 the blocks of even index are 4-byte aligned and those of odd index are 2 bytes off, the
+// same for every lane: odd blocks read the two aligned words around each word and funnel-shift.
+// Lane (g, t) takes bytes 4t..4t+3 of each 16-byte piece: for half h, piece s, word j of ql serves the groups
+// r = j (low nibbles) and r = j + 2 (high nibbles); the qh word serves r = 0..3 (2 bits each).
+__device__ __forceinline__ void mma_s8_16x8x16(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t b0) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.s32.s8.s8.s32 {%0, %1, %2, %3}, {%4, %5}, {%6}, {%0, %1, %2, %3};"
+                 : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3]) : "r"(a0), "r"(a1), "r"(b0));
+}
+__device__ __forceinline__ uint32_t ldg_stream32(const void * p) {
+    uint32_t v;
+    asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+struct cols_item6 {
+    uint32_t ql[2][2][2];     // [half h][word j: l / l + 32][piece s]
+    uint32_t qh[2][2];        // [half h][piece s]
+    uint32_t sc[4];           // 16 int8 scales
+    uint32_t d;               // f16 bits
+};
+template <bool ODD>
+__device__ __forceinline__ uint32_t cols_ld6(const uint8_t * blk, int off) {
+    if (!ODD) return ldg_stream32(blk + off);
+    return __funnelshift_r(ldg_stream32(blk + off - 2), ldg_stream32(blk + off + 2), 16);
+}
+template <bool ODD>
+__device__ __forceinline__ void cols_load6(cols_item6 & it, const uint8_t * blk, int t) {
+#pragma unroll
+    for (int h = 0; h < 2; h++)
+#pragma unroll
+        for (int s = 0; s < 2; s++) {
+            it.ql[h][0][s] = cols_ld6<ODD>(blk, 64 * h + 16 * s + 4 * t);
+            it.ql[h][1][s] = cols_ld6<ODD>(blk, 64 * h + 32 + 16 * s + 4 * t);
+            it.qh[h][s]    = cols_ld6<ODD>(blk, 128 + 32 * h + 16 * s + 4 * t);
+        }
+    if (!ODD) {
+#pragma unroll
+        for (int i = 0; i < 4; i++) it.sc[i] = ldg_stream32(blk + 192 + 4 * i);
+    } else {
+        uint32_t w[5];
+#pragma unroll
+        for (int i = 0; i < 5; i++) w[i] = ldg_stream32(blk + 190 + 4 * i);
+#pragma unroll
+        for (int i = 0; i < 4; i++) it.sc[i] = __funnelshift_r(w[i], w[i + 1], 16);
+    }
+    it.d = *reinterpret_cast<const unsigned short *>(blk + 208);
+}
+// sign-extended byte i of w as float
+__device__ __forceinline__ float cols_s8f(uint32_t w, int i) {
+    return (float) ((int) (w << (24 - 8 * i)) >> 24);      // (__byte_perm ignores prmt's sign-replicate selector bit)
+}
+__device__ __forceinline__ void cols_item6_mma(const cols_item6 & ia, const cols_item6 & ib, int item, int g, int t,
+                                               const int8_t * yq_col, const float2 * yds, const int * yns, bool col_ok, float (&acc)[4]) {
+    const float dA = f16_bits_to_f32(ia.d), dB = f16_bits_to_f32(ib.d);
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            const int B = item * 8 + 4 * h + r;                         // the 32-block of the activations
+            const float4 ds = __ldg(reinterpret_cast<const float4 *>(yds + (size_t) B * COLS_N + 2 * t));     // .x, .z: d of columns 2t, 2t + 1
+            float tA0 = 0.0f, tA1 = 0.0f, tB0 = 0.0f, tB1 = 0.0f;
+#pragma unroll
+            for (int s = 0; s < 2; s++) {
+                const uint32_t a0 = ((ia.ql[h][r & 1][s] >> (4 * (r >> 1))) & 0x0F0F0F0Fu) | (((ia.qh[h][s] >> (2 * r)) & 0x03030303u) << 4);
+                const uint32_t a1 = ((ib.ql[h][r & 1][s] >> (4 * (r >> 1))) & 0x0F0F0F0Fu) | (((ib.qh[h][s] >> (2 * r)) & 0x03030303u) << 4);
+                uint32_t b0 = 0u;
+                if (col_ok) b0 = __ldg(reinterpret_cast<const uint32_t *>(yq_col + (size_t) B * (32 * COLS_N) + 16 * s + 4 * t));
+                const int2 ns = __ldg(reinterpret_cast<const int2 *>(yns + (size_t) (2 * B + s) * COLS_N + 2 * t));
+                int c[4] = { ns.x, ns.y, ns.x, ns.y };                  // -32 * sum16: the weights enter as q, not q - 32
+                mma_s8_16x8x16(c, a0, a1, b0);
+                const int si = 8 * h + 2 * r + s;                       // scale of this 16-weight group
+                const float fA = cols_s8f(ia.sc[si >> 2], si & 3), fB = cols_s8f(ib.sc[si >> 2], si & 3);
+                tA0 += fA * (float) c[0]; tA1 += fA * (float) c[1];
+                tB0 += fB * (float) c[2]; tB1 += fB * (float) c[3];
+            }
+            acc[0] += (dA * ds.x) * tA0; acc[1] += (dA * ds.z) * tA1;
+            acc[2] += (dB * ds.x) * tB0; acc[3] += (dB * ds.z) * tB1;
+        }
+    }
+}
+
 // KS = 8 (default): the 8 warps of a CTA split K of one tile, partial tiles meet in shared memory;
 // KS = 1 (tuning variant): every warp owns whole tiles -- no barrier, no shared-memory reduction.
 // A row's value does not depend on the grid in either; the two differ in the f32 summation order over K.
@@ -201,13 +292,13 @@ __global__ void __launch_bounds__(COLS_NW * 32, COLS_CTAS) k_mmvq_cols(const __g
         const cols_node & np = a.nodes[nip];
         const int row = (up - np.unit0) * 16 + ptid;
         if (ptid < 16 && row < np.m)
-            l2_prefetch_bulk(np.w + (size_t) row * np.row_stride, (uint32_t) ((np.k >> 8) * (np.type == T_Q5_K ? 176 : 144)));
+            l2_prefetch_bulk(np.w + (size_t) row * np.row_stride, (uint32_t) (((np.k >> 8) * cols_block_bytes(np.type)) & ~15));
     };
     // KS = 1: 16 warps x whole tiles ahead would not fit L2; a warp requests 8 super-blocks (1152 B of each of its 16
     // rows) at a time, 8 ahead of the one it works on, across tile boundaries
     auto prefetch_chunk = [&](const cols_node & np, int row0p, int b0) {
-        const int nb = min(8, (np.k >> 8) - b0), bs = np.type == T_Q5_K ? 176 : 144;
-        if (lane < 16 && row0p + lane < np.m && nb > 0)
+        const int nb = min(8, (np.k >> 8) - b0), bs = cols_block_bytes(np.type);
+        if (np.type != T_Q6_K && lane < 16 && row0p + lane < np.m && nb > 0)
             l2_prefetch_bulk(np.w + (size_t) (row0p + lane) * np.row_stride + (size_t) b0 * bs, (uint32_t) (nb * bs));
     };
     const int PD = COLS_PREFETCH_UNITS;
@@ -232,6 +323,15 @@ __global__ void __launch_bounds__(COLS_NW * 32, COLS_CTAS) k_mmvq_cols(const __g
         const float2 * yds = nd.yds;
         const bool col_ok = g < nd.n;
         float acc[4] = { 0.0f, 0.0f, 0.0f, 0.0f };
+        if (nd.type == T_Q6_K) {
+            const int * yns = cols_yns(nd);
+            for (int it = kw; it < items; it += KS) {
+                cols_item6 ia, ib;
+                if (it & 1) { cols_load6<true>(ia, pa + (size_t) it * 210, t);  cols_load6<true>(ib, pb + (size_t) it * 210, t); }
+                else        { cols_load6<false>(ia, pa + (size_t) it * 210, t); cols_load6<false>(ib, pb + (size_t) it * 210, t); }
+                cols_item6_mma(ia, ib, it, g, t, yq_col, yds, yns, col_ok, acc);
+            }
+        } else
         for (int it = kw; it < items; it += KS) {
             if (KS == 1 && (it & 7) == 0) {
                 if (it + 8 < items) prefetch_chunk(nd, row0, it + 8);
@@ -272,15 +372,16 @@ __global__ void __launch_bounds__(COLS_NW * 32, COLS_CTAS) k_mmvq_cols(const __g
 // ---------------------------------------------------------------- host side
 static inline bool cols_node_ok(int type, const uint8_t * w, int64_t row_stride, int64_t m, int64_t k, const float * x,
                                 int64_t x_stride_bytes, int64_t n) {
-    if (type != T_Q4_K && type != T_Q5_K) return false;
+    if (type != T_Q4_K && type != T_Q5_K && type != T_Q6_K) return false;
     if (n < 2 || n > COLS_N || m < 1 || k < 256 || k % 256 != 0) return false;
     if (m >= (int64_t) 1 << 31 || k >= (int64_t) 1 << 24) return false;
     if ((reinterpret_cast<uintptr_t>(w) & 15) || (row_stride & 15) || (reinterpret_cast<uintptr_t>(x) & 3) || (x_stride_bytes & 3)) return false;
-    return row_stride >= k / 256 * (type == T_Q5_K ? 176 : 144);
+    return row_stride >= k / 256 * (type == T_Q6_K ? 210 : (type == T_Q5_K ? 176 : 144));
 }
 static inline size_t cols_ws_bytes(int64_t k, int64_t n) {
     (void) n;
-    return (((size_t) COLS_N * k + 127) & ~(size_t) 127) + (((size_t) (k / 32) * COLS_N * sizeof(float2) + 127) & ~(size_t) 127);
+    // int8 [k/32][8][32]  +  (d, d * sum) [k/32][8]  +  -32 * sum16 [k/16][8]
+    return (((size_t) COLS_N * k + 127) & ~(size_t) 127) + (((size_t) (k / 32) * COLS_N * (sizeof(float2) + 2 * sizeof(int)) + 127) & ~(size_t) 127);
 }
 
 struct cols_builder {

@@ -368,7 +368,7 @@ def test_mul_mat_batch_few_columns(kern, oracle, n):
     import b200
     import torch
     mats = [("q4_K", 300, 4096), ("q6_K", 130, 1024), ("q8_0", 96, 2048), ("q5_K", 4096, 1024), ("q4_0", 64, 4096),
-            ("q4_K", 17, 256), ("q5_K", 33, 11008), ("q4_K", 4096, 14336)]
+            ("q4_K", 17, 256), ("q5_K", 33, 11008), ("q4_K", 4096, 14336), ("q6_K", 200, 4096), ("q6_K", 49, 14336), ("q6_K", 1024, 2048)]
     c0 = kern.launch_count()
     for i, (t, m, k) in enumerate(mats):
         w_np = random_blocks(t, m, k, seed=40 + i)
@@ -382,7 +382,7 @@ def test_mul_mat_batch_few_columns(kern, oracle, n):
         got = y.cpu().numpy()
         want = oracle.mul_mat(t, w_np, m, k, np.ascontiguousarray(x_np[:, :k]), mode=1)
         assert oracle.nmse(want, got) <= NMSE_ORACLE, (t, m, k, n)
-        if t in ("q4_K", "q5_K"):
+        if t in ("q4_K", "q5_K") or (t == "q6_K" and k % 2048 == 0):     # Q6_K rows must be 16-byte multiples for the MMA path
             # the MMA list kernel (mmvq_cols.cuh): a column's value depends on that column alone -- the first two
             # columns computed as an n = 2 node give the same bits; and the result is reproducible
             y2 = torch.zeros((2, m), dtype=torch.float32, device=kern.device)
