@@ -1,4 +1,4 @@
-// mmvq_cols.cuh — decode at batch 2..8 (MUL_MAT with a few activation columns), Q4_K / Q5_K weights:
+// mmvq_cols.cuh — decode at batch 2..8 (MUL_MAT with a few activation columns), Q4_K / Q5_K / Q6_K weights:
 // ONE launch pair per list of independent nodes, int8 tensor-core MMA on the weight nibbles as they are.
 //
 // The reference sends n <= 8 through mul_mat_vec_q with ncols_dst template instances (src/ggml-cuda/mmvq.cu:139-226,
