@@ -67,6 +67,36 @@ def test_format_table_and_errors(built):
     assert lib.b200_acts_scratch_bytes(4096, 1) == 4096 + 128 * 4
 
 
+def test_batch_workspace_size_covers_every_list_path(built):
+    """b200_mul_mat_batch_workspace_size is host arithmetic: it must cover what the list paths carve out of the
+    workspace -- one q8 record (k + k/8 bytes) per one-column node for the persistent kernel, the three activation
+    planes of the MMA list kernel (8 k int8 + k/32 x 8 x (8 + 8) bytes) per node with 2..8 columns, and the
+    largest single-node need on top -- and grow with the list."""
+    import b200
+    lib = b200.load_library()
+
+    def size(nodes):
+        arr = (b200.MulMatNode * len(nodes))(*nodes)
+        return int(lib.b200_mul_mat_batch_workspace_size(arr, len(nodes)))
+
+    def node(t, m, k, n):
+        return b200.mul_mat_node(t, 0x10000, m, k, 0x20000, n, 0x30000)
+
+    assert size([]) >= 256
+    for k in (4096, 14336):
+        one = size([node("q4_K", 4096, k, 1)])
+        assert one >= k + k // 8
+        assert size([node("q4_K", 4096, k, 1)] * 10) >= 10 * (k + k // 8)
+        for n in (2, 4, 8):
+            for t in ("q4_K", "q5_K", "q6_K"):
+                assert size([node(t, 4096, k, n)]) >= 8 * k + (k // 32) * 8 * 16, (t, k, n)
+            assert size([node("q4_K", 4096, k, n), node("q6_K", 1024, k, n)]) >= 2 * (8 * k + (k // 32) * 8 * 16)
+            assert size([node("q8_0", 4096, k, n)]) >= n * (k + k // 8)          # one persistent entry per column
+        big = size([node("q4_K", 4096, k, 512)])
+        assert big >= 512 * k                                                     # batched path: activations staged once
+        assert size([node("q4_K", 4096, k, 512), node("q4_K", 4096, k, 1)]) >= big + k + k // 8
+
+
 def test_no_device_fails_loudly(built):
     import torch
     import b200
