@@ -272,7 +272,7 @@ def measure_per_node_launches(torch, kern, stack, reps):
     """Comparison leg: the same step issued as one launch per MUL_MAT (GGML_B200_NO_BATCH_KERNEL=1: the
     per-node fused decode kernel with programmatic dependent launch), replayed from a CUDA graph.
     Returns seconds per step."""
-    os.environ["GGML_B200_NO_BATCH_KERNEL"] = "1"
+    prev = kern.set_option("no_batch_kernel", 1)
     try:
         stack.compute()
         torch.cuda.synchronize()
@@ -282,7 +282,7 @@ def measure_per_node_launches(torch, kern, stack, reps):
         g.replay()
         sec = timed_loop(torch, g.replay, reps) / reps
     finally:
-        del os.environ["GGML_B200_NO_BATCH_KERNEL"]
+        kern.set_option("no_batch_kernel", prev)
     return sec
 
 
@@ -351,6 +351,66 @@ def measure_decode_batches(torch, kern, stack, peak):
         out[f"n={n}"] = {"ms_per_pass": round(sec * 1e3, 4), "launches": launches, "weight_GBps": round(wbytes / sec / 1e9, 1),
                          "frac": round(wbytes / sec / 1e9 / peak, 3), "tok_s": round(n / sec, 1)}
         del g, xs, ys, ws
+    return out
+
+
+def measure_decode_chain(torch, kern, stack, peak, reps=50):
+    """The same resident stack with the dependency structure a decoder pass really has (what a ggml decode graph
+    gives the backend): per layer q/k/v read the layer input, wo reads q (stand-in for the attention output), gate/up
+    read wo, down reads up, the next layer reads down, the output matrix reads the last down -- 129 chain links for
+    Llama-2-7B.  ONE b200_mul_mat_batch call: the dependent nodes ride the same persistent launch (completion
+    counters + in-launch activation quantization).  Checked bit for bit against the same list cut at every link
+    (option no_chain: one launch group per link, the round-1 behaviour), which is also timed."""
+    import b200
+    mats, dev = stack.mats, kern.device
+    assert (len(mats) - 1) % 7 == 0
+    layers = (len(mats) - 1) // 7
+    bufs = {"h0": torch.rand((1, mats[0].k), device=dev) * 2 - 1}
+    plan = []
+    cur = "h0"
+    for l in range(layers):
+        q, kk, v, o, g, u, d = (7 * l + j for j in range(7))
+        plan += [(q, cur, f"q{l}"), (kk, cur, f"k{l}"), (v, cur, f"v{l}"), (o, f"q{l}", f"o{l}"),
+                 (g, f"o{l}", f"g{l}"), (u, f"o{l}", f"u{l}"), (d, f"u{l}", f"d{l}")]
+        cur = f"d{l}"
+    plan.append((len(mats) - 1, cur, "logits"))
+    for i, src, dst in plan:
+        lo, hi = stack.rows[i]
+        bufs[dst] = torch.zeros((1, hi - lo), dtype=torch.float32, device=dev)
+    nodes = (b200.MulMatNode * len(plan))(*[
+        b200.mul_mat_node(mats[i].type, stack.weights[i].data_ptr(), stack.rows[i][1] - stack.rows[i][0], mats[i].k,
+                          bufs[src].data_ptr(), 1, bufs[dst].data_ptr(), const_weights=True) for i, src, dst in plan])
+    ws = torch.empty(int(kern.lib.b200_mul_mat_batch_workspace_size(nodes, len(plan))) + 256, dtype=torch.uint8, device=dev)
+    groups = len({g for g, _, _ in b200.batch_plan(kern.lib, nodes)})
+    links = sum(1 for _, dep, _ in b200.batch_plan(kern.lib, nodes) if dep >= 0)
+    fn = lambda: kern.mul_mat_batch(nodes, ws=ws)       # noqa: E731
+    out = {"nodes": len(plan), "launch_groups": groups, "in_launch_waits": links}
+    results = {}
+    for mode in ("chained", "cut"):
+        prev = kern.set_option("no_chain", 1 if mode == "cut" else 0)
+        try:
+            for b in bufs.values():
+                if b is not bufs["h0"]:
+                    b.zero_()
+            fn()
+            torch.cuda.synchronize()
+            results[mode] = torch.cat([bufs[dst].view(-1) for _, _, dst in plan]).clone()
+            c0 = kern.launch_count()
+            fn()
+            launches = kern.launch_count() - c0
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                fn()
+            g.replay()
+            sec = timed_loop(torch, g.replay, reps) / reps
+            out[mode] = {"ms_per_pass": round(sec * 1e3, 4), "launches": launches,
+                         "GBps": round(stack.local_alg_bytes / sec / 1e9, 1), "frac": round(stack.local_alg_bytes / sec / 1e9 / peak, 3),
+                         "passes_per_s": round(1.0 / sec, 1)}
+            del g
+        finally:
+            kern.set_option("no_chain", prev)
+    out["bit_identical_to_cut_list"] = bool(torch.equal(results["chained"].view(torch.int32), results["cut"].view(torch.int32)))
+    out["finite"] = bool(torch.isfinite(results["chained"]).all())
     return out
 
 
@@ -597,6 +657,10 @@ def main():
             line["decode_batches"] = measure_decode_batches(torch, kern, stack, peak)
         except Exception as e:                   # noqa: BLE001
             line["decode_batches"] = {"error": str(e)[:200]}
+        try:
+            line["decode_chain"] = measure_decode_chain(torch, kern, stack, peak)
+        except Exception as e:                   # noqa: BLE001
+            line["decode_chain"] = {"error": str(e)[:200]}
         _, info = cpu_reference()
         line["cpu_baseline"] = {k: info[k] for k in ("value", "unit", "cores", "kind", "sample")}
     if rank == 0:

@@ -20,6 +20,10 @@ BLOCK_ELEMS = {"q4_0": 32, "q8_0": 32, "q8_1": 32, "q4_K": 256, "q5_K": 256, "q6
 BLOCK_BYTES = {"q4_0": 18, "q8_0": 34, "q8_1": 36, "q4_K": 144, "q5_K": 176, "q6_K": 210}
 QUANT_TYPES = ("q4_0", "q8_0", "q4_K", "q5_K", "q6_K")
 MMVQ_MAX_N = 8
+# enum b200_option (include/ggml_b200.h)
+OPT = {"mmvq_generic": 0, "mmvq_no_fused": 1, "batch_single": 2, "no_batch_kernel": 3, "mmq_bn": 4,
+       "mmq_force_unaligned": 5, "no_chain": 6, "mmq_route": 7}
+ERR_FLAG_INDEX = 1
 
 
 class B200Error(RuntimeError):
@@ -91,8 +95,26 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
     lib.b200_mul_mat_batch_workspace_size.argtypes = [C.POINTER(MulMatNode), i64]
     lib.b200_mul_mat_batch.restype = i32
     lib.b200_mul_mat_batch.argtypes = [C.POINTER(MulMatNode), i64, vp, sz, vp]
+    lib.b200_mul_mat_batch_plan.restype = i32
+    lib.b200_mul_mat_batch_plan.argtypes = [C.POINTER(MulMatNode), i64, C.POINTER(C.c_int32)]
     lib.b200_launch_count.restype = C.c_uint64
+    lib.b200_acts_record_bytes.restype = sz;     lib.b200_acts_record_bytes.argtypes = [i64]
+    lib.b200_acts_columns_bytes.restype = sz;    lib.b200_acts_columns_bytes.argtypes = [i64, i64]
+    lib.b200_quantize_acts_record.restype = i32; lib.b200_quantize_acts_record.argtypes = [vp, i64, vp, vp]
+    lib.b200_quantize_acts_columns.restype = i32; lib.b200_quantize_acts_columns.argtypes = [vp, sz, i64, i64, vp, vp]
+    lib.b200_set_option.restype = i32;           lib.b200_set_option.argtypes = [i32, i32]
+    lib.b200_device_error_flags.restype = C.c_uint; lib.b200_device_error_flags.argtypes = [i32]
     return lib
+
+
+def batch_plan(lib, nodes, count: Optional[int] = None):
+    """[(launch group, waits-for list index or -1, route)] per node: how b200_mul_mat_batch would issue the list."""
+    count = len(nodes) if count is None else count
+    out = (C.c_int32 * (3 * max(count, 1)))()
+    rc = lib.b200_mul_mat_batch_plan(nodes, count, out)
+    if rc != 0:
+        raise B200Error(f"mul_mat_batch_plan: code {rc}")
+    return [(out[3 * i], out[3 * i + 1], out[3 * i + 2]) for i in range(count)]
 
 
 def _a4i(v):
@@ -127,6 +149,27 @@ class Kernels:
     def launch_count(self) -> int:
         return int(self.lib.b200_launch_count())
 
+    def set_option(self, name: str, value: int) -> int:
+        """b200_set_option: force one of the candidate kernels (tests / benches); returns the previous value."""
+        return int(self.lib.b200_set_option(OPT[name], int(value)))
+
+    def option(self, name: str, value: int):
+        """context manager: `with kern.option("mmvq_generic", 1): ...`"""
+        kern = self
+
+        class _Ctx:
+            def __enter__(self_inner):
+                self_inner.prev = kern.set_option(name, value)
+
+            def __exit__(self_inner, *exc):
+                kern.set_option(name, self_inner.prev)
+        return _Ctx()
+
+    def device_error_flags(self, clear: bool = True) -> int:
+        """sticky error bits set by kernels (bit 0: GET_ROWS index outside the table); synchronizes first."""
+        self.torch.cuda.synchronize()
+        return int(self.lib.b200_device_error_flags(1 if clear else 0))
+
     def to_device(self, arr):
         """numpy array (any dtype) -> device tensor of the same dtype/shape."""
         return self.torch.from_numpy(arr).to(self.device)
@@ -159,6 +202,23 @@ class Kernels:
         out = torch.empty((n, k // 32 * 36), dtype=torch.uint8, device=self.device)
         self._check(self.lib.b200_quantize_row_q8_1(x.data_ptr(), x.stride(0) * 4, k, n, out.data_ptr(), self._stream()),
                     "quantize_row_q8_1")
+        return out
+
+    def quantize_acts_record(self, x):
+        """x: f32 [k] -> the decode list kernel's q8 record (uint8, layout: include/ggml_b200.h)."""
+        torch = self.torch
+        k = x.numel()
+        out = torch.zeros(int(self.lib.b200_acts_record_bytes(k)), dtype=torch.uint8, device=self.device)
+        self._check(self.lib.b200_quantize_acts_record(x.data_ptr(), k, out.data_ptr(), self._stream()), "quantize_acts_record")
+        return out
+
+    def quantize_acts_columns(self, x):
+        """x: f32 [n, k], n <= 8 -> the MMA list kernel's activation columns (uint8, layout: include/ggml_b200.h)."""
+        torch = self.torch
+        n, k = x.shape
+        out = torch.zeros(int(self.lib.b200_acts_columns_bytes(k, n)), dtype=torch.uint8, device=self.device)
+        self._check(self.lib.b200_quantize_acts_columns(x.data_ptr(), x.stride(0) * 4, k, n, out.data_ptr(), self._stream()),
+                    "quantize_acts_columns")
         return out
 
     # ------------------------------------------------------------------ GET_ROWS

@@ -4,7 +4,9 @@
 
 #include <atomic>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <mutex>
 
 using namespace b200;
 
@@ -14,7 +16,73 @@ extern "C" void b200_count_launch(uint64_t n) { g_launches.fetch_add(n, std::mem
 
 extern "C" uint64_t b200_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
-extern "C" int b200_abi_version(void) { return 1; }
+extern "C" int b200_abi_version(void) { return 2; }
+
+// ---------------------------------------------------------------- run-time options
+// Path switches the tests and the benches flip (one kernel against another on the same inputs).  Each starts
+// from its environment variable, read ONCE; after that b200_set_option is the only way to change it, so no
+// launch path ever calls getenv.
+namespace {
+struct opt_def { const char * env; int dflt; };
+const opt_def g_opt_defs[B200_OPT_COUNT] = {
+    /* B200_OPT_MMVQ_GENERIC        */ { "GGML_B200_MMVQ_GENERIC", 0 },
+    /* B200_OPT_MMVQ_NO_FUSED       */ { "GGML_B200_MMVQ_NO_FUSED", 0 },
+    /* B200_OPT_BATCH_SINGLE        */ { "GGML_B200_BATCH_SINGLE", -1 },
+    /* B200_OPT_NO_BATCH_KERNEL     */ { "GGML_B200_NO_BATCH_KERNEL", 0 },
+    /* B200_OPT_MMQ_BN              */ { "GGML_B200_MMQ_BN", 0 },
+    /* B200_OPT_MMQ_FORCE_UNALIGNED */ { "GGML_B200_MMQ_FORCE_UNALIGNED", 0 },
+    /* B200_OPT_NO_CHAIN            */ { "GGML_B200_NO_CHAIN", 0 },
+    /* B200_OPT_MMQ_ROUTE           */ { "GGML_B200_MMQ_ROUTE", 0 },
+};
+std::atomic<int> g_opt[B200_OPT_COUNT];
+std::once_flag   g_opt_once;
+void opt_init() {
+    std::call_once(g_opt_once, [] {
+        for (int i = 0; i < B200_OPT_COUNT; i++) {
+            const char * v = getenv(g_opt_defs[i].env);
+            g_opt[i].store(v && *v ? atoi(v) : g_opt_defs[i].dflt, std::memory_order_relaxed);
+        }
+    });
+}
+}
+extern "C" int b200_option(int id) {
+    if (id < 0 || id >= B200_OPT_COUNT) return 0;
+    opt_init();
+    return g_opt[id].load(std::memory_order_relaxed);
+}
+extern "C" int b200_set_option(int id, int value) {
+    if (id < 0 || id >= B200_OPT_COUNT) return 0;
+    opt_init();
+    return g_opt[id].exchange(value, std::memory_order_relaxed);
+}
+
+// ---------------------------------------------------------------- sticky device-side error flags
+// Kernels cannot return codes: the ones that can meet bad DATA (a GET_ROWS index outside the table) set a bit in a
+// word of mapped pinned host memory; b200_device_error_flags() reads it on the host (meaningful once the stream
+// that ran the kernel has been synchronized).
+namespace {
+std::mutex g_err_mutex;
+unsigned * g_err_host = nullptr;
+}
+extern "C" unsigned * b200_error_word_dev(void) {
+    std::lock_guard<std::mutex> lock(g_err_mutex);
+    if (!g_err_host) {
+        void * p = nullptr;
+        if (cudaHostAlloc(&p, 64, cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+        memset(p, 0, 64);
+        g_err_host = (unsigned *) p;
+    }
+    void * d = nullptr;
+    if (cudaHostGetDevicePointer(&d, g_err_host, 0) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return (unsigned *) d;
+}
+extern "C" unsigned b200_device_error_flags(int clear) {
+    std::lock_guard<std::mutex> lock(g_err_mutex);
+    if (!g_err_host) return 0;
+    const unsigned v = *(volatile unsigned *) g_err_host;
+    if (clear) *(volatile unsigned *) g_err_host = 0;
+    return v;
+}
 
 extern "C" const char * b200_error_string(int code) {
     if (code < 0) return cudaGetErrorString((cudaError_t) (-code));
@@ -25,6 +93,8 @@ extern "C" const char * b200_error_string(int code) {
         case B200_ERR_STRIDE:    return "bad stride / alignment";
         case B200_ERR_WORKSPACE: return "workspace missing or too small";
         case B200_ERR_NO_DEVICE: return "no sm_100 device";
+        case B200_ERR_INDEX:     return "row index outside the table";
+        case B200_NOT_APPLICABLE: return "no kernel of this library applies to the call";
         default:                 return "unknown error";
     }
 }

@@ -18,6 +18,8 @@
 #include "../../include/ggml_b200.h"
 
 extern "C" void b200_count_launch(uint64_t n);   // internal launch counter (capi.cu)
+extern "C" int  b200_option(int id);             // run-time path switch (capi.cu; enum b200_option)
+extern "C" unsigned * b200_error_word_dev(void); // device pointer of the sticky error word (capi.cu)
 
 namespace b200 {
 

@@ -206,25 +206,30 @@ __global__ void __launch_bounds__(256) k_dequantize_4d(const uint8_t * __restric
 }
 
 // ---------------------------------------------------------------- GET_ROWS
-// grid (ceil(k/8/256), n_rows); a row index outside the table traps in the reference (GGML_ASSERT,
-// src/ggml-cpu/ops.cpp:5147); here such rows are left untouched and reported through *bad.
+// grid (ceil(k/8/256), n_rows); a row index outside the table aborts in the reference (GGML_ASSERT,
+// src/ggml-cpu/ops.cpp:5147).  A kernel cannot return a code: such rows are ZERO-FILLED (never stale memory)
+// and bit 0 of the library's sticky error word is set (b200_device_error_flags -> B200_ERR_INDEX; the plugin
+// aborts on it at its next synchronize, like the reference).
 template <int T, typename OUT>
 __global__ void __launch_bounds__(256) k_get_rows(const uint8_t * __restrict__ table, int64_t row_stride, int64_t k, int64_t table_rows,
                                                   const uint8_t * __restrict__ rows, int64_t rows_stride,
-                                                  uint8_t * __restrict__ dst, int64_t dst_row_stride, int * __restrict__ bad) {
+                                                  uint8_t * __restrict__ dst, int64_t dst_row_stride, unsigned * __restrict__ bad) {
     const int64_t i = (int64_t) blockIdx.x * 256 + threadIdx.x;
     if (i * 8 >= k) return;
     const int64_t out_row = blockIdx.y;
     const int32_t r = *reinterpret_cast<const int32_t *>(rows + out_row * rows_stride);
+    OUT * p = reinterpret_cast<OUT *>(dst + out_row * dst_row_stride) + i * 8;
+    float v[8];
     if (r < 0 || r >= table_rows) {
-        if (bad && i == 0) atomicExch(bad, 1);
+        if (bad && i == 0) atomicOr_system(bad, 1u);
+#pragma unroll
+        for (int j = 0; j < 8; j++) v[j] = 0.0f;
+        store8<OUT>(p, v, (reinterpret_cast<uintptr_t>(p) & (8 * sizeof(OUT) - 1)) == 0);
         return;
     }
     constexpr int cpb = fmt<T>::qk / 8;
     const int64_t blk = i / cpb;
-    float v[8];
     dequant8<T>(table + (int64_t) r * row_stride + blk * fmt<T>::bytes, (int) (i - blk * cpb), v);
-    OUT * p = reinterpret_cast<OUT *>(dst + out_row * dst_row_stride) + i * 8;
     store8<OUT>(p, v, (reinterpret_cast<uintptr_t>(p) & (8 * sizeof(OUT) - 1)) == 0);
 }
 
@@ -291,6 +296,7 @@ extern "C" int b200_get_rows(int type, const void * table_dev, size_t table_row_
     if (k < 0 || n_rows < 0 || k % type_qk(type) != 0) return B200_ERR_SHAPE;
     if (k == 0 || n_rows == 0) return B200_OK;
     cudaStream_t st = (cudaStream_t) stream;
+    unsigned * bad = b200_error_word_dev();
     // gridDim.y is limited to 65535: walk the output rows in slabs
     for (int64_t r0 = 0; r0 < n_rows; r0 += 65535) {
         const int64_t nr = n_rows - r0 < 65535 ? n_rows - r0 : 65535;
@@ -298,7 +304,7 @@ extern "C" int b200_get_rows(int type, const void * table_dev, size_t table_row_
         const uint8_t * rows = (const uint8_t *) rows_dev + r0 * rows_stride_bytes;
         uint8_t * dst = (uint8_t *) dst_dev + r0 * dst_row_stride_bytes;
 #define CALL(T, OUT) k_get_rows<T, OUT><<<grid, 256, 0, st>>>((const uint8_t *) table_dev, (int64_t) table_row_stride_bytes, k, table_rows, \
-                                                             rows, (int64_t) rows_stride_bytes, dst, (int64_t) dst_row_stride_bytes, nullptr);
+                                                             rows, (int64_t) rows_stride_bytes, dst, (int64_t) dst_row_stride_bytes, bad);
         DISPATCH_TYPE_OUT(type, out_type, CALL)
 #undef CALL
         b200_count_launch(1);

@@ -1,6 +1,6 @@
 // mmq.cu — host side of the batched tensor-core MUL_MAT (kernel: mmq_tc.cuh).
 // Replaces ggml_cuda_mul_mat_q / mul_mat_q_case / launch_mul_mat_q (reference src/ggml-cuda/mmq.cu:71-143,
-// mmq.cuh:3542-3712): converts the activations to fp16 once (instead of quantize_mmq_q8_1), encodes a
+// mmq.cuh:3542-3712): converts the activations to bf16 once (instead of quantize_mmq_q8_1), encodes a
 // TMA descriptor over them and launches one CTA per 128 x BN output tile.
 #include "common.cuh"
 #include "mmq_tc.cuh"
@@ -35,13 +35,8 @@ template <int T, int BN, bool ALIGNED>
 int launch_mmq(const mmq_args & a, const CUtensorMap & tmap, const CUtensorMap & tmap_w, cudaStream_t st) {
     auto kern = k_mmq_tc<T, BN, ALIGNED>;
     const size_t smem = mmq_smem<BN>::total(a.raw_pitch, mmq_rs<T>::value);
-    static size_t smem_set[64];
-    int dev = 0; cudaGetDevice(&dev); if (dev < 0 || dev >= 64) dev = 0;
-    if (smem > smem_set[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
-        if (e != cudaSuccess) return -(int) e;
-        smem_set[dev] = smem;
-    }
+    static smem_limit lim;
+    if (const int rc = lim.ensure(kern, smem)) return rc;
     const dim3 grid((unsigned) ceil_div(a.m, MMQ_BM), (unsigned) ceil_div(a.n, BN));
     kern<<<grid, MMQ_THREADS, smem, st>>>(a, tmap, tmap_w);
     b200_count_launch(1);
@@ -67,7 +62,7 @@ int launch_mmq_bn(const mmq_args & a, const CUtensorMap & tmap, const CUtensorMa
 }
 
 int pick_bn(int64_t m, int64_t n, int sm_count) {
-    const int forced = env_int("GGML_B200_MMQ_BN", 0);
+    const int forced = b200_option(B200_OPT_MMQ_BN);
     if (forced == 32 || forced == 64 || forced == 128 || forced == 256) return forced;
     if (n <= 32) return 32;
     if (n <= 64) return 64;
@@ -85,7 +80,7 @@ int pick_bn(int64_t m, int64_t n, int sm_count) {
 extern "C" size_t b200_mul_mat_q_workspace_size(int64_t m, int64_t k, int64_t n) {
     (void) m;
     if (k <= 0 || n <= 0) return 256;
-    return (size_t) n * (size_t) k * sizeof(__half) + 512;
+    return (size_t) n * (size_t) k * sizeof(__nv_bfloat16) + 512;
 }
 
 extern "C" int b200_mul_mat_q(int type, const void * w_dev, size_t w_row_stride_bytes, int64_t m, int64_t k,
@@ -101,27 +96,27 @@ extern "C" int b200_mul_mat_q(int type, const void * w_dev, size_t w_row_stride_
     if (!workspace_dev || workspace_bytes < b200_mul_mat_q_workspace_size(m, k, n)) return B200_ERR_WORKSPACE;
     if (k > 0x7FFFFFFF || n > 0x7FFFFFFF) return B200_ERR_SHAPE;
 
-    // 1. activations -> fp16 [n][k]
+    // 1. activations -> bf16 [n][k]
     uint16_t * xb = (uint16_t *) (((uintptr_t) workspace_dev + 255) & ~(uintptr_t) 255);
     for (int64_t r0 = 0; r0 < n; r0 += 65535) {
         const int64_t nr = n - r0 < 65535 ? n - r0 : 65535;
         const dim3 grid((unsigned) ceil_div(k, 1024), (unsigned) nr);
-        k_f32_to_f16<<<grid, 256, 0, st>>>((const uint8_t *) x_dev + r0 * x_row_stride_bytes, (int64_t) x_row_stride_bytes, k, xb + r0 * k);
+        k_f32_to_bf16<<<grid, 256, 0, st>>>((const uint8_t *) x_dev + r0 * x_row_stride_bytes, (int64_t) x_row_stride_bytes, k, xb + r0 * k);
         b200_count_launch(1);
     }
     B200_RETURN_IF_LAUNCH_FAILED();
 
-    // 2. TMA descriptor over the fp16 activations: dims {k, n}, box {64, BN}, 128-byte swizzle, zero fill
+    // 2. TMA descriptor over the bf16 activations: dims {k, n}, box {64, BN}, 128-byte swizzle, zero fill
     const dev_caps & caps = current_caps();
     const int bn = pick_bn(m, n, caps.sm_count);
     encode_tiled_fn encode = get_encode_tiled();
     if (!encode) return B200_ERR_NO_DEVICE;
     CUtensorMap tmap;
     const cuuint64_t gdim[2]    = { (cuuint64_t) k, (cuuint64_t) n };
-    const cuuint64_t gstride[1] = { (cuuint64_t) k * sizeof(__half) };
+    const cuuint64_t gstride[1] = { (cuuint64_t) k * sizeof(__nv_bfloat16) };
     const cuuint32_t box[2]     = { (cuuint32_t) MMQ_BK, (cuuint32_t) bn };
     const cuuint32_t estr[2]    = { 1, 1 };
-    const CUresult cr = encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, xb, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+    const CUresult cr = encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, xb, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (cr != CUDA_SUCCESS) return B200_ERR_STRIDE;
 
@@ -131,7 +126,7 @@ extern "C" int b200_mul_mat_q(int type, const void * w_dev, size_t w_row_stride_
     a.dst = dst_dev; a.dst_col_stride = (int64_t) (dst_col_stride_bytes / 4);
     a.nblk = (int) (k / type_qk(type)); a.raw_pitch = 0;
     const bool aligned0 = type != T_Q6_K && ((uintptr_t) w_dev % 16 == 0) && (w_row_stride_bytes % 16 == 0) &&
-                         !env_int("GGML_B200_MMQ_FORCE_UNALIGNED", 0);
+                         !b200_option(B200_OPT_MMQ_FORCE_UNALIGNED);
     // aligned rows: a second descriptor over the raw weight bytes as 32-bit words, dims {row words, m}, box {slab words, 128}
     bool aligned = aligned0;
     CUtensorMap tmap_w;

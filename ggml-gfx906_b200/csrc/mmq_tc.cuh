@@ -7,14 +7,18 @@
 // rescaling in registers after every block.
 //
 // Design.  A per-32 (or per-16) block scale cannot ride through an integer TMEM accumulator: with
-// kind::i8 every 32-deep slice would need its own accumulator drained and FMA-scaled on the CUDA
-// cores — 128xN f32 FMAs per 128xNx32 MACs caps the tensor pipe below ~40 % of its i8 rate.  So the
-// scale is folded into the WEIGHT operand instead: producer warps dequantize the quant blocks to
-// fp16 (exact integer -> fp16 via the 0x6400 magic, one HFMA2 per two weights) straight into the
-// UMMA canonical K-major SWIZZLE_128B shared-memory layout, activations are converted once to fp16
-// and fetched by TMA with the same swizzle, and a single tcgen05.mma.kind::f16 chain accumulates
-// the whole K extent in f32 in TMEM.  Accuracy is better than the q8_1 route (activations keep 11
-// mantissa bits instead of <= 7 bits per 32-block; weights keep 11) and there is no per-block drain.
+// kind::i8 every 32-deep slice needs its own accumulator drained and FMA-scaled on the CUDA cores
+// (that route is built and measured in mmq_i8.cuh).  Here the scale is folded into the WEIGHT operand
+// instead: producer warps dequantize the quant blocks to bf16 (exact integer -> bf16 via the 0x4300
+// magic, one HFMA2.BF16 per two weights) straight into the UMMA canonical K-major SWIZZLE_128B
+// shared-memory layout, activations are converted once to bf16 and fetched by TMA with the same
+// swizzle, and a single tcgen05.mma.kind::f16 chain accumulates the whole K extent in f32 in TMEM.
+// bf16, not fp16: both operands then have the exponent range of f32, so the result is as indifferent
+// to the magnitude of activations and block scales (|x| ~ 1e5 after un-normalised residual sums, d * sc
+// up to 65504 * 63, subnormal d) as the reference's per-block q8_1 route is (src/ggml-cuda/quantize.cu:
+// 50-143); fp16 operands overflowed to inf / flushed to zero there.  8 significand bits per operand is
+// the precision class of q8_1 itself (<= 7 bits per 32-block): measured NMSE ~5e-6 against 5e-4 allowed.
+// kind::f16 rejects mixed f16 x bf16 operands (measured: illegal instruction), so both are bf16.
 //
 // CTA = one 128 x BN output tile, 10 warps:
 //   warps 0-7  weight producers (two threads per row: each expands 32 of every 64 elements), then the
@@ -79,16 +83,22 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(const void * smem_ptr) {
     return addr | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
 }
 
-// ---------------------------------------------------------------- exact small-int -> fp16 helpers
-// (x & mask) | 0x6400 in each 16-bit lane is the fp16 value 1024 + x for 0 <= x < 1024
-__device__ __forceinline__ __half2 u32_as_h2(uint32_t v) { return *reinterpret_cast<__half2 *>(&v); }
-__device__ __forceinline__ uint32_t h2_as_u32(__half2 v) { return *reinterpret_cast<uint32_t *>(&v); }
+// ---------------------------------------------------------------- exact small-int -> bf16 helpers
+// (x & mask) | 0x4300 in each 16-bit lane is the bf16 value 128 + x for 0 <= x < 128 (7 stored mantissa bits)
+typedef __nv_bfloat162 wt2;                  // two weights / activations as the tensor core reads them
+__device__ __forceinline__ wt2 u32_as_h2(uint32_t v) { return *reinterpret_cast<wt2 *>(&v); }
+__device__ __forceinline__ uint32_t h2_as_u32(wt2 v) { return *reinterpret_cast<uint32_t *>(&v); }
+__device__ __forceinline__ wt2 f32_to_wt2(float f) { return __float2bfloat162_rn(f); }
 // bytes (b0,b1) or (b2,b3) of w spread to the low byte of each 16-bit lane
 __device__ __forceinline__ uint32_t spread01(uint32_t w) { return __byte_perm(w, 0, 0x4140); }
 __device__ __forceinline__ uint32_t spread23(uint32_t w) { return __byte_perm(w, 0, 0x4342); }
-__device__ __forceinline__ __half2 magic_to_h2(uint32_t lanes, float bias) {
-    // lanes hold integers < 1024 in each 16-bit half; returns (int - bias) exactly
-    return __hsub2(u32_as_h2(lanes | 0x64006400u), __float2half2_rn(1024.0f + bias));
+// the same with the byte's sign replicated into the high byte of the lane (prmt's sign-replicate selector bit,
+// which __byte_perm masks off): each lane = the byte sign-extended to 16 bits
+__device__ __forceinline__ uint32_t spread01_sx(uint32_t w) { uint32_t r; asm("prmt.b32 %0, %1, %2, 0x9180;" : "=r"(r) : "r"(w), "r"(0u)); return r; }
+__device__ __forceinline__ uint32_t spread23_sx(uint32_t w) { uint32_t r; asm("prmt.b32 %0, %1, %2, 0xB3A2;" : "=r"(r) : "r"(w), "r"(0u)); return r; }
+__device__ __forceinline__ wt2 magic_to_h2(uint32_t lanes, float bias) {
+    // lanes hold integers < 128 in each 16-bit half; returns (int - bias) exactly (|int - bias| < 256)
+    return __hsub2(u32_as_h2(lanes | 0x43004300u), f32_to_wt2(128.0f + bias));
 }
 
 } // namespace b200
@@ -120,7 +130,7 @@ __device__ __forceinline__ void slab_words(const uint8_t * s, uint32_t (&w)[N]) 
     for (int i = 0; i < N; i++) w[i] = t[W0 - 4 * C0 + i];
 }
 
-__device__ __forceinline__ void store_chunk(uint8_t * a_row, int row7, int c, __half2 v0, __half2 v1, __half2 v2, __half2 v3) {
+__device__ __forceinline__ void store_chunk(uint8_t * a_row, int row7, int c, wt2 v0, wt2 v1, wt2 v2, wt2 v3) {
     uint4 o;
     o.x = h2_as_u32(v0); o.y = h2_as_u32(v1); o.z = h2_as_u32(v2); o.w = h2_as_u32(v3);
     *reinterpret_cast<uint4 *>(a_row + ((c ^ row7) << 4)) = o;
@@ -149,11 +159,11 @@ template <bool HAS_QH> struct expander_k45 {
             if (hi != half) continue;
             int sc, mn;
             k4_scale_min(hdr[1], hdr[2], hdr[3], 2 * SUB + hi, sc, mn);
-            const __half2 d1 = __float2half2_rn(d * (float) sc);
-            const __half2 m1 = __float2half2_rn(-(dmin * (float) mn));
+            const wt2 d1 = f32_to_wt2(d * (float) sc);
+            const wt2 m1 = f32_to_wt2(-(dmin * (float) mn));
 #pragma unroll
             for (int cc = 0; cc < 4; cc++) {
-                __half2 v[4];
+                wt2 v[4];
 #pragma unroll
                 for (int j = 0; j < 4; j++) {
                     const uint32_t w  = q[2 * cc + (j >> 1)];
@@ -194,8 +204,8 @@ template <> struct expander<T_Q6_K> {
             const int l0 = 8 * (c & 3);
             const int sidx = 8 * h + 2 * st + (l0 >> 4);
             const int scv = (int) (int8_t) ((sc[sidx >> 2] >> (8 * (sidx & 3))) & 0xFFu);
-            const __half2 ds = __float2half2_rn(d * (float) scv);
-            __half2 v[4];
+            const wt2 ds = f32_to_wt2(d * (float) scv);
+            wt2 v[4];
 #pragma unroll
             for (int j = 0; j < 4; j++) {
                 const uint32_t wl = ql[8 * (c >> 2) + 2 * (c & 3) + (j >> 1)];
@@ -227,10 +237,10 @@ template <> struct expander<T_Q4_0> {
             uint32_t qs[4];
 #pragma unroll
             for (int i = 0; i < 4; i++) qs[i] = b == 0 ? __funnelshift_r(w[i], w[i + 1], 16) : w[5 + i];
-            const __half2 d = __float2half2_rn(f16_bits_to_f32(b == 0 ? w[0] : (w[4] >> 16)));
+            const wt2 d = f32_to_wt2(f16_bits_to_f32(b == 0 ? w[0] : (w[4] >> 16)));
 #pragma unroll
             for (int cc = 0; cc < 4; cc++) {
-                __half2 v[4];
+                wt2 v[4];
 #pragma unroll
                 for (int j = 0; j < 4; j++) {
                     const uint32_t x = qs[2 * (cc & 1) + (j >> 1)];
@@ -258,16 +268,21 @@ template <> struct expander<T_Q8_0> {
                 for (int cc = 0; cc < 4; cc++) store_zero_chunk(a_row, row7, 4 * b + cc);
                 continue;
             }
-            const __half2 d = __float2half2_rn(f16_bits_to_f32(b == 0 ? w[0] : (w[8] >> 16)));
+            // int8 q = (q & 127) - 128 * sign: bf16 holds 128 + (q & 127) exactly (the magic), the sign bit of the
+            // sign-extended lane, masked at bit 14, IS bf16 2.0 -> t2 = -128 d (1 + sign), v = (128 + (q & 127)) d + t2:
+            // every term exact, one rounding
+            const wt2 d = f32_to_wt2(f16_bits_to_f32(b == 0 ? w[0] : (w[8] >> 16)));
+            const wt2 dm64 = __hmul2(d, f32_to_wt2(-64.0f)), dm128 = __hmul2(d, f32_to_wt2(-128.0f));
 #pragma unroll
             for (int cc = 0; cc < 4; cc++) {
-                __half2 v[4];
+                wt2 v[4];
 #pragma unroll
                 for (int j = 0; j < 4; j++) {
                     const int wi = 2 * cc + (j >> 1);
                     const uint32_t x = b == 0 ? __funnelshift_r(w[wi], w[wi + 1], 16) : w[9 + wi];
-                    const uint32_t lanes = (((j & 1) ? spread23(x) : spread01(x)) ^ 0x00800080u) & 0x00FF00FFu;
-                    v[j] = __hmul2(magic_to_h2(lanes, 128.0f), d);
+                    const uint32_t sx = (j & 1) ? spread23_sx(x) : spread01_sx(x);
+                    const wt2 t2 = __hfma2(u32_as_h2(sx & 0x40004000u), dm64, dm128);
+                    v[j] = __hfma2(u32_as_h2((sx & 0x007F007Fu) | 0x43004300u), d, t2);
                 }
                 store_chunk(a_row, row7, 4 * b + cc, v[0], v[1], v[2], v[3]);
             }
@@ -492,9 +507,9 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b, const __g
     } else {
         // ===================================================== MMA issuer
         if (lane == 0) {
-            // instruction descriptor: D=f32, A=f16, B=f16 (kind::f16 rejects mixed f16 x bf16 operands: measured,
+            // instruction descriptor: D=f32, A=bf16, B=bf16 (kind::f16 rejects mixed f16 x bf16 operands: measured,
             // illegal instruction), both K-major, N=BN, M=128
-            constexpr uint32_t idesc = (1u << 4) | (0u << 7) | (0u << 10) | ((uint32_t) (BN >> 3) << 17) | ((uint32_t) (MMQ_BM >> 4) << 24);
+            constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t) (BN >> 3) << 17) | ((uint32_t) (MMQ_BM >> 4) << 24);
             for (int kt = 0; kt < nkt; kt++) {
                 const int st = kt % ST;
                 mbar_wait(&full[st], (uint32_t) ((kt / ST) & 1));
@@ -519,15 +534,15 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b, const __g
     }
 }
 
-// f32 [n, k] (row stride in bytes) -> fp16 [n, k] packed, RN
-__global__ void __launch_bounds__(256) k_f32_to_f16(const uint8_t * __restrict__ x, int64_t x_row_stride, int64_t k, uint16_t * __restrict__ y) {
+// f32 [n, k] (row stride in bytes) -> bf16 [n, k] packed, RN (the full exponent range of f32 survives)
+__global__ void __launch_bounds__(256) k_f32_to_bf16(const uint8_t * __restrict__ x, int64_t x_row_stride, int64_t k, uint16_t * __restrict__ y) {
     const int64_t row = blockIdx.y;
     const int64_t i = ((int64_t) blockIdx.x * 256 + threadIdx.x) * 4;
     if (i >= k) return;
     const float * xr = reinterpret_cast<const float *>(x + row * x_row_stride);
     uint16_t * yr = y + row * k;
     auto cvt = [](float f) -> uint16_t {
-        return __half_as_ushort(__float2half_rn(f));
+        return __bfloat16_as_ushort(__float2bfloat16_rn(f));
     };
     if (i + 3 < k && (reinterpret_cast<uintptr_t>(xr + i) & 15) == 0) {
         const float4 v = *reinterpret_cast<const float4 *>(xr + i);

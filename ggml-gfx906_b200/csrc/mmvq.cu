@@ -13,6 +13,7 @@
 #include "mmvq_batch.cuh"
 #include "mmvq_cols.cuh"
 
+#include <cstring>
 #include <vector>
 
 namespace b200 {
@@ -205,7 +206,8 @@ extern "C" int b200_mul_mat_ex(int type_a, const void * a_dev, const int64_t ne_
 
 // ---------------------------------------------------------------- a list of MUL_MAT nodes
 extern "C" size_t b200_mul_mat_batch_workspace_size(const b200_mul_mat_node * nodes, int64_t count) {
-    // the largest single-node need + one q8 activation record per decode node (persistent launches)
+    // the largest single-node need + one q8 activation record per decode node (persistent launches) + the
+    // completion counters of the (at most three, one per format family) launches of a flush
     size_t need = 256, acts = 0;
     for (int64_t i = 0; i < count; i++) {
         const size_t s = b200_mul_mat_workspace_size(nodes[i].type_a, nodes[i].ne_a, nodes[i].ne_b);
@@ -216,56 +218,90 @@ extern "C" size_t b200_mul_mat_batch_workspace_size(const b200_mul_mat_node * no
             acts += per_col > tile ? per_col : tile;
         }
     }
-    return need + acts + 256;
+    return need + acts + 3 * BATCH_DONE_BYTES + 256;
 }
 
-// Pointer ranges a pending persistent launch reads (x) and writes (dst): a node joins the launch only if
-// it neither reads nor writes what an earlier node of the launch writes, nor writes what one reads.
+// What the pending launches read (x) and write (dst), indexed by address: a new node is checked against it for
+// read-after-write, write-after-write and write-after-read.  Intervals are kept sorted by their start; none is longer
+// than `maxlen`, so a query only walks the few neighbours that can overlap (a decode pass is ~230 nodes and this runs
+// on the host every step outside a CUDA graph).
 namespace {
-struct range_set {
-    struct iv { uintptr_t lo, hi; };
+struct hazard_index {
+    struct iv { uintptr_t lo, hi; short owner, idx; };          // owner: 0..2 = format family builder, 3 = the MMA list kernel
     std::vector<iv> v;
-    uintptr_t lo = ~(uintptr_t) 0, hi = 0;
-    void clear() { v.clear(); lo = ~(uintptr_t) 0; hi = 0; }
-    void add(uintptr_t a, uintptr_t b) { v.push_back({a, b}); if (a < lo) lo = a; if (b > hi) hi = b; }
-    bool hits(uintptr_t a, uintptr_t b) const {
-        if (a >= hi || b <= lo) return false;                 // outside the hull: the common case
-        for (const iv & i : v) if (a < i.hi && i.lo < b) return true;
-        return false;
+    uintptr_t maxlen = 0;
+    void clear() { v.clear(); maxlen = 0; }
+    void add(uintptr_t lo, uintptr_t hi, int owner, int idx) {
+        if (hi - lo > maxlen) maxlen = hi - lo;
+        size_t a = 0, b = v.size();
+        while (a < b) { const size_t mid = (a + b) / 2; if (v[mid].lo < lo) a = mid + 1; else b = mid; }
+        // the same range again (q/k/v read one x): keep the latest owner index only
+        if (a < v.size() && v[a].lo == lo && v[a].hi == hi && v[a].owner == owner) { if (idx > v[a].idx) v[a].idx = (short) idx; return; }
+        v.insert(v.begin() + (ptrdiff_t) a, iv{ lo, hi, (short) owner, (short) idx });
     }
+    // every interval overlapping [lo, hi): fn(owner, idx)
+    template <typename F> void query(uintptr_t lo, uintptr_t hi, F fn) const {
+        size_t a = 0, b = v.size();
+        while (a < b) { const size_t mid = (a + b) / 2; if (v[mid].lo < hi) a = mid + 1; else b = mid; }   // first with lo >= hi
+        for (size_t i = a; i-- > 0; ) {
+            if (v[i].lo + maxlen <= lo) break;               // nothing further left can reach lo
+            if (v[i].hi > lo) fn((int) v[i].owner, (int) v[i].idx);
+        }
+    }
+};
+struct batch_state {
+    batch_builder * fam[3];
+    cols_builder  * cols;
+    hazard_index reads, writes;
+    batch_state() { for (int f = 0; f < 3; f++) fam[f] = new batch_builder(f); cols = new cols_builder(); }
 };
 }
 
-extern "C" int b200_mul_mat_batch(const b200_mul_mat_node * nodes, int64_t count,
-                                  void * workspace_dev, size_t workspace_bytes, void * stream) {
+// plan != nullptr: dry run -- nothing is launched, no device is touched; plan[3 i .. 3 i + 2] = (launch group of node i,
+// list index of the node it waits for inside that group or -1, route: 0 per-node call, 1 persistent list, 2 MMA list)
+static int run_list(const b200_mul_mat_node * nodes, int64_t count, void * workspace_dev, size_t workspace_bytes, void * stream,
+                    int32_t * plan) {
     if (count < 0 || (count > 0 && !nodes)) return B200_ERR_SHAPE;
+    const bool dry = plan != nullptr;
+    int group = 0;
+    if (dry) { workspace_dev = (void *) (uintptr_t) 0x1000; workspace_bytes = (size_t) 1 << 40; }
     cudaStream_t st = (cudaStream_t) stream;
-    const bool persistent = !env_int("GGML_B200_NO_BATCH_KERNEL", 0);
-    // one builder (28 KB parameter block, reused) per format family = kernel instantiation; the nodes of a
-    // pending set are independent, so sorting them into per-family launches keeps the semantics
-    static thread_local batch_builder * fam_bb[3] = { nullptr, nullptr, nullptr };
-    static thread_local range_set reads, writes;
-    static thread_local cols_builder * cols_bb = nullptr;       // nodes with 2..8 columns (Q4_K / Q5_K): the MMA list kernel
-    if (!cols_bb) cols_bb = new cols_builder();
-    cols_bb->reset();
+    const bool persistent = !b200_option(B200_OPT_NO_BATCH_KERNEL);
+    const bool chain = !b200_option(B200_OPT_NO_CHAIN);
+    // one builder (28 KB parameter block, reused) per format family = kernel instantiation, one for the MMA list
+    // kernel (2..8 columns); per thread, because different backends may be driven from different threads
+    static thread_local batch_state * S = nullptr;
+    if (!S) S = new batch_state();
+    batch_builder ** fam_bb = S->fam;
+    cols_builder * cols_bb = S->cols;
+    hazard_index & reads = S->reads, & writes = S->writes;
     static const int use_cols = env_int("GGML_B200_COLS_KERNEL", 1);
-    if (!fam_bb[0]) { for (int f = 0; f < 3; f++) fam_bb[f] = new batch_builder(f); }
+    static const int colmax = env_int("GGML_B200_BATCH_COLS", 8);
     ws_cursor cur;
     cur.reset((uint8_t *) workspace_dev, workspace_bytes);
     for (int f = 0; f < 3; f++) fam_bb[f]->reset();
+    cols_bb->reset();
     reads.clear(); writes.clear();
-    const int grid = current_caps().sm_count;
+    const int grid = dry ? 148 : current_caps().sm_count;
+    auto nothing_pending = [&]() { return fam_bb[0]->empty() && fam_bb[1]->empty() && fam_bb[2]->empty() && cols_bb->empty(); };
     auto flush = [&]() -> int {
         reads.clear(); writes.clear();
         int rc = B200_OK;
+        if (dry) {
+            if (!nothing_pending()) group++;
+            for (int f = 0; f < 3; f++) fam_bb[f]->reset();
+            cols_bb->reset();
+            cur.reset((uint8_t *) workspace_dev, workspace_bytes);
+            return rc;
+        }
         for (int f = 0; f < 3 && rc == B200_OK; f++) {
             batch_builder * bb = fam_bb[f];
             if (bb->empty()) continue;
-            // one node (a dependent chain's link): small ones take the per-node decode kernel (same per-row
+            // one node (a launch of its own): small ones take the per-node decode kernel (same per-row
             // arithmetic, one launch instead of two); from ~4 MB of Q4_K/Q5_K weights the persistent pair is
             // faster even alone (4096x11008: 11.2 us against 17.4 us, profiles/r01m_single_probe.txt).
-            // GGML_B200_BATCH_SINGLE=1 / 0 forces the persistent / the per-node kernel.
-            const int single_mode = env_int("GGML_B200_BATCH_SINGLE", -1);
+            // option batch_single = 1 / 0 forces the persistent / the per-node kernel.
+            const int single_mode = b200_option(B200_OPT_BATCH_SINGLE);
             const batch_node nd = bb->args.nodes[0];
             const bool single_persistent = single_mode >= 0 ? single_mode != 0
                                          : (f == 0 && (int64_t) nd.m * nd.row_bytes >= (int64_t) 4 << 20);
@@ -274,6 +310,16 @@ extern "C" int b200_mul_mat_batch(const b200_mul_mat_node * nodes, int64_t count
                 if (rc == B200_STREAM_NOT_APPLICABLE) rc = batch_launch(*bb, st);
             } else {
                 rc = batch_launch(*bb, st);
+            }
+            if (rc == B200_STREAM_NOT_APPLICABLE) {
+                // rows too long for two ring stages: the nodes of this builder one by one, in list order
+                rc = B200_OK;
+                for (int j = 0; j < bb->args.count && rc == B200_OK; j++) {
+                    const b200_mul_mat_node & o = nodes[bb->orig[j]];
+                    const batch_node & bn = bb->args.nodes[j];
+                    const int64_t ne_b[4] = { o.ne_b[0], 1, 1, 1 };            // an entry is one column of its node
+                    rc = b200_mul_mat_ex(o.type_a, o.a_dev, o.ne_a, o.nb_a, bn.x, ne_b, o.nb_b, bn.dst, workspace_dev, workspace_bytes, o.flags, stream);
+                }
             }
             bb->reset();
         }
@@ -288,64 +334,97 @@ extern "C" int b200_mul_mat_batch(const b200_mul_mat_node * nodes, int64_t count
         // a few columns (decode at batch 2..8) ride the persistent launch as one entry per column, back to back:
         // the CTA streams its slab of W once from HBM and finds it in L2 for the other columns (a node's slab per
         // CTA is 64-200 KB), which beats the per-node kernel's two launches per MUL_MAT up to GGML_B200_BATCH_COLS
-        static const int colmax = env_int("GGML_B200_BATCH_COLS", 8);
         const int64_t ncols = nd.ne_b[1];
-        const bool plain = persistent && type_is_quant(nd.type_a) && nd.ne_b[0] == k && ncols >= 1 && (ncols == 1 || ncols <= colmax) &&
+        const bool flat = nd.ne_b[0] == k && nd.ne_a[2] == 1 && nd.ne_a[3] == 1 && nd.ne_b[2] == 1 && nd.ne_b[3] == 1 &&
+                          nd.nb_a[0] == (size_t) type_bytes(nd.type_a) && nd.nb_b[0] == sizeof(float);
+        const bool plain = persistent && flat && type_is_quant(nd.type_a) && ncols >= 1 && (ncols == 1 || ncols <= colmax) &&
                            (ncols == 1 || nd.nb_b[1] % 16 == 0) &&
-                           nd.ne_a[2] == 1 && nd.ne_a[3] == 1 && nd.ne_b[2] == 1 && nd.ne_b[3] == 1 &&
-                           nd.nb_a[0] == (size_t) type_bytes(nd.type_a) && nd.nb_b[0] == sizeof(float) &&
                            batch_node_ok(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, nd.b_dev);
-        if (persistent && use_cols && ncols >= 2 && nd.ne_b[0] == k && nd.ne_a[2] == 1 && nd.ne_a[3] == 1 && nd.ne_b[2] == 1 && nd.ne_b[3] == 1 &&
-            nd.nb_a[0] == (size_t) type_bytes(nd.type_a) && nd.nb_b[0] == sizeof(float) &&
-            cols_node_ok(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, nd.b_dev, (int64_t) nd.nb_b[1], ncols)) {
-            const uintptr_t x0 = (uintptr_t) nd.b_dev, x1 = x0 + (size_t) (ncols - 1) * nd.nb_b[1] + (size_t) k * 4;
-            const uintptr_t d0 = (uintptr_t) nd.dst_dev, d1 = d0 + (size_t) m * ncols * 4;
-            if (cols_bb->full() || writes.hits(x0, x1) || writes.hits(d0, d1) || reads.hits(d0, d1)) {
-                const int rc = flush();
-                if (rc) return rc;
-            }
+        const bool to_cols = persistent && use_cols && flat && ncols >= 2 &&
+                             cols_node_ok(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, nd.b_dev, (int64_t) nd.nb_b[1], ncols);
+        if (!to_cols && !plain) {
+            int rc = flush();
+            if (rc) return rc;
+            if (dry) { plan[3 * i] = group++; plan[3 * i + 1] = -1; plan[3 * i + 2] = 0; continue; }
+            rc = b200_mul_mat_ex(nd.type_a, nd.a_dev, nd.ne_a, nd.nb_a, nd.b_dev, nd.ne_b, nd.nb_b, nd.dst_dev,
+                                 workspace_dev, workspace_bytes, nd.flags, stream);
+            if (rc) return rc;
+            continue;
+        }
+        const uintptr_t x0 = (uintptr_t) nd.b_dev, x1 = x0 + (size_t) (ncols - 1) * nd.nb_b[1] + (size_t) k * 4;
+        const uintptr_t d0 = (uintptr_t) nd.dst_dev, d1 = d0 + (size_t) m * ncols * 4;
+        const int owner = to_cols ? 3 : batch_family(nd.type_a);
+        // hazards against what is pending: inside the same persistent launch they become a dependency (dep = the
+        // latest such node; a CTA finishes nodes in order, so its counter covers the earlier ones), anywhere else
+        // (another launch of this flush, the MMA list kernel, several columns, chaining switched off) they cut the list
+        int dep = -1;
+        bool cut = false, x_written = false;
+        auto on_hit = [&](int o, int idx) { if (o != owner || owner == 3 || !chain || ncols != 1) cut = true; else if (idx > dep) dep = idx; };
+        writes.query(x0, x1, [&](int o, int idx) { x_written = true; on_hit(o, idx); });      // read after write
+        writes.query(d0, d1, on_hit);                                                          // write after write
+        reads.query(d0, d1, on_hit);                                                           // write after read
+        if (cut) {
+            const int rc = flush();
+            if (rc) return rc;
+            dep = -1; x_written = false;
+        }
+        if (to_cols) {
+            if (cols_bb->full()) { const int rc = flush(); if (rc) return rc; }
             bool ok = cols_bb->add(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, nd.b_dev, (int64_t) nd.nb_b[1], ncols, nd.dst_dev, cur);
-            if (!ok && !(fam_bb[0]->empty() && fam_bb[1]->empty() && fam_bb[2]->empty() && cols_bb->empty())) {
+            if (!ok && !nothing_pending()) {
                 const int rc = flush();
                 if (rc) return rc;
                 ok = cols_bb->add(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, nd.b_dev, (int64_t) nd.nb_b[1], ncols, nd.dst_dev, cur);
             }
-            if (ok) { reads.add(x0, x1); writes.add(d0, d1); continue; }
+            if (ok) {
+                reads.add(x0, x1, 3, cols_bb->args.count - 1); writes.add(d0, d1, 3, cols_bb->args.count - 1);
+                if (dry) { plan[3 * i] = group; plan[3 * i + 1] = -1; plan[3 * i + 2] = 2; }
+                continue;
+            }
+            if (!plain) {
+                int rc = flush();
+                if (rc) return rc;
+                if (dry) { plan[3 * i] = group++; plan[3 * i + 1] = -1; plan[3 * i + 2] = 0; continue; }
+                rc = b200_mul_mat_ex(nd.type_a, nd.a_dev, nd.ne_a, nd.nb_a, nd.b_dev, nd.ne_b, nd.nb_b, nd.dst_dev,
+                                     workspace_dev, workspace_bytes, nd.flags, stream);
+                if (rc) return rc;
+                continue;
+            }
         }
-        if (plain) {
-            const uintptr_t x0 = (uintptr_t) nd.b_dev, x1 = x0 + (size_t) (ncols - 1) * nd.nb_b[1] + (size_t) k * 4;
-            const uintptr_t d0 = (uintptr_t) nd.dst_dev, d1 = d0 + (size_t) m * ncols * 4;
-            batch_builder * bb = fam_bb[batch_family(nd.type_a)];
-            if (writes.hits(x0, x1) || writes.hits(d0, d1) || reads.hits(d0, d1)) {
+        batch_builder * bb = fam_bb[batch_family(nd.type_a)];
+        const bool cw = (nd.flags & B200_MUL_MAT_CONST_WEIGHTS) != 0;
+        int64_t c = 0;
+        for (; c < ncols; c++) {
+            const float * xc = (const float *) ((const uint8_t *) nd.b_dev + c * nd.nb_b[1]);
+            float * dc = nd.dst_dev + c * m;
+            if (bb->full()) {
                 const int rc = flush();
                 if (rc) return rc;
+                dep = -1; x_written = false;
             }
-            const bool cw = (nd.flags & B200_MUL_MAT_CONST_WEIGHTS) != 0;
-            int64_t c = 0;
-            for (; c < ncols; c++) {
-                const float * xc = (const float *) ((const uint8_t *) nd.b_dev + c * nd.nb_b[1]);
-                float * dc = nd.dst_dev + c * m;
-                if (bb->full()) {
-                    const int rc = flush();
-                    if (rc) return rc;
-                }
-                bool ok = bb->add(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, xc, dc, cw, grid, cur);
-                if (!ok && !(fam_bb[0]->empty() && fam_bb[1]->empty() && fam_bb[2]->empty() && cols_bb->empty())) {  // workspace full: launch what is pending, start over
-                    const int rc = flush();
-                    if (rc) return rc;
-                    ok = bb->add(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, xc, dc, cw, grid, cur);
-                }
-                if (!ok) break;
-            }
-            if (c == ncols) { reads.add(x0, x1); writes.add(d0, d1); continue; }
-            if (c > 0) {                              // some columns are pending and the rest has no room: not reachable with a
-                const int rc = flush();               // workspace of b200_mul_mat_batch_workspace_size; finish them, then recompute the node
+            bool ok = bb->add(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, xc, dc, cw, grid, cur, dep, x_written && dep >= 0, (int) i);
+            if (!ok && !nothing_pending()) {                   // workspace full: launch what is pending, start over
+                const int rc = flush();
                 if (rc) return rc;
+                dep = -1; x_written = false;
+                ok = bb->add(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, xc, dc, cw, grid, cur, -1, false, (int) i);
             }
-            // no room even for one record: the per-node path below reports the workspace error
+            if (!ok) break;
         }
+        if (c == ncols) {
+            const int idx = bb->args.count - 1;
+            reads.add(x0, x1, owner, idx); writes.add(d0, d1, owner, idx);
+            if (dry) {
+                const int dp = bb->args.nodes[idx].dep;
+                plan[3 * i] = group; plan[3 * i + 1] = dp >= 0 ? bb->orig[dp] : -1; plan[3 * i + 2] = 1;
+            }
+            continue;
+        }
+        // no room even for one record (not reachable with a workspace of b200_mul_mat_batch_workspace_size): finish
+        // what is pending, then the per-node path reports the workspace error or computes the node
         int rc = flush();
         if (rc) return rc;
+        if (dry) { plan[3 * i] = group++; plan[3 * i + 1] = -1; plan[3 * i + 2] = 0; continue; }
         rc = b200_mul_mat_ex(nd.type_a, nd.a_dev, nd.ne_a, nd.nb_a, nd.b_dev, nd.ne_b, nd.nb_b, nd.dst_dev,
                              workspace_dev, workspace_bytes, nd.flags, stream);
         if (rc) return rc;
@@ -353,5 +432,57 @@ extern "C" int b200_mul_mat_batch(const b200_mul_mat_node * nodes, int64_t count
     return flush();
 }
 
-// tuning aid used by tools/: every fused decode launch writes 8 globaltimer stamps per CTA into buf
+extern "C" int b200_mul_mat_batch(const b200_mul_mat_node * nodes, int64_t count,
+                                  void * workspace_dev, size_t workspace_bytes, void * stream) {
+    return run_list(nodes, count, workspace_dev, workspace_bytes, stream, nullptr);
+}
+
+// How b200_mul_mat_batch would issue the list (host arithmetic only; no device needed).
+extern "C" int b200_mul_mat_batch_plan(const b200_mul_mat_node * nodes, int64_t count, int32_t * plan) {
+    if (!plan) return B200_ERR_SHAPE;
+    return run_list(nodes, count, nullptr, 0, nullptr, plan);
+}
+
+// ---------------------------------------------------------------- the list kernels' quantizers on their own
+// (tests compare their output bit for bit with quantize_row_q8_1_ref; the layouts are documented in the header)
+extern "C" size_t b200_acts_record_bytes(int64_t k) { return k > 0 ? batch_acts_record_bytes(k) : 0; }
+extern "C" size_t b200_acts_columns_bytes(int64_t k, int64_t n) { return k > 0 ? cols_ws_bytes(k, n) : 0; }
+
+extern "C" int b200_quantize_acts_record(const float * x_dev, int64_t k, void * record_dev, void * stream) {
+    if (k < 256 || k % 256 != 0 || k > 32768) return B200_ERR_SHAPE;
+    if (((uintptr_t) x_dev & 15) || ((uintptr_t) record_dev & 127)) return B200_ERR_STRIDE;
+    static thread_local batch_args * a = nullptr;
+    if (!a) a = new batch_args();
+    a->count = 1; a->kmax = (int) k; a->done = nullptr;
+    batch_node & nd = a->nodes[0];
+    memset(&nd, 0, sizeof(nd));
+    nd.x = x_dev; nd.acts = (const uint8_t *) record_dev; nd.k = (int) k; nd.qflags = BATCH_Q_PRE | BATCH_Q_LOAD; nd.dep = -1;
+    const dim3 grid((unsigned) ceil_div(k / 32, 8), 1);
+    k_quantize_batch<<<grid, 256, 0, (cudaStream_t) stream>>>(*a);
+    b200_count_launch(1);
+    B200_RETURN_IF_LAUNCH_FAILED();
+    return B200_OK;
+}
+
+extern "C" int b200_quantize_acts_columns(const float * x_dev, size_t x_row_stride_bytes, int64_t k, int64_t n, void * columns_dev, void * stream) {
+    if (k < 256 || k % 256 != 0 || n < 1 || n > COLS_N) return B200_ERR_SHAPE;
+    if (((uintptr_t) x_dev & 3) || (x_row_stride_bytes & 3) || ((uintptr_t) columns_dev & 127)) return B200_ERR_STRIDE;
+    static thread_local cols_args * a = nullptr;
+    if (!a) a = new cols_args();
+    a->count = 1; a->units = 0; a->kmax = (int) k; a->pad = 0;
+    cols_node & nd = a->nodes[0];
+    memset(&nd, 0, sizeof(nd));
+    nd.x = x_dev; nd.k = (int) k; nd.n = (int) n; nd.x_stride = (int) (x_row_stride_bytes / 4); nd.quantize = 1;
+    nd.yq = (int8_t *) columns_dev;
+    nd.yds = (float2 *) ((uint8_t *) columns_dev + (((size_t) COLS_N * k + 127) & ~(size_t) 127));
+    const dim3 grid((unsigned) ceil_div(k / 32, 8), 1, COLS_N);
+    k_quantize_cols<<<grid, 256, 0, (cudaStream_t) stream>>>(*a);
+    b200_count_launch(1);
+    B200_RETURN_IF_LAUNCH_FAILED();
+    return B200_OK;
+}
+
+#ifdef B200_TUNING
+// tuning builds only: every fused decode launch writes 8 globaltimer stamps per CTA into buf
 extern "C" __attribute__((visibility("default"))) void b200_debug_timestamps(void * buf) { g_fused_dbg = (unsigned long long *) buf; }
+#endif

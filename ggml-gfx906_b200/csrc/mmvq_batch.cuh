@@ -27,9 +27,20 @@
 //         computes it (row-split results stay bit-identical).  Every consumer warp observes every stage
 //         (mbarrier phases are parity bits: a waiter that skipped stages could mistake phase n-2 for n).
 //
-// Nodes of one launch must be independent (no node reads what another writes): b200_mul_mat_batch checks
-// the pointer ranges and cuts the list where they are not.
+// Dependent nodes (a decode pass is a chain: wo reads what q/k/v wrote, gate/up read wo ...) ride in the SAME launch:
+// a node that reads (or overwrites) what an earlier node of the launch writes carries that node's index as `dep`.
+//   * every CTA bumps a per-node completion counter in global memory (release, gpu scope) when its consumer warps
+//     have stored their last row of a node that something depends on;
+//   * the activation-producer warp of a dependent node acquire-spins on done[dep] == gridDim.x before it publishes
+//     the node to the consumers, which then quantize x = the producer node's dst (L2 -> registers -> the
+//     activation buffer, the same q8_1 values and layout as k_quantize_batch) themselves;
+//   * weights keep streaming through the ring meanwhile, so the cost of a chain link is one L2 round trip for the
+//     flag, one for x and the quantization (~1 us), not a kernel boundary (7-17 us measured, profiles/r01m).
+// The grid is one CTA per SM with 226 KB of shared memory each: all CTAs are co-resident, so the spins terminate.
+// The role CUDA-graph capture plays in the reference (src/ggml-cuda/ggml-cuda.cu:2876-3041) is played by this.
+// b200_mul_mat_batch derives `dep` from the pointer ranges; hazards between different launches still cut the list.
 #pragma once
+#include <vector>
 #include "mmvq_fused.cuh"
 
 namespace b200 {
@@ -53,16 +64,33 @@ struct batch_node {                      // 64 bytes
     int   m, k;
     int   row_bytes;
     int   rows_per_cta;                  // slab height (even)
-    unsigned char type, R, W, G, contiguous, quantize, pad[2];   // quantize: this node's x is not the previous node's
+    unsigned char type, R, W, G, contiguous, qflags;             // qflags: BATCH_Q_*
+    short dep;                                                   // index of the node of this launch to wait for, -1: none
 };
+constexpr int BATCH_Q_PRE    = 1;    // k_quantize_batch writes this node's q8 record (nd.acts) before the launch
+constexpr int BATCH_Q_LOAD   = 2;    // the activation producer bulk-copies nd.acts into the activation buffer
+constexpr int BATCH_Q_INK    = 4;    // the consumers quantize nd.x (written by node `dep` of this launch) into the buffer
+constexpr int BATCH_Q_SAME   = 8;    // same x, k and format as the previous node: the consumers keep their registers
+constexpr int BATCH_Q_SIGNAL = 16;   // a later node waits for this one: CTAs bump done[i] after their last row
 static_assert(sizeof(batch_node) == 64, "batch_node is part of the kernel parameter block");
 
 struct batch_args {
     int count, S, slot_stride, acts_stride;
     int off_part, off_acts, off_slots, const_weights;
     int NB, kmax, nwc, pad;
+    unsigned * done;                     // per-node completion counters (workspace; zeroed by k_quantize_batch)
     batch_node nodes[BATCH_MAX_NODES];
 };
+
+// gpu-scope release / acquire on the completion counters
+__device__ __forceinline__ void red_release_gpu_add(unsigned * p, unsigned v) {
+    asm volatile("red.release.gpu.global.add.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned * p) {
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 
 // mbarrier ops on precomputed shared-window addresses (no generic -> shared conversion per call)
 __device__ __forceinline__ void mbar_wait_a(uint32_t bar, uint32_t parity) {
@@ -88,8 +116,8 @@ __device__ __forceinline__ uint32_t batch_acts_bytes(int k) { return (uint32_t) 
 // (measured: 23 % of the kernel).  Instead every lane of a warp keeps ONE descriptor (node base + lane),
 // fetched 32 nodes at a time, and the warp broadcasts the current node's fields by shuffle.
 struct node_r {
-    const uint8_t * w; float * dst; const uint8_t * acts; int64_t row_stride;
-    int m, k, row_bytes, rows_per_cta, type, R, W, G, contiguous;
+    const uint8_t * w; const float * x; float * dst; const uint8_t * acts; int64_t row_stride;
+    int m, k, row_bytes, rows_per_cta, type, R, W, G, contiguous, qflags, dep;
 };
 __device__ __forceinline__ uint64_t shfl_u64(uint64_t v, int src) {
     const uint32_t lo = __shfl_sync(0xFFFFFFFFu, (uint32_t) v, src), hi = __shfl_sync(0xFFFFFFFFu, (uint32_t) (v >> 32), src);
@@ -104,13 +132,15 @@ struct node_cache {
             base = i & ~31;
             const int j = base + lane < a.count ? base + lane : a.count - 1;
             const batch_node & nd = a.nodes[j];
-            c.w = nd.w; c.dst = nd.dst; c.acts = nd.acts; c.row_stride = nd.row_stride;
+            c.w = nd.w; c.x = nd.x; c.dst = nd.dst; c.acts = nd.acts; c.row_stride = nd.row_stride;
             c.m = nd.m; c.k = nd.k; c.row_bytes = nd.row_bytes; c.rows_per_cta = nd.rows_per_cta;
             c.type = nd.type; c.R = nd.R; c.W = nd.W; c.G = nd.G; c.contiguous = nd.contiguous;
+            c.qflags = nd.qflags; c.dep = nd.dep;
         }
         const int src = i & 31;
         node_r r;
         r.w = reinterpret_cast<const uint8_t *>(shfl_u64(reinterpret_cast<uint64_t>(c.w), src));
+        r.x = reinterpret_cast<const float *>(shfl_u64(reinterpret_cast<uint64_t>(c.x), src));
         r.dst = reinterpret_cast<float *>(shfl_u64(reinterpret_cast<uint64_t>(c.dst), src));
         r.acts = reinterpret_cast<const uint8_t *>(shfl_u64(reinterpret_cast<uint64_t>(c.acts), src));
         r.row_stride = (int64_t) shfl_u64((uint64_t) c.row_stride, src);
@@ -118,6 +148,8 @@ struct node_cache {
         r.row_bytes = __shfl_sync(0xFFFFFFFFu, c.row_bytes, src); r.rows_per_cta = __shfl_sync(0xFFFFFFFFu, c.rows_per_cta, src);
         const int packed = __shfl_sync(0xFFFFFFFFu, c.type | (c.R << 8) | (c.W << 16) | (c.G << 20) | (c.contiguous << 24), src);
         r.type = packed & 0xFF; r.R = (packed >> 8) & 0xFF; r.W = (packed >> 16) & 0xF; r.G = (packed >> 20) & 0xF; r.contiguous = (packed >> 24) & 1;
+        const int packed2 = __shfl_sync(0xFFFFFFFFu, c.qflags | (c.dep << 8), src);
+        r.qflags = packed2 & 0xFF; r.dep = packed2 >> 8;              // arithmetic shift: dep = -1 survives
         return r;
     }
 };
@@ -140,7 +172,8 @@ __global__ void __launch_bounds__(256) k_quantize_batch(const __grid_constant__ 
     const batch_node & nd = a.nodes[blockIdx.y];
     const int kb = blockIdx.x * 8 + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
-    if (!nd.quantize || kb * 32 >= nd.k) return;
+    if (blockIdx.x == 0 && threadIdx.x == 0 && a.done) a.done[blockIdx.y] = 0u;
+    if (!(nd.qflags & BATCH_Q_PRE) || kb * 32 >= nd.k) return;
     const float x = __ldg(nd.x + kb * 32 + lane);
     const float amax = warp_max(fabsf(x));
     const float d  = __fdiv_rn(amax, 127.0f);
@@ -165,13 +198,59 @@ struct cnode {
     int type, R, W, G;
     int skew0, rs16;          // formats whose rows are not 16-byte aligned: (address of slab row i) % 16 = (skew0 + i * rs16) % 16
     int contiguous;
+    int qflags;               // BATCH_Q_*
+    const float * x;          // BATCH_Q_INK: the f32 activations to quantize (another node's dst)
+    unsigned * signal;        // BATCH_Q_SIGNAL: this node's completion counter
 };
 static_assert(sizeof(cnode) <= BATCH_AHDR, "consumer header");
 
 // ---------------------------------------------------------------- consumer: one node
 // cc: running count of row pairs ("chunks") this CTA has seen; chunk j belongs to group j % G.
+// The consumers of a dependent node quantize its activations themselves: x (another node's dst, complete and visible:
+// the activation producer acquired its counter before publishing this node) -> q8_1 values in the activation buffer,
+// bit for bit what k_quantize_batch writes (same arithmetic, same swizzle).  8 lanes per 32-value block, all consumer
+// warps; x is read past L1 (it was written by other SMs during this launch).
+__device__ __forceinline__ void batch_quantize_ink(const float * x, const int k, uint8_t * actbuf, const int cw, const int lane, const int nwc) {
+    int8_t * q = reinterpret_cast<int8_t *>(actbuf);
+    float  * yd = reinterpret_cast<float *>(actbuf + k);
+    const int nblk32 = k >> 5;
+    const int sub = lane >> 3, l8 = lane & 7;
+    constexpr int U = 4;                                      // loads in flight per lane
+    for (int blk0 = cw * 4 + sub; blk0 < nblk32; blk0 += nwc * 4 * U) {
+        float4 vv[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const int blk = blk0 + u * nwc * 4;
+            if (blk < nblk32) vv[u] = __ldcg(reinterpret_cast<const float4 *>(x + blk * 32 + l8 * 4));
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const int blk = blk0 + u * nwc * 4;
+            if (blk < nblk32) {                               // (k % 128 == 0: uniform over each group of 8 lanes)
+                const float4 v = vv[u];
+                float amax = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
+#pragma unroll
+                for (int o = 1; o < 8; o <<= 1) amax = fmaxf(amax, __shfl_xor_sync(0xFFFFFFFFu, amax, o));
+                const float d  = __fdiv_rn(amax, 127.0f);
+                const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+                const float xs[4] = { v.x, v.y, v.z, v.w };
+                uint32_t packed = 0;
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const float r  = roundf(__fmul_rn(xs[j], id));
+                    const int   qi = fabsf(r) < 2147483648.0f ? (int) r : (int) 0x80000000;
+                    packed |= (uint32_t) (qi & 0xFF) << (8 * j);
+                }
+                const int e = blk * 32 + l8 * 4, idx = e >> 7, pc = (e >> 4) & 7;
+                *reinterpret_cast<uint32_t *>(q + idx * 128 + (((pc + idx) & 7) << 4) + (e & 15)) = packed;
+                if (l8 == 0) yd[blk] = __half2float(__float2half_rn(d));
+            }
+        }
+    }
+}
+
 template <int T>
-__device__ __forceinline__ void batch_consume(const cnode & nd, const int cw, const int lane,
+__device__ __forceinline__ void batch_consume(const cnode & nd, acts128 & acts, const int cw, const int lane,
                                               int & st_s, uint32_t & st_ph, int & cc, int & git,
                                               const uint8_t * actbuf, const uint32_t acts_free, const uint32_t full, const uint32_t empty,
                                               float * part, const uint8_t * slots, const int S, const int slot_stride) {
@@ -185,9 +264,9 @@ __device__ __forceinline__ void batch_consume(const cnode & nd, const int cw, co
     const int idx = wg * 32 + lane;                      // the 128-weight item of a row this lane owns
     const bool active = g < G && idx < items;
 
-    // the slice of K this lane owns, in registers for the node
-    acts128 acts;
-    if (active) {
+    // the slice of K this lane owns, in registers for the node (kept from the previous node when it has the same
+    // activations, k and format: q/k/v, gate/up)
+    if (active && !(nd.qflags & BATCH_Q_SAME)) {
         const int8_t * yq = reinterpret_cast<const int8_t *>(actbuf);
         const float  * yd = reinterpret_cast<const float *>(actbuf + nd.k);
         const float4 d4 = *reinterpret_cast<const float4 *>(yd + idx * 4);
@@ -308,6 +387,7 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
     uint64_t * empty      = full + BATCH_MAX_STAGES;
     uint64_t * acts_ready = full + 2 * BATCH_MAX_STAGES;
     uint64_t * acts_free  = acts_ready + BATCH_MAX_ABUF;
+    unsigned * sdone      = reinterpret_cast<unsigned *>(acts_free + BATCH_MAX_ABUF);   // [8] consumer warps done with node i % 8
     float    * part       = reinterpret_cast<float *>(smem + a.off_part);
     uint8_t  * actbufs    = smem + a.off_acts;
     uint8_t  * slots      = smem + a.off_slots;
@@ -318,6 +398,7 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
     if (tid == 0) {
         for (int s = 0; s < S; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], a.nwc); }
         for (int u = 0; u < NB; u++) { mbar_init(&acts_ready[u], 1); mbar_init(&acts_free[u], a.nwc); }
+        for (int u = 0; u < 8; u++) sdone[u] = 0u;
         mbar_fence_init();
     }
     __syncthreads();
@@ -381,6 +462,16 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
             batch_slab(nd, slab_v, r_begin, nrows);
             const int u = i % NB;
             if (i >= NB) mbar_wait(&acts_free[u], (uint32_t) (((i / NB) - 1) & 1));
+            if (nd.dep >= 0) {
+                // the node this one reads from (or must not overtake) is complete on EVERY CTA: acquire its counter.
+                // All CTAs are resident (one per SM), so the wait ends; a bound turns a logic error into a trap, not a hang.
+                if (lane == 0) {
+                    const unsigned * ctr = a.done + nd.dep;
+                    unsigned spins = 0;
+                    while (ld_acquire_gpu(ctr) < gridDim.x) { if (++spins > (1u << 25)) __trap(); }
+                }
+                __syncwarp();
+            }
             if (lane == 0) {
                 uint8_t * buf = actbufs + (size_t) u * a.acts_stride;
                 cnode * hd = reinterpret_cast<cnode *>(buf);
@@ -388,9 +479,14 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
                 hd->r_begin = r_begin; hd->nrows = nrows; hd->type = nd.type; hd->R = nd.R; hd->W = nd.W; hd->G = nd.G;
                 hd->skew0 = (int) (reinterpret_cast<uintptr_t>(nd.w + (int64_t) r_begin * nd.row_stride) & 15);
                 hd->rs16 = (int) (nd.row_stride & 15); hd->contiguous = nd.contiguous;
-                const uint32_t bytes = batch_acts_bytes(nd.k);    // k % 256 == 0: a multiple of 16
-                mbar_arrive_expect_tx(&acts_ready[u], bytes);     // release: the header is visible to whoever sees the phase complete
-                bulk_g2s(buf + BATCH_AHDR, nd.acts, bytes, &acts_ready[u]);
+                hd->qflags = nd.qflags; hd->x = nd.x; hd->signal = a.done + i;
+                if (nd.qflags & BATCH_Q_LOAD) {
+                    const uint32_t bytes = batch_acts_bytes(nd.k);    // k % 256 == 0: a multiple of 16
+                    mbar_arrive_expect_tx(&acts_ready[u], bytes);     // release: the header is visible to whoever sees the phase complete
+                    bulk_g2s(buf + BATCH_AHDR, nd.acts, bytes, &acts_ready[u]);
+                } else {
+                    mbar_arrive_cta(&acts_ready[u]);                    // the consumers quantize x themselves, or keep their registers
+                }
             }
             __syncwarp();
         }
@@ -402,11 +498,16 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
     int st_s = 0, cc = 0, layout_w = 0, git = 0;
     uint32_t st_ph = 0;
     const uint32_t full_a = smem_u32(full), empty_a = smem_u32(empty), ready_a = smem_u32(acts_ready), free_a = smem_u32(acts_free);
-    const int slot_stride = a.slot_stride, count = a.count, acts_stride = a.acts_stride;
+    const int slot_stride = a.slot_stride, count = a.count, acts_stride = a.acts_stride, nwc = a.nwc;
+    acts128 acts = {};                                    // survives from node to node (BATCH_Q_SAME)
     for (int i = 0, u = 0, uph = 0; i < count; i++) {
-        const uint8_t * buf = actbufs + u * acts_stride;
+        uint8_t * buf = actbufs + u * acts_stride;
         mbar_wait_a(ready_a + 8 * u, (uint32_t) uph);
         const cnode nd = *reinterpret_cast<const cnode *>(buf);
+        if (nd.qflags & BATCH_Q_INK) {
+            batch_quantize_ink(nd.x, nd.k, buf + BATCH_AHDR, cw, lane, nwc);
+            named_bar_sync(14, nwc * 32);                 // ids 1 .. 7 belong to the row groups (W > 1 -> G <= 7), 15 to the layout change
+        }
         // the partials area is laid out per W and only rows that need several warps (W > 1) use it: as long
         // as every such node of the list has the same W, the groups, their barriers and their buffer
         // parity (git) simply carry on across nodes; a different W needs every consumer warp to be past its
@@ -416,12 +517,26 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
             layout_w = nd.W;
         }
         if (FAM == 2) {
-            if (nd.type == T_Q8_0) batch_consume<T_Q8_0>(nd, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
-            else                   batch_consume<T_Q4_0>(nd, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
+            if (nd.type == T_Q8_0) batch_consume<T_Q8_0>(nd, acts, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
+            else                   batch_consume<T_Q4_0>(nd, acts, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
         }
-        else if (FAM == 1)          batch_consume<T_Q6_K>(nd, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
-        else if (nd.type == T_Q5_K) batch_consume<T_Q5_K>(nd, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
-        else                   batch_consume<T_Q4_K>(nd, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
+        else if (FAM == 1) { acts128 a6; batch_consume<T_Q6_K>(nd, a6, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride); }
+        else if (nd.type == T_Q5_K) batch_consume<T_Q5_K>(nd, acts, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
+        else                   batch_consume<T_Q4_K>(nd, acts, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
+        if (nd.qflags & BATCH_Q_SIGNAL) {
+            // this warp's rows of node i are stored; the last of the CTA's consumer warps to get here releases them
+            // to the other CTAs (cta-scope fences chain the warps' stores to the gpu-scope release)
+            __syncwarp();
+            if (lane == 0) {
+                __threadfence_block();
+                const unsigned old = atomicAdd(&sdone[i & 7], 1u);
+                if (old == (unsigned) nwc - 1u) {
+                    sdone[i & 7] = 0u;
+                    __threadfence();
+                    red_release_gpu_add(nd.signal, 1u);
+                }
+            }
+        }
         if (++u == NB) { u = 0; uph ^= 1; }
     }
 }
@@ -459,29 +574,49 @@ struct ws_cursor {
 
 static inline int batch_family(int type) { return type == T_Q6_K ? 1 : ((type == T_Q4_0 || type == T_Q8_0) ? 2 : 0); }
 
+constexpr size_t BATCH_DONE_BYTES = (BATCH_MAX_NODES * sizeof(unsigned) + 127) & ~(size_t) 127;   // completion counters of one launch
+
 struct batch_builder {
     batch_args args;
     int max_slot = 0;
     bool all_const = true;
     int  fam = 0;                     // format family of this builder's nodes (kernel instantiation)
+    std::vector<int> orig;            // index of each node in the caller's list (fallback replay)
     explicit batch_builder(int family) : fam(family) { reset(); }
     int64_t bytes_w14 = 0, bytes_w12 = 0;                       // weight bytes of nodes that gain / do not gain from 14 consumer warps
-    void reset() { args.count = 0; args.kmax = 0; max_slot = 0; all_const = true; bytes_w14 = bytes_w12 = 0; }
+    void reset() { args.count = 0; args.kmax = 0; args.done = nullptr; max_slot = 0; all_const = true; bytes_w14 = bytes_w12 = 0; orig.clear(); }
     bool full() const { return args.count >= BATCH_MAX_NODES; }
     bool empty() const { return args.count == 0; }
 
+    // dep: index (in this builder) of the latest node this one must wait for (it reads or overwrites what that node
+    // writes, or overwrites what it reads), -1: none; x_from_dep: x is written by a node of this builder.
     // false: the workspace cannot hold this node's activation record
-    bool add(int type, const uint8_t * w, int64_t row_stride, int64_t m, int64_t k, const float * x, float * dst, bool const_w, int grid, ws_cursor & cur) {
+    bool add(int type, const uint8_t * w, int64_t row_stride, int64_t m, int64_t k, const float * x, float * dst, bool const_w, int grid,
+             ws_cursor & cur, int dep = -1, bool x_from_dep = false, int orig_index = -1) {
         static const int slot_target = env_int("GGML_B200_BATCH_SLOT_BYTES", 46080);
+        if (!args.done) {                                       // first node since reset: the launch's completion counters
+            if (BATCH_DONE_BYTES > cur.left) return false;
+            args.done = reinterpret_cast<unsigned *>(cur.p); cur.p += BATCH_DONE_BYTES; cur.left -= BATCH_DONE_BYTES;
+        }
         batch_node & nd = args.nodes[args.count];
         const batch_node * prev = args.count > 0 ? &args.nodes[args.count - 1] : nullptr;
-        if (prev && prev->x == x && prev->k == k) {
-            nd.acts = prev->acts; nd.quantize = 0;              // same activations as the previous node (gate/up, q/k/v)
+        const bool same_x = prev && prev->x == x && prev->k == k;
+        nd.dep = (short) dep;
+        if (same_x && prev->type == type && fam != 1) {           // (Q6_K's 27-word items leave no registers to keep them in)
+            // same activations and format as the previous node (q/k/v, gate/up): the consumers keep their registers.
+            // (the previous node already waited for whatever wrote x; a hazard of this node's own dst still sets dep)
+            nd.acts = prev->acts; nd.qflags = BATCH_Q_SAME;
+        } else if (x_from_dep) {
+            nd.acts = nullptr; nd.qflags = BATCH_Q_INK;         // quantized inside the launch, after node dep
+        } else if (same_x && !(prev->qflags & BATCH_Q_INK) && prev->acts) {
+            nd.acts = prev->acts; nd.qflags = BATCH_Q_LOAD;     // another format on the same activations: the record is shared
         } else {
             const size_t need = batch_acts_record_bytes(k);
             if (need > cur.left) return false;
-            nd.acts = cur.p; nd.quantize = 1; cur.p += need; cur.left -= need;
+            nd.acts = cur.p; nd.qflags = BATCH_Q_PRE | BATCH_Q_LOAD; cur.p += need; cur.left -= need;
         }
+        if (dep >= 0) args.nodes[dep].qflags |= BATCH_Q_SIGNAL;
+        orig.push_back(orig_index);
         args.count++;
         nd.w = w; nd.x = x; nd.dst = dst; nd.row_stride = row_stride; nd.m = (int) m; nd.k = (int) k;
         nd.row_bytes = (int) (k / type_qk(type) * type_bytes(type));
@@ -496,7 +631,6 @@ struct batch_builder {
         if (R > (nd.W > 1 ? BATCH_RMAX : BATCH_RMAX_W1)) R = nd.W > 1 ? BATCH_RMAX : BATCH_RMAX_W1;
         nd.R = (unsigned char) R;
         nd.contiguous = row_stride == nd.row_bytes ? 1 : 0;
-        nd.pad[0] = nd.pad[1] = 0;
         int rpc = (int) ceil_div(m, grid);
         rpc += rpc & 1;
         nd.rows_per_cta = rpc;
@@ -536,7 +670,7 @@ static int batch_launch(batch_builder & bb, cudaStream_t st) {
         a.nodes[i].G = (unsigned char) (a.nodes[i].W == 1 && G > 12 ? 12 : G);
     }
     a.slot_stride = (bb.max_slot + 127) & ~127;
-    a.off_part    = (2 * BATCH_MAX_STAGES + 2 * BATCH_MAX_ABUF) * 8;
+    a.off_part    = (2 * BATCH_MAX_STAGES + 2 * BATCH_MAX_ABUF) * 8 + 8 * (int) sizeof(unsigned);
     a.off_acts    = (a.off_part + 2 * BATCH_NWC * BATCH_RMAX * (int) sizeof(float) + 127) & ~127;
     a.acts_stride = BATCH_AHDR + (int) batch_acts_record_bytes(a.kmax);
     int NB = nb_env < 2 ? 2 : (nb_env > BATCH_MAX_ABUF ? BATCH_MAX_ABUF : nb_env);
@@ -550,14 +684,9 @@ static int batch_launch(batch_builder & bb, cudaStream_t st) {
     a.S = S;
     const size_t smem = (size_t) a.off_slots + (size_t) S * a.slot_stride;
 
-    static size_t smem_set[3][64];
-    int dev = 0; cudaGetDevice(&dev); if (dev < 0 || dev >= 64) dev = 0;
+    static smem_limit lim[3];
     auto kern = bb.fam == 2 ? k_mmvq_batch<2> : (bb.fam == 1 ? k_mmvq_batch<1> : k_mmvq_batch<0>);
-    if (smem > smem_set[bb.fam][dev]) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
-        if (e != cudaSuccess) return -(int) e;
-        smem_set[bb.fam][dev] = smem;
-    }
+    if (const int rc = lim[bb.fam].ensure(kern, smem)) return rc;
     // 1. every activation vector of the list -> q8 (one launch)
     {
         const dim3 grid((unsigned) ceil_div(a.kmax / 32, 8), (unsigned) a.count);

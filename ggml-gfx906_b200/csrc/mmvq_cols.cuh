@@ -431,12 +431,9 @@ static int cols_launch(cols_builder & cb, cudaStream_t st) {
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
-    // whole tiles per warp (GGML_B200_COLS_KS=1) measured 7 % slower than the K split even on long lists
-    // (profiles/r01o_bs_probe.txt): the per-tile barrier is not what bounds the kernel
-    static const int ks_env = env_int("GGML_B200_COLS_KS", 8);
-    const bool ks1 = ks_env == 1;
-    if (ks1) cfg.gridDim = dim3((unsigned) (caps.sm_count * COLS_CTAS));
-    const cudaError_t e = ks1 ? cudaLaunchKernelEx(&cfg, k_mmvq_cols<1>, a) : cudaLaunchKernelEx(&cfg, k_mmvq_cols<8>, a);
+    // (whole tiles per warp, k_mmvq_cols<1>, measured 7 % slower than the K split even on long lists,
+    // profiles/r01o_bs_probe.txt; that instantiation is no longer built)
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, k_mmvq_cols<8>, a);
     if (e != cudaSuccess) return -(int) e;
     b200_count_launch(1);
     return B200_OK;

@@ -38,10 +38,18 @@ __device__ __forceinline__ int dp4a_us(uint32_t a, int b, int c) {
     return d;
 }
 
+// Tuning instrumentation (per-CTA globaltimer stamps, skip-the-math modes) exists only in -DB200_TUNING builds;
+// the product kernel carries none of it.
+#ifdef B200_TUNING
 __device__ __forceinline__ unsigned long long gtime() {
     unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t;
 }
 #define FUSED_STAMP(slot) do { if (a.dbg && lane == 0) a.dbg[(size_t) blockIdx.x * 8 + (slot)] = gtime(); } while (0)
+#define FUSED_DBG_MODE(bit) (a.dbg_mode & (bit))
+#else
+#define FUSED_STAMP(slot) do { } while (0)
+#define FUSED_DBG_MODE(bit) 0
+#endif
 
 constexpr int FUSED_RB = 2;          // rows a warp carries at once (one shuffle tree per pair)
 
@@ -334,8 +342,10 @@ struct fused_args {
     int     contiguous;       // rows back to back in memory -> one bulk copy per stage
     int     row_pitch;        // non-contiguous: bytes between rows inside a slot (multiple of 16)
     int     early_weights;    // weights are constant: request them before the grid dependency resolves
+#ifdef B200_TUNING
     int     dbg_mode;         // tuning aid: 1 = skip the dot products, 2 = skip the quantization
     unsigned long long * dbg; // tuning aid: per-CTA globaltimer stamps (NULL in normal use)
+#endif
 };
 
 constexpr int FUSED_MAX_WARPS = 10;   // up to 9 consumer warps + the producer
@@ -382,7 +392,9 @@ k_mmvq_fused(const fused_args a) {
                 const int rows_here = (nrows - b * R < R) ? (nrows - b * R) : R;
                 const uint8_t * src = a.w + (r_begin + (int64_t) b * R) * a.row_stride;
                 uint8_t * slot = slots + (size_t) s * a.slot_stride;
+#ifdef B200_TUNING
                 if (a.dbg && blockIdx.x == 0 && b < 120) a.dbg[2048 + b] = gtime();
+#endif
                 if (a.contiguous) {
                     const uint32_t off = (uint32_t) (reinterpret_cast<uintptr_t>(src) & 15);
                     const uint32_t bytes = (off + (uint32_t) rows_here * (uint32_t) a.row_bytes + 15u) & ~15u;
@@ -411,7 +423,7 @@ k_mmvq_fused(const fused_args a) {
     // 1. quantize x (bit-exact quantize_row_q8_1_ref values) into shared memory: 8 lanes per q8 block
     pdl_wait();
     if (warp == 0) FUSED_STAMP(1);
-    if (!(a.dbg_mode & 2)) {
+    if (!FUSED_DBG_MODE(2)) {
         const int nblk32 = a.k >> 5;
         const int sub = lane >> 3, l8 = lane & 7;
         constexpr int U = 4;                                  // loads in flight per lane
@@ -480,7 +492,9 @@ k_mmvq_fused(const fused_args a) {
         const int s = b % S;
         mbar_wait(&full[s], (uint32_t) ((b / S) & 1));      // every lane waits (see the producer's note)
         if (warp == 0 && b == 0) FUSED_STAMP(3);
+#ifdef B200_TUNING
         if (a.dbg && blockIdx.x == 0 && warp == 0 && lane == 0 && b < 120) a.dbg[2048 + 128 + b] = gtime();
+#endif
         if (warp == 0 && b == nbatch - 1) FUSED_STAMP(4);
         const int rows_here = (nrows - b * R < R) ? (nrows - b * R) : R;
         const uint8_t * slot = slots + (size_t) s * a.slot_stride;
@@ -490,7 +504,7 @@ k_mmvq_fused(const fused_args a) {
         // chunks (row pairs) are dealt to the groups round-robin over the CTA's whole slab, not per slot
         const int c_first = (g - (b * (R / FUSED_RB)) % G + G) % G;
 
-        for (int c = c_first; c < nchunks && !(a.dbg_mode & 1); c += G) {
+        for (int c = c_first; c < nchunks && !FUSED_DBG_MODE(1); c += G) {
             const int r0 = c * FUSED_RB;
             float acc[FUSED_RB];
 #pragma unroll
@@ -526,7 +540,9 @@ k_mmvq_fused(const fused_args a) {
         }
         __syncwarp();
         if (lane == 0) mbar_arrive_cta(&empty[s]);          // this warp is done with the slot
+#ifdef B200_TUNING
         if (a.dbg && blockIdx.x == 0 && warp == NWC - 1 && lane == 0 && b < 120) a.dbg[2048 + 256 + b] = gtime();
+#endif
         if (c_first < nchunks) work_it++;
         if (W > 1 && c_first < nchunks) {
             // the W warps of the group meet; warp 0 of the group adds the partials in fixed order.  The
@@ -555,15 +571,17 @@ k_mmvq_fused(const fused_args a) {
 namespace b200 {
 
 // ================================================================= host side
-static unsigned long long * g_fused_dbg = nullptr;   // set through b200_debug_timestamps (tools/ only)
+#ifdef B200_TUNING
+static unsigned long long * g_fused_dbg = nullptr;   // set through b200_debug_timestamps (tuning builds only)
+#endif
 
 template <int T, int IPL>
 static int launch_fused(fused_args a, cudaStream_t st) {
     const dev_caps & caps = current_caps();
-    const int ring_env = env_int("GGML_B200_FUSED_RING_BYTES", 98304);   // two kernels' CTAs share an SM
-    const int slot_env = env_int("GGML_B200_FUSED_SLOT_BYTES", 9216);
-    const int cps_env  = env_int("GGML_B200_FUSED_CTAS_PER_SM", 1);
-    const int pdl      = env_int("GGML_B200_FUSED_PDL", 1);
+    static const int ring_env = env_int("GGML_B200_FUSED_RING_BYTES", 98304);   // two kernels' CTAs share an SM
+    static const int slot_env = env_int("GGML_B200_FUSED_SLOT_BYTES", 9216);
+    static const int cps_env  = env_int("GGML_B200_FUSED_CTAS_PER_SM", 1);
+    static const int pdl      = env_int("GGML_B200_FUSED_PDL", 1);
 
     int mult = slot_env / (FUSED_RB * a.row_bytes);
     if (mult < 1) mult = 1;
@@ -584,24 +602,20 @@ static int launch_fused(fused_args a, cudaStream_t st) {
     if (smem > (size_t) caps.smem_optin) return B200_STREAM_NOT_APPLICABLE;
 
     auto kern = k_mmvq_fused<T, IPL>;
-    static size_t smem_set[64];
-    int dev = 0; cudaGetDevice(&dev); if (dev < 0 || dev >= 64) dev = 0;
-    if (smem > smem_set[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
-        if (e != cudaSuccess) return -(int) e;
-        smem_set[dev] = smem;
-    }
+    static smem_limit lim;
+    if (const int rc = lim.ensure(kern, smem)) return rc;
+    const int dev = current_device_slot();
     int64_t grid = (int64_t) caps.sm_count * cps;
     const int64_t max_grid = ceil_div(a.m, FUSED_RB);
     if (grid > max_grid) grid = max_grid;
     a.rows_per_cta = (int) ceil_div(a.m, grid);
     grid = ceil_div(a.m, a.rows_per_cta);
 
-    static bool carve_set[64];
-    if (!carve_set[dev]) {
+    static std::atomic<bool> carve_set[64];
+    if (!carve_set[dev].load(std::memory_order_acquire)) {
         // two kernels' CTAs must fit an SM at once (the next mat-vec prefetches while this one computes)
         cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-        carve_set[dev] = true;
+        carve_set[dev].store(true, std::memory_order_release);
     }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned) grid); cfg.blockDim = dim3((unsigned) ((a.W * a.G + 1) * 32));
@@ -635,7 +649,7 @@ static int launch_fused_t(fused_args a, cudaStream_t st) {
 // dst[m] = W[m, k] . x[k]; returns B200_OK, B200_STREAM_NOT_APPLICABLE (caller falls back) or an error.
 static int mmvq_fused_try(int type, const uint8_t * w, int64_t row_stride, int64_t m, int64_t k,
                           const float * x, float * dst, bool const_weights, cudaStream_t st) {
-    if (env_int("GGML_B200_MMVQ_NO_FUSED", 0)) return B200_STREAM_NOT_APPLICABLE;
+    if (b200_option(B200_OPT_MMVQ_NO_FUSED)) return B200_STREAM_NOT_APPLICABLE;
     if (m < 1 || k < 1024 || k % 256 != 0 || k > 131072) return B200_STREAM_NOT_APPLICABLE;
     if (reinterpret_cast<uintptr_t>(x) % 16 != 0) return B200_STREAM_NOT_APPLICABLE;
     const int64_t row_bytes = k / type_qk(type) * type_bytes(type);
@@ -644,8 +658,10 @@ static int mmvq_fused_try(int type, const uint8_t * w, int64_t row_stride, int64
     a.w = w; a.row_stride = row_stride; a.m = m; a.x = x; a.dst = dst; a.k = (int) k; a.row_bytes = (int) row_bytes;
     a.contiguous = row_stride == row_bytes ? 1 : 0;
     a.early_weights = const_weights ? 1 : 0;
+#ifdef B200_TUNING
     a.dbg = g_fused_dbg;
     a.dbg_mode = env_int("GGML_B200_FUSED_DBG_MODE", 0);
+#endif
     switch (type) {
         case T_Q4_K: return launch_fused_t<T_Q4_K>(a, st);
         case T_Q5_K: return launch_fused_t<T_Q5_K>(a, st);

@@ -18,11 +18,13 @@
 //
 // Grid: one CTA per contiguous slab of rows, sized so that the grid is a multiple of the SM count.
 #pragma once
+#include <atomic>
+#include <cstdlib>
 #include "common.cuh"
 
 namespace b200 {
 
-constexpr int B200_STREAM_NOT_APPLICABLE = 1000;
+constexpr int B200_STREAM_NOT_APPLICABLE = B200_NOT_APPLICABLE;
 
 // ---------------------------------------------------------------- PTX helpers (mbarrier + bulk copy)
 __device__ __forceinline__ uint32_t smem_u32(const void * p) { return (uint32_t) __cvta_generic_to_shared(p); }
@@ -462,21 +464,47 @@ k_mmvq_stream(const stream_args a) {
 }
 
 // ================================================================= host side
+// Per-device facts and per-(kernel, device) attribute state are shared by every thread that drives a backend
+// (different backends may run on different threads): atomics, no locks on the launch path.
 struct dev_caps { int sm_count; int smem_optin; };
-inline const dev_caps & current_caps() {
-    static dev_caps caps[64];
-    static bool     have[64];
+inline int current_device_slot() {
     int dev = 0;
     cudaGetDevice(&dev);
-    if (dev < 0 || dev >= 64) dev = 0;
-    if (!have[dev]) {
-        cudaDeviceGetAttribute(&caps[dev].sm_count, cudaDevAttrMultiProcessorCount, dev);
-        cudaDeviceGetAttribute(&caps[dev].smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
-        have[dev] = true;
+    return (dev < 0 || dev >= 64) ? 0 : dev;
+}
+inline const dev_caps & current_caps() {
+    static dev_caps caps[64];
+    static std::atomic<int> have[64];
+    const int dev = current_device_slot();
+    if (have[dev].load(std::memory_order_acquire) != 2) {
+        int expect = 0;
+        if (have[dev].compare_exchange_strong(expect, 1, std::memory_order_acq_rel)) {
+            cudaDeviceGetAttribute(&caps[dev].sm_count, cudaDevAttrMultiProcessorCount, dev);
+            cudaDeviceGetAttribute(&caps[dev].smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+            have[dev].store(2, std::memory_order_release);
+        } else {
+            while (have[dev].load(std::memory_order_acquire) != 2) { }
+        }
     }
     return caps[dev];
 }
+// raise a kernel's dynamic shared-memory limit on the current device (monotone; safe to race: the attribute is
+// only ever raised, and a thread never launches with more than it has itself asked for)
+struct smem_limit {
+    std::atomic<size_t> set[64];
+    template <typename K> int ensure(K kern, size_t smem) {
+        const int dev = current_device_slot();
+        if (smem > set[dev].load(std::memory_order_acquire)) {
+            const cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+            if (e != cudaSuccess) return -(int) e;
+            size_t cur = set[dev].load(std::memory_order_relaxed);
+            while (cur < smem && !set[dev].compare_exchange_weak(cur, smem, std::memory_order_release)) { }
+        }
+        return B200_OK;
+    }
+};
 
+// tuning knobs (ring depth, slot sizes ..): environment, read once per process at first use
 inline int env_int(const char * name, int dflt) {
     const char * v = getenv(name);
     return v && *v ? atoi(v) : dflt;
@@ -485,9 +513,9 @@ inline int env_int(const char * name, int dflt) {
 template <int T, int NCOLS, int IPL>
 static int launch_stream(stream_args a, int nw, cudaStream_t st) {
     const dev_caps & caps = current_caps();
-    const int S_env    = env_int("GGML_B200_MMVQ_STAGES", 4);
-    const int slot_env = env_int("GGML_B200_MMVQ_SLOT_BYTES", 8192);
-    const int cps_env  = env_int("GGML_B200_MMVQ_CTAS_PER_SM", 0);
+    static const int S_env    = env_int("GGML_B200_MMVQ_STAGES", 4);
+    static const int slot_env = env_int("GGML_B200_MMVQ_SLOT_BYTES", 8192);
+    static const int cps_env  = env_int("GGML_B200_MMVQ_CTAS_PER_SM", 0);
 
     a.S = S_env < 1 ? 1 : (S_env > 8 ? 8 : S_env);
     a.R = slot_env / a.row_bytes;
@@ -503,13 +531,8 @@ static int launch_stream(stream_args a, int nw, cudaStream_t st) {
     if (smem > (size_t) caps.smem_optin) return B200_STREAM_NOT_APPLICABLE;
 
     auto kern = k_mmvq_stream<T, NCOLS, IPL>;
-    static size_t smem_set[64];
-    int dev = 0; cudaGetDevice(&dev); if (dev < 0 || dev >= 64) dev = 0;
-    if (smem > smem_set[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
-        if (e != cudaSuccess) return -(int) e;
-        smem_set[dev] = smem;
-    }
+    static smem_limit lim;
+    if (const int rc = lim.ensure(kern, smem)) return rc;
     int occ = 1;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, nw * 32, smem);
     if (occ < 1) return B200_STREAM_NOT_APPLICABLE;
@@ -556,8 +579,7 @@ static int launch_stream_t(stream_args a, cudaStream_t st) {
 static int mmvq_stream_try(int type, const uint8_t * w, int64_t row_stride, int64_t m, int64_t k,
                            const int8_t * yq, const float * yd, int64_t n, float * dst, int64_t dst_col_stride,
                            cudaStream_t st) {
-    const int disabled = env_int("GGML_B200_MMVQ_GENERIC", 0);
-    if (disabled) return B200_STREAM_NOT_APPLICABLE;
+    if (b200_option(B200_OPT_MMVQ_GENERIC)) return B200_STREAM_NOT_APPLICABLE;
     if (m < 1 || n < 1 || n > 8 || k < 256) return B200_STREAM_NOT_APPLICABLE;
     const int64_t row_bytes = k / type_qk(type) * type_bytes(type);
     if (row_bytes > 60000 || row_stride < row_bytes) return B200_STREAM_NOT_APPLICABLE;

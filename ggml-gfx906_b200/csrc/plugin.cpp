@@ -248,6 +248,13 @@ static void b200_backend_synchronize(ggml_backend_t backend) {
     b200_backend_ctx * ctx = (b200_backend_ctx *) backend->context;
     CUDA_OK(cudaSetDevice(ctx->device));
     CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    // bad DATA met by a kernel (a GET_ROWS index outside the table): the reference asserts on the host
+    // (src/ggml-cpu/ops.cpp:5147); a kernel can only flag it, the abort happens here
+    const unsigned flags = b200_device_error_flags(1);
+    if (flags & 1u) {
+        b200_log("GET_ROWS: row index outside the table (%s)\n", b200_error_string(B200_ERR_INDEX));
+        GGML_ABORT("ggml-b200: GET_ROWS index out of range");
+    }
 }
 
 static bool op_is_noop(const struct ggml_tensor * t) {

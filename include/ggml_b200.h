@@ -49,6 +49,8 @@ enum b200_error {
     B200_ERR_STRIDE      = 3, /* dimension 0 not contiguous, or misaligned strides */
     B200_ERR_WORKSPACE   = 4, /* workspace too small / NULL */
     B200_ERR_NO_DEVICE   = 5, /* no sm_100 device visible */
+    B200_ERR_INDEX       = 6, /* a GET_ROWS index outside the table (reported by b200_device_error_flags) */
+    B200_NOT_APPLICABLE  = 1000, /* internal: the fast path declined; never returned by the entry points below */
 };
 
 /* ---- library / device ---------------------------------------------------------------------
@@ -59,6 +61,29 @@ B200_API const char * b200_error_string(int code);
 B200_API int          b200_device_count(void);                 /* devices with compute capability 10.x */
 B200_API int          b200_device_info(int device, char * name, size_t name_len,
                                        size_t * free_bytes, size_t * total_bytes, int * sm_count, int * cc);
+
+/* ---- run-time path switches ----------------------------------------------------------------
+ * Which kernel serves a call is chosen by shape; tests and benches force the other candidates to
+ * compare them on the same inputs.  Each option starts from its environment variable (read once,
+ * at first use); b200_set_option returns the previous value.  No launch path reads the environment.
+ * (replaces the GGML_CUDA_FORCE_* compile-time switches, src/ggml-cuda/ggml-cuda.cu:2029-2060.) */
+enum b200_option {
+    B200_OPT_MMVQ_GENERIC        = 0, /* GGML_B200_MMVQ_GENERIC=1: one-warp-per-row kernel for every n <= 8 call */
+    B200_OPT_MMVQ_NO_FUSED       = 1, /* GGML_B200_MMVQ_NO_FUSED=1: n = 1 without the fused quantize + mat-vec kernel */
+    B200_OPT_BATCH_SINGLE        = 2, /* GGML_B200_BATCH_SINGLE=1/0: a one-node list takes the persistent / the per-node kernel (-1: by size) */
+    B200_OPT_NO_BATCH_KERNEL     = 3, /* GGML_B200_NO_BATCH_KERNEL=1: lists run as one launch per node */
+    B200_OPT_MMQ_BN              = 4, /* GGML_B200_MMQ_BN=32|64|128|256: tile width of the batched kernel */
+    B200_OPT_MMQ_FORCE_UNALIGNED = 5, /* GGML_B200_MMQ_FORCE_UNALIGNED=1: per-row raw copies instead of TMA slab tiles */
+    B200_OPT_NO_CHAIN            = 6, /* GGML_B200_NO_CHAIN=1: a list is cut at every read-after-write instead of chaining inside one launch */
+    B200_OPT_MMQ_ROUTE           = 7, /* GGML_B200_MMQ_ROUTE=1|2: batched MUL_MAT through the bf16 / the q8_1 int8 tensor-core kernel (0: by shape) */
+    B200_OPT_COUNT
+};
+B200_API int b200_set_option(int option, int value);
+
+/* Sticky error bits set by kernels that met bad data (bit 0: B200_ERR_INDEX); valid once the stream that ran
+ * the kernel is synchronized.  replaces the GGML_ASSERT on the row index in ggml_compute_forward_get_rows_q
+ * (src/ggml-cpu/ops.cpp:5147).  clear != 0 resets the word. */
+B200_API unsigned b200_device_error_flags(int clear);
 
 /* ---- format table -------------------------------------------------------------------------
  * replaces ggml_blck_size / ggml_type_size / ggml_row_size for the hot-path types (include/ggml.h:716-721) */
@@ -130,7 +155,9 @@ B200_API int    b200_mul_mat_ex(int type_a, const void * a_dev, const int64_t ne
                                 float * dst_dev, void * workspace_dev, size_t workspace_bytes,
                                 uint32_t flags, void * stream);
 
-/* A whole list of MUL_MAT nodes in one call, issued back to back on `stream` in list order.
+/* A whole list of MUL_MAT nodes in one call, with the semantics of issuing them back to back on `stream` in list order
+ * (a node may read what an earlier node of the list writes: decode mat-vecs of one format family then ride ONE
+ * persistent launch, chained by per-node completion counters; other hazards cut the list into several launches).
  * replaces the node loop of ggml_backend_cuda_graph_compute -> evaluate_and_capture_cuda_graph ->
  * ggml_cuda_compute_forward (src/ggml-cuda/ggml-cuda.cu:2226-2520, 2870-2960) for graphs made of
  * MUL_MAT nodes: one host call per graph instead of one per node.  workspace_dev is shared by the
@@ -152,6 +179,11 @@ B200_API size_t b200_mul_mat_batch_workspace_size(const b200_mul_mat_node * node
 B200_API int    b200_mul_mat_batch(const b200_mul_mat_node * nodes, int64_t count,
                                    void * workspace_dev, size_t workspace_bytes, void * stream);
 
+/* How the list would be issued, without touching a device: plan[3 i] = launch group of node i (nodes of a group share
+ * one launch pair per format family), plan[3 i + 1] = list index of the node it waits for INSIDE its launch (-1: none),
+ * plan[3 i + 2] = route (0: per-node call, 1: persistent list kernel, 2: 2..8-column MMA list kernel). */
+B200_API int    b200_mul_mat_batch_plan(const b200_mul_mat_node * nodes, int64_t count, int32_t * plan);
+
 /* The two legs separately (2-D, for tests and benches).
  * b200_quantize_acts: f32 [n, k] -> the planar q8 scratch the matvec consumes (same values as
  *   quantize_row_q8_1: int8 plane [n][k] followed by the per-32 scales d as f32 [n][k/32]).
@@ -168,6 +200,18 @@ B200_API int    b200_mul_mat_q(int type, const void * w_dev, size_t w_row_stride
                                const float * x_dev, size_t x_row_stride_bytes, int64_t n,
                                float * dst_dev, size_t dst_col_stride_bytes,
                                void * workspace_dev, size_t workspace_bytes, void * stream);
+
+/* The quantizers of the two list kernels on their own (for bit-exact tests against quantize_row_q8_1_ref,
+ * src/ggml-quants.c:225-258).  Layouts (implementation detail of b200_mul_mat_batch's workspace):
+ *   record  (decode list kernel, one vector of k values): int8 plane [k], 128-value items with their eight 16-byte
+ *            pieces rotated (piece p of item i is stored at piece (p + i) % 8), then f32 d[k/32] (the fp16-rounded scale);
+ *   columns (2..8-column MMA list kernel): int8 [k/32][8][32] (the 8 padded columns of a 32-block side by side), then at
+ *            the next 128-byte boundary float2 (d, d * sum(q)) [k/32][8], then int32 -32 * sum16(q) [k/16][8]. */
+B200_API size_t b200_acts_record_bytes(int64_t k);
+B200_API size_t b200_acts_columns_bytes(int64_t k, int64_t n);
+B200_API int    b200_quantize_acts_record(const float * x_dev, int64_t k, void * record_dev, void * stream);
+B200_API int    b200_quantize_acts_columns(const float * x_dev, size_t x_row_stride_bytes, int64_t k, int64_t n,
+                                           void * columns_dev, void * stream);
 
 /* Number of kernels this library has launched since load (bench.py's gpu_launches). */
 B200_API uint64_t b200_launch_count(void);

@@ -25,7 +25,7 @@ import sys
 import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-spec = importlib.util.spec_from_file_location("ggml_host", os.path.join(ROOT, "ggml-gfx906_b200", "ggml_host.py"))
+spec = importlib.util.spec_from_file_location("ggml_host", os.path.join(ROOT, "tests", "ggml_host.py"))
 gh = importlib.util.module_from_spec(spec)
 spec.loader.exec_module(gh)
 

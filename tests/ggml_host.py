@@ -1,4 +1,4 @@
-"""ctypes view of ggml's PUBLIC C API (include/ggml.h, include/ggml-backend.h, include/ggml-alloc.h).
+"""TEST / BENCH HARNESS (not product code).  ctypes view of ggml's PUBLIC C API (include/ggml.h, include/ggml-backend.h, include/ggml-alloc.h).
 
 This is the *host application* side of the drop-in boundary: the same calls an unmodified ggml
 program makes (examples/simple/simple-backend.cpp:50-140 — init context, build a graph with
@@ -43,7 +43,7 @@ class _InitParams(C.Structure):
 
 def default_ggml_dir() -> str:
     here = os.path.dirname(os.path.abspath(__file__))
-    return os.environ.get("GGML_B200_HOST_DIR", os.path.join(here, "..", "oracle", "_ref", "bin"))
+    return os.environ.get("GGML_B200_HOST_DIR", os.path.join(here, "..", "oracle", "_ref", "bin"))   # tests/ -> repo root
 
 
 class GgmlHost:

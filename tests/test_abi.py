@@ -53,7 +53,7 @@ def test_plugin_exports_every_declared_symbol(built):
 def test_format_table_and_errors(built):
     import b200
     lib = b200.load_library()
-    assert lib.b200_abi_version() == 1
+    assert lib.b200_abi_version() == 2
     for t in b200.QUANT_TYPES:
         assert lib.b200_block_elems(b200.TYPE_ID[t]) == b200.BLOCK_ELEMS[t]
         assert lib.b200_block_bytes(b200.TYPE_ID[t]) == b200.BLOCK_BYTES[t]

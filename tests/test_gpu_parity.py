@@ -159,19 +159,81 @@ def test_quantize_q8_1_strided_rows(kern, oracle):
     assert np.array_equal(got, want)
 
 
+def _q8_1_reference(oracle, x):
+    """(int8 values [k], fp16-rounded d as f32 [k/32], integer sums [k/32]) of quantize_row_q8_1_ref"""
+    blocks = oracle.quantize_q8_1(x).reshape(-1, 36)
+    d = blocks[:, 0:2].copy().view(np.float16).astype(np.float32).reshape(-1)
+    q = blocks[:, 4:36].copy().view(np.int8).reshape(-1)
+    return q, d, q.reshape(-1, 32).astype(np.int32).sum(axis=1)
+
+
+@pytest.mark.parametrize("case", list(_act_cases().keys()))
+def test_quantize_list_record_vs_oracle(kern, oracle, case):
+    """k_quantize_batch, the quantizer on the headline path (decode list kernel): its record, un-swizzled on the host,
+    is quantize_row_q8_1_ref bit for bit (ties, tiny values and outliers included)."""
+    for x in _act_cases()[case][:2]:
+        k = x.size
+        rec = kern.quantize_acts_record(kern.to_device(x)).cpu().numpy()
+        e = np.arange(k)
+        idx, pc = e >> 7, (e >> 4) & 7
+        pos = idx * 128 + (((pc + idx) & 7) << 4) + (e & 15)
+        got_q = rec[:k].view(np.int8)[pos]
+        got_d = rec[k:k + k // 32 * 4].view(np.float32)
+        q, d, _ = _q8_1_reference(oracle, x)
+        assert np.array_equal(got_q, q)
+        assert np.array_equal(u32(got_d), u32(d))
+
+
+@pytest.mark.parametrize("case", list(_act_cases().keys()))
+@pytest.mark.parametrize("n", [2, 5, 8])
+def test_quantize_list_columns_vs_oracle(kern, oracle, case, n):
+    """k_quantize_cols (decode at batch 2..8): int8 [k/32][8][32] + (d, d * sum) + -32 * sum16, against
+    quantize_row_q8_1_ref per column; padding columns carry zero scales."""
+    base = _act_cases()[case]
+    x = np.ascontiguousarray(np.resize(base, (n, base.shape[1])) * np.linspace(1.0, 2.0, n, dtype=np.float32)[:, None])
+    k = x.shape[1]
+    buf = kern.quantize_acts_columns(kern.to_device(x)).cpu().numpy()
+    yq = buf[:8 * k].view(np.int8).reshape(k // 32, 8, 32)
+    off = (8 * k + 127) & ~127
+    yds = buf[off:off + k // 32 * 8 * 8].view(np.float32).reshape(k // 32, 8, 2)
+    yns = buf[off + k // 32 * 8 * 8: off + k // 32 * 8 * 8 + k // 16 * 8 * 4].view(np.int32).reshape(k // 16, 8)
+    for c in range(n):
+        q, d, sums = _q8_1_reference(oracle, x[c])
+        assert np.array_equal(yq[:, c, :].reshape(-1), q), c
+        assert np.array_equal(u32(yds[:, c, 0]), u32(d)), c
+        assert np.array_equal(u32(yds[:, c, 1]), u32(d * sums.astype(np.float32))), c
+        s16 = q.reshape(-1, 16).astype(np.int32).sum(axis=1)
+        assert np.array_equal(yns[:, c], -32 * s16), c
+    for c in range(n, 8):
+        assert not yds[:, c, :].any() and not yns[:, c].any()
+
+
+def test_get_rows_index_out_of_range_is_reported(kern, oracle):
+    """the reference asserts on a row index outside the table (src/ggml-cpu/ops.cpp:5147); here the row is zero-filled
+    (never stale memory), the good rows are right and the library's sticky error flag is raised."""
+    import b200
+    import torch
+    t, n_vocab, k = "q4_K", 100, 1024
+    blocks = random_blocks(t, n_vocab, k, seed=5)
+    rows = np.array([3, n_vocab, 7, -1, 99], dtype=np.int32)
+    assert kern.device_error_flags() == 0
+    got = kern.get_rows(t, dev_blocks(kern, blocks), k, torch.from_numpy(rows).to(kern.device)).cpu().numpy()
+    assert kern.device_error_flags() & b200.ERR_FLAG_INDEX
+    assert kern.device_error_flags() == 0            # reading clears it
+    good = [0, 2, 4]
+    assert np.array_equal(u32(got[good]), u32(oracle.get_rows(t, blocks, k, rows[good])))
+    assert not got[[1, 3]].any()
+
+
 # ---------------------------------------------------------------------------- MUL_MAT, decode (n <= 8)
 def _mmvq_both(kern, monkeypatch, t, w, m, k, x):
     """run the matvec through the streaming kernel (default) and the generic kernel"""
     outs = {}
     for mode in ("stream", "generic"):
-        if mode == "generic":
-            monkeypatch.setenv("GGML_B200_MMVQ_GENERIC", "1")
-        else:
-            monkeypatch.delenv("GGML_B200_MMVQ_GENERIC", raising=False)
-        xd = kern.to_device(x)
-        scratch = kern.quantize_acts(xd)
-        outs[mode] = kern.mul_mat_vec_q(t, dev_blocks(kern, w), m, k, scratch, x.shape[0]).cpu().numpy()
-    monkeypatch.delenv("GGML_B200_MMVQ_GENERIC", raising=False)
+        with kern.option("mmvq_generic", 1 if mode == "generic" else 0):
+            xd = kern.to_device(x)
+            scratch = kern.quantize_acts(xd)
+            outs[mode] = kern.mul_mat_vec_q(t, dev_blocks(kern, w), m, k, scratch, x.shape[0]).cpu().numpy()
     return outs
 
 
@@ -194,8 +256,6 @@ MMVQ_SHAPES = [(16, 256), (1, 256), (5, 512), (33, 1024), (257, 4096), (64, 1100
 @pytest.mark.parametrize("m,k", MMVQ_SHAPES)
 @pytest.mark.parametrize("n", [1, 2, 4, 5, 8])
 def test_mul_mat_vec_vs_oracle(kern, oracle, monkeypatch, t, m, k, n):
-    if n in (2, 5) and k > 4096:
-        pytest.skip("column-count sweep only at the smaller k")
     w = random_blocks(t, m, k, seed=100 + m + k)
     x = np.random.default_rng(7 + n).uniform(-1, 1, size=(n, k)).astype(np.float32)
     want = oracle.mul_mat(t, w, m, k, x, mode=1)
@@ -297,9 +357,8 @@ def test_mul_mat_fused_decode_vs_oracle(kern, oracle, monkeypatch, t, m, k):
         got = kern.mul_mat(t, wd, m, k, xd, const_weights=const).cpu().numpy().reshape(1, m)
         assert np.isfinite(got).all()
         assert oracle.nmse(want, got) <= NMSE_ORACLE, (const, oracle.nmse(want, got))
-    monkeypatch.setenv("GGML_B200_MMVQ_NO_FUSED", "1")
-    two = kern.mul_mat(t, wd, m, k, xd).cpu().numpy().reshape(1, m)
-    monkeypatch.delenv("GGML_B200_MMVQ_NO_FUSED")
+    with kern.option("mmvq_no_fused", 1):
+        two = kern.mul_mat(t, wd, m, k, xd).cpu().numpy().reshape(1, m)
     assert oracle.nmse(two, got) <= NMSE_ORACLE
 
 
@@ -397,11 +456,8 @@ def test_mul_mat_batch_few_columns(kern, oracle, n):
                 xc = kern.to_device(np.ascontiguousarray(x_np[c:c + 1, :k]))
                 one = (b200.MulMatNode * 2)(b200.mul_mat_node(t, w.data_ptr(), m, k, xc.data_ptr(), 1, y1.data_ptr()),
                                             b200.mul_mat_node(t, w.data_ptr(), m, k, xc.data_ptr(), 1, y1.data_ptr()))
-                os.environ["GGML_B200_BATCH_SINGLE"] = "1"
-                try:
+                with kern.option("batch_single", 1):
                     kern.mul_mat_batch((b200.MulMatNode * 1)(one[0]))
-                finally:
-                    del os.environ["GGML_B200_BATCH_SINGLE"]
                 assert np.array_equal(u32(y1.cpu().numpy().reshape(-1)), u32(got[c])), (t, m, k, n, c)
     assert kern.launch_count() > c0
 
@@ -459,11 +515,8 @@ def test_mul_mat_persistent_batch_vs_oracle(kern, oracle, shared_x):
             import torch
             y1 = torch.zeros((1, m), dtype=torch.float32, device=kern.device)
             one = (b200.MulMatNode * 1)(b200.mul_mat_node(t, w.data_ptr(), m, k, x.data_ptr(), 1, y1.data_ptr()))
-            os.environ["GGML_B200_BATCH_SINGLE"] = "1"
-            try:
+            with kern.option("batch_single", 1):
                 kern.mul_mat_batch(one)
-            finally:
-                del os.environ["GGML_B200_BATCH_SINGLE"]
             single = y1.cpu().numpy().reshape(-1)
         assert np.array_equal(u32(single), u32(got.reshape(-1))), (t, m, k)
 
@@ -525,9 +578,11 @@ def test_mul_mat_persistent_batch_many_nodes_and_strided_rows(kern, oracle):
     assert oracle.nmse(want, got) <= NMSE_ORACLE
 
 
-def test_mul_mat_persistent_batch_cuts_at_dependencies(kern, oracle):
-    """a node that reads (or overwrites) what an earlier node of the list writes must not share its
-    launch: chain y1 = W1 x, y2 = W2 y1, then a node that overwrites y1."""
+def test_mul_mat_persistent_batch_chains_dependencies(kern, oracle):
+    """a node that reads (or overwrites) what an earlier node of the list writes: chain y1 = W1 x, y2 = W2 y1, then a
+    node that overwrites y1.  Default: all three ride ONE persistent launch (per-node completion counters, the
+    dependent node's activations quantized inside the launch); option no_chain = 1: the list is cut at every hazard
+    (three launch groups).  Same bits either way, and the same as three separate calls."""
     import b200
     import torch
     w1_np, w2_np, w3_np = random_blocks("q4_K", 4096, 1024, seed=1), random_blocks("q5_K", 200, 4096, seed=2), random_blocks("q4_K", 4096, 2048, seed=3)
@@ -541,23 +596,157 @@ def test_mul_mat_persistent_batch_cuts_at_dependencies(kern, oracle):
         b200.mul_mat_node("q4_K", w1.data_ptr(), 4096, 1024, x.data_ptr(), 1, y1.data_ptr()),
         b200.mul_mat_node("q5_K", w2.data_ptr(), 200, 4096, y1.data_ptr(), 1, y2.data_ptr()),
         b200.mul_mat_node("q4_K", w3.data_ptr(), 4096, 2048, x3.data_ptr(), 1, y1.data_ptr()))
-    c0 = kern.launch_count()
-    kern.mul_mat_batch(nodes)
-    # three launch groups of one node: the two small ones take the per-node kernel (1 launch each), the 4.7 MB
-    # one the (quantize, persistent) pair -- same bits either way
-    assert kern.launch_count() - c0 == 4
     r1 = kern.mul_mat("q4_K", w1, 4096, 1024, x)
     r2 = kern.mul_mat("q5_K", w2, 200, 4096, r1)
     r3 = kern.mul_mat("q4_K", w3, 4096, 2048, x3)
-    assert np.array_equal(u32(y2.cpu().numpy().reshape(-1)), u32(r2.cpu().numpy().reshape(-1)))
-    assert np.array_equal(u32(y1.cpu().numpy().reshape(-1)), u32(r3.cpu().numpy().reshape(-1)))
+    for no_chain, launches in ((0, 2), (1, 4)):
+        y1.zero_(); y2.zero_()
+        with kern.option("no_chain", no_chain):
+            c0 = kern.launch_count()
+            kern.mul_mat_batch(nodes)
+            # chained: one (quantize, persistent) pair.  cut: three groups of one node -- the two small ones take the
+            # per-node kernel (1 launch each), the 4.7 MB one the (quantize, persistent) pair
+            assert kern.launch_count() - c0 == launches, (no_chain, kern.launch_count() - c0)
+        assert np.array_equal(u32(y2.cpu().numpy().reshape(-1)), u32(r2.cpu().numpy().reshape(-1))), no_chain
+        assert np.array_equal(u32(y1.cpu().numpy().reshape(-1)), u32(r3.cpu().numpy().reshape(-1))), no_chain
     assert oracle.nmse(oracle.mul_mat("q5_K", w2_np, 200, 4096, r1.cpu().numpy().reshape(1, 4096), mode=1), y2.cpu().numpy()) <= NMSE_ORACLE
+
+
+def _decoder_chain(kern, types, hidden, ffn, layers, vocab, seed):
+    """The dependency structure of a decoder pass on small shapes: per layer q/k/v read h, wo reads q (stand-in for the
+    attention output), gate/up read wo, down reads up; the next layer reads down; the output matrix reads the last
+    down.  Returns (nodes, weights (numpy, device), buffers, order) for b200_mul_mat_batch."""
+    import b200
+    import torch
+    tq, tk, tv, to, tg, tu, td, tout = types
+    dev = kern.device
+    h0_np = np.random.default_rng(seed).uniform(-1, 1, size=(1, hidden)).astype(np.float32)
+    h0 = kern.to_device(h0_np)
+    specs, bufs = [], {"h0": h0}
+    cur = "h0"
+    for l in range(layers):
+        for nm, t in (("q", tq), ("k", tk), ("v", tv)):
+            specs.append((t, hidden, hidden, cur, f"{nm}{l}"))
+        specs.append((to, hidden, hidden, f"q{l}", f"o{l}"))
+        specs.append((tg, ffn, hidden, f"o{l}", f"g{l}"))
+        specs.append((tu, ffn, hidden, f"o{l}", f"u{l}"))
+        specs.append((td, hidden, ffn, f"u{l}", f"d{l}"))
+        cur = f"d{l}"
+    specs.append((tout, vocab, hidden, cur, "logits"))
+    ws_np, ws = [], []
+    for i, (t, m, k, src, dst) in enumerate(specs):
+        w = random_blocks(t, m, k, seed=seed + 13 * i)
+        ws_np.append(w); ws.append(dev_blocks(kern, w))
+        bufs[dst] = torch.zeros((1, m), dtype=torch.float32, device=dev)
+    nodes = (b200.MulMatNode * len(specs))(*[
+        b200.mul_mat_node(t, w.data_ptr(), m, k, bufs[src].data_ptr(), 1, bufs[dst].data_ptr(), const_weights=True)
+        for (t, m, k, src, dst), w in zip(specs, ws)])
+    return nodes, specs, ws_np, ws, bufs, h0_np
+
+
+CHAIN_MIXES = {
+    "q4_K": ("q4_K",) * 8,
+    "q4_K+q5_K": ("q4_K", "q5_K", "q4_K", "q5_K", "q4_K", "q4_K", "q5_K", "q4_K"),
+    "q6_K": ("q6_K",) * 8,
+    "q4_0+q8_0": ("q4_0", "q4_0", "q8_0", "q4_0", "q8_0", "q8_0", "q4_0", "q8_0"),
+    "q4_K_M-like": ("q4_K", "q4_K", "q6_K", "q4_K", "q4_K", "q4_K", "q6_K", "q6_K"),
+}
+
+
+@pytest.mark.parametrize("mix", list(CHAIN_MIXES.keys()))
+def test_mul_mat_chain_decoder_layers(kern, oracle, mix):
+    """A whole (small) decoder pass as ONE list with its real dependency structure.  Chained inside the persistent
+    launch(es) it must give, bit for bit, what the cut list (option no_chain) gives and what node-by-node calls
+    give; replayed from a CUDA graph 20 times the bits never change (a missed dependency would show as a race);
+    every node is within NMSE 1e-9 of the oracle fed with the node's actual input."""
+    import torch
+    hidden, ffn, layers, vocab = 1024, 2816, 3, 3000
+    nodes, specs, ws_np, ws, bufs, h0_np = _decoder_chain(kern, CHAIN_MIXES[mix], hidden, ffn, layers, vocab, seed=500)
+    names = [dst for (_, _, _, _, dst) in specs]
+
+    def snapshot():
+        return {nm: bufs[nm].cpu().numpy().copy() for nm in names}
+
+    def clear():
+        for nm in names:
+            bufs[nm].zero_()
+
+    with kern.option("no_chain", 1):
+        clear()
+        c0 = kern.launch_count()
+        kern.mul_mat_batch(nodes)
+        cut_launches = kern.launch_count() - c0
+    cut = snapshot()
+    clear()
+    c0 = kern.launch_count()
+    kern.mul_mat_batch(nodes)
+    chained_launches = kern.launch_count() - c0
+    got = snapshot()
+    one_family = mix in ("q4_K", "q4_K+q5_K", "q6_K", "q4_0+q8_0")
+    if one_family:
+        assert chained_launches == 2, chained_launches          # one (quantize, persistent) pair for the whole pass
+    assert chained_launches < cut_launches, (chained_launches, cut_launches)
+    for nm in names:
+        assert np.array_equal(u32(got[nm]), u32(cut[nm])), (mix, nm)
+    # node by node, each fed with the chained run's own intermediate values
+    inputs = {"h0": h0_np, **got}
+    for (t, m, k, src, dst), w_np in zip(specs, ws_np):
+        want = oracle.mul_mat(t, w_np, m, k, inputs[src].reshape(1, k), mode=1)
+        assert oracle.nmse(want, got[dst]) <= NMSE_ORACLE, (mix, dst)
+    # replay: same bits every time
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        kern.mul_mat_batch(nodes)
+    for rep in range(20):
+        if rep % 5 == 0:
+            clear()
+        g.replay()
+        torch.cuda.synchronize()
+        now = snapshot()
+        for nm in names:
+            assert np.array_equal(u32(now[nm]), u32(got[nm])), (mix, rep, nm)
+
+
+def test_mul_mat_chain_write_after_read_and_reused_buffers(kern, oracle):
+    """hazards other than read-after-write inside one launch: a residual-style buffer that is read, overwritten and read
+    again (A = W1 x; B = W2 A; A = W3 B; C = W4 A), and two nodes writing one buffer in turn.  Same bits as the cut list."""
+    import b200
+    import torch
+    k = 1024
+    ws_np = [random_blocks("q4_K", k, k, seed=70 + i) for i in range(5)]
+    ws = [dev_blocks(kern, w) for w in ws_np]
+    x = kern.to_device(np.random.default_rng(71).uniform(-1, 1, size=(1, k)).astype(np.float32))
+    A, B, C = (torch.zeros((1, k), dtype=torch.float32, device=kern.device) for _ in range(3))
+    plan = [(0, x, A), (1, A, B), (2, B, A), (3, A, C), (4, x, C), (0, C, B)]
+    nodes = (b200.MulMatNode * len(plan))(*[b200.mul_mat_node("q4_K", ws[wi].data_ptr(), k, k, src.data_ptr(), 1, dst.data_ptr()) for wi, src, dst in plan])
+    outs = {}
+    for no_chain in (1, 0):
+        for t_ in (A, B, C):
+            t_.zero_()
+        with kern.option("no_chain", no_chain):
+            c0 = kern.launch_count()
+            kern.mul_mat_batch(nodes)
+            n_launch = kern.launch_count() - c0
+        outs[no_chain] = [t_.cpu().numpy().copy() for t_ in (A, B, C)] + [n_launch]
+    assert outs[0][3] == 2 and outs[1][3] > 2, (outs[0][3], outs[1][3])
+    for a, b in zip(outs[0][:3], outs[1][:3]):
+        assert np.array_equal(u32(a), u32(b))
+    # and against a step-by-step evaluation
+    r = kern.mul_mat("q4_K", ws[0], k, k, x)
+    r = kern.mul_mat("q4_K", ws[1], k, k, r)
+    a2 = kern.mul_mat("q4_K", ws[2], k, k, r)
+    c1 = kern.mul_mat("q4_K", ws[4], k, k, x)
+    b2 = kern.mul_mat("q4_K", ws[0], k, k, c1)
+    assert np.array_equal(u32(outs[0][0]), u32(a2.cpu().numpy()))
+    assert np.array_equal(u32(outs[0][2]), u32(c1.cpu().numpy()))
+    assert np.array_equal(u32(outs[0][1]), u32(b2.cpu().numpy()))
 
 
 @pytest.mark.parametrize("t", FUSED_TYPES)
 @pytest.mark.parametrize("m,k", FUSED_SHAPES)
 def test_mul_mat_persistent_single_node(kern, oracle, monkeypatch, t, m, k):
-    """one node through the persistent kernel (GGML_B200_BATCH_SINGLE=1): bit-identical to the per-node kernel."""
+    """one node through the persistent kernel (option batch_single = 1): bit-identical to the per-node kernel."""
     import b200
     import torch
     w_np = random_blocks(t, m, k, seed=3 * m + k)
@@ -565,9 +754,8 @@ def test_mul_mat_persistent_single_node(kern, oracle, monkeypatch, t, m, k):
     w, x = dev_blocks(kern, w_np), kern.to_device(x_np)
     y = torch.zeros((1, m), dtype=torch.float32, device=kern.device)
     nodes = (b200.MulMatNode * 1)(b200.mul_mat_node(t, w.data_ptr(), m, k, x.data_ptr(), 1, y.data_ptr()))
-    monkeypatch.setenv("GGML_B200_BATCH_SINGLE", "1")
-    kern.mul_mat_batch(nodes)
-    monkeypatch.delenv("GGML_B200_BATCH_SINGLE")
+    with kern.option("batch_single", 1):
+        kern.mul_mat_batch(nodes)
     single = kern.mul_mat(t, w, m, k, x).cpu().numpy().reshape(-1)
     assert np.array_equal(u32(single), u32(y.cpu().numpy().reshape(-1)))
     assert oracle.nmse(oracle.mul_mat(t, w_np, m, k, x_np, mode=1), y.cpu().numpy()) <= NMSE_ORACLE
@@ -599,9 +787,9 @@ def test_mul_mat_vec_full_size_sampled_rows(kern, oracle, t, m, k):
 
 
 # ---------------------------------------------------------------------------- MUL_MAT, batched (tensor cores)
-# The batched kernel multiplies fp16-dequantized weights with bf16-rounded activations and accumulates
+# The batched kernel multiplies bf16-dequantized weights with bf16-rounded activations and accumulates
 # in f32 (mmq_tc.cuh).  Bar: test-backend-ops' NMSE gate (5e-4) against exact-activation truth (oracle
-# mode 0) — in practice ~1e-5 — and against ggml-cpu's own output where a golden vector exists.
+# mode 0) — in practice ~5e-6 — and against ggml-cpu's own output where a golden vector exists.
 NMSE_TC = 5e-5
 
 
@@ -660,11 +848,11 @@ def test_mul_mat_q_unaligned_rows(kern, oracle, monkeypatch, t):
 
 @pytest.mark.parametrize("bn", [32, 64, 128, 256])
 def test_mul_mat_q_every_tile_width(kern, oracle, monkeypatch, bn):
-    monkeypatch.setenv("GGML_B200_MMQ_BN", str(bn))
     t, m, k, n = "q4_K", 256, 1024, 300
     w = random_blocks(t, m, k, seed=bn)
     x = np.random.default_rng(bn).standard_normal(size=(n, k)).astype(np.float32)
-    got = kern.mul_mat_q(t, dev_blocks(kern, w), m, k, kern.to_device(x)).cpu().numpy()
+    with kern.option("mmq_bn", bn):
+        got = kern.mul_mat_q(t, dev_blocks(kern, w), m, k, kern.to_device(x)).cpu().numpy()
     assert oracle.nmse(oracle.mul_mat(t, w, m, k, x, mode=0), got) <= NMSE_TC
 
 
@@ -679,3 +867,111 @@ def test_mul_mat_q_full_size_sampled(kern, oracle, t, m, k):
     rows = np.unique(np.concatenate([[0, 127, 128, m - 1], np.random.default_rng(4).integers(0, m, size=28)]))
     want = oracle.mul_mat(t, np.ascontiguousarray(w[rows]), len(rows), k, x, mode=0)
     assert oracle.nmse(want, got[:, rows]) <= NMSE_TC
+
+
+@pytest.mark.parametrize("t", QUANT_TYPES)
+@pytest.mark.parametrize("scale", [1e5, 1e-6, 3e30, 1e-30])
+def test_mul_mat_q_scale_invariance(kern, oracle, t, scale):
+    """the batched path must be as indifferent to magnitude as the reference's per-block q8_1 route
+    (src/ggml-cuda/quantize.cu:50-143) and ggml-cpu: activations scaled by 1e5 / 1e-6 / 3e30 / 1e-30, one all-zero
+    column, one column with a single outlier.  NMSE per column against exact-activation truth."""
+    m, k, n = 200, 2048, 24
+    w = random_blocks(t, m, k, seed=77)
+    x = np.random.default_rng(78).standard_normal(size=(n, k)).astype(np.float32) * np.float32(scale)
+    x[5] = 0.0
+    x[6, 100] *= 1000.0
+    want = oracle.mul_mat(t, w, m, k, x, mode=0)
+    got = kern.mul_mat_q(t, dev_blocks(kern, w), m, k, kern.to_device(x)).cpu().numpy()
+    assert np.isfinite(got).all()
+    assert not got[5].any()
+    for c in range(n):
+        if c != 5:
+            assert oracle.nmse(want[c], got[c]) <= NMSE_REF, (c, oracle.nmse(want[c], got[c]))
+    assert oracle.nmse(want, got) <= NMSE_TC
+
+
+@pytest.mark.parametrize("t", QUANT_TYPES)
+def test_mul_mat_q_adversarial_block_scales(kern, oracle, t):
+    """edge scale fields in the weights (0, subnormal d, +-65504, sc = m = 63, Q6_K scale -128) on the batched path:
+    finite wherever the truth is finite, NMSE per ROW (a row of huge blocks must not hide a row of tiny ones) and
+    overall within the harness gate."""
+    m, k, n = 96, 2304, 20
+    w = adversarial_blocks(t, m, k, seed=31)
+    x = np.random.default_rng(32).standard_normal(size=(n, k)).astype(np.float32)
+    want = oracle.mul_mat(t, w, m, k, x, mode=0)
+    got = kern.mul_mat_q(t, dev_blocks(kern, w), m, k, kern.to_device(x)).cpu().numpy()
+    fin = np.isfinite(want)
+    assert np.array_equal(np.isfinite(got), fin)
+    for r in range(m):
+        f = fin[:, r]
+        if f.any() and np.abs(want[f, r]).max() > 0:
+            assert oracle.nmse(want[f, r], got[f, r]) <= NMSE_REF, (r, oracle.nmse(want[f, r], got[f, r]))
+    assert oracle.nmse(want[fin], got[fin]) <= NMSE_REF
+
+
+def test_mul_mat_q_matches_mat_vec_route_at_the_switch(kern, oracle):
+    """n = 8 takes the q8_1 mat-vec route, n = 9 the tensor-core route: the first 8 columns of both must agree within
+    the harness gate even for large activations (no cliff at the switch)."""
+    t, m, k = "q4_K", 256, 4096
+    w = random_blocks(t, m, k, seed=5)
+    x = (np.random.default_rng(6).standard_normal(size=(9, k)) * 3e4).astype(np.float32)
+    wd = dev_blocks(kern, w)
+    y8 = kern.mul_mat(t, wd, m, k, kern.to_device(x[:8])).cpu().numpy().reshape(8, m)
+    y9 = kern.mul_mat(t, wd, m, k, kern.to_device(x)).cpu().numpy().reshape(9, m)
+    assert np.isfinite(y9).all()
+    assert oracle.nmse(y8, y9[:8]) <= NMSE_REF
+
+
+# ---------------------------------------------------------------------------- BASELINE configs[3] / configs[4] at full size
+@pytest.mark.parametrize("t,m,k", [("q4_K", 28672, 8192), ("q4_K", 8192, 28672), ("q6_K", 4096, 14336), ("q4_K", 14336, 4096)])
+def test_configs34_decode_full_size_sampled_rows(kern, oracle, t, m, k):
+    """the Llama-3-70B FFN shapes of configs[4] and the Llama-3-8B shapes of configs[3], decode (n = 1 and 8) through the
+    list entry point: every output finite, a seeded sample of rows against the oracle, and row independence (the
+    row-split property): the sampled rows as a sub-matrix give the same bits."""
+    import b200
+    import torch
+    rng = np.random.default_rng(m + k)
+    rows = np.unique(np.concatenate([[0, 127, 128, m - 1], rng.integers(0, m, size=60)]))
+    sub = random_blocks(t, len(rows), k, seed=k)
+    rb = sub.shape[1]
+    wd = torch.randint(0, 256, (m * rb,), dtype=torch.uint8, device=kern.device)      # filler rows: any bytes are legal quants ..
+    wv = wd.view(m, rb)
+    for off in ((0, 2) if t != "q6_K" else (208,)):                                  # .. with sane fp16 scale fields
+        wv[:, off::(144 if t != "q6_K" else 210)] = 0
+        wv[:, off + 1::(144 if t != "q6_K" else 210)] = 0x20 if t != "q6_K" else 0x10
+    wv[torch.from_numpy(rows).to(kern.device).long()] = kern.to_device(sub)
+    for n in (1, 8):
+        x_np = rng.uniform(-1, 1, size=(n, k)).astype(np.float32)
+        x = kern.to_device(x_np)
+        y = torch.zeros((n, m), dtype=torch.float32, device=kern.device)
+        kern.mul_mat_batch((b200.MulMatNode * 1)(b200.mul_mat_node(t, wd.data_ptr(), m, k, x.data_ptr(), n, y.data_ptr())))
+        got = y.cpu().numpy()
+        assert np.isfinite(got).all()
+        want = oracle.mul_mat(t, sub, len(rows), k, x_np, mode=1)
+        assert oracle.nmse(want, got[:, rows]) <= NMSE_ORACLE, (n, oracle.nmse(want, got[:, rows]))
+        ys = torch.zeros((n, len(rows)), dtype=torch.float32, device=kern.device)
+        sd = kern.to_device(sub.reshape(-1))
+        kern.mul_mat_batch((b200.MulMatNode * 1)(b200.mul_mat_node(t, sd.data_ptr(), len(rows), k, x.data_ptr(), n, ys.data_ptr())))
+        assert np.array_equal(u32(ys.cpu().numpy()), u32(got[:, rows])), n
+
+
+@pytest.mark.parametrize("t,m,k", [("q4_K", 14336, 4096), ("q6_K", 4096, 14336), ("q4_K", 28672, 8192)])
+def test_configs34_prefill_n2048_sampled(kern, oracle, t, m, k):
+    """prefill n = 2048 (configs[3]; and the configs[4] gate/up shape): finite everywhere, sampled rows x sampled columns
+    against exact-activation truth."""
+    import torch
+    n = 2048
+    rng = np.random.default_rng(m + k + 1)
+    rows = np.unique(np.concatenate([[0, 127, 128, m - 1], rng.integers(0, m, size=20)]))
+    cols = np.unique(np.concatenate([[0, 255, 256, n - 1], rng.integers(0, n, size=60)]))
+    sub = random_blocks(t, len(rows), k, seed=k + 1)
+    rb = sub.shape[1]
+    wd = torch.zeros((m, rb), dtype=torch.uint8, device=kern.device)
+    wd[torch.from_numpy(rows).to(kern.device).long()] = kern.to_device(sub)
+    x_np = rng.uniform(-1, 1, size=(n, k)).astype(np.float32)
+    got = kern.mul_mat_q(t, wd.view(-1), m, k, kern.to_device(x_np)).cpu().numpy()
+    assert np.isfinite(got).all()
+    want = oracle.mul_mat(t, sub, len(rows), k, np.ascontiguousarray(x_np[cols]), mode=0)
+    assert oracle.nmse(want, got[np.ix_(cols, rows)]) <= NMSE_TC
+    other = np.setdiff1d(np.arange(m), rows)[:500]
+    assert not got[:, other].any()                      # all-zero weight rows give exact zeros
