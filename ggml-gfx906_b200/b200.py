@@ -43,6 +43,19 @@ class MulMatNode(C.Structure):
                 ("ne_b", C.c_int64 * 4), ("nb_b", C.c_size_t * 4), ("dst_dev", C.c_void_p)]
 
 
+class PeerGroup(C.Structure):
+    """struct b200_peer_group (include/ggml_b200.h): base[r] = this process's mapping of rank r's symmetric region."""
+    _fields_ = [("n_ranks", C.c_int32), ("rank", C.c_int32), ("base", C.c_void_p * 8), ("bytes", C.c_size_t)]
+
+
+def peer_group(rank: int, bases, nbytes: int) -> PeerGroup:
+    pg = PeerGroup()
+    pg.n_ranks = len(bases); pg.rank = rank; pg.bytes = nbytes
+    for r, b in enumerate(bases):
+        pg.base[r] = int(b)
+    return pg
+
+
 def mul_mat_node(t: str, a_ptr: int, m: int, k: int, b_ptr: int, n: int, dst_ptr: int,
                  a_row_stride: Optional[int] = None, b_row_stride: Optional[int] = None, const_weights: bool = False) -> MulMatNode:
     """A plain 2-D node: W[m rows of k] x X[n rows of k] -> dst[n][m]."""
@@ -95,6 +108,9 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
     lib.b200_mul_mat_batch_workspace_size.argtypes = [C.POINTER(MulMatNode), i64]
     lib.b200_mul_mat_batch.restype = i32
     lib.b200_mul_mat_batch.argtypes = [C.POINTER(MulMatNode), i64, vp, sz, vp]
+    lib.b200_peer_ctrl_bytes.restype = sz
+    lib.b200_mul_mat_batch_peers.restype = i32
+    lib.b200_mul_mat_batch_peers.argtypes = [C.POINTER(MulMatNode), i64, C.POINTER(PeerGroup), vp, sz, vp]
     lib.b200_mul_mat_batch_plan.restype = i32
     lib.b200_mul_mat_batch_plan.argtypes = [C.POINTER(MulMatNode), i64, C.POINTER(C.c_int32)]
     lib.b200_launch_count.restype = C.c_uint64
@@ -286,6 +302,14 @@ class Kernels:
                                              _a4s(nb_b), out.data_ptr(), ws.data_ptr(), ws.numel(), flags, self._stream()),
                     "mul_mat")
         return out
+
+    def mul_mat_batch_peers(self, nodes, peers: PeerGroup, count: Optional[int] = None, ws=None):
+        """row split: the list on this rank's row blocks with the gather fused into the launch (every rank calls it)."""
+        count = len(nodes) if count is None else count
+        if ws is None:
+            ws = self.workspace(int(self.lib.b200_mul_mat_batch_workspace_size(nodes, count)))
+        self._check(self.lib.b200_mul_mat_batch_peers(nodes, count, C.byref(peers), ws.data_ptr(), ws.numel(), self._stream()),
+                    "mul_mat_batch_peers")
 
     def mul_mat_batch(self, nodes, count: Optional[int] = None, ws=None):
         """nodes: a ctypes array of MulMatNode (see mul_mat_node); one host call for the whole list."""

@@ -259,10 +259,25 @@ struct batch_state {
 
 // plan != nullptr: dry run -- nothing is launched, no device is touched; plan[3 i .. 3 i + 2] = (launch group of node i,
 // list index of the node it waits for inside that group or -1, route: 0 per-node call, 1 persistent list, 2 MMA list)
+constexpr size_t PEER_CTRL_BYTES = 8192;          // head of the symmetric region: per format family an epoch word + 448 counters
+constexpr size_t PEER_CTRL_FAMILY = 2048;
+
 static int run_list(const b200_mul_mat_node * nodes, int64_t count, void * workspace_dev, size_t workspace_bytes, void * stream,
-                    int32_t * plan) {
+                    int32_t * plan, const b200_peer_group * pg = nullptr) {
     if (count < 0 || (count > 0 && !nodes)) return B200_ERR_SHAPE;
     const bool dry = plan != nullptr;
+    // row split (b200_mul_mat_batch_peers): the local copy of the symmetric region and the distances to the others
+    long long peer_delta[BATCH_MAX_PEERS];
+    int n_peers = 0;
+    uintptr_t sym_lo = 0, sym_hi = 0;
+    if (pg) {
+        if (pg->n_ranks < 1 || pg->n_ranks > BATCH_MAX_PEERS + 1 || pg->rank < 0 || pg->rank >= pg->n_ranks || pg->bytes < PEER_CTRL_BYTES) return B200_ERR_SHAPE;
+        for (int r = 0; r < pg->n_ranks; r++) {
+            if (!pg->base[r] || ((uintptr_t) pg->base[r] & 127)) return B200_ERR_STRIDE;
+            if (r != pg->rank) peer_delta[n_peers++] = (long long) ((intptr_t) pg->base[r] - (intptr_t) pg->base[pg->rank]);
+        }
+        sym_lo = (uintptr_t) pg->base[pg->rank] + PEER_CTRL_BYTES; sym_hi = (uintptr_t) pg->base[pg->rank] + pg->bytes;
+    }
     int group = 0;
     if (dry) { workspace_dev = (void *) (uintptr_t) 0x1000; workspace_bytes = (size_t) 1 << 40; }
     cudaStream_t st = (cudaStream_t) stream;
@@ -279,7 +294,11 @@ static int run_list(const b200_mul_mat_node * nodes, int64_t count, void * works
     static const int colmax = env_int("GGML_B200_BATCH_COLS", 8);
     ws_cursor cur;
     cur.reset((uint8_t *) workspace_dev, workspace_bytes);
-    for (int f = 0; f < 3; f++) fam_bb[f]->reset();
+    auto reset_family = [&](int f) {
+        fam_bb[f]->reset();
+        if (pg) fam_bb[f]->set_peers((unsigned *) ((uint8_t *) pg->base[pg->rank] + f * PEER_CTRL_FAMILY), peer_delta, n_peers);
+    };
+    for (int f = 0; f < 3; f++) reset_family(f);
     cols_bb->reset();
     reads.clear(); writes.clear();
     const int grid = dry ? 148 : current_caps().sm_count;
@@ -289,7 +308,7 @@ static int run_list(const b200_mul_mat_node * nodes, int64_t count, void * works
         int rc = B200_OK;
         if (dry) {
             if (!nothing_pending()) group++;
-            for (int f = 0; f < 3; f++) fam_bb[f]->reset();
+            for (int f = 0; f < 3; f++) reset_family(f);
             cols_bb->reset();
             cur.reset((uint8_t *) workspace_dev, workspace_bytes);
             return rc;
@@ -303,14 +322,15 @@ static int run_list(const b200_mul_mat_node * nodes, int64_t count, void * works
             // option batch_single = 1 / 0 forces the persistent / the per-node kernel.
             const int single_mode = b200_option(B200_OPT_BATCH_SINGLE);
             const batch_node nd = bb->args.nodes[0];
-            const bool single_persistent = single_mode >= 0 ? single_mode != 0
-                                         : (f == 0 && (int64_t) nd.m * nd.row_bytes >= (int64_t) 4 << 20);
+            const bool single_persistent = bb->args.last_scatter >= 0 ? true : (single_mode >= 0 ? single_mode != 0
+                                         : (f == 0 && (int64_t) nd.m * nd.row_bytes >= (int64_t) 4 << 20));
             if (bb->args.count == 1 && !single_persistent) {
                 rc = mmvq_fused_try(nd.type, nd.w, nd.row_stride, nd.m, nd.k, nd.x, nd.dst, bb->all_const, st);
                 if (rc == B200_STREAM_NOT_APPLICABLE) rc = batch_launch(*bb, st);
             } else {
                 rc = batch_launch(*bb, st);
             }
+            if (rc == B200_STREAM_NOT_APPLICABLE && bb->args.last_scatter >= 0) rc = B200_ERR_SHAPE;   // no per-node path scatters
             if (rc == B200_STREAM_NOT_APPLICABLE) {
                 // rows too long for two ring stages: the nodes of this builder one by one, in list order
                 rc = B200_OK;
@@ -321,7 +341,7 @@ static int run_list(const b200_mul_mat_node * nodes, int64_t count, void * works
                     rc = b200_mul_mat_ex(o.type_a, o.a_dev, o.ne_a, o.nb_a, bn.x, ne_b, o.nb_b, bn.dst, workspace_dev, workspace_bytes, o.flags, stream);
                 }
             }
-            bb->reset();
+            reset_family(f);
         }
         if (rc == B200_OK && !cols_bb->empty()) { rc = cols_launch(*cols_bb, st); cols_bb->reset(); }
         // stream order: the next launch's quantizer starts after these launches have finished with the workspace
@@ -343,6 +363,7 @@ static int run_list(const b200_mul_mat_node * nodes, int64_t count, void * works
         const bool to_cols = persistent && use_cols && flat && ncols >= 2 &&
                              cols_node_ok(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, nd.b_dev, (int64_t) nd.nb_b[1], ncols);
         if (!to_cols && !plain) {
+            if (pg && (uintptr_t) nd.dst_dev + 4 > sym_lo - PEER_CTRL_BYTES && (uintptr_t) nd.dst_dev < sym_hi) return B200_ERR_SHAPE;   // cannot scatter this shape
             int rc = flush();
             if (rc) return rc;
             if (dry) { plan[3 * i] = group++; plan[3 * i + 1] = -1; plan[3 * i + 2] = 0; continue; }
@@ -354,6 +375,10 @@ static int run_list(const b200_mul_mat_node * nodes, int64_t count, void * works
         const uintptr_t x0 = (uintptr_t) nd.b_dev, x1 = x0 + (size_t) (ncols - 1) * nd.nb_b[1] + (size_t) k * 4;
         const uintptr_t d0 = (uintptr_t) nd.dst_dev, d1 = d0 + (size_t) m * ncols * 4;
         const int owner = to_cols ? 3 : batch_family(nd.type_a);
+        // row split: a dst inside the symmetric region is scattered to every rank -- only the persistent list kernel does that
+        const bool scatter = pg && d0 >= sym_lo && d1 <= sym_hi;
+        if (pg && !scatter && d1 > sym_lo - PEER_CTRL_BYTES && d0 < sym_hi) return B200_ERR_STRIDE;     // straddles the region / its control block
+        if (scatter && (to_cols || ncols != 1)) return B200_ERR_SHAPE;
         // hazards against what is pending: inside the same persistent launch they become a dependency (dep = the
         // latest such node; a CTA finishes nodes in order, so its counter covers the earlier ones), anywhere else
         // (another launch of this flush, the MMA list kernel, several columns, chaining switched off) they cut the list
@@ -402,12 +427,18 @@ static int run_list(const b200_mul_mat_node * nodes, int64_t count, void * works
                 if (rc) return rc;
                 dep = -1; x_written = false;
             }
-            bool ok = bb->add(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, xc, dc, cw, grid, cur, dep, x_written && dep >= 0, (int) i);
+#ifdef B200_TUNING
+            // timing experiments only (wrong results): 1 = wait but take pre-quantized x, 2 = quantize in the launch but do not wait
+            static const int chain_dbg = env_int("GGML_B200_CHAIN_DBG", 0);
+            if (chain_dbg == 1) x_written = false;
+            if (chain_dbg == 2 && dep >= 0) { dep = -2; }
+#endif
+            bool ok = bb->add(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, xc, dc, cw, grid, cur, dep < 0 ? -1 : dep, x_written && dep != -1, (int) i, scatter);
             if (!ok && !nothing_pending()) {                   // workspace full: launch what is pending, start over
                 const int rc = flush();
                 if (rc) return rc;
                 dep = -1; x_written = false;
-                ok = bb->add(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, xc, dc, cw, grid, cur, -1, false, (int) i);
+                ok = bb->add(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, xc, dc, cw, grid, cur, -1, false, (int) i, scatter);
             }
             if (!ok) break;
         }
@@ -435,6 +466,14 @@ static int run_list(const b200_mul_mat_node * nodes, int64_t count, void * works
 extern "C" int b200_mul_mat_batch(const b200_mul_mat_node * nodes, int64_t count,
                                   void * workspace_dev, size_t workspace_bytes, void * stream) {
     return run_list(nodes, count, workspace_dev, workspace_bytes, stream, nullptr);
+}
+
+// Row split: the same list on every rank's row blocks, the gather fused into the launch (mmvq_batch.cuh).
+extern "C" size_t b200_peer_ctrl_bytes(void) { return PEER_CTRL_BYTES; }
+extern "C" int b200_mul_mat_batch_peers(const b200_mul_mat_node * nodes, int64_t count, const b200_peer_group * peers,
+                                        void * workspace_dev, size_t workspace_bytes, void * stream) {
+    if (!peers) return B200_ERR_SHAPE;
+    return run_list(nodes, count, workspace_dev, workspace_bytes, stream, nullptr, peers);
 }
 
 // How b200_mul_mat_batch would issue the list (host arithmetic only; no device needed).
@@ -485,4 +524,5 @@ extern "C" int b200_quantize_acts_columns(const float * x_dev, size_t x_row_stri
 #ifdef B200_TUNING
 // tuning builds only: every fused decode launch writes 8 globaltimer stamps per CTA into buf
 extern "C" __attribute__((visibility("default"))) void b200_debug_timestamps(void * buf) { g_fused_dbg = (unsigned long long *) buf; }
+extern "C" __attribute__((visibility("default"))) void b200_debug_batch_stamps(void * buf) { g_batch_dbg = (unsigned long long *) buf; }
 #endif

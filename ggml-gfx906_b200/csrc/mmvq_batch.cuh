@@ -38,6 +38,15 @@
 //     flag, one for x and the quantization (~1 us), not a kernel boundary (7-17 us measured, profiles/r01m).
 // The grid is one CTA per SM with 226 KB of shared memory each: all CTAs are co-resident, so the spins terminate.
 // The role CUDA-graph capture plays in the reference (src/ggml-cuda/ggml-cuda.cu:2876-3041) is played by this.
+//
+// Row split over the GPUs of a box (reference: peer-copy gather after every MUL_MAT, ggml-cuda.cu:1670-1739): the
+// gather is FUSED into this kernel.  Every rank runs the same list on its row blocks; a node whose dst lies in the
+// symmetric region (one copy per rank, peer-mapped: NVLink / NVSwitch) stores each finished row into EVERY rank's copy
+// (plain st.global on the peer addresses, as the rows are produced), and its completion counter is bumped on every
+// rank (red.release.sys); waits compare against epoch x ranks x CTAs (counters only grow; the epoch word is bumped by
+// the launch's quantize pre-pass).  A dependent node therefore waits for the gathered vector exactly as it waits for
+// a local one, and CTA 0 leaves the kernel only when the last scattered node is complete on all ranks: when the
+// launch is done, every rank holds every row.
 // b200_mul_mat_batch derives `dep` from the pointer ranges; hazards between different launches still cut the list.
 #pragma once
 #include <vector>
@@ -72,24 +81,58 @@ constexpr int BATCH_Q_LOAD   = 2;    // the activation producer bulk-copies nd.a
 constexpr int BATCH_Q_INK    = 4;    // the consumers quantize nd.x (written by node `dep` of this launch) into the buffer
 constexpr int BATCH_Q_SAME   = 8;    // same x, k and format as the previous node: the consumers keep their registers
 constexpr int BATCH_Q_SIGNAL = 16;   // a later node waits for this one: CTAs bump done[i] after their last row
+constexpr int BATCH_Q_SCATTER = 32;  // dst lies in the symmetric region: rows and the completion counter go to every rank
+constexpr int BATCH_MAX_PEERS = 7;   // other ranks of the box
 static_assert(sizeof(batch_node) == 64, "batch_node is part of the kernel parameter block");
 
 struct batch_args {
     int count, S, slot_stride, acts_stride;
     int off_part, off_acts, off_slots, const_weights;
     int NB, kmax, nwc, pad;
-    unsigned * done;                     // per-node completion counters (workspace; zeroed by k_quantize_batch)
+    unsigned * done;                     // per-node completion counters (workspace, zeroed by k_quantize_batch; or the symmetric
+                                         // region's control block, never zeroed: see epoch)
+    unsigned * epoch;                    // row split: launches of this family so far (bumped by k_quantize_batch); else NULL
+    long long  peer_delta[BATCH_MAX_PEERS];   // row split: byte distance from the local copy of the symmetric region to rank p's
+    int        n_peers, last_scatter;    // other ranks; index of the last BATCH_Q_SCATTER node (the launch's closing barrier), -1
+#ifdef B200_TUNING
+    unsigned long long * dbg;            // [node < 96][CTA][4] globaltimer stamps: consumers released, CTA done, flag seen, first stage
+#endif
     batch_node nodes[BATCH_MAX_NODES];
 };
+#ifdef B200_TUNING
+#define BATCH_STAMP(node, slot) do { if (a.dbg && (node) < 96) a.dbg[((size_t) (node) * gridDim.x + blockIdx.x) * 8 + (slot)] = gtime(); } while (0)
+#else
+#define BATCH_STAMP(node, slot) do { } while (0)
+#endif
 
 // gpu-scope release / acquire on the completion counters
 __device__ __forceinline__ void red_release_gpu_add(unsigned * p, unsigned v) {
     asm volatile("red.release.gpu.global.add.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
 }
-__device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned * p) {
+__device__ __forceinline__ unsigned ld_relaxed_gpu(const unsigned * p) {
     unsigned v;
-    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
+}
+__device__ __forceinline__ void red_release_sys_add(unsigned * p, unsigned v) {
+    asm volatile("red.release.sys.global.add.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_relaxed_sys(const unsigned * p) {
+    unsigned v;
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+// wait until counter *ctr has reached `target` (counters only grow; wrap-safe).  One lane polls; a bound turns a logic
+// error (or a rank that never launched) into a trap instead of a hang.
+__device__ __forceinline__ void batch_wait_counter(const unsigned * ctr, unsigned target, bool sys) {
+    unsigned spins = 0;
+    if (sys) {
+        while ((int) (ld_relaxed_sys(ctr) - target) < 0) { if (++spins > (1u << 26)) __trap(); }
+        asm volatile("fence.acq_rel.sys;" ::: "memory");
+    } else {
+        while ((int) (ld_relaxed_gpu(ctr) - target) < 0) { if (++spins > (1u << 25)) __trap(); }
+        asm volatile("fence.acq_rel.gpu;" ::: "memory");
+    }
 }
 
 // mbarrier ops on precomputed shared-window addresses (no generic -> shared conversion per call)
@@ -172,7 +215,10 @@ __global__ void __launch_bounds__(256) k_quantize_batch(const __grid_constant__ 
     const batch_node & nd = a.nodes[blockIdx.y];
     const int kb = blockIdx.x * 8 + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
-    if (blockIdx.x == 0 && threadIdx.x == 0 && a.done) a.done[blockIdx.y] = 0u;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        if (a.epoch) { if (blockIdx.y == 0) *a.epoch += 1u; }      // row split: counters keep growing, the epoch moves the target
+        else if (a.done) a.done[blockIdx.y] = 0u;
+    }
     if (!(nd.qflags & BATCH_Q_PRE) || kb * 32 >= nd.k) return;
     const float x = __ldg(nd.x + kb * 32 + lane);
     const float amax = warp_max(fabsf(x));
@@ -215,7 +261,7 @@ __device__ __forceinline__ void batch_quantize_ink(const float * x, const int k,
     float  * yd = reinterpret_cast<float *>(actbuf + k);
     const int nblk32 = k >> 5;
     const int sub = lane >> 3, l8 = lane & 7;
-    constexpr int U = 4;                                      // loads in flight per lane
+    constexpr int U = 4;                                      // loads in flight per lane (8 would cover k = 11008 in one round trip but spills the consumers)
     for (int blk0 = cw * 4 + sub; blk0 < nblk32; blk0 += nwc * 4 * U) {
         float4 vv[U];
 #pragma unroll
@@ -249,8 +295,17 @@ __device__ __forceinline__ void batch_quantize_ink(const float * x, const int k,
     }
 }
 
+// a finished row value -> dst, and (row split) -> the same place in every other rank's copy of the symmetric region
+__device__ __forceinline__ void batch_store_row(float * p, float v, const batch_args & a, bool scatter) {
+    *p = v;
+    if (scatter) {
+#pragma unroll 1
+        for (int r = 0; r < a.n_peers; r++) *reinterpret_cast<float *>(reinterpret_cast<char *>(p) + a.peer_delta[r]) = v;
+    }
+}
+
 template <int T>
-__device__ __forceinline__ void batch_consume(const cnode & nd, acts128 & acts, const int cw, const int lane,
+__device__ __forceinline__ void batch_consume(const batch_args & a, const cnode & nd, acts128 & acts, const int cw, const int lane,
                                               int & st_s, uint32_t & st_ph, int & cc, int & git,
                                               const uint8_t * actbuf, const uint32_t acts_free, const uint32_t full, const uint32_t empty,
                                               float * part, const uint8_t * slots, const int S, const int slot_stride) {
@@ -263,6 +318,7 @@ __device__ __forceinline__ void batch_consume(const cnode & nd, acts128 & acts, 
     const int items = nd.k >> 7;
     const int idx = wg * 32 + lane;                      // the 128-weight item of a row this lane owns
     const bool active = g < G && idx < items;
+    const bool scatter = (nd.qflags & BATCH_Q_SCATTER) != 0;
 
     // the slice of K this lane owns, in registers for the node (kept from the previous node when it has the same
     // activations, k and format: q/k/v, gate/up)
@@ -343,7 +399,7 @@ __device__ __forceinline__ void batch_consume(const cnode & nd, acts128 & acts, 
                 for (int off = 8; off > 0; off >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, off);
                 const int r = r0 + (lane >> 4);
                 if ((lane & 15) == 0 && r < rows_here) {
-                    if (W == 1) dst[lb * R + r] = v;
+                    if (W == 1) batch_store_row(dst + lb * R + r, v, a, scatter);
                     else        pb[r * W + wg] = v;
                 }
             }
@@ -363,7 +419,7 @@ __device__ __forceinline__ void batch_consume(const cnode & nd, acts128 & acts, 
                     if (r < rows_here) {
                         float v = 0.0f;
                         for (int u = 0; u < W; u++) v += pb[r * W + u];
-                        dst[lb * R + r] = v;
+                        batch_store_row(dst + lb * R + r, v, a, scatter);
                     }
                 }
             }
@@ -454,6 +510,9 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
     if (warp == 1) {
         // ===================================================== activation producer: q8 activations of node i -> buffer i % NB
         pdl_wait();                                               // k_quantize_batch (and whatever made x) is done
+        // arrivals a complete node has had: one per CTA (and per rank), times the launches so far when counters are not reset
+        const unsigned per_launch = (unsigned) (a.n_peers + 1) * gridDim.x;   // (scattered nodes; gridDim.x for local ones)
+        const unsigned epoch_now = a.epoch ? ld_relaxed_sys(a.epoch) : 1u;
         node_cache cache;
         int slab_v = (int) blockIdx.x;
         for (int i = 0; i < a.count; i++) {
@@ -466,9 +525,10 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
                 // the node this one reads from (or must not overtake) is complete on EVERY CTA: acquire its counter.
                 // All CTAs are resident (one per SM), so the wait ends; a bound turns a logic error into a trap, not a hang.
                 if (lane == 0) {
-                    const unsigned * ctr = a.done + nd.dep;
-                    unsigned spins = 0;
-                    while (ld_acquire_gpu(ctr) < gridDim.x) { if (++spins > (1u << 25)) __trap(); }
+                    // a scattered node is complete when every CTA of every rank has arrived, a local one when every CTA has
+                    const bool dep_all = (a.nodes[nd.dep].qflags & BATCH_Q_SCATTER) != 0;
+                    batch_wait_counter(a.done + nd.dep, (dep_all ? per_launch : gridDim.x) * epoch_now, a.n_peers > 0);
+                    BATCH_STAMP(i, 2);
                 }
                 __syncwarp();
             }
@@ -490,6 +550,11 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
             }
             __syncwarp();
         }
+        // row split: the launch is over when the last scattered node is complete on every rank -- CTA 0 stays for it
+        if (a.n_peers > 0 && a.last_scatter >= 0 && blockIdx.x == 0) {
+            if (lane == 0) batch_wait_counter(a.done + a.last_scatter, per_launch * epoch_now, true);
+            __syncwarp();
+        }
         return;
     }
 
@@ -504,10 +569,16 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
         uint8_t * buf = actbufs + u * acts_stride;
         mbar_wait_a(ready_a + 8 * u, (uint32_t) uph);
         const cnode nd = *reinterpret_cast<const cnode *>(buf);
+        if (cw == 0 && lane == 0) BATCH_STAMP(i, 0);
         if (nd.qflags & BATCH_Q_INK) {
             batch_quantize_ink(nd.x, nd.k, buf + BATCH_AHDR, cw, lane, nwc);
             named_bar_sync(14, nwc * 32);                 // ids 1 .. 7 belong to the row groups (W > 1 -> G <= 7), 15 to the layout change
         }
+        if (cw == 0 && lane == 0) BATCH_STAMP(i, 3);
+#ifdef B200_TUNING
+        const int st_s0 = st_s;
+        if (cw == 0 && nd.nrows > 0) { mbar_wait_a(full_a + 8 * st_s0, st_ph); if (lane == 0) BATCH_STAMP(i, 4); }     // (a second wait on a completed phase returns at once)
+#endif
         // the partials area is laid out per W and only rows that need several warps (W > 1) use it: as long
         // as every such node of the list has the same W, the groups, their barriers and their buffer
         // parity (git) simply carry on across nodes; a different W needs every consumer warp to be past its
@@ -517,23 +588,32 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
             layout_w = nd.W;
         }
         if (FAM == 2) {
-            if (nd.type == T_Q8_0) batch_consume<T_Q8_0>(nd, acts, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
-            else                   batch_consume<T_Q4_0>(nd, acts, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
+            if (nd.type == T_Q8_0) batch_consume<T_Q8_0>(a, nd, acts, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
+            else                   batch_consume<T_Q4_0>(a, nd, acts, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
         }
-        else if (FAM == 1) { acts128 a6; batch_consume<T_Q6_K>(nd, a6, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride); }
-        else if (nd.type == T_Q5_K) batch_consume<T_Q5_K>(nd, acts, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
-        else                   batch_consume<T_Q4_K>(nd, acts, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
+        else if (FAM == 1) { acts128 a6; batch_consume<T_Q6_K>(a, nd, a6, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride); }
+        else if (nd.type == T_Q5_K) batch_consume<T_Q5_K>(a, nd, acts, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
+        else                   batch_consume<T_Q4_K>(a, nd, acts, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
+        if (cw == 0 && lane == 0) BATCH_STAMP(i, 5);
         if (nd.qflags & BATCH_Q_SIGNAL) {
             // this warp's rows of node i are stored; the last of the CTA's consumer warps to get here releases them
             // to the other CTAs (cta-scope fences chain the warps' stores to the gpu-scope release)
             __syncwarp();
             if (lane == 0) {
-                __threadfence_block();
+                asm volatile("fence.acq_rel.cta;" ::: "memory");
                 const unsigned old = atomicAdd(&sdone[i & 7], 1u);
                 if (old == (unsigned) nwc - 1u) {
+                    asm volatile("fence.acq_rel.cta;" ::: "memory");      // the other warps' arrivals, hence their stores, are observed ..
                     sdone[i & 7] = 0u;
-                    __threadfence();
-                    red_release_gpu_add(nd.signal, 1u);
+                    if (nd.qflags & BATCH_Q_SCATTER) {                     // .. and released (cumulatively) to every rank
+                        red_release_sys_add(nd.signal, 1u);
+#pragma unroll 1
+                        for (int r = 0; r < a.n_peers; r++)
+                            red_release_sys_add(reinterpret_cast<unsigned *>(reinterpret_cast<char *>(nd.signal) + a.peer_delta[r]), 1u);
+                    } else {
+                        red_release_gpu_add(nd.signal, 1u);                // .. and released (cumulatively) to the other CTAs
+                    }
+                    BATCH_STAMP(i, 1);
                 }
             }
         }
@@ -584,7 +664,17 @@ struct batch_builder {
     std::vector<int> orig;            // index of each node in the caller's list (fallback replay)
     explicit batch_builder(int family) : fam(family) { reset(); }
     int64_t bytes_w14 = 0, bytes_w12 = 0;                       // weight bytes of nodes that gain / do not gain from 14 consumer warps
-    void reset() { args.count = 0; args.kmax = 0; args.done = nullptr; max_slot = 0; all_const = true; bytes_w14 = bytes_w12 = 0; orig.clear(); }
+    int waited = -1;                  // the latest node some earlier node of this launch already waits for
+    void reset() {
+        args.count = 0; args.kmax = 0; args.done = nullptr; args.epoch = nullptr; args.n_peers = 0; args.last_scatter = -1;
+        max_slot = 0; all_const = true; bytes_w14 = bytes_w12 = 0; orig.clear(); waited = -1;
+    }
+    // row split: the family's control block in the local copy of the symmetric region (epoch word, then the counters)
+    // and the byte distances to the other ranks' copies
+    void set_peers(unsigned * ctrl, const long long * delta, int n_peers) {
+        args.epoch = ctrl; args.done = ctrl + 16; args.n_peers = n_peers;
+        for (int r = 0; r < n_peers; r++) args.peer_delta[r] = delta[r];
+    }
     bool full() const { return args.count >= BATCH_MAX_NODES; }
     bool empty() const { return args.count == 0; }
 
@@ -592,7 +682,7 @@ struct batch_builder {
     // writes, or overwrites what it reads), -1: none; x_from_dep: x is written by a node of this builder.
     // false: the workspace cannot hold this node's activation record
     bool add(int type, const uint8_t * w, int64_t row_stride, int64_t m, int64_t k, const float * x, float * dst, bool const_w, int grid,
-             ws_cursor & cur, int dep = -1, bool x_from_dep = false, int orig_index = -1) {
+             ws_cursor & cur, int dep = -1, bool x_from_dep = false, int orig_index = -1, bool scatter = false) {
         static const int slot_target = env_int("GGML_B200_BATCH_SLOT_BYTES", 46080);
         if (!args.done) {                                       // first node since reset: the launch's completion counters
             if (BATCH_DONE_BYTES > cur.left) return false;
@@ -601,7 +691,11 @@ struct batch_builder {
         batch_node & nd = args.nodes[args.count];
         const batch_node * prev = args.count > 0 ? &args.nodes[args.count - 1] : nullptr;
         const bool same_x = prev && prev->x == x && prev->k == k;
-        nd.dep = (short) dep;
+        // a CTA finishes nodes in order and the activation producer publishes them in order: once a node has waited for
+        // node d, every node <= d is complete for all later nodes too -- they need no wait of their own (a poll under
+        // load queues behind the SM's outstanding weight copies: measured ~3 us, profiles/r02e_chain_stamps.txt)
+        nd.dep = (short) (dep > waited ? dep : -1);
+        if (dep > waited) waited = dep;
         if (same_x && prev->type == type && fam != 1) {           // (Q6_K's 27-word items leave no registers to keep them in)
             // same activations and format as the previous node (q/k/v, gate/up): the consumers keep their registers.
             // (the previous node already waited for whatever wrote x; a hazard of this node's own dst still sets dep)
@@ -615,7 +709,8 @@ struct batch_builder {
             if (need > cur.left) return false;
             nd.acts = cur.p; nd.qflags = BATCH_Q_PRE | BATCH_Q_LOAD; cur.p += need; cur.left -= need;
         }
-        if (dep >= 0) args.nodes[dep].qflags |= BATCH_Q_SIGNAL;
+        if (nd.dep >= 0) args.nodes[nd.dep].qflags |= BATCH_Q_SIGNAL;
+        if (scatter) { nd.qflags |= BATCH_Q_SCATTER; args.last_scatter = args.count; }
         orig.push_back(orig_index);
         args.count++;
         nd.w = w; nd.x = x; nd.dst = dst; nd.row_stride = row_stride; nd.m = (int) m; nd.k = (int) k;
@@ -652,22 +747,35 @@ struct batch_builder {
     }
 };
 
+#ifdef B200_TUNING
+static unsigned long long * g_batch_dbg = nullptr;   // set through b200_debug_batch_stamps (tuning builds only)
+#endif
 static int batch_launch(batch_builder & bb, cudaStream_t st) {
     if (bb.empty()) return B200_OK;
+#ifdef B200_TUNING
+    bb.args.dbg = g_batch_dbg;
+#endif
     const dev_caps & caps = current_caps();
     batch_args & a = bb.args;
     static const int s_env = env_int("GGML_B200_BATCH_STAGES", BATCH_MAX_STAGES);
     static const int nb_env = env_int("GGML_B200_BATCH_ABUF", 2);
     static const int pdl = env_int("GGML_B200_FUSED_PDL", 1);
     a.const_weights = bb.all_const ? 1 : 0;
+    if (a.last_scatter >= 0) a.nodes[a.last_scatter].qflags |= BATCH_Q_SIGNAL;      // the closing barrier of a row-split launch
     // consumer warps: 12 (14 warps = 448 threads) is 1-1.5 % faster on one-warp rows (k <= 4096) than 14; rows of
     // 7 warps (k = 28672, the Llama-3-70B down projection) leave 5 of 12 idle but fill 14 (60 % -> 85 % of the
     // measured HBM peak), rows of 2 warps gain 2 %.  Both are within the 128-register ceiling (<= 4 warps / SMSP).
     static const int nwc_env = env_int("GGML_B200_BATCH_NWC", 0);
-    a.nwc = nwc_env == 12 || nwc_env == 14 ? nwc_env : (bb.bytes_w14 > bb.bytes_w12 ? 14 : 12);
+    // A launch with chain links is bound by the LATENCY of a node on one CTA (a dependent node cannot start before the
+    // previous one has finished everywhere): 14 warps take the 14 row pairs of a 4096-row slab in one round instead of two
+    // (measured, profiles/r02c_chain_stamps.txt: 1.25 us per round of row pairs).
+    static const int chain_nwc = env_int("GGML_B200_CHAIN_NWC", 14);
+    bool chained = false;
+    for (int i = 0; i < a.count; i++) chained = chained || a.nodes[i].dep >= 0;
+    a.nwc = nwc_env == 12 || nwc_env == 14 ? nwc_env : (chained ? chain_nwc : (bb.bytes_w14 > bb.bytes_w12 ? 14 : 12));
     for (int i = 0; i < a.count; i++) {
         const int G = a.nwc / a.nodes[i].W;
-        a.nodes[i].G = (unsigned char) (a.nodes[i].W == 1 && G > 12 ? 12 : G);
+        a.nodes[i].G = (unsigned char) (a.nodes[i].W == 1 && G > 12 && !chained ? 12 : G);
     }
     a.slot_stride = (bb.max_slot + 127) & ~127;
     a.off_part    = (2 * BATCH_MAX_STAGES + 2 * BATCH_MAX_ABUF) * 8 + 8 * (int) sizeof(unsigned);

@@ -60,3 +60,30 @@ def gather_rows(dist, out, bounds: Sequence[int], rank: int):
         if r != rank:
             out[:, bounds[r]:bounds[r + 1]] = parts[r, :, :sizes[r]]
     return out
+
+
+class SymmetricRegion:
+    """One buffer per rank, every rank's copy mapped into every process (NVLink peer mappings), for
+    b200_mul_mat_batch_peers: the row blocks a rank computes are stored straight into all copies from inside the
+    persistent launch.  Plumbing only: torch.distributed's symmetric memory does the allocation and the handle
+    exchange (CUDA VMM / IPC); `bases[r]` is the address of rank r's copy in THIS process.  The first
+    `ctrl_bytes` bytes belong to the kernel library (zeroed here); `data` is the rest as a uint8 tensor."""
+
+    def __init__(self, dist, nbytes: int, device, ctrl_bytes: int):
+        import torch
+        import torch.distributed._symmetric_memory as symm
+        self.rank, self.world = dist.get_rank(), dist.get_world_size()
+        self.nbytes = (int(nbytes) + ctrl_bytes + 255) // 256 * 256
+        self.buf = symm.empty(self.nbytes, dtype=torch.uint8, device=device)
+        self.handle = symm.rendezvous(self.buf, dist.group.WORLD.group_name)
+        self.bases = [int(p) for p in self.handle.buffer_ptrs]
+        assert len(self.bases) == self.world and self.bases[self.rank] == self.buf.data_ptr()
+        self.buf.zero_()
+        torch.cuda.synchronize()
+        dist.barrier()
+        self.ctrl_bytes = ctrl_bytes
+        self.data = self.buf[ctrl_bytes:]
+
+    def peer_group(self):
+        import b200
+        return b200.peer_group(self.rank, self.bases, self.nbytes)

@@ -179,6 +179,31 @@ B200_API size_t b200_mul_mat_batch_workspace_size(const b200_mul_mat_node * node
 B200_API int    b200_mul_mat_batch(const b200_mul_mat_node * nodes, int64_t count,
                                    void * workspace_dev, size_t workspace_bytes, void * stream);
 
+/* ---- row split over the GPUs of one box -------------------------------------------------------
+ * replaces the per-MUL_MAT broadcast + peer-copy gather of ggml_cuda_op_mul_mat for split tensors
+ * (src/ggml-cuda/ggml-cuda.cu:1441-1759, call sites :1670-1739) and what a separate ncclAllGather would do.
+ *
+ * Every rank (a process per GPU, or a device of one process) holds its ROW BLOCK of each weight matrix and one copy of
+ * a "symmetric region": `bytes` bytes at base[r] for rank r, all copies mapped into this process (CUDA IPC / peer
+ * access: NVLink).  The first b200_peer_ctrl_bytes() bytes of the region are control words owned by the library (zero
+ * them once, before the first call); the rest is the caller's, laid out identically on every rank.
+ * b200_mul_mat_batch_peers is b200_mul_mat_batch with one addition: a node whose dst_dev lies in the LOCAL copy of the
+ * region stores every finished output row into EVERY rank's copy at the same offset, from inside the persistent
+ * launch, and the call's work on `stream` completes only when the scattered rows of all ranks have landed locally.
+ * If rank r passes dst_dev = base[r] + off + 4 * row_low(r) for a node, every rank ends with the whole output vector at
+ * base[*] + off -- the all-gather, fused.  A node may read such a gathered vector as its activations (chained inside
+ * the launch like any other dependency).  All ranks must issue the same list (SPMD); scattered nodes must be
+ * one-column decode nodes of the persistent list kernel (other shapes return B200_ERR_SHAPE).  The caller keeps a rank
+ * from starting the next call while another rank still reads the region (as with NCCL). */
+typedef struct b200_peer_group {
+    int32_t n_ranks, rank;
+    void *  base[8];
+    size_t  bytes;
+} b200_peer_group;
+B200_API size_t b200_peer_ctrl_bytes(void);
+B200_API int    b200_mul_mat_batch_peers(const b200_mul_mat_node * nodes, int64_t count, const b200_peer_group * peers,
+                                         void * workspace_dev, size_t workspace_bytes, void * stream);
+
 /* How the list would be issued, without touching a device: plan[3 i] = launch group of node i (nodes of a group share
  * one launch pair per format family), plan[3 i + 1] = list index of the node it waits for INSIDE its launch (-1: none),
  * plan[3 i + 2] = route (0: per-node call, 1: persistent list kernel, 2: 2..8-column MMA list kernel). */

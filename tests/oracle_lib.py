@@ -123,3 +123,15 @@ def random_blocks(t, nrows, k, seed):
         raw[:, :, off] = (v & 0xFF).astype(np.uint8)
         raw[:, :, off + 1] = (v >> 8).astype(np.uint8)
     return raw.reshape(nrows, nb * bs)
+
+
+def scale_blocks(t, blocks, factor):
+    """multiply every fp16 scale field of the blocks by `factor` (in place, RN to fp16): dequantized values scale with it"""
+    nrows = blocks.shape[0]
+    raw = blocks.reshape(nrows, -1, BLOCK_BYTES[t])
+    for off in F16_FIELDS[t]:
+        v = (raw[:, :, off].astype(np.uint16) | (raw[:, :, off + 1].astype(np.uint16) << 8)).view(np.float16)
+        v = (v.astype(np.float32) * np.float32(factor)).astype(np.float16).view(np.uint16)
+        raw[:, :, off] = (v & 0xFF).astype(np.uint8)
+        raw[:, :, off + 1] = (v >> 8).astype(np.uint8)
+    return blocks

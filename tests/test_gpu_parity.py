@@ -24,6 +24,12 @@ def u32(a):
     return np.ascontiguousarray(a).view(np.uint32)
 
 
+def nmse64(want, got):
+    """NMSE in float64 (the oracle's helper squares in f32: values near 1e+-30 over/underflow there)"""
+    w, g = np.asarray(want, dtype=np.float64).reshape(-1), np.asarray(got, dtype=np.float64).reshape(-1)
+    return float(((w - g) ** 2).sum() / (w ** 2).sum())
+
+
 def dev_blocks(kern, blocks):
     return kern.to_device(np.ascontiguousarray(blocks).reshape(-1))
 
@@ -633,9 +639,16 @@ def _decoder_chain(kern, types, hidden, ffn, layers, vocab, seed):
         specs.append((td, hidden, ffn, f"u{l}", f"d{l}"))
         cur = f"d{l}"
     specs.append((tout, vocab, hidden, cur, "logits"))
-    ws_np, ws = [], []
+    # random blocks amplify (|y| ~ 30 |x| per node): without the normalisations of a real model the chain would overflow
+    # after a few layers, so every node's scale fields are calibrated to unit output RMS on the way (a stand-in for them)
+    from oracle_lib import Oracle, scale_blocks
+    orc = Oracle()
+    ws_np, ws, vals = [], [], {"h0": h0_np}
     for i, (t, m, k, src, dst) in enumerate(specs):
         w = random_blocks(t, m, k, seed=seed + 13 * i)
+        y = orc.mul_mat(t, w, m, k, vals[src].reshape(1, k), mode=1)
+        scale_blocks(t, w, 1.0 / max(float(np.sqrt(np.mean(y.astype(np.float64) ** 2))), 1e-30))
+        vals[dst] = orc.mul_mat(t, w, m, k, vals[src].reshape(1, k), mode=1)
         ws_np.append(w); ws.append(dev_blocks(kern, w))
         bufs[dst] = torch.zeros((1, m), dtype=torch.float32, device=dev)
     nodes = (b200.MulMatNode * len(specs))(*[
@@ -738,9 +751,9 @@ def test_mul_mat_chain_write_after_read_and_reused_buffers(kern, oracle):
     a2 = kern.mul_mat("q4_K", ws[2], k, k, r)
     c1 = kern.mul_mat("q4_K", ws[4], k, k, x)
     b2 = kern.mul_mat("q4_K", ws[0], k, k, c1)
-    assert np.array_equal(u32(outs[0][0]), u32(a2.cpu().numpy()))
-    assert np.array_equal(u32(outs[0][2]), u32(c1.cpu().numpy()))
-    assert np.array_equal(u32(outs[0][1]), u32(b2.cpu().numpy()))
+    assert np.array_equal(u32(outs[0][0].reshape(-1)), u32(a2.cpu().numpy().reshape(-1)))
+    assert np.array_equal(u32(outs[0][2].reshape(-1)), u32(c1.cpu().numpy().reshape(-1)))
+    assert np.array_equal(u32(outs[0][1].reshape(-1)), u32(b2.cpu().numpy().reshape(-1)))
 
 
 @pytest.mark.parametrize("t", FUSED_TYPES)
@@ -886,8 +899,8 @@ def test_mul_mat_q_scale_invariance(kern, oracle, t, scale):
     assert not got[5].any()
     for c in range(n):
         if c != 5:
-            assert oracle.nmse(want[c], got[c]) <= NMSE_REF, (c, oracle.nmse(want[c], got[c]))
-    assert oracle.nmse(want, got) <= NMSE_TC
+            assert nmse64(want[c], got[c]) <= NMSE_REF, (c, nmse64(want[c], got[c]))
+    assert nmse64(want, got) <= NMSE_TC
 
 
 @pytest.mark.parametrize("t", QUANT_TYPES)
