@@ -43,8 +43,9 @@
 // gather is FUSED into this kernel.  Every rank runs the same list on its row blocks; a node whose dst lies in the
 // symmetric region (one copy per rank, peer-mapped: NVLink / NVSwitch) stores each finished row into EVERY rank's copy
 // (plain st.global on the peer addresses, as the rows are produced), and its completion counter is bumped on every
-// rank (red.release.sys); waits compare against epoch x ranks x CTAs (counters only grow; the epoch word is bumped by
-// the launch's quantize pre-pass).  A dependent node therefore waits for the gathered vector exactly as it waits for
+// rank (red.release.sys).  The counters are double-buffered by the parity of the launch count ("epoch", bumped by the
+// launch's quantize pre-pass, which also zeroes the OTHER set: no rank can touch that set before this rank has finished
+// the current launch, because every rank's closing barrier needs it).  A dependent node waits for the gathered vector exactly as it waits for
 // a local one, and CTA 0 leaves the kernel only when the last scattered node is complete on all ranks: when the
 // launch is done, every rank holds every row.
 // b200_mul_mat_batch derives `dep` from the pointer ranges; hazards between different launches still cut the list.
@@ -215,9 +216,17 @@ __global__ void __launch_bounds__(256) k_quantize_batch(const __grid_constant__ 
     const batch_node & nd = a.nodes[blockIdx.y];
     const int kb = blockIdx.x * 8 + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-        if (a.epoch) { if (blockIdx.y == 0) *a.epoch += 1u; }      // row split: counters keep growing, the epoch moves the target
-        else if (a.done) a.done[blockIdx.y] = 0u;
+    if (a.epoch) {
+        // row split: this launch counts in set (epoch & 1); the other set is zeroed for the next launch (see the header)
+        if (blockIdx.x == 0 && blockIdx.y == 0) {
+            __shared__ unsigned e_new;
+            if (threadIdx.x == 0) { e_new = *a.epoch + 1u; *a.epoch = e_new; }
+            __syncthreads();
+            unsigned * other = a.done + ((e_new + 1u) & 1u) * BATCH_MAX_NODES;
+            for (int j = threadIdx.x; j < BATCH_MAX_NODES; j += 256) other[j] = 0u;
+        }
+    } else if (blockIdx.x == 0 && threadIdx.x == 0 && a.done) {
+        a.done[blockIdx.y] = 0u;
     }
     if (!(nd.qflags & BATCH_Q_PRE) || kb * 32 >= nd.k) return;
     const float x = __ldg(nd.x + kb * 32 + lane);
@@ -510,9 +519,9 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
     if (warp == 1) {
         // ===================================================== activation producer: q8 activations of node i -> buffer i % NB
         pdl_wait();                                               // k_quantize_batch (and whatever made x) is done
-        // arrivals a complete node has had: one per CTA (and per rank), times the launches so far when counters are not reset
-        const unsigned per_launch = (unsigned) (a.n_peers + 1) * gridDim.x;   // (scattered nodes; gridDim.x for local ones)
-        const unsigned epoch_now = a.epoch ? ld_relaxed_sys(a.epoch) : 1u;
+        // arrivals a complete node has had: one per CTA, for a scattered node from every rank
+        const unsigned per_launch = (unsigned) (a.n_peers + 1) * gridDim.x;
+        unsigned * const done_set = a.done + (a.epoch ? (ld_relaxed_sys(a.epoch) & 1u) * BATCH_MAX_NODES : 0u);
         node_cache cache;
         int slab_v = (int) blockIdx.x;
         for (int i = 0; i < a.count; i++) {
@@ -527,7 +536,7 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
                 if (lane == 0) {
                     // a scattered node is complete when every CTA of every rank has arrived, a local one when every CTA has
                     const bool dep_all = (a.nodes[nd.dep].qflags & BATCH_Q_SCATTER) != 0;
-                    batch_wait_counter(a.done + nd.dep, (dep_all ? per_launch : gridDim.x) * epoch_now, a.n_peers > 0);
+                    batch_wait_counter(done_set + nd.dep, dep_all ? per_launch : gridDim.x, a.n_peers > 0);
                     BATCH_STAMP(i, 2);
                 }
                 __syncwarp();
@@ -539,7 +548,7 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
                 hd->r_begin = r_begin; hd->nrows = nrows; hd->type = nd.type; hd->R = nd.R; hd->W = nd.W; hd->G = nd.G;
                 hd->skew0 = (int) (reinterpret_cast<uintptr_t>(nd.w + (int64_t) r_begin * nd.row_stride) & 15);
                 hd->rs16 = (int) (nd.row_stride & 15); hd->contiguous = nd.contiguous;
-                hd->qflags = nd.qflags; hd->x = nd.x; hd->signal = a.done + i;
+                hd->qflags = nd.qflags; hd->x = nd.x; hd->signal = done_set + i;
                 if (nd.qflags & BATCH_Q_LOAD) {
                     const uint32_t bytes = batch_acts_bytes(nd.k);    // k % 256 == 0: a multiple of 16
                     mbar_arrive_expect_tx(&acts_ready[u], bytes);     // release: the header is visible to whoever sees the phase complete
@@ -552,7 +561,7 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
         }
         // row split: the launch is over when the last scattered node is complete on every rank -- CTA 0 stays for it
         if (a.n_peers > 0 && a.last_scatter >= 0 && blockIdx.x == 0) {
-            if (lane == 0) batch_wait_counter(a.done + a.last_scatter, per_launch * epoch_now, true);
+            if (lane == 0) batch_wait_counter(done_set + a.last_scatter, per_launch, true);
             __syncwarp();
         }
         return;

@@ -106,14 +106,23 @@ def main():
         torch.cuda.synchronize()
         dist.barrier()
 
+    def say(msg):
+        if os.environ.get("PEERS_VERBOSE"):
+            print(f"[rank {rank}] {msg}", flush=True)
+
+    # the mapping itself: write a word into every other rank's copy with a plain torch op, read our own back
+    probe = region.data[pos - 128: pos - 124].view(torch.int32) if pos >= 128 else None
     ws = None
     for chain in (False, True):
+        say(f"chain={chain}")
         nodes, keep = make_nodes(chain)
         ws = torch.empty(int(kern.lib.b200_mul_mat_batch_workspace_size(nodes, len(specs))) + 256, dtype=torch.uint8, device=dev)
         for rep in range(3):                        # eager, the epochs advance
             clear()
             kern.mul_mat_batch_peers(nodes, pg, ws=ws)
+            say(f"launched rep {rep}")
             check(f"chain={chain} eager rep {rep}")
+            say(f"checked rep {rep}")
         clear()
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g):

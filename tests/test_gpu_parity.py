@@ -988,3 +988,39 @@ def test_configs34_prefill_n2048_sampled(kern, oracle, t, m, k):
     assert oracle.nmse(want, got[np.ix_(cols, rows)]) <= NMSE_TC
     other = np.setdiff1d(np.arange(m), rows)[:500]
     assert not got[:, other].any()                      # all-zero weight rows give exact zeros
+
+
+def test_mul_mat_batch_peers_group_of_one(kern, oracle):
+    """b200_mul_mat_batch_peers with a single rank (no peers): the symmetric-region bookkeeping (control block, epochs
+    that advance from call to call, the closing barrier) on one GPU; same bits as b200_mul_mat_batch.  The multi-rank
+    scatter itself needs >= 2 GPUs (tests/test_gpu_peers.py)."""
+    import b200
+    import torch
+    hidden, ffn = 1024, 3072
+    ctrl = int(kern.lib.b200_peer_ctrl_bytes())
+    region = torch.zeros(ctrl + 4 * (hidden + 2 * ffn + hidden) + 1024, dtype=torch.uint8, device=kern.device)
+    base = region.data_ptr()
+    assert base % 128 == 0
+    data = region[ctrl:]
+    h0 = np.random.default_rng(1).uniform(-1, 1, size=(1, hidden)).astype(np.float32)
+    data[:4 * hidden].view(torch.float32).copy_(torch.from_numpy(h0.reshape(-1)))
+    offs = {"h0": 0, "g": 4 * hidden, "u": 4 * (hidden + ffn), "d": 4 * (hidden + 2 * ffn)}
+    specs = [(ffn, hidden, "h0", "g"), (ffn, hidden, "h0", "u"), (hidden, ffn, "u", "d")]
+    ws_np = [random_blocks("q4_K", m, k, seed=60 + i) for i, (m, k, _, _) in enumerate(specs)]
+    wd = [dev_blocks(kern, w) for w in ws_np]
+    nodes = (b200.MulMatNode * 3)(*[b200.mul_mat_node("q4_K", w.data_ptr(), m, k, base + ctrl + offs[src], 1, base + ctrl + offs[dst])
+                                    for (m, k, src, dst), w in zip(specs, wd)])
+    pg = b200.peer_group(0, [base], region.numel())
+    outs = []
+    for rep in range(3):
+        data[4 * hidden:].zero_()
+        kern.mul_mat_batch_peers(nodes, pg)
+        torch.cuda.synchronize()
+        outs.append(data[4 * hidden:4 * (2 * hidden + 2 * ffn)].view(torch.float32).cpu().numpy().copy())
+    data[4 * hidden:].zero_()
+    kern.mul_mat_batch(nodes)
+    torch.cuda.synchronize()
+    plain = data[4 * hidden:4 * (2 * hidden + 2 * ffn)].view(torch.float32).cpu().numpy().copy()
+    for o in outs:
+        assert np.array_equal(u32(o), u32(plain))
+    assert np.isfinite(plain).all() and np.abs(plain).max() > 0
