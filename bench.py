@@ -1,23 +1,30 @@
 #!/usr/bin/env python
 """bench.py — the headline measurement of the B200 ggml quantized hot path.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--stack ...]
 
-Workload (N = 1): BASELINE.json configs[2] — the decode mat-vec (n = 1) over every projection of
-Llama-2-7B in Q4_K (226 matrices, 3.716 GB of quant blocks, far larger than L2, so every step
-streams its weights from HBM; no L2 flush is needed).  A "step" is one token: 226 MUL_MATs issued
-through the C ABI (b200_mul_mat: activation quantization + mat-vec each).
-  metric  quant_matvec_GBps  = algorithmic bytes of the step / step time
-  value   device-resident: weights, activations and outputs in HBM, the step replayed from a CUDA graph
-  e2e     the same step with HOST activations and outputs: pinned host -> device copy of every
-          activation vector, the 226 C-ABI calls, device -> pinned host copy of every output, all
-          inside the timed region (weights are the model: uploaded once, as ggml does)
-N > 1: the row-split path (BASELINE configs[4] semantics on the same stack): every matrix has N x
-the rows, rank r owns an equal row block, each mat-vec is followed by an all-gather of the f32 row
-blocks so that every rank holds the full output.  Per-GPU work is constant (weak scaling).
+N = 1 (default workload: BASELINE.json configs[2]): the decode mat-vec (n = 1) over every projection of Llama-2-7B in
+Q4_K: 225 matrices, 3.716 GB of quant blocks, far larger than L2, so every step streams its weights from HBM (no L2
+flush needed).  A "step" is one token: ONE b200_mul_mat_batch call (one quantize + one persistent launch).
+  metric  quant_matvec_GBps = algorithmic bytes of the step / step time
+  value   device-resident: weights, activations and outputs in HBM, the step replayed from a CUDA graph, K steps
+  e2e     the same step through the ggml plugin boundary, the calls an unmodified ggml program makes:
+          ggml_backend_tensor_set_async (pinned host activations, ggml_backend_b200_host_buffer_type) ->
+          ggml_backend_graph_compute_async on B200_0 -> ggml_backend_tensor_get_async (pinned host outputs) ->
+          ggml_backend_synchronize, every step inside the timed region (weights are the model: uploaded once)
+  extras  decode_chain (the same stack with the dependency structure of a real decoder pass, one launch),
+          decode_batches (n = 2/4/8), prefill (tensor-core path, with its own roofline against the measured tcgen05
+          peaks), support kernels, the CPU baseline (the unmodified reference's ggml-cpu).
+N > 1 (default workload: BASELINE configs[4]): 16 layers of the Llama-3-70B FFN (gate, up 28672 x 8192; down 8192 x 28672)
+in Q4_K with the ROWS SPLIT over the ranks (strong scaling: the job is the same at every N).  Every rank computes its
+row blocks and stores them straight into every rank's copy of the output arena from inside the persistent launch
+(b200_mul_mat_batch_peers: the all-gather fused into the kernel, NVLink peer stores + system-scope completion flags);
+the per-group NCCL all-gather is kept as the baseline leg.  After the timed regions every rank re-computes a sample of
+OTHER ranks' rows from regenerated weights and compares bit for bit.  `--stack llama2-7b` keeps round 1's weak-scaling
+run (rows x N).
 
---impl reference times the reference's own CPU implementation (ggml-cpu from oracle/_ref, all host
-threads) on a bounded sample of the same workload.
+--impl reference times the reference's own CPU implementation (ggml-cpu from oracle/_ref, all host threads) on a
+bounded sample of the same workload.
 """
 from __future__ import annotations
 
@@ -140,71 +147,173 @@ def scale_blocks_device(torch, wtype, weights, factor):
         v[:, off:off + 2] = f.to(torch.float16).view(torch.uint8).view(-1, 2)
 
 
+def mul_mat_groups(mats):
+    """MUL_MAT groups of a decoder pass = runs of matrices that read the same activations (q/k/v, gate/up) or stand alone
+    (wo, down, output): the granularity at which a row-split model has to gather (one gather per group)."""
+    groups, i = [], 0
+    while i < len(mats):
+        nm = mats[i].name.split(".")[-1]
+        run = {"wq": 3, "gate": 2}.get(nm, 1)
+        groups.append(list(range(i, min(i + run, len(mats)))))
+        i += run
+    return groups
+
+
+def chain_plan(mats):
+    """(matrix index, source vector, destination vector) with the dependency structure of a decoder pass: the first group
+    of a layer reads the layer input, every later group reads the LAST output of the group before it (wo the attention
+    stand-in = the last of q/k/v, gate/up read wo, down reads up), the next layer reads down, the output matrix the last down."""
+    plan, cur = [], "h0"
+    for g in mul_mat_groups(mats):
+        for i in g:
+            plan.append((i, cur, f"y{i}"))
+        cur = f"y{g[-1]}"
+    return plan
+
+
 class DecodeStack:
-    """All matrices of the workload resident on one device + host/device activation and output arenas.
+    """All matrices of the workload resident on one device, activations and the output arena.
 
-    world > 1 (row split): rank r owns rows [b_r, b_{r+1}) of every matrix (row_split.split_bounds).  The
-    output arena is RANK-MAJOR: y[r] holds rank r's row blocks of all matrices back to back, so that after
-    the step's single persistent launch ONE all-gather of the arena leaves every rank with every output
-    (matrix i, rank r's rows at y[r, off_i : off_i + rows_r(i)])."""
+    Output arena ("full-vector layout"): matrix i owns m_i floats at off[i]; with the rows split over `world` ranks
+    (row_split.split_bounds) rank r's row block sits at off[i] + bounds[i][r] -- on EVERY rank once gathered.  world > 1:
+    the arena is a symmetric region (one copy per rank, peer-mapped) for the fused gather of b200_mul_mat_batch_peers;
+    the NCCL baseline leg uses a second arena in group-rank-major layout (one all_gather_into_tensor per MUL_MAT group)."""
 
-    def __init__(self, kern, mats, n, rank=0, world=1):
+    def __init__(self, kern, mats, rank=0, world=1, dist=None):
         import torch
         import b200
         import row_split
-        assert n == 1
-        self.torch, self.kern, self.mats, self.n, self.rank, self.world = torch, kern, mats, n, rank, world
+        self.torch, self.kern, self.mats, self.rank, self.world, self.dist = torch, kern, mats, rank, world, dist
         dev = kern.device
         self.bounds = [row_split.split_bounds(mt.m, world) for mt in mats]
         self.rows = [(b[rank], b[rank + 1]) for b in self.bounds]                   # my row block per matrix
         for b in self.bounds:
             assert len({b[r + 1] - b[r] for r in range(world)}) == 1, "bench shapes split evenly"
-        self.weights = [random_blocks_device(torch, dev, mt.type, hi - lo, mt.k, 0xB200 + 7919 * i + rank)
+        self.weights = [random_blocks_device(torch, dev, mt.type, hi - lo, mt.k, self.weight_seed(i, rank))
                         for i, (mt, (lo, hi)) in enumerate(zip(mats, self.rows))]
-        x_off, y_off, xo, yo = [], [], 0, 0
-        for mt, (lo, hi) in zip(mats, self.rows):
-            x_off.append(xo); xo += n * mt.k
-            y_off.append(yo); yo += n * (hi - lo)                                   # my block; same size on every rank
-        self.x_off, self.y_off, self.local_out = x_off, y_off, yo
+        self.groups = mul_mat_groups(mats)
+        # ---- activations: one private vector per matrix (the independent list), identical on every rank
+        x_off, xo = [], 0
+        for mt in mats:
+            x_off.append(xo); xo += mt.k
+        self.x_off = x_off
         g = torch.Generator(device="cpu"); g.manual_seed(1234)
         self.x_host = (torch.rand(xo, generator=g) * 2 - 1).pin_memory()
-        self.y_host = torch.empty(world * yo, dtype=torch.float32).pin_memory()
         self.x_dev = self.x_host.to(dev)
-        self.y_dev = torch.zeros((world, yo), dtype=torch.float32, device=dev)
-        Nodes = b200.MulMatNode * len(mats)
-        self.nodes = Nodes(*[
-            b200.mul_mat_node(mt.type, w.data_ptr(), hi - lo, mt.k, self.x_dev.data_ptr() + 4 * x_off[i], n,
-                              self.y_dev[rank].data_ptr() + 4 * y_off[i], const_weights=True)
-            for i, (mt, w, (lo, hi)) in enumerate(zip(mats, self.weights, self.rows))])
+        # ---- output arena, full-vector layout (+ h0 for the chain at the front)
+        self.h0_len = mats[0].k
+        off, yo = [], self.h0_len
+        for mt in mats:
+            off.append(yo); yo += (mt.m + 31) // 32 * 32
+        self.off, self.arena_len = off, yo
+        self.region = None
+        if world > 1:
+            ctrl = int(kern.lib.b200_peer_ctrl_bytes())
+            try:
+                self.region = row_split.SymmetricRegion(dist, 4 * yo, dev, ctrl)
+                self.y_dev = self.region.data[:4 * yo].view(torch.float32)
+                self.pg = self.region.peer_group()
+            except Exception as e:              # noqa: BLE001 - no peer mapping on this box: only the NCCL leg runs
+                sys.stderr.write(f"[bench r{rank}] symmetric memory unavailable ({str(e)[:200]}): fused gather leg skipped\n")
+                self.region = None
+        if self.region is None:
+            self.y_dev = torch.zeros(yo, dtype=torch.float32, device=dev)
+        gh = torch.Generator(device="cpu"); gh.manual_seed(4321)
+        self.y_dev[:self.h0_len].copy_(torch.rand(self.h0_len, generator=gh) * 2 - 1)
+        self.y_host = torch.empty(yo, dtype=torch.float32).pin_memory()
+
+        def node(i, xptr, dptr):
+            mt, (lo, hi) = mats[i], self.rows[i]
+            return b200.mul_mat_node(mt.type, self.weights[i].data_ptr(), hi - lo, mt.k, xptr, 1, dptr, const_weights=True)
+
+        ybase = self.y_dev.data_ptr()
+        self.nodes = (b200.MulMatNode * len(mats))(*[
+            node(i, self.x_dev.data_ptr() + 4 * x_off[i], ybase + 4 * (off[i] + self.rows[i][0])) for i in range(len(mats))])
         self.ws = torch.empty(int(kern.lib.b200_mul_mat_batch_workspace_size(self.nodes, len(mats))) + 256,
                               dtype=torch.uint8, device=dev)
+        # ---- the same matrices with the dependency structure of a decoder pass (inputs = arena vectors)
+        self.plan = chain_plan(mats)
+        src_off = {"h0": 0, **{f"y{i}": off[i] for i in range(len(mats))}}
+        self.chain_nodes = (b200.MulMatNode * len(mats))(*[
+            node(i, ybase + 4 * src_off[src], ybase + 4 * (off[i] + self.rows[i][0])) for i, src, _ in self.plan])
+        self.chain_calibrated = False
+        # ---- NCCL baseline leg (world > 1): group-rank-major arena, one all-gather per MUL_MAT group
+        if world > 1:
+            self.nccl_segs, self.nccl_nodes, pos = [], [], 0
+            gsz = [sum(self.rows[i][1] - self.rows[i][0] for i in g_) for g_ in self.groups]
+            self.y_nccl = torch.zeros(world * sum(gsz), dtype=torch.float32, device=dev)
+            for g_, sz in zip(self.groups, gsz):
+                seg = self.y_nccl[pos: pos + world * sz]
+                mine, p2, sub = seg[rank * sz:(rank + 1) * sz], 0, []
+                for i in g_:
+                    sub.append(node(i, self.x_dev.data_ptr() + 4 * x_off[i], mine.data_ptr() + 4 * p2))
+                    p2 += self.rows[i][1] - self.rows[i][0]
+                self.nccl_segs.append((seg, mine))
+                self.nccl_nodes.append((b200.MulMatNode * len(sub))(*sub))
+                pos += world * sz
         self.local_weight_bytes = sum(int(w.numel()) for w in self.weights)
         self.local_alg_bytes = sum((hi - lo) * (mt.k // workloads.BLOCK_ELEMS[mt.type]) * workloads.BLOCK_BYTES[mt.type]
-                                   + n * mt.k * 4 + n * (hi - lo) * 4 for mt, (lo, hi) in zip(mats, self.rows))
-        self.x_bytes, self.y_bytes = 4 * xo, 4 * world * yo
+                                   + mt.k * 4 + (hi - lo) * 4 for mt, (lo, hi) in zip(mats, self.rows))
+        self.x_bytes, self.y_bytes = 4 * xo, 4 * (yo - self.h0_len)
 
+    @staticmethod
+    def weight_seed(i, rank):
+        return 0xB200 + 7919 * i + rank
+
+    # ------------------------------------------------------------------ one step
     def compute(self):
-        """Every MUL_MAT of the step in one C-ABI call (one quantize + one persistent launch); with the rows
-        split over ranks, one all-gather of the rank-major output arena follows."""
-        self.kern.mul_mat_batch(self.nodes, ws=self.ws)
-        if self.world > 1:
-            import torch.distributed as dist
-            dist.all_gather_into_tensor(self.y_dev.view(-1), self.y_dev[self.rank])
+        """Every MUL_MAT of the step in one C-ABI call: one quantize + one persistent launch; with the rows split over
+        ranks the launch also stores every finished row into every rank's arena (the gather, fused)."""
+        if self.world > 1 and self.region is not None:
+            self.kern.mul_mat_batch_peers(self.nodes, self.pg, ws=self.ws)
+        elif self.world > 1:
+            self.compute_nccl()
+        else:
+            self.kern.mul_mat_batch(self.nodes, ws=self.ws)
 
+    def compute_chain(self):
+        if self.world > 1:
+            self.kern.mul_mat_batch_peers(self.chain_nodes, self.pg, ws=self.ws)
+        else:
+            self.kern.mul_mat_batch(self.chain_nodes, ws=self.ws)
+
+    def compute_nccl(self):
+        """baseline: one persistent launch + one NCCL all-gather per MUL_MAT group (what a row-split model does without the fusion)"""
+        for sub, (seg, mine) in zip(self.nccl_nodes, self.nccl_segs):
+            self.kern.mul_mat_batch(sub, ws=self.ws)
+            self.dist.all_gather_into_tensor(seg, mine)
+
+    def calibrate_chain(self):
+        """Random blocks amplify (|y| ~ 30 |x| per node): without the normalisations of a real model the chain overflows
+        after a few layers.  Stand-in for them: every matrix's fp16 scale fields are scaled, once, to unit output RMS
+        (row-split: every rank applies the same factor, computed from the gathered vector)."""
+        if self.chain_calibrated:
+            return
+        import b200
+        torch, kern = self.torch, self.kern
+        for idx, (i, _, _) in enumerate(self.plan):
+            mt = self.mats[i]
+            one = (b200.MulMatNode * 1)(self.chain_nodes[idx])
+            for it in range(2):                       # measure the gain, rescale, recompute (the next node reads the calibrated output)
+                if self.world > 1:
+                    kern.mul_mat_batch_peers(one, self.pg, ws=self.ws)
+                    torch.cuda.synchronize(); self.dist.barrier()
+                else:
+                    kern.mul_mat_batch(one, ws=self.ws)
+                if it == 0:
+                    rms = float(self.y_dev[self.off[i]: self.off[i] + mt.m].double().pow(2).mean().sqrt())
+                    scale_blocks_device(torch, mt.type, self.weights[i], 1.0 / max(rms, 1e-30))
+        self.chain_calibrated = True
+
+    # ------------------------------------------------------------------ C-ABI end to end (extra leg)
     def _e2e_setup(self, chunks):
         """Split the node list into `chunks` consecutive sub-lists with their activation / output ranges, so
         that the host->device copy of sub-list c+1 and the device->host copy of sub-list c-1 overlap the
         persistent launch of sub-list c (three streams, events in between)."""
-        import ctypes
         import b200
         torch = self.torch
         n = len(self.mats)
-        edges = [round(i * n / chunks) for i in range(chunks + 1)]
-        # balance by weight bytes rather than by node count
         total = sum(int(w.numel()) for w in self.weights)
-        # cut points as fractions of the weight bytes: a short first and last sub-list (BENCH_E2E_EDGE of the bytes
-        # each) keep the two copies that nothing can overlap -- the first sub-list's activations in, the last
-        # sub-list's outputs out -- small
         edge = float(os.environ.get("BENCH_E2E_EDGE", "0.1"))
         if chunks >= 4 and 0.0 < edge < 0.25:
             cuts = [edge + (1.0 - 2.0 * edge) * j / (chunks - 2) for j in range(chunks - 1)]
@@ -219,27 +328,29 @@ class DecodeStack:
         edges = sorted(set(edges))
         self.e2e_chunks = []
         xo_end = self.x_off + [self.x_host.numel()]
-        yo_end = self.y_off + [self.local_out]
+        yo_end = self.off + [self.arena_len]
         for a, b in zip(edges[:-1], edges[1:]):
             sub = (b200.MulMatNode * (b - a))(*[self.nodes[i] for i in range(a, b)])
             self.e2e_chunks.append((sub, b - a, xo_end[a], xo_end[b], yo_end[a], yo_end[b]))
         self.s_h2d, self.s_d2h = torch.cuda.Stream(), torch.cuda.Stream()
 
     def step_e2e(self):
-        """pinned host activations -> device, every MUL_MAT, outputs -> pinned host.  Single GPU: pipelined over
-        sub-lists; with the rows split over ranks the gather needs the whole arena, so the step is serial."""
+        """pinned host activations -> device, every MUL_MAT, outputs -> pinned host, through the C ABI.  Single GPU:
+        pipelined over sub-lists (copies overlap the persistent launches).  Row split: the step is one fused launch; only
+        rank 0 moves host data (every rank holds the gathered outputs; one copy of them leaves the box)."""
         torch = self.torch
         if self.world > 1:
-            self.x_dev.copy_(self.x_host, non_blocking=True)
+            if self.rank == 0:
+                self.x_dev.copy_(self.x_host, non_blocking=True)
             self.compute()
-            self.y_host.copy_(self.y_dev.view(-1), non_blocking=True)
+            if self.rank == 0:
+                self.y_host[self.h0_len:].copy_(self.y_dev[self.h0_len:], non_blocking=True)
             return
         if not hasattr(self, "e2e_chunks"):
             self._e2e_setup(env_int("BENCH_E2E_CHUNKS", 4))
         cur = torch.cuda.current_stream()
         self.s_h2d.wait_stream(cur)                       # the previous step is done with x_dev
         self.s_d2h.wait_stream(cur)
-        y_flat = self.y_dev.view(-1)
         for sub, cnt, x0, x1, y0, y1 in self.e2e_chunks:
             with torch.cuda.stream(self.s_h2d):
                 self.x_dev[x0:x1].copy_(self.x_host[x0:x1], non_blocking=True)
@@ -249,8 +360,33 @@ class DecodeStack:
             ev_out = torch.cuda.Event(); ev_out.record(cur)
             with torch.cuda.stream(self.s_d2h):
                 self.s_d2h.wait_event(ev_out)
-                self.y_host[y0:y1].copy_(y_flat[y0:y1], non_blocking=True)
+                self.y_host[y0:y1].copy_(self.y_dev[y0:y1], non_blocking=True)
         cur.wait_stream(self.s_d2h)                       # the step ends when its last output is on the host
+
+    # ------------------------------------------------------------------ N-rank parity, carried by the bench line itself
+    def selfcheck(self, sample_mats=4, sample_rows=256):
+        """After a step every rank must hold every row.  Each rank regenerates the weights of ANOTHER rank's row block
+        (same seeds), recomputes its first rows through the same kernel (a row's bits do not depend on the sub-matrix it
+        is computed in) and compares with what the gather left in its own arena, bit for bit."""
+        import b200
+        torch, kern = self.torch, self.kern
+        other = (self.rank + 1) % self.world
+        checked, ok = 0, True
+        step = max(1, len(self.mats) // sample_mats)
+        for i in range(0, len(self.mats), step):
+            mt = self.mats[i]
+            lo, hi = self.bounds[i][other], self.bounds[i][other + 1]
+            nr = min(sample_rows, hi - lo)
+            w = random_blocks_device(torch, kern.device, mt.type, hi - lo, mt.k, self.weight_seed(i, other))
+            rb = workloads.BLOCK_BYTES[mt.type] * (mt.k // workloads.BLOCK_ELEMS[mt.type])
+            y = torch.zeros(nr, dtype=torch.float32, device=kern.device)
+            one = (b200.MulMatNode * 1)(b200.mul_mat_node(mt.type, w.data_ptr(), nr, mt.k, self.x_dev.data_ptr() + 4 * self.x_off[i], 1, y.data_ptr()))
+            kern.mul_mat_batch(one)
+            got = self.y_dev[self.off[i] + lo: self.off[i] + lo + nr]
+            ok = ok and bool(torch.equal(y.view(torch.int32), got.view(torch.int32))) and bool(torch.isfinite(y).all()) and bool(y.abs().max() > 0)
+            checked += nr
+            del w, rb
+        return checked, ok
 
 
 # ------------------------------------------------------------------------------------- timing
@@ -362,78 +498,192 @@ def measure_decode_batches(torch, kern, stack, peak):
     return out
 
 
-def measure_decode_chain(torch, kern, stack, peak, reps=50):
-    """The same resident stack with the dependency structure a decoder pass really has (what a ggml decode graph
-    gives the backend): per layer q/k/v read the layer input, wo reads q (stand-in for the attention output), gate/up
-    read wo, down reads up, the next layer reads down, the output matrix reads the last down -- 129 chain links for
-    Llama-2-7B.  ONE b200_mul_mat_batch call: the dependent nodes ride the same persistent launch (completion
-    counters + in-launch activation quantization).  Checked bit for bit against the same list cut at every link
-    (option no_chain: one launch group per link, the round-1 behaviour), which is also timed."""
+def measure_decode_chain(torch, kern, stack, peak, reps=50, dist=None):
+    """The same resident stack with the dependency structure a decoder pass really has (what a ggml decode graph gives
+    the backend): per layer q/k/v read the layer input, wo reads the last of them (stand-in for the attention output),
+    gate/up read wo, down reads up, the next layer reads down, the output matrix reads the last down -- 129 chain links
+    for Llama-2-7B.  ONE list call: the dependent nodes ride the same persistent launch (completion counters +
+    in-launch activation quantization; row split: the gathered vectors feed the next node inside the launch).
+    Checked bit for bit against the same list cut at every link (option no_chain: one launch group per link, round 1's
+    behaviour), which is also timed (single GPU)."""
     import b200
-    mats, dev = stack.mats, kern.device
-    assert (len(mats) - 1) % 7 == 0
-    layers = (len(mats) - 1) // 7
-    bufs = {"h0": torch.rand((1, mats[0].k), device=dev) * 2 - 1}
-    plan = []
-    cur = "h0"
-    for l in range(layers):
-        q, kk, v, o, g, u, d = (7 * l + j for j in range(7))
-        plan += [(q, cur, f"q{l}"), (kk, cur, f"k{l}"), (v, cur, f"v{l}"), (o, f"q{l}", f"o{l}"),
-                 (g, f"o{l}", f"g{l}"), (u, f"o{l}", f"u{l}"), (d, f"u{l}", f"d{l}")]
-        cur = f"d{l}"
-    plan.append((len(mats) - 1, cur, "logits"))
-    for i, src, dst in plan:
-        lo, hi = stack.rows[i]
-        bufs[dst] = torch.zeros((1, hi - lo), dtype=torch.float32, device=dev)
-    # random blocks amplify (|y| ~ 30 |x| per node): without the normalisations of a real model the chain overflows
-    # after a few layers.  Stand-in for them: every node's fp16 scale fields are calibrated, once, to unit output RMS.
-    if not getattr(stack, "chain_calibrated", False):
-        for i, src, dst in plan:
-            mt = mats[i]
-            y = kern.mul_mat(mt.type, stack.weights[i], stack.rows[i][1] - stack.rows[i][0], mt.k, bufs[src])
-            rms = float(y.double().pow(2).mean().sqrt())
-            scale_blocks_device(torch, mt.type, stack.weights[i], 1.0 / max(rms, 1e-30))
-            bufs[dst].copy_(kern.mul_mat(mt.type, stack.weights[i], stack.rows[i][1] - stack.rows[i][0], mt.k, bufs[src]).view(1, -1))
-        stack.chain_calibrated = True
-    nodes = (b200.MulMatNode * len(plan))(*[
-        b200.mul_mat_node(mats[i].type, stack.weights[i].data_ptr(), stack.rows[i][1] - stack.rows[i][0], mats[i].k,
-                          bufs[src].data_ptr(), 1, bufs[dst].data_ptr(), const_weights=True) for i, src, dst in plan])
-    ws = torch.empty(int(kern.lib.b200_mul_mat_batch_workspace_size(nodes, len(plan))) + 256, dtype=torch.uint8, device=dev)
-    groups = len({g for g, _, _ in b200.batch_plan(kern.lib, nodes)})
-    links = sum(1 for _, dep, _ in b200.batch_plan(kern.lib, nodes) if dep >= 0)
-    fn = lambda: kern.mul_mat_batch(nodes, ws=ws)       # noqa: E731
-    out = {"nodes": len(plan), "launch_groups": groups, "in_launch_waits": links}
+    stack.calibrate_chain()
+    plan_rows = b200.batch_plan(kern.lib, stack.chain_nodes)
+    out = {"nodes": len(stack.plan), "launch_groups": len({g for g, _, _ in plan_rows}),
+           "in_launch_waits": sum(1 for _, dep, _ in plan_rows if dep >= 0),
+           "structure": "per layer: first group reads the layer input, each later group reads the last output of the group before (q/k/v -> wo -> gate/up -> down -> next layer), output matrix last"}
+    arena = stack.y_dev[stack.h0_len:]
     results = {}
-    for mode in ("chained", "cut"):
+    modes = ("chained", "cut") if stack.world == 1 else ("chained",)
+    for mode in modes:
         prev = kern.set_option("no_chain", 1 if mode == "cut" else 0)
         try:
-            for b in bufs.values():
-                if b is not bufs["h0"]:
-                    b.zero_()
-            fn()
+            arena.zero_()
+            if dist is not None:
+                torch.cuda.synchronize(); dist.barrier()
+            stack.compute_chain()
             torch.cuda.synchronize()
-            results[mode] = torch.cat([bufs[dst].view(-1) for _, _, dst in plan]).clone()
+            if dist is not None:
+                dist.barrier()
+            results[mode] = arena.clone()
             c0 = kern.launch_count()
-            fn()
+            stack.compute_chain()
             launches = kern.launch_count() - c0
+            torch.cuda.synchronize()
+            if dist is not None:
+                dist.barrier()
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
-                fn()
+                stack.compute_chain()
             g.replay()
-            sec = timed_loop(torch, g.replay, reps) / reps
-            out[mode] = {"ms_per_pass": round(sec * 1e3, 4), "launches": launches,
-                         "GBps": round(stack.local_alg_bytes / sec / 1e9, 1), "frac": round(stack.local_alg_bytes / sec / 1e9 / peak, 3),
-                         "passes_per_s": round(1.0 / sec, 1)}
+            sec = timed_loop(torch, g.replay, reps, dist) / reps
+            alg = stack.local_alg_bytes * stack.world
+            out[mode] = {"ms_per_pass": round(sec * 1e3, 4), "launches": launches, "GBps": round(alg / sec / 1e9, 1),
+                         "frac_per_gpu": round(alg / stack.world / sec / 1e9 / peak, 3), "passes_per_s": round(1.0 / sec, 1)}
+            torch.cuda.synchronize()
             del g
         finally:
             kern.set_option("no_chain", prev)
-    out["bit_identical_to_cut_list"] = bool(torch.equal(results["chained"].view(torch.int32), results["cut"].view(torch.int32)))
+    if "cut" in results:
+        out["bit_identical_to_cut_list"] = bool(torch.equal(results["chained"].view(torch.int32), results["cut"].view(torch.int32)))
     out["finite"] = bool(torch.isfinite(results["chained"]).all())
     return out
 
 
+# ------------------------------------------------------------------------------------- end to end through the ggml plugin
+class PluginStep:
+    """The step as an unmodified ggml program runs it on our backend: libggml-b200.so loaded into the reference's own
+    libggml (oracle/_ref/bin) with ggml_backend_load, a ggml graph of the workload's MUL_MAT nodes allocated on device
+    B200_0, and per step
+        ggml_backend_tensor_set_async(X  <- pinned host)   one tensor holding every activation vector (the nodes read views)
+        ggml_backend_graph_compute_async                   the plugin hands the MUL_MAT run to b200_mul_mat_batch, CUDA-graph replay
+        ggml_backend_tensor_get_async(Y  -> pinned host)   one tensor holding every output (placed with ggml_backend_tensor_alloc)
+        ggml_backend_synchronize
+    Pinned host memory comes from ggml_backend_b200_host_buffer_type.  chain=True builds the decoder-pass dependency
+    structure instead (node outputs feed the next nodes directly; host traffic = first activation in, last output out)."""
+
+    def __init__(self, stack, chain=False):
+        import ctypes as C
+        import numpy as np
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import ggml_host
+        self.C, self.np = C, np
+        ref_bin = os.path.join(ROOT, "oracle", "_ref", "bin")
+        plugin = os.path.join(PKG, "libggml-b200.so")
+        if not (os.path.exists(os.path.join(ref_bin, "libggml-base.so")) and os.path.exists(plugin)):
+            raise RuntimeError("oracle/_ref or libggml-b200.so not built")
+        host = self.host = ggml_host.GgmlHost(ref_bin)
+        b = host.base
+        vp, sz, i64 = C.c_void_p, C.c_size_t, C.c_int64
+        b.ggml_view_2d.restype = vp;                   b.ggml_view_2d.argtypes = [vp, vp, i64, i64, sz, sz]
+        b.ggml_get_data.restype = vp;                  b.ggml_get_data.argtypes = [vp]
+        b.ggml_backend_tensor_alloc.restype = C.c_int; b.ggml_backend_tensor_alloc.argtypes = [vp, vp, vp]
+        b.ggml_backend_tensor_set_async.restype = None; b.ggml_backend_tensor_set_async.argtypes = [vp, vp, vp, sz, sz]
+        b.ggml_backend_tensor_get_async.restype = None; b.ggml_backend_tensor_get_async.argtypes = [vp, vp, vp, sz, sz]
+        b.ggml_backend_buft_alloc_buffer.restype = vp; b.ggml_backend_buft_alloc_buffer.argtypes = [vp, sz]
+        b.ggml_backend_buffer_get_base.restype = vp;   b.ggml_backend_buffer_get_base.argtypes = [vp]
+        b.ggml_backend_buffer_set_usage.restype = None; b.ggml_backend_buffer_set_usage.argtypes = [vp, C.c_int]
+        host.load_plugin(plugin)
+        dev = host.device_by_name("B200_0")
+        if not dev:
+            raise RuntimeError("device B200_0 not registered")
+        self.backend = host.init_device(dev)
+        plug = C.CDLL(plugin)
+        plug.ggml_backend_b200_host_buffer_type.restype = vp
+        mats = stack.mats
+        n = len(mats)
+        T = ggml_host.GGML_TYPE
+        # weights: their own context and buffer, marked as weights (what llama.cpp does), uploaded once
+        self.ctx_w = host.new_context(n_tensors=n + 8)
+        self.w = [b.ggml_new_tensor_2d(self.ctx_w, T[mt.type], mt.k, hi - lo) for mt, (lo, hi) in zip(mats, stack.rows)]
+        self.buf_w = b.ggml_backend_alloc_ctx_tensors(self.ctx_w, self.backend)
+        if not self.buf_w:
+            raise MemoryError("weights")
+        b.ggml_backend_buffer_set_usage(self.buf_w, 1)           # GGML_BACKEND_BUFFER_USAGE_WEIGHTS
+        for t, wt in zip(self.w, stack.weights):
+            host.tensor_set(t, wt.cpu().numpy())
+        # activations X (every vector, the nodes read views) and outputs Y (every result, placed by hand) in one buffer
+        plan = stack.plan if chain else [(i, None, None) for i in range(n)]
+        xlen = stack.h0_len if chain else stack.x_host.numel()
+        ylen = sum((mt.m + 31) // 32 * 32 for mt in mats)
+        self.ctx_io = host.new_context(n_tensors=2 * n + 16, graph_nodes=2 * n + 64)
+        self.X = b.ggml_new_tensor_1d(self.ctx_io, T["f32"], xlen)
+        self.Y = b.ggml_new_tensor_1d(self.ctx_io, T["f32"], ylen)
+        xv = []
+        if not chain:
+            for i, mt in enumerate(mats):
+                xv.append(b.ggml_view_2d(self.ctx_io, self.X, mt.k, 1, 4 * mt.k, 4 * stack.x_off[i]))
+        else:
+            xv.append(b.ggml_view_2d(self.ctx_io, self.X, stack.h0_len, 1, 4 * stack.h0_len, 0))
+        self.buf_io = b.ggml_backend_alloc_ctx_tensors(self.ctx_io, self.backend)
+        if not self.buf_io:
+            raise MemoryError("activations")
+        self.ctx_g = host.new_context(n_tensors=n + 16, graph_nodes=2 * n + 64)
+        ybase = b.ggml_get_data(self.Y)
+        ys, yoff, pos = {}, [], 0
+        for idx, (i, src, _) in enumerate(plan):
+            mt = mats[i]
+            x = xv[i] if not chain else (xv[0] if src == "h0" else ys[src])
+            y = b.ggml_mul_mat(self.ctx_g, self.w[i], x)
+            if b.ggml_backend_tensor_alloc(self.buf_io, y, ybase + 4 * pos) != 0:
+                raise RuntimeError("ggml_backend_tensor_alloc")
+            ys[f"y{i}"] = y
+            yoff.append(pos)
+            pos += (mt.m + 31) // 32 * 32
+        self.graph = b.ggml_new_graph_custom(self.ctx_g, max(2048, 2 * n + 64), False)
+        last = None
+        for idx, (i, _, _) in enumerate(plan):
+            b.ggml_build_forward_expand(self.graph, ys[f"y{i}"])
+            last = i
+        self.chain, self.yoff, self.ys, self.last = chain, yoff, ys, last
+        # pinned host staging from the plugin's host buffer type
+        buft = plug.ggml_backend_b200_host_buffer_type()
+        self.h_bytes_in = 4 * xlen
+        self.h_bytes_out = 4 * ylen if not chain else 4 * mats[last].m
+        self.hbuf = b.ggml_backend_buft_alloc_buffer(buft, self.h_bytes_in + 4 * ylen + 256)
+        if not self.hbuf:
+            raise MemoryError("pinned host buffer")
+        hbase = b.ggml_backend_buffer_get_base(self.hbuf)
+        self.h_in, self.h_out = hbase, hbase + (self.h_bytes_in + 127) // 128 * 128
+        src_host = stack.y_dev[:stack.h0_len].cpu().numpy() if chain else stack.x_host.numpy()
+        C.memmove(self.h_in, src_host.ctypes.data, self.h_bytes_in)
+
+    def step(self):
+        b = self.host.base
+        b.ggml_backend_tensor_set_async(self.backend, self.X, self.h_in, 0, self.h_bytes_in)
+        st = b.ggml_backend_graph_compute_async(self.backend, self.graph)
+        if st != 0:
+            raise RuntimeError(f"graph_compute status {st}")
+        if self.chain:
+            b.ggml_backend_tensor_get_async(self.backend, self.ys[f"y{self.last}"], self.h_out, 0, self.h_bytes_out)
+        else:
+            b.ggml_backend_tensor_get_async(self.backend, self.Y, self.h_out, 0, self.h_bytes_out)
+        b.ggml_backend_synchronize(self.backend)
+
+    def outputs(self):
+        """host copy of the last step's outputs as a float32 array (all outputs, or the chain's last vector)"""
+        n = self.h_bytes_out // 4
+        return self.np.ctypeslib.as_array((self.C.c_float * n).from_address(self.h_out)).copy()
+
+    def timed(self, steps, warmup=3):
+        for _ in range(max(3, warmup)):                  # the plugin captures a repeated graph on its 2nd sight, replays from the 3rd
+            self.step()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            self.step()
+        return time.perf_counter() - t0
+
+    def close(self):
+        b = self.host.base
+        for buf in (self.buf_io, self.buf_w, self.hbuf):
+            if buf:
+                b.ggml_backend_buffer_free(buf)
+        b.ggml_free(self.ctx_g); b.ggml_free(self.ctx_io); b.ggml_free(self.ctx_w)
+        b.ggml_backend_free(self.backend)
+
+
 # ------------------------------------------------------------------------------------- the CPU reference
-def cpu_reference(budget_s=12.0, sample_layers=4, steps=None, warmup=1):
+def cpu_reference(budget_s=12.0, sample_layers=4, steps=None, warmup=1, stack_name="llama2-7b"):
     """The reference's own CPU implementation of the path (ggml-cpu, unmodified, compiled from
     /root/reference into oracle/_ref by oracle/Makefile) on a bounded sample of the workload:
     `sample_layers` Llama-2-7B layers (7 matrices each, Q4_K, n = 1) as one ggml graph on the CPU
@@ -444,7 +694,10 @@ def cpu_reference(budget_s=12.0, sample_layers=4, steps=None, warmup=1):
     import oracle_lib
     ref_bin = os.path.join(ROOT, "oracle", "_ref", "bin")
     cores = os.cpu_count() or 1
-    mats = workloads.llama2_7b_stack("q4_K", n_layers=sample_layers)[:-1]
+    if stack_name == "llama3-70b-ffn":
+        mats = workloads.llama3_70b_ffn(n_layers=1)                 # 3 matrices, 397 MB >> host L3
+    else:
+        mats = workloads.llama2_7b_stack("q4_K", n_layers=sample_layers)[:-1]
     alg = sum(mt.algorithmic_bytes(1) for mt in mats)
     if os.path.exists(os.path.join(ref_bin, "libggml-base.so")):
         host = ggml_host.GgmlHost(ref_bin)
@@ -486,8 +739,9 @@ def cpu_reference(budget_s=12.0, sample_layers=4, steps=None, warmup=1):
         kind = "port"
     gbps = alg * reps / el / 1e9
     return gbps, {"value": round(gbps, 2), "unit": UNIT, "cores": cores, "kind": kind,
-                  "sample": f"{len(mats)} matrices ({len(mats) // 7} Llama-2-7B layers, Q4_K, n=1, "
-                            f"{alg / 1e6:.0f} MB) x {reps} passes in {el:.1f} s",
+                  "sample": (f"{len(mats)} matrices (1 Llama-3-70B FFN layer, Q4_K, n=1, " if stack_name == "llama3-70b-ffn" else
+                             f"{len(mats)} matrices ({len(mats) // 7} Llama-2-7B layers, Q4_K, n=1, ")
+                            + f"{alg / 1e6:.0f} MB) x {reps} passes in {el:.1f} s",
                   "ms_per_pass": round(el / reps * 1e3, 3)}
 
 
@@ -513,15 +767,83 @@ def ncu_traffic():
 def run_reference(args, rank):
     if rank != 0:
         return
-    gbps, info = cpu_reference(steps=args.steps, warmup=args.warmup)
+    stack_name = args.stack or ("llama2-7b" if args.gpus <= 1 else "llama3-70b-ffn")
+    gbps, info = cpu_reference(steps=args.steps, warmup=args.warmup, stack_name=stack_name)
+    wl = WORKLOAD if stack_name == "llama2-7b" else "llama3-70b FFN (gate, up 28672x8192; down 8192x28672), Q4_K, decode mat-vec n=1 (BASELINE configs[4])"
     line = {"impl": "reference", "metric": METRIC, "value": info["value"], "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": info["ms_per_pass"], "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "int8 dot (q8_K activations), f32 accumulate",
-            "data": "synthetic", "config": {"workload": WORKLOAD, "n": 1, "sample": info["sample"]},
+            "scaling": "strong", "vs_baseline": None, "dtype": "int8 dot (q8_K activations), f32 accumulate",
+            "data": "synthetic", "config": {"workload": wl, "n": 1, "sample": info["sample"]},
             "cpu_baseline": {k: info[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": info["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
+
+
+def tensor_peaks(kern):
+    """MEASURED_PEAKS.json (driver: cuBLAS bf16 8192^3, burst and sustained) + this run's tcgen05 micro-kernel
+    (b200_tensor_peak: operands resident in shared memory, nothing but the MMA issue loop) for bf16 and int8."""
+    out = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            mp = json.load(f)
+        out["bf16_cublas_burst_TFLOPs"] = mp.get("bf16_tflops"); out["bf16_cublas_sustained_TFLOPs"] = mp.get("bf16_tflops_sustained")
+    except (OSError, ValueError):
+        out["bf16_cublas_burst_TFLOPs"], out["bf16_cublas_sustained_TFLOPs"] = 1590.0, 1400.0
+        out["note"] = "MEASURED_PEAKS.json absent: fallback figures of B200_PROFILING.md"
+    try:
+        out["tcgen05_bf16_TFLOPs"] = round(kern.tensor_peak("bf16", iters=8192, reps=5) / 1e12, 1)
+        out["tcgen05_int8_TOPs"] = round(kern.tensor_peak("i8", iters=8192, reps=5) / 1e12, 1)
+    except Exception as e:                       # noqa: BLE001
+        out["error"] = str(e)[:200]
+    return out
+
+
+def measure_prefill_all(torch, kern, peaks):
+    """The batched (tensor-core) term of the metric: BASELINE configs[1] (Q8_0 / Q4_0, n = 512, Llama-2-7B FFN shapes) and
+    configs[3] prefill shapes at n = 2048, TFLOP/s = 2 m n k / time, with the roofline of the best figure."""
+    out = {"n512": measure_prefill(torch, kern, n=512)}
+    n2048 = {}
+    for mt in (workloads.Mat("q4_K.14336x4096", "q4_K", 14336, 4096), workloads.Mat("q6_K.4096x14336", "q6_K", 4096, 14336),
+               workloads.Mat("q8_0.11008x4096", "q8_0", 11008, 4096)):
+        w = random_blocks_device(torch, kern.device, mt.type, mt.m, mt.k, 78)
+        x = torch.rand((2048, mt.k), device=kern.device) * 2 - 1
+        y = torch.empty((2048, mt.m), dtype=torch.float32, device=kern.device)
+        fn = lambda: kern.mul_mat(mt.type, w, mt.m, mt.k, x, out=y)      # noqa: E731
+        for _ in range(3):
+            fn()
+        sec = timed_loop(torch, fn, 5) / 5
+        n2048[mt.name] = round(mt.flops(2048) / sec / 1e12, 2)
+        del w, x, y
+    out["n2048"] = n2048
+    best = max(list(out["n512"].values()) + list(n2048.values()))
+    sustained = peaks.get("bf16_cublas_sustained_TFLOPs") or 1400.0
+    out["roofline"] = {"bound": "tensor", "kernel": "k_mmq_tc (tcgen05 kind::f16, bf16 operands, f32 TMEM accumulator)", "achieved": best,
+                       "peak": sustained, "unit": "TFLOP/s", "frac": round(best / sustained, 4),
+                       "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (cuBLAS, driver-measured)",
+                       "frac_of_tcgen05_bf16_micro_kernel": round(best / peaks["tcgen05_bf16_TFLOPs"], 4) if peaks.get("tcgen05_bf16_TFLOPs") else None,
+                       "frac_of_tcgen05_int8_micro_kernel": round(best / peaks["tcgen05_int8_TOPs"], 4) if peaks.get("tcgen05_int8_TOPs") else None,
+                       "traffic": None}
+    return out
+
+
+def capture(torch, fn):
+    """fn captured into a CUDA graph (None when capture fails: the step then runs eagerly)"""
+    try:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            fn()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            fn()
+        return g
+    except Exception as e:                       # noqa: BLE001 - capture is an optimisation, not a requirement
+        sys.stderr.write(f"[bench] CUDA graph capture failed ({e}); timing eager launches\n")
+        torch.cuda.synchronize()
+        return None
 
 
 def main():
@@ -530,11 +852,11 @@ def main():
     ap.add_argument("--steps", type=int, default=300)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--wtype", default="q4_K", help="weight format of the stack (default: the headline Q4_K)")
-    ap.add_argument("--stack", default="llama2-7b", choices=["llama2-7b", "llama3-70b-ffn"],
-                    help="llama2-7b: the headline stack, rows x N at N GPUs (weak scaling); llama3-70b-ffn: BASELINE "
-                         "configs[4], 16 layers of the 8192x28672 Q4_K FFN row-split over the N GPUs (strong scaling)")
-    ap.add_argument("--no-extras", action="store_true", help="skip the prefill figure and the CPU baseline")
+    ap.add_argument("--wtype", default="q4_K", help="weight format of the llama2-7b stack (default: the headline Q4_K)")
+    ap.add_argument("--stack", default=None, choices=["llama2-7b", "llama3-70b-ffn"],
+                    help="default: llama2-7b at 1 GPU (BASELINE configs[2]); llama3-70b-ffn at N > 1 (configs[4]: 16 layers of the "
+                         "8192x28672 Q4_K FFN, rows split over the N GPUs, strong scaling).  llama2-7b at N > 1: rows x N (weak scaling)")
+    ap.add_argument("--no-extras", action="store_true", help="skip the secondary figures and the CPU baseline")
     args = ap.parse_args()
     rank = env_int("RANK", 0)
     world = env_int("WORLD_SIZE", 1)
@@ -543,6 +865,8 @@ def main():
         run_reference(args, rank)
         return
     args.warmup = max(args.warmup, 3)
+    if args.stack is None:
+        args.stack = "llama2-7b" if world == 1 else "llama3-70b-ffn"
 
     import torch
     import b200
@@ -555,41 +879,30 @@ def main():
     kern = b200.Kernels(device=local_rank)
     strong = args.stack == "llama3-70b-ffn"
     mats = workloads.llama3_70b_ffn(n_layers=16) if strong else workloads.llama2_7b_stack(args.wtype, row_mult=world)
-    stack = DecodeStack(kern, mats, 1, rank, world)
+    stack = DecodeStack(kern, mats, rank, world, dist)
     lib = kern.lib
+    fused = world > 1 and stack.region is not None
     dbg("stack built")
 
     # ---- warm-up (eager), then capture the step into a CUDA graph
     for _ in range(args.warmup):
         stack.compute()
     torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
     dbg("eager warm-up done")
     c0 = int(lib.b200_launch_count())
-    graph, step = None, stack.compute
-    try:
-        side = torch.cuda.Stream()
-        side.wait_stream(torch.cuda.current_stream())
-        with torch.cuda.stream(side):
-            stack.compute()
-        torch.cuda.current_stream().wait_stream(side)
-        torch.cuda.synchronize()
-        c0 = int(lib.b200_launch_count())
-        graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(graph):
-            stack.compute()
-        step = graph.replay
-    except Exception as e:                       # noqa: BLE001 - capture is an optimisation, not a requirement
-        sys.stderr.write(f"[bench] CUDA graph capture failed ({e}); timing eager launches\n")
-        graph = None
-        torch.cuda.synchronize()
-        c0 = int(lib.b200_launch_count())
-        stack.compute()
+    stack.compute()
     launches_per_step = int(lib.b200_launch_count()) - c0
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    graph = capture(torch, stack.compute)
+    step = graph.replay if graph is not None else stack.compute
     dbg(f"capture done (graph={graph is not None})")
     for _ in range(3):
         step()
     torch.cuda.synchronize()
-    dbg("graph warm-up done")
 
     # ---- device-resident timed region
     clocks = ClockSampler(local_rank)
@@ -597,19 +910,68 @@ def main():
         clocks.start()
     sec = timed_loop(torch, step, args.steps, dist)
     dbg("device-resident region done")
-    # keep the sampler running through the e2e region too (short regions give few samples)
-    # ---- end-to-end: host activations in, host outputs out, every step
-    def e2e_step():
-        stack.step_e2e()
-        torch.cuda.current_stream().synchronize()
-    for _ in range(3):
-        e2e_step()
-    sec_e2e = timed_loop(torch, e2e_step, args.steps, dist)
+
+    # ---- N-rank parity carried by the line itself, and the NCCL baseline leg
+    multi = None
+    if world > 1:
+        torch.cuda.synchronize(); dist.barrier()
+        checked, ok = stack.selfcheck()
+        flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device="cuda")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        multi = {"gather": "fused into the persistent launch (peer stores over NVLink + system-scope completion flags)" if fused
+                           else "NCCL all_gather_into_tensor per MUL_MAT group (symmetric memory unavailable)",
+                 "selfcheck": {"rows_recomputed_per_rank": checked, "of_rank": "(rank + 1) % N", "bit_identical_on_every_rank": bool(flag.item())}}
+        if fused and not args.no_extras:
+            try:
+                for _ in range(3):
+                    stack.compute_nccl()
+                torch.cuda.synchronize(); dist.barrier()
+                c0 = int(lib.b200_launch_count())
+                stack.compute_nccl()
+                nl = int(lib.b200_launch_count()) - c0
+                gn = capture(torch, stack.compute_nccl)
+                fn = gn.replay if gn is not None else stack.compute_nccl
+                for _ in range(3):
+                    fn()
+                reps = max(10, min(args.steps, 50))
+                sec_n = timed_loop(torch, fn, reps, dist) / reps
+                multi["nccl_per_group_baseline"] = {"ms_per_step": round(sec_n * 1e3, 4), "groups": len(stack.groups), "launches": nl,
+                                                    "GBps": round(stack.local_alg_bytes * world / sec_n / 1e9, 1)}
+                del gn
+            except Exception as e:               # noqa: BLE001
+                multi["nccl_per_group_baseline"] = {"error": str(e)[:200]}
+        dbg("multi-rank legs done")
+
+    # ---- end to end, host buffers, every step
+    e2e_path, plug = None, None
+    if world == 1:
+        try:
+            plug = PluginStep(stack)
+            sec_e2e = plug.timed(args.steps, args.warmup)
+            out = plug.outputs()
+            ref_out = stack.y_dev[stack.h0_len:].cpu().numpy()
+            if out.shape != ref_out.shape or not (out.view("uint32") == ref_out.view("uint32")).all():
+                raise RuntimeError("plugin outputs differ from the C-ABI outputs")
+            e2e_path = ("pinned host (ggml_backend_b200_host_buffer_type) -> ggml_backend_tensor_set_async -> ggml_backend_graph_compute_async "
+                        "on B200_0 (plugin: b200_mul_mat_batch, CUDA-graph replay) -> ggml_backend_tensor_get_async -> ggml_backend_synchronize; "
+                        "outputs bit-identical to the C-ABI step; host wall clock")
+            h2d, d2h = plug.h_bytes_in, plug.h_bytes_out
+        except Exception as e:                   # noqa: BLE001
+            sys.stderr.write(f"[bench] plugin e2e leg unavailable ({str(e)[:300]}); timing the C-ABI e2e\n")
+            plug = None
+    if plug is None:
+        def e2e_step():
+            stack.step_e2e()
+            torch.cuda.current_stream().synchronize()
+        for _ in range(3):
+            e2e_step()
+        sec_e2e = timed_loop(torch, e2e_step, args.steps, dist)
+        e2e_path = ("pinned host activations -> b200_mul_mat_batch" + ("_peers" if fused else "") + " (C ABI) -> pinned host outputs, sync per step"
+                    + ("; rank 0 moves the host data (every rank holds the gathered outputs)" if world > 1 else "; pipelined over 4 sub-lists"))
+        h2d, d2h = stack.x_bytes, stack.y_bytes
     dbg("e2e region done")
     clk = clocks.stop() if rank == 0 else None
-
-    # parity guard: the host copy of the outputs is what the device computed, and it is finite
-    if not bool(torch.isfinite(stack.y_host).all()):
+    if not bool(torch.isfinite(stack.y_dev).all()):
         raise RuntimeError("non-finite outputs")
 
     alg_total = stack.local_alg_bytes * world                       # every rank does the same amount
@@ -623,33 +985,24 @@ def main():
     k_sec, k_bytes = sec / args.steps, stack.local_alg_bytes
     peak, peak_src = hbm_peak()
     achieved = k_bytes / k_sec / 1e9
-    traffic = ncu_traffic()
-    per_node_sec = None
-    if world == 1 and not args.no_extras:
-        try:
-            per_node_sec = measure_per_node_launches(torch, kern, stack, reps=max(5, min(args.steps, 20)))
-        except Exception as e:                   # noqa: BLE001
-            sys.stderr.write(f"[bench] per-node comparison leg failed: {e}\n")
-
+    traffic = ncu_traffic() if (world == 1 and args.stack == "llama2-7b" and args.wtype == "q4_K") else None
+    wl = ("llama3-70b FFN (gate, up 28672x8192; down 8192x28672) x 16 layers, Q4_K, decode mat-vec n=1, rows split over the GPUs (BASELINE configs[4])"
+          if strong else (WORKLOAD if args.wtype == "q4_K" else WORKLOAD.replace("Q4_K", args.wtype)))
     line = {
         "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": round(sec / args.steps * 1e3, 4), "higher_is_better": True,
-        "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "int8 dot (q8_1 activations), f32 accumulate",
+        "scaling": "strong" if (strong or world == 1) else "weak", "vs_baseline": None, "dtype": "int8 dot (q8_1 activations), f32 accumulate",
         "data": "synthetic",
-        "config": {"workload": "llama3-70b FFN (gate, up 28672x8192; down 8192x28672) x 16 layers, Q4_K, decode mat-vec n=1, rows split over the GPUs (BASELINE configs[4])"
-                               if strong else (WORKLOAD if args.wtype == "q4_K" else WORKLOAD.replace("Q4_K", args.wtype)),
-                   "n": 1, "matrices": len(mats), "row_mult": 1 if strong else world,
-                   "weight_bytes_per_gpu": stack.local_weight_bytes,
-                   "algorithmic_bytes_per_step": alg_total,
-                   "l2": f"inputs larger than L2 ({stack.local_weight_bytes / 1e9:.1f} GB of weights per GPU streamed once per step; no flush)",
+        "config": {"workload": wl, "n": 1, "matrices": len(mats), "row_mult": 1 if strong else world,
+                   "weight_bytes_per_gpu": stack.local_weight_bytes, "algorithmic_bytes_per_step": alg_total,
+                   "l2": f"inputs larger than L2 ({stack.local_weight_bytes / 1e9:.2f} GB of weights per GPU streamed once per step; no flush)",
                    "launch": "CUDA graph replay" if graph is not None else "eager",
-                   "parallelism": "single GPU" if world == 1 else f"row-split x{world}: one persistent launch per rank + one NCCL all-gather of the rank-major output arena per step"},
-        "e2e": {"value": round(e2e, 1), "unit": UNIT, "h2d_bytes_per_step": stack.x_bytes,
-                "d2h_bytes_per_step": stack.y_bytes, "ms_per_step": round(sec_e2e / args.steps * 1e3, 4),
-                "path": "pinned host activations -> b200_mul_mat_batch (C ABI) -> pinned host outputs, sync per step"
-                        + ("; pipelined over 4 sub-lists (copies overlap the persistent launches)" if world == 1 else "")},
+                   "parallelism": "single GPU" if world == 1 else
+                                  (f"row-split x{world}: one persistent launch per rank; finished rows stored into every rank's arena from inside the launch" if fused
+                                   else f"row-split x{world}: one persistent launch + one NCCL all-gather per MUL_MAT group")},
+        "e2e": {"value": round(e2e, 1), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                "ms_per_step": round(sec_e2e / args.steps * 1e3, 4), "path": e2e_path},
         "gpu_launches": launches_per_step * args.steps,
-        "decode_tok_s": round(args.steps / sec, 1),
         "weight_GBps": round(weight_total * args.steps / sec / 1e9, 1),
         "roofline": {"bound": "hbm", "kernel": "k_mmvq_batch (persistent list mat-vec; + k_quantize_batch pre-pass in the same timed launch pair)",
                      "achieved": round(achieved, 1),
@@ -657,28 +1010,63 @@ def main():
                      "frac_of_8TBps_spec": round(achieved / 8000.0, 4),
                      "us_per_launch": round(k_sec * 1e6, 3), "bytes_per_launch": int(k_bytes),
                      "traffic": traffic},
-        "one_launch_per_mul_mat": None if per_node_sec is None else {
-            "ms_per_step": round(per_node_sec * 1e3, 4), "GBps": round(stack.local_alg_bytes / per_node_sec / 1e9, 1),
-            "note": "same step as 225 per-node fused decode launches (CUDA graph + PDL), for comparison"},
         "clocks": clk,
     }
+    if multi is not None:
+        line["multi_gpu"] = multi
+    if not args.no_extras:
+        try:
+            line["decode_chain"] = measure_decode_chain(torch, kern, stack, peak, reps=50, dist=dist)
+            ch = line["decode_chain"].get("chained")
+            if ch and world == 1:
+                line["roofline_decode_tok_s"] = {"bound": "hbm", "what": "GEMM-only decode passes/s of the dependent chain (the tok/s term of the metric; no attention / norms)",
+                                                 "achieved": ch["passes_per_s"], "peak": round(peak * 1e9 / stack.local_alg_bytes, 1), "unit": "passes/s",
+                                                 "frac": round(ch["passes_per_s"] / (peak * 1e9 / stack.local_alg_bytes), 4), "traffic": None}
+        except Exception as e:                   # noqa: BLE001
+            line["decode_chain"] = {"error": str(e)[:300]}
+    if plug is not None and not args.no_extras:
+        try:
+            pc = PluginStep(stack, chain=True)
+            sec_c = pc.timed(min(args.steps, 100), 3)
+            n_c = min(args.steps, 100)
+            got = pc.outputs()
+            li = stack.plan[-1][0]
+            want = stack.y_dev[stack.off[li]: stack.off[li] + mats[li].m].cpu().numpy()
+            line["decode_chain"]["e2e_through_plugin"] = {
+                "ms_per_pass": round(sec_c / n_c * 1e3, 4), "GBps": round(stack.local_alg_bytes * n_c / sec_c / 1e9, 1),
+                "h2d_bytes_per_step": pc.h_bytes_in, "d2h_bytes_per_step": pc.h_bytes_out,
+                "logits_bit_identical_to_c_abi_chain": bool((got.view("uint32") == want.view("uint32")).all()),
+                "path": "ggml graph with the chain's dependencies on B200_0: first activation in, last output out"}
+            pc.close()
+        except Exception as e:                   # noqa: BLE001
+            line.setdefault("decode_chain", {})["e2e_through_plugin"] = {"error": str(e)[:300]}
+    if plug is not None:
+        plug.close()
     if rank == 0 and world == 1 and not args.no_extras:
-        try:
-            line["prefill_n512_TFLOPs"] = measure_prefill(torch, kern)
-        except Exception as e:                   # noqa: BLE001
-            line["prefill_n512_TFLOPs"] = {"error": str(e)[:200]}
-        try:
-            line["support_kernels"] = measure_support(torch, kern, peak)
-        except Exception as e:                   # noqa: BLE001
-            line["support_kernels"] = {"error": str(e)[:200]}
-        try:
-            line["decode_batches"] = measure_decode_batches(torch, kern, stack, peak)
-        except Exception as e:                   # noqa: BLE001
-            line["decode_batches"] = {"error": str(e)[:200]}
-        try:
-            line["decode_chain"] = measure_decode_chain(torch, kern, stack, peak)
-        except Exception as e:                   # noqa: BLE001
-            line["decode_chain"] = {"error": str(e)[:200]}
+        def leg(name, fn):
+            try:
+                line[name] = fn()
+            except Exception as e:               # noqa: BLE001
+                line[name] = {"error": str(e)[:200]}
+        leg("one_launch_per_mul_mat", lambda: (lambda t: {"ms_per_step": round(t * 1e3, 4), "GBps": round(stack.local_alg_bytes / t / 1e9, 1),
+                                                          "note": "same step as 225 per-node fused decode launches (CUDA graph + PDL), for comparison"})(
+            measure_per_node_launches(torch, kern, stack, reps=max(5, min(args.steps, 20)))))
+        peaks = tensor_peaks(kern)
+        line["tensor_peaks"] = peaks
+        leg("prefill_TFLOPs", lambda: measure_prefill_all(torch, kern, peaks))
+        leg("support_kernels", lambda: measure_support(torch, kern, peak))
+        leg("decode_batches", lambda: measure_decode_batches(torch, kern, stack, peak))
+        def c_abi_e2e():
+            def e2e_step():
+                stack.step_e2e()
+                torch.cuda.current_stream().synchronize()
+            for _ in range(3):
+                e2e_step()
+            n_ = min(args.steps, 100)
+            t = timed_loop(torch, e2e_step, n_) / n_
+            return {"ms_per_step": round(t * 1e3, 4), "GBps": round(stack.local_alg_bytes / t / 1e9, 1),
+                    "path": "b200_mul_mat_batch (C ABI) with torch pinned tensors, copies pipelined over 4 sub-lists on 3 streams"}
+        leg("e2e_c_abi_pipelined", c_abi_e2e)
         _, info = cpu_reference()
         line["cpu_baseline"] = {k: info[k] for k in ("value", "unit", "cores", "kind", "sample")}
     if rank == 0:

@@ -118,6 +118,8 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
     lib.b200_acts_columns_bytes.restype = sz;    lib.b200_acts_columns_bytes.argtypes = [i64, i64]
     lib.b200_quantize_acts_record.restype = i32; lib.b200_quantize_acts_record.argtypes = [vp, i64, vp, vp]
     lib.b200_quantize_acts_columns.restype = i32; lib.b200_quantize_acts_columns.argtypes = [vp, sz, i64, i64, vp, vp]
+    lib.b200_tensor_peak.restype = i32
+    lib.b200_tensor_peak.argtypes = [i32, vp, vp, vp, i32, i32, C.POINTER(C.c_double), vp]
     lib.b200_set_option.restype = i32;           lib.b200_set_option.argtypes = [i32, i32]
     lib.b200_device_error_flags.restype = C.c_uint; lib.b200_device_error_flags.argtypes = [i32]
     return lib
@@ -180,6 +182,24 @@ class Kernels:
             def __exit__(self_inner, *exc):
                 kern.set_option(name, self_inner.prev)
         return _Ctx()
+
+    def tensor_peak(self, kind: str, iters: int = 4096, reps: int = 5) -> float:
+        """ops/s (2 x MACs) of the tcgen05 micro-kernel: kind "i8" or "bf16" (include/ggml_b200.h: b200_tensor_peak)."""
+        torch = self.torch
+        a = torch.randint(0, 127, (128, 128), dtype=torch.uint8, device=self.device)
+        b = torch.randint(0, 127, (256, 128), dtype=torch.uint8, device=self.device)
+        out = C.c_double(0.0)
+        self._check(self.lib.b200_tensor_peak(0 if kind == "i8" else 1, a.data_ptr(), b.data_ptr(), None, iters, reps,
+                                              C.byref(out), self._stream()), "tensor_peak")
+        return float(out.value)
+
+    def tensor_peak_verify(self, kind: str, a, b):
+        """one 128 x 256 x 128-byte product by the micro-kernel: a [128,128] / b [256,128] uint8 views -> [128,256] int32 / float32"""
+        torch = self.torch
+        out = torch.zeros((128, 256), dtype=torch.int32, device=self.device)
+        self._check(self.lib.b200_tensor_peak(0 if kind == "i8" else 1, a.data_ptr(), b.data_ptr(), out.data_ptr(), 1, 1,
+                                              None, self._stream()), "tensor_peak")
+        return out if kind == "i8" else out.view(torch.float32)
 
     def device_error_flags(self, clear: bool = True) -> int:
         """sticky error bits set by kernels (bit 0: GET_ROWS index outside the table); synchronizes first."""

@@ -535,7 +535,7 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b, const __g
 }
 
 // f32 [n, k] (row stride in bytes) -> bf16 [n, k] packed, RN (the full exponent range of f32 survives)
-__global__ void __launch_bounds__(256) k_f32_to_bf16(const uint8_t * __restrict__ x, int64_t x_row_stride, int64_t k, uint16_t * __restrict__ y) {
+static __global__ void __launch_bounds__(256) k_f32_to_bf16(const uint8_t * __restrict__ x, int64_t x_row_stride, int64_t k, uint16_t * __restrict__ y) {
     const int64_t row = blockIdx.y;
     const int64_t i = ((int64_t) blockIdx.x * 256 + threadIdx.x) * 4;
     if (i >= k) return;

@@ -238,6 +238,17 @@ B200_API int    b200_quantize_acts_record(const float * x_dev, int64_t k, void *
 B200_API int    b200_quantize_acts_columns(const float * x_dev, size_t x_row_stride_bytes, int64_t k, int64_t n,
                                            void * columns_dev, void * stream);
 
+/* ---- what the tensor cores of this box deliver -------------------------------------------------
+ * A tcgen05 micro-kernel (operands resident in shared memory, accumulator in TMEM, nothing but the MMA issue loop):
+ * kind 0 = kind::i8 (s8 x s8 -> s32), kind 1 = kind::f16 with bf16 operands (-> f32).  The denominators of the batched
+ * MUL_MAT's roofline (BASELINE.json: "int8 TOPS ... against the int8 dense peak"); the reference measures no peak.
+ * a_dev: [128][128] bytes, b_dev: [256][128] bytes, row-major, K contiguous.  out_dev != NULL: one CTA, one pass over
+ * the 128 bytes of K, accumulators written as [128][256] 32-bit words (verification).  out_dev == NULL: every SM issues
+ * iters x 4 MMAs of 128 x 256 x 32 bytes per launch, `reps` launches are timed with CUDA events (the call synchronizes
+ * on its own events) and 2 x MACs / s over the whole GPU is returned in *ops_per_s. */
+B200_API int b200_tensor_peak(int kind, const void * a_dev, const void * b_dev, void * out_dev, int iters, int reps,
+                              double * ops_per_s, void * stream);
+
 /* Number of kernels this library has launched since load (bench.py's gpu_launches). */
 B200_API uint64_t b200_launch_count(void);
 

@@ -1024,3 +1024,24 @@ def test_mul_mat_batch_peers_group_of_one(kern, oracle):
     for o in outs:
         assert np.array_equal(u32(o), u32(plain))
     assert np.isfinite(plain).all() and np.abs(plain).max() > 0
+
+
+def test_tensor_peak_micro_kernel_arithmetic(kern):
+    """the tcgen05 micro-kernel behind the int8 / bf16 tensor peaks computes what its descriptor says:
+    kind::i8 (s8 x s8 -> s32) exactly, kind::f16 with bf16 operands -> f32 exactly on small integers."""
+    import torch
+    rng = np.random.default_rng(9)
+    a = rng.integers(-128, 128, size=(128, 128)).astype(np.int8)
+    b = rng.integers(-128, 128, size=(256, 128)).astype(np.int8)
+    got = kern.tensor_peak_verify("i8", kern.to_device(a.view(np.uint8)), kern.to_device(b.view(np.uint8))).cpu().numpy()
+    want = a.astype(np.int32) @ b.astype(np.int32).T
+    assert np.array_equal(got, want)
+    af = rng.integers(-8, 9, size=(128, 64)).astype(np.float32)
+    bf = rng.integers(-8, 9, size=(256, 64)).astype(np.float32)
+    ab = torch.from_numpy(af).to(torch.bfloat16).view(torch.uint8).reshape(128, 128).to(kern.device)
+    bb = torch.from_numpy(bf).to(torch.bfloat16).view(torch.uint8).reshape(256, 128).to(kern.device)
+    gotf = kern.tensor_peak_verify("bf16", ab, bb).cpu().numpy()
+    assert np.array_equal(gotf, af @ bf.T)
+    # and the timed mode returns something sane: between 0.2 and 20 peta-ops for int8
+    ops = kern.tensor_peak("i8", iters=512, reps=2)
+    assert 2e14 < ops < 2e16, ops

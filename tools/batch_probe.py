@@ -10,7 +10,7 @@ reps = int(sys.argv[1]) if len(sys.argv) > 1 else 20
 wtype = sys.argv[2] if len(sys.argv) > 2 else "q4_K"
 kern = b200.Kernels()
 mats = workloads.llama3_8b_q4_k_m_stack() if wtype == "l3mix" else workloads.llama2_7b_stack(wtype)
-stack = bench.DecodeStack(kern, mats, 1)
+stack = bench.DecodeStack(kern, mats)
 stack.compute(); torch.cuda.synchronize()
 if reps == 0:
     stack.compute(); torch.cuda.synchronize()

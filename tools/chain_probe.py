@@ -9,7 +9,7 @@ import b200, bench, workloads
 kern = b200.Kernels()
 layers = int(os.environ.get("CHAIN_LAYERS", "32"))
 mats = workloads.llama2_7b_stack("q4_K", n_layers=layers)
-stack = bench.DecodeStack(kern, mats, 1)
+stack = bench.DecodeStack(kern, mats)
 peak, _ = bench.hbm_peak()
 for _ in range(3):
     stack.compute()
