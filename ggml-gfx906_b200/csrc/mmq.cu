@@ -4,6 +4,7 @@
 // TMA descriptor over them and launches one CTA per 128 x BN output tile.
 #include "common.cuh"
 #include "mmq_tc.cuh"
+#include "mmq_i8.cuh"
 
 #include <mutex>
 #include <cstring>
@@ -77,10 +78,89 @@ int pick_bn(int64_t m, int64_t n, int sm_count) {
 
 } // namespace
 
+// ---------------------------------------------------------------- the int8 route (mmq_i8.cuh)
+static size_t i8_yq_bytes(int64_t k, int64_t n_pad) { return ((size_t) n_pad * (size_t) k + 255) & ~(size_t) 255; }
+static size_t i8_ds_bytes(int64_t k, int64_t n_pad) { return (size_t) ((k + 127) / 128) * (size_t) n_pad * 4 * sizeof(float2); }
+
+template <int T, int BN>
+static int launch_mmq_i8(const mmq_i8_args & a, const CUtensorMap & tmap_b, const CUtensorMap & tmap_w, cudaStream_t st) {
+    auto kern = k_mmq_i8<T, BN>;
+    const size_t smem = mmq_i8_smem<BN>::total(a.raw_pitch, MMQI_RS);
+    static smem_limit lim;
+    if (const int rc = lim.ensure(kern, smem)) return rc;
+    const dim3 grid((unsigned) ceil_div(a.m, MMQI_BM), (unsigned) ceil_div(a.n, BN));
+    kern<<<grid, MMQI_THREADS, smem, st>>>(a, tmap_b, tmap_w);
+    b200_count_launch(1);
+    B200_RETURN_IF_LAUNCH_FAILED();
+    return B200_OK;
+}
+template <int T>
+static int launch_mmq_i8_bn(mmq_i8_args a, const CUtensorMap & tmap_b, const CUtensorMap & tmap_w, int bn, cudaStream_t st) {
+    a.raw_pitch = slab<T>::pitch;
+    switch (bn) {
+        case 32:  return launch_mmq_i8<T, 32>(a, tmap_b, tmap_w, st);
+        case 64:  return launch_mmq_i8<T, 64>(a, tmap_b, tmap_w, st);
+        default:  return launch_mmq_i8<T, 128>(a, tmap_b, tmap_w, st);
+    }
+}
+
+// B200_NOT_APPLICABLE: this format / alignment has no int8 route (the caller takes the bf16 kernel)
+static int mul_mat_q_i8(int type, const void * w_dev, size_t w_row_stride_bytes, int64_t m, int64_t k,
+                        const float * x_dev, size_t x_row_stride_bytes, int64_t n, float * dst_dev, size_t dst_col_stride_bytes,
+                        void * workspace_dev, cudaStream_t st) {
+    if (type == T_Q6_K) return B200_NOT_APPLICABLE;                    // scales per 16 weights: two groups per K = 32 MMA
+    if ((uintptr_t) w_dev % 16 != 0 || w_row_stride_bytes % 16 != 0 || b200_row_bytes(type, k) % 4 != 0 || k % 16 != 0) return B200_NOT_APPLICABLE;
+    encode_tiled_fn encode = get_encode_tiled();
+    if (!encode) return B200_ERR_NO_DEVICE;
+    const int forced = b200_option(B200_OPT_MMQ_BN);
+    const int bn = (forced == 32 || forced == 64 || forced == 128) ? forced : (n <= 32 ? 32 : (n <= 64 ? 64 : 128));
+    const int64_t n_pad = ceil_div(n, 128) * 128;
+    int8_t * yq = (int8_t *) (((uintptr_t) workspace_dev + 255) & ~(uintptr_t) 255);
+    float2 * ds = (float2 *) ((uint8_t *) yq + i8_yq_bytes(k, n_pad));
+    // 1. activations -> q8_1 (int8 plane + (d, s) pairs), the analogue of quantize_mmq_q8_1 (src/ggml-cuda/quantize.cu:50-143)
+    for (int64_t r0 = 0; r0 < n_pad; r0 += 65535) {
+        const int64_t nr = n_pad - r0 < 65535 ? n_pad - r0 : 65535;
+        const dim3 grid((unsigned) ceil_div(ceil_div(k, 128) * 4, 8), (unsigned) nr);
+        k_quantize_mmq_q8_1<<<grid, 256, 0, st>>>((const uint8_t *) x_dev + r0 * x_row_stride_bytes, (int64_t) x_row_stride_bytes, k,
+                                                  n - r0 > 0 ? n - r0 : 0, n_pad, yq + r0 * k, ds + r0 * 4);
+        b200_count_launch(1);
+    }
+    B200_RETURN_IF_LAUNCH_FAILED();
+    // 2. descriptors: activations {k, n_pad} bytes, box {128, bn}, 128-byte swizzle; raw weights as in the bf16 route
+    CUtensorMap tmap_b, tmap_w;
+    const cuuint32_t estr[2] = { 1, 1 };
+    {
+        const cuuint64_t gdim[2] = { (cuuint64_t) k, (cuuint64_t) n_pad };
+        const cuuint64_t gstride[1] = { (cuuint64_t) k };
+        const cuuint32_t box[2] = { 128, (cuuint32_t) bn };
+        if (encode(&tmap_b, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, yq, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) return B200_NOT_APPLICABLE;
+        const int slab_words = (type == T_Q8_0 ? 272 : (type == T_Q5_K ? 176 : 144)) / 4;
+        const cuuint64_t wdim[2] = { (cuuint64_t) (b200_row_bytes(type, k) / 4), (cuuint64_t) m };
+        const cuuint64_t wstride[1] = { (cuuint64_t) w_row_stride_bytes };
+        const cuuint32_t wbox[2] = { (cuuint32_t) slab_words, (cuuint32_t) MMQI_BM };
+        if (encode(&tmap_w, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<void *>(w_dev), wdim, wstride, wbox, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) return B200_NOT_APPLICABLE;
+    }
+    mmq_i8_args a;
+    a.m = m; a.k = k; a.n = n; a.n_pad = n_pad; a.dst = dst_dev; a.dst_col_stride = (int64_t) (dst_col_stride_bytes / 4);
+    a.ds = ds; a.nblk = (int) (k / type_qk(type)); a.raw_pitch = 0;
+    switch (type) {
+        case T_Q4_0: return launch_mmq_i8_bn<T_Q4_0>(a, tmap_b, tmap_w, bn, st);
+        case T_Q8_0: return launch_mmq_i8_bn<T_Q8_0>(a, tmap_b, tmap_w, bn, st);
+        case T_Q4_K: return launch_mmq_i8_bn<T_Q4_K>(a, tmap_b, tmap_w, bn, st);
+        case T_Q5_K: return launch_mmq_i8_bn<T_Q5_K>(a, tmap_b, tmap_w, bn, st);
+        default: return B200_NOT_APPLICABLE;
+    }
+}
+
 extern "C" size_t b200_mul_mat_q_workspace_size(int64_t m, int64_t k, int64_t n) {
     (void) m;
     if (k <= 0 || n <= 0) return 256;
-    return (size_t) n * (size_t) k * sizeof(__nv_bfloat16) + 512;
+    const size_t bf16 = (size_t) n * (size_t) k * sizeof(__nv_bfloat16);
+    const int64_t n_pad = ceil_div(n, 128) * 128;
+    const size_t i8 = i8_yq_bytes(k, n_pad) + i8_ds_bytes(k, n_pad);
+    return (bf16 > i8 ? bf16 : i8) + 512;
 }
 
 extern "C" int b200_mul_mat_q(int type, const void * w_dev, size_t w_row_stride_bytes, int64_t m, int64_t k,
@@ -96,6 +176,13 @@ extern "C" int b200_mul_mat_q(int type, const void * w_dev, size_t w_row_stride_
     if (!workspace_dev || workspace_bytes < b200_mul_mat_q_workspace_size(m, k, n)) return B200_ERR_WORKSPACE;
     if (k > 0x7FFFFFFF || n > 0x7FFFFFFF) return B200_ERR_SHAPE;
 
+    // The q8_1 int8 route (option mmq_route = 2; measured slower than the bf16 route on B200, DESIGN.md §4.4: the per-block
+    // drain of the accumulators is bound by the CUDA cores, not by the tensor pipe) ..
+    if (b200_option(B200_OPT_MMQ_ROUTE) == 2) {
+        const int rc = mul_mat_q_i8(type, w_dev, w_row_stride_bytes, m, k, x_dev, x_row_stride_bytes, n, dst_dev, dst_col_stride_bytes, workspace_dev, st);
+        if (rc != B200_NOT_APPLICABLE) return rc;
+    }
+    // .. and the bf16 route.
     // 1. activations -> bf16 [n][k]
     uint16_t * xb = (uint16_t *) (((uintptr_t) workspace_dev + 255) & ~(uintptr_t) 255);
     for (int64_t r0 = 0; r0 < n; r0 += 65535) {

@@ -1045,3 +1045,67 @@ def test_tensor_peak_micro_kernel_arithmetic(kern):
     # and the timed mode returns something sane: between 0.2 and 20 peta-ops for int8
     ops = kern.tensor_peak("i8", iters=512, reps=2)
     assert 2e14 < ops < 2e16, ops
+
+
+# ---------------------------------------------------------------------------- MUL_MAT, batched, the q8_1 int8 tensor-core route
+I8_TYPES = ["q4_0", "q8_0", "q4_K", "q5_K"]
+I8_SHAPES = [(128, 256, 16), (130, 512, 33), (300, 1024, 64), (257, 2048, 100), (128, 4096, 128), (384, 1024, 129),
+             (200, 768, 257), (64, 11008, 48), (1, 256, 17), (129, 256, 300)]
+
+
+@pytest.mark.parametrize("t", I8_TYPES)
+@pytest.mark.parametrize("m,k,n", I8_SHAPES)
+def test_mul_mat_q_int8_route_vs_oracle(kern, oracle, t, m, k, n):
+    """option mmq_route = 2: activations quantized to q8_1, one tcgen05 kind::i8 MMA per 32-block, block scales applied to
+    the drained int32 tiles (mmq_i8.cuh) -- the reference's own arithmetic (src/ggml-cuda/mmq.cuh:796-1092), so the
+    result is within f32 summation-order noise of the oracle's q8_1 mode and within the harness gate of exact truth."""
+    w = random_blocks(t, m, k, seed=300 + m + k)
+    x = np.random.default_rng(17 + n).uniform(-1, 1, size=(n, k)).astype(np.float32)
+    with kern.option("mmq_route", 2):
+        c0 = kern.launch_count()
+        got = kern.mul_mat_q(t, dev_blocks(kern, w), m, k, kern.to_device(x)).cpu().numpy()
+        assert kern.launch_count() - c0 == 2          # quantize_mmq_q8_1 + the tile kernel
+    assert got.shape == (n, m) and np.isfinite(got).all()
+    assert oracle.nmse(oracle.mul_mat(t, w, m, k, x, mode=1), got) <= NMSE_ORACLE, oracle.nmse(oracle.mul_mat(t, w, m, k, x, mode=1), got)
+    assert oracle.nmse(oracle.mul_mat(t, w, m, k, x, mode=0), got) <= NMSE_REF
+
+
+@pytest.mark.parametrize("t", ["q4_0", "q8_0"])
+@pytest.mark.parametrize("k,int8", [(32, False), (96, False), (32 * 37, False), (256 * 3, True), (256 * 5 + 0, True)])
+def test_mul_mat_q_int8_route_applicability(kern, oracle, t, k, int8):
+    """the int8 route needs 16-byte-multiple rows (2-D TMA tiles of raw slabs): k % 256 == 0 for the 18 / 34-byte blocks.
+    Other k (tails) silently take the bf16 kernel -- still inside the harness gate, one launch less or more."""
+    m, n = 70, 20
+    w = random_blocks(t, m, k, seed=k)
+    x = np.random.default_rng(k).uniform(-1, 1, size=(n, k)).astype(np.float32)
+    with kern.option("mmq_route", 2):
+        got = kern.mul_mat_q(t, dev_blocks(kern, w), m, k, kern.to_device(x)).cpu().numpy()
+    assert oracle.nmse(oracle.mul_mat(t, w, m, k, x, mode=0), got) <= NMSE_REF
+    q8 = oracle.nmse(oracle.mul_mat(t, w, m, k, x, mode=1), got)
+    assert (q8 <= NMSE_ORACLE) == int8, (k, q8)
+
+
+@pytest.mark.parametrize("t", I8_TYPES)
+def test_mul_mat_q_int8_route_scales_and_adversarial(kern, oracle, t):
+    """per-block q8_1 scaling makes the int8 route indifferent to magnitude by construction; edge block scales included"""
+    m, k, n = 96, 2304, 40
+    w = adversarial_blocks(t, m, k, seed=31)
+    x = (np.random.default_rng(32).standard_normal(size=(n, k)) * 1e5).astype(np.float32)
+    x[3] = 0.0
+    with kern.option("mmq_route", 2):
+        got = kern.mul_mat_q(t, dev_blocks(kern, w), m, k, kern.to_device(x)).cpu().numpy()
+    want = oracle.mul_mat(t, w, m, k, x, mode=1)
+    fin = np.isfinite(want)
+    assert np.array_equal(np.isfinite(got), fin)
+    assert nmse64(want[fin], got[fin]) <= 1e-9
+    assert not got[3].any()
+
+
+@pytest.mark.parametrize("bn", [32, 64, 128])
+def test_mul_mat_q_int8_route_every_tile_width(kern, oracle, bn):
+    t, m, k, n = "q4_K", 256, 1024, 300
+    w = random_blocks(t, m, k, seed=bn)
+    x = np.random.default_rng(bn).standard_normal(size=(n, k)).astype(np.float32)
+    with kern.option("mmq_route", 2), kern.option("mmq_bn", bn):
+        got = kern.mul_mat_q(t, dev_blocks(kern, w), m, k, kern.to_device(x)).cpu().numpy()
+    assert oracle.nmse(oracle.mul_mat(t, w, m, k, x, mode=1), got) <= NMSE_ORACLE
