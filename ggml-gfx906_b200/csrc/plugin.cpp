@@ -290,6 +290,46 @@ static void b200_compute_node(b200_backend_ctx * ctx, struct ggml_tensor * node)
             const int out_type = dst->type == GGML_TYPE_F32 ? B200_TYPE_F32 : B200_TYPE_F16;
             B200_OK_OR_ABORT(b200_dequantize_4d((int) s0->type, s0->data, s0->ne, s0->nb, dst->data, out_type, dst->ne, dst->nb, ctx->stream));
         } break;
+        case GGML_OP_RMS_NORM: {
+            float eps;
+            memcpy(&eps, node->op_params, sizeof(float));
+            B200_OK_OR_ABORT(b200_rms_norm((const float *) s0->data, s0->ne, s0->nb, (float *) node->data, eps, ctx->stream));
+        } break;
+        case GGML_OP_ADD:
+        case GGML_OP_MUL:
+            B200_OK_OR_ABORT(b200_bin_bcast(node->op == GGML_OP_ADD ? 0 : 1, (const float *) s0->data, s0->ne, s0->nb,
+                                            (const float *) s1->data, s1->ne, s1->nb, (float *) node->data, ctx->stream));
+            break;
+        case GGML_OP_GLU: {
+            // SWIGLU: one tensor whose rows hold [x | g] (or [g | x] when swapped), or two tensors (src/ggml-cpu/ops.cpp:3551-3610)
+            const int32_t swapped = ((const int32_t *) node->op_params)[1];
+            const int64_t nc = s1 ? s0->ne[0] : s0->ne[0] / 2;
+            const char * x = (const char *) s0->data, * g = s1 ? (const char *) s1->data : (const char *) s0->data;
+            if (!s1) { x += swapped ? nc * sizeof(float) : 0; g += swapped ? 0 : nc * sizeof(float); }
+            B200_OK_OR_ABORT(b200_swiglu((const float *) x, s0->nb[1], (const float *) g, s1 ? s1->nb[1] : s0->nb[1], nc, ggml_nrows(s0),
+                                         (float *) node->data, ctx->stream));
+        } break;
+        case GGML_OP_ROPE: {
+            const int32_t * p = (const int32_t *) node->op_params;
+            const int n_dims = p[1], mode = p[2], n_ctx_orig = p[4];
+            float freq_base, freq_scale, ext_factor, attn_factor, beta_fast, beta_slow, corr[2];
+            memcpy(&freq_base, p + 5, 4); memcpy(&freq_scale, p + 6, 4); memcpy(&ext_factor, p + 7, 4);
+            memcpy(&attn_factor, p + 8, 4); memcpy(&beta_fast, p + 9, 4); memcpy(&beta_slow, p + 10, 4);
+            ggml_rope_yarn_corr_dims(n_dims, n_ctx_orig, freq_base, beta_fast, beta_slow, corr);
+            const struct ggml_tensor * s2 = node->src[2];
+            B200_OK_OR_ABORT(b200_rope((const float *) s0->data, s0->ne, s0->nb, (float *) node->data, node->nb, (const int32_t *) s1->data,
+                                       s2 ? (const float *) s2->data : nullptr, n_dims, (mode & GGML_ROPE_TYPE_NEOX) ? 1 : 0,
+                                       freq_base, freq_scale, ext_factor, attn_factor, corr[0], corr[1], ctx->stream));
+        } break;
+        case GGML_OP_SOFT_MAX: {
+            float scale, max_bias;
+            memcpy(&scale, (const float *) node->op_params + 0, 4); memcpy(&max_bias, (const float *) node->op_params + 1, 4);
+            const struct ggml_tensor * s2 = node->src[2];
+            const int64_t none[4] = { 0, 0, 1, 1 }; const size_t nonb[4] = { 0, 0, 0, 0 };
+            B200_OK_OR_ABORT(b200_soft_max((const float *) s0->data, s0->ne, s0->nb, s1 ? s1->data : nullptr, s1 ? (int) s1->type : 0,
+                                           s1 ? s1->ne : none, s1 ? s1->nb : nonb, s2 ? (const float *) s2->data : nullptr, scale, max_bias,
+                                           (float *) node->data, ctx->stream));
+        } break;
         default:
             b200_log("graph_compute: op %s was never claimed by supports_op\n", ggml_op_name(node->op));
             GGML_ABORT("ggml-b200: unsupported op");
@@ -550,6 +590,29 @@ static bool b200_dev_supports_op(ggml_backend_dev_t dev, const struct ggml_tenso
             const struct ggml_tensor * dst = op->op == GGML_OP_CPY ? s1 : op;
             return s0 && dst && is_hot_quant(s0->type) && (dst->type == GGML_TYPE_F32 || dst->type == GGML_TYPE_F16) &&
                    s0->nb[0] == ggml_type_size(s0->type) && ggml_nelements(s0) == ggml_nelements(dst);
+        }
+        // the f32 ops between the MUL_MATs of a decoder layer (csrc/layer_ops.cu)
+        case GGML_OP_RMS_NORM:
+            return s0 && s0->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 && s0->nb[0] == sizeof(float) && ggml_is_contiguous(op);
+        case GGML_OP_ADD:
+        case GGML_OP_MUL:
+            return s0 && s1 && s0->type == GGML_TYPE_F32 && s1->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 &&
+                   ggml_is_contiguous(op) && ggml_are_same_shape(s0, op) && ggml_can_repeat(s1, s0);
+        case GGML_OP_GLU:
+            return s0 && ggml_get_glu_op(op) == GGML_GLU_OP_SWIGLU && s0->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 &&
+                   ggml_is_contiguous_1(s0) && ggml_is_contiguous(op) && (!s1 || (s1->type == GGML_TYPE_F32 && ggml_is_contiguous_1(s1)));
+        case GGML_OP_ROPE: {
+            const int mode = ((const int32_t *) op->op_params)[2];
+            const struct ggml_tensor * s2 = op->src[2];
+            return s0 && s1 && s0->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 && s1->type == GGML_TYPE_I32 &&
+                   (mode & ~GGML_ROPE_TYPE_NEOX) == 0 && s0->nb[0] == sizeof(float) && op->nb[0] == sizeof(float) && s0->ne[0] % 2 == 0 &&
+                   (!s2 || s2->type == GGML_TYPE_F32);
+        }
+        case GGML_OP_SOFT_MAX: {
+            const struct ggml_tensor * s2 = op->src[2];
+            return s0 && s0->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 && s0->nb[0] == sizeof(float) && ggml_is_contiguous(op) &&
+                   (!s1 || ((s1->type == GGML_TYPE_F32 || s1->type == GGML_TYPE_F16) && s1->nb[0] == ggml_type_size(s1->type))) &&
+                   (!s2 || s2->type == GGML_TYPE_F32);
         }
         default:
             return false;

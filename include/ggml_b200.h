@@ -238,6 +238,30 @@ B200_API int    b200_quantize_acts_record(const float * x_dev, int64_t k, void *
 B200_API int    b200_quantize_acts_columns(const float * x_dev, size_t x_row_stride_bytes, int64_t k, int64_t n,
                                            void * columns_dev, void * stream);
 
+/* ---- the f32 ops between the MUL_MATs of a decoder layer -----------------------------------------
+ * so that a Llama graph stays on the device between our mat-muls.  Values follow the reference's CPU
+ * operators (src/ggml-cpu/ops.cpp:4138-4186 rms_norm, :3551-3610 swiglu, :6049-6330 rope, :5685-5790 soft_max;
+ * src/ggml-cpu/binary-ops.cpp) within test-backend-ops' NMSE gates; they replace src/ggml-cuda/norm.cu, binbcast.cu,
+ * unary.cu (GLU), rope.cu and softmax.cu for these cases.  f32 only; dim 0 contiguous unless stated; dst contiguous.
+ *   b200_rms_norm:  dst = x / sqrt(mean(x^2 over dim 0) + eps)
+ *   b200_bin_bcast: op 0 = ADD, 1 = MUL; b is broadcast over a (ne_a[i] % ne_b[i] == 0), any strides; dst has a's shape
+ *   b200_swiglu:    dst[r, c] = silu(x[r, c]) * g[r, c], rows of nc values (the two halves of one tensor, or two tensors)
+ *   b200_rope:      ggml_rope_ext, normal (neox = 0: pairs (2i, 2i+1)) or NeoX (pairs (i, i + n_dims/2)); pos_dev: ne[2] int32;
+ *                   freq_factors_dev: n_dims/2 floats or NULL; corr_dim0/1 from ggml_rope_yarn_corr_dims (src/ggml.c:4088-4096)
+ *   b200_soft_max:  softmax over dim 0 of x * scale + slope(head) * mask, mask f32 / f16 [ne0, >= ne1, ne2m, ne3m] broadcast over
+ *                   dims 2, 3 (or NULL), ALiBi slopes from max_bias (head = dim 2), optional per-head sinks */
+B200_API int b200_rms_norm(const float * x_dev, const int64_t ne[4], const size_t nb[4], float * dst_dev, float eps, void * stream);
+B200_API int b200_bin_bcast(int op, const float * a_dev, const int64_t ne_a[4], const size_t nb_a[4],
+                            const float * b_dev, const int64_t ne_b[4], const size_t nb_b[4], float * dst_dev, void * stream);
+B200_API int b200_swiglu(const float * x_dev, size_t x_row_stride_bytes, const float * g_dev, size_t g_row_stride_bytes,
+                         int64_t nc, int64_t rows, float * dst_dev, void * stream);
+B200_API int b200_rope(const float * x_dev, const int64_t ne[4], const size_t nb[4], float * dst_dev, const size_t nb_dst[4],
+                       const int32_t * pos_dev, const float * freq_factors_dev, int n_dims, int neox,
+                       float freq_base, float freq_scale, float ext_factor, float attn_factor, float corr_dim0, float corr_dim1, void * stream);
+B200_API int b200_soft_max(const float * x_dev, const int64_t ne[4], const size_t nb[4], const void * mask_dev, int mask_type,
+                           const int64_t ne_mask[4], const size_t nb_mask[4], const float * sinks_dev, float scale, float max_bias,
+                           float * dst_dev, void * stream);
+
 /* ---- what the tensor cores of this box deliver -------------------------------------------------
  * A tcgen05 micro-kernel (operands resident in shared memory, accumulator in TMEM, nothing but the MMA issue loop):
  * kind 0 = kind::i8 (s8 x s8 -> s32), kind 1 = kind::f16 with bf16 operands (-> f32).  The denominators of the batched
