@@ -31,6 +31,11 @@ struct mmvq_args {
     int64_t ne12, ne13;     // activation/dst channels (grid y, z)
     int64_t r2, r3;         // broadcast ratios ne12/ne02, ne13/ne03
     int64_t n;              // columns per channel
+    // MUL_MAT_ID (mixture of experts): channel (i12 = slot e, i13 = token t) multiplies expert ids[e, t] of the stack
+    // a[k, m, n_as] with activation row (e % ne11, t); NULL for plain MUL_MAT
+    const uint8_t * ids;
+    int64_t ids_nb0, ids_nb1, n_as, ne11;
+    unsigned * bad;         // sticky error word: an expert id outside [0, n_as)
 };
 
 template <int T, int NCOLS>
@@ -39,8 +44,20 @@ __global__ void __launch_bounds__(128) k_mmvq_generic(const mmvq_args a) {
     const int64_t row = (int64_t) blockIdx.x * 4 + warp;
     if (row >= a.m) return;
     const int64_t i12 = blockIdx.y, i13 = blockIdx.z;
-    const uint8_t * wrow = a.w + row * a.w_row_stride + (i12 / a.r2) * a.w_nb2 + (i13 / a.r3) * a.w_nb3;
-    const int64_t col0 = (i13 * a.ne12 + i12) * a.n;          // first column of this channel in the scratch
+    const uint8_t * wrow;
+    int64_t col0;                                             // first column of this channel in the scratch
+    if (a.ids) {
+        const int32_t e = *reinterpret_cast<const int32_t *>(a.ids + i12 * a.ids_nb0 + i13 * a.ids_nb1);
+        if (e < 0 || e >= a.n_as) {                           // the reference asserts (src/ggml-cpu/ggml-cpu.c:1556): flag it, write zeros
+            if (lane == 0) { if (a.bad && row == 0) atomicOr_system(a.bad, 1u); a.dst[i12 * a.dst_nb2 + i13 * a.dst_nb3 + row] = 0.0f; }
+            return;
+        }
+        wrow = a.w + row * a.w_row_stride + (int64_t) e * a.w_nb2;
+        col0 = i13 * a.ne11 + i12 % a.ne11;
+    } else {
+        wrow = a.w + row * a.w_row_stride + (i12 / a.r2) * a.w_nb2 + (i13 / a.r3) * a.w_nb3;
+        col0 = (i13 * a.ne12 + i12) * a.n;
+    }
     const int64_t nsub = a.k / 32;
 
     float acc[NCOLS];
@@ -129,7 +146,7 @@ extern "C" int b200_mul_mat_vec_q(int type, const void * w_dev, size_t w_row_str
     a.dst = dst_dev;
     a.m = m; a.k = k; a.w_row_stride = (int64_t) w_row_stride_bytes; a.w_nb2 = 0; a.w_nb3 = 0;
     a.dst_col_stride = (int64_t) (dst_col_stride_bytes / 4); a.dst_nb2 = 0; a.dst_nb3 = 0;
-    a.ne12 = 1; a.ne13 = 1; a.r2 = 1; a.r3 = 1; a.n = n;
+    a.ne12 = 1; a.ne13 = 1; a.r2 = 1; a.r3 = 1; a.n = n; a.ids = nullptr; a.bad = nullptr;
     return mmvq_dispatch(type, a, (cudaStream_t) stream);
 }
 
@@ -189,7 +206,7 @@ extern "C" int b200_mul_mat_ex(int type_a, const void * a_dev, const int64_t ne_
         a.w = (const uint8_t *) a_dev; a.yq = yq; a.yd = yd; a.dst = dst_dev;
         a.m = m; a.k = k; a.w_row_stride = (int64_t) nb_a[1]; a.w_nb2 = (int64_t) nb_a[2]; a.w_nb3 = (int64_t) nb_a[3];
         a.dst_col_stride = m; a.dst_nb2 = m * n; a.dst_nb3 = m * n * ne12;
-        a.ne12 = ne12; a.ne13 = ne13; a.r2 = ne12 / ne_a[2]; a.r3 = ne13 / ne_a[3]; a.n = n;
+        a.ne12 = ne12; a.ne13 = ne13; a.r2 = ne12 / ne_a[2]; a.r3 = ne13 / ne_a[3]; a.n = n; a.ids = nullptr; a.bad = nullptr;
         return mmvq_dispatch(type_a, a, st);
     }
     // batched path, one 2-D problem per (i12, i13) channel
@@ -201,6 +218,61 @@ extern "C" int b200_mul_mat_ex(int type_a, const void * a_dev, const int64_t ne_
                                 workspace_bytes - (size_t) (ws - (uint8_t *) workspace_dev), st);
         if (rc) return rc;
     }
+    return B200_OK;
+}
+
+// ---------------------------------------------------------------- MUL_MAT_ID (mixture of experts)
+// dst[m, e, t] = as[:, :, ids[e, t]] x b[:, e % ne_b[1], t]: every (slot, token) pair is a one-column mat-vec on the expert the
+// ids tensor names.  The ids stay on the device (the reference copies them to the host and synchronizes for its
+// batched path, src/ggml-cuda/ggml-cuda.cu:2092-2233; its decode path passes them to the kernel, mmvq.cu:163-166, as here).
+extern "C" size_t b200_mul_mat_id_workspace_size(int type_a, const int64_t ne_a[4], const int64_t ne_b[4]) {
+    if (!type_is_quant(type_a) || ne_a[0] <= 0) return 256;
+    return b200_acts_scratch_bytes(ne_a[0], ne_b[1] * ne_b[2]) + 512;
+}
+extern "C" int b200_mul_mat_id(int type_a, const void * as_dev, const int64_t ne_a[4], const size_t nb_a[4],
+                               const float * b_dev, const int64_t ne_b[4], const size_t nb_b[4],
+                               const int32_t * ids_dev, const int64_t ne_ids[2], const size_t nb_ids[2],
+                               float * dst_dev, void * workspace_dev, size_t workspace_bytes, void * stream) {
+    if (!type_is_quant(type_a)) return B200_ERR_TYPE;
+    const int64_t k = ne_a[0], m = ne_a[1], n_as = ne_a[2];
+    const int64_t ne11 = ne_b[1], n_tok = ne_b[2], n_used = ne_ids[0];
+    if (k < 0 || m < 0 || n_as < 1 || ne_a[3] != 1 || ne_b[3] != 1 || ne_b[0] != k || k % type_qk(type_a) != 0) return B200_ERR_SHAPE;
+    if (ne_ids[1] != n_tok || ne11 < 1 || n_used < 1 || n_used % ne11 != 0 || n_used > 65535 || n_tok > 65535) return n_tok == 0 || n_used == 0 ? B200_OK : B200_ERR_SHAPE;
+    if (nb_a[0] != (size_t) type_bytes(type_a) || nb_b[0] != sizeof(float) || nb_b[1] % 4 || nb_b[2] % 4 || nb_ids[0] % 4 || nb_ids[1] % 4) return B200_ERR_STRIDE;
+    if (m == 0 || n_tok == 0) return B200_OK;
+    cudaStream_t st = (cudaStream_t) stream;
+    if (k == 0) return -(int) cudaMemsetAsync(dst_dev, 0, (size_t) (m * n_used * n_tok) * 4, st);
+    if (!workspace_dev || workspace_bytes < b200_mul_mat_id_workspace_size(type_a, ne_a, ne_b)) return B200_ERR_WORKSPACE;
+    uint8_t * ws = (uint8_t *) (((uintptr_t) workspace_dev + 255) & ~(uintptr_t) 255);
+    const int64_t cols = ne11 * n_tok;
+    const size_t qbytes = ((size_t) cols * (size_t) k + 255) / 256 * 256;
+    int8_t * yq = (int8_t *) ws;
+    float  * yd = (float *) (ws + qbytes);
+    for (int64_t t = 0; t < n_tok; t++) {                      // scratch column index = t * ne11 + row of b
+        if (nb_b[2] == (size_t) ne11 * nb_b[1] && t > 0) break;   // token slabs back to back: one call covered them all
+        const float * src = (const float *) ((const uint8_t *) b_dev + t * nb_b[2]);
+        const int64_t rows = nb_b[2] == (size_t) ne11 * nb_b[1] ? cols : ne11;
+        const int rc = b200_quantize_acts_planes(src, nb_b[1], k, rows, yq + t * ne11 * k, yd + t * ne11 * (k / 32), st);
+        if (rc) return rc;
+    }
+    mmvq_args a;
+    a.w = (const uint8_t *) as_dev; a.yq = yq; a.yd = yd; a.dst = dst_dev;
+    a.m = m; a.k = k; a.w_row_stride = (int64_t) nb_a[1]; a.w_nb2 = (int64_t) nb_a[2]; a.w_nb3 = 0;
+    a.dst_col_stride = m; a.dst_nb2 = m; a.dst_nb3 = m * n_used;
+    a.ne12 = n_used; a.ne13 = n_tok; a.r2 = 1; a.r3 = 1; a.n = 1;
+    a.ids = (const uint8_t *) ids_dev; a.ids_nb0 = (int64_t) nb_ids[0]; a.ids_nb1 = (int64_t) nb_ids[1]; a.n_as = n_as; a.ne11 = ne11;
+    a.bad = b200_error_word_dev();
+    int rc;
+    switch (type_a) {
+        case T_Q4_0: rc = launch_generic<T_Q4_0>(a, st); break;
+        case T_Q8_0: rc = launch_generic<T_Q8_0>(a, st); break;
+        case T_Q4_K: rc = launch_generic<T_Q4_K>(a, st); break;
+        case T_Q5_K: rc = launch_generic<T_Q5_K>(a, st); break;
+        default:     rc = launch_generic<T_Q6_K>(a, st); break;
+    }
+    if (rc != B200_OK) return rc;
+    b200_count_launch(1);
+    B200_RETURN_IF_LAUNCH_FAILED();
     return B200_OK;
 }
 

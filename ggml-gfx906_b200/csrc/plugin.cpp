@@ -272,6 +272,11 @@ static void b200_compute_node(b200_backend_ctx * ctx, struct ggml_tensor * node)
             B200_OK_OR_ABORT(b200_mul_mat((int) s0->type, s0->data, s0->ne, s0->nb, (const float *) s1->data, s1->ne, s1->nb,
                                           (float *) node->data, ctx->ws, ctx->ws_size, ctx->stream));
             break;
+        case GGML_OP_MUL_MAT_ID: {
+            const struct ggml_tensor * ids = node->src[2];
+            B200_OK_OR_ABORT(b200_mul_mat_id((int) s0->type, s0->data, s0->ne, s0->nb, (const float *) s1->data, s1->ne, s1->nb,
+                                             (const int32_t *) ids->data, ids->ne, ids->nb, (float *) node->data, ctx->ws, ctx->ws_size, ctx->stream));
+        } break;
         case GGML_OP_GET_ROWS: {
             // dst[:, i10, i11, i12] = dequant(src0[:, rows[i10, i11, i12], i11, i12])  (src/ggml-cpu/ops.cpp:5121-5165)
             const int out_type = node->type == GGML_TYPE_F32 ? B200_TYPE_F32 : B200_TYPE_F16;
@@ -403,7 +408,13 @@ static enum ggml_status b200_backend_graph_compute(ggml_backend_t backend, struc
                    const size_t w = b200_mul_mat_batch_workspace_size(r.data(), (int64_t) r.size());
                    if (w > need) need = w;
                },
-               [&](struct ggml_tensor * node) { n_work++; has_split = has_split || tensor_is_split(node->src[0]); });
+               [&](struct ggml_tensor * node) {
+                   n_work++; has_split = has_split || tensor_is_split(node->src[0]);
+                   if (node->op == GGML_OP_MUL_MAT_ID) {
+                       const size_t w = b200_mul_mat_id_workspace_size((int) node->src[0]->type, node->src[0]->ne, node->src[1]->ne);
+                       if (w > need) need = w;
+                   }
+               });
     if (need > ctx->ws_size) {
         CUDA_OK(cudaStreamSynchronize(ctx->stream));
         if (ctx->ws) CUDA_OK(cudaFree(ctx->ws));
@@ -581,6 +592,12 @@ static bool b200_dev_supports_op(ggml_backend_dev_t dev, const struct ggml_tenso
                    s0->nb[0] == ggml_type_size(s0->type) && s1->nb[0] == sizeof(float) && ggml_is_contiguous(op) &&
                    s0->ne[2] > 0 && s0->ne[3] > 0 && s1->ne[2] % s0->ne[2] == 0 && s1->ne[3] % s0->ne[3] == 0 &&
                    s1->ne[2] <= 65535 && s1->ne[3] <= 65535;
+        case GGML_OP_MUL_MAT_ID: {
+            const struct ggml_tensor * ids = op->src[2];
+            return s0 && s1 && ids && is_hot_quant(s0->type) && s1->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 && ids->type == GGML_TYPE_I32 &&
+                   s0->nb[0] == ggml_type_size(s0->type) && s1->nb[0] == sizeof(float) && ggml_is_contiguous(op) && s0->ne[3] == 1 && s1->ne[3] == 1 &&
+                   s1->ne[1] >= 1 && ids->ne[0] % s1->ne[1] == 0 && ids->ne[0] <= 65535 && ids->ne[1] <= 65535;
+        }
         case GGML_OP_GET_ROWS:
             return s0 && s1 && is_hot_quant(s0->type) && s1->type == GGML_TYPE_I32 && op->type == GGML_TYPE_F32 &&
                    s0->nb[0] == ggml_type_size(s0->type) && op->nb[0] == sizeof(float) && s1->ne[3] == 1;

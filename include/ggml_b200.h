@@ -155,6 +155,17 @@ B200_API int    b200_mul_mat_ex(int type_a, const void * a_dev, const int64_t ne
                                 float * dst_dev, void * workspace_dev, size_t workspace_bytes,
                                 uint32_t flags, void * stream);
 
+/* MUL_MAT_ID (mixture of experts): dst[m, e, t] = as[k, m, ids[e, t]] x b[k, e % ne_b[1], t] for slot e < ne_ids[0], token
+ * t < ne_ids[1] = ne_b[2]; as_dev: the experts' weights [k, m, n_as] (quantized rows), ids_dev: int32 [n_used, n_tokens] with
+ * byte strides nb_ids (may be a view).  replaces ggml_cuda_mul_mat_id (src/ggml-cuda/ggml-cuda.cu:2092-2233) and the ids
+ * path of mul_mat_vec_q (src/ggml-cuda/mmvq.cu:163-166, 556-569); the ids never leave the device.  An id outside
+ * [0, n_as) zero-fills its column and raises bit 0 of b200_device_error_flags. */
+B200_API size_t b200_mul_mat_id_workspace_size(int type_a, const int64_t ne_a[4], const int64_t ne_b[4]);
+B200_API int    b200_mul_mat_id(int type_a, const void * as_dev, const int64_t ne_a[4], const size_t nb_a[4],
+                                const float * b_dev, const int64_t ne_b[4], const size_t nb_b[4],
+                                const int32_t * ids_dev, const int64_t ne_ids[2], const size_t nb_ids[2],
+                                float * dst_dev, void * workspace_dev, size_t workspace_bytes, void * stream);
+
 /* A whole list of MUL_MAT nodes in one call, with the semantics of issuing them back to back on `stream` in list order
  * (a node may read what an earlier node of the list writes: decode mat-vecs of one format family then ride ONE
  * persistent launch, chained by per-node completion counters; other hazards cut the list into several launches).

@@ -47,7 +47,7 @@ def check_harness_output(rc, out, min_supported):
 
 
 @pytest.mark.parametrize("op,min_ok", [("GET_ROWS", 20), ("CPY", 10), ("MUL_MAT", 135),
-                                       ("RMS_NORM", 10), ("ADD", 30), ("MUL", 25), ("SWIGLU", 2), ("ROPE", 100), ("SOFT_MAX", 190)])
+                                       ("RMS_NORM", 10), ("ADD", 30), ("MUL", 25), ("SWIGLU", 2), ("ROPE", 100), ("SOFT_MAX", 190), ("MUL_MAT_ID", 100)])
 def test_reference_harness(op, min_ok):
     """test-backend-ops test -b B200_0 -o <op>: every case we claim must pass against ggml-cpu, and
     the number of claimed (not 'not supported') cases must be at least what the five formats imply."""
