@@ -336,7 +336,7 @@ constexpr size_t PEER_CTRL_BYTES = 16384;         // head of the symmetric regio
 static_assert(64 + 2 * BATCH_MAX_NODES * sizeof(unsigned) <= PEER_CTRL_FAMILY && 3 * PEER_CTRL_FAMILY <= PEER_CTRL_BYTES, "control block");
 
 static int run_list(const b200_mul_mat_node * nodes, int64_t count, void * workspace_dev, size_t workspace_bytes, void * stream,
-                    int32_t * plan, const b200_peer_group * pg = nullptr) {
+                    int32_t * plan, const b200_peer_group * pg = nullptr, long long remote_delta = 0) {
     if (count < 0 || (count > 0 && !nodes)) return B200_ERR_SHAPE;
     const bool dry = plan != nullptr;
     // row split (b200_mul_mat_batch_peers): the local copy of the symmetric region and the distances to the others
@@ -370,6 +370,7 @@ static int run_list(const b200_mul_mat_node * nodes, int64_t count, void * works
     auto reset_family = [&](int f) {
         fam_bb[f]->reset();
         if (pg) fam_bb[f]->set_peers((unsigned *) ((uint8_t *) pg->base[pg->rank] + f * PEER_CTRL_FAMILY), peer_delta, n_peers);
+        if (remote_delta) { fam_bb[f]->args.n_peers = 1; fam_bb[f]->args.peer_delta[0] = remote_delta; }    // one-way: no control block, no epochs
     };
     for (int f = 0; f < 3; f++) reset_family(f);
     cols_bb->reset();
@@ -436,7 +437,7 @@ static int run_list(const b200_mul_mat_node * nodes, int64_t count, void * works
         const bool to_cols = persistent && use_cols && flat && ncols >= 2 &&
                              cols_node_ok(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, nd.b_dev, (int64_t) nd.nb_b[1], ncols);
         if (!to_cols && !plain) {
-            if (pg && (uintptr_t) nd.dst_dev + 4 > sym_lo - PEER_CTRL_BYTES && (uintptr_t) nd.dst_dev < sym_hi) return B200_ERR_SHAPE;   // cannot scatter this shape
+            if (remote_delta || (pg && (uintptr_t) nd.dst_dev + 4 > sym_lo - PEER_CTRL_BYTES && (uintptr_t) nd.dst_dev < sym_hi)) return B200_ERR_SHAPE;   // cannot scatter this shape
             int rc = flush();
             if (rc) return rc;
             if (dry) { plan[3 * i] = group++; plan[3 * i + 1] = -1; plan[3 * i + 2] = 0; continue; }
@@ -449,7 +450,7 @@ static int run_list(const b200_mul_mat_node * nodes, int64_t count, void * works
         const uintptr_t d0 = (uintptr_t) nd.dst_dev, d1 = d0 + (size_t) m * ncols * 4;
         const int owner = to_cols ? 3 : batch_family(nd.type_a);
         // row split: a dst inside the symmetric region is scattered to every rank -- only the persistent list kernel does that
-        const bool scatter = pg && d0 >= sym_lo && d1 <= sym_hi;
+        const bool scatter = (pg && d0 >= sym_lo && d1 <= sym_hi) || remote_delta != 0;
         if (pg && !scatter && d1 > sym_lo - PEER_CTRL_BYTES && d0 < sym_hi) return B200_ERR_STRIDE;     // straddles the region / its control block
         if (scatter && (to_cols || ncols != 1)) return B200_ERR_SHAPE;
         // hazards against what is pending: inside the same persistent launch they become a dependency (dep = the
@@ -547,6 +548,16 @@ extern "C" int b200_mul_mat_batch_peers(const b200_mul_mat_node * nodes, int64_t
                                         void * workspace_dev, size_t workspace_bytes, void * stream) {
     if (!peers) return B200_ERR_SHAPE;
     return run_list(nodes, count, workspace_dev, workspace_bytes, stream, nullptr, peers);
+}
+
+// One-way variant for a single process driving several devices (the ggml split buffer): every node's finished rows are
+// ALSO stored at dst_dev + remote_delta_bytes, an address in another device's memory (peer access enabled by the caller).
+// No cross-device protocol: the remote rows are complete when this call's work on `stream` is (the caller orders the
+// reader with an event).  One-column decode nodes only (B200_ERR_SHAPE otherwise).
+extern "C" int b200_mul_mat_batch_remote(const b200_mul_mat_node * nodes, int64_t count, int64_t remote_delta_bytes,
+                                         void * workspace_dev, size_t workspace_bytes, void * stream) {
+    if (remote_delta_bytes == 0 || remote_delta_bytes % 4 != 0) return B200_ERR_STRIDE;
+    return run_list(nodes, count, workspace_dev, workspace_bytes, stream, nullptr, nullptr, (long long) remote_delta_bytes);
 }
 
 // How b200_mul_mat_batch would issue the list (host arithmetic only; no device needed).

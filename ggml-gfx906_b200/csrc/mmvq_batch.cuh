@@ -520,7 +520,8 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
         // ===================================================== activation producer: q8 activations of node i -> buffer i % NB
         pdl_wait();                                               // k_quantize_batch (and whatever made x) is done
         // arrivals a complete node has had: one per CTA, for a scattered node from every rank
-        const unsigned per_launch = (unsigned) (a.n_peers + 1) * gridDim.x;
+        // (one-way scatter, epoch == NULL: the other device only receives rows, it takes no part in the counters)
+        const unsigned per_launch = (unsigned) (a.epoch ? a.n_peers + 1 : 1) * gridDim.x;
         unsigned * const done_set = a.done + (a.epoch ? (ld_relaxed_sys(a.epoch) & 1u) * BATCH_MAX_NODES : 0u);
         node_cache cache;
         int slab_v = (int) blockIdx.x;
@@ -536,7 +537,7 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
                 if (lane == 0) {
                     // a scattered node is complete when every CTA of every rank has arrived, a local one when every CTA has
                     const bool dep_all = (a.nodes[nd.dep].qflags & BATCH_Q_SCATTER) != 0;
-                    batch_wait_counter(done_set + nd.dep, dep_all ? per_launch : gridDim.x, a.n_peers > 0);
+                    batch_wait_counter(done_set + nd.dep, dep_all ? per_launch : gridDim.x, a.epoch != nullptr);
                     BATCH_STAMP(i, 2);
                 }
                 __syncwarp();
@@ -560,7 +561,7 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
             __syncwarp();
         }
         // row split: the launch is over when the last scattered node is complete on every rank -- CTA 0 stays for it
-        if (a.n_peers > 0 && a.last_scatter >= 0 && blockIdx.x == 0) {
+        if (a.epoch && a.n_peers > 0 && a.last_scatter >= 0 && blockIdx.x == 0) {
             if (lane == 0) batch_wait_counter(done_set + a.last_scatter, per_launch, true);
             __syncwarp();
         }
@@ -614,7 +615,7 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
                 if (old == (unsigned) nwc - 1u) {
                     asm volatile("fence.acq_rel.cta;" ::: "memory");      // the other warps' arrivals, hence their stores, are observed ..
                     sdone[i & 7] = 0u;
-                    if (nd.qflags & BATCH_Q_SCATTER) {                     // .. and released (cumulatively) to every rank
+                    if ((nd.qflags & BATCH_Q_SCATTER) && a.epoch) {        // .. and released (cumulatively) to every rank
                         red_release_sys_add(nd.signal, 1u);
 #pragma unroll 1
                         for (int r = 0; r < a.n_peers; r++)

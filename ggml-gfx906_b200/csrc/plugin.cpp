@@ -81,6 +81,7 @@ static bool buft_is_b200_split(ggml_backend_buffer_type_t buft);
 // row-split weights (plugin_split.inc)
 static bool split_mul_mat_supported(const struct ggml_tensor * op);
 static void split_mul_mat(b200_backend_ctx * ctx, struct ggml_tensor * node);
+static void split_prepare(b200_backend_ctx * ctx, const struct ggml_tensor * node);
 static bool tensor_is_split(const struct ggml_tensor * t) { return t && t->buffer && buft_is_b200_split(t->buffer->buft); }
 
 // ================================================================= device buffer
@@ -200,7 +201,8 @@ static ggml_backend_buffer_t b200_host_buft_alloc_buffer(ggml_backend_buffer_typ
 // ================================================================= backend (one stream)
 struct graph_key_entry {
     int op; int type; const void * data;
-    const void * src_data[3]; int src_type[3];
+    const void * src_data[3]; int src_type[3]; int src_usage[3];       // usage: weights buffers change the launch flags baked into a capture
+    int32_t op_params[16];
     int64_t ne[4]; size_t nb[4];
     int64_t sne[3][4]; size_t snb[3][4];
     bool operator==(const graph_key_entry & o) const { return memcmp(this, &o, sizeof(*this)) == 0; }
@@ -212,10 +214,16 @@ struct b200_backend_ctx {
     cudaStream_t stream    = nullptr;
     void *       ws        = nullptr;
     size_t       ws_size   = 0;
-    // CUDA-graph replay of repeated graph_compute() calls
-    std::vector<graph_key_entry> last_key;
-    cudaGraphExec_t              exec = nullptr;
-    bool                         exec_valid = false;
+    // CUDA-graph replay of repeated graph_compute() calls: a small LRU of captured graphs, so that the alternating
+    // splits ggml_backend_sched hands a backend (one graph_compute per split) each find their own capture
+    struct cached_graph {
+        std::vector<graph_key_entry> key;
+        cudaGraphExec_t exec = nullptr;      // captured on the second sight of the key, replayed from the third
+        uint64_t last_use = 0;
+    };
+    static constexpr int GRAPH_CACHE = 8;
+    cached_graph                 cache[GRAPH_CACHE];
+    uint64_t                     use_clock = 0;
     bool                         graphs_enabled = true;
     uint64_t                     n_replays = 0, n_captures = 0, n_eager = 0;
     std::vector<b200_mul_mat_node> run;      // scratch: the current run of MUL_MAT nodes
@@ -228,7 +236,7 @@ static void b200_backend_free(ggml_backend_t backend) {
     b200_backend_ctx * ctx = (b200_backend_ctx *) backend->context;
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-    if (ctx->exec) cudaGraphExecDestroy(ctx->exec);
+    for (auto & c : ctx->cache) if (c.exec) cudaGraphExecDestroy(c.exec);
     if (ctx->ws) cudaFree(ctx->ws);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -382,11 +390,14 @@ static void make_key(struct ggml_cgraph * cgraph, std::vector<graph_key_entry> &
         graph_key_entry e;
         memset(&e, 0, sizeof(e));
         e.op = (int) t->op; e.type = (int) t->type; e.data = t->data;
+        memcpy(e.op_params, t->op_params, sizeof(e.op_params));
         for (int d = 0; d < 4; d++) { e.ne[d] = t->ne[d]; e.nb[d] = t->nb[d]; }
         for (int s = 0; s < 3; s++) {
             const struct ggml_tensor * src = t->src[s];
             if (!src) continue;
             e.src_data[s] = src->data; e.src_type[s] = (int) src->type;
+            const struct ggml_tensor * base = src->view_src ? src->view_src : src;
+            e.src_usage[s] = base->buffer ? (int) base->buffer->usage : 0;
             for (int d = 0; d < 4; d++) { e.sne[s][d] = src->ne[d]; e.snb[s][d] = src->nb[d]; }
         }
         key.push_back(e);
@@ -409,7 +420,8 @@ static enum ggml_status b200_backend_graph_compute(ggml_backend_t backend, struc
                    if (w > need) need = w;
                },
                [&](struct ggml_tensor * node) {
-                   n_work++; has_split = has_split || tensor_is_split(node->src[0]);
+                   n_work++;
+                   if (tensor_is_split(node->src[0])) { has_split = true; split_prepare(ctx, node); }
                    if (node->op == GGML_OP_MUL_MAT_ID) {
                        const size_t w = b200_mul_mat_id_workspace_size((int) node->src[0]->type, node->src[0]->ne, node->src[1]->ne);
                        if (w > need) need = w;
@@ -420,29 +432,38 @@ static enum ggml_status b200_backend_graph_compute(ggml_backend_t backend, struc
         if (ctx->ws) CUDA_OK(cudaFree(ctx->ws));
         ctx->ws_size = need + (need >> 2) + (1u << 20);
         CUDA_OK(cudaMalloc(&ctx->ws, ctx->ws_size));
-        ctx->exec_valid = false;     // captured launches hold the old pointer
-        ctx->last_key.clear();
+        for (auto & c : ctx->cache) {        // captured launches hold the old pointer
+            if (c.exec) { cudaGraphExecDestroy(c.exec); c.exec = nullptr; }
+            c.key.clear();
+        }
     }
 
     // Replay policy: a graph seen twice in a row (same ops, shapes, strides, data pointers) is captured
     // on its second appearance and replayed from the third on.  Single-node graphs (test-backend-ops)
     // never pay for a capture.
-    bool use_graph = false, capture = false;
+    bool capture = false;
+    b200_backend_ctx::cached_graph * slot = nullptr;
     if (ctx->graphs_enabled && n_work >= 4 && !has_split) {
-        std::vector<graph_key_entry> key;
+        static thread_local std::vector<graph_key_entry> key;
         make_key(cgraph, key);
-        if (key == ctx->last_key) {
-            use_graph = true;
-            capture = !ctx->exec_valid;
-        } else {
-            ctx->last_key.swap(key);
-            ctx->exec_valid = false;
+        b200_backend_ctx::cached_graph * lru = &ctx->cache[0];
+        for (auto & c : ctx->cache) {
+            if (!c.key.empty() && c.key == key) { slot = &c; break; }
+            if (c.last_use < lru->last_use) lru = &c;
         }
-    }
-    if (use_graph && !capture) {
-        CUDA_OK(cudaGraphLaunch(ctx->exec, ctx->stream));
-        ctx->n_replays++;
-        return GGML_STATUS_SUCCESS;
+        if (slot) {
+            slot->last_use = ++ctx->use_clock;
+            if (slot->exec) {
+                CUDA_OK(cudaGraphLaunch(slot->exec, ctx->stream));
+                ctx->n_replays++;
+                return GGML_STATUS_SUCCESS;
+            }
+            capture = true;                  // second sight: capture now
+        } else {                             // first sight: remember the key in the least recently used slot, run eagerly
+            if (lru->exec) { cudaGraphExecDestroy(lru->exec); lru->exec = nullptr; }
+            lru->key = key;
+            lru->last_use = ++ctx->use_clock;
+        }
     }
     if (capture) CUDA_OK(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeRelaxed));
     walk_graph(cgraph, run,
@@ -453,12 +474,10 @@ static enum ggml_status b200_backend_graph_compute(ggml_backend_t backend, struc
     if (capture) {
         cudaGraph_t graph = nullptr;
         CUDA_OK(cudaStreamEndCapture(ctx->stream, &graph));
-        if (ctx->exec) { cudaGraphExecDestroy(ctx->exec); ctx->exec = nullptr; }
-        CUDA_OK(cudaGraphInstantiate(&ctx->exec, graph, 0));
+        CUDA_OK(cudaGraphInstantiate(&slot->exec, graph, 0));
         CUDA_OK(cudaGraphDestroy(graph));
-        ctx->exec_valid = true;
         ctx->n_captures++;
-        CUDA_OK(cudaGraphLaunch(ctx->exec, ctx->stream));
+        CUDA_OK(cudaGraphLaunch(slot->exec, ctx->stream));
     } else {
         ctx->n_eager++;
     }

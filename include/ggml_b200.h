@@ -215,6 +215,14 @@ B200_API size_t b200_peer_ctrl_bytes(void);
 B200_API int    b200_mul_mat_batch_peers(const b200_mul_mat_node * nodes, int64_t count, const b200_peer_group * peers,
                                          void * workspace_dev, size_t workspace_bytes, void * stream);
 
+/* One-way variant for ONE process driving several devices (ggml's split buffer, src/ggml-cuda/ggml-cuda.cu:1700-1740): every
+ * node's finished rows are ALSO stored at dst_dev + remote_delta_bytes, an address in another device's memory (peer
+ * access enabled by the caller) -- the row block lands in the main device's dst from inside the launch instead of by a
+ * cudaMemcpy2DAsync after it.  No cross-device protocol: the remote rows are complete when this call's work on `stream`
+ * is (the caller orders the reader with an event).  One-column decode nodes only. */
+B200_API int    b200_mul_mat_batch_remote(const b200_mul_mat_node * nodes, int64_t count, int64_t remote_delta_bytes,
+                                          void * workspace_dev, size_t workspace_bytes, void * stream);
+
 /* How the list would be issued, without touching a device: plan[3 i] = launch group of node i (nodes of a group share
  * one launch pair per format family), plan[3 i + 1] = list index of the node it waits for INSIDE its launch (-1: none),
  * plan[3 i + 2] = route (0: per-node call, 1: persistent list kernel, 2: 2..8-column MMA list kernel). */
