@@ -212,7 +212,7 @@ extern "C" int b200_mul_mat_q(int type, const void * w_dev, size_t w_row_stride_
     a.w = (const uint8_t *) w_dev; a.w_row_stride = (int64_t) w_row_stride_bytes; a.m = m; a.k = k; a.n = n;
     a.dst = dst_dev; a.dst_col_stride = (int64_t) (dst_col_stride_bytes / 4);
     a.nblk = (int) (k / type_qk(type)); a.raw_pitch = 0;
-    const bool aligned0 = type != T_Q6_K && ((uintptr_t) w_dev % 16 == 0) && (w_row_stride_bytes % 16 == 0) &&
+    const bool aligned0 = ((uintptr_t) w_dev % 16 == 0) && (w_row_stride_bytes % 16 == 0) &&
                          !b200_option(B200_OPT_MMQ_FORCE_UNALIGNED);
     // aligned rows: a second descriptor over the raw weight bytes as 32-bit words, dims {row words, m}, box {slab words, 128}
     bool aligned = aligned0;
@@ -220,7 +220,8 @@ extern "C" int b200_mul_mat_q(int type, const void * w_dev, size_t w_row_stride_
     memset(&tmap_w, 0, sizeof(tmap_w));
     if (aligned && b200_row_bytes(type, k) % 4 != 0) aligned = false;      // the descriptor counts the row in 32-bit words
     if (aligned) {
-        const int slab_words = (type == T_Q8_0 ? 272 : (type == T_Q5_K ? 176 : 144)) / 4;
+        // (Q6_K: 60-word box over 210-byte blocks, the expander removes the 2-byte skew of odd slabs: slab_tma<> in mmq_tc.cuh)
+        const int slab_words = type == T_Q6_K ? 60 : (type == T_Q8_0 ? 272 : (type == T_Q5_K ? 176 : 144)) / 4;
         const cuuint64_t wdim[2]    = { (cuuint64_t) (b200_row_bytes(type, k) / 4), (cuuint64_t) m };
         const cuuint64_t wstride[1] = { (cuuint64_t) w_row_stride_bytes };
         const cuuint32_t wbox[2]    = { (cuuint32_t) slab_words, (cuuint32_t) MMQ_BM };
@@ -234,7 +235,7 @@ extern "C" int b200_mul_mat_q(int type, const void * w_dev, size_t w_row_stride_
         case T_Q8_0: return launch_mmq_bn<T_Q8_0>(a, tmap, tmap_w, bn, aligned, st);
         case T_Q4_K: return launch_mmq_bn<T_Q4_K>(a, tmap, tmap_w, bn, aligned, st);
         case T_Q5_K: return launch_mmq_bn<T_Q5_K>(a, tmap, tmap_w, bn, aligned, st);
-        case T_Q6_K: return launch_mmq_bn<T_Q6_K>(a, tmap, tmap_w, bn, false, st);
+        case T_Q6_K: return launch_mmq_bn<T_Q6_K>(a, tmap, tmap_w, bn, aligned, st);
         default: return B200_ERR_TYPE;
     }
 }

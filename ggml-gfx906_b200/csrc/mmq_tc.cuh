@@ -115,8 +115,28 @@ template <> struct slab<T_Q8_0> { static constexpr int bytes = 272, pitch = 272,
 template <> struct slab<T_Q4_K> { static constexpr int bytes = 144, pitch = 144, pitch_unaligned = 176; };
 template <> struct slab<T_Q5_K> { static constexpr int bytes = 176, pitch = 176, pitch_unaligned = 208; };
 template <> struct slab<T_Q6_K> { static constexpr int bytes = 210, pitch = 240, pitch_unaligned = 240; };
+// 2-D TMA tile of one raw slab (rows 16-byte aligned in memory): box width in 32-bit words and first word of slab s.
+// A TMA box must start on a 16-byte boundary of the row.  Q6_K blocks are 210 bytes: slab s starts (210 s) % 16 = 0, 2, ..
+// 14 bytes past one; the box is 60 words (240 bytes >= 14 + 210, an odd multiple of 16: conflict-free 16-byte shared
+// loads) and the expander reads its words `skew` bytes further in (word offset as a template parameter, the remaining
+// 0 / 2 bytes by funnel shift).
+template <int T> struct slab_tma {
+    static constexpr int box_words = T == T_Q6_K ? 60 : slab<T>::bytes / 4;
+    static __host__ __device__ __forceinline__ int word0(int s) { return T == T_Q6_K ? ((210 * s) >> 4) << 2 : s * (slab<T>::bytes / 4); }
+    static __host__ __device__ __forceinline__ int skew(int s)  { return T == T_Q6_K ? (210 * s) & 15 : 0; }
+};
 
 // words [W0, W0+N) of the slab via 16-byte shared loads (conflict-free: PITCH/16 is odd)
+// the same for data that starts `sh` bits (0 or 16) into word W0: one more word, funnel shifts
+template <int W0, int N>
+__device__ __forceinline__ void slab_words(const uint8_t * s, uint32_t (&w)[N]);
+template <int W0, int N>
+__device__ __forceinline__ void slab_words_sh(const uint8_t * s, uint32_t sh, uint32_t (&w)[N]) {
+    uint32_t t[N + 1];
+    slab_words<W0, N + 1>(s, t);
+#pragma unroll
+    for (int i = 0; i < N; i++) w[i] = __funnelshift_r(t[i], t[i + 1], sh);
+}
 template <int W0, int N>
 __device__ __forceinline__ void slab_words(const uint8_t * s, uint32_t (&w)[N]) {
     constexpr int C0 = W0 / 4, C1 = (W0 + N + 3) / 4;
@@ -186,17 +206,36 @@ template <> struct expander<T_Q5_K> : expander_k45<true> {};
 template <> struct expander<T_Q6_K> {
     uint32_t sc[4];       // 16 int8 scales
     float d;
-    __device__ __forceinline__ void begin_slab(const uint8_t * s, int /*nvalid*/) {
+    int wo = 0;           // the slab starts 4 wo + sh / 8 bytes into its slot (2-D TMA tiles of 210-byte blocks: slab_tma<>)
+    uint32_t sh = 0;
+    __device__ __forceinline__ void set_skew(int sk) { wo = sk >> 2; sh = (uint32_t) (sk & 3) * 8u; }
+    template <int WO> __device__ __forceinline__ void begin_slab_wo(const uint8_t * s) {
         uint32_t t[5];
-        slab_words<48, 5>(s, t);          // bytes 192..211: scales[16], d
+        slab_words_sh<48 + WO, 5>(s, sh, t);        // bytes 192..211: scales[16], d
         sc[0] = t[0]; sc[1] = t[1]; sc[2] = t[2]; sc[3] = t[3];
         d = f16_bits_to_f32(t[4]);
     }
+    __device__ __forceinline__ void begin_slab(const uint8_t * s, int /*nvalid*/) {
+        switch (wo) {                               // uniform over the CTA
+            case 0: begin_slab_wo<0>(s); break;
+            case 1: begin_slab_wo<1>(s); break;
+            case 2: begin_slab_wo<2>(s); break;
+            default: begin_slab_wo<3>(s); break;
+        }
+    }
     template <int SUB> __device__ __forceinline__ void expand64(const uint8_t * s, uint8_t * a_row, int row7, int half) {
+        switch (wo) {
+            case 0: expand64_wo<SUB, 0>(s, a_row, row7, half); break;
+            case 1: expand64_wo<SUB, 1>(s, a_row, row7, half); break;
+            case 2: expand64_wo<SUB, 2>(s, a_row, row7, half); break;
+            default: expand64_wo<SUB, 3>(s, a_row, row7, half); break;
+        }
+    }
+    template <int SUB, int WO> __device__ __forceinline__ void expand64_wo(const uint8_t * s, uint8_t * a_row, int row7, int half) {
         constexpr int h = SUB >> 1, p = SUB & 1;
         uint32_t ql[16], qh[8];
-        slab_words<16 * h, 16>(s, ql);            // ql[64h .. 64h+64)
-        slab_words<32 + 8 * h, 8>(s, qh);         // qh[32h .. 32h+32)
+        slab_words_sh<16 * h + WO, 16>(s, sh, ql);           // ql[64h .. 64h+64)
+        slab_words_sh<32 + 8 * h + WO, 8>(s, sh, qh);        // qh[32h .. 32h+32)
 #pragma unroll
         for (int c = 0; c < 8; c++) {
             if ((c >> 2) != half) continue;
@@ -438,6 +477,7 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b, const __g
                 __syncwarp();
             }
             if (!ALIGNED) named_bar_sync(1 + pw, 64);        // the pair's other warp reads the realigned rows
+            if constexpr (T == T_Q6_K) ex.set_skew(ALIGNED ? slab_tma<T>::skew(s) : 0);
             ex.begin_slab(slab_ptr, slab_valid_blocks(s));
 #pragma unroll
             for (int sub = 0; sub < 4; sub++) {
@@ -493,8 +533,8 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b, const __g
                     while (next_slab < nslab && next_slab <= kt / 4 + RS - 1) {
                         const int r = next_slab % RS;
                         if (next_slab >= RS) mbar_wait(&raw_empty[r], (uint32_t) (((next_slab / RS) - 1) & 1));
-                        mbar_arrive_expect_tx(&raw_full[r * 4], (uint32_t) (MMQ_BM * slab<T>::bytes));
-                        tma_load_2d(raw + (size_t) r * MMQ_BM * a.raw_pitch, &tmap_w, next_slab * (slab<T>::bytes / 4), (int) m0, &raw_full[r * 4]);
+                        mbar_arrive_expect_tx(&raw_full[r * 4], (uint32_t) (MMQ_BM * slab_tma<T>::box_words * 4));
+                        tma_load_2d(raw + (size_t) r * MMQ_BM * a.raw_pitch, &tmap_w, slab_tma<T>::word0(next_slab), (int) m0, &raw_full[r * 4]);
                         next_slab++;
                     }
                 }
