@@ -562,7 +562,7 @@ class PluginStep:
     Pinned host memory comes from ggml_backend_b200_host_buffer_type.  chain=True builds the decoder-pass dependency
     structure instead (node outputs feed the next nodes directly; host traffic = first activation in, last output out)."""
 
-    def __init__(self, stack, chain=False):
+    def __init__(self, stack, chain=False, chunks=1):
         import ctypes as C
         import numpy as np
         sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -583,6 +583,10 @@ class PluginStep:
         b.ggml_backend_buft_alloc_buffer.restype = vp; b.ggml_backend_buft_alloc_buffer.argtypes = [vp, sz]
         b.ggml_backend_buffer_get_base.restype = vp;   b.ggml_backend_buffer_get_base.argtypes = [vp]
         b.ggml_backend_buffer_set_usage.restype = None; b.ggml_backend_buffer_set_usage.argtypes = [vp, C.c_int]
+        b.ggml_backend_event_new.restype = vp;         b.ggml_backend_event_new.argtypes = [vp]
+        b.ggml_backend_event_free.restype = None;      b.ggml_backend_event_free.argtypes = [vp]
+        b.ggml_backend_event_record.restype = None;    b.ggml_backend_event_record.argtypes = [vp, vp]
+        b.ggml_backend_event_wait.restype = None;      b.ggml_backend_event_wait.argtypes = [vp, vp]
         host.load_plugin(plugin)
         dev = host.device_by_name("B200_0")
         if not dev:
@@ -630,12 +634,43 @@ class PluginStep:
             ys[f"y{i}"] = y
             yoff.append(pos)
             pos += (mt.m + 31) // 32 * 32
-        self.graph = b.ggml_new_graph_custom(self.ctx_g, max(2048, 2 * n + 64), False)
+        # `chunks` > 1 (independent list only): the step as `chunks` sub-graphs over consecutive node ranges, so that a program
+        # with three backend instances on the device (= three streams) can overlap the host copies of one range with the
+        # compute of another, ordered by ggml_backend_event_record / _wait -- what ggml_backend_sched does between splits
+        if chain:
+            chunks = 1
+        edges = [0, n]
+        if chunks > 1:
+            total = sum(int(wt.numel()) for wt in stack.weights)
+            edge = 0.1
+            cuts = [edge + (1.0 - 2.0 * edge) * j / (chunks - 2) for j in range(chunks - 1)] if chunks >= 4 else [j / chunks for j in range(1, chunks)]
+            edges, acc, nxt = [0], 0, 0
+            for i, wt in enumerate(stack.weights):
+                acc += int(wt.numel())
+                while nxt < len(cuts) and acc >= total * cuts[nxt]:
+                    edges.append(i + 1); nxt += 1
+            edges = sorted(set(edges + [n]))
+        self.ranges, self.graphs = [], []
         last = None
-        for idx, (i, _, _) in enumerate(plan):
-            b.ggml_build_forward_expand(self.graph, ys[f"y{i}"])
-            last = i
-        self.chain, self.yoff, self.ys, self.last = chain, yoff, ys, last
+        for a_, b_ in zip(edges[:-1], edges[1:]):
+            ctx_c = host.new_context(n_tensors=8, graph_nodes=2 * (b_ - a_) + 64)
+            g = b.ggml_new_graph_custom(ctx_c, max(256, 2 * (b_ - a_) + 64), False)
+            for idx in range(a_, b_):
+                b.ggml_build_forward_expand(g, ys[f"y{plan[idx][0]}"])
+                last = plan[idx][0]
+            x0 = 0 if chain else 4 * stack.x_off[a_]
+            x1 = 4 * xlen if (chain or b_ == n) else 4 * stack.x_off[b_]
+            y0 = 4 * yoff[a_]
+            y1 = 4 * ylen if b_ == n else 4 * yoff[b_]
+            self.graphs.append((ctx_c, g))
+            self.ranges.append((x0, x1, y0, y1))
+        self.graph = self.graphs[0][1]
+        self.chain, self.yoff, self.ys, self.last, self.chunks = chain, yoff, ys, last, len(self.graphs)
+        self.be_in = self.be_out = None
+        if self.chunks > 1:
+            self.be_in, self.be_out = host.init_device(dev), host.init_device(dev)
+            self.ev_in = [b.ggml_backend_event_new(dev) for _ in self.graphs]
+            self.ev_out = [b.ggml_backend_event_new(dev) for _ in self.graphs]
         # pinned host staging from the plugin's host buffer type
         buft = plug.ggml_backend_b200_host_buffer_type()
         self.h_bytes_in = 4 * xlen
@@ -650,6 +685,20 @@ class PluginStep:
 
     def step(self):
         b = self.host.base
+        if self.chunks > 1:
+            for c, ((x0, x1, y0, y1), (_, g)) in enumerate(zip(self.ranges, self.graphs)):
+                b.ggml_backend_tensor_set_async(self.be_in, self.X, self.h_in + x0, x0, x1 - x0)
+                b.ggml_backend_event_record(self.ev_in[c], self.be_in)
+                b.ggml_backend_event_wait(self.backend, self.ev_in[c])
+                if b.ggml_backend_graph_compute_async(self.backend, g) != 0:
+                    raise RuntimeError("graph_compute")
+                b.ggml_backend_event_record(self.ev_out[c], self.backend)
+                b.ggml_backend_event_wait(self.be_out, self.ev_out[c])
+                b.ggml_backend_tensor_get_async(self.be_out, self.Y, self.h_out + y0, y0, y1 - y0)
+            b.ggml_backend_synchronize(self.be_out)
+            b.ggml_backend_synchronize(self.backend)
+            b.ggml_backend_synchronize(self.be_in)
+            return
         b.ggml_backend_tensor_set_async(self.backend, self.X, self.h_in, 0, self.h_bytes_in)
         st = b.ggml_backend_graph_compute_async(self.backend, self.graph)
         if st != 0:
@@ -678,7 +727,13 @@ class PluginStep:
         for buf in (self.buf_io, self.buf_w, self.hbuf):
             if buf:
                 b.ggml_backend_buffer_free(buf)
+        for ctx_c, _ in self.graphs:
+            b.ggml_free(ctx_c)
         b.ggml_free(self.ctx_g); b.ggml_free(self.ctx_io); b.ggml_free(self.ctx_w)
+        if self.chunks > 1:
+            for ev in self.ev_in + self.ev_out:
+                b.ggml_backend_event_free(ev)
+            b.ggml_backend_free(self.be_in); b.ggml_backend_free(self.be_out)
         b.ggml_backend_free(self.backend)
 
 
@@ -946,7 +1001,7 @@ def main():
     e2e_path, plug = None, None
     if world == 1:
         try:
-            plug = PluginStep(stack)
+            plug = PluginStep(stack, chunks=env_int("BENCH_E2E_CHUNKS", 4))
             sec_e2e = plug.timed(args.steps, args.warmup)
             out = plug.outputs()
             ref_out = stack.y_dev[stack.h0_len:].cpu().numpy()
@@ -954,7 +1009,9 @@ def main():
                 raise RuntimeError("plugin outputs differ from the C-ABI outputs")
             e2e_path = ("pinned host (ggml_backend_b200_host_buffer_type) -> ggml_backend_tensor_set_async -> ggml_backend_graph_compute_async "
                         "on B200_0 (plugin: b200_mul_mat_batch, CUDA-graph replay) -> ggml_backend_tensor_get_async -> ggml_backend_synchronize; "
-                        "outputs bit-identical to the C-ABI step; host wall clock")
+                        + (f"the step as {plug.chunks} sub-graphs on three backend instances of the device (copy-in / compute / copy-out streams "
+                           "ordered by ggml_backend_event_record / _wait), so host copies overlap compute; " if plug.chunks > 1 else "")
+                        + "outputs bit-identical to the C-ABI step; host wall clock")
             h2d, d2h = plug.h_bytes_in, plug.h_bytes_out
         except Exception as e:                   # noqa: BLE001
             sys.stderr.write(f"[bench] plugin e2e leg unavailable ({str(e)[:300]}); timing the C-ABI e2e\n")
