@@ -100,6 +100,10 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
     lib.b200_quantize_acts.restype = i32;        lib.b200_quantize_acts.argtypes = [vp, sz, i64, i64, vp, vp]
     lib.b200_mul_mat_vec_q.restype = i32
     lib.b200_mul_mat_vec_q.argtypes = [i32, vp, sz, i64, i64, vp, i64, vp, sz, vp]
+    lib.b200_static_scratch_bytes.restype = sz
+    lib.b200_static_scratch_bytes.argtypes = []
+    lib.b200_mul_mat_vec_static.restype = i32
+    lib.b200_mul_mat_vec_static.argtypes = [i32, vp, sz, i64, i64, vp, sz, i64, vp, sz, vp]
     lib.b200_mul_mat_q_workspace_size.restype = sz
     lib.b200_mul_mat_q_workspace_size.argtypes = [i64, i64, i64]
     lib.b200_mul_mat_q.restype = i32
@@ -288,6 +292,14 @@ class Kernels:
                                                 scratch.data_ptr(), n, out.data_ptr(), out.stride(0) * 4, self._stream()),
                     "mul_mat_vec_q")
         return out
+
+    def mul_mat_vec_static(self, t: str, w, m: int, k: int, x, out, w_row_stride: Optional[int] = None) -> int:
+        """b200_mul_mat_vec_static: quantize + matvec on the library's static device scratch; allocates nothing (the
+        caller passes `out` [n, m] f32).  Returns the C return code (0, or B200_ERR_TOO_LARGE = 7 ..) unchecked."""
+        n = x.shape[0]
+        return int(self.lib.b200_mul_mat_vec_static(TYPE_ID[t], w.data_ptr(), w_row_stride or row_bytes(t, k), m, k,
+                                                    x.data_ptr(), x.stride(0) * 4, n, out.data_ptr(), out.stride(0) * 4,
+                                                    self._stream()))
 
     def mul_mat_q(self, t: str, w, m: int, k: int, x, out=None, w_row_stride: Optional[int] = None):
         torch = self.torch

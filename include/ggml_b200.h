@@ -50,6 +50,7 @@ enum b200_error {
     B200_ERR_WORKSPACE   = 4, /* workspace too small / NULL */
     B200_ERR_NO_DEVICE   = 5, /* no sm_100 device visible */
     B200_ERR_INDEX       = 6, /* a GET_ROWS index outside the table (reported by b200_device_error_flags) */
+    B200_ERR_TOO_LARGE   = 7, /* the problem needs more than the fixed static scratch (b200_mul_mat_vec_static) */
     B200_NOT_APPLICABLE  = 1000, /* internal: the fast path declined; never returned by the entry points below */
 };
 
@@ -239,6 +240,21 @@ B200_API int    b200_quantize_acts(const float * x_dev, size_t x_row_stride_byte
 B200_API int    b200_mul_mat_vec_q(int type, const void * w_dev, size_t w_row_stride_bytes, int64_t m, int64_t k,
                                    const void * acts_scratch_dev, int64_t n,
                                    float * dst_dev, size_t dst_col_stride_bytes, void * stream);
+
+/* b200_mul_mat_vec_static: b200_quantize_acts + b200_mul_mat_vec_q in one call that allocates nothing — for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  It has
+ * no counterpart in the reference.  The activation scratch is a
+ * static __device__ array of B200_STATIC_SCRATCH_BYTES that every GPU loading the library holds until exit; a
+ * problem with b200_acts_scratch_bytes(k, n) above that returns B200_ERR_TOO_LARGE.  x_dev: f32 [n][k] (rows
+ * x_row_stride_bytes apart), n <= B200_MMVQ_MAX_N, dst as for b200_mul_mat_vec_q; results are identical to the
+ * two-call sequence.  All calls on a device share the array: calls whose GPU work may overlap (different streams or
+ * host threads) race and must be serialized by the caller. */
+#define B200_STATIC_SCRATCH_BYTES (1 << 20)
+B200_API size_t b200_static_scratch_bytes(void);
+B200_API int    b200_mul_mat_vec_static(int type, const void * w_dev, size_t w_row_stride_bytes, int64_t m, int64_t k,
+                                        const float * x_dev, size_t x_row_stride_bytes, int64_t n,
+                                        float * dst_dev, size_t dst_col_stride_bytes, void * stream);
+
 B200_API size_t b200_mul_mat_q_workspace_size(int64_t m, int64_t k, int64_t n);
 B200_API int    b200_mul_mat_q(int type, const void * w_dev, size_t w_row_stride_bytes, int64_t m, int64_t k,
                                const float * x_dev, size_t x_row_stride_bytes, int64_t n,
