@@ -105,6 +105,22 @@ struct batch_args {
 #else
 #define BATCH_STAMP(node, slot) do { } while (0)
 #endif
+#ifdef B200_TUNING
+// cycle accumulators of one thread (row 95 - which of the stamp table, 8 per CTA): T0 = clock64() .. ACC(var) adds the cycles since
+#define BATCH_ACC_DECL(var) long long var = 0
+#define BATCH_ACC_T0(t) const long long t = clock64()
+#define BATCH_ACC_ADD(var, t) var += clock64() - t
+#define BATCH_ACC_OUT(row, slot, var) do { if (a.dbg) a.dbg[((size_t) (row) * gridDim.x + blockIdx.x) * 8 + (slot)] = (unsigned long long) (var); } while (0)
+#define BATCH_TUN_PARAMS , long long & acc_full, long long & acc_bar
+#define BATCH_TUN_ARGS , acc_full, acc_bar
+#else
+#define BATCH_TUN_PARAMS
+#define BATCH_TUN_ARGS
+#define BATCH_ACC_DECL(var) do { } while (0)
+#define BATCH_ACC_T0(t) do { } while (0)
+#define BATCH_ACC_ADD(var, t) do { } while (0)
+#define BATCH_ACC_OUT(row, slot, var) do { } while (0)
+#endif
 
 // gpu-scope release / acquire on the completion counters
 __device__ __forceinline__ void red_release_gpu_add(unsigned * p, unsigned v) {
@@ -317,7 +333,7 @@ template <int T>
 __device__ __forceinline__ void batch_consume(const batch_args & a, const cnode & nd, acts128 & acts, const int cw, const int lane,
                                               int & st_s, uint32_t & st_ph, int & cc, int & git,
                                               const uint8_t * actbuf, const uint32_t acts_free, const uint32_t full, const uint32_t empty,
-                                              float * part, const uint8_t * slots, const int S, const int slot_stride) {
+                                              float * part, const uint8_t * slots, const int S, const int slot_stride BATCH_TUN_PARAMS) {
     using IT = hitem<T>;
     const int W = nd.W, G = nd.G, R = nd.R;
     const int r_begin = nd.r_begin, nrows = nd.nrows, pitch = nd.pitch;
@@ -359,7 +375,9 @@ __device__ __forceinline__ void batch_consume(const batch_args & a, const cnode 
     int cmod = cc % G;                                    // owner group of the next chunk
     for (int lb = 0; lb < nbatch; lb++) {
         const int s = st_s;
+        { BATCH_ACC_T0(t_w);
         mbar_wait_a(full + 8 * s, st_ph);                 // every lane polls (a single polling lane sleeps out its time slice)
+        BATCH_ACC_ADD(acc_full, t_w); }
         if (++st_s == S) { st_s = 0; st_ph ^= 1u; }
         const int rows_here = (nrows - lb * R < R) ? (nrows - lb * R) : R;
         const int nchunks = (rows_here + FUSED_RB - 1) / FUSED_RB;
@@ -419,7 +437,9 @@ __device__ __forceinline__ void batch_consume(const batch_args & a, const cnode 
             // the W warps of the group meet; warp 0 of the group adds the partials in fixed order.  pb
             // alternates per working stage of the group: the buffer written two working stages later is
             // only touched after the barrier in between, which warp 0 reaches after these reads.
+            { BATCH_ACC_T0(t_w);
             named_bar_sync(1 + g, W * 32);
+            BATCH_ACC_ADD(acc_bar, t_w); }
             if (wg == 0) {
                 for (int j = lane; ; j += 32) {
                     const int c = c_first + (j / FUSED_RB) * G;
@@ -468,6 +488,7 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
     }
     __syncthreads();
     pdl_launch();
+    if (tid == 0) BATCH_STAMP(0, 6);
 
     if (warp == 0) {
         // ===================================================== weight producer: slabs of every node -> stage ring
@@ -477,6 +498,7 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
         bool lap0 = true;
         int slab_v = (int) blockIdx.x;
         node_cache cache;
+        BATCH_ACC_DECL(acc_empty); BATCH_ACC_T0(t_begin);
         for (int i = 0; i < a.count; i++) {
             const node_r nd = cache.get(a, i, lane);
             int r_begin, nrows;
@@ -485,7 +507,9 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
             const int nbatch = (nrows + R - 1) / R;
             const int row_pitch = batch_row_pitch(nd.row_bytes);
             for (int lb = 0; lb < nbatch; lb++) {
+                { BATCH_ACC_T0(t_w);
                 if (!lap0) mbar_wait(&empty[s], ph);              // the whole warp polls
+                BATCH_ACC_ADD(acc_empty, t_w); }
                 if (lane == 0) {
                     const int rows_here = (nrows - lb * R < R) ? (nrows - lb * R) : R;
                     const uint8_t * src = nd.w + (int64_t) (r_begin + lb * R) * nd.row_stride;
@@ -513,6 +537,7 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
                 if (++s == S) { s = 0; ph ^= 1u; lap0 = false; }
             }
         }
+        if (lane == 0) { BATCH_STAMP(0, 7); BATCH_ACC_DECL(acc_total); BATCH_ACC_ADD(acc_total, t_begin); BATCH_ACC_OUT(95, 0, acc_empty); BATCH_ACC_OUT(95, 1, acc_total); }
         return;
     }
 
@@ -575,9 +600,12 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
     const uint32_t full_a = smem_u32(full), empty_a = smem_u32(empty), ready_a = smem_u32(acts_ready), free_a = smem_u32(acts_free);
     const int slot_stride = a.slot_stride, count = a.count, acts_stride = a.acts_stride, nwc = a.nwc;
     acts128 acts = {};                                    // survives from node to node (BATCH_Q_SAME)
+    BATCH_ACC_DECL(acc_full); BATCH_ACC_DECL(acc_bar); BATCH_ACC_DECL(acc_ready); BATCH_ACC_DECL(acc_layout); BATCH_ACC_T0(t_begin);
     for (int i = 0, u = 0, uph = 0; i < count; i++) {
         uint8_t * buf = actbufs + u * acts_stride;
+        { BATCH_ACC_T0(t_w);
         mbar_wait_a(ready_a + 8 * u, (uint32_t) uph);
+        BATCH_ACC_ADD(acc_ready, t_w); }
         const cnode nd = *reinterpret_cast<const cnode *>(buf);
         if (cw == 0 && lane == 0) BATCH_STAMP(i, 0);
         if (nd.qflags & BATCH_Q_INK) {
@@ -594,16 +622,16 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
         // parity (git) simply carry on across nodes; a different W needs every consumer warp to be past its
         // last reduction before the new layout is written
         if (nd.W > 1) {
-            if (layout_w != 0 && layout_w != nd.W) { named_bar_sync(BATCH_NWC + 1, a.nwc * 32); git = 0; }
+            if (layout_w != 0 && layout_w != nd.W) { BATCH_ACC_T0(t_w); named_bar_sync(BATCH_NWC + 1, a.nwc * 32); git = 0; BATCH_ACC_ADD(acc_layout, t_w); }
             layout_w = nd.W;
         }
         if (FAM == 2) {
-            if (nd.type == T_Q8_0) batch_consume<T_Q8_0>(a, nd, acts, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
-            else                   batch_consume<T_Q4_0>(a, nd, acts, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
+            if (nd.type == T_Q8_0) batch_consume<T_Q8_0>(a, nd, acts, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride BATCH_TUN_ARGS);
+            else                   batch_consume<T_Q4_0>(a, nd, acts, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride BATCH_TUN_ARGS);
         }
-        else if (FAM == 1) { acts128 a6; batch_consume<T_Q6_K>(a, nd, a6, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride); }
-        else if (nd.type == T_Q5_K) batch_consume<T_Q5_K>(a, nd, acts, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
-        else                   batch_consume<T_Q4_K>(a, nd, acts, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride);
+        else if (FAM == 1) { acts128 a6; batch_consume<T_Q6_K>(a, nd, a6, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride BATCH_TUN_ARGS); }
+        else if (nd.type == T_Q5_K) batch_consume<T_Q5_K>(a, nd, acts, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride BATCH_TUN_ARGS);
+        else                   batch_consume<T_Q4_K>(a, nd, acts, cw, lane, st_s, st_ph, cc, git, buf + BATCH_AHDR, free_a + 8 * u, full_a, empty_a, part, slots, S, slot_stride BATCH_TUN_ARGS);
         if (cw == 0 && lane == 0) BATCH_STAMP(i, 5);
         if (nd.qflags & BATCH_Q_SIGNAL) {
             // this warp's rows of node i are stored; the last of the CTA's consumer warps to get here releases them
@@ -628,6 +656,11 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
             }
         }
         if (++u == NB) { u = 0; uph ^= 1; }
+    }
+    if (lane == 0 && (cw == 0 || cw == 9)) {
+        BATCH_ACC_DECL(acc_total); BATCH_ACC_ADD(acc_total, t_begin);
+        const int row = cw == 0 ? 94 : 93;
+        BATCH_ACC_OUT(row, 0, acc_full); BATCH_ACC_OUT(row, 1, acc_bar); BATCH_ACC_OUT(row, 2, acc_ready); BATCH_ACC_OUT(row, 3, acc_layout); BATCH_ACC_OUT(row, 4, acc_total);
     }
 }
 
