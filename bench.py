@@ -466,6 +466,40 @@ def measure_support(torch, kern, peak):
     return out
 
 
+def measure_gguf_load(torch, kern, gib=1.0):
+    """Secondary figure: GGUF file (page cache, /tmp) -> HBM through b200_gguf_load (pinned staging ring + async H2D),
+    wall clock around the call + stream sync; the device image is checked against the file afterwards."""
+    import tempfile
+    import time
+    import numpy as np
+    import b200
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import gguf_files as gf
+    rb = b200.row_bytes("q4_K", 4096)
+    n_t = max(2, int(gib * (1 << 30) / (11008 * rb)))
+    rng = np.random.default_rng(1)
+    raw = rng.integers(0, 256, size=11008 * rb, dtype=np.uint8).tobytes()
+    tensors = [(f"blk.{i}.ffn_up.weight", [4096, 11008], 12, raw) for i in range(n_t)]
+    with tempfile.TemporaryDirectory(dir="/tmp") as d:
+        p = os.path.join(d, "bench.gguf")
+        gf.write(p, [("general.architecture", gf.STR, "llama")], tensors)
+        with b200.Gguf(p, kern.lib) as g:
+            buf = torch.empty(g.device_bytes, dtype=torch.uint8, device=kern.device)
+            best = None
+            for _ in range(3):
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                kern._check(kern.lib.b200_gguf_load(g.h, buf.data_ptr(), buf.numel(), kern._stream()), "gguf_load")
+                torch.cuda.synchronize()
+                dt = time.perf_counter() - t0
+                best = dt if best is None else min(best, dt)
+            last = g.tensors()[-1]
+            ok = buf[last["device_offset"]:last["device_offset"] + last["nbytes"]].cpu().numpy().tobytes() == raw
+            nbytes = g.data_bytes
+    return {"GBps": round(nbytes / best / 1e9, 2), "file_GB": round(nbytes / 1e9, 3), "tensors": n_t, "image_matches_file": bool(ok),
+            "path": "pread (page cache) -> 8 x 16 MiB pinned staging ring (one reader thread per stage) -> cudaMemcpyAsync"}
+
+
 def measure_decode_batches(torch, kern, stack, peak):
     """Secondary figure: the same stack (same resident weights) with n = 2, 4, 8 activation columns per MUL_MAT
     (decode at batch n, BASELINE configs[3]): one b200_mul_mat_batch list per pass (Q4_K / Q5_K: the MMA list
@@ -1113,6 +1147,7 @@ def main():
         leg("prefill_TFLOPs", lambda: measure_prefill_all(torch, kern, peaks))
         leg("support_kernels", lambda: measure_support(torch, kern, peak))
         leg("decode_batches", lambda: measure_decode_batches(torch, kern, stack, peak))
+        leg("gguf_load", lambda: measure_gguf_load(torch, kern))
         def c_abi_e2e():
             def e2e_step():
                 stack.step_e2e()

@@ -48,6 +48,12 @@ class PeerGroup(C.Structure):
     _fields_ = [("n_ranks", C.c_int32), ("rank", C.c_int32), ("base", C.c_void_p * 8), ("bytes", C.c_size_t)]
 
 
+class GgufTensorInfo(C.Structure):
+    """struct b200_gguf_tensor_info (include/ggml_b200.h)."""
+    _fields_ = [("name", C.c_char_p), ("type", C.c_int32), ("n_dims", C.c_int32), ("ne", C.c_int64 * 4),
+                ("file_offset", C.c_uint64), ("nbytes", C.c_uint64), ("device_offset", C.c_uint64)]
+
+
 def peer_group(rank: int, bases, nbytes: int) -> PeerGroup:
     pg = PeerGroup()
     pg.n_ranks = len(bases); pg.rank = rank; pg.bytes = nbytes
@@ -126,7 +132,121 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
     lib.b200_tensor_peak.argtypes = [i32, vp, vp, vp, i32, i32, C.POINTER(C.c_double), vp]
     lib.b200_set_option.restype = i32;           lib.b200_set_option.argtypes = [i32, i32]
     lib.b200_device_error_flags.restype = C.c_uint; lib.b200_device_error_flags.argtypes = [i32]
+    u64 = C.c_uint64
+    lib.b200_gguf_open.restype = i32;            lib.b200_gguf_open.argtypes = [C.c_char_p, C.POINTER(vp)]
+    lib.b200_gguf_close.restype = None;          lib.b200_gguf_close.argtypes = [vp]
+    lib.b200_gguf_last_error.restype = C.c_char_p
+    lib.b200_gguf_version.restype = C.c_uint32;  lib.b200_gguf_version.argtypes = [vp]
+    lib.b200_gguf_alignment.restype = sz;        lib.b200_gguf_alignment.argtypes = [vp]
+    lib.b200_gguf_data_offset.restype = u64;     lib.b200_gguf_data_offset.argtypes = [vp]
+    lib.b200_gguf_data_bytes.restype = u64;      lib.b200_gguf_data_bytes.argtypes = [vp]
+    lib.b200_gguf_n_kv.restype = i64;            lib.b200_gguf_n_kv.argtypes = [vp]
+    lib.b200_gguf_find_key.restype = i64;        lib.b200_gguf_find_key.argtypes = [vp, C.c_char_p]
+    lib.b200_gguf_key.restype = C.c_char_p;      lib.b200_gguf_key.argtypes = [vp, i64]
+    lib.b200_gguf_kv_type.restype = i32;         lib.b200_gguf_kv_type.argtypes = [vp, i64]
+    lib.b200_gguf_arr_type.restype = i32;        lib.b200_gguf_arr_type.argtypes = [vp, i64]
+    lib.b200_gguf_arr_n.restype = u64;           lib.b200_gguf_arr_n.argtypes = [vp, i64]
+    lib.b200_gguf_val_data.restype = vp;         lib.b200_gguf_val_data.argtypes = [vp, i64]
+    lib.b200_gguf_val_str.restype = C.c_char_p;  lib.b200_gguf_val_str.argtypes = [vp, i64, u64]
+    lib.b200_gguf_val_number.restype = i32
+    lib.b200_gguf_val_number.argtypes = [vp, i64, C.POINTER(C.c_double), C.POINTER(i64)]
+    lib.b200_gguf_n_tensors.restype = i64;       lib.b200_gguf_n_tensors.argtypes = [vp]
+    lib.b200_gguf_find_tensor.restype = i64;     lib.b200_gguf_find_tensor.argtypes = [vp, C.c_char_p]
+    lib.b200_gguf_tensor.restype = i32;          lib.b200_gguf_tensor.argtypes = [vp, i64, C.POINTER(GgufTensorInfo)]
+    lib.b200_gguf_type_row_bytes.restype = sz;   lib.b200_gguf_type_row_bytes.argtypes = [i32, i64]
+    lib.b200_gguf_device_bytes.restype = sz;     lib.b200_gguf_device_bytes.argtypes = [vp]
+    lib.b200_gguf_load.restype = i32;            lib.b200_gguf_load.argtypes = [vp, vp, sz, vp]
+    lib.b200_gguf_load_tensors.restype = i32
+    lib.b200_gguf_load_tensors.argtypes = [vp, C.POINTER(i64), C.POINTER(vp), i64, vp]
     return lib
+
+
+class Gguf:
+    """b200_gguf_* (include/ggml_b200.h): the reader half needs no GPU.  Mirrors gguf_init_from_file(no_alloc) + the
+    gguf_get_* getters of the reference (include/gguf.h:78-128); a refused file raises B200Error with the reader's text."""
+    _NP = {0: "<u1", 1: "<i1", 2: "<u2", 3: "<i2", 4: "<u4", 5: "<i4", 6: "<f4", 7: "<i1", 10: "<u8", 11: "<i8", 12: "<f8"}
+
+    def __init__(self, path: str, lib: Optional[C.CDLL] = None):
+        self.lib = lib or load_library()
+        h = C.c_void_p()
+        rc = self.lib.b200_gguf_open(os.fsencode(path), C.byref(h))
+        if rc != 0:
+            raise B200Error(f"gguf_open({path}): {self.lib.b200_gguf_last_error().decode(errors='replace')} (code {rc})")
+        self.h = h
+
+    def close(self):
+        if self.h:
+            self.lib.b200_gguf_close(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    @property
+    def version(self): return int(self.lib.b200_gguf_version(self.h))
+    @property
+    def alignment(self): return int(self.lib.b200_gguf_alignment(self.h))
+    @property
+    def data_offset(self): return int(self.lib.b200_gguf_data_offset(self.h))
+    @property
+    def data_bytes(self): return int(self.lib.b200_gguf_data_bytes(self.h))
+    @property
+    def device_bytes(self): return int(self.lib.b200_gguf_device_bytes(self.h))
+
+    def keys(self):
+        return [self.lib.b200_gguf_key(self.h, i).decode() for i in range(self.lib.b200_gguf_n_kv(self.h))]
+
+    def value(self, key: str):
+        """python value of a key: int / float / bool / str, or a numpy array / list of str for arrays"""
+        import numpy as np
+        i = self.lib.b200_gguf_find_key(self.h, key.encode())
+        if i < 0:
+            raise KeyError(key)
+        t = self.lib.b200_gguf_kv_type(self.h, i)
+        if t == 9:
+            et, n = self.lib.b200_gguf_arr_type(self.h, i), int(self.lib.b200_gguf_arr_n(self.h, i))
+            if et == 8:
+                return [self.lib.b200_gguf_val_str(self.h, i, j).decode() for j in range(n)]
+            dt = np.dtype(self._NP[et])
+            raw = C.string_at(self.lib.b200_gguf_val_data(self.h, i), n * dt.itemsize) if n else b""
+            return np.frombuffer(raw, dtype=dt).copy()
+        if t == 8:
+            return self.lib.b200_gguf_val_str(self.h, i, 0).decode()
+        d, v = C.c_double(), C.c_int64()
+        rc = self.lib.b200_gguf_val_number(self.h, i, C.byref(d), C.byref(v))
+        if rc != 0:
+            raise B200Error(f"gguf value {key}: code {rc}")
+        return bool(v.value) if t == 7 else (float(d.value) if t in (6, 12) else int(v.value))
+
+    def tensors(self):
+        """[dict(name, type, n_dims, ne, file_offset, nbytes, device_offset)] in file order"""
+        out = []
+        ti = GgufTensorInfo()
+        for i in range(self.lib.b200_gguf_n_tensors(self.h)):
+            rc = self.lib.b200_gguf_tensor(self.h, i, C.byref(ti))
+            if rc != 0:
+                raise B200Error(f"gguf_tensor({i}): code {rc}")
+            out.append(dict(name=ti.name.decode(), type=int(ti.type), n_dims=int(ti.n_dims), ne=[int(x) for x in ti.ne],
+                            file_offset=int(ti.file_offset), nbytes=int(ti.nbytes), device_offset=int(ti.device_offset)))
+        return out
+
+    def find_tensor(self, name: str) -> int:
+        return int(self.lib.b200_gguf_find_tensor(self.h, name.encode()))
+
+    def load(self, kern: "Kernels"):
+        """every tensor into one fresh device buffer (uint8); returns it (tensor i at tensors()[i]['device_offset'])"""
+        torch = kern.torch
+        buf = torch.empty(max(self.device_bytes, 256), dtype=torch.uint8, device=kern.device)
+        kern._check(self.lib.b200_gguf_load(self.h, buf.data_ptr(), buf.numel(), kern._stream()), "gguf_load")
+        return buf
+
+    def load_tensors(self, kern: "Kernels", ids, dsts):
+        n = len(ids)
+        kern._check(self.lib.b200_gguf_load_tensors(self.h, (C.c_int64 * n)(*ids), (C.c_void_p * n)(*[int(d) for d in dsts]), n,
+                                                    kern._stream()), "gguf_load_tensors")
 
 
 def batch_plan(lib, nodes, count: Optional[int] = None):

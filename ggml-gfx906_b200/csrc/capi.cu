@@ -95,6 +95,7 @@ extern "C" const char * b200_error_string(int code) {
         case B200_ERR_NO_DEVICE: return "no sm_100 device";
         case B200_ERR_INDEX:     return "row index outside the table";
         case B200_ERR_TOO_LARGE: return "problem exceeds the static scratch (B200_STATIC_SCRATCH_BYTES): use the entry point that takes a caller workspace";
+        case B200_ERR_FILE:      return "GGUF file could not be opened, parsed or read (see b200_gguf_last_error)";
         case B200_NOT_APPLICABLE: return "no kernel of this library applies to the call";
         default:                 return "unknown error";
     }

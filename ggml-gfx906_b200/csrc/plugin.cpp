@@ -723,6 +723,7 @@ static struct ggml_backend_feature * b200_get_features(ggml_backend_reg_t) {
 static void * b200_reg_get_proc_address(ggml_backend_reg_t, const char * name) {
     if (strcmp(name, "ggml_backend_split_buffer_type") == 0) return (void *) ggml_backend_b200_split_buffer_type;
     if (strcmp(name, "ggml_backend_get_features") == 0) return (void *) b200_get_features;
+    if (strcmp(name, "ggml_backend_b200_load_gguf") == 0) return (void *) ggml_backend_b200_load_gguf;
     return nullptr;
 }
 
@@ -814,6 +815,62 @@ void ggml_backend_b200_get_device_description(int device, char * description, si
 }
 void ggml_backend_b200_get_device_memory(int device, size_t * free_bytes, size_t * total_bytes) {
     if (b200_device_info(device, nullptr, 0, free_bytes, total_bytes, nullptr, nullptr) != 0) { *free_bytes = 0; *total_bytes = 0; }
+}
+
+// GGUF file -> tensors in a device buffer, in one call: what gguf_init_from_file(params.ctx != NULL) does into host memory
+// (src/gguf.cpp:640-735: one ggml_context holding every tensor of the file, named, data filled in), here with the data in
+// a buffer of ggml_backend_b200_buffer_type(device), streamed through the kernel library's pinned staging ring
+// (b200_gguf_load_tensors) instead of read() + ggml_backend_tensor_set per tensor.  *ctx_out owns the tensor metadata
+// (ggml_free), the returned buffer owns the bytes (ggml_backend_buffer_free); NULL on any failure.
+ggml_backend_buffer_t ggml_backend_b200_load_gguf(const char * fname, int device, struct ggml_context ** ctx_out) {
+    if (!fname || !ctx_out) return nullptr;
+    *ctx_out = nullptr;
+    ggml_backend_buffer_type_t buft = b200_buffer_type(device);
+    if (!buft || !buft->device) { b200_log("invalid device %d\n", device); return nullptr; }
+    b200_gguf * g = nullptr;
+    if (b200_gguf_open(fname, &g) != 0) { b200_log("%s: %s\n", fname, b200_gguf_last_error()); return nullptr; }
+    const int64_t n = b200_gguf_n_tensors(g);
+    struct ggml_init_params ip = { /* .mem_size = */ (size_t) (n + 1) * ggml_tensor_overhead(), /* .mem_buffer = */ nullptr, /* .no_alloc = */ true };
+    struct ggml_context * ctx = ggml_init(ip);
+    std::vector<int64_t> ids;
+    std::vector<void *>  dsts;
+    ggml_backend_buffer_t buf = nullptr;
+    bool ok = ctx != nullptr;
+    for (int64_t i = 0; ok && i < n; i++) {
+        b200_gguf_tensor_info ti;
+        ok = b200_gguf_tensor(g, i, &ti) == 0;
+        if (!ok) break;
+        struct ggml_tensor * t = ggml_new_tensor(ctx, (enum ggml_type) ti.type, GGML_MAX_DIMS, ti.ne);
+        ok = t != nullptr && ggml_nbytes(t) == ti.nbytes;
+        if (ok) ggml_set_name(t, ti.name);
+    }
+    if (ok && n > 0) {
+        buf = ggml_backend_alloc_ctx_tensors_from_buft(ctx, buft);
+        ok = buf != nullptr;
+    }
+    if (ok && buf) {
+        ggml_backend_buffer_set_usage(buf, GGML_BACKEND_BUFFER_USAGE_WEIGHTS);
+        int64_t i = 0;
+        for (struct ggml_tensor * t = ggml_get_first_tensor(ctx); t != nullptr; t = ggml_get_next_tensor(ctx, t), i++) {
+            ids.push_back(i);
+            dsts.push_back(t->data);
+        }
+        int prev = 0;
+        CUDA_OK(cudaGetDevice(&prev));
+        CUDA_OK(cudaSetDevice(device));
+        const int rc = b200_gguf_load_tensors(g, ids.data(), dsts.data(), (int64_t) ids.size(), /* stream = */ nullptr);
+        if (rc == 0) CUDA_OK(cudaStreamSynchronize(nullptr));
+        CUDA_OK(cudaSetDevice(prev));
+        if (rc != 0) { b200_log("%s: %s\n", fname, rc == B200_ERR_FILE ? b200_gguf_last_error() : b200_error_string(rc)); ok = false; }
+    }
+    b200_gguf_close(g);
+    if (!ok) {
+        if (buf) ggml_backend_buffer_free(buf);
+        if (ctx) ggml_free(ctx);
+        return nullptr;
+    }
+    *ctx_out = ctx;
+    return buf;
 }
 
 } // extern "C"

@@ -51,6 +51,7 @@ enum b200_error {
     B200_ERR_NO_DEVICE   = 5, /* no sm_100 device visible */
     B200_ERR_INDEX       = 6, /* a GET_ROWS index outside the table (reported by b200_device_error_flags) */
     B200_ERR_TOO_LARGE   = 7, /* the problem needs more than the fixed static scratch (b200_mul_mat_vec_static) */
+    B200_ERR_FILE        = 8, /* a GGUF file could not be opened, parsed or read (text: b200_gguf_last_error) */
     B200_NOT_APPLICABLE  = 1000, /* internal: the fast path declined; never returned by the entry points below */
 };
 
@@ -296,6 +297,54 @@ B200_API int b200_rope(const float * x_dev, const int64_t ne[4], const size_t nb
 B200_API int b200_soft_max(const float * x_dev, const int64_t ne[4], const size_t nb[4], const void * mask_dev, int mask_type,
                            const int64_t ne_mask[4], const size_t nb_mask[4], const float * sinks_dev, float scale, float max_bias,
                            float * dst_dev, void * stream);
+
+/* ---- GGUF file -> device ---------------------------------------------------------------------
+ * The container on the input side of the path.  b200_gguf_open reads header, key/value pairs and tensor
+ * infos with the acceptance rules of gguf_init_from_file_impl (src/gguf.cpp:319-735; format include/gguf.h:1-31) and
+ * keeps the file open; no tensor data is read.  replaces gguf_init_from_file(no_alloc) + the gguf_get_* getters
+ * (include/gguf.h:78-128) for reading, and — b200_gguf_load — the per-tensor read + ggml_backend_tensor_set loop of the
+ * reference's examples (a synchronous pageable cudaMemcpy per tensor, src/ggml-cuda/ggml-cuda.cu:614-621): tensor
+ * bytes go file -> a ring of eight 16 MiB pinned staging buffers -> device with cudaMemcpyAsync, one reader
+ * thread per stage filling the next stages while earlier ones are in flight.  The bytes on the device are ggml's canonical block bytes.
+ * Host-only calls (everything but the two load calls) need no GPU.  Value types = enum gguf_type (include/gguf.h:53-68):
+ * 0 u8, 1 i8, 2 u16, 3 i16, 4 u32, 5 i32, 6 f32, 7 bool, 8 string, 9 array, 10 u64, 11 i64, 12 f64. */
+typedef struct b200_gguf b200_gguf;
+typedef struct b200_gguf_tensor_info {
+    const char * name;          /* owned by the handle */
+    int32_t      type;          /* enum ggml_type */
+    int32_t      n_dims;
+    int64_t      ne[4];
+    uint64_t     file_offset;   /* absolute byte offset of the tensor's data in the file */
+    uint64_t     nbytes;        /* ggml_nbytes */
+    uint64_t     device_offset; /* where b200_gguf_load puts it, relative to base_dev (256-byte aligned) */
+} b200_gguf_tensor_info;
+B200_API int          b200_gguf_open(const char * path, b200_gguf ** out);      /* B200_ERR_FILE + b200_gguf_last_error() */
+B200_API void         b200_gguf_close(b200_gguf * g);
+B200_API const char * b200_gguf_last_error(void);                               /* of the calling thread */
+B200_API uint32_t     b200_gguf_version(const b200_gguf * g);
+B200_API size_t       b200_gguf_alignment(const b200_gguf * g);
+B200_API uint64_t     b200_gguf_data_offset(const b200_gguf * g);
+B200_API uint64_t     b200_gguf_data_bytes(const b200_gguf * g);
+B200_API int64_t      b200_gguf_n_kv(const b200_gguf * g);
+B200_API int64_t      b200_gguf_find_key(const b200_gguf * g, const char * key);          /* -1 if absent */
+B200_API const char * b200_gguf_key(const b200_gguf * g, int64_t key_id);
+B200_API int          b200_gguf_kv_type(const b200_gguf * g, int64_t key_id);             /* 9 for arrays */
+B200_API int          b200_gguf_arr_type(const b200_gguf * g, int64_t key_id);
+B200_API uint64_t     b200_gguf_arr_n(const b200_gguf * g, int64_t key_id);
+B200_API const void * b200_gguf_val_data(const b200_gguf * g, int64_t key_id);            /* raw little-endian scalar / array bytes */
+B200_API const char * b200_gguf_val_str(const b200_gguf * g, int64_t key_id, uint64_t j); /* string value (j = 0) or j-th array string */
+B200_API int          b200_gguf_val_number(const b200_gguf * g, int64_t key_id, double * as_f64, int64_t * as_i64);
+B200_API int64_t      b200_gguf_n_tensors(const b200_gguf * g);
+B200_API int64_t      b200_gguf_find_tensor(const b200_gguf * g, const char * name);      /* -1 if absent */
+B200_API int          b200_gguf_tensor(const b200_gguf * g, int64_t tensor_id, b200_gguf_tensor_info * out);
+B200_API size_t       b200_gguf_type_row_bytes(int type, int64_t ne0);                    /* ggml_row_size for every ggml type; 0 = invalid */
+/* Device image: every tensor at base_dev + device_offset, in file order.  base_dev 256-byte aligned, bytes >=
+ * b200_gguf_device_bytes().  The call returns when the last copy has left the staging buffers (the handle may then be
+ * closed); the copies are ordered on `stream` like any cudaMemcpyAsync. */
+B200_API size_t       b200_gguf_device_bytes(const b200_gguf * g);
+B200_API int          b200_gguf_load(b200_gguf * g, void * base_dev, size_t bytes, void * stream);
+/* The same for chosen tensors at caller-chosen addresses (the plugin: tensor->data of a ggml buffer). */
+B200_API int          b200_gguf_load_tensors(b200_gguf * g, const int64_t * tensor_ids, void * const * dst_dev, int64_t count, void * stream);
 
 /* ---- what the tensor cores of this box deliver -------------------------------------------------
  * A tcgen05 micro-kernel (operands resident in shared memory, accumulator in TMEM, nothing but the MMA issue loop):

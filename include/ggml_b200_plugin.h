@@ -27,6 +27,8 @@ extern "C" {
 struct ggml_backend;
 struct ggml_backend_reg;
 struct ggml_backend_buffer_type;
+struct ggml_backend_buffer;
+struct ggml_context;
 
 /* loader entry points (src/ggml-backend-impl.h:214-218) */
 B200_API struct ggml_backend_reg * ggml_backend_init(void);
@@ -42,6 +44,16 @@ B200_API struct ggml_backend_buffer_type * ggml_backend_b200_host_buffer_type(vo
 B200_API int                               ggml_backend_b200_get_device_count(void);
 B200_API void                              ggml_backend_b200_get_device_description(int device, char * description, size_t description_size);
 B200_API void                              ggml_backend_b200_get_device_memory(int device, size_t * free_bytes, size_t * total_bytes);
+
+
+/* GGUF file -> named tensors in a buffer of ggml_backend_b200_buffer_type(device), in one call (also reachable as the
+ * registry proc "ggml_backend_b200_load_gguf").  The device-side counterpart of gguf_init_from_file with params.ctx set
+ * (include/gguf.h:72-80, src/gguf.cpp:640-735), which fills a host context: *ctx_out receives a no_alloc ggml_context
+ * holding every tensor of the file (ggml_get_tensor(ctx, name)), their data streamed file -> pinned staging ring -> HBM
+ * by b200_gguf_load_tensors (include/ggml_b200.h) and marked GGML_BACKEND_BUFFER_USAGE_WEIGHTS.  Key/value metadata:
+ * b200_gguf_* or the reference's own gguf_init_from_file(no_alloc).  Returns NULL (and logs why) on failure; a file
+ * without tensors returns NULL with *ctx_out set. */
+B200_API struct ggml_backend_buffer * ggml_backend_b200_load_gguf(const char * fname, int device, struct ggml_context ** ctx_out);
 
 #ifdef __cplusplus
 }

@@ -243,3 +243,57 @@ def test_decoder_layer_stays_on_device_vs_ggml_cpu(host_and_backends, n):
     for rep in range(1, 4):
         assert all(np.isfinite(o).all() for o in results["gpu"][rep])
         assert not np.array_equal(results["gpu"][rep][0], results["gpu"][0][0])
+
+
+def test_load_gguf_through_the_plugin_then_mul_mat(host_and_backends, tmp_path):
+    """ggml_backend_b200_load_gguf (registry proc): file -> named tensors in a B200_0 buffer; the bytes read back through
+    ggml_backend_tensor_get are the file's, and a MUL_MAT on a loaded weight equals ggml-cpu on the same blocks."""
+    import ctypes as C
+    import gguf_files as gf
+    import ggml_host
+    host, cpu, gpu = host_and_backends
+    b = host.base
+    m, k = 512, 2048
+    ws = {t: np.ascontiguousarray(random_blocks(t, m, k, seed=71 + i)) for i, t in enumerate(QUANT_TYPES)}
+    norm = np.random.default_rng(3).standard_normal(k).astype(np.float32)
+    tensors = [(f"blk.{i}.w", [k, m], ggml_host.GGML_TYPE[t], ws[t].tobytes()) for i, t in enumerate(QUANT_TYPES)]
+    tensors.insert(2, ("norm.weight", [k], 0, norm.tobytes()))
+    p = str(tmp_path / "model.gguf")
+    gf.write(p, gf.sample_kvs(), tensors, alignment=64)
+    reg = b.ggml_backend_dev_backend_reg(b.ggml_backend_get_device(gpu))
+    fn = b.ggml_backend_reg_get_proc_address(reg, b"ggml_backend_b200_load_gguf")
+    assert fn, "registry proc ggml_backend_b200_load_gguf missing"
+    load = C.CFUNCTYPE(C.c_void_p, C.c_char_p, C.c_int, C.POINTER(C.c_void_p))(fn)
+    ctx = C.c_void_p()
+    assert not load(str(tmp_path / "absent.gguf").encode(), 0, C.byref(ctx)) and not ctx
+    buf = load(p.encode(), 0, C.byref(ctx))
+    assert buf and ctx
+    b.ggml_get_tensor.restype = C.c_void_p; b.ggml_get_tensor.argtypes = [C.c_void_p, C.c_char_p]
+    try:
+        for name, _, _, raw in tensors:
+            t = b.ggml_get_tensor(ctx, name.encode())
+            assert t, name
+            assert host.tensor_get(t, dtype=np.uint8).tobytes() == raw, name
+        x = np.random.default_rng(5).uniform(-1, 1, size=(3, k)).astype(np.float32)
+        for i, tname in enumerate(QUANT_TYPES):
+            w = b.ggml_get_tensor(ctx, f"blk.{i}.w".encode())
+            gctx = host.new_context()
+            xb = b.ggml_new_tensor_2d(gctx, ggml_host.GGML_TYPE["f32"], k, 3)
+            y = b.ggml_mul_mat(gctx, w, xb)
+            g = b.ggml_new_graph(gctx)
+            b.ggml_build_forward_expand(g, y)
+            gbuf = b.ggml_backend_alloc_ctx_tensors(gctx, gpu)      # allocates only xb and y: w already has a buffer
+            assert gbuf
+            try:
+                host.tensor_set(xb, x)
+                assert b.ggml_backend_graph_compute(gpu, g) == ggml_host.GGML_STATUS_SUCCESS
+                got = host.tensor_get(y).reshape(3, m)
+            finally:
+                b.ggml_backend_buffer_free(gbuf)
+                b.ggml_free(gctx)
+            want = host.mul_mat(cpu, tname, ws[tname], m, k, x)
+            err = float(((want.astype(np.float64) - got) ** 2).sum() / (want.astype(np.float64) ** 2).sum())
+            assert err <= 5e-4, (tname, err)
+    finally:
+        b.ggml_backend_buffer_free(buf)
+        b.ggml_free(ctx)
