@@ -305,6 +305,44 @@ void b200o_quantize_row_q8_1(const float * x, void * vy, int64_t k) {
     }
 }
 
+/* quantize_row_q8_K_ref, src/ggml-quants.c:2555-2592 (block_q8_K: f32 d | i8 qs[256] | i16 bsums[16], src/ggml-common.h:338-343;
+ * nearest_int :444-449 = round to nearest even through the 1.5 * 2^23 magic number): per 256 values the FIRST element of
+ * largest magnitude maps to -127 (iscale = -127 / max, max signed), q = min(127, nearest_int(iscale * x)), d = 1 / iscale.
+ * This is what ggml-cpu quantizes the activations of a K-quant MUL_MAT to (vec_dot_type Q8_K, src/ggml-cpu/ggml-cpu.c:270-300).
+ * Planar output: q[k] int8, d[k/256] f32, bsums[k/16] int16 (sums of 16 quants). */
+static int nearest_int_q(float fval) {
+    float val = fval + 12582912.f;
+    int i; memcpy(&i, &val, sizeof(int));
+    return (i & 0x007fffff) - 0x00400000;
+}
+void b200o_quantize_row_q8_K(const float * x, int8_t * q, float * d, int16_t * bsums, int64_t k) {
+    const int64_t nb = k / 256;
+    for (int64_t i = 0; i < nb; i++, x += 256, q += 256, bsums += 16) {
+        float max = 0, amax = 0;
+        for (int j = 0; j < 256; j++) {
+            const float ax = fabsf(x[j]);
+            if (ax > amax) { amax = ax; max = x[j]; }
+        }
+        if (!amax) {
+            d[i] = 0;
+            memset(q, 0, 256);
+            memset(bsums, 0, 16 * sizeof(int16_t));   /* the reference leaves bsums unwritten here; its consumers multiply them by d = 0 */
+            continue;
+        }
+        const float iscale = -127.f / max;
+        for (int j = 0; j < 256; j++) {
+            const int v = nearest_int_q(iscale * x[j]);
+            q[j] = (int8_t) (v < 127 ? v : 127);
+        }
+        for (int j = 0; j < 16; j++) {
+            int sum = 0;
+            for (int ii = 0; ii < 16; ii++) sum += q[j * 16 + ii];
+            bsums[j] = (int16_t) sum;
+        }
+        d[i] = 1 / iscale;
+    }
+}
+
 /* src/ggml-quants.c:199-222 */
 void b200o_quantize_row_q8_0(const float * x, void * vy, int64_t k) {
     uint8_t * y = (uint8_t *) vy;
@@ -370,6 +408,15 @@ void b200o_mul_mat(int type, const void * w, size_t row_stride, int64_t m, int64
             b200o_dequantize_row(B200O_Q8_1, q, xq + j * k, k);
         }
         free(q);
+    } else if (mode == 2) {
+        int8_t  * q  = (int8_t *)  malloc((size_t) k);
+        float   * d  = (float *)   malloc(sizeof(float) * (size_t)(k / 256));
+        int16_t * bs = (int16_t *) malloc(sizeof(int16_t) * (size_t)(k / 16));
+        for (int64_t j = 0; j < n; j++) {
+            b200o_quantize_row_q8_K(x + j * k, q, d, bs, k);
+            for (int64_t t = 0; t < k; t++) xq[j * k + t] = d[t / 256] * (float) q[t];   /* dequantize_row_q8_K, :2594-2604 */
+        }
+        free(q); free(d); free(bs);
     } else {
         memcpy(xq, x, sizeof(float) * (size_t)(k * n));
     }

@@ -55,6 +55,9 @@ void b200o_dequantize_row_f16(int type, const void * x, uint16_t * y, int64_t k)
 
 /* quantize_row_q8_1_ref (src/ggml-quants.c:225-258): f32[k] -> block_q8_1[k/32] */
 void b200o_quantize_row_q8_1(const float * x, void * y, int64_t k);
+/* quantize_row_q8_K_ref (src/ggml-quants.c:2555-2592): f32[k], k % 256 == 0 -> planar q[k] int8, d[k/256] f32, bsums[k/16]
+ * int16: the activation format of ggml-cpu's K-quant MUL_MAT (and of this backend's 2..8-column decode kernel) */
+void b200o_quantize_row_q8_K(const float * x, int8_t * q, float * d, int16_t * bsums, int64_t k);
 /* quantize_row_q8_0_ref (src/ggml-quants.c:199-222) and quantize_row_q4_0_ref (:41-76): used to
  * make random-quantized weights without the reference present */
 void b200o_quantize_row_q8_0(const float * x, void * y, int64_t k);
@@ -71,6 +74,9 @@ void b200o_get_rows(int type, const void * table, size_t row_stride, int64_t k,
  *   mode 1: W dequantized, X round-tripped through q8_1 (quantize_row_q8_1_ref then d*q) — the
  *           arithmetic the GPU path (and the reference CUDA path, src/ggml-cuda/mmvq.cu:536-543)
  *           performs; the GPU result must match this one to f32 rounding.
+ *   mode 2: W dequantized, X round-tripped through Q8_K (quantize_row_q8_K_ref then d*q; k % 256 == 0) — the arithmetic of
+ *           ggml-cpu's K-quant MUL_MAT (src/ggml-cpu/quants.c:550-623 et al.) and of this backend's decode kernel for
+ *           2..8 columns of Q4_K / Q5_K / Q6_K weights.
  * W rows are row_stride bytes apart; X rows are k floats. */
 void b200o_mul_mat(int type, const void * w, size_t row_stride, int64_t m, int64_t k,
                    const float * x, int64_t n, float * dst, int mode);

@@ -138,5 +138,29 @@ def main():
     print("wrote", path, os.path.getsize(path), "bytes;", len(out), "arrays")
 
 
+def main_v2():
+    """tests/golden/golden_v2.npz: quantize_row_q8_K_ref (src/ggml-quants.c:2555-2592) — the activation format of ggml-cpu's
+    K-quant MUL_MAT, which the 2..8-column decode kernel uses too.  Separate file: golden_v1.npz is left as committed."""
+    host = gh.GgmlHost(os.path.join(ROOT, "oracle", "_ref", "bin"))
+    rng = np.random.default_rng(0xB201)
+    xs = [rng.uniform(-1, 1, size=1024).astype(np.float32), (rng.standard_normal(1024) * 10).astype(np.float32)]
+    z = rng.uniform(-1, 1, size=768).astype(np.float32); z[256:512] = 0.0; xs.append(z)          # an all-zero super-block
+    o = rng.uniform(-1e-3, 1e-3, size=256).astype(np.float32); o[17] = 300.0; xs.append(o)         # outlier (positive max -> -127)
+    o = rng.uniform(-1e-3, 1e-3, size=256).astype(np.float32); o[100] = -4e4; xs.append(o)         # negative max -> +127 ... min(127, v)
+    t = rng.uniform(-0.5, 0.5, size=256).astype(np.float32); t[9] = 1.0; t[200] = -1.0; xs.append(t)   # |max| tie: the FIRST one counts
+    t = rng.uniform(-0.5, 0.5, size=256).astype(np.float32); t[9] = -1.0; t[200] = 1.0; xs.append(t)
+    tie = np.array([(j + 0.5) / 127.0 * (1 if j % 2 else -1) for j in range(255)] + [-1.0], dtype=np.float32); xs.append(tie)  # x.5 ties
+    xs.append((rng.uniform(-1, 1, size=256) * 1e-30).astype(np.float32))
+    xs.append((rng.uniform(-1, 1, size=256) * 1e30).astype(np.float32))
+    x = np.concatenate(xs)
+    q, d, bs = host.quantize_q8_K(x)
+    zero = d == 0
+    bs = bs.reshape(-1, 16).copy(); bs[zero] = 0        # the reference leaves bsums of an all-zero block unwritten
+    out = {"q8_K_x": x, "q8_K_q": q, "q8_K_d": d, "q8_K_bsums": bs.reshape(-1)}
+    path = os.path.join(ROOT, "tests", "golden", "golden_v2.npz")
+    np.savez_compressed(path, **out)
+    print("wrote", path, os.path.getsize(path), "bytes;", len(out), "arrays")
+
+
 if __name__ == "__main__":
-    sys.exit(main())
+    sys.exit(main_v2() if "v2" in sys.argv[1:] else main())

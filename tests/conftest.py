@@ -28,6 +28,12 @@ def golden():
 
 
 @pytest.fixture(scope="session")
+def golden2():
+    """quantize_row_q8_K_ref vectors (oracle/gen_golden.py v2)"""
+    return np.load(os.path.join(ROOT, "tests", "golden", "golden_v2.npz"))
+
+
+@pytest.fixture(scope="session")
 def oracle():
     import oracle_lib
     return oracle_lib.Oracle()

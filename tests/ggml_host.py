@@ -83,6 +83,7 @@ class GgmlHost:
         b.ggml_fp16_to_fp32_row.restype = None;         b.ggml_fp16_to_fp32_row.argtypes = [vp, vp, i64]
         b.ggml_fp32_to_fp16_row.restype = None;         b.ggml_fp32_to_fp16_row.argtypes = [vp, vp, i64]
         b.quantize_row_q8_1_ref.restype = None;         b.quantize_row_q8_1_ref.argtypes = [vp, vp, i64]
+        b.quantize_row_q8_K_ref.restype = None;         b.quantize_row_q8_K_ref.argtypes = [vp, vp, i64]
         for t in QUANT_TYPES:
             f = getattr(b, f"dequantize_row_{t}")
             f.restype = None; f.argtypes = [vp, vp, i64]
@@ -180,6 +181,19 @@ class GgmlHost:
         out = np.empty(x.size // 32 * 36, dtype=np.uint8)
         self.base.quantize_row_q8_1_ref(x.ctypes.data, out.ctypes.data, x.size)
         return out
+
+    def quantize_q8_K(self, x: np.ndarray):
+        """quantize_row_q8_K_ref -> (q int8 [k], d f32 [k/256], bsums int16 [k/16]) taken out of the block_q8_K structs
+        (f32 d | i8 qs[256] | i16 bsums[16] = 292 bytes, src/ggml-common.h:338-343)"""
+        x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1)
+        nb = x.size // 256
+        out = np.zeros(nb * 292, dtype=np.uint8)
+        self.base.quantize_row_q8_K_ref(x.ctypes.data, out.ctypes.data, x.size)
+        blk = out.reshape(nb, 292)
+        d = np.ascontiguousarray(blk[:, 0:4]).view(np.float32).reshape(-1)
+        q = np.ascontiguousarray(blk[:, 4:260]).view(np.int8).reshape(-1)
+        bs = np.ascontiguousarray(blk[:, 260:292]).view(np.int16).reshape(-1)
+        return q, d, bs
 
     def fp16_to_fp32(self, h: np.ndarray) -> np.ndarray:
         h = np.ascontiguousarray(h, dtype=np.uint16)

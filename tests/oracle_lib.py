@@ -34,6 +34,7 @@ class Oracle:
         L.b200o_dequantize_row_f16.argtypes = [C.c_int, vp, vp, i64]
         L.b200o_quantize_row_q8_1.argtypes = [vp, vp, i64]
         L.b200o_quantize_row_q8_0.argtypes = [vp, vp, i64]
+        L.b200o_quantize_row_q8_K.argtypes = [vp, vp, vp, vp, i64]
         L.b200o_quantize_row_q4_0.argtypes = [vp, vp, i64]
         L.b200o_get_rows.argtypes = [C.c_int, vp, sz, i64, vp, i64, vp]
         L.b200o_mul_mat.argtypes = [C.c_int, vp, sz, i64, i64, vp, i64, vp, C.c_int]
@@ -66,6 +67,15 @@ class Oracle:
         out = np.empty(x.size // 32 * 36, dtype=np.uint8)
         self.lib.b200o_quantize_row_q8_1(x.ctypes.data, out.ctypes.data, x.size)
         return out
+
+    def quantize_q8_K(self, x):
+        """quantize_row_q8_K_ref -> (q int8 [k], d f32 [k/256], bsums int16 [k/16])"""
+        x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1)
+        q = np.empty(x.size, dtype=np.int8)
+        d = np.empty(x.size // 256, dtype=np.float32)
+        bs = np.empty(x.size // 16, dtype=np.int16)
+        self.lib.b200o_quantize_row_q8_K(x.ctypes.data, q.ctypes.data, d.ctypes.data, bs.ctypes.data, x.size)
+        return q, d, bs
 
     def quantize(self, t, x):
         """q8_0 / q4_0 only (the K-quant quantizers are not on the hot path; see random_blocks)."""

@@ -70,3 +70,33 @@ def test_mul_mat_live_vs_reference_cpu(oracle, ref_host, t):
         ref_host.base.ggml_backend_free(cpu)
     got = oracle.mul_mat(t, w, m, k, x, mode=1)
     assert oracle.nmse(want, got) < 5e-4
+
+
+def test_quantize_q8_K_random(oracle, ref_host):
+    rng = np.random.default_rng(23)
+    for scale in (1.0, 1e-3, 1e3, 1e-30, 1e30):
+        x = (rng.standard_normal(256 * 512) * scale).astype(np.float32)
+        x[rng.integers(0, x.size, size=64)] = 0.0
+        q, d, bs = oracle.quantize_q8_K(x)
+        rq, rd, rbs = ref_host.quantize_q8_K(x)
+        assert np.array_equal(q, rq) and np.array_equal(d.view(np.uint32), rd.view(np.uint32)) and np.array_equal(bs, rbs), scale
+    # magnitude ties with opposite signs, all-equal blocks
+    x = np.tile(np.array([1.0, -1.0], dtype=np.float32), 128)
+    for v in (x, -x, np.full(256, 3.0, dtype=np.float32), np.full(256, -3.0, dtype=np.float32)):
+        q, d, bs = oracle.quantize_q8_K(v)
+        rq, rd, rbs = ref_host.quantize_q8_K(v)
+        assert np.array_equal(q, rq) and np.array_equal(d.view(np.uint32), rd.view(np.uint32)) and np.array_equal(bs, rbs)
+
+
+@pytest.mark.parametrize("t", ("q4_K", "q5_K", "q6_K"))
+def test_mul_mat_q8_K_mode_live_vs_reference_cpu(oracle, ref_host, t):
+    rng = np.random.default_rng(29)
+    m, k, n = 48, 2048, 5
+    w = ref_host.quantize(t, rng.uniform(-1, 1, size=(m, k)).astype(np.float32))
+    x = (rng.standard_normal((n, k)) * 3).astype(np.float32)
+    cpu = ref_host.cpu_backend(2)
+    try:
+        want = ref_host.mul_mat(cpu, t, w, m, k, x)
+    finally:
+        ref_host.base.ggml_backend_free(cpu)
+    assert oracle.nmse(want, oracle.mul_mat(t, w, m, k, x, mode=2)) < 1e-10
