@@ -597,8 +597,8 @@ extern "C" int b200_quantize_acts_columns(const float * x_dev, size_t x_row_stri
     memset(&nd, 0, sizeof(nd));
     nd.x = x_dev; nd.k = (int) k; nd.n = (int) n; nd.x_stride = (int) (x_row_stride_bytes / 4); nd.quantize = 1;
     nd.yq = (int8_t *) columns_dev;
-    nd.yds = (float2 *) ((uint8_t *) columns_dev + (((size_t) COLS_N * k + 127) & ~(size_t) 127));
-    const dim3 grid((unsigned) ceil_div(k / 32, 8), 1, COLS_N);
+    nd.ym = (uint8_t *) columns_dev + (((size_t) COLS_N * k + 127) & ~(size_t) 127);
+    const dim3 grid((unsigned) (k / 256), 1, COLS_N);
     k_quantize_cols<<<grid, 256, 0, (cudaStream_t) stream>>>(*a);
     b200_count_launch(1);
     B200_RETURN_IF_LAUNCH_FAILED();

@@ -5,22 +5,24 @@
 // one dp4a chain per column) and larger n to the MMQ tiles (mmq.cuh).  On B200 the dp4a chains make the decode
 // list kernel issue-bound as soon as there is more than one column (measured: time = n x the one-column time even
 // with the weights in L2), so here a warp multiplies a 16-row x 32-weight sub-block by the 8 (padded) columns
-// with one mma.sync.m16n8k32.s8 and applies the block scales on the 16x8 int32 result:
+// with one mma.sync.m16n8k32 (u8 weights x s8 activations) and applies the block scales to the 16x8 int32 result:
 //   * the k4 nibble layout IS the A fragment: lane (g, t) takes bytes 8t..8t+7 of a 32-byte quant chunk of rows g
-//     and g + 8 (the k order inside a 32-block is free as long as A and B agree), whose low / high nibbles are the
-//     sub-blocks 2j / 2j+1;
-//   * activations are quantized once per list to int8, the 8 columns of a 32-block side by side, + (d, d * sum)
-//     pairs per 32-block (q8_1 arithmetic), and read as B fragments from global memory (L1-resident: 10 k bytes);
+//     and g + 8 (the k order inside a 32-block is free as long as A and B agree); the low nibbles (x & 0x0F) are
+//     sub-block 2j, the high nibbles enter as x & 0xF0 = 16 q (u8), their int32 sums are shifted back exactly;
+//   * activations are quantized once per list with the arithmetic of ggml-cpu's K-quant MUL_MAT, Q8_K
+//     (quantize_row_q8_K_ref, src/ggml-quants.c:2555-2592: ONE f32 scale per 256 values and column) -- not the q8_1
+//     of the n = 1 path: with one activation scale per super-block the block scales are applied in integers
+//     (acc += sc * C, one IMAD per result instead of I2F + FMUL + FFMA), the -dmin * m * sum(q) term of Q4_K / Q5_K
+//     and the -32 offset of Q6_K become two tiny MMAs on the per-block activation sums (bsums, split into two
+//     bytes), and a super-block costs ~180 instructions per warp instead of 431 (round 1);
 //   * work unit = (node, 16-row tile), dealt round-robin to two CTAs per SM; the 8 warps of a CTA split K in
 //     256-weight super-blocks; whole tiles are requested into L2 two units ahead by bulk prefetches, the warps'
-//     own loads then hit L2, and the registers hold the activation fragments half a super-block ahead of their
-//     MMAs; partial 16x8 tiles meet in shared memory and are added in fixed warp order: a row's value does not
-//     depend on the grid.
-// Measured (profiles/r01o_bs_probe.txt, r01p_ncu_k_mmvq_cols_summary.txt): 2.85 TB/s on the weight bytes of the
-// Llama-2-7B Q4_K stack at 8 columns (44 % of the measured HBM peak, 6100 tok/s = 4x one-column decode); issue-bound
-// (441 instructions per 16-row super-block column, 61 % issue-active with 4 warps per scheduler).
+//     own loads then hit L2; partial 16x8 tiles meet in shared memory and are added in fixed warp order: a row's
+//     value does not depend on the grid, a column's value does not depend on the other columns.
+// Values: NMSE <= 1e-9 against the oracle's Q8_K arithmetic (mode 2), which is ggml-cpu's to 1e-10.
 #pragma once
 #include "mmvq_batch.cuh"
+#include <type_traits>
 
 namespace b200 {
 
@@ -42,7 +44,7 @@ struct cols_node {
     const float   * x;        // activations [n][x_stride floats]
     float         * dst;      // [n][m]
     int8_t        * yq;       // workspace: int8 [k / 32][8][32] (the 8 columns of a 32-block side by side: a B-fragment load touches 2 lines)
-    float2        * yds;      // workspace: (d, d * sum) [k / 32][8]
+    uint8_t       * ym;       // workspace: per super-block f32 d [8 columns], then the activation sums (cols_meta below)
     int64_t row_stride;
     int   m, k, n, x_stride, unit0;     // unit0: index of this node's first 16-row tile in the launch
     unsigned char type, quantize, pad[2];
@@ -55,45 +57,99 @@ struct cols_args {
     cols_node nodes[COLS_MAX_NODES];
 };
 
-// third activation plane, behind yds: int32 [k / 16][8] = -32 * (sum of the 16 int8 activations)
-__device__ __host__ __forceinline__ int * cols_yns(const cols_node & nd) { return reinterpret_cast<int *>(nd.yds + (size_t) (nd.k / 32) * COLS_N); }
-
-// ---------------------------------------------------------------- activations of the list: f32 -> int8 columns
-// grid (ceil(kmax / 32 / 8), count, 8), block 256: one warp per 32 values of one column (q8_1 arithmetic as quantize.cu)
-__global__ void __launch_bounds__(256) k_quantize_cols(const __grid_constant__ cols_args a) {
-    const cols_node & nd = a.nodes[blockIdx.y];
-    const int kb = blockIdx.x * 8 + (threadIdx.x >> 5), c = blockIdx.z;
-    const int lane = threadIdx.x & 31;
-    if (!nd.quantize || kb * 32 >= nd.k) return;
-    if (c >= nd.n) {                                      // padding columns: zero scale pairs, q never read as non-zero
-        if (lane == 0) nd.yds[kb * COLS_N + c] = make_float2(0.0f, 0.0f);
-        if (lane < 2) cols_yns(nd)[(2 * kb + lane) * COLS_N + c] = 0;
-        return;
-    }
-    const float x = __ldg(nd.x + (size_t) c * nd.x_stride + kb * 32 + lane);
-    const float amax = warp_max(fabsf(x));
-    const float d  = __fdiv_rn(amax, 127.0f);
-    const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
-    const float v  = roundf(__fmul_rn(x, id));
-    const int   qi = fabsf(v) < 2147483648.0f ? (int) v : (int) 0x80000000;
-    const int   q8 = (int) (int8_t) (qi & 0xFF);
-    nd.yq[((size_t) kb * COLS_N + c) * 32 + lane] = (int8_t) q8;
-    int sum = q8;
-#pragma unroll
-    for (int off = 8; off > 0; off >>= 1) sum += __shfl_xor_sync(0xFFFFFFFFu, sum, off);
-    // Q6_K weights are (q - 32) * scale per 16 weights: -32 * (sum of the 16 activations) is the C input of that MMA
-    if ((lane & 15) == 0) cols_yns(nd)[(2 * kb + (lane >> 4)) * COLS_N + c] = -32 * sum;
-    sum += __shfl_xor_sync(0xFFFFFFFFu, sum, 16);
-    if (lane == 0) {
-        const float dh = __half2float(__float2half_rn(d));
-        nd.yds[kb * COLS_N + c] = make_float2(dh, dh * (float) sum);
-    }
+// The planes behind yq, for nsb = k / 256 super-blocks (block_q8_K of the reference is f32 d | i8 qs[256] | i16 bsums[16]):
+//   d   f32   [nsb][8 columns]
+//   s32 uint2 [nsb][8 columns][2]  word pair t: .x = low bytes (sum & 63), .y = high bytes (sum >> 6) of the sums of the
+//                                  32-blocks 4t..4t+3 -- the B fragments of the m16n8k16 MMAs against the 6-bit mins
+//   s16 uint2 [nsb][8 columns][4]  the same for the sums of 16 (bsums), groups 4t..4t+3 -- against Q6_K's int8 scales
+struct cols_meta {
+    const float * d; const uint2 * s32; const uint2 * s16;
+};
+__device__ __host__ __forceinline__ cols_meta cols_meta_of(const uint8_t * ym, int k) {
+    const size_t nsb = (size_t) (k >> 8);
+    return { reinterpret_cast<const float *>(ym), reinterpret_cast<const uint2 *>(ym + nsb * 32), reinterpret_cast<const uint2 *>(ym + nsb * 160) };
 }
 
-// ---------------------------------------------------------------- the MMA
-__device__ __forceinline__ void mma_s8_16x8x32(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
-    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
-                 : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+// ---------------------------------------------------------------- activations of the list: f32 -> Q8_K columns
+// grid (kmax / 256, count, 8), block 256: one CTA per super-block of one column, one value per thread.
+// Bit-exact quantize_row_q8_K_ref: the FIRST value of largest magnitude maps to -127, round to nearest even, min(127, .).
+__global__ void __launch_bounds__(256) k_quantize_cols(const __grid_constant__ cols_args a) {
+    __shared__ unsigned long long skey[8];
+    __shared__ float smax;
+    const cols_node & nd = a.nodes[blockIdx.y];
+    const int sb = blockIdx.x, c = blockIdx.z;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (!nd.quantize || sb * 256 >= nd.k) return;
+    const cols_meta M = cols_meta_of(nd.ym, nd.k);
+    float  * dp  = const_cast<float *>(M.d) + sb * COLS_N + c;
+    uint8_t * p32 = reinterpret_cast<uint8_t *>(const_cast<uint2 *>(M.s32) + (sb * COLS_N + c) * 2);
+    uint8_t * p16 = reinterpret_cast<uint8_t *>(const_cast<uint2 *>(M.s16) + (sb * COLS_N + c) * 4);
+    if (c >= nd.n) {                                      // padding columns: zero scale and sums, q never read as non-zero
+        if (threadIdx.x == 0) *dp = 0.0f;
+        if (threadIdx.x < 4)  reinterpret_cast<uint32_t *>(p32)[threadIdx.x] = 0u;
+        if (threadIdx.x < 8)  reinterpret_cast<uint32_t *>(p16)[threadIdx.x] = 0u;
+        return;
+    }
+    const int j = threadIdx.x;
+    const float x = __ldg(nd.x + (size_t) c * nd.x_stride + sb * 256 + j);
+    // argmax |x| with the lowest index winning ties: key = |x| bits : (255 - j)
+    unsigned long long key = ((unsigned long long) (__float_as_uint(x) & 0x7FFFFFFFu) << 8) | (unsigned) (255 - j);
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) { const unsigned long long o = __shfl_xor_sync(0xFFFFFFFFu, key, off); key = o > key ? o : key; }
+    if (lane == 0) skey[warp] = key;
+    __syncthreads();
+    key = skey[0];
+#pragma unroll
+    for (int w = 1; w < 8; w++) key = skey[w] > key ? skey[w] : key;
+    if (j == 255 - (int) (key & 0xFFu)) smax = x;
+    __syncthreads();
+    const float mx = smax;
+    int q = 0;
+    float d = 0.0f;
+    if ((key >> 8) != 0ull) {                             // amax != 0
+        const float iscale = __fdiv_rn(-127.0f, mx);
+        q = min(127, __float2int_rn(__fmul_rn(iscale, x)));
+        d = __fdiv_rn(1.0f, iscale);
+    }
+    nd.yq[((size_t) (sb * 8 + warp) * COLS_N + c) * 32 + lane] = (int8_t) q;
+    int sum = q;
+#pragma unroll
+    for (int off = 8; off > 0; off >>= 1) sum += __shfl_xor_sync(0xFFFFFFFFu, sum, off);
+    if ((lane & 15) == 0) {                               // sums of 16: group 2 * warp + (lane >> 4)
+        const int gi = 2 * warp + (lane >> 4);
+        p16[(gi >> 2) * 8 + (gi & 3)]     = (uint8_t) (sum & 63);
+        p16[(gi >> 2) * 8 + 4 + (gi & 3)] = (uint8_t) (sum >> 6);
+    }
+    sum += __shfl_xor_sync(0xFFFFFFFFu, sum, 16);
+    if (lane == 0) {                                      // sum of the 32-block `warp`
+        p32[(warp >> 2) * 8 + (warp & 3)]     = (uint8_t) (sum & 63);
+        p32[(warp >> 2) * 8 + 4 + (warp & 3)] = (uint8_t) (sum >> 6);
+    }
+    if (threadIdx.x == 0) *dp = d;
+}
+
+// ---------------------------------------------------------------- the MMAs (C = 0: the scales differ per 32-block)
+// m16n8k32, A = u8 weights (rows g / g + 8, k slots 4t.. and 16 + 4t..), B = s8 activations (column g)
+__device__ __forceinline__ void mma_u8s8_16x8x32(int (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%10, %10, %10, %10};"
+        : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "r"(0));
+}
+// m16n8k16, A = u8 (mins, 6-bit weights) or s8 (Q6_K scales), B = s8
+template <bool SIGNED_A>
+__device__ __forceinline__ void mma_16x8x16(int (&d)[4], uint32_t a0, uint32_t a1, uint32_t b0) {
+    if (SIGNED_A)
+        asm("mma.sync.aligned.m16n8k16.row.col.s32.s8.s8.s32 {%0, %1, %2, %3}, {%4, %5}, {%6}, {%7, %7, %7, %7};"
+            : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]) : "r"(a0), "r"(a1), "r"(b0), "r"(0));
+    else
+        asm("mma.sync.aligned.m16n8k16.row.col.s32.u8.s8.s32 {%0, %1, %2, %3}, {%4, %5}, {%6}, {%7, %7, %7, %7};"
+            : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]) : "r"(a0), "r"(a1), "r"(b0), "r"(0));
+}
+// byte i of w, zero- / sign-extended (one PRMT each; __byte_perm drops prmt's sign-replicate selector bit)
+template <int I> __device__ __forceinline__ int byte_u(uint32_t w) { return (int) __byte_perm(w, 0u, 0x4440 + I); }
+template <int I> __device__ __forceinline__ int byte_s(uint32_t w) {
+    int r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(w), "r"(0), "n"(I | ((I | 8) << 4) | ((I | 8) << 8) | ((I | 8) << 12)));
+    return r;
 }
 
 // streaming loads of the weights: read-only path, not kept in L1 (L1 is for the activation columns)
@@ -115,77 +171,73 @@ __device__ __forceinline__ void l2_prefetch_bulk(const void * p, uint32_t bytes)
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(p), "r"(bytes) : "memory");
 }
 
-// The words of one 128-weight item (half a super-block) of one row that lane (g, t) needs.  The MMA's k order
-// inside a 32-block is free as long as A and B agree: lane t takes bytes 8t..8t+7 of the 32-byte quant chunk
-// (one 8-byte load) as its k slots 4t..4t+3 and 16+4t..16+4t+3, and the same bytes of the activation block.
-struct cols_item {            // one 256-weight super-block of one row, as lane (g, t) needs it
+// The words of one 256-weight super-block of one row that lane (g, t) needs.  The MMA's k order inside a 32-block is
+// free as long as A and B agree: lane t takes bytes 8t..8t+7 of the 32-byte quant chunk (one 8-byte load) as its k
+// slots 4t..4t+3 and 16+4t..16+4t+3, and the same bytes of the activation block.
+struct cols_item {
     uint4 hdr;                // d, dmin (f16 x 2) + 12 scale bytes
     uint2 q[4];               // [32-byte quant chunk] bytes 8t..8t+7
     uint2 h;                  // Q5_K: high-bit bytes 8t..8t+7
 };
 
-__device__ __forceinline__ void cols_load(cols_item & it, const uint8_t * row, int item, int t, bool q5) {
-    const uint8_t * blk = row + (size_t) item * (q5 ? 176 : 144);
+template <bool Q5>
+__device__ __forceinline__ void cols_load(cols_item & it, const uint8_t * row, int item, int t) {
+    const uint8_t * blk = row + (size_t) item * (Q5 ? 176 : 144);
     it.hdr = ldg_stream128(blk);
-    const uint8_t * qs = blk + (q5 ? 48 : 16) + 8 * t;
+    const uint8_t * qs = blk + (Q5 ? 48 : 16) + 8 * t;
 #pragma unroll
     for (int p = 0; p < 4; p++) it.q[p] = ldg_stream64(qs + 32 * p);
-    if (q5) it.h = ldg_stream64(blk + 16 + 8 * t);
+    if (Q5) it.h = ldg_stream64(blk + 16 + 8 * t);
 }
 
-// d * sc and dmin * m of the item's four sub-blocks (get_scale_min_k4 on four bytes at a time)
-__device__ __forceinline__ void cols_scales(const uint4 & hdr, int half, float (&dsc)[4], float (&dmn)[4]) {
-    const float2 dm = __half22float2(*reinterpret_cast<const __half2 *>(&hdr.x));
-    uint32_t sc, mn;
-    if (half == 0) { sc = hdr.y & 0x3F3F3F3Fu; mn = hdr.z & 0x3F3F3F3Fu; }
-    else {
-        sc = (hdr.w & 0x0F0F0F0Fu) | ((hdr.y >> 2) & 0x30303030u);
-        mn = ((hdr.w >> 4) & 0x0F0F0F0Fu) | ((hdr.z >> 2) & 0x30303030u);
-    }
-#pragma unroll
-    for (int q = 0; q < 4; q++) {
-        dsc[q] = dm.x * (float) ((sc >> (8 * q)) & 0xFFu);
-        dmn[q] = dm.y * (float) ((mn >> (8 * q)) & 0xFFu);
-    }
+// bit S of every byte of h, moved to bit 4
+template <int S> __device__ __forceinline__ uint32_t cols_hbit(uint32_t h) {
+    return (S <= 4 ? (h << (4 - S)) : (h >> (S - 4))) & 0x10101010u;
 }
 
-// B fragments and (d, d * sum) pairs of four consecutive 32-blocks (half a super-block), requested together
-struct cols_acts { uint2 b[4]; float4 ds[4]; };
-__device__ __forceinline__ void cols_load_acts(cols_acts & y, const int8_t * yq_col, const float2 * yds, int blk0, int t, bool col_ok) {
-    const int8_t * yq = yq_col + (size_t) blk0 * (32 * COLS_N) + 8 * t;
-#pragma unroll
-    for (int q = 0; q < 4; q++) {
-        y.b[q] = make_uint2(0u, 0u);
-        if (col_ok) y.b[q] = __ldg(reinterpret_cast<const uint2 *>(yq + q * (32 * COLS_N)));
-        y.ds[q] = __ldg(reinterpret_cast<const float4 *>(yds + (size_t) (blk0 + q) * COLS_N + 2 * t));   // columns 2t, 2t + 1
-    }
-}
-
-// Half a super-block of rows g and g + 8 against the 8 columns: 4 MMAs (one per 32-weight sub-block), block
-// scales applied to the 16x8 int32 result.
-__device__ __forceinline__ void cols_half_mma(const cols_item & ia, const cols_item & ib, const int half, bool q5,
-                                              const cols_acts & y, float (&acc)[4]) {
-    float dscA[4], dmnA[4], dscB[4], dmnB[4];
-    cols_scales(ia.hdr, half, dscA, dmnA);
-    cols_scales(ib.hdr, half, dscB, dmnB);
-#pragma unroll
-    for (int q = 0; q < 4; q++) {
-        const int p = half * 2 + (q >> 1), sh = (q & 1) * 4;
-        uint32_t a0 = (ia.q[p].x >> sh) & 0x0F0F0F0Fu, a1 = (ib.q[p].x >> sh) & 0x0F0F0F0Fu;
-        uint32_t a2 = (ia.q[p].y >> sh) & 0x0F0F0F0Fu, a3 = (ib.q[p].y >> sh) & 0x0F0F0F0Fu;
-        if (q5) {
-            const int s = half * 4 + q;                                  // bit s of qh belongs to sub-block s
-            a0 |= ((ia.h.x >> s) & 0x01010101u) << 4; a1 |= ((ib.h.x >> s) & 0x01010101u) << 4;
-            a2 |= ((ia.h.y >> s) & 0x01010101u) << 4; a3 |= ((ib.h.y >> s) & 0x01010101u) << 4;
+// One super-block of rows g and g + 8 against the 8 columns: 8 MMAs (one per 32-weight sub-block), the 6-bit block
+// scales applied to the int32 results, the mins through two small MMAs on the activations' block sums.
+//   sum_k w y = d dy sum_b sc_b (q_b . y_b) - dmin dy sum_b m_b sum(y_b)
+template <bool Q5>
+__device__ __forceinline__ void cols_sb_mma(const cols_item & ia, const cols_item & ib, const uint2 (&b)[8], const float2 dy,
+                                            const uint2 s32, const int t, float (&acc)[4]) {
+    // get_scale_min_k4, four sub-blocks per word
+    const uint32_t scA[2] = { ia.hdr.y & 0x3F3F3F3Fu, (ia.hdr.w & 0x0F0F0F0Fu) | ((ia.hdr.y >> 2) & 0x30303030u) };
+    const uint32_t mnA[2] = { ia.hdr.z & 0x3F3F3F3Fu, ((ia.hdr.w >> 4) & 0x0F0F0F0Fu) | ((ia.hdr.z >> 2) & 0x30303030u) };
+    const uint32_t scB[2] = { ib.hdr.y & 0x3F3F3F3Fu, (ib.hdr.w & 0x0F0F0F0Fu) | ((ib.hdr.y >> 2) & 0x30303030u) };
+    const uint32_t mnB[2] = { ib.hdr.z & 0x3F3F3F3Fu, ((ib.hdr.w >> 4) & 0x0F0F0F0Fu) | ((ib.hdr.z >> 2) & 0x30303030u) };
+    int lo[4] = { 0, 0, 0, 0 }, hi[4] = { 0, 0, 0, 0 };      // hi: the high-nibble sub-blocks of Q4_K, 16 x too large
+    auto one = [&](auto Q) {
+        constexpr int q = decltype(Q)::value, p = q >> 1;
+        uint32_t a0, a1, a2, a3;
+        if (!Q5) {
+            constexpr uint32_t msk = (q & 1) ? 0xF0F0F0F0u : 0x0F0F0F0Fu;
+            a0 = ia.q[p].x & msk; a1 = ib.q[p].x & msk; a2 = ia.q[p].y & msk; a3 = ib.q[p].y & msk;
+        } else {
+            constexpr int sh = (q & 1) * 4;                    // bit q of qh belongs to sub-block q
+            a0 = ((ia.q[p].x >> sh) & 0x0F0F0F0Fu) | cols_hbit<q>(ia.h.x); a1 = ((ib.q[p].x >> sh) & 0x0F0F0F0Fu) | cols_hbit<q>(ib.h.x);
+            a2 = ((ia.q[p].y >> sh) & 0x0F0F0F0Fu) | cols_hbit<q>(ia.h.y); a3 = ((ib.q[p].y >> sh) & 0x0F0F0F0Fu) | cols_hbit<q>(ib.h.y);
         }
-        int c[4] = { 0, 0, 0, 0 };
-        mma_s8_16x8x32(c, a0, a1, a2, a3, y.b[q].x, y.b[q].y);
-        const float4 ds = y.ds[q];
-        acc[0] += dscA[q] * (ds.x * (float) c[0]) - dmnA[q] * ds.y;
-        acc[1] += dscA[q] * (ds.z * (float) c[1]) - dmnA[q] * ds.w;
-        acc[2] += dscB[q] * (ds.x * (float) c[2]) - dmnB[q] * ds.y;
-        acc[3] += dscB[q] * (ds.z * (float) c[3]) - dmnB[q] * ds.w;
-    }
+        int c[4];
+        mma_u8s8_16x8x32(c, a0, a1, a2, a3, b[q].x, b[q].y);
+        const int sA = byte_u<q & 3>(scA[q >> 2]), sB = byte_u<q & 3>(scB[q >> 2]);
+        if (!Q5 && (q & 1)) { hi[0] += sA * c[0]; hi[1] += sA * c[1]; hi[2] += sB * c[2]; hi[3] += sB * c[3]; }
+        else                { lo[0] += sA * c[0]; lo[1] += sA * c[1]; lo[2] += sB * c[2]; lo[3] += sB * c[3]; }
+    };
+    one(std::integral_constant<int, 0>()); one(std::integral_constant<int, 1>()); one(std::integral_constant<int, 2>());
+    one(std::integral_constant<int, 3>()); one(std::integral_constant<int, 4>()); one(std::integral_constant<int, 5>());
+    one(std::integral_constant<int, 6>()); one(std::integral_constant<int, 7>());
+    // sum_b m_b * sum32_b: A = the mins (k = sub-block; lanes t >= 2 hold zero B words), sums = lo + 64 hi
+    int cl[4], ch[4];
+    const uint32_t am0 = t == 0 ? mnA[0] : mnA[1], am1 = t == 0 ? mnB[0] : mnB[1];
+    mma_16x8x16<false>(cl, am0, am1, s32.x);
+    mma_16x8x16<false>(ch, am0, am1, s32.y);
+    const float2 dmA = __half22float2(*reinterpret_cast<const __half2 *>(&ia.hdr.x));
+    const float2 dmB = __half22float2(*reinterpret_cast<const __half2 *>(&ib.hdr.x));
+    acc[0] += dy.x * (dmA.x * (float) (lo[0] + (hi[0] >> 4)) - dmA.y * (float) (cl[0] + 64 * ch[0]));
+    acc[1] += dy.y * (dmA.x * (float) (lo[1] + (hi[1] >> 4)) - dmA.y * (float) (cl[1] + 64 * ch[1]));
+    acc[2] += dy.x * (dmB.x * (float) (lo[2] + (hi[2] >> 4)) - dmB.y * (float) (cl[2] + 64 * ch[2]));
+    acc[3] += dy.y * (dmB.x * (float) (lo[3] + (hi[3] >> 4)) - dmB.y * (float) (cl[3] + 64 * ch[3]));
 }
 
 // ---------------------------------------------------------------- Q6_K: one m16n8k16 MMA per 16-weight scale group
@@ -194,10 +246,7 @@ __device__ __forceinline__ void cols_half_mma(const cols_item & ia, const cols_i
 // same for every lane: odd blocks read the two aligned words around each word and funnel-shift.
 // Lane (g, t) takes bytes 4t..4t+3 of each 16-byte piece: for half h, piece s, word j of ql serves the groups
 // r = j (low nibbles) and r = j + 2 (high nibbles); the qh word serves r = 0..3 (2 bits each).
-__device__ __forceinline__ void mma_s8_16x8x16(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t b0) {
-    asm volatile("mma.sync.aligned.m16n8k16.row.col.s32.s8.s8.s32 {%0, %1, %2, %3}, {%4, %5}, {%6}, {%0, %1, %2, %3};"
-                 : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3]) : "r"(a0), "r"(a1), "r"(b0));
-}
+//   sum_k w y = d dy (sum_g sc_g (q_g . y_g) - 32 sum_g sc_g sum16_g),  q in 0..63 (u8), sc int8
 __device__ __forceinline__ uint32_t ldg_stream32(const void * p) {
     uint32_t v;
     asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p));
@@ -236,38 +285,39 @@ __device__ __forceinline__ void cols_load6(cols_item6 & it, const uint8_t * blk,
     }
     it.d = *reinterpret_cast<const unsigned short *>(blk + 208);
 }
-// sign-extended byte i of w as float
-__device__ __forceinline__ float cols_s8f(uint32_t w, int i) {
-    return (float) ((int) (w << (24 - 8 * i)) >> 24);      // (__byte_perm ignores prmt's sign-replicate selector bit)
-}
-__device__ __forceinline__ void cols_item6_mma(const cols_item6 & ia, const cols_item6 & ib, int item, int g, int t,
-                                               const int8_t * yq_col, const float2 * yds, const int * yns, bool col_ok, float (&acc)[4]) {
+__device__ __forceinline__ void cols_item6_mma(const cols_item6 & ia, const cols_item6 & ib, int item, int t,
+                                               const int8_t * yq_col, const float2 dy, const uint2 s16, bool col_ok, float (&acc)[4]) {
+    int ai[4] = { 0, 0, 0, 0 };
+    auto group = [&](auto H, auto R, auto S) {
+        constexpr int h = decltype(H)::value, r = decltype(R)::value, s = decltype(S)::value;
+        const int B = item * 8 + 4 * h + r;                         // the 32-block of the activations
+        const uint32_t a0 = ((ia.ql[h][r & 1][s] >> (4 * (r >> 1))) & 0x0F0F0F0Fu) | (((ia.qh[h][s] >> (2 * r)) & 0x03030303u) << 4);
+        const uint32_t a1 = ((ib.ql[h][r & 1][s] >> (4 * (r >> 1))) & 0x0F0F0F0Fu) | (((ib.qh[h][s] >> (2 * r)) & 0x03030303u) << 4);
+        uint32_t b0 = 0u;
+        if (col_ok) b0 = __ldg(reinterpret_cast<const uint32_t *>(yq_col + (size_t) B * (32 * COLS_N) + 16 * s + 4 * t));
+        int c[4];
+        mma_16x8x16<false>(c, a0, a1, b0);
+        constexpr int si = 8 * h + 2 * r + s;                       // scale of this 16-weight group
+        const int fA = byte_s<si & 3>(ia.sc[si >> 2]), fB = byte_s<si & 3>(ib.sc[si >> 2]);
+        ai[0] += fA * c[0]; ai[1] += fA * c[1]; ai[2] += fB * c[2]; ai[3] += fB * c[3];
+    };
+    using I0 = std::integral_constant<int, 0>; using I1 = std::integral_constant<int, 1>;
+    using I2 = std::integral_constant<int, 2>; using I3 = std::integral_constant<int, 3>;
+    group(I0(), I0(), I0()); group(I0(), I0(), I1()); group(I0(), I1(), I0()); group(I0(), I1(), I1());
+    group(I0(), I2(), I0()); group(I0(), I2(), I1()); group(I0(), I3(), I0()); group(I0(), I3(), I1());
+    group(I1(), I0(), I0()); group(I1(), I0(), I1()); group(I1(), I1(), I0()); group(I1(), I1(), I1());
+    group(I1(), I2(), I0()); group(I1(), I2(), I1()); group(I1(), I3(), I0()); group(I1(), I3(), I1());
+    // sum_g sc_g * sum16_g: A = the int8 scales (k = group: bytes 4t..4t+3), sums = lo + 64 hi
+    const uint32_t sa = t == 0 ? ia.sc[0] : (t == 1 ? ia.sc[1] : (t == 2 ? ia.sc[2] : ia.sc[3]));
+    const uint32_t sb = t == 0 ? ib.sc[0] : (t == 1 ? ib.sc[1] : (t == 2 ? ib.sc[2] : ib.sc[3]));
+    int cl[4], ch[4];
+    mma_16x8x16<true>(cl, sa, sb, s16.x);
+    mma_16x8x16<true>(ch, sa, sb, s16.y);
     const float dA = f16_bits_to_f32(ia.d), dB = f16_bits_to_f32(ib.d);
-#pragma unroll
-    for (int h = 0; h < 2; h++) {
-#pragma unroll
-        for (int r = 0; r < 4; r++) {
-            const int B = item * 8 + 4 * h + r;                         // the 32-block of the activations
-            const float4 ds = __ldg(reinterpret_cast<const float4 *>(yds + (size_t) B * COLS_N + 2 * t));     // .x, .z: d of columns 2t, 2t + 1
-            float tA0 = 0.0f, tA1 = 0.0f, tB0 = 0.0f, tB1 = 0.0f;
-#pragma unroll
-            for (int s = 0; s < 2; s++) {
-                const uint32_t a0 = ((ia.ql[h][r & 1][s] >> (4 * (r >> 1))) & 0x0F0F0F0Fu) | (((ia.qh[h][s] >> (2 * r)) & 0x03030303u) << 4);
-                const uint32_t a1 = ((ib.ql[h][r & 1][s] >> (4 * (r >> 1))) & 0x0F0F0F0Fu) | (((ib.qh[h][s] >> (2 * r)) & 0x03030303u) << 4);
-                uint32_t b0 = 0u;
-                if (col_ok) b0 = __ldg(reinterpret_cast<const uint32_t *>(yq_col + (size_t) B * (32 * COLS_N) + 16 * s + 4 * t));
-                const int2 ns = __ldg(reinterpret_cast<const int2 *>(yns + (size_t) (2 * B + s) * COLS_N + 2 * t));
-                int c[4] = { ns.x, ns.y, ns.x, ns.y };                  // -32 * sum16: the weights enter as q, not q - 32
-                mma_s8_16x8x16(c, a0, a1, b0);
-                const int si = 8 * h + 2 * r + s;                       // scale of this 16-weight group
-                const float fA = cols_s8f(ia.sc[si >> 2], si & 3), fB = cols_s8f(ib.sc[si >> 2], si & 3);
-                tA0 += fA * (float) c[0]; tA1 += fA * (float) c[1];
-                tB0 += fB * (float) c[2]; tB1 += fB * (float) c[3];
-            }
-            acc[0] += (dA * ds.x) * tA0; acc[1] += (dA * ds.z) * tA1;
-            acc[2] += (dB * ds.x) * tB0; acc[3] += (dB * ds.z) * tB1;
-        }
-    }
+    acc[0] += (dA * dy.x) * (float) (ai[0] - 32 * (cl[0] + 64 * ch[0]));
+    acc[1] += (dA * dy.y) * (float) (ai[1] - 32 * (cl[1] + 64 * ch[1]));
+    acc[2] += (dB * dy.x) * (float) (ai[2] - 32 * (cl[2] + 64 * ch[2]));
+    acc[3] += (dB * dy.y) * (float) (ai[3] - 32 * (cl[3] + 64 * ch[3]));
 }
 
 // KS = 8 (default): the 8 warps of a CTA split K of one tile, partial tiles meet in shared memory;
@@ -313,37 +363,48 @@ __global__ void __launch_bounds__(COLS_NW * 32, COLS_CTAS) k_mmvq_cols(const __g
         while (ni + 1 < a.count && u >= a.nodes[ni + 1].unit0) ni++;
         const cols_node & nd = a.nodes[ni];
         const int row0 = (u - nd.unit0) * 16, items = nd.k >> 8;
-        const bool q5 = nd.type == T_Q5_K;
         const int ra = min(row0 + g, nd.m - 1), rb = min(row0 + g + 8, nd.m - 1);      // tail rows: recomputed, never stored
         const uint8_t * pa = nd.w + (size_t) ra * nd.row_stride;
         const uint8_t * pb = nd.w + (size_t) rb * nd.row_stride;
         if (KS > 1) prefetch_unit(u + PD * ustride, nip);
         else if (u + ustride < a.units) { while (nip + 1 < a.count && u + ustride >= a.nodes[nip + 1].unit0) nip++; }   // nip: the next tile's node
         const int8_t * yq_col = nd.yq + g * 32;
-        const float2 * yds = nd.yds;
+        const cols_meta M = cols_meta_of(nd.ym, nd.k);
         const bool col_ok = g < nd.n;
         float acc[4] = { 0.0f, 0.0f, 0.0f, 0.0f };
         if (nd.type == T_Q6_K) {
-            const int * yns = cols_yns(nd);
             for (int it = kw; it < items; it += KS) {
                 cols_item6 ia, ib;
                 if (it & 1) { cols_load6<true>(ia, pa + (size_t) it * 210, t);  cols_load6<true>(ib, pb + (size_t) it * 210, t); }
                 else        { cols_load6<false>(ia, pa + (size_t) it * 210, t); cols_load6<false>(ib, pb + (size_t) it * 210, t); }
-                cols_item6_mma(ia, ib, it, g, t, yq_col, yds, yns, col_ok, acc);
+                const float2 dy = __ldg(reinterpret_cast<const float2 *>(M.d + it * COLS_N + 2 * t));       // columns 2t, 2t + 1
+                const uint2 s16 = __ldg(M.s16 + (it * COLS_N + g) * 4 + t);                                 // column g, groups 4t..4t+3
+                cols_item6_mma(ia, ib, it, t, yq_col, dy, s16, col_ok, acc);
             }
-        } else
-        for (int it = kw; it < items; it += KS) {
-            if (KS == 1 && (it & 7) == 0) {
-                if (it + 8 < items) prefetch_chunk(nd, row0, it + 8);
-                else if (u + ustride < a.units) prefetch_chunk(a.nodes[nip], (u + ustride - a.nodes[nip].unit0) * 16, 0);
-            }
-            cols_item ia, ib;
-            cols_acts y0, y1;
-            cols_load(ia, pa, it, t, q5); cols_load(ib, pb, it, t, q5);
-            cols_load_acts(y0, yq_col, yds, it * 8, t, col_ok);
-            cols_load_acts(y1, yq_col, yds, it * 8 + 4, t, col_ok);
-            cols_half_mma(ia, ib, 0, q5, y0, acc);
-            cols_half_mma(ia, ib, 1, q5, y1, acc);
+        } else {
+            auto tile = [&](auto Q5) {
+                constexpr bool q5 = decltype(Q5)::value;
+                for (int it = kw; it < items; it += KS) {
+                    if (KS == 1 && (it & 7) == 0) {
+                        if (it + 8 < items) prefetch_chunk(nd, row0, it + 8);
+                        else if (u + ustride < a.units) prefetch_chunk(a.nodes[nip], (u + ustride - a.nodes[nip].unit0) * 16, 0);
+                    }
+                    cols_item ia, ib;
+                    uint2 b[8];
+                    cols_load<q5>(ia, pa, it, t); cols_load<q5>(ib, pb, it, t);
+                    const int8_t * yq = yq_col + (size_t) it * (8 * 32 * COLS_N) + 8 * t;
+#pragma unroll
+                    for (int q = 0; q < 8; q++) {
+                        b[q] = make_uint2(0u, 0u);
+                        if (col_ok) b[q] = __ldg(reinterpret_cast<const uint2 *>(yq + q * (32 * COLS_N)));
+                    }
+                    const float2 dy = __ldg(reinterpret_cast<const float2 *>(M.d + it * COLS_N + 2 * t));   // columns 2t, 2t + 1
+                    uint2 s32 = make_uint2(0u, 0u);
+                    if (t < 2) s32 = __ldg(M.s32 + (it * COLS_N + g) * 2 + t);                              // column g, sub-blocks 4t..4t+3
+                    cols_sb_mma<q5>(ia, ib, b, dy, s32, t, acc);
+                }
+            };
+            if (nd.type == T_Q5_K) tile(std::true_type()); else tile(std::false_type());
         }
         if (KS == 1) {
             // c fragment layout: acc[0..1] = row g, columns 2t, 2t + 1; acc[2..3] = row g + 8
@@ -380,8 +441,8 @@ static inline bool cols_node_ok(int type, const uint8_t * w, int64_t row_stride,
 }
 static inline size_t cols_ws_bytes(int64_t k, int64_t n) {
     (void) n;
-    // int8 [k/32][8][32]  +  (d, d * sum) [k/32][8]  +  -32 * sum16 [k/16][8]
-    return (((size_t) COLS_N * k + 127) & ~(size_t) 127) + (((size_t) (k / 32) * COLS_N * (sizeof(float2) + 2 * sizeof(int)) + 127) & ~(size_t) 127);
+    // int8 [k/32][8][32]  +  per super-block: f32 d [8], sums of 32 (2 x 8 bytes) [8], sums of 16 (4 x 8 bytes) [8] (cols_meta)
+    return (((size_t) COLS_N * k + 127) & ~(size_t) 127) + (((size_t) (k / 256) * COLS_N * (4 + 16 + 32) + 127) & ~(size_t) 127);
 }
 
 struct cols_builder {
@@ -395,12 +456,12 @@ struct cols_builder {
         cols_node & nd = args.nodes[args.count];
         const cols_node * prev = args.count > 0 ? &args.nodes[args.count - 1] : nullptr;
         if (prev && prev->x == x && prev->k == k && prev->n == n && prev->x_stride == (int) (x_stride_bytes / 4)) {
-            nd.yq = prev->yq; nd.yds = prev->yds; nd.quantize = 0;     // same activations as the previous node (gate/up, q/k/v)
+            nd.yq = prev->yq; nd.ym = prev->ym; nd.quantize = 0;     // same activations as the previous node (gate/up, q/k/v)
         } else {
             const size_t need = cols_ws_bytes(k, n);
             if (need > cur.left) return false;
             nd.yq = reinterpret_cast<int8_t *>(cur.p);
-            nd.yds = reinterpret_cast<float2 *>(cur.p + (((size_t) COLS_N * k + 127) & ~(size_t) 127));
+            nd.ym = cur.p + (((size_t) COLS_N * k + 127) & ~(size_t) 127);
             nd.quantize = 1; cur.p += need; cur.left -= need;
         }
         nd.w = w; nd.x = x; nd.dst = dst; nd.row_stride = row_stride; nd.m = (int) m; nd.k = (int) k; nd.n = (int) n;
@@ -418,7 +479,7 @@ static int cols_launch(cols_builder & cb, cudaStream_t st) {
     cols_args & a = cb.args;
     static const int pdl = env_int("GGML_B200_FUSED_PDL", 1);
     {
-        const dim3 grid((unsigned) ceil_div(a.kmax / 32, 8), (unsigned) a.count, COLS_N);
+        const dim3 grid((unsigned) (a.kmax / 256), (unsigned) a.count, COLS_N);
         k_quantize_cols<<<grid, 256, 0, st>>>(a);
         b200_count_launch(1);
     }

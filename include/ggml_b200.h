@@ -266,8 +266,10 @@ B200_API int    b200_mul_mat_q(int type, const void * w_dev, size_t w_row_stride
  * src/ggml-quants.c:225-258).  Layouts (implementation detail of b200_mul_mat_batch's workspace):
  *   record  (decode list kernel, one vector of k values): int8 plane [k], 128-value items with their eight 16-byte
  *            pieces rotated (piece p of item i is stored at piece (p + i) % 8), then f32 d[k/32] (the fp16-rounded scale);
- *   columns (2..8-column MMA list kernel): int8 [k/32][8][32] (the 8 padded columns of a 32-block side by side), then at
- *            the next 128-byte boundary float2 (d, d * sum(q)) [k/32][8], then int32 -32 * sum16(q) [k/16][8]. */
+ *   columns (2..8-column MMA list kernel; Q8_K arithmetic, quantize_row_q8_K_ref, src/ggml-quants.c:2555-2592): int8
+ *            [k/32][8][32] (the 8 padded columns of a 32-block side by side), then at the next 128-byte boundary f32 d
+ *            [k/256][8], then the sums of the 32-blocks as byte pairs (sum & 63, sum >> 6): uint8 [k/256][8][2][2][4] (column,
+ *            half of the super-block, low / high bytes, sub-block), then the sums of 16 (bsums) likewise: uint8 [k/256][8][4][2][4]. */
 B200_API size_t b200_acts_record_bytes(int64_t k);
 B200_API size_t b200_acts_columns_bytes(int64_t k, int64_t n);
 B200_API int    b200_quantize_acts_record(const float * x_dev, int64_t k, void * record_dev, void * stream);

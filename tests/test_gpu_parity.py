@@ -193,25 +193,51 @@ def test_quantize_list_record_vs_oracle(kern, oracle, case):
 @pytest.mark.parametrize("case", list(_act_cases().keys()))
 @pytest.mark.parametrize("n", [2, 5, 8])
 def test_quantize_list_columns_vs_oracle(kern, oracle, case, n):
-    """k_quantize_cols (decode at batch 2..8): int8 [k/32][8][32] + (d, d * sum) + -32 * sum16, against
-    quantize_row_q8_1_ref per column; padding columns carry zero scales."""
+    """k_quantize_cols (decode at batch 2..8): int8 [k/32][8][32], then per super-block the f32 scale of each column and the
+    sums of 32 / of 16 quants as (sum & 63, sum >> 6) byte pairs -- bit for bit quantize_row_q8_K_ref
+    (src/ggml-quants.c:2555-2592) per column; padding columns carry zero scales and sums."""
     base = _act_cases()[case]
-    x = np.ascontiguousarray(np.resize(base, (n, base.shape[1])) * np.linspace(1.0, 2.0, n, dtype=np.float32)[:, None])
+    k = base.shape[1] // 256 * 256
+    x = np.ascontiguousarray(np.resize(base[:, :k], (n, k)) * np.linspace(1.0, 2.0, n, dtype=np.float32)[:, None])
+    if case == "ties":       # equal magnitudes of opposite sign inside a super-block: the first one sets the sign of the scale
+        x[0, 5], x[0, 200] = -np.abs(x[0]).max() * 2, np.abs(x[0]).max() * 2
+        x[1, 7], x[1, 100] = np.abs(x[1]).max() * 2, -np.abs(x[1]).max() * 2
+    buf = kern.quantize_acts_columns(kern.to_device(x)).cpu().numpy()
+    nsb = k // 256
+    yq = buf[:8 * k].view(np.int8).reshape(k // 32, 8, 32)
+    off = (8 * k + 127) & ~127
+    d = buf[off:off + nsb * 32].view(np.float32).reshape(nsb, 8)
+    s32 = buf[off + nsb * 32: off + nsb * 160].reshape(nsb, 8, 2, 2, 4)        # [sb][col][t][lo / hi][4 sub-blocks]
+    s16 = buf[off + nsb * 160: off + nsb * 416].reshape(nsb, 8, 4, 2, 4)
+    for c in range(n):
+        q, dq, bs = oracle.quantize_q8_K(x[c])
+        assert np.array_equal(yq[:, c, :].reshape(-1), q), c
+        assert np.array_equal(u32(d[:, c]), u32(dq)), c
+        sums16 = bs.reshape(nsb, 4, 4).astype(np.int32)
+        got16 = s16[:, c, :, 0, :].astype(np.int32) + 64 * s16[:, c, :, 1, :].view(np.int8).astype(np.int32)
+        assert np.array_equal(got16, sums16), c
+        assert (s16[:, c, :, 0, :] < 64).all()
+        sums32 = bs.reshape(nsb, 2, 4, 2).astype(np.int32).sum(axis=3)
+        got32 = s32[:, c, :, 0, :].astype(np.int32) + 64 * s32[:, c, :, 1, :].view(np.int8).astype(np.int32)
+        assert np.array_equal(got32, sums32), c
+    for c in range(n, 8):
+        assert not d[:, c].any() and not s32[:, c].any() and not s16[:, c].any()
+
+
+def test_quantize_list_columns_golden(kern, golden2):
+    """the reference's own quantize_row_q8_K_ref outputs (tests/golden/golden_v2.npz) through k_quantize_cols"""
+    x = np.stack([golden2["q8_K_x"], golden2["q8_K_x"]])
     k = x.shape[1]
     buf = kern.quantize_acts_columns(kern.to_device(x)).cpu().numpy()
     yq = buf[:8 * k].view(np.int8).reshape(k // 32, 8, 32)
     off = (8 * k + 127) & ~127
-    yds = buf[off:off + k // 32 * 8 * 8].view(np.float32).reshape(k // 32, 8, 2)
-    yns = buf[off + k // 32 * 8 * 8: off + k // 32 * 8 * 8 + k // 16 * 8 * 4].view(np.int32).reshape(k // 16, 8)
-    for c in range(n):
-        q, d, sums = _q8_1_reference(oracle, x[c])
-        assert np.array_equal(yq[:, c, :].reshape(-1), q), c
-        assert np.array_equal(u32(yds[:, c, 0]), u32(d)), c
-        assert np.array_equal(u32(yds[:, c, 1]), u32(d * sums.astype(np.float32))), c
-        s16 = q.reshape(-1, 16).astype(np.int32).sum(axis=1)
-        assert np.array_equal(yns[:, c], -32 * s16), c
-    for c in range(n, 8):
-        assert not yds[:, c, :].any() and not yns[:, c].any()
+    d = buf[off:off + k // 256 * 32].view(np.float32).reshape(-1, 8)
+    s16 = buf[off + k // 256 * 160: off + k // 256 * 416].reshape(-1, 8, 4, 2, 4)
+    for c in range(2):
+        assert np.array_equal(yq[:, c, :].reshape(-1), golden2["q8_K_q"])
+        assert np.array_equal(u32(d[:, c]), u32(golden2["q8_K_d"]))
+        got16 = s16[:, c, :, 0, :].astype(np.int32) + 64 * s16[:, c, :, 1, :].view(np.int8).astype(np.int32)
+        assert np.array_equal(got16.reshape(-1), golden2["q8_K_bsums"].astype(np.int32))
 
 
 def test_get_rows_index_out_of_range_is_reported(kern, oracle):
@@ -445,9 +471,11 @@ def test_mul_mat_batch_few_columns(kern, oracle, n):
         nodes = (b200.MulMatNode * 1)(b200.mul_mat_node(t, w.data_ptr(), m, k, x.data_ptr(), n, y.data_ptr(), b_row_stride=4 * (k + pad)))
         kern.mul_mat_batch(nodes)
         got = y.cpu().numpy()
-        want = oracle.mul_mat(t, w_np, m, k, np.ascontiguousarray(x_np[:, :k]), mode=1)
+        on_mma_kernel = t in ("q4_K", "q5_K") or (t == "q6_K" and k % 2048 == 0)     # Q6_K rows must be 16-byte multiples for the MMA path
+        # the MMA list kernel takes its activations through Q8_K like ggml-cpu (oracle mode 2), the others through q8_1
+        want = oracle.mul_mat(t, w_np, m, k, np.ascontiguousarray(x_np[:, :k]), mode=2 if on_mma_kernel else 1)
         assert oracle.nmse(want, got) <= NMSE_ORACLE, (t, m, k, n)
-        if t in ("q4_K", "q5_K") or (t == "q6_K" and k % 2048 == 0):     # Q6_K rows must be 16-byte multiples for the MMA path
+        if on_mma_kernel:
             # the MMA list kernel (mmvq_cols.cuh): a column's value depends on that column alone -- the first two
             # columns computed as an n = 2 node give the same bits; and the result is reproducible
             y2 = torch.zeros((2, m), dtype=torch.float32, device=kern.device)
