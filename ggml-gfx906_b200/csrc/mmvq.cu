@@ -476,7 +476,7 @@ static int run_list(const b200_mul_mat_node * nodes, int64_t count, void * works
                 ok = cols_bb->add(nd.type_a, (const uint8_t *) nd.a_dev, (int64_t) nd.nb_a[1], m, k, nd.b_dev, (int64_t) nd.nb_b[1], ncols, nd.dst_dev, cur);
             }
             if (ok) {
-                reads.add(x0, x1, 3, cols_bb->args.count - 1); writes.add(d0, d1, 3, cols_bb->args.count - 1);
+                reads.add(x0, x1, 3, cols_bb->count() - 1); writes.add(d0, d1, 3, cols_bb->count() - 1);
                 if (dry) { plan[3 * i] = group; plan[3 * i + 1] = -1; plan[3 * i + 2] = 2; }
                 continue;
             }

@@ -180,14 +180,12 @@ struct cols_item {
     uint2 h;                  // Q5_K: high-bit bytes 8t..8t+7
 };
 
-template <bool Q5>
-__device__ __forceinline__ void cols_load(cols_item & it, const uint8_t * row, int item, int t) {
-    const uint8_t * blk = row + (size_t) item * (Q5 ? 176 : 144);
+__device__ __forceinline__ void cols_load_any(cols_item & it, const uint8_t * blk, int t, bool q5) {
     it.hdr = ldg_stream128(blk);
-    const uint8_t * qs = blk + (Q5 ? 48 : 16) + 8 * t;
+    const uint8_t * qs = blk + (q5 ? 48 : 16) + 8 * t;
 #pragma unroll
     for (int p = 0; p < 4; p++) it.q[p] = ldg_stream64(qs + 32 * p);
-    if (Q5) it.h = ldg_stream64(blk + 16 + 8 * t);
+    if (q5) it.h = ldg_stream64(blk + 16 + 8 * t);
 }
 
 // bit S of every byte of h, moved to bit 4
@@ -198,14 +196,23 @@ template <int S> __device__ __forceinline__ uint32_t cols_hbit(uint32_t h) {
 // One super-block of rows g and g + 8 against the 8 columns: 8 MMAs (one per 32-weight sub-block), the 6-bit block
 // scales applied to the int32 results, the mins through two small MMAs on the activations' block sums.
 //   sum_k w y = d dy sum_b sc_b (q_b . y_b) - dmin dy sum_b m_b sum(y_b)
+// While it runs it rolls the NEXT super-block of the warp (blocks at na / nb, of a Q4_K or Q5_K row: nq5) into ia / ib,
+// each word as soon as its last use is behind: the loads stay in flight for one whole super-block of work (an L2 round
+// trip) without a second set of registers.  na == nullptr: nothing follows.
 template <bool Q5>
-__device__ __forceinline__ void cols_sb_mma(const cols_item & ia, const cols_item & ib, const uint2 (&b)[8], const float2 dy,
-                                            const uint2 s32, const int t, float (&acc)[4]) {
+__device__ __forceinline__ void cols_sb_mma(cols_item & ia, cols_item & ib, const uint2 (&b)[8], const float2 dy,
+                                            const uint2 s32, const int t, float (&acc)[4],
+                                            const uint8_t * na, const uint8_t * nb, const bool nq5) {
     // get_scale_min_k4, four sub-blocks per word
     const uint32_t scA[2] = { ia.hdr.y & 0x3F3F3F3Fu, (ia.hdr.w & 0x0F0F0F0Fu) | ((ia.hdr.y >> 2) & 0x30303030u) };
     const uint32_t mnA[2] = { ia.hdr.z & 0x3F3F3F3Fu, ((ia.hdr.w >> 4) & 0x0F0F0F0Fu) | ((ia.hdr.z >> 2) & 0x30303030u) };
     const uint32_t scB[2] = { ib.hdr.y & 0x3F3F3F3Fu, (ib.hdr.w & 0x0F0F0F0Fu) | ((ib.hdr.y >> 2) & 0x30303030u) };
     const uint32_t mnB[2] = { ib.hdr.z & 0x3F3F3F3Fu, ((ib.hdr.w >> 4) & 0x0F0F0F0Fu) | ((ib.hdr.z >> 2) & 0x30303030u) };
+    const float2 dmA = __half22float2(*reinterpret_cast<const __half2 *>(&ia.hdr.x));
+    const float2 dmB = __half22float2(*reinterpret_cast<const __half2 *>(&ib.hdr.x));
+    const bool more = na != nullptr;
+    const uint8_t * nqa = na + (nq5 ? 48 : 16) + 8 * t, * nqb = nb + (nq5 ? 48 : 16) + 8 * t;
+    if (more) { ia.hdr = ldg_stream128(na); ib.hdr = ldg_stream128(nb); }
     int lo[4] = { 0, 0, 0, 0 }, hi[4] = { 0, 0, 0, 0 };      // hi: the high-nibble sub-blocks of Q4_K, 16 x too large
     auto one = [&](auto Q) {
         constexpr int q = decltype(Q)::value, p = q >> 1;
@@ -223,6 +230,7 @@ __device__ __forceinline__ void cols_sb_mma(const cols_item & ia, const cols_ite
         const int sA = byte_u<q & 3>(scA[q >> 2]), sB = byte_u<q & 3>(scB[q >> 2]);
         if (!Q5 && (q & 1)) { hi[0] += sA * c[0]; hi[1] += sA * c[1]; hi[2] += sB * c[2]; hi[3] += sB * c[3]; }
         else                { lo[0] += sA * c[0]; lo[1] += sA * c[1]; lo[2] += sB * c[2]; lo[3] += sB * c[3]; }
+        if ((q & 1) && more) { ia.q[p] = ldg_stream64(nqa + 32 * p); ib.q[p] = ldg_stream64(nqb + 32 * p); }     // chunk p is done
     };
     one(std::integral_constant<int, 0>()); one(std::integral_constant<int, 1>()); one(std::integral_constant<int, 2>());
     one(std::integral_constant<int, 3>()); one(std::integral_constant<int, 4>()); one(std::integral_constant<int, 5>());
@@ -232,8 +240,7 @@ __device__ __forceinline__ void cols_sb_mma(const cols_item & ia, const cols_ite
     const uint32_t am0 = t == 0 ? mnA[0] : mnA[1], am1 = t == 0 ? mnB[0] : mnB[1];
     mma_16x8x16<false>(cl, am0, am1, s32.x);
     mma_16x8x16<false>(ch, am0, am1, s32.y);
-    const float2 dmA = __half22float2(*reinterpret_cast<const __half2 *>(&ia.hdr.x));
-    const float2 dmB = __half22float2(*reinterpret_cast<const __half2 *>(&ib.hdr.x));
+    if (more && nq5) { ia.h = ldg_stream64(na + 16 + 8 * t); ib.h = ldg_stream64(nb + 16 + 8 * t); }
     acc[0] += dy.x * (dmA.x * (float) (lo[0] + (hi[0] >> 4)) - dmA.y * (float) (cl[0] + 64 * ch[0]));
     acc[1] += dy.y * (dmA.x * (float) (lo[1] + (hi[1] >> 4)) - dmA.y * (float) (cl[1] + 64 * ch[1]));
     acc[2] += dy.x * (dmB.x * (float) (lo[2] + (hi[2] >> 4)) - dmB.y * (float) (cl[2] + 64 * ch[2]));
@@ -359,6 +366,8 @@ __global__ void __launch_bounds__(COLS_NW * 32, COLS_CTAS) k_mmvq_cols(const __g
         prefetch_chunk(a.nodes[nip], (u - a.nodes[nip].unit0) * 16, 0);
     }
     asm volatile("griddepcontrol.wait;" ::: "memory");        // the quantizer of this list has finished
+    cols_item ia, ib;          // the warp's current Q4_K / Q5_K super-block of rows g and g + 8 ...
+    bool have = false;         // ... already requested by the step before (also across a tile boundary)
     for (; u < a.units; u += ustride, par ^= 1) {
         while (ni + 1 < a.count && u >= a.nodes[ni + 1].unit0) ni++;
         const cols_node & nd = a.nodes[ni];
@@ -368,30 +377,49 @@ __global__ void __launch_bounds__(COLS_NW * 32, COLS_CTAS) k_mmvq_cols(const __g
         const uint8_t * pb = nd.w + (size_t) rb * nd.row_stride;
         if (KS > 1) prefetch_unit(u + PD * ustride, nip);
         else if (u + ustride < a.units) { while (nip + 1 < a.count && u + ustride >= a.nodes[nip + 1].unit0) nip++; }   // nip: the next tile's node
+        // the warp's first super-block of its NEXT tile, if that is a Q4_K / Q5_K one
+        const uint8_t * pan = nullptr, * pbn = nullptr;
+        bool q5n = false;
+        if (u + ustride < a.units) {
+            int nin = ni;
+            while (nin + 1 < a.count && u + ustride >= a.nodes[nin + 1].unit0) nin++;
+            const cols_node & nn = a.nodes[nin];
+            if (nn.type != T_Q6_K && (nn.k >> 8) > kw) {
+                const int r0n = (u + ustride - nn.unit0) * 16;
+                q5n = nn.type == T_Q5_K;
+                pan = nn.w + (size_t) min(r0n + g, nn.m - 1) * nn.row_stride + (size_t) kw * (q5n ? 176 : 144);
+                pbn = nn.w + (size_t) min(r0n + g + 8, nn.m - 1) * nn.row_stride + (size_t) kw * (q5n ? 176 : 144);
+            }
+        }
         const int8_t * yq_col = nd.yq + g * 32;
         const cols_meta M = cols_meta_of(nd.ym, nd.k);
         const bool col_ok = g < nd.n;
         float acc[4] = { 0.0f, 0.0f, 0.0f, 0.0f };
         if (nd.type == T_Q6_K) {
             for (int it = kw; it < items; it += KS) {
-                cols_item6 ia, ib;
-                if (it & 1) { cols_load6<true>(ia, pa + (size_t) it * 210, t);  cols_load6<true>(ib, pb + (size_t) it * 210, t); }
-                else        { cols_load6<false>(ia, pa + (size_t) it * 210, t); cols_load6<false>(ib, pb + (size_t) it * 210, t); }
+                cols_item6 ia6, ib6;
+                if (it & 1) { cols_load6<true>(ia6, pa + (size_t) it * 210, t);  cols_load6<true>(ib6, pb + (size_t) it * 210, t); }
+                else        { cols_load6<false>(ia6, pa + (size_t) it * 210, t); cols_load6<false>(ib6, pb + (size_t) it * 210, t); }
                 const float2 dy = __ldg(reinterpret_cast<const float2 *>(M.d + it * COLS_N + 2 * t));       // columns 2t, 2t + 1
                 const uint2 s16 = __ldg(M.s16 + (it * COLS_N + g) * 4 + t);                                 // column g, groups 4t..4t+3
-                cols_item6_mma(ia, ib, it, t, yq_col, dy, s16, col_ok, acc);
+                cols_item6_mma(ia6, ib6, it, t, yq_col, dy, s16, col_ok, acc);
             }
-        } else {
+            if (pan) { cols_load_any(ia, pan, t, q5n); cols_load_any(ib, pbn, t, q5n); }
+            have = pan != nullptr;
+        } else if (kw < items) {
             auto tile = [&](auto Q5) {
                 constexpr bool q5 = decltype(Q5)::value;
+                constexpr int bs = q5 ? 176 : 144;
+                if (!have) { cols_load_any(ia, pa + (size_t) kw * bs, t, q5); cols_load_any(ib, pb + (size_t) kw * bs, t, q5); }
                 for (int it = kw; it < items; it += KS) {
                     if (KS == 1 && (it & 7) == 0) {
                         if (it + 8 < items) prefetch_chunk(nd, row0, it + 8);
                         else if (u + ustride < a.units) prefetch_chunk(a.nodes[nip], (u + ustride - a.nodes[nip].unit0) * 16, 0);
                     }
-                    cols_item ia, ib;
+                    const bool last = it + KS >= items;
+                    const uint8_t * na = last ? pan : pa + (size_t) (it + KS) * bs;
+                    const uint8_t * nb = last ? pbn : pb + (size_t) (it + KS) * bs;
                     uint2 b[8];
-                    cols_load<q5>(ia, pa, it, t); cols_load<q5>(ib, pb, it, t);
                     const int8_t * yq = yq_col + (size_t) it * (8 * 32 * COLS_N) + 8 * t;
 #pragma unroll
                     for (int q = 0; q < 8; q++) {
@@ -401,10 +429,13 @@ __global__ void __launch_bounds__(COLS_NW * 32, COLS_CTAS) k_mmvq_cols(const __g
                     const float2 dy = __ldg(reinterpret_cast<const float2 *>(M.d + it * COLS_N + 2 * t));   // columns 2t, 2t + 1
                     uint2 s32 = make_uint2(0u, 0u);
                     if (t < 2) s32 = __ldg(M.s32 + (it * COLS_N + g) * 2 + t);                              // column g, sub-blocks 4t..4t+3
-                    cols_sb_mma<q5>(ia, ib, b, dy, s32, t, acc);
+                    cols_sb_mma<q5>(ia, ib, b, dy, s32, t, acc, na, nb, last ? q5n : q5);
                 }
             };
             if (nd.type == T_Q5_K) tile(std::true_type()); else tile(std::false_type());
+            have = pan != nullptr;
+        } else {
+            have = false;
         }
         if (KS == 1) {
             // c fragment layout: acc[0..1] = row g, columns 2t, 2t + 1; acc[2..3] = row g + 8
@@ -430,6 +461,147 @@ __global__ void __launch_bounds__(COLS_NW * 32, COLS_CTAS) k_mmvq_cols(const __g
     }
 }
 
+// ---------------------------------------------------------------- Q4_K / Q5_K: tiles staged through a TMA ring
+// k_mmvq_cols above reads its weights with per-lane loads out of L2 (behind bulk L2 prefetches): at most ~40 KB in flight
+// per SM, every 8-byte load touching eight 128-byte lines, and the kernel stood at 50 % of the HBM peak with every
+// pipe below 60 % (profiles/r03c_ncu_k_mmvq_cols_q8k_summary.txt; rolling the next super-block's words into the
+// registers or dropping the per-tile barrier changed nothing).  Here, as in the one-column list kernel (mmvq_batch.cuh):
+// one persistent CTA per SM; a producer warp streams (32-row tile) x (8 super-blocks) chunks -- the weights and the matching
+// slice of the quantized activations -- into a ring of three 62 KB stages with 1-D bulk copies (one per row + three;
+// full / empty mbarriers), so ~190 KB are in flight per SM and no consumer load ever leaves the SM; sixteen consumer
+// warps take one super-block of 16 rows each out of shared memory (row pitch = 32 mod 128 bytes: the 8-byte fragment
+// loads of a warp cover all banks twice, the minimum); their partial 16x8 tiles go to a double-buffered shared array
+// and an epilogue warp adds them in fixed order and stores -- no CTA-wide barrier anywhere.
+constexpr int RING_NWC      = 16;                  // consumer warps: warp w -> rows 16 (w >> 3).., super-block (w & 7) of a chunk
+constexpr int RING_NPROD    = 3;                   // producer warps: a bulk copy is a per-lane serial issue (~100 cycles each); one
+                                                   // producer warp could not feed the ring (consumers waited 43 % of the time)
+constexpr int RING_THREADS  = (RING_NWC + RING_NPROD + 1) * 32;   // consumers + producers + epilogue warp (20 warps: 96 registers)
+constexpr int RING_CI       = 8;                   // super-blocks per chunk
+constexpr int RING_ROWS     = 32;
+constexpr int RING_PITCH_MAX = RING_CI * 176 + 32;  // 1440 (Q5_K); Q4_K rows use 1184 of it
+constexpr int RING_OFF_YQ   = RING_ROWS * RING_PITCH_MAX;      // 46080: the chunk's activations follow its weights:
+constexpr int RING_OFF_D    = RING_OFF_YQ + RING_CI * 8 * 32 * COLS_N;     //   int8 [8 super-blocks][8 sub-blocks][8 columns][32]
+constexpr int RING_OFF_S32  = RING_OFF_D + RING_CI * COLS_N * 4;           //   f32 d [8][8 columns]
+constexpr int RING_STAGE    = RING_OFF_S32 + RING_CI * COLS_N * 16;        //   sums of 32 [8][8 columns][2] uint2  -> 63744
+constexpr int RING_STAGES   = 3;
+constexpr int RING_OFF_RED  = RING_STAGES * RING_STAGE;        // float red[2][RING_NWC][128]
+constexpr int RING_OFF_BAR  = RING_OFF_RED + 2 * RING_NWC * 128 * 4;
+constexpr int RING_SMEM     = RING_OFF_BAR + 128;
+
+__device__ __forceinline__ uint2 lds64(const uint8_t * p) { return *reinterpret_cast<const uint2 *>(p); }
+
+__global__ void __launch_bounds__(RING_THREADS, 1) k_mmvq_cols_ring(const __grid_constant__ cols_args a) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint64_t * full = reinterpret_cast<uint64_t *>(smem + RING_OFF_BAR), * empty = full + RING_STAGES;
+    uint64_t * red_full = empty + RING_STAGES, * red_empty = red_full + 2;
+    float (*red)[RING_NWC][128] = reinterpret_cast<float (*)[RING_NWC][128]>(smem + RING_OFF_RED);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < RING_STAGES; s++) { mbar_init(&full[s], RING_NPROD); mbar_init(&empty[s], RING_NWC); }
+        for (int b = 0; b < 2; b++) { mbar_init(&red_full[b], RING_NWC); mbar_init(&red_empty[b], 1); }
+        mbar_fence_init();
+    }
+    __syncthreads();
+    int ni = 0;
+    if (warp >= RING_NWC && warp < RING_NWC + RING_NPROD) {
+        // ---------------- producers: warp p copies rows 11 p .. 11 p + 10 of the tile's chunk (one per lane) and one activation plane
+        const int pw = warp - RING_NWC, r_lo = 11 * pw, r = r_lo + lane;
+        int stage = 0; uint32_t phase = 0;
+        asm volatile("griddepcontrol.wait;" ::: "memory");        // the quantizer of this list has finished
+        for (int u = blockIdx.x; u < a.units; u += gridDim.x) {
+            while (ni + 1 < a.count && u >= a.nodes[ni + 1].unit0) ni++;
+            const cols_node & nd = a.nodes[ni];
+            const int row0 = (u - nd.unit0) * RING_ROWS, items = nd.k >> 8, bs = nd.type == T_Q5_K ? 176 : 144;
+            const int rows = min(RING_ROWS, nd.m - row0), pitch = RING_CI * bs + 32;
+            const int my_rows = max(0, min(rows, r_lo + 11) - r_lo);
+            const uint8_t * src = nd.w + (size_t) (row0 + r) * nd.row_stride;
+            const cols_meta M = cols_meta_of(nd.ym, nd.k);
+            for (int c0 = 0; c0 < items; c0 += RING_CI) {
+                const uint32_t ci = (uint32_t) min(RING_CI, items - c0), bytes = ci * (uint32_t) bs;
+                uint8_t * st = smem + stage * RING_STAGE;
+                mbar_wait(&empty[stage], phase ^ 1u);
+                const uint32_t abytes = ci * (pw == 0 ? 8 * 32 * COLS_N : (pw == 1 ? COLS_N * 4 : COLS_N * 16));
+                if (lane == 0) mbar_arrive_expect_tx(&full[stage], bytes * (uint32_t) my_rows + abytes);
+                __syncwarp();
+                if (lane < 11 && r < rows) bulk_g2s(st + r * pitch, src + (size_t) c0 * bs, bytes, &full[stage]);
+                if (lane == 11) {
+                    if (pw == 0)      bulk_g2s(st + RING_OFF_YQ, nd.yq + (size_t) c0 * (8 * 32 * COLS_N), abytes, &full[stage]);
+                    else if (pw == 1) bulk_g2s(st + RING_OFF_D, M.d + (size_t) c0 * COLS_N, abytes, &full[stage]);
+                    else              bulk_g2s(st + RING_OFF_S32, M.s32 + (size_t) c0 * COLS_N * 2, abytes, &full[stage]);
+                }
+                if (++stage == RING_STAGES) { stage = 0; phase ^= 1u; }
+            }
+        }
+    } else if (warp == RING_NWC + RING_NPROD) {
+        // ---------------- epilogue: sum the eight partial tiles of each row half in warp order, store
+        int par = 0; uint32_t rphase = 0;
+        for (int u = blockIdx.x; u < a.units; u += gridDim.x) {
+            while (ni + 1 < a.count && u >= a.nodes[ni + 1].unit0) ni++;
+            const cols_node & nd = a.nodes[ni];
+            const int row0 = (u - nd.unit0) * RING_ROWS;
+            mbar_wait(&red_full[par], rphase);
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                const int e = lane + 32 * j, half = e >> 7, idx = e & 127, l = idx >> 2, i = idx & 3;
+                float v = 0.0f;
+#pragma unroll
+                for (int w = 0; w < 8; w++) v += red[par][half * 8 + w][idx];
+                // c fragment layout: element i of lane l = (g, t): row g + 8 (i >> 1), column 2t + (i & 1)
+                const int row = row0 + 16 * half + (l >> 2) + 8 * (i >> 1), col = 2 * (l & 3) + (i & 1);
+                if (row < nd.m && col < nd.n) nd.dst[(size_t) col * nd.m + row] = v;
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cta(&red_empty[par]);
+            if ((par ^= 1) == 0) rphase ^= 1u;
+        }
+    } else {
+        // ---------------- consumers
+        const int g = lane >> 2, t = lane & 3, half = warp >> 3, slot = warp & 7;
+        int stage = 0, par = 0; uint32_t phase = 0, rphase = 0;
+        for (int u = blockIdx.x; u < a.units; u += gridDim.x) {
+            while (ni + 1 < a.count && u >= a.nodes[ni + 1].unit0) ni++;
+            const cols_node & nd = a.nodes[ni];
+            const int items = nd.k >> 8;
+            const bool q5 = nd.type == T_Q5_K;
+            const int bs = q5 ? 176 : 144, pitch = RING_CI * bs + 32;
+            float acc[4] = { 0.0f, 0.0f, 0.0f, 0.0f };
+            for (int c0 = 0; c0 < items; c0 += RING_CI) {
+                mbar_wait(&full[stage], phase);
+                if (c0 + slot < items) {
+                    const uint8_t * st = smem + stage * RING_STAGE;
+                    const uint8_t * ra = st + (16 * half + g) * pitch + slot * bs, * rb = ra + 8 * pitch;
+                    uint2 b[8];          // columns >= n hold whatever the workspace held: their results are never stored
+#pragma unroll
+                    for (int q = 0; q < 8; q++) b[q] = lds64(st + RING_OFF_YQ + (slot * 8 + q) * (32 * COLS_N) + g * 32 + 8 * t);
+                    const uint2 dyb = lds64(st + RING_OFF_D + slot * (COLS_N * 4) + 8 * t);                 // columns 2t, 2t + 1
+                    const float2 dy = make_float2(__uint_as_float(dyb.x), __uint_as_float(dyb.y));
+                    uint2 s32 = make_uint2(0u, 0u);
+                    if (t < 2) s32 = lds64(st + RING_OFF_S32 + (slot * COLS_N + g) * 16 + 8 * t);           // column g, sub-blocks 4t..4t+3
+                    cols_item ia, ib;
+                    ia.hdr = lds128(ra); ib.hdr = lds128(rb);
+                    const int qo = (q5 ? 48 : 16) + 8 * t;
+#pragma unroll
+                    for (int p = 0; p < 4; p++) { ia.q[p] = lds64(ra + qo + 32 * p); ib.q[p] = lds64(rb + qo + 32 * p); }
+                    if (q5) {
+                        ia.h = lds64(ra + 16 + 8 * t); ib.h = lds64(rb + 16 + 8 * t);
+                        cols_sb_mma<true>(ia, ib, b, dy, s32, t, acc, nullptr, nullptr, false);
+                    } else {
+                        cols_sb_mma<false>(ia, ib, b, dy, s32, t, acc, nullptr, nullptr, false);
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive_cta(&empty[stage]);
+                if (++stage == RING_STAGES) { stage = 0; phase ^= 1u; }
+            }
+            mbar_wait(&red_empty[par], rphase ^ 1u);             // the epilogue has read this buffer's previous tile
+            *reinterpret_cast<float4 *>(&red[par][warp][lane * 4]) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cta(&red_full[par]);
+            if ((par ^= 1) == 0) rphase ^= 1u;
+        }
+    }
+}
+
 // ---------------------------------------------------------------- host side
 static inline bool cols_node_ok(int type, const uint8_t * w, int64_t row_stride, int64_t m, int64_t k, const float * x,
                                 int64_t x_stride_bytes, int64_t n) {
@@ -446,29 +618,40 @@ static inline size_t cols_ws_bytes(int64_t k, int64_t n) {
 }
 
 struct cols_builder {
-    cols_args args;
+    cols_args args;       // Q6_K nodes: k_mmvq_cols, 16-row tiles
+    cols_args ring;       // Q4_K / Q5_K nodes: k_mmvq_cols_ring, 32-row tiles
+    // the activations quantized last (nodes of either list that read the same x share them: q/k/v, gate/up)
+    const float * last_x; int64_t last_k, last_n, last_stride; int8_t * last_yq; uint8_t * last_ym;
     cols_builder() { reset(); }
-    void reset() { args.count = 0; args.units = 0; args.kmax = 0; args.pad = 0; }
-    bool full() const { return args.count >= COLS_MAX_NODES; }
-    bool empty() const { return args.count == 0; }
+    void reset() {
+        args.count = 0; args.units = 0; args.kmax = 0; args.pad = 0;
+        ring.count = 0; ring.units = 0; ring.kmax = 0; ring.pad = 0;
+        last_x = nullptr; last_k = last_n = last_stride = 0; last_yq = nullptr; last_ym = nullptr;
+    }
+    bool full() const { return args.count >= COLS_MAX_NODES || ring.count >= COLS_MAX_NODES; }
+    bool empty() const { return args.count == 0 && ring.count == 0; }
+    int  count() const { return args.count + ring.count; }
     bool add(int type, const uint8_t * w, int64_t row_stride, int64_t m, int64_t k, const float * x, int64_t x_stride_bytes,
              int64_t n, float * dst, ws_cursor & cur) {
-        cols_node & nd = args.nodes[args.count];
-        const cols_node * prev = args.count > 0 ? &args.nodes[args.count - 1] : nullptr;
-        if (prev && prev->x == x && prev->k == k && prev->n == n && prev->x_stride == (int) (x_stride_bytes / 4)) {
-            nd.yq = prev->yq; nd.ym = prev->ym; nd.quantize = 0;     // same activations as the previous node (gate/up, q/k/v)
+        static const int use_ring = env_int("GGML_B200_COLS_RING", 1);
+        cols_args & A = (type != T_Q6_K && use_ring) ? ring : args;
+        const int tile = &A == &ring ? RING_ROWS : 16;
+        cols_node & nd = A.nodes[A.count];
+        if (last_x == x && last_k == k && last_n == n && last_stride == x_stride_bytes) {
+            nd.yq = last_yq; nd.ym = last_ym; nd.quantize = 0;     // same activations as the node before (gate/up, q/k/v)
         } else {
             const size_t need = cols_ws_bytes(k, n);
             if (need > cur.left) return false;
             nd.yq = reinterpret_cast<int8_t *>(cur.p);
             nd.ym = cur.p + (((size_t) COLS_N * k + 127) & ~(size_t) 127);
             nd.quantize = 1; cur.p += need; cur.left -= need;
+            last_x = x; last_k = k; last_n = n; last_stride = x_stride_bytes; last_yq = nd.yq; last_ym = nd.ym;
         }
         nd.w = w; nd.x = x; nd.dst = dst; nd.row_stride = row_stride; nd.m = (int) m; nd.k = (int) k; nd.n = (int) n;
-        nd.x_stride = (int) (x_stride_bytes / 4); nd.unit0 = args.units; nd.type = (unsigned char) type; nd.pad[0] = nd.pad[1] = 0;
-        args.units += (int) ((m + 15) / 16);
-        if (nd.k > args.kmax) args.kmax = nd.k;
-        args.count++;
+        nd.x_stride = (int) (x_stride_bytes / 4); nd.unit0 = A.units; nd.type = (unsigned char) type; nd.pad[0] = nd.pad[1] = 0;
+        A.units += (int) ((m + tile - 1) / tile);
+        if (nd.k > A.kmax) A.kmax = nd.k;
+        A.count++;
         return true;
     }
 };
@@ -476,27 +659,43 @@ struct cols_builder {
 static int cols_launch(cols_builder & cb, cudaStream_t st) {
     if (cb.empty()) return B200_OK;
     const dev_caps & caps = current_caps();
-    cols_args & a = cb.args;
     static const int pdl = env_int("GGML_B200_FUSED_PDL", 1);
-    {
-        const dim3 grid((unsigned) (a.kmax / 256), (unsigned) a.count, COLS_N);
-        k_quantize_cols<<<grid, 256, 0, st>>>(a);
+    // 1. the activations of both lists (a node that shares them with an earlier node of either list does nothing)
+    for (cols_args * A : { &cb.ring, &cb.args }) {
+        if (A->count == 0) continue;
+        const dim3 grid((unsigned) (A->kmax / 256), (unsigned) A->count, COLS_N);
+        k_quantize_cols<<<grid, 256, 0, st>>>(*A);
         b200_count_launch(1);
     }
-    int ctas = caps.sm_count * COLS_CTAS;
-    if (ctas > a.units) ctas = a.units;
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned) ctas); cfg.blockDim = dim3(COLS_NW * 32);
-    cfg.dynamicSmemBytes = 0; cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
-    // (whole tiles per warp, k_mmvq_cols<1>, measured 7 % slower than the K split even on long lists,
-    // profiles/r01o_bs_probe.txt; that instantiation is no longer built)
-    const cudaError_t e = cudaLaunchKernelEx(&cfg, k_mmvq_cols<8>, a);
-    if (e != cudaSuccess) return -(int) e;
-    b200_count_launch(1);
+    // 2. Q4_K / Q5_K tiles through the TMA ring (starts streaming weights while the quantizers drain)
+    if (cb.ring.count) {
+        static smem_limit lim;
+        if (const int rc = lim.ensure(k_mmvq_cols_ring, RING_SMEM)) return rc;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned) min(caps.sm_count, cb.ring.units)); cfg.blockDim = dim3(RING_THREADS);
+        cfg.dynamicSmemBytes = RING_SMEM; cfg.stream = st;
+        cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
+        const cudaError_t e = cudaLaunchKernelEx(&cfg, k_mmvq_cols_ring, cb.ring);
+        if (e != cudaSuccess) return -(int) e;
+        b200_count_launch(1);
+    }
+    // 3. Q6_K tiles (per-lane loads behind L2 prefetches)
+    if (cb.args.count) {
+        cols_args & a = cb.args;
+        int ctas = caps.sm_count * COLS_CTAS;
+        if (ctas > a.units) ctas = a.units;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned) ctas); cfg.blockDim = dim3(COLS_NW * 32);
+        cfg.dynamicSmemBytes = 0; cfg.stream = st;
+        cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
+        static const int ks1 = env_int("GGML_B200_COLS_KS", 8) == 1;      // tuning: whole tiles per warp instead of the K split
+        const cudaError_t e = ks1 ? cudaLaunchKernelEx(&cfg, k_mmvq_cols<1>, a) : cudaLaunchKernelEx(&cfg, k_mmvq_cols<8>, a);
+        if (e != cudaSuccess) return -(int) e;
+        b200_count_launch(1);
+    }
     return B200_OK;
 }
 
