@@ -265,33 +265,39 @@ struct cols_item6 {
     uint32_t sc[4];           // 16 int8 scales
     uint32_t d;               // f16 bits
 };
-template <bool ODD>
-__device__ __forceinline__ uint32_t cols_ld6(const uint8_t * blk, int off) {
-    if (!ODD) return ldg_stream32(blk + off);
-    return __funnelshift_r(ldg_stream32(blk + off - 2), ldg_stream32(blk + off + 2), 16);
+template <bool SMEM> __device__ __forceinline__ uint32_t cols_ld32(const uint8_t * p) {
+    if (SMEM) return *reinterpret_cast<const uint32_t *>(p);
+    return ldg_stream32(p);
 }
-template <bool ODD>
+template <bool ODD, bool SMEM>
+__device__ __forceinline__ uint32_t cols_ld6(const uint8_t * blk, int off) {
+    if (!ODD) return cols_ld32<SMEM>(blk + off);
+    return __funnelshift_r(cols_ld32<SMEM>(blk + off - 2), cols_ld32<SMEM>(blk + off + 2), 16);
+}
+template <bool ODD, bool SMEM = false>
 __device__ __forceinline__ void cols_load6(cols_item6 & it, const uint8_t * blk, int t) {
 #pragma unroll
     for (int h = 0; h < 2; h++)
 #pragma unroll
         for (int s = 0; s < 2; s++) {
-            it.ql[h][0][s] = cols_ld6<ODD>(blk, 64 * h + 16 * s + 4 * t);
-            it.ql[h][1][s] = cols_ld6<ODD>(blk, 64 * h + 32 + 16 * s + 4 * t);
-            it.qh[h][s]    = cols_ld6<ODD>(blk, 128 + 32 * h + 16 * s + 4 * t);
+            it.ql[h][0][s] = cols_ld6<ODD, SMEM>(blk, 64 * h + 16 * s + 4 * t);
+            it.ql[h][1][s] = cols_ld6<ODD, SMEM>(blk, 64 * h + 32 + 16 * s + 4 * t);
+            it.qh[h][s]    = cols_ld6<ODD, SMEM>(blk, 128 + 32 * h + 16 * s + 4 * t);
         }
     if (!ODD) {
 #pragma unroll
-        for (int i = 0; i < 4; i++) it.sc[i] = ldg_stream32(blk + 192 + 4 * i);
+        for (int i = 0; i < 4; i++) it.sc[i] = cols_ld32<SMEM>(blk + 192 + 4 * i);
     } else {
         uint32_t w[5];
 #pragma unroll
-        for (int i = 0; i < 5; i++) w[i] = ldg_stream32(blk + 190 + 4 * i);
+        for (int i = 0; i < 5; i++) w[i] = cols_ld32<SMEM>(blk + 190 + 4 * i);
 #pragma unroll
         for (int i = 0; i < 4; i++) it.sc[i] = __funnelshift_r(w[i], w[i + 1], 16);
     }
     it.d = *reinterpret_cast<const unsigned short *>(blk + 208);
 }
+// yq_col: the column's int8 plane, [32-block][8 columns][32] from block 8 * item on (global memory, or the stage of the ring)
+template <bool SMEM = false>
 __device__ __forceinline__ void cols_item6_mma(const cols_item6 & ia, const cols_item6 & ib, int item, int t,
                                                const int8_t * yq_col, const float2 dy, const uint2 s16, bool col_ok, float (&acc)[4]) {
     int ai[4] = { 0, 0, 0, 0 };
@@ -301,7 +307,8 @@ __device__ __forceinline__ void cols_item6_mma(const cols_item6 & ia, const cols
         const uint32_t a0 = ((ia.ql[h][r & 1][s] >> (4 * (r >> 1))) & 0x0F0F0F0Fu) | (((ia.qh[h][s] >> (2 * r)) & 0x03030303u) << 4);
         const uint32_t a1 = ((ib.ql[h][r & 1][s] >> (4 * (r >> 1))) & 0x0F0F0F0Fu) | (((ib.qh[h][s] >> (2 * r)) & 0x03030303u) << 4);
         uint32_t b0 = 0u;
-        if (col_ok) b0 = __ldg(reinterpret_cast<const uint32_t *>(yq_col + (size_t) B * (32 * COLS_N) + 16 * s + 4 * t));
+        if (SMEM) b0 = *reinterpret_cast<const uint32_t *>(yq_col + B * (32 * COLS_N) + 16 * s + 4 * t);
+        else if (col_ok) b0 = __ldg(reinterpret_cast<const uint32_t *>(yq_col + (size_t) B * (32 * COLS_N) + 16 * s + 4 * t));
         int c[4];
         mma_16x8x16<false>(c, a0, a1, b0);
         constexpr int si = 8 * h + 2 * r + s;                       // scale of this 16-weight group
@@ -478,27 +485,38 @@ constexpr int RING_NPROD    = 3;                   // producer warps: a bulk cop
 constexpr int RING_THREADS  = (RING_NWC + RING_NPROD + 1) * 32;   // consumers + producers + epilogue warp (20 warps: 96 registers)
 constexpr int RING_CI       = 8;                   // super-blocks per chunk
 constexpr int RING_ROWS     = 32;
-constexpr int RING_PITCH_MAX = RING_CI * 176 + 32;  // 1440 (Q5_K); Q4_K rows use 1184 of it
-constexpr int RING_OFF_YQ   = RING_ROWS * RING_PITCH_MAX;      // 46080: the chunk's activations follow its weights:
-constexpr int RING_OFF_D    = RING_OFF_YQ + RING_CI * 8 * 32 * COLS_N;     //   int8 [8 super-blocks][8 sub-blocks][8 columns][32]
-constexpr int RING_OFF_S32  = RING_OFF_D + RING_CI * COLS_N * 4;           //   f32 d [8][8 columns]
-constexpr int RING_STAGE    = RING_OFF_S32 + RING_CI * COLS_N * 16;        //   sums of 32 [8][8 columns][2] uint2  -> 63744
 constexpr int RING_STAGES   = 3;
-constexpr int RING_OFF_RED  = RING_STAGES * RING_STAGE;        // float red[2][RING_NWC][128]
-constexpr int RING_OFF_BAR  = RING_OFF_RED + 2 * RING_NWC * 128 * 4;
-constexpr int RING_SMEM     = RING_OFF_BAR + 128;
+// shared-memory geometry of a family: 0 = Q4_K / Q5_K (rows of 8 x 144 / 176 bytes + 32: pitch = 32 mod 128, the 8-byte
+// fragment loads of the 8 row groups cover every bank twice), 1 = Q6_K (8 x 210 = 1680 = 16 mod 128: its 4-byte loads, 16
+// bytes per row group, cover every bank once).  A stage = the chunk's weights, then the matching slice of the activations:
+//   int8 [8 super-blocks][8 sub-blocks][8 columns][32] | f32 d [8][8 columns] | sums of 32 [8][8][2] uint2 or sums of 16 [8][8][4] uint2
+template <int FAM> struct ring_geo {
+    static constexpr int pitch_max = FAM ? RING_CI * 210 : RING_CI * 176 + 32;
+    static constexpr int off_yq    = RING_ROWS * pitch_max;
+    static constexpr int off_d     = off_yq + RING_CI * 8 * 32 * COLS_N;
+    static constexpr int off_s     = off_d + RING_CI * COLS_N * 4;
+    static constexpr int s_bytes   = FAM ? COLS_N * 32 : COLS_N * 16;           // per super-block
+    static constexpr int stage     = off_s + RING_CI * s_bytes;                 // 63744 / 72448
+    static constexpr int off_red   = RING_STAGES * stage;                       // float red[RING_NWC][128]
+    static constexpr int off_bar   = off_red + RING_NWC * 128 * 4;
+    static constexpr int smem      = off_bar + 128;                             // 199552 / 225664
+};
+static_assert(ring_geo<1>::smem <= 232448, "the Q6_K ring must fit the 227 KB of shared memory a CTA can have");
+__device__ __forceinline__ int ring_pitch(int type) { return type == T_Q6_K ? RING_CI * 210 : (type == T_Q5_K ? RING_CI * 176 + 32 : RING_CI * 144 + 32); }
 
 __device__ __forceinline__ uint2 lds64(const uint8_t * p) { return *reinterpret_cast<const uint2 *>(p); }
 
+template <int FAM>
 __global__ void __launch_bounds__(RING_THREADS, 1) k_mmvq_cols_ring(const __grid_constant__ cols_args a) {
+    using G = ring_geo<FAM>;
     extern __shared__ __align__(128) uint8_t smem[];
-    uint64_t * full = reinterpret_cast<uint64_t *>(smem + RING_OFF_BAR), * empty = full + RING_STAGES;
-    uint64_t * red_full = empty + RING_STAGES, * red_empty = red_full + 2;
-    float (*red)[RING_NWC][128] = reinterpret_cast<float (*)[RING_NWC][128]>(smem + RING_OFF_RED);
+    uint64_t * full = reinterpret_cast<uint64_t *>(smem + G::off_bar), * empty = full + RING_STAGES;
+    uint64_t * red_full = empty + RING_STAGES, * red_empty = red_full + 1;
+    float (*red)[128] = reinterpret_cast<float (*)[128]>(smem + G::off_red);     // one buffer: the epilogue is done with a tile long before the next one ends
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
         for (int s = 0; s < RING_STAGES; s++) { mbar_init(&full[s], RING_NPROD); mbar_init(&empty[s], RING_NWC); }
-        for (int b = 0; b < 2; b++) { mbar_init(&red_full[b], RING_NWC); mbar_init(&red_empty[b], 1); }
+        mbar_init(red_full, RING_NWC); mbar_init(red_empty, 1);
         mbar_fence_init();
     }
     __syncthreads();
@@ -511,93 +529,102 @@ __global__ void __launch_bounds__(RING_THREADS, 1) k_mmvq_cols_ring(const __grid
         for (int u = blockIdx.x; u < a.units; u += gridDim.x) {
             while (ni + 1 < a.count && u >= a.nodes[ni + 1].unit0) ni++;
             const cols_node & nd = a.nodes[ni];
-            const int row0 = (u - nd.unit0) * RING_ROWS, items = nd.k >> 8, bs = nd.type == T_Q5_K ? 176 : 144;
-            const int rows = min(RING_ROWS, nd.m - row0), pitch = RING_CI * bs + 32;
+            const int row0 = (u - nd.unit0) * RING_ROWS, items = nd.k >> 8, bs = cols_block_bytes(nd.type);
+            const int rows = min(RING_ROWS, nd.m - row0), pitch = ring_pitch(nd.type);
             const int my_rows = max(0, min(rows, r_lo + 11) - r_lo);
             const uint8_t * src = nd.w + (size_t) (row0 + r) * nd.row_stride;
             const cols_meta M = cols_meta_of(nd.ym, nd.k);
             for (int c0 = 0; c0 < items; c0 += RING_CI) {
                 const uint32_t ci = (uint32_t) min(RING_CI, items - c0), bytes = ci * (uint32_t) bs;
-                uint8_t * st = smem + stage * RING_STAGE;
+                uint8_t * st = smem + stage * G::stage;
                 mbar_wait(&empty[stage], phase ^ 1u);
-                const uint32_t abytes = ci * (pw == 0 ? 8 * 32 * COLS_N : (pw == 1 ? COLS_N * 4 : COLS_N * 16));
+                const uint32_t abytes = ci * (pw == 0 ? 8 * 32 * COLS_N : (pw == 1 ? COLS_N * 4 : G::s_bytes));
                 if (lane == 0) mbar_arrive_expect_tx(&full[stage], bytes * (uint32_t) my_rows + abytes);
                 __syncwarp();
                 if (lane < 11 && r < rows) bulk_g2s(st + r * pitch, src + (size_t) c0 * bs, bytes, &full[stage]);
                 if (lane == 11) {
-                    if (pw == 0)      bulk_g2s(st + RING_OFF_YQ, nd.yq + (size_t) c0 * (8 * 32 * COLS_N), abytes, &full[stage]);
-                    else if (pw == 1) bulk_g2s(st + RING_OFF_D, M.d + (size_t) c0 * COLS_N, abytes, &full[stage]);
-                    else              bulk_g2s(st + RING_OFF_S32, M.s32 + (size_t) c0 * COLS_N * 2, abytes, &full[stage]);
+                    if (pw == 0)      bulk_g2s(st + G::off_yq, nd.yq + (size_t) c0 * (8 * 32 * COLS_N), abytes, &full[stage]);
+                    else if (pw == 1) bulk_g2s(st + G::off_d, M.d + (size_t) c0 * COLS_N, abytes, &full[stage]);
+                    else if (FAM)     bulk_g2s(st + G::off_s, M.s16 + (size_t) c0 * COLS_N * 4, abytes, &full[stage]);
+                    else              bulk_g2s(st + G::off_s, M.s32 + (size_t) c0 * COLS_N * 2, abytes, &full[stage]);
                 }
                 if (++stage == RING_STAGES) { stage = 0; phase ^= 1u; }
             }
         }
     } else if (warp == RING_NWC + RING_NPROD) {
         // ---------------- epilogue: sum the eight partial tiles of each row half in warp order, store
-        int par = 0; uint32_t rphase = 0;
-        for (int u = blockIdx.x; u < a.units; u += gridDim.x) {
+        uint32_t rphase = 0;
+        for (int u = blockIdx.x; u < a.units; u += gridDim.x, rphase ^= 1u) {
             while (ni + 1 < a.count && u >= a.nodes[ni + 1].unit0) ni++;
             const cols_node & nd = a.nodes[ni];
             const int row0 = (u - nd.unit0) * RING_ROWS;
-            mbar_wait(&red_full[par], rphase);
+            mbar_wait(red_full, rphase);
 #pragma unroll
             for (int j = 0; j < 8; j++) {
                 const int e = lane + 32 * j, half = e >> 7, idx = e & 127, l = idx >> 2, i = idx & 3;
                 float v = 0.0f;
 #pragma unroll
-                for (int w = 0; w < 8; w++) v += red[par][half * 8 + w][idx];
+                for (int w = 0; w < 8; w++) v += red[half * 8 + w][idx];
                 // c fragment layout: element i of lane l = (g, t): row g + 8 (i >> 1), column 2t + (i & 1)
                 const int row = row0 + 16 * half + (l >> 2) + 8 * (i >> 1), col = 2 * (l & 3) + (i & 1);
                 if (row < nd.m && col < nd.n) nd.dst[(size_t) col * nd.m + row] = v;
             }
             __syncwarp();
-            if (lane == 0) mbar_arrive_cta(&red_empty[par]);
-            if ((par ^= 1) == 0) rphase ^= 1u;
+            if (lane == 0) mbar_arrive_cta(red_empty);
         }
     } else {
         // ---------------- consumers
         const int g = lane >> 2, t = lane & 3, half = warp >> 3, slot = warp & 7;
-        int stage = 0, par = 0; uint32_t phase = 0, rphase = 0;
-        for (int u = blockIdx.x; u < a.units; u += gridDim.x) {
+        int stage = 0; uint32_t phase = 0, rphase = 0;
+        for (int u = blockIdx.x; u < a.units; u += gridDim.x, rphase ^= 1u) {
             while (ni + 1 < a.count && u >= a.nodes[ni + 1].unit0) ni++;
             const cols_node & nd = a.nodes[ni];
             const int items = nd.k >> 8;
             const bool q5 = nd.type == T_Q5_K;
-            const int bs = q5 ? 176 : 144, pitch = RING_CI * bs + 32;
+            const int bs = cols_block_bytes(nd.type), pitch = ring_pitch(nd.type);
             float acc[4] = { 0.0f, 0.0f, 0.0f, 0.0f };
             for (int c0 = 0; c0 < items; c0 += RING_CI) {
                 mbar_wait(&full[stage], phase);
                 if (c0 + slot < items) {
-                    const uint8_t * st = smem + stage * RING_STAGE;
+                    const uint8_t * st = smem + stage * G::stage;
                     const uint8_t * ra = st + (16 * half + g) * pitch + slot * bs, * rb = ra + 8 * pitch;
-                    uint2 b[8];          // columns >= n hold whatever the workspace held: their results are never stored
-#pragma unroll
-                    for (int q = 0; q < 8; q++) b[q] = lds64(st + RING_OFF_YQ + (slot * 8 + q) * (32 * COLS_N) + g * 32 + 8 * t);
-                    const uint2 dyb = lds64(st + RING_OFF_D + slot * (COLS_N * 4) + 8 * t);                 // columns 2t, 2t + 1
+                    const uint2 dyb = lds64(st + G::off_d + slot * (COLS_N * 4) + 8 * t);                   // columns 2t, 2t + 1
                     const float2 dy = make_float2(__uint_as_float(dyb.x), __uint_as_float(dyb.y));
-                    uint2 s32 = make_uint2(0u, 0u);
-                    if (t < 2) s32 = lds64(st + RING_OFF_S32 + (slot * COLS_N + g) * 16 + 8 * t);           // column g, sub-blocks 4t..4t+3
-                    cols_item ia, ib;
-                    ia.hdr = lds128(ra); ib.hdr = lds128(rb);
-                    const int qo = (q5 ? 48 : 16) + 8 * t;
-#pragma unroll
-                    for (int p = 0; p < 4; p++) { ia.q[p] = lds64(ra + qo + 32 * p); ib.q[p] = lds64(rb + qo + 32 * p); }
-                    if (q5) {
-                        ia.h = lds64(ra + 16 + 8 * t); ib.h = lds64(rb + 16 + 8 * t);
-                        cols_sb_mma<true>(ia, ib, b, dy, s32, t, acc, nullptr, nullptr, false);
+                    // (columns >= n hold whatever the workspace held: their results are never stored)
+                    if (FAM) {
+                        const uint2 s16 = lds64(st + G::off_s + (slot * COLS_N + g) * 32 + 8 * t);          // column g, groups 4t..4t+3
+                        const int8_t * yq = reinterpret_cast<const int8_t *>(st + G::off_yq) + g * 32;
+                        cols_item6 ia, ib;
+                        if (slot & 1) { cols_load6<true, true>(ia, ra, t);  cols_load6<true, true>(ib, rb, t); }
+                        else          { cols_load6<false, true>(ia, ra, t); cols_load6<false, true>(ib, rb, t); }
+                        cols_item6_mma<true>(ia, ib, slot, t, yq, dy, s16, true, acc);
                     } else {
-                        cols_sb_mma<false>(ia, ib, b, dy, s32, t, acc, nullptr, nullptr, false);
+                        uint2 b[8];
+#pragma unroll
+                        for (int q = 0; q < 8; q++) b[q] = lds64(st + G::off_yq + (slot * 8 + q) * (32 * COLS_N) + g * 32 + 8 * t);
+                        uint2 s32 = make_uint2(0u, 0u);
+                        if (t < 2) s32 = lds64(st + G::off_s + (slot * COLS_N + g) * 16 + 8 * t);           // column g, sub-blocks 4t..4t+3
+                        cols_item ia, ib;
+                        ia.hdr = lds128(ra); ib.hdr = lds128(rb);
+                        const int qo = (q5 ? 48 : 16) + 8 * t;
+#pragma unroll
+                        for (int p = 0; p < 4; p++) { ia.q[p] = lds64(ra + qo + 32 * p); ib.q[p] = lds64(rb + qo + 32 * p); }
+                        if (q5) {
+                            ia.h = lds64(ra + 16 + 8 * t); ib.h = lds64(rb + 16 + 8 * t);
+                            cols_sb_mma<true>(ia, ib, b, dy, s32, t, acc, nullptr, nullptr, false);
+                        } else {
+                            cols_sb_mma<false>(ia, ib, b, dy, s32, t, acc, nullptr, nullptr, false);
+                        }
                     }
                 }
                 __syncwarp();
                 if (lane == 0) mbar_arrive_cta(&empty[stage]);
                 if (++stage == RING_STAGES) { stage = 0; phase ^= 1u; }
             }
-            mbar_wait(&red_empty[par], rphase ^ 1u);             // the epilogue has read this buffer's previous tile
-            *reinterpret_cast<float4 *>(&red[par][warp][lane * 4]) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+            mbar_wait(red_empty, rphase ^ 1u);                   // the epilogue has read the previous tile
+            *reinterpret_cast<float4 *>(&red[warp][lane * 4]) = make_float4(acc[0], acc[1], acc[2], acc[3]);
             __syncwarp();
-            if (lane == 0) mbar_arrive_cta(&red_full[par]);
-            if ((par ^= 1) == 0) rphase ^= 1u;
+            if (lane == 0) mbar_arrive_cta(red_full);
         }
     }
 }
@@ -618,24 +645,26 @@ static inline size_t cols_ws_bytes(int64_t k, int64_t n) {
 }
 
 struct cols_builder {
-    cols_args args;       // Q6_K nodes: k_mmvq_cols, 16-row tiles
-    cols_args ring;       // Q4_K / Q5_K nodes: k_mmvq_cols_ring, 32-row tiles
+    cols_args args;       // tuning (GGML_B200_COLS_RING=0): k_mmvq_cols, 16-row tiles
+    cols_args ring;       // Q4_K / Q5_K nodes: k_mmvq_cols_ring<0>, 32-row tiles
+    cols_args ring6;      // Q6_K nodes: k_mmvq_cols_ring<1>
     // the activations quantized last (nodes of either list that read the same x share them: q/k/v, gate/up)
     const float * last_x; int64_t last_k, last_n, last_stride; int8_t * last_yq; uint8_t * last_ym;
     cols_builder() { reset(); }
     void reset() {
         args.count = 0; args.units = 0; args.kmax = 0; args.pad = 0;
         ring.count = 0; ring.units = 0; ring.kmax = 0; ring.pad = 0;
+        ring6.count = 0; ring6.units = 0; ring6.kmax = 0; ring6.pad = 0;
         last_x = nullptr; last_k = last_n = last_stride = 0; last_yq = nullptr; last_ym = nullptr;
     }
-    bool full() const { return args.count >= COLS_MAX_NODES || ring.count >= COLS_MAX_NODES; }
-    bool empty() const { return args.count == 0 && ring.count == 0; }
-    int  count() const { return args.count + ring.count; }
+    bool full() const { return args.count >= COLS_MAX_NODES || ring.count >= COLS_MAX_NODES || ring6.count >= COLS_MAX_NODES; }
+    bool empty() const { return args.count == 0 && ring.count == 0 && ring6.count == 0; }
+    int  count() const { return args.count + ring.count + ring6.count; }
     bool add(int type, const uint8_t * w, int64_t row_stride, int64_t m, int64_t k, const float * x, int64_t x_stride_bytes,
              int64_t n, float * dst, ws_cursor & cur) {
         static const int use_ring = env_int("GGML_B200_COLS_RING", 1);
-        cols_args & A = (type != T_Q6_K && use_ring) ? ring : args;
-        const int tile = &A == &ring ? RING_ROWS : 16;
+        cols_args & A = !use_ring ? args : (type == T_Q6_K ? ring6 : ring);
+        const int tile = use_ring ? RING_ROWS : 16;
         cols_node & nd = A.nodes[A.count];
         if (last_x == x && last_k == k && last_n == n && last_stride == x_stride_bytes) {
             nd.yq = last_yq; nd.ym = last_ym; nd.quantize = 0;     // same activations as the node before (gate/up, q/k/v)
@@ -661,7 +690,7 @@ static int cols_launch(cols_builder & cb, cudaStream_t st) {
     const dev_caps & caps = current_caps();
     static const int pdl = env_int("GGML_B200_FUSED_PDL", 1);
     // 1. the activations of both lists (a node that shares them with an earlier node of either list does nothing)
-    for (cols_args * A : { &cb.ring, &cb.args }) {
+    for (cols_args * A : { &cb.ring, &cb.ring6, &cb.args }) {
         if (A->count == 0) continue;
         const dim3 grid((unsigned) (A->kmax / 256), (unsigned) A->count, COLS_N);
         k_quantize_cols<<<grid, 256, 0, st>>>(*A);
@@ -670,19 +699,22 @@ static int cols_launch(cols_builder & cb, cudaStream_t st) {
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
-    // 2. Q4_K / Q5_K tiles through the TMA ring (starts streaming weights while the quantizers drain)
-    if (cb.ring.count) {
-        static smem_limit lim;
-        if (const int rc = lim.ensure(k_mmvq_cols_ring, RING_SMEM)) return rc;
+    // 2. the tiles through the TMA ring, one launch per family (starts while the quantizers drain)
+    auto ring_launch = [&](auto kern, size_t smem, cols_args & A, smem_limit & lim) -> int {
+        if (const int rc = lim.ensure(kern, smem)) return rc;
         cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3((unsigned) min(caps.sm_count, cb.ring.units)); cfg.blockDim = dim3(RING_THREADS);
-        cfg.dynamicSmemBytes = RING_SMEM; cfg.stream = st;
+        cfg.gridDim = dim3((unsigned) min(caps.sm_count, A.units)); cfg.blockDim = dim3(RING_THREADS);
+        cfg.dynamicSmemBytes = smem; cfg.stream = st;
         cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
-        const cudaError_t e = cudaLaunchKernelEx(&cfg, k_mmvq_cols_ring, cb.ring);
+        const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, A);
         if (e != cudaSuccess) return -(int) e;
         b200_count_launch(1);
-    }
-    // 3. Q6_K tiles (per-lane loads behind L2 prefetches)
+        return B200_OK;
+    };
+    static smem_limit lim0, lim1;
+    if (cb.ring.count)  { if (const int rc = ring_launch(k_mmvq_cols_ring<0>, ring_geo<0>::smem, cb.ring, lim0)) return rc; }
+    if (cb.ring6.count) { if (const int rc = ring_launch(k_mmvq_cols_ring<1>, ring_geo<1>::smem, cb.ring6, lim1)) return rc; }
+    // 3. tuning fallback: per-lane loads behind L2 prefetches
     if (cb.args.count) {
         cols_args & a = cb.args;
         int ctas = caps.sm_count * COLS_CTAS;
