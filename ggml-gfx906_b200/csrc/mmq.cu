@@ -35,7 +35,7 @@ encode_tiled_fn get_encode_tiled() {
 template <int T, int BN, bool ALIGNED>
 int launch_mmq(const mmq_args & a, const CUtensorMap & tmap, const CUtensorMap & tmap_w, cudaStream_t st) {
     auto kern = k_mmq_tc<T, BN, ALIGNED>;
-    const size_t smem = mmq_smem<BN>::total(a.raw_pitch, mmq_rs<T>::value);
+    const size_t smem = mmq_smem<BN>::total(a.raw_pitch, mmq_rs<T, BN>::value);
     static smem_limit lim;
     if (const int rc = lim.ensure(kern, smem)) return rc;
     const dim3 grid((unsigned) ceil_div(a.m, MMQ_BM), (unsigned) ceil_div(a.n, BN));
@@ -58,12 +58,16 @@ int launch_mmq_bn(const mmq_args & a, const CUtensorMap & tmap, const CUtensorMa
         case 32:  return launch_mmq_al<T, 32>(a, tmap, tmap_w, aligned, st);
         case 64:  return launch_mmq_al<T, 64>(a, tmap, tmap_w, aligned, st);
         case 128: return launch_mmq_al<T, 128>(a, tmap, tmap_w, aligned, st);
+        case 512: if constexpr (T != T_Q8_0) return launch_mmq_al<T, 512>(a, tmap, tmap_w, aligned, st);     // (Q8_0: pick_bn never says 512)
         default:  return launch_mmq_al<T, 256>(a, tmap, tmap_w, aligned, st);
     }
 }
 
-int pick_bn(int64_t m, int64_t n, int sm_count) {
+int pick_bn(int type, int64_t m, int64_t n, int sm_count) {
     const int forced = b200_option(B200_OPT_MMQ_BN);
+    // 512 columns = two 256-column accumulators per CTA; Q8_0's 272-byte raw slabs do not fit beside two 64 KB activation stages
+    const bool can512 = type != T_Q8_0;
+    if (forced == 512 && can512) return 512;
     if (forced == 32 || forced == 64 || forced == 128 || forced == 256) return forced;
     if (n <= 32) return 32;
     if (n <= 64) return 64;
@@ -73,6 +77,12 @@ int pick_bn(int64_t m, int64_t n, int sm_count) {
     const int64_t tm = ceil_div(m, MMQ_BM);
     const int64_t w128 = ceil_div(tm * ceil_div(n, 128), sm_count) * (600 + 128);
     const int64_t w256 = ceil_div(tm * ceil_div(n, 256), sm_count) * (600 + 256);
+    // .. and a 512-column tile (two accumulators fed by one expansion) measured 1.76 x the stage time of a 256-column one
+    // (14336x4096 at n = 2048: 4 waves in 257 us against 7 waves in 256 us, profiles/r03j_prefill_bn512.txt -- with two
+    // N = 256 MMAs per 16-deep step the stage is bound by shared-memory bandwidth: A is read twice): it wins where it
+    // saves waves
+    const int64_t w512 = ceil_div(tm * ceil_div(n, 512), sm_count) * 1507;
+    if (can512 && n > 256 && w512 < w256 && w512 < w128) return 512;
     return w256 <= w128 ? 256 : 128;
 }
 
@@ -195,13 +205,13 @@ extern "C" int b200_mul_mat_q(int type, const void * w_dev, size_t w_row_stride_
 
     // 2. TMA descriptor over the bf16 activations: dims {k, n}, box {64, BN}, 128-byte swizzle, zero fill
     const dev_caps & caps = current_caps();
-    const int bn = pick_bn(m, n, caps.sm_count);
+    const int bn = pick_bn(type, m, n, caps.sm_count);
     encode_tiled_fn encode = get_encode_tiled();
     if (!encode) return B200_ERR_NO_DEVICE;
     CUtensorMap tmap;
     const cuuint64_t gdim[2]    = { (cuuint64_t) k, (cuuint64_t) n };
     const cuuint64_t gstride[1] = { (cuuint64_t) k * sizeof(__nv_bfloat16) };
-    const cuuint32_t box[2]     = { (cuuint32_t) MMQ_BK, (cuuint32_t) bn };
+    const cuuint32_t box[2]     = { (cuuint32_t) MMQ_BK, (cuuint32_t) (bn > 256 ? 256 : bn) };   // (512: two boxes per stage)
     const cuuint32_t estr[2]    = { 1, 1 };
     const CUresult cr = encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, xb, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);

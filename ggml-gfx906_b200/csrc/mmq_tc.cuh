@@ -347,7 +347,7 @@ struct mmq_args {
 constexpr int MMQ_BM = 128;
 constexpr int MMQ_BK = 64;           // K elements per MMA stage (one 128-byte swizzle row)
 constexpr int MMQ_RS = 3;            // raw slab ring depth (2 for the formats with slabs > 200 bytes: shared memory)
-template <int T> struct mmq_rs { static constexpr int value = slab<T>::bytes > 200 ? 2 : MMQ_RS; };
+template <int T, int BN = 256> struct mmq_rs { static constexpr int value = (slab<T>::bytes > 200 || BN > 256) ? 2 : MMQ_RS; };
 constexpr int MMQ_THREADS = 320;      // 8 weight-producer warps (two threads per row) + activation loader + MMA issuer
 #ifndef MMQ_STAGES_SMALL
 #define MMQ_STAGES_SMALL 4
@@ -359,11 +359,15 @@ constexpr int MMQ_THREADS = 320;      // 8 weight-producer warps (two threads pe
 template <int BN> struct mmq_cfg {
     // (tried: 2 stages + 2 CTAs per SM for BN <= 128 to double the weight-expansion producers per tensor pipe:
     //  no gain at n = 512, profiles/r01g_prefill_probe.txt; -DMMQ_STAGES_SMALL=2 -DMMQ_CTAS_SMALL=2 rebuilds it)
-    static constexpr int stages   = BN <= 128 ? MMQ_STAGES_SMALL : 3;
+    // BN = 512: two 256-column accumulators (all 512 TMEM columns) fed by ONE expansion of the weights -- the weight
+    // producers, not the tensor pipe, bound this kernel (~1200 cycles per 64-deep stage whatever BN), so the second
+    // accumulator's MMAs are nearly free; its 64 KB activation stages leave room for two stages only
+    static constexpr int stages   = BN <= 128 ? MMQ_STAGES_SMALL : (BN > 256 ? 2 : 3);
     static constexpr int ctas_per_sm = BN <= 128 ? MMQ_CTAS_SMALL : 1;
     static constexpr int a_bytes  = MMQ_BM * 128;
     static constexpr int b_bytes  = BN * 128;
     static constexpr int tmem_cols = BN < 32 ? 32 : BN;
+    static constexpr int halves   = BN > 256 ? 2 : 1;          // MMAs of N = BN / halves (N <= 256 per instruction)
 };
 
 // dynamic shared memory map (offsets from a 1024-byte aligned base)
@@ -382,7 +386,8 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b, const __g
     constexpr int ST = CFG::stages;
     constexpr int SLAB_ELEMS = 256;
     constexpr int BLK_PER_SLAB = SLAB_ELEMS / fmt<T>::qk;       // 1 or 8
-    constexpr int RS = mmq_rs<T>::value;
+    constexpr int RS = mmq_rs<T, BN>::value;
+    constexpr int NH = CFG::halves, BNH = BN / NH;
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t * smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t) 1023);
@@ -541,7 +546,9 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b, const __g
                 const int st = kt % ST;
                 if (kt >= ST) mbar_wait(&empty[st], (uint32_t) (((kt / ST) - 1) & 1));
                 mbar_arrive_expect_tx(&full[st], (uint32_t) CFG::b_bytes);
-                tma_load_2d(b_tiles + (size_t) st * CFG::b_bytes, &tmap_b, kt * MMQ_BK, (int) n0, &full[st]);
+#pragma unroll
+                for (int h = 0; h < NH; h++)       // a TMA box has at most 256 rows
+                    tma_load_2d(b_tiles + (size_t) st * CFG::b_bytes + (size_t) h * BNH * 128, &tmap_b, kt * MMQ_BK, (int) n0 + h * BNH, &full[st]);
             }
         }
     } else {
@@ -549,17 +556,20 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b, const __g
         if (lane == 0) {
             // instruction descriptor: D=f32, A=bf16, B=bf16 (kind::f16 rejects mixed f16 x bf16 operands: measured,
             // illegal instruction), both K-major, N=BN, M=128
-            constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t) (BN >> 3) << 17) | ((uint32_t) (MMQ_BM >> 4) << 24);
+            constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t) (BNH >> 3) << 17) | ((uint32_t) (MMQ_BM >> 4) << 24);
             for (int kt = 0; kt < nkt; kt++) {
                 const int st = kt % ST;
                 mbar_wait(&full[st], (uint32_t) ((kt / ST) & 1));
                 tc_fence_after();
                 const uint64_t da = umma_desc_sw128(a_tiles + (size_t) st * CFG::a_bytes);
-                const uint64_t db = umma_desc_sw128(b_tiles + (size_t) st * CFG::b_bytes);
 #pragma unroll
-                for (int k4 = 0; k4 < MMQ_BK / 16; k4++) {
-                    // +32 bytes (2 x 16-byte units) along K inside the 128-byte swizzle row
-                    umma_f16(tmem_base, da + (uint64_t) (2 * k4), db + (uint64_t) (2 * k4), idesc, (kt > 0 || k4 > 0) ? 1u : 0u);
+                for (int h = 0; h < NH; h++) {
+                    const uint64_t db = umma_desc_sw128(b_tiles + (size_t) st * CFG::b_bytes + (size_t) h * BNH * 128);
+#pragma unroll
+                    for (int k4 = 0; k4 < MMQ_BK / 16; k4++) {
+                        // +32 bytes (2 x 16-byte units) along K inside the 128-byte swizzle row
+                        umma_f16(tmem_base + (uint32_t) (h * BNH), da + (uint64_t) (2 * k4), db + (uint64_t) (2 * k4), idesc, (kt > 0 || k4 > 0) ? 1u : 0u);
+                    }
                 }
                 umma_commit(&empty[st]);             // frees the stage when these MMAs retire
             }

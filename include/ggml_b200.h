@@ -74,7 +74,7 @@ enum b200_option {
     B200_OPT_MMVQ_NO_FUSED       = 1, /* GGML_B200_MMVQ_NO_FUSED=1: n = 1 without the fused quantize + mat-vec kernel */
     B200_OPT_BATCH_SINGLE        = 2, /* GGML_B200_BATCH_SINGLE=1/0: a one-node list takes the persistent / the per-node kernel (-1: by size) */
     B200_OPT_NO_BATCH_KERNEL     = 3, /* GGML_B200_NO_BATCH_KERNEL=1: lists run as one launch per node */
-    B200_OPT_MMQ_BN              = 4, /* GGML_B200_MMQ_BN=32|64|128|256: tile width of the batched kernel */
+    B200_OPT_MMQ_BN              = 4, /* GGML_B200_MMQ_BN=32|64|128|256|512: tile width of the batched kernel */
     B200_OPT_MMQ_FORCE_UNALIGNED = 5, /* GGML_B200_MMQ_FORCE_UNALIGNED=1: per-row raw copies instead of TMA slab tiles */
     B200_OPT_NO_CHAIN            = 6, /* GGML_B200_NO_CHAIN=1: a list is cut at every read-after-write instead of chaining inside one launch */
     B200_OPT_MMQ_ROUTE           = 7, /* GGML_B200_MMQ_ROUTE=1|2: batched MUL_MAT through the bf16 / the q8_1 int8 tensor-core kernel (0: by shape) */
