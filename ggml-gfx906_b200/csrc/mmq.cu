@@ -38,10 +38,16 @@ int launch_mmq(const mmq_args & a, const CUtensorMap & tmap, const CUtensorMap &
     const size_t smem = mmq_smem<BN>::total(a.raw_pitch, mmq_rs<T, BN>::value);
     static smem_limit lim;
     if (const int rc = lim.ensure(kern, smem)) return rc;
-    const dim3 grid((unsigned) ceil_div(a.m, MMQ_BM), (unsigned) ceil_div(a.n, BN));
+    const dim3 grid((unsigned) ceil_div(a.m, MMQ_BM), (unsigned) ceil_div(a.n, BN), (unsigned) (a.ksplit > 1 ? a.ksplit : 1));
     kern<<<grid, MMQ_THREADS, smem, st>>>(a, tmap, tmap_w);
     b200_count_launch(1);
     B200_RETURN_IF_LAUNCH_FAILED();
+    if (a.ksplit > 1) {
+        const dim3 rgrid((unsigned) ceil_div(a.m, 1024), (unsigned) a.n);
+        k_mmq_reduce<<<rgrid, 256, 0, st>>>(a.part, a.ksplit, a.m, a.n, a.dst, a.dst_col_stride);
+        b200_count_launch(1);
+        B200_RETURN_IF_LAUNCH_FAILED();
+    }
     return B200_OK;
 }
 
@@ -63,7 +69,25 @@ int launch_mmq_bn(const mmq_args & a, const CUtensorMap & tmap, const CUtensorMa
     }
 }
 
-int pick_bn(int type, int64_t m, int64_t n, int sm_count) {
+// Split K when the tiles leave more than half of the SMs idle (4096 x k at n = 512: 32-64 tiles on 148 SMs): z CTAs per tile
+// contract a share of the 256-deep slabs each and a second small kernel adds their partial tiles in split order.
+// Returns the number of splits (1: none) and the slabs per split.
+int pick_ksplit(int64_t m, int64_t n, int64_t k, int bn, int sm_count, int * slabs_per_split) {
+    const int64_t tiles = ceil_div(m, MMQ_BM) * ceil_div(n, bn), nslab = ceil_div(k, 256);
+    *slabs_per_split = (int) nslab;
+    static const int max_split = env_int("GGML_B200_MMQ_KSPLIT", 4);
+    if (max_split < 2 || bn > 256 || n <= 8 || tiles * 2 > sm_count || nslab < 8) return 1;
+    int ks = (int) (sm_count / tiles);
+    if (ks > max_split) ks = max_split;
+    if (ks > nslab / 4) ks = (int) (nslab / 4);
+    if (ks < 2) return 1;
+    const int per = (int) ceil_div(nslab, ks);
+    ks = (int) ceil_div(nslab, per);            // no empty split
+    *slabs_per_split = per;
+    return ks < 2 ? 1 : ks;
+}
+
+int pick_bn(int type, int64_t m, int64_t n, int64_t k, int sm_count) {
     const int forced = b200_option(B200_OPT_MMQ_BN);
     // 512 columns = two 256-column accumulators per CTA; Q8_0's 272-byte raw slabs do not fit beside two 64 KB activation stages
     const bool can512 = type != T_Q8_0;
@@ -72,18 +96,24 @@ int pick_bn(int type, int64_t m, int64_t n, int sm_count) {
     if (n <= 32) return 32;
     if (n <= 64) return 64;
     if (n <= 128) return 128;
-    // larger n: fewer waves wins.  A tile's time is the weight expansion (independent of BN, measured ~ the MMA
-    // time of 600 columns) + its MMAs (~ BN): cost = waves x (600 + BN)   (profiles/r01g_prefill_probe.txt)
-    const int64_t tm = ceil_div(m, MMQ_BM);
-    const int64_t w128 = ceil_div(tm * ceil_div(n, 128), sm_count) * (600 + 128);
-    const int64_t w256 = ceil_div(tm * ceil_div(n, 256), sm_count) * (600 + 256);
-    // .. and a 512-column tile (two accumulators fed by one expansion) measured 1.76 x the stage time of a 256-column one
-    // (14336x4096 at n = 2048: 4 waves in 257 us against 7 waves in 256 us, profiles/r03j_prefill_bn512.txt -- with two
-    // N = 256 MMAs per 16-deep step the stage is bound by shared-memory bandwidth: A is read twice): it wins where it
-    // saves waves
-    const int64_t w512 = ceil_div(tm * ceil_div(n, 512), sm_count) * 1507;
-    if (can512 && n > 256 && w512 < w256 && w512 < w128) return 512;
-    return w256 <= w128 ? 256 : 128;
+    // larger n: time = waves x slabs per CTA x the stage time of the tile width, + the partial-tile traffic of a K split.
+    // Stage times in units of the MMA time of one column (measured, profiles/r01g_prefill_probe.txt, r03j_prefill_bn512.txt):
+    // the weight expansion costs ~600 whatever the width, the MMAs their columns; a 512-column tile (two accumulators fed by
+    // one expansion) measured 1.76 x the 256-column stage (shared-memory bandwidth: A is read once per accumulator).
+    const int widths[3] = { 128, 256, 512 };
+    const double stage[3] = { 600 + 128, 600 + 256, 1507 };
+    int best = 256; double best_cost = 0;
+    for (int i = 0; i < 3; i++) {
+        const int bn = widths[i];
+        if (bn == 512 && !(can512 && n > 256)) continue;
+        int per = 0;
+        const int ks = pick_ksplit(m, n, k, bn, sm_count, &per);
+        const int64_t ctas = ceil_div(m, MMQ_BM) * ceil_div(n, bn) * ks;
+        double cost = (double) ceil_div(ctas, sm_count) * per * 4.0 * stage[i];
+        if (ks > 1) cost += (double) (ks + 1) * (double) m * (double) n * 1.0e-3;      // partial tiles written and re-read (~6 TB/s)
+        if (best_cost == 0 || cost < best_cost * 0.999) { best = bn; best_cost = cost; }
+    }
+    return best;
 }
 
 } // namespace
@@ -170,7 +200,16 @@ extern "C" size_t b200_mul_mat_q_workspace_size(int64_t m, int64_t k, int64_t n)
     const size_t bf16 = (size_t) n * (size_t) k * sizeof(__nv_bfloat16);
     const int64_t n_pad = ceil_div(n, 128) * 128;
     const size_t i8 = i8_yq_bytes(k, n_pad) + i8_ds_bytes(k, n_pad);
-    return (bf16 > i8 ? bf16 : i8) + 512;
+    // split-K partial tiles (at most 4 splits, and only for matrices of at most sm_count / 2 tiles: a few MB)
+    int sm = 0, dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sm <= 0) { cudaGetLastError(); sm = 148; }
+    size_t part = 0;
+    for (int bn : { 32, 64, 128, 256, 512 }) {
+        int per = 0;
+        const int ks = pick_ksplit(m, n, k, bn, sm, &per);
+        if (ks > 1) { const size_t p = (size_t) ks * (size_t) m * (size_t) n * sizeof(float) + 256; if (p > part) part = p; }
+    }
+    return (((bf16 > i8 ? bf16 : i8) + 255) & ~(size_t) 255) + part + 512;
 }
 
 extern "C" int b200_mul_mat_q(int type, const void * w_dev, size_t w_row_stride_bytes, int64_t m, int64_t k,
@@ -205,7 +244,7 @@ extern "C" int b200_mul_mat_q(int type, const void * w_dev, size_t w_row_stride_
 
     // 2. TMA descriptor over the bf16 activations: dims {k, n}, box {64, BN}, 128-byte swizzle, zero fill
     const dev_caps & caps = current_caps();
-    const int bn = pick_bn(type, m, n, caps.sm_count);
+    const int bn = pick_bn(type, m, n, k, caps.sm_count);
     encode_tiled_fn encode = get_encode_tiled();
     if (!encode) return B200_ERR_NO_DEVICE;
     CUtensorMap tmap;
@@ -222,6 +261,8 @@ extern "C" int b200_mul_mat_q(int type, const void * w_dev, size_t w_row_stride_
     a.w = (const uint8_t *) w_dev; a.w_row_stride = (int64_t) w_row_stride_bytes; a.m = m; a.k = k; a.n = n;
     a.dst = dst_dev; a.dst_col_stride = (int64_t) (dst_col_stride_bytes / 4);
     a.nblk = (int) (k / type_qk(type)); a.raw_pitch = 0;
+    a.ksplit = pick_ksplit(m, n, k, bn, caps.sm_count, &a.slabs_per_split);
+    a.part = (float *) (((uintptr_t) (xb + (size_t) n * (size_t) k) + 255) & ~(uintptr_t) 255);      // behind the bf16 activations
     const bool aligned0 = ((uintptr_t) w_dev % 16 == 0) && (w_row_stride_bytes % 16 == 0) &&
                          !b200_option(B200_OPT_MMQ_FORCE_UNALIGNED);
     // aligned rows: a second descriptor over the raw weight bytes as 32-bit words, dims {row words, m}, box {slab words, 128}

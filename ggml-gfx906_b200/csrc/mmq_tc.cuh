@@ -342,6 +342,10 @@ struct mmq_args {
     int64_t dst_col_stride;    // floats
     int     nblk;              // blocks per row (k / qk)
     int     raw_pitch;         // bytes per row slot in the raw ring
+    // split K (matrices with fewer tiles than SMs): CTA z of a tile contracts 256-deep slabs [z * slabs_per_split, ..) and
+    // writes its partial tile to part[z][j][i] (column stride m); k_mmq_reduce adds the partials in split order
+    int     ksplit, slabs_per_split;
+    float * part;
 };
 
 constexpr int MMQ_BM = 128;
@@ -405,8 +409,12 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b, const __g
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int64_t m0 = (int64_t) blockIdx.x * MMQ_BM;
     const int64_t n0 = (int64_t) blockIdx.y * BN;
-    const int nkt   = (int) ((a.k + MMQ_BK - 1) / MMQ_BK);               // 64-deep MMA stages
-    const int nslab = (int) ((a.k + SLAB_ELEMS - 1) / SLAB_ELEMS);
+    // this CTA's share of K: slabs [s0, s0 + nslab), stages [kt0, kt0 + nkt) -- ring slots and parities count from 0
+    const int nslab_all = (int) ((a.k + SLAB_ELEMS - 1) / SLAB_ELEMS);
+    const int s0    = a.ksplit > 1 ? (int) blockIdx.z * a.slabs_per_split : 0;
+    const int nslab = a.ksplit > 1 ? min(a.slabs_per_split, nslab_all - s0) : nslab_all;
+    const int kt0   = 4 * s0;
+    const int nkt   = min((int) ((a.k + MMQ_BK - 1) / MMQ_BK) - kt0, 4 * nslab);      // 64-deep MMA stages
 
     if (tid == 0) {
         for (int s = 0; s < ST; s++) { mbar_init(&full[s], 256 + 1); mbar_init(&empty[s], 1); }
@@ -435,13 +443,13 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b, const __g
 #pragma unroll
         for (int r = 0; r < RS; r++) my_raw[r] = raw + ((size_t) r * MMQ_BM + prow) * a.raw_pitch;
 
-        auto slab_valid_blocks = [&](int s) {
-            const int left = a.nblk - s * BLK_PER_SLAB;
+        auto slab_valid_blocks = [&](int s) {            // s: index within this CTA's share
+            const int left = a.nblk - (s0 + s) * BLK_PER_SLAB;
             return left < BLK_PER_SLAB ? left : BLK_PER_SLAB;
         };
         auto issue_raw = [&](int s) {
             const int r = s % RS;
-            const uint8_t * src = wrow + (size_t) s * BLK_PER_SLAB * fmt<T>::bytes;
+            const uint8_t * src = wrow + (size_t) (s0 + s) * BLK_PER_SLAB * fmt<T>::bytes;
             const uint32_t nbytes = (uint32_t) slab_valid_blocks(s) * fmt<T>::bytes;
             const uint32_t off = ALIGNED ? 0u : (uint32_t) (reinterpret_cast<uintptr_t>(src) & 15);
             const uint32_t cp = (off + nbytes + 15u) & ~15u;
@@ -462,7 +470,7 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b, const __g
             if (!ALIGNED && half == 0) {
                 // shift every row of this warp down to its 16-byte aligned slot start (2-byte granules,
                 // lanes side by side: conflict-free), in place
-                const uint8_t * src = wrow + (size_t) s * BLK_PER_SLAB * fmt<T>::bytes;
+                const uint8_t * src = wrow + (size_t) (s0 + s) * BLK_PER_SLAB * fmt<T>::bytes;
                 const int my_off = (int) (reinterpret_cast<uintptr_t>(src) & 15);
                 constexpr int NU16 = (slab<T>::bytes + 1) / 2;
                 for (int rr = 0; rr < 32; rr++) {
@@ -482,7 +490,7 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b, const __g
                 __syncwarp();
             }
             if (!ALIGNED) named_bar_sync(1 + pw, 64);        // the pair's other warp reads the realigned rows
-            if constexpr (T == T_Q6_K) ex.set_skew(ALIGNED ? slab_tma<T>::skew(s) : 0);
+            if constexpr (T == T_Q6_K) ex.set_skew(ALIGNED ? slab_tma<T>::skew(s0 + s) : 0);
             ex.begin_slab(slab_ptr, slab_valid_blocks(s));
 #pragma unroll
             for (int sub = 0; sub < 4; sub++) {
@@ -511,6 +519,8 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b, const __g
         mbar_wait(tmem_full, 0);
         tc_fence_after();
         const int64_t out_row = m0 + prow;
+        float * out = a.ksplit > 1 ? a.part + (size_t) blockIdx.z * (size_t) a.n * (size_t) a.m : a.dst;
+        const int64_t out_stride = a.ksplit > 1 ? a.m : a.dst_col_stride;
         const uint32_t taddr = tmem_base + ((uint32_t) (pw * 32) << 16);      // a warp reaches TMEM lanes 32 (warp % 4) ..
         constexpr int CH = BN >= 16 ? BN / 2 : BN;                             // .. the pair splits the columns
 #pragma unroll 1
@@ -522,7 +532,7 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b, const __g
             if (out_row < a.m) {
 #pragma unroll
                 for (int j = 0; j < 8; j++) {
-                    if (n0 + c0 + j < a.n) a.dst[(n0 + c0 + j) * a.dst_col_stride + out_row] = __uint_as_float(v[j]);
+                    if (n0 + c0 + j < a.n) out[(n0 + c0 + j) * out_stride + out_row] = __uint_as_float(v[j]);
                 }
             }
         }
@@ -539,7 +549,7 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b, const __g
                         const int r = next_slab % RS;
                         if (next_slab >= RS) mbar_wait(&raw_empty[r], (uint32_t) (((next_slab / RS) - 1) & 1));
                         mbar_arrive_expect_tx(&raw_full[r * 4], (uint32_t) (MMQ_BM * slab_tma<T>::box_words * 4));
-                        tma_load_2d(raw + (size_t) r * MMQ_BM * a.raw_pitch, &tmap_w, slab_tma<T>::word0(next_slab), (int) m0, &raw_full[r * 4]);
+                        tma_load_2d(raw + (size_t) r * MMQ_BM * a.raw_pitch, &tmap_w, slab_tma<T>::word0(s0 + next_slab), (int) m0, &raw_full[r * 4]);
                         next_slab++;
                     }
                 }
@@ -548,7 +558,7 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b, const __g
                 mbar_arrive_expect_tx(&full[st], (uint32_t) CFG::b_bytes);
 #pragma unroll
                 for (int h = 0; h < NH; h++)       // a TMA box has at most 256 rows
-                    tma_load_2d(b_tiles + (size_t) st * CFG::b_bytes + (size_t) h * BNH * 128, &tmap_b, kt * MMQ_BK, (int) n0 + h * BNH, &full[st]);
+                    tma_load_2d(b_tiles + (size_t) st * CFG::b_bytes + (size_t) h * BNH * 128, &tmap_b, (kt0 + kt) * MMQ_BK, (int) n0 + h * BNH, &full[st]);
             }
         }
     } else {
@@ -602,6 +612,30 @@ static __global__ void __launch_bounds__(256) k_f32_to_bf16(const uint8_t * __re
         *reinterpret_cast<uint2 *>(yr + i) = o;
     } else {
         for (int j = 0; j < 4 && i + j < k; j++) yr[i + j] = cvt(xr[i + j]);
+    }
+}
+
+// split K: dst[j][i] = part[0][j][i] + part[1][j][i] + ..  (fixed order: the result does not depend on the grid)
+static __global__ void __launch_bounds__(256) k_mmq_reduce(const float * __restrict__ part, int ksplit, int64_t m, int64_t n,
+                                                           float * __restrict__ dst, int64_t dst_col_stride) {
+    const int64_t j = blockIdx.y;
+    const int64_t i = ((int64_t) blockIdx.x * 256 + threadIdx.x) * 4;
+    if (i >= m) return;
+    const float * p = part + j * m + i;
+    float * d = dst + j * dst_col_stride + i;
+    if (i + 3 < m && ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(d)) & 15) == 0 && ((m * n) & 3) == 0) {
+        float4 acc = *reinterpret_cast<const float4 *>(p);
+        for (int z = 1; z < ksplit; z++) {
+            const float4 v = *reinterpret_cast<const float4 *>(p + (size_t) z * m * n);
+            acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+        }
+        *reinterpret_cast<float4 *>(d) = acc;
+    } else {
+        for (int e = 0; e < 4 && i + e < m; e++) {
+            float acc = p[e];
+            for (int z = 1; z < ksplit; z++) acc += p[e + (size_t) z * m * n];
+            d[e] = acc;
+        }
     }
 }
 
