@@ -34,50 +34,60 @@ __device__ __forceinline__ q8_result quantize32(float x) {
     return { q, d, sum };
 }
 
-// 8 lanes per 32-value block (a float4 each): grid (ceil(k/32 / 32), n), block 256 = 32 blocks of 32 values.
-// Same arithmetic as quantize32 (max and integer sum are order-independent), a quarter of the instructions and
-// 16-byte loads: the one-value-per-lane form measured 1.25 TB/s (profiles/r01i_support_probe.txt).
+// 8 lanes per 32-value block (a float4 each), FOUR blocks per lane group: grid (ceil(k/32 / 128), n), block 256 = 128 blocks
+// of 32 values; a thread's four 16-byte loads are issued before any arithmetic (64 bytes in flight per thread: with one
+// block per group the kernel sat at 48 % of the HBM peak, latency-bound).  Same arithmetic as quantize32 (max and integer sum
+// are order-independent); the one-value-per-lane form measured 1.25 TB/s (profiles/r01i_support_probe.txt).
 __global__ void __launch_bounds__(256) k_quantize_q8_1(const uint8_t * __restrict__ x, int64_t x_row_stride, int64_t k,
                                                        uint8_t * __restrict__ y) {
-    const int64_t kb = (int64_t) blockIdx.x * 32 + (threadIdx.x >> 3);
     const int l8 = threadIdx.x & 7;
-    const bool live = kb * 32 < k;                  // whole 8-lane groups are live or not: shuffles stay inside a group
     const int64_t row = blockIdx.y;
     const float * xr = reinterpret_cast<const float *>(x + row * x_row_stride);
-    float v[4] = { 0.0f, 0.0f, 0.0f, 0.0f };
-    if (live) {
-        if ((reinterpret_cast<uintptr_t>(xr) & 15) == 0) {
-            const float4 t = __ldg(reinterpret_cast<const float4 *>(xr + kb * 32 + l8 * 4));
-            v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
-        } else {
+    const bool al = (reinterpret_cast<uintptr_t>(xr) & 15) == 0;
+    float v[4][4];
+    int64_t kbs[4];
 #pragma unroll
-            for (int j = 0; j < 4; j++) v[j] = xr[kb * 32 + l8 * 4 + j];
+    for (int u = 0; u < 4; u++) {
+        const int64_t kb = (int64_t) blockIdx.x * 128 + u * 32 + (threadIdx.x >> 3);
+        kbs[u] = kb;
+        v[u][0] = v[u][1] = v[u][2] = v[u][3] = 0.0f;
+        if (kb * 32 < k) {                          // whole 8-lane groups are live or not: shuffles stay inside a group
+            if (al) {
+                const float4 t = __ldg(reinterpret_cast<const float4 *>(xr + kb * 32 + l8 * 4));
+                v[u][0] = t.x; v[u][1] = t.y; v[u][2] = t.z; v[u][3] = t.w;
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; j++) v[u][j] = xr[kb * 32 + l8 * 4 + j];
+            }
         }
     }
-    float amax = fmaxf(fmaxf(fabsf(v[0]), fabsf(v[1])), fmaxf(fabsf(v[2]), fabsf(v[3])));
 #pragma unroll
-    for (int o = 1; o < 8; o <<= 1) amax = fmaxf(amax, __shfl_xor_sync(0xFFFFFFFFu, amax, o));
-    const float d  = __fdiv_rn(amax, 127.0f);
-    const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
-    uint32_t packed = 0;
-    int sum = 0;
+    for (int u = 0; u < 4; u++) {
+        float amax = fmaxf(fmaxf(fabsf(v[u][0]), fabsf(v[u][1])), fmaxf(fabsf(v[u][2]), fabsf(v[u][3])));
 #pragma unroll
-    for (int j = 0; j < 4; j++) {
-        const float r  = roundf(__fmul_rn(v[j], id));
-        const int   qi = fabsf(r) < 2147483648.0f ? (int) r : (int) 0x80000000;     // see quantize32
-        const int   q  = (int) (int8_t) (qi & 0xFF);
-        packed |= (uint32_t) (q & 0xFF) << (8 * j);
-        sum += q;
-    }
+        for (int o = 1; o < 8; o <<= 1) amax = fmaxf(amax, __shfl_xor_sync(0xFFFFFFFFu, amax, o));
+        const float d  = __fdiv_rn(amax, 127.0f);
+        const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+        uint32_t packed = 0;
+        int sum = 0;
 #pragma unroll
-    for (int o = 1; o < 8; o <<= 1) sum += __shfl_xor_sync(0xFFFFFFFFu, sum, o);
-    if (!live) return;
-    uint8_t * b = y + (row * (k / 32) + kb) * 36;                                    // blocks are 4-byte aligned (36 B)
-    *reinterpret_cast<uint32_t *>(b + 4 + 4 * l8) = packed;
-    if (l8 == 0) {
-        const __half hd = __float2half_rn(d);
-        const __half hs = __float2half_rn(__fmul_rn((float) sum, d));
-        *reinterpret_cast<__half2 *>(b) = __halves2half2(hd, hs);
+        for (int j = 0; j < 4; j++) {
+            const float r  = roundf(__fmul_rn(v[u][j], id));
+            const int   qi = fabsf(r) < 2147483648.0f ? (int) r : (int) 0x80000000;     // see quantize32
+            const int   q  = (int) (int8_t) (qi & 0xFF);
+            packed |= (uint32_t) (q & 0xFF) << (8 * j);
+            sum += q;
+        }
+#pragma unroll
+        for (int o = 1; o < 8; o <<= 1) sum += __shfl_xor_sync(0xFFFFFFFFu, sum, o);
+        if (kbs[u] * 32 >= k) continue;
+        uint8_t * b = y + (row * (k / 32) + kbs[u]) * 36;                                // blocks are 4-byte aligned (36 B)
+        *reinterpret_cast<uint32_t *>(b + 4 + 4 * l8) = packed;
+        if (l8 == 0) {
+            const __half hd = __float2half_rn(d);
+            const __half hs = __float2half_rn(__fmul_rn((float) sum, d));
+            *reinterpret_cast<__half2 *>(b) = __halves2half2(hd, hs);
+        }
     }
 }
 
@@ -116,7 +126,7 @@ extern "C" int b200_quantize_row_q8_1(const float * x_dev, size_t x_row_stride_b
     if (k == 0 || n == 0) return B200_OK;
     for (int64_t r0 = 0; r0 < n; r0 += 65535) {
         const int64_t nr = n - r0 < 65535 ? n - r0 : 65535;
-        const dim3 grid((unsigned) ceil_div(k / 32, 32), (unsigned) nr);
+        const dim3 grid((unsigned) ceil_div(k / 32, 128), (unsigned) nr);
         k_quantize_q8_1<<<grid, 256, 0, (cudaStream_t) stream>>>((const uint8_t *) x_dev + r0 * x_row_stride_bytes, (int64_t) x_row_stride_bytes, k,
                                                                 (uint8_t *) y_dev + r0 * (k / 32) * 36);
         b200_count_launch(1);
