@@ -636,6 +636,8 @@ static inline bool cols_node_ok(int type, const uint8_t * w, int64_t row_stride,
     if (n < 2 || n > COLS_N || m < 1 || k < 256 || k % 256 != 0) return false;
     if (m >= (int64_t) 1 << 31 || k >= (int64_t) 1 << 24) return false;
     if ((reinterpret_cast<uintptr_t>(w) & 15) || (row_stride & 15) || (reinterpret_cast<uintptr_t>(x) & 3) || (x_stride_bytes & 3)) return false;
+    // Q6_K: the ring copies chunks of 8 super-blocks (8 x 210 = 1680 bytes, a multiple of 16); a shorter last chunk would not be one
+    if (type == T_Q6_K && (k / 256) % 8 != 0) return false;
     return row_stride >= k / 256 * (type == T_Q6_K ? 210 : (type == T_Q5_K ? 176 : 144));
 }
 static inline size_t cols_ws_bytes(int64_t k, int64_t n) {

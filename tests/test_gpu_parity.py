@@ -496,6 +496,26 @@ def test_mul_mat_batch_few_columns(kern, oracle, n):
     assert kern.launch_count() > c0
 
 
+def test_mul_mat_batch_few_columns_padded_row_stride(kern, oracle):
+    """weight rows padded to a 16-byte multiple: Q6_K with a super-block count that is not a multiple of 8 must stay off the
+    TMA ring (its chunks would not be multiples of 16 bytes) and take the one-column entries; Q4_K / Q6_K rows that do
+    qualify are read with the padded stride"""
+    import b200
+    import torch
+    for t, m, k, mode in (("q6_K", 70, 2304, 1), ("q6_K", 70, 2048, 2), ("q4_K", 70, 2304, 2), ("q5_K", 33, 768, 2)):
+        w_np = random_blocks(t, m, k, seed=91)
+        rb = w_np.shape[1]
+        stride = (rb + 15) // 16 * 16 + 32
+        wp = np.zeros((m, stride), dtype=np.uint8)
+        wp[:, :rb] = w_np
+        w = kern.to_device(wp.reshape(-1))
+        x_np = np.random.default_rng(92).uniform(-1, 1, size=(4, k)).astype(np.float32)
+        x = kern.to_device(x_np)
+        y = torch.zeros((4, m), dtype=torch.float32, device=kern.device)
+        kern.mul_mat_batch((b200.MulMatNode * 1)(b200.mul_mat_node(t, w.data_ptr(), m, k, x.data_ptr(), 4, y.data_ptr(), a_row_stride=stride)))
+        assert oracle.nmse(oracle.mul_mat(t, w_np, m, k, x_np, mode=mode), y.cpu().numpy()) <= NMSE_ORACLE, (t, m, k)
+
+
 def _batch_nodes(kern, mats, seed0=0, shared_x=False):
     import b200
     import torch
