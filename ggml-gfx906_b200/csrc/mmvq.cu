@@ -331,9 +331,10 @@ struct batch_state {
 
 // plan != nullptr: dry run -- nothing is launched, no device is touched; plan[3 i .. 3 i + 2] = (launch group of node i,
 // list index of the node it waits for inside that group or -1, route: 0 per-node call, 1 persistent list, 2 MMA list)
-constexpr size_t PEER_CTRL_FAMILY = 4096;         // per format family (= launch of a flush): an epoch word + two sets of 448 counters
-constexpr size_t PEER_CTRL_BYTES = 16384;         // head of the symmetric region
-static_assert(64 + 2 * BATCH_MAX_NODES * sizeof(unsigned) <= PEER_CTRL_FAMILY && 3 * PEER_CTRL_FAMILY <= PEER_CTRL_BYTES, "control block");
+constexpr size_t PEER_CTRL_FAMILY = 8192;         // per format family (= launch of a flush): an epoch word, two sets of 448 node counters
+                                                  // (one arrival per rank) and two sets of 448 local arrival counters (one per CTA)
+constexpr size_t PEER_CTRL_BYTES = 32768;         // head of the symmetric region
+static_assert(64 + 4 * BATCH_MAX_NODES * sizeof(unsigned) <= PEER_CTRL_FAMILY && 3 * PEER_CTRL_FAMILY <= PEER_CTRL_BYTES, "control block");
 
 static int run_list(const b200_mul_mat_node * nodes, int64_t count, void * workspace_dev, size_t workspace_bytes, void * stream,
                     int32_t * plan, const b200_peer_group * pg = nullptr, long long remote_delta = 0) {

@@ -42,8 +42,9 @@
 // Row split over the GPUs of a box (reference: peer-copy gather after every MUL_MAT, ggml-cuda.cu:1670-1739): the
 // gather is FUSED into this kernel.  Every rank runs the same list on its row blocks; a node whose dst lies in the
 // symmetric region (one copy per rank, peer-mapped: NVLink / NVSwitch) stores each finished row into EVERY rank's copy
-// (plain st.global on the peer addresses, as the rows are produced), and its completion counter is bumped on every
-// rank (red.release.sys).  The counters are double-buffered by the parity of the launch count ("epoch", bumped by the
+// (plain st.global on the peer addresses, as the rows are produced); the CTAs of a rank meet on a local arrival counter
+// (system-scope fence, then a gpu-scope add) and the last of them bumps the node's completion counter on every rank
+// (one arrival per rank).  The counters are double-buffered by the parity of the launch count ("epoch", bumped by the
 // launch's quantize pre-pass, which also zeroes the OTHER set: no rank can touch that set before this rank has finished
 // the current launch, because every rank's closing barrier needs it).  A dependent node waits for the gathered vector exactly as it waits for
 // a local one, and CTA 0 leaves the kernel only when the last scattered node is complete on all ranks: when the
@@ -133,6 +134,9 @@ __device__ __forceinline__ unsigned ld_relaxed_gpu(const unsigned * p) {
 }
 __device__ __forceinline__ void red_release_sys_add(unsigned * p, unsigned v) {
     asm volatile("red.release.sys.global.add.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void red_relaxed_sys_add(unsigned * p, unsigned v) {
+    asm volatile("red.relaxed.sys.global.add.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
 }
 __device__ __forceinline__ unsigned ld_relaxed_sys(const unsigned * p) {
     unsigned v;
@@ -239,7 +243,7 @@ __global__ void __launch_bounds__(256) k_quantize_batch(const __grid_constant__ 
             if (threadIdx.x == 0) { e_new = *a.epoch + 1u; *a.epoch = e_new; }
             __syncthreads();
             unsigned * other = a.done + ((e_new + 1u) & 1u) * BATCH_MAX_NODES;
-            for (int j = threadIdx.x; j < BATCH_MAX_NODES; j += 256) other[j] = 0u;
+            for (int j = threadIdx.x; j < BATCH_MAX_NODES; j += 256) { other[j] = 0u; other[j + 2 * BATCH_MAX_NODES] = 0u; }   // + the local arrivals
         }
     } else if (blockIdx.x == 0 && threadIdx.x == 0 && a.done) {
         a.done[blockIdx.y] = 0u;
@@ -544,9 +548,11 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
     if (warp == 1) {
         // ===================================================== activation producer: q8 activations of node i -> buffer i % NB
         pdl_wait();                                               // k_quantize_batch (and whatever made x) is done
-        // arrivals a complete node has had: one per CTA, for a scattered node from every rank
+        // arrivals a complete node has had: one per CTA; for a scattered node one per rank
         // (one-way scatter, epoch == NULL: the other device only receives rows, it takes no part in the counters)
-        const unsigned per_launch = (unsigned) (a.epoch ? a.n_peers + 1 : 1) * gridDim.x;
+        // (row split: the CTAs of a rank meet on a LOCAL arrival counter and the last one signals every rank once -- a counter
+        //  that took an add from every CTA of every rank, 8 x 148 remote atomics on one word per node, cost ~20 us per link)
+        const unsigned per_launch = a.epoch ? (unsigned) (a.n_peers + 1) : gridDim.x;
         unsigned * const done_set = a.done + (a.epoch ? (ld_relaxed_sys(a.epoch) & 1u) * BATCH_MAX_NODES : 0u);
         node_cache cache;
         int slab_v = (int) blockIdx.x;
@@ -643,11 +649,21 @@ k_mmvq_batch(const __grid_constant__ batch_args a) {
                 if (old == (unsigned) nwc - 1u) {
                     asm volatile("fence.acq_rel.cta;" ::: "memory");      // the other warps' arrivals, hence their stores, are observed ..
                     sdone[i & 7] = 0u;
-                    if ((nd.qflags & BATCH_Q_SCATTER) && a.epoch) {        // .. and released (cumulatively) to every rank
-                        red_release_sys_add(nd.signal, 1u);
+                    if ((nd.qflags & BATCH_Q_SCATTER) && a.epoch) {        // .. and released (cumulatively) to every rank:
+                        // this CTA's rows are performed system-wide (one fence), it arrives on the rank's local counter of
+                        // the node (two sets behind the signal word), and the LAST CTA of the rank adds one to the node's
+                        // counter on every rank (fence + relaxed add = a release pattern on each).  A red.release.sys per
+                        // rank from every CTA made each link cost 44 us on 8 GPUs (profiles/r03p_bench_8gpu.json).
+                        asm volatile("fence.acq_rel.sys;" ::: "memory");
+                        unsigned prior;
+                        asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], %2;" : "=r"(prior) : "l"(nd.signal + 2 * BATCH_MAX_NODES), "r"(1u) : "memory");
+                        if (prior == gridDim.x - 1u) {
+                            asm volatile("fence.acq_rel.sys;" ::: "memory");
+                            red_relaxed_sys_add(nd.signal, 1u);
 #pragma unroll 1
-                        for (int r = 0; r < a.n_peers; r++)
-                            red_release_sys_add(reinterpret_cast<unsigned *>(reinterpret_cast<char *>(nd.signal) + a.peer_delta[r]), 1u);
+                            for (int r = 0; r < a.n_peers; r++)
+                                red_relaxed_sys_add(reinterpret_cast<unsigned *>(reinterpret_cast<char *>(nd.signal) + a.peer_delta[r]), 1u);
+                        }
                     } else {
                         red_release_gpu_add(nd.signal, 1u);                // .. and released (cumulatively) to the other CTAs
                     }
