@@ -15,10 +15,12 @@ from typing import Optional
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("GGML_B200_KERNELS_LIB") or os.path.join(HERE, "libggml_b200_kernels.so")   # override: tuning builds
 
-TYPE_ID = {"f32": 0, "f16": 1, "q4_0": 2, "q8_0": 8, "q8_1": 9, "q4_K": 12, "q5_K": 13, "q6_K": 14, "i32": 26, "bf16": 30}
-BLOCK_ELEMS = {"q4_0": 32, "q8_0": 32, "q8_1": 32, "q4_K": 256, "q5_K": 256, "q6_K": 256}
-BLOCK_BYTES = {"q4_0": 18, "q8_0": 34, "q8_1": 36, "q4_K": 144, "q5_K": 176, "q6_K": 210}
-QUANT_TYPES = ("q4_0", "q8_0", "q4_K", "q5_K", "q6_K")
+TYPE_ID = {"f32": 0, "f16": 1, "q4_0": 2, "q8_0": 8, "q8_1": 9, "q4_K": 12, "q5_K": 13, "q6_K": 14, "i32": 26, "bf16": 30,
+           "q4_1": 3, "q5_0": 6, "q5_1": 7, "iq4_nl": 20}
+BLOCK_ELEMS = {"q4_0": 32, "q8_0": 32, "q8_1": 32, "q4_K": 256, "q5_K": 256, "q6_K": 256, "q4_1": 32, "q5_0": 32, "q5_1": 32, "iq4_nl": 32}
+BLOCK_BYTES = {"q4_0": 18, "q8_0": 34, "q8_1": 36, "q4_K": 144, "q5_K": 176, "q6_K": 210, "q4_1": 20, "q5_0": 22, "q5_1": 24, "iq4_nl": 18}
+QUANT_TYPES = ("q4_0", "q8_0", "q4_K", "q5_K", "q6_K")           # the hot path: every kernel
+EXTRA_TYPES = ("q4_1", "q5_0", "q5_1", "iq4_nl")                 # dequantize / GET_ROWS / CPY and the general mat-vec only
 MMVQ_MAX_N = 8
 # enum b200_option (include/ggml_b200.h)
 OPT = {"mmvq_generic": 0, "mmvq_no_fused": 1, "batch_single": 2, "no_batch_kernel": 3, "mmq_bn": 4,
@@ -342,7 +344,8 @@ class Kernels:
     # ------------------------------------------------------------------ dequantize_row_*
     def dequantize_row(self, t: str, blocks, n_elems: int, out_dtype: str = "f32"):
         torch = self.torch
-        out = torch.empty(n_elems, dtype=torch.float32 if out_dtype == "f32" else torch.float16, device=self.device)
+        dt = {"f32": torch.float32, "f16": torch.float16, "bf16": torch.bfloat16}[out_dtype]
+        out = torch.empty(n_elems, dtype=dt, device=self.device)
         self._check(self.lib.b200_dequantize_row(TYPE_ID[t], blocks.data_ptr(), out.data_ptr(), n_elems,
                                                  TYPE_ID[out_dtype], self._stream()), "dequantize_row")
         return out

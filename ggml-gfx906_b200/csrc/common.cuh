@@ -8,6 +8,11 @@
 //   Q4_K :295-306  144 B / 256  f16 d | f16 dmin | u8 scales[12] | u8 qs[128]
 //   Q5_K :312-324  176 B / 256  f16 d | f16 dmin | u8 scales[12] | u8 qh[32] | u8 qs[128]
 //   Q6_K :330-336  210 B / 256  u8 ql[128] | u8 qh[64] | i8 scales[16] | f16 d
+// and, served by the general kernels only (dequantize / GET_ROWS / CPY, the one-warp-per-row mat-vec):
+//   Q4_1 :177-189   20 B / 32   f16 d | f16 m | u8 qs[16]             w = q * d + m
+//   Q5_0 :191-196   22 B / 32   f16 d | u8 qh[4] | u8 qs[16]          w = ((q | h << 4) - 16) * d, h = bit j / j + 16 of qh
+//   Q5_1 :198-211   24 B / 32   f16 d | f16 m | u8 qh[4] | u8 qs[16]  w = (q | h << 4) * d + m
+//   IQ4_NL :427-431 18 B / 32   f16 d | u8 qs[16]                     w = kvalues_iq4nl[q] * d
 #pragma once
 
 #include <cuda_fp16.h>
@@ -28,6 +33,7 @@ enum : int {
     T_F32 = B200_TYPE_F32, T_F16 = B200_TYPE_F16, T_Q4_0 = B200_TYPE_Q4_0, T_Q8_0 = B200_TYPE_Q8_0,
     T_Q8_1 = B200_TYPE_Q8_1, T_Q4_K = B200_TYPE_Q4_K, T_Q5_K = B200_TYPE_Q5_K, T_Q6_K = B200_TYPE_Q6_K,
     T_BF16 = B200_TYPE_BF16, T_I32 = B200_TYPE_I32,
+    T_Q4_1 = B200_TYPE_Q4_1, T_Q5_0 = B200_TYPE_Q5_0, T_Q5_1 = B200_TYPE_Q5_1, T_IQ4_NL = B200_TYPE_IQ4_NL,
 };
 
 template <int T> struct fmt;
@@ -36,10 +42,14 @@ template <> struct fmt<T_Q8_0> { static constexpr int qk = 32,  bytes = 34;  };
 template <> struct fmt<T_Q4_K> { static constexpr int qk = 256, bytes = 144; };
 template <> struct fmt<T_Q5_K> { static constexpr int qk = 256, bytes = 176; };
 template <> struct fmt<T_Q6_K> { static constexpr int qk = 256, bytes = 210; };
+template <> struct fmt<T_Q4_1> { static constexpr int qk = 32,  bytes = 20;  };
+template <> struct fmt<T_Q5_0> { static constexpr int qk = 32,  bytes = 22;  };
+template <> struct fmt<T_Q5_1> { static constexpr int qk = 32,  bytes = 24;  };
+template <> struct fmt<T_IQ4_NL> { static constexpr int qk = 32, bytes = 18; };
 
 __host__ __device__ inline int type_qk(int t) {
     switch (t) {
-        case T_Q4_0: case T_Q8_0: case T_Q8_1: return 32;
+        case T_Q4_0: case T_Q8_0: case T_Q8_1: case T_Q4_1: case T_Q5_0: case T_Q5_1: case T_IQ4_NL: return 32;
         case T_Q4_K: case T_Q5_K: case T_Q6_K: return 256;
         case T_F32: case T_F16: case T_BF16: case T_I32: return 1;
         default: return 0;
@@ -48,13 +58,24 @@ __host__ __device__ inline int type_qk(int t) {
 __host__ __device__ inline int type_bytes(int t) {
     switch (t) {
         case T_Q4_0: return 18; case T_Q8_0: return 34; case T_Q8_1: return 36;
+        case T_Q4_1: return 20; case T_Q5_0: return 22; case T_Q5_1: return 24; case T_IQ4_NL: return 18;
         case T_Q4_K: return 144; case T_Q5_K: return 176; case T_Q6_K: return 210;
         case T_F32: case T_I32: return 4; case T_F16: case T_BF16: return 2;
         default: return 0;
     }
 }
+// the five formats of the hot path (every kernel) ..
 __host__ __device__ inline bool type_is_quant(int t) {
     return t == T_Q4_0 || t == T_Q8_0 || t == T_Q4_K || t == T_Q5_K || t == T_Q6_K;
+}
+// .. and those plus the formats only the general kernels serve
+__host__ __device__ inline bool type_is_block(int t) {
+    return type_is_quant(t) || t == T_Q4_1 || t == T_Q5_0 || t == T_Q5_1 || t == T_IQ4_NL;
+}
+// kvalues_iq4nl (src/ggml-common.h:1109-1112) as four little-endian words: entry q = byte (q & 3) of word q >> 2
+__device__ __forceinline__ int iq4nl_value(int q) {
+    const uint32_t w = q < 8 ? (q < 4 ? 0xBFAD9881u : 0xF6EADDCFu) : (q < 12 ? 0x26190D01u : 0x71594535u);
+    return (int) (int8_t) ((w >> (8 * (q & 3))) & 0xFFu);
 }
 
 // ---------------------------------------------------------------- unaligned-safe global loads

@@ -43,6 +43,33 @@ template <> __device__ __forceinline__ void dequant8<T_Q8_0>(const uint8_t * b, 
     }
 }
 
+// ---- the formats only the general kernels serve (32-weight blocks, 2-byte aligned; reference src/ggml-quants.c:327-399, 2512-2528).
+// Chunk c: elements 8c..8c+7; elements 0..15 are the low nibbles of qs[0..15], 16..31 the high nibbles.
+template <bool HAS_M, bool HAS_QH, bool NL>
+__device__ __forceinline__ void dequant8_32(const uint8_t * b, int c, float (&y)[8]) {
+    const float d = f16_bits_to_f32(ld_u16(b));
+    const float m = HAS_M ? f16_bits_to_f32(ld_u16(b + 2)) : 0.0f;
+    constexpr int oqh = HAS_M ? 4 : 2, oqs = oqh + (HAS_QH ? 4 : 0);
+    const uint8_t * q = b + oqs + 8 * (c & 1);
+    const uint32_t w0 = ld_u32_a2(q), w1 = ld_u32_a2(q + 4);
+    uint32_t qh = 0;
+    if (HAS_QH) qh = ld_u32_a2(b + oqh) >> (8 * c);          // bit j (low nibbles) / j + 16 (high nibbles): element 8c + i -> bit 8c + i
+    const int sh = (c >> 1) * 4;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        const uint32_t w = i < 4 ? w0 : w1;
+        int v = (int) ((w >> (8 * (i & 3) + sh)) & 0xFu);
+        if (HAS_QH) v |= (int) ((qh >> i) & 1u) << 4;
+        if (NL)               y[i] = __fmul_rn(d, (float) iq4nl_value(v));                       // d * kvalues_iq4nl[q]
+        else if (HAS_M)       y[i] = __fadd_rn(__fmul_rn((float) v, d), m);                      // x * d + m
+        else if (HAS_QH)      y[i] = __fmul_rn((float) (v - 16), d);                             // (x - 16) * d
+    }
+}
+template <> __device__ __forceinline__ void dequant8<T_Q4_1>(const uint8_t * b, int c, float (&y)[8]) { dequant8_32<true, false, false>(b, c, y); }
+template <> __device__ __forceinline__ void dequant8<T_Q5_0>(const uint8_t * b, int c, float (&y)[8]) { dequant8_32<false, true, false>(b, c, y); }
+template <> __device__ __forceinline__ void dequant8<T_Q5_1>(const uint8_t * b, int c, float (&y)[8]) { dequant8_32<true, true, false>(b, c, y); }
+template <> __device__ __forceinline__ void dequant8<T_IQ4_NL>(const uint8_t * b, int c, float (&y)[8]) { dequant8_32<false, false, true>(b, c, y); }
+
 // Q4_K / Q5_K share everything but the 5th bit.  Element e = 8c: 64-element group g = e/64; inside
 // the group the first 32 are low nibbles (scale pair 2g), the next 32 high nibbles (pair 2g+1) of
 // qs[32g .. 32g+31].
@@ -157,6 +184,22 @@ __device__ __forceinline__ void store8_paired(float * p, const float (&v)[8]) {
     reinterpret_cast<float4 *>(q)[odd ? 3 : 2] = s2;
 }
 
+// bf16 output (replaces ggml_get_to_bf16_cuda, src/ggml-cuda/convert.cu:650-659): RN-even narrowing of the f32 values
+template <> __device__ __forceinline__ void store8<__nv_bfloat16>(__nv_bfloat16 * p, const float (&y)[8], bool vec_ok) {
+    if (vec_ok) {
+        uint4 v;
+        __nv_bfloat162 t;
+        t = __floats2bfloat162_rn(y[0], y[1]); v.x = *reinterpret_cast<uint32_t *>(&t);
+        t = __floats2bfloat162_rn(y[2], y[3]); v.y = *reinterpret_cast<uint32_t *>(&t);
+        t = __floats2bfloat162_rn(y[4], y[5]); v.z = *reinterpret_cast<uint32_t *>(&t);
+        t = __floats2bfloat162_rn(y[6], y[7]); v.w = *reinterpret_cast<uint32_t *>(&t);
+        *reinterpret_cast<uint4 *>(p) = v;
+    } else {
+#pragma unroll
+        for (int i = 0; i < 8; i++) p[i] = __float2bfloat16_rn(y[i]);
+    }
+}
+
 // ---------------------------------------------------------------- contiguous row(s)
 template <int T, typename OUT>
 __global__ void __launch_bounds__(256) k_dequantize_row(const uint8_t * __restrict__ x, OUT * __restrict__ y, int64_t n_chunks) {
@@ -264,18 +307,24 @@ __global__ void __launch_bounds__(256) k_get_rows(const uint8_t * __restrict__ t
 using namespace b200;
 
 
+#define DISPATCH_OUT(T, out_type, CALL) \
+    if (out_type == T_F32) { CALL(T, float) } else if (out_type == T_F16) { CALL(T, __half) } else { CALL(T, __nv_bfloat16) }
 #define DISPATCH_TYPE_OUT(type, out_type, CALL)                                              \
     switch (type) {                                                                          \
-        case T_Q4_0: if (out_type == T_F32) { CALL(T_Q4_0, float) } else { CALL(T_Q4_0, __half) } break; \
-        case T_Q8_0: if (out_type == T_F32) { CALL(T_Q8_0, float) } else { CALL(T_Q8_0, __half) } break; \
-        case T_Q4_K: if (out_type == T_F32) { CALL(T_Q4_K, float) } else { CALL(T_Q4_K, __half) } break; \
-        case T_Q5_K: if (out_type == T_F32) { CALL(T_Q5_K, float) } else { CALL(T_Q5_K, __half) } break; \
-        case T_Q6_K: if (out_type == T_F32) { CALL(T_Q6_K, float) } else { CALL(T_Q6_K, __half) } break; \
+        case T_Q4_0: DISPATCH_OUT(T_Q4_0, out_type, CALL) break;                             \
+        case T_Q8_0: DISPATCH_OUT(T_Q8_0, out_type, CALL) break;                             \
+        case T_Q4_K: DISPATCH_OUT(T_Q4_K, out_type, CALL) break;                             \
+        case T_Q5_K: DISPATCH_OUT(T_Q5_K, out_type, CALL) break;                             \
+        case T_Q6_K: DISPATCH_OUT(T_Q6_K, out_type, CALL) break;                             \
+        case T_Q4_1: DISPATCH_OUT(T_Q4_1, out_type, CALL) break;                             \
+        case T_Q5_0: DISPATCH_OUT(T_Q5_0, out_type, CALL) break;                             \
+        case T_Q5_1: DISPATCH_OUT(T_Q5_1, out_type, CALL) break;                             \
+        case T_IQ4_NL: DISPATCH_OUT(T_IQ4_NL, out_type, CALL) break;                         \
         default: return B200_ERR_TYPE;                                                       \
     }
 
 extern "C" int b200_dequantize_row(int type, const void * x_dev, void * y_dev, int64_t n_elems, int out_type, void * stream) {
-    if (!type_is_quant(type) || (out_type != T_F32 && out_type != T_F16)) return B200_ERR_TYPE;
+    if (!type_is_block(type) || (out_type != T_F32 && out_type != T_F16 && out_type != T_BF16)) return B200_ERR_TYPE;
     if (n_elems < 0 || n_elems % type_qk(type) != 0) return B200_ERR_SHAPE;
     if (n_elems == 0) return B200_OK;
     const int64_t n_chunks = n_elems / 8;
@@ -291,7 +340,7 @@ extern "C" int b200_dequantize_row(int type, const void * x_dev, void * y_dev, i
 
 extern "C" int b200_dequantize_4d(int type, const void * x_dev, const int64_t ne_src[4], const size_t nb_src[4],
                                   void * y_dev, int out_type, const int64_t ne_dst[4], const size_t nb_dst[4], void * stream) {
-    if (!type_is_quant(type) || (out_type != T_F32 && out_type != T_F16)) return B200_ERR_TYPE;
+    if (!type_is_block(type) || (out_type != T_F32 && out_type != T_F16 && out_type != T_BF16)) return B200_ERR_TYPE;
     int64_t n_src = 1, n_dst = 1;
     for (int i = 0; i < 4; i++) {
         if (ne_src[i] < 0 || ne_dst[i] < 0) return B200_ERR_SHAPE;
@@ -317,7 +366,7 @@ extern "C" int b200_dequantize_4d(int type, const void * x_dev, const int64_t ne
 extern "C" int b200_get_rows(int type, const void * table_dev, size_t table_row_stride_bytes, int64_t k, int64_t table_rows,
                              const int32_t * rows_dev, size_t rows_stride_bytes, int64_t n_rows,
                              void * dst_dev, int out_type, size_t dst_row_stride_bytes, void * stream) {
-    if (!type_is_quant(type) || (out_type != T_F32 && out_type != T_F16)) return B200_ERR_TYPE;
+    if (!type_is_block(type) || (out_type != T_F32 && out_type != T_F16 && out_type != T_BF16)) return B200_ERR_TYPE;
     if (k < 0 || n_rows < 0 || k % type_qk(type) != 0) return B200_ERR_SHAPE;
     if (k == 0 || n_rows == 0) return B200_OK;
     cudaStream_t st = (cudaStream_t) stream;

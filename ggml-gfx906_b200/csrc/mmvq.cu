@@ -30,7 +30,8 @@ struct mmvq_args {
     int64_t dst_nb2, dst_nb3; // floats
     int64_t ne12, ne13;     // activation/dst channels (grid y, z)
     int64_t r2, r3;         // broadcast ratios ne12/ne02, ne13/ne03
-    int64_t n;              // columns per channel
+    int64_t n;              // columns per channel (of this launch)
+    int64_t col_stride_n;   // columns per channel in the scratch (0: = n)
     // MUL_MAT_ID (mixture of experts): channel (i12 = slot e, i13 = token t) multiplies expert ids[e, t] of the stack
     // a[k, m, n_as] with activation row (e % ne11, t); NULL for plain MUL_MAT
     const uint8_t * ids;
@@ -56,7 +57,7 @@ __global__ void __launch_bounds__(128) k_mmvq_generic(const mmvq_args a) {
         col0 = i13 * a.ne11 + i12 % a.ne11;
     } else {
         wrow = a.w + row * a.w_row_stride + (i12 / a.r2) * a.w_nb2 + (i13 / a.r3) * a.w_nb3;
-        col0 = (i13 * a.ne12 + i12) * a.n;
+        col0 = (i13 * a.ne12 + i12) * (a.col_stride_n ? a.col_stride_n : a.n);
     }
     const int64_t nsub = a.k / 32;
 
@@ -106,8 +107,8 @@ static int mmvq_dispatch(int type, const mmvq_args & a, cudaStream_t st) {
     if (a.m == 0 || a.n == 0 || a.ne12 == 0 || a.ne13 == 0) return B200_OK;
     if (a.ne12 > 65535 || a.ne13 > 65535) return B200_ERR_SHAPE;
     int rc = B200_ERR_TYPE;
-    // fast path: plain 2-D matrix, rows contiguous
-    if (a.ne12 == 1 && a.ne13 == 1) {
+    // fast path: plain 2-D matrix, rows contiguous (the five hot-path formats)
+    if (a.ne12 == 1 && a.ne13 == 1 && type_is_quant(type)) {
         rc = mmvq_stream_try(type, a.w, a.w_row_stride, a.m, a.k, a.yq, a.yd, a.n, a.dst, a.dst_col_stride, st);
         if (rc == B200_OK) return rc;
         if (rc != B200_STREAM_NOT_APPLICABLE) return rc;
@@ -118,6 +119,10 @@ static int mmvq_dispatch(int type, const mmvq_args & a, cudaStream_t st) {
         case T_Q4_K: rc = launch_generic<T_Q4_K>(a, st); break;
         case T_Q5_K: rc = launch_generic<T_Q5_K>(a, st); break;
         case T_Q6_K: rc = launch_generic<T_Q6_K>(a, st); break;
+        case T_Q4_1: rc = launch_generic<T_Q4_1>(a, st); break;
+        case T_Q5_0: rc = launch_generic<T_Q5_0>(a, st); break;
+        case T_Q5_1: rc = launch_generic<T_Q5_1>(a, st); break;
+        case T_IQ4_NL: rc = launch_generic<T_IQ4_NL>(a, st); break;
         default: return B200_ERR_TYPE;
     }
     if (rc != B200_OK) return rc;
@@ -133,7 +138,7 @@ using namespace b200;
 extern "C" int b200_mul_mat_vec_q(int type, const void * w_dev, size_t w_row_stride_bytes, int64_t m, int64_t k,
                                   const void * acts_scratch_dev, int64_t n,
                                   float * dst_dev, size_t dst_col_stride_bytes, void * stream) {
-    if (!type_is_quant(type)) return B200_ERR_TYPE;
+    if (!type_is_block(type)) return B200_ERR_TYPE;
     if (m < 0 || k < 0 || n < 0 || n > B200_MMVQ_MAX_N || k % type_qk(type) != 0) return B200_ERR_SHAPE;
     if (dst_col_stride_bytes % 4 != 0 || w_row_stride_bytes % 2 != 0) return B200_ERR_STRIDE;
     if (m == 0 || n == 0) return B200_OK;
@@ -146,17 +151,17 @@ extern "C" int b200_mul_mat_vec_q(int type, const void * w_dev, size_t w_row_str
     a.dst = dst_dev;
     a.m = m; a.k = k; a.w_row_stride = (int64_t) w_row_stride_bytes; a.w_nb2 = 0; a.w_nb3 = 0;
     a.dst_col_stride = (int64_t) (dst_col_stride_bytes / 4); a.dst_nb2 = 0; a.dst_nb3 = 0;
-    a.ne12 = 1; a.ne13 = 1; a.r2 = 1; a.r3 = 1; a.n = n; a.ids = nullptr; a.bad = nullptr;
+    a.ne12 = 1; a.ne13 = 1; a.r2 = 1; a.r3 = 1; a.n = n; a.col_stride_n = 0; a.ids = nullptr; a.bad = nullptr;
     return mmvq_dispatch(type, a, (cudaStream_t) stream);
 }
 
 // ---------------------------------------------------------------- the MUL_MAT dispatcher
 extern "C" size_t b200_mul_mat_workspace_size(int type_a, const int64_t ne_a[4], const int64_t ne_b[4]) {
-    if (!type_is_quant(type_a)) return 0;
+    if (!type_is_block(type_a)) return 0;
     const int64_t k = ne_a[0], m = ne_a[1], n = ne_b[1];
     const int64_t cols = ne_b[1] * ne_b[2] * ne_b[3];
     if (k <= 0 || cols <= 0) return 256;
-    if (n <= B200_MMVQ_MAX_N) return b200_acts_scratch_bytes(k, cols) + 256;
+    if (n <= B200_MMVQ_MAX_N || !type_is_quant(type_a)) return b200_acts_scratch_bytes(k, cols) + 256;
     return b200_mul_mat_q_workspace_size(m, k, cols) + 256;
 }
 
@@ -169,7 +174,7 @@ extern "C" int b200_mul_mat(int type_a, const void * a_dev, const int64_t ne_a[4
 extern "C" int b200_mul_mat_ex(int type_a, const void * a_dev, const int64_t ne_a[4], const size_t nb_a[4],
                                const float * b_dev, const int64_t ne_b[4], const size_t nb_b[4],
                                float * dst_dev, void * workspace_dev, size_t workspace_bytes, uint32_t flags, void * stream) {
-    if (!type_is_quant(type_a)) return B200_ERR_TYPE;
+    if (!type_is_block(type_a)) return B200_ERR_TYPE;
     const int64_t k = ne_a[0], m = ne_a[1], n = ne_b[1];
     for (int i = 0; i < 4; i++) if (ne_a[i] < 0 || ne_b[i] < 0) return B200_ERR_SHAPE;
     if (ne_b[0] != k || k % type_qk(type_a) != 0) return B200_ERR_SHAPE;
@@ -184,14 +189,15 @@ extern "C" int b200_mul_mat_ex(int type_a, const void * a_dev, const int64_t ne_
     if (workspace_bytes < b200_mul_mat_workspace_size(type_a, ne_a, ne_b) || !workspace_dev) return B200_ERR_WORKSPACE;
     uint8_t * ws = (uint8_t *) (((uintptr_t) workspace_dev + 255) & ~(uintptr_t) 255);
 
-    if (n == 1 && ne12 == 1 && ne13 == 1) {
+    if (n == 1 && ne12 == 1 && ne13 == 1 && type_is_quant(type_a)) {
         // decode fast path: activation quantization fused into the mat-vec, one launch
         const int rc = mmvq_fused_try(type_a, (const uint8_t *) a_dev, (int64_t) nb_a[1], m, k, b_dev, dst_dev,
                                       (flags & B200_MUL_MAT_CONST_WEIGHTS) != 0, st);
         if (rc != B200_STREAM_NOT_APPLICABLE) return rc;
     }
-    if (n <= B200_MMVQ_MAX_N) {
+    if (n <= B200_MMVQ_MAX_N || !type_is_quant(type_a)) {
         // quantize every activation column once: scratch column index = (i13*ne12 + i12)*n + j
+        // (Q4_1 / Q5_0 / Q5_1 / IQ4_NL have no tensor-core kernel: more than 8 columns run as groups of 8 on the general mat-vec)
         const int64_t cols = n * ne12 * ne13;
         const size_t qbytes = ((size_t) cols * (size_t) k + 255) / 256 * 256;
         int8_t * yq = (int8_t *) ws;
@@ -206,8 +212,18 @@ extern "C" int b200_mul_mat_ex(int type_a, const void * a_dev, const int64_t ne_
         a.w = (const uint8_t *) a_dev; a.yq = yq; a.yd = yd; a.dst = dst_dev;
         a.m = m; a.k = k; a.w_row_stride = (int64_t) nb_a[1]; a.w_nb2 = (int64_t) nb_a[2]; a.w_nb3 = (int64_t) nb_a[3];
         a.dst_col_stride = m; a.dst_nb2 = m * n; a.dst_nb3 = m * n * ne12;
-        a.ne12 = ne12; a.ne13 = ne13; a.r2 = ne12 / ne_a[2]; a.r3 = ne13 / ne_a[3]; a.n = n; a.ids = nullptr; a.bad = nullptr;
-        return mmvq_dispatch(type_a, a, st);
+        a.ne12 = ne12; a.ne13 = ne13; a.r2 = ne12 / ne_a[2]; a.r3 = ne13 / ne_a[3]; a.n = n; a.col_stride_n = 0; a.ids = nullptr; a.bad = nullptr;
+        if (n <= B200_MMVQ_MAX_N) return mmvq_dispatch(type_a, a, st);
+        // groups of 8 columns of every channel: a channel's columns sit n apart in the scratch, its dst m * n apart
+        for (int64_t j0 = 0; j0 < n; j0 += B200_MMVQ_MAX_N) {
+            mmvq_args g = a;
+            g.n = n - j0 < B200_MMVQ_MAX_N ? n - j0 : B200_MMVQ_MAX_N;
+            g.yq = yq + j0 * k; g.yd = yd + j0 * (k / 32); g.dst = dst_dev + j0 * m;
+            g.col_stride_n = n;
+            const int rc = mmvq_dispatch(type_a, g, st);
+            if (rc) return rc;
+        }
+        return B200_OK;
     }
     // batched path, one 2-D problem per (i12, i13) channel
     for (int64_t i13 = 0; i13 < ne13; i13++) for (int64_t i12 = 0; i12 < ne12; i12++) {
@@ -226,14 +242,14 @@ extern "C" int b200_mul_mat_ex(int type_a, const void * a_dev, const int64_t ne_
 // ids tensor names.  The ids stay on the device (the reference copies them to the host and synchronizes for its
 // batched path, src/ggml-cuda/ggml-cuda.cu:2092-2233; its decode path passes them to the kernel, mmvq.cu:163-166, as here).
 extern "C" size_t b200_mul_mat_id_workspace_size(int type_a, const int64_t ne_a[4], const int64_t ne_b[4]) {
-    if (!type_is_quant(type_a) || ne_a[0] <= 0) return 256;
+    if (!type_is_block(type_a) || ne_a[0] <= 0) return 256;
     return b200_acts_scratch_bytes(ne_a[0], ne_b[1] * ne_b[2]) + 512;
 }
 extern "C" int b200_mul_mat_id(int type_a, const void * as_dev, const int64_t ne_a[4], const size_t nb_a[4],
                                const float * b_dev, const int64_t ne_b[4], const size_t nb_b[4],
                                const int32_t * ids_dev, const int64_t ne_ids[2], const size_t nb_ids[2],
                                float * dst_dev, void * workspace_dev, size_t workspace_bytes, void * stream) {
-    if (!type_is_quant(type_a)) return B200_ERR_TYPE;
+    if (!type_is_block(type_a)) return B200_ERR_TYPE;
     const int64_t k = ne_a[0], m = ne_a[1], n_as = ne_a[2];
     const int64_t ne11 = ne_b[1], n_tok = ne_b[2], n_used = ne_ids[0];
     if (k < 0 || m < 0 || n_as < 1 || ne_a[3] != 1 || ne_b[3] != 1 || ne_b[0] != k || k % type_qk(type_a) != 0) return B200_ERR_SHAPE;
@@ -259,7 +275,7 @@ extern "C" int b200_mul_mat_id(int type_a, const void * as_dev, const int64_t ne
     a.w = (const uint8_t *) as_dev; a.yq = yq; a.yd = yd; a.dst = dst_dev;
     a.m = m; a.k = k; a.w_row_stride = (int64_t) nb_a[1]; a.w_nb2 = (int64_t) nb_a[2]; a.w_nb3 = 0;
     a.dst_col_stride = m; a.dst_nb2 = m; a.dst_nb3 = m * n_used;
-    a.ne12 = n_used; a.ne13 = n_tok; a.r2 = 1; a.r3 = 1; a.n = 1;
+    a.ne12 = n_used; a.ne13 = n_tok; a.r2 = 1; a.r3 = 1; a.n = 1; a.col_stride_n = 0;
     a.ids = (const uint8_t *) ids_dev; a.ids_nb0 = (int64_t) nb_ids[0]; a.ids_nb1 = (int64_t) nb_ids[1]; a.n_as = n_as; a.ne11 = ne11;
     a.bad = b200_error_word_dev();
     int rc;
@@ -268,6 +284,10 @@ extern "C" int b200_mul_mat_id(int type_a, const void * as_dev, const int64_t ne
         case T_Q8_0: rc = launch_generic<T_Q8_0>(a, st); break;
         case T_Q4_K: rc = launch_generic<T_Q4_K>(a, st); break;
         case T_Q5_K: rc = launch_generic<T_Q5_K>(a, st); break;
+        case T_Q4_1: rc = launch_generic<T_Q4_1>(a, st); break;
+        case T_Q5_0: rc = launch_generic<T_Q5_0>(a, st); break;
+        case T_Q5_1: rc = launch_generic<T_Q5_1>(a, st); break;
+        case T_IQ4_NL: rc = launch_generic<T_IQ4_NL>(a, st); break;
         default:     rc = launch_generic<T_Q6_K>(a, st); break;
     }
     if (rc != B200_OK) return rc;

@@ -61,6 +61,10 @@ static void b200_log(const char * fmt, ...) {
 static bool is_hot_quant(enum ggml_type t) {
     return t == GGML_TYPE_Q4_0 || t == GGML_TYPE_Q8_0 || t == GGML_TYPE_Q4_K || t == GGML_TYPE_Q5_K || t == GGML_TYPE_Q6_K;
 }
+// .. and the formats the kernel library serves with its general kernels only (dequantize / GET_ROWS / CPY, one-warp-per-row mat-vec)
+static bool is_block_quant(enum ggml_type t) {
+    return is_hot_quant(t) || t == GGML_TYPE_Q4_1 || t == GGML_TYPE_Q5_0 || t == GGML_TYPE_Q5_1 || t == GGML_TYPE_IQ4_NL;
+}
 
 // ================================================================= contexts
 struct b200_device_ctx {
@@ -300,7 +304,7 @@ static void b200_compute_node(b200_backend_ctx * ctx, struct ggml_tensor * node)
         case GGML_OP_DUP:
         case GGML_OP_CONT: {
             const struct ggml_tensor * dst = node->op == GGML_OP_CPY ? node->src[1] : node;
-            const int out_type = dst->type == GGML_TYPE_F32 ? B200_TYPE_F32 : B200_TYPE_F16;
+            const int out_type = dst->type == GGML_TYPE_F32 ? B200_TYPE_F32 : (dst->type == GGML_TYPE_F16 ? B200_TYPE_F16 : B200_TYPE_BF16);
             B200_OK_OR_ABORT(b200_dequantize_4d((int) s0->type, s0->data, s0->ne, s0->nb, dst->data, out_type, dst->ne, dst->nb, ctx->stream));
         } break;
         case GGML_OP_RMS_NORM: {
@@ -607,24 +611,24 @@ static bool b200_dev_supports_op(ggml_backend_dev_t dev, const struct ggml_tenso
         case GGML_OP_TRANSPOSE:
             return true;
         case GGML_OP_MUL_MAT:
-            return s0 && s1 && is_hot_quant(s0->type) && s1->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 &&
+            return s0 && s1 && is_block_quant(s0->type) && s1->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 &&
                    s0->nb[0] == ggml_type_size(s0->type) && s1->nb[0] == sizeof(float) && ggml_is_contiguous(op) &&
                    s0->ne[2] > 0 && s0->ne[3] > 0 && s1->ne[2] % s0->ne[2] == 0 && s1->ne[3] % s0->ne[3] == 0 &&
                    s1->ne[2] <= 65535 && s1->ne[3] <= 65535;
         case GGML_OP_MUL_MAT_ID: {
             const struct ggml_tensor * ids = op->src[2];
-            return s0 && s1 && ids && is_hot_quant(s0->type) && s1->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 && ids->type == GGML_TYPE_I32 &&
+            return s0 && s1 && ids && is_block_quant(s0->type) && s1->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 && ids->type == GGML_TYPE_I32 &&
                    s0->nb[0] == ggml_type_size(s0->type) && s1->nb[0] == sizeof(float) && ggml_is_contiguous(op) && s0->ne[3] == 1 && s1->ne[3] == 1 &&
                    s1->ne[1] >= 1 && ids->ne[0] % s1->ne[1] == 0 && ids->ne[0] <= 65535 && ids->ne[1] <= 65535;
         }
         case GGML_OP_GET_ROWS:
-            return s0 && s1 && is_hot_quant(s0->type) && s1->type == GGML_TYPE_I32 && op->type == GGML_TYPE_F32 &&
+            return s0 && s1 && is_block_quant(s0->type) && s1->type == GGML_TYPE_I32 && op->type == GGML_TYPE_F32 &&
                    s0->nb[0] == ggml_type_size(s0->type) && op->nb[0] == sizeof(float) && s1->ne[3] == 1;
         case GGML_OP_CPY:
         case GGML_OP_DUP:
         case GGML_OP_CONT: {
             const struct ggml_tensor * dst = op->op == GGML_OP_CPY ? s1 : op;
-            return s0 && dst && is_hot_quant(s0->type) && (dst->type == GGML_TYPE_F32 || dst->type == GGML_TYPE_F16) &&
+            return s0 && dst && is_block_quant(s0->type) && (dst->type == GGML_TYPE_F32 || dst->type == GGML_TYPE_F16 || dst->type == GGML_TYPE_BF16) &&
                    s0->nb[0] == ggml_type_size(s0->type) && ggml_nelements(s0) == ggml_nelements(dst);
         }
         // the f32 ops between the MUL_MATs of a decoder layer (csrc/layer_ops.cu)

@@ -66,6 +66,42 @@ template <typename LD> struct unpack32<T_Q8_0, LD> {
     }
 };
 
+// ---- the formats only the general kernels serve: value = scale * q - mn with q >= 0 for the *_1 formats (mn = -m)
+template <bool HAS_M, bool HAS_QH, bool NL, typename LD>
+__device__ __forceinline__ void unpack32_x(const uint8_t * b, sub32 & o) {
+    const float d = f16_bits_to_f32(LD::u16(b));
+    constexpr int oqh = HAS_M ? 4 : 2, oqs = oqh + (HAS_QH ? 4 : 0);
+    const uint32_t qh = HAS_QH ? LD::u32(b + oqh) : 0u;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const uint32_t w = LD::u32(b + oqs + 4 * j);
+        uint32_t lo = w & 0x0F0F0F0Fu, hi = (w >> 4) & 0x0F0F0F0Fu;
+        if (HAS_QH) {
+            // bit 4j + i of qh -> bit 4 of byte i (elements 4j..4j+3), bit 16 + 4j + i likewise for the high nibbles
+            const uint32_t bl = (qh >> (4 * j)) & 0xFu, bh = (qh >> (16 + 4 * j)) & 0xFu;
+            lo |= ((bl & 1u) << 4) | ((bl & 2u) << 11) | ((bl & 4u) << 18) | ((bl & 8u) << 25);
+            hi |= ((bh & 1u) << 4) | ((bh & 2u) << 11) | ((bh & 4u) << 18) | ((bh & 8u) << 25);
+        }
+        if (NL) {
+            uint32_t tl = 0, th = 0;
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                tl |= (uint32_t) (iq4nl_value((int) ((lo >> (8 * i)) & 0xFu)) & 0xFF) << (8 * i);
+                th |= (uint32_t) (iq4nl_value((int) ((hi >> (8 * i)) & 0xFu)) & 0xFF) << (8 * i);
+            }
+            lo = tl; hi = th;
+        } else if (HAS_QH && !HAS_M) {
+            lo = (uint32_t) __vsubss4((int) lo, 0x10101010); hi = (uint32_t) __vsubss4((int) hi, 0x10101010);     // Q5_0: q - 16
+        }
+        o.q[j] = (int) lo; o.q[j + 4] = (int) hi;
+    }
+    o.sA = d; o.sB = d; o.mn = HAS_M ? -f16_bits_to_f32(LD::u16(b + 2)) : 0.0f;
+}
+template <typename LD> struct unpack32<T_Q4_1, LD> { static __device__ __forceinline__ void run(const uint8_t * b, int, sub32 & o) { unpack32_x<true, false, false, LD>(b, o); } };
+template <typename LD> struct unpack32<T_Q5_0, LD> { static __device__ __forceinline__ void run(const uint8_t * b, int, sub32 & o) { unpack32_x<false, true, false, LD>(b, o); } };
+template <typename LD> struct unpack32<T_Q5_1, LD> { static __device__ __forceinline__ void run(const uint8_t * b, int, sub32 & o) { unpack32_x<true, true, false, LD>(b, o); } };
+template <typename LD> struct unpack32<T_IQ4_NL, LD> { static __device__ __forceinline__ void run(const uint8_t * b, int, sub32 & o) { unpack32_x<false, false, true, LD>(b, o); } };
+
 template <bool HAS_QH, typename LD>
 __device__ __forceinline__ void unpack32_k45(const uint8_t * b, int s, sub32 & o) {
     const float d    = f16_bits_to_f32(LD::u16(b));

@@ -33,11 +33,15 @@ enum b200_type {
     B200_TYPE_F32  = 0,
     B200_TYPE_F16  = 1,
     B200_TYPE_Q4_0 = 2,
+    B200_TYPE_Q4_1 = 3,   /* Q4_1, Q5_0, Q5_1, IQ4_NL: dequantize / GET_ROWS / CPY and the general mat-vec (MUL_MAT, MUL_MAT_ID) only */
+    B200_TYPE_Q5_0 = 6,
+    B200_TYPE_Q5_1 = 7,
     B200_TYPE_Q8_0 = 8,
     B200_TYPE_Q8_1 = 9,
     B200_TYPE_Q4_K = 12,
     B200_TYPE_Q5_K = 13,
     B200_TYPE_Q6_K = 14,
+    B200_TYPE_IQ4_NL = 20,
     B200_TYPE_I32  = 26,
     B200_TYPE_BF16 = 30,
 };
@@ -98,7 +102,8 @@ B200_API size_t b200_row_bytes(int type, int64_t k);
  * (src/ggml-cuda/convert.cu:661-764); values bit-exact with dequantize_row_<type>
  * (src/ggml-quants.c:307-325, 401-415, 1352-1374, 1554-1579, 1762-1791) and, for f16 output,
  * with the RN-even narrowing of those f32 values.
- * x_dev: n_elems/QK contiguous blocks.  out_type: B200_TYPE_F32 or B200_TYPE_F16. */
+ * x_dev: n_elems/QK contiguous blocks.  out_type: B200_TYPE_F32, B200_TYPE_F16 or B200_TYPE_BF16 (RN-even narrowing:
+ * ggml_get_to_bf16_cuda, src/ggml-cuda/convert.cu:650-659).  Also Q4_1 / Q5_0 / Q5_1 / IQ4_NL (src/ggml-quants.c:327-399, 2512-2528). */
 B200_API int b200_dequantize_row(int type, const void * x_dev, void * y_dev, int64_t n_elems,
                                  int out_type, void * stream);
 

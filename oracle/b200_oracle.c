@@ -26,12 +26,18 @@ enum {
     Q4_K_BYTES = 144, /* f16 d | f16 dmin | u8 scales[12] | u8 qs[128]       */
     Q5_K_BYTES = 176, /* f16 d | f16 dmin | u8 scales[12] | u8 qh[32] | u8 qs[128] */
     Q6_K_BYTES = 210, /* u8 ql[128] | u8 qh[64] | i8 scales[16] | f16 d      */
+    /* the formats only the general kernels serve (src/ggml-common.h:178-187, 198-202, 206-216, 416-419) */
+    Q4_1_BYTES = 20,  /* f16 d | f16 m | u8 qs[16]                           */
+    Q5_0_BYTES = 22,  /* f16 d | u8 qh[4] | u8 qs[16]                        */
+    Q5_1_BYTES = 24,  /* f16 d | f16 m | u8 qh[4] | u8 qs[16]                */
+    IQ4_NL_BYTES = 18, /* f16 d | u8 qs[16]                                  */
 };
 
 int b200o_block_elems(int type) {
     switch (type) {
         case B200O_F32: case B200O_F16: return 1;
         case B200O_Q4_0: case B200O_Q8_0: case B200O_Q8_1: return 32;
+        case B200O_Q4_1: case B200O_Q5_0: case B200O_Q5_1: case B200O_IQ4_NL: return 32;
         case B200O_Q4_K: case B200O_Q5_K: case B200O_Q6_K: return 256;
         default: return 0;
     }
@@ -47,6 +53,10 @@ size_t b200o_block_bytes(int type) {
         case B200O_Q4_K: return Q4_K_BYTES;
         case B200O_Q5_K: return Q5_K_BYTES;
         case B200O_Q6_K: return Q6_K_BYTES;
+        case B200O_Q4_1: return Q4_1_BYTES;
+        case B200O_Q5_0: return Q5_0_BYTES;
+        case B200O_Q5_1: return Q5_1_BYTES;
+        case B200O_IQ4_NL: return IQ4_NL_BYTES;
         default: return 0;
     }
 }
@@ -142,6 +152,66 @@ static void dq_q8_0(const uint8_t * x, float * y, int64_t k) {
         const float d = b200o_fp16_to_fp32(rd16(b));
         for (int j = 0; j < 32; j++) {
             y[i * 32 + j] = (float)(int8_t) b[2 + j] * d;
+        }
+    }
+}
+
+/* src/ggml-quants.c:327-346 — y[j] = (qs[j] & 15) * d + m ; y[j+16] = (qs[j] >> 4) * d + m */
+static void dq_q4_1(const uint8_t * x, float * y, int64_t k) {
+    for (int64_t i = 0; i < k / 32; i++) {
+        const uint8_t * b = x + i * Q4_1_BYTES;
+        const float d = b200o_fp16_to_fp32(rd16(b)), m = b200o_fp16_to_fp32(rd16(b + 2));
+        for (int j = 0; j < 16; j++) {
+            const int x0 = b[4 + j] & 0x0F, x1 = b[4 + j] >> 4;
+            y[i * 32 + j]      = (float) x0 * d + m;
+            y[i * 32 + j + 16] = (float) x1 * d + m;
+        }
+    }
+}
+
+/* src/ggml-quants.c:348-372 — fifth bit j (elements 0..15) / j + 16 (elements 16..31) of the 32-bit qh, value - 16 */
+static void dq_q5_0(const uint8_t * x, float * y, int64_t k) {
+    for (int64_t i = 0; i < k / 32; i++) {
+        const uint8_t * b = x + i * Q5_0_BYTES;
+        const float d = b200o_fp16_to_fp32(rd16(b));
+        const uint32_t qh = (uint32_t) b[2] | ((uint32_t) b[3] << 8) | ((uint32_t) b[4] << 16) | ((uint32_t) b[5] << 24);
+        for (int j = 0; j < 16; j++) {
+            const uint8_t xh_0 = (uint8_t) (((qh >> (j + 0)) << 4) & 0x10);
+            const uint8_t xh_1 = (uint8_t) ((qh >> (j + 12)) & 0x10);
+            const int32_t x0 = ((b[6 + j] & 0x0F) | xh_0) - 16;
+            const int32_t x1 = ((b[6 + j] >> 4) | xh_1) - 16;
+            y[i * 32 + j]      = (float) x0 * d;
+            y[i * 32 + j + 16] = (float) x1 * d;
+        }
+    }
+}
+
+/* src/ggml-quants.c:374-399 */
+static void dq_q5_1(const uint8_t * x, float * y, int64_t k) {
+    for (int64_t i = 0; i < k / 32; i++) {
+        const uint8_t * b = x + i * Q5_1_BYTES;
+        const float d = b200o_fp16_to_fp32(rd16(b)), m = b200o_fp16_to_fp32(rd16(b + 2));
+        const uint32_t qh = (uint32_t) b[4] | ((uint32_t) b[5] << 8) | ((uint32_t) b[6] << 16) | ((uint32_t) b[7] << 24);
+        for (int j = 0; j < 16; j++) {
+            const uint8_t xh_0 = (uint8_t) (((qh >> (j + 0)) << 4) & 0x10);
+            const uint8_t xh_1 = (uint8_t) ((qh >> (j + 12)) & 0x10);
+            const int x0 = (b[8 + j] & 0x0F) | xh_0;
+            const int x1 = (b[8 + j] >> 4) | xh_1;
+            y[i * 32 + j]      = (float) x0 * d + m;
+            y[i * 32 + j + 16] = (float) x1 * d + m;
+        }
+    }
+}
+
+/* src/ggml-quants.c:2512-2528 with kvalues_iq4nl (src/ggml-common.h:1088-1090) */
+static const int8_t iq4nl_values[16] = { -127, -104, -83, -65, -49, -35, -22, -10, 1, 13, 25, 38, 53, 69, 89, 113 };
+static void dq_iq4_nl(const uint8_t * x, float * y, int64_t k) {
+    for (int64_t i = 0; i < k / 32; i++) {
+        const uint8_t * b = x + i * IQ4_NL_BYTES;
+        const float d = b200o_fp16_to_fp32(rd16(b));
+        for (int j = 0; j < 16; j++) {
+            y[i * 32 + j]      = d * (float) iq4nl_values[b[2 + j] & 0xf];
+            y[i * 32 + j + 16] = d * (float) iq4nl_values[b[2 + j] >> 4];
         }
     }
 }
@@ -254,6 +324,10 @@ void b200o_dequantize_row(int type, const void * x, float * y, int64_t k) {
         case B200O_Q4_K: dq_q4_K((const uint8_t *) x, y, k); break;
         case B200O_Q5_K: dq_q5_K((const uint8_t *) x, y, k); break;
         case B200O_Q6_K: dq_q6_K((const uint8_t *) x, y, k); break;
+        case B200O_Q4_1: dq_q4_1((const uint8_t *) x, y, k); break;
+        case B200O_Q5_0: dq_q5_0((const uint8_t *) x, y, k); break;
+        case B200O_Q5_1: dq_q5_1((const uint8_t *) x, y, k); break;
+        case B200O_IQ4_NL: dq_iq4_nl((const uint8_t *) x, y, k); break;
         case B200O_Q8_1: {
             /* d * q (used for the mode-1 MUL_MAT oracle) */
             const uint8_t * p = (const uint8_t *) x;

@@ -29,11 +29,15 @@ enum b200o_type {
     B200O_F32  = 0,
     B200O_F16  = 1,
     B200O_Q4_0 = 2,
+    B200O_Q4_1 = 3,
+    B200O_Q5_0 = 6,
+    B200O_Q5_1 = 7,
     B200O_Q8_0 = 8,
     B200O_Q8_1 = 9,
     B200O_Q4_K = 12,
     B200O_Q5_K = 13,
     B200O_Q6_K = 14,
+    B200O_IQ4_NL = 20,
 };
 
 /* elements per block / bytes per block (src/ggml-common.h:170-336) */
@@ -47,7 +51,8 @@ float    b200o_fp16_to_fp32(uint16_t h);
 uint16_t b200o_fp32_to_fp16(float f);
 
 /* dequantize_row_<type>: k elements (k % block_elems == 0) from blocks at x -> f32 at y.
- * src/ggml-quants.c:307-325 (q4_0), 401-415 (q8_0), 1352-1374 (q4_K), 1554-1579 (q5_K), 1762-1791 (q6_K) */
+ * src/ggml-quants.c:307-325 (q4_0), 401-415 (q8_0), 1352-1374 (q4_K), 1554-1579 (q5_K), 1762-1791 (q6_K),
+ * 327-346 (q4_1), 348-372 (q5_0), 374-399 (q5_1), 2512-2528 (iq4_nl) */
 void b200o_dequantize_row(int type, const void * x, float * y, int64_t k);
 /* same, then f32 -> f16 RN-even (what "dequantize to f16" means for the CPU path: to_float then
  * ggml_fp32_to_fp16_row, src/ggml.c:455-470) */

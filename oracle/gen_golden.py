@@ -157,6 +157,16 @@ def main_v2():
     zero = d == 0
     bs = bs.reshape(-1, 16).copy(); bs[zero] = 0        # the reference leaves bsums of an all-zero block unwritten
     out = {"q8_K_x": x, "q8_K_q": q, "q8_K_d": d, "q8_K_bsums": bs.reshape(-1)}
+    # the formats only the general kernels serve: random-quantized rows + raw random blocks with edge fp16 fields, dequantized
+    for t in gh.EXTRA_TYPES:
+        F16_FIELDS[t] = {"q4_1": (0, 2), "q5_0": (0,), "q5_1": (0, 2), "iq4_nl": (0,)}[t]
+        xw = rng.uniform(-1.0, 1.0, size=(4, K)).astype(np.float32)
+        xw[2] *= 1e-3
+        blocks = np.concatenate([host.quantize(t, xw, None), adversarial_blocks(t, rng)], axis=0)
+        deq = np.stack([host.dequantize(t, blocks[r], K) for r in range(blocks.shape[0])])
+        out[f"{t}_blocks"] = blocks
+        out[f"{t}_deq_f32"] = deq
+        out[f"{t}_deq_f16"] = host.fp32_to_fp16(deq.reshape(-1)).reshape(deq.shape)
     path = os.path.join(ROOT, "tests", "golden", "golden_v2.npz")
     np.savez_compressed(path, **out)
     print("wrote", path, os.path.getsize(path), "bytes;", len(out), "arrays")

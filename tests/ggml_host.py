@@ -21,11 +21,14 @@ import numpy as np
 # enum ggml_type (include/ggml.h:370-412)
 GGML_TYPE = {
     "f32": 0, "f16": 1, "q4_0": 2, "q4_1": 3, "q5_0": 6, "q5_1": 7, "q8_0": 8, "q8_1": 9,
-    "q2_K": 10, "q3_K": 11, "q4_K": 12, "q5_K": 13, "q6_K": 14, "q8_K": 15, "i32": 26,
+    "q2_K": 10, "q3_K": 11, "q4_K": 12, "q5_K": 13, "q6_K": 14, "q8_K": 15, "iq4_nl": 20, "i32": 26,
 }
-BLOCK_ELEMS = {"f32": 1, "f16": 1, "i32": 1, "q4_0": 32, "q8_0": 32, "q8_1": 32, "q4_K": 256, "q5_K": 256, "q6_K": 256}
-BLOCK_BYTES = {"f32": 4, "f16": 2, "i32": 4, "q4_0": 18, "q8_0": 34, "q8_1": 36, "q4_K": 144, "q5_K": 176, "q6_K": 210}
+BLOCK_ELEMS = {"f32": 1, "f16": 1, "i32": 1, "q4_0": 32, "q8_0": 32, "q8_1": 32, "q4_K": 256, "q5_K": 256, "q6_K": 256,
+               "q4_1": 32, "q5_0": 32, "q5_1": 32, "iq4_nl": 32}
+BLOCK_BYTES = {"f32": 4, "f16": 2, "i32": 4, "q4_0": 18, "q8_0": 34, "q8_1": 36, "q4_K": 144, "q5_K": 176, "q6_K": 210,
+               "q4_1": 20, "q5_0": 22, "q5_1": 24, "iq4_nl": 18}
 QUANT_TYPES = ("q4_0", "q8_0", "q4_K", "q5_K", "q6_K")
+EXTRA_TYPES = ("q4_1", "q5_0", "q5_1", "iq4_nl")
 
 GGML_BACKEND_DEVICE_TYPE_CPU = 0
 GGML_BACKEND_DEVICE_TYPE_GPU = 1
@@ -84,7 +87,7 @@ class GgmlHost:
         b.ggml_fp32_to_fp16_row.restype = None;         b.ggml_fp32_to_fp16_row.argtypes = [vp, vp, i64]
         b.quantize_row_q8_1_ref.restype = None;         b.quantize_row_q8_1_ref.argtypes = [vp, vp, i64]
         b.quantize_row_q8_K_ref.restype = None;         b.quantize_row_q8_K_ref.argtypes = [vp, vp, i64]
-        for t in QUANT_TYPES:
+        for t in QUANT_TYPES + EXTRA_TYPES:
             f = getattr(b, f"dequantize_row_{t}")
             f.restype = None; f.argtypes = [vp, vp, i64]
         b.ggml_backend_alloc_ctx_tensors.restype = vp;  b.ggml_backend_alloc_ctx_tensors.argtypes = [vp, vp]

@@ -12,10 +12,12 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_DIR = os.path.join(ROOT, "oracle")
 
-TYPE_ID = {"f32": 0, "f16": 1, "q4_0": 2, "q8_0": 8, "q8_1": 9, "q4_K": 12, "q5_K": 13, "q6_K": 14}
-BLOCK_ELEMS = {"q4_0": 32, "q8_0": 32, "q8_1": 32, "q4_K": 256, "q5_K": 256, "q6_K": 256}
-BLOCK_BYTES = {"q4_0": 18, "q8_0": 34, "q8_1": 36, "q4_K": 144, "q5_K": 176, "q6_K": 210}
-QUANT_TYPES = ("q4_0", "q8_0", "q4_K", "q5_K", "q6_K")
+TYPE_ID = {"f32": 0, "f16": 1, "q4_0": 2, "q8_0": 8, "q8_1": 9, "q4_K": 12, "q5_K": 13, "q6_K": 14,
+           "q4_1": 3, "q5_0": 6, "q5_1": 7, "iq4_nl": 20}
+BLOCK_ELEMS = {"q4_0": 32, "q8_0": 32, "q8_1": 32, "q4_K": 256, "q5_K": 256, "q6_K": 256, "q4_1": 32, "q5_0": 32, "q5_1": 32, "iq4_nl": 32}
+BLOCK_BYTES = {"q4_0": 18, "q8_0": 34, "q8_1": 36, "q4_K": 144, "q5_K": 176, "q6_K": 210, "q4_1": 20, "q5_0": 22, "q5_1": 24, "iq4_nl": 18}
+QUANT_TYPES = ("q4_0", "q8_0", "q4_K", "q5_K", "q6_K")           # the hot path: every kernel
+EXTRA_TYPES = ("q4_1", "q5_0", "q5_1", "iq4_nl")                 # dequantize / GET_ROWS / CPY and the general mat-vec only
 
 
 def build():
@@ -114,9 +116,11 @@ class Oracle:
 # Seeded synthetic weights that need neither the reference nor a K-quant quantizer: every bit
 # pattern of the integer fields of a block is legal, so random bytes with sane fp16 scale fields are
 # valid "random-quantized" weights.  Scales are drawn so that dequantized values are O(1).
-F16_FIELDS = {"q4_0": (0,), "q8_0": (0,), "q4_K": (0, 2), "q5_K": (0, 2), "q6_K": (208,)}
+F16_FIELDS = {"q4_0": (0,), "q8_0": (0,), "q4_K": (0, 2), "q5_K": (0, 2), "q6_K": (208,),
+              "q4_1": (0, 2), "q5_0": (0,), "q5_1": (0, 2), "iq4_nl": (0,)}
 _SCALE_RANGE = {"q4_0": (0.02, 0.15), "q8_0": (0.001, 0.01), "q4_K": (0.0005, 0.004),
-                "q5_K": (0.0003, 0.002), "q6_K": (0.0001, 0.0006)}
+                "q5_K": (0.0003, 0.002), "q6_K": (0.0001, 0.0006),
+                "q4_1": (0.02, 0.1), "q5_0": (0.01, 0.06), "q5_1": (0.01, 0.05), "iq4_nl": (0.002, 0.008)}
 
 
 def random_blocks(t, nrows, k, seed):

@@ -89,8 +89,8 @@ def test_batch_workspace_size_covers_every_list_path(built):
         assert size([node("q4_K", 4096, k, 1)] * 10) >= 10 * (k + k // 8)
         for n in (2, 4, 8):
             for t in ("q4_K", "q5_K", "q6_K"):
-                assert size([node(t, 4096, k, n)]) >= 8 * k + (k // 32) * 8 * 16, (t, k, n)
-            assert size([node("q4_K", 4096, k, n), node("q6_K", 1024, k, n)]) >= 2 * (8 * k + (k // 32) * 8 * 16)
+                assert size([node(t, 4096, k, n)]) >= 8 * k + (k // 256) * 8 * 52, (t, k, n)      # int8 columns + Q8_K scales and sums
+            assert size([node("q4_K", 4096, k, n), node("q6_K", 1024, k, n)]) >= 2 * (8 * k + (k // 256) * 8 * 52)
             assert size([node("q8_0", 4096, k, n)]) >= n * (k + k // 8)          # one persistent entry per column
         big = size([node("q4_K", 4096, k, 512)])
         assert big >= 512 * k                                                     # batched path: activations staged once

@@ -4,10 +4,10 @@ random inputs than the committed fixtures.  Skips where oracle/_ref is absent.""
 import numpy as np
 import pytest
 
-from oracle_lib import BLOCK_BYTES, BLOCK_ELEMS, QUANT_TYPES, random_blocks
+from oracle_lib import BLOCK_BYTES, BLOCK_ELEMS, EXTRA_TYPES, QUANT_TYPES, random_blocks
 
 
-@pytest.mark.parametrize("t", QUANT_TYPES)
+@pytest.mark.parametrize("t", QUANT_TYPES + EXTRA_TYPES)
 def test_dequantize_random_bytes(oracle, ref_host, t):
     # raw random bytes incl. arbitrary fp16 scale bit patterns (inf/nan compare by bits)
     rng = np.random.default_rng(7)
@@ -19,7 +19,7 @@ def test_dequantize_random_bytes(oracle, ref_host, t):
         assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), (t, rep)
 
 
-@pytest.mark.parametrize("t", QUANT_TYPES)
+@pytest.mark.parametrize("t", QUANT_TYPES + EXTRA_TYPES)
 def test_dequantize_quantized_weights(oracle, ref_host, t):
     rng = np.random.default_rng(11)
     k = 1024
@@ -50,14 +50,14 @@ def test_weight_quantizers(oracle, ref_host, t):
     assert np.array_equal(oracle.quantize(t, x), ref_host.quantize(t, x))
 
 
-@pytest.mark.parametrize("t", QUANT_TYPES)
+@pytest.mark.parametrize("t", QUANT_TYPES + EXTRA_TYPES)
 def test_random_blocks_are_sane(oracle, t):
     b = random_blocks(t, 4, 1024, seed=3)
     y = np.stack([oracle.dequantize(t, b[r], 1024) for r in range(4)])
     assert np.isfinite(y).all() and 0.05 < np.abs(y).max() < 64.0
 
 
-@pytest.mark.parametrize("t", QUANT_TYPES)
+@pytest.mark.parametrize("t", QUANT_TYPES + EXTRA_TYPES)
 def test_mul_mat_live_vs_reference_cpu(oracle, ref_host, t):
     rng = np.random.default_rng(19)
     m, k, n = 48, 1024, 5
