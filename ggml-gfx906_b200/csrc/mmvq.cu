@@ -297,19 +297,23 @@ extern "C" int b200_mul_mat_id(int type_a, const void * as_dev, const int64_t ne
 }
 
 // ---------------------------------------------------------------- a list of MUL_MAT nodes
+constexpr int LIST_LANES = 3;        // independent batched nodes of a list run on up to three streams (side_lanes below)
 extern "C" size_t b200_mul_mat_batch_workspace_size(const b200_mul_mat_node * nodes, int64_t count) {
     // the largest single-node need + one q8 activation record per decode node (persistent launches) + the
     // completion counters of the (at most three, one per format family) launches of a flush
-    size_t need = 256, acts = 0;
+    size_t need = 256, acts = 0, batched = 0;
+    int n_batched = 0;
     for (int64_t i = 0; i < count; i++) {
         const size_t s = b200_mul_mat_workspace_size(nodes[i].type_a, nodes[i].ne_a, nodes[i].ne_b);
         if (s > need) need = s;
+        if (nodes[i].ne_b[1] > B200_MMVQ_MAX_N) { n_batched++; if (s > batched) batched = s; }      // may share the lanes (side_lanes)
         if (nodes[i].ne_b[1] >= 1 && nodes[i].ne_b[1] <= B200_MMVQ_MAX_N && nodes[i].ne_a[0] > 0) {
             const size_t per_col = (size_t) nodes[i].ne_b[1] * batch_acts_record_bytes(nodes[i].ne_a[0]);
             const size_t tile = nodes[i].ne_b[1] >= 2 ? cols_ws_bytes(nodes[i].ne_a[0], nodes[i].ne_b[1]) : 0;
             acts += per_col > tile ? per_col : tile;
         }
     }
+    if (n_batched > 1 && LIST_LANES * (batched + 256) > need) need = LIST_LANES * (batched + 256);
     return need + acts + 3 * BATCH_DONE_BYTES + 256;
 }
 
@@ -355,6 +359,31 @@ constexpr size_t PEER_CTRL_FAMILY = 8192;         // per format family (= launch
                                                   // (one arrival per rank) and two sets of 448 local arrival counters (one per CTA)
 constexpr size_t PEER_CTRL_BYTES = 32768;         // head of the symmetric region
 static_assert(64 + 4 * BATCH_MAX_NODES * sizeof(unsigned) <= PEER_CTRL_FAMILY && 3 * PEER_CTRL_FAMILY <= PEER_CTRL_BYTES, "control block");
+
+// Independent batched (n > 8) nodes of a list -- wq / wk / wv, gate / up of a prefill graph -- run side by side: the caller's
+// stream plus two side streams forked and joined by events (capturable: a captured list becomes parallel graph branches),
+// each lane with its own third of the workspace.  A 1024 x 4096 matrix at n = 512 fills 64 of 148 SMs for 34 us on its own.
+namespace {
+struct side_lanes {
+    cudaStream_t s[LIST_LANES - 1] = {};
+    cudaEvent_t  fork = nullptr, join[LIST_LANES - 1] = {};
+    bool ok = false, tried = false;
+};
+side_lanes & get_side_lanes() {
+    static thread_local side_lanes lanes[64];       // per host thread and device: a backend is driven by one thread at a time
+    side_lanes & L = lanes[current_device_slot()];
+    if (!L.tried) {
+        L.tried = true;
+        bool ok = cudaEventCreateWithFlags(&L.fork, cudaEventDisableTiming) == cudaSuccess;
+        for (int i = 0; i < LIST_LANES - 1 && ok; i++)
+            ok = cudaStreamCreateWithFlags(&L.s[i], cudaStreamNonBlocking) == cudaSuccess &&
+                 cudaEventCreateWithFlags(&L.join[i], cudaEventDisableTiming) == cudaSuccess;
+        if (!ok) cudaGetLastError();
+        L.ok = ok;
+    }
+    return L;
+}
+}
 
 static int run_list(const b200_mul_mat_node * nodes, int64_t count, void * workspace_dev, size_t workspace_bytes, void * stream,
                     int32_t * plan, const b200_peer_group * pg = nullptr, long long remote_delta = 0) {
@@ -443,6 +472,23 @@ static int run_list(const b200_mul_mat_node * nodes, int64_t count, void * works
         cur.reset((uint8_t *) workspace_dev, workspace_bytes);
         return rc;
     };
+    // batched nodes in flight on the lanes (see side_lanes): their activation and output ranges
+    struct inflight { uintptr_t x0, x1, d0, d1; };
+    inflight infl[LIST_LANES];
+    int n_inflight = 0;
+    static const int use_lanes = env_int("GGML_B200_LIST_LANES", 1);
+    auto join_lanes = [&]() -> int {
+        if (n_inflight > 1) {
+            side_lanes & L = get_side_lanes();
+            for (int j = 1; j < n_inflight; j++) {
+                cudaError_t e = cudaEventRecord(L.join[j - 1], L.s[j - 1]);
+                if (e == cudaSuccess) e = cudaStreamWaitEvent(st, L.join[j - 1], 0);
+                if (e != cudaSuccess) return -(int) e;
+            }
+        }
+        n_inflight = 0;
+        return B200_OK;
+    };
     for (int64_t i = 0; i < count; i++) {
         const b200_mul_mat_node & nd = nodes[i];
         const int64_t k = nd.ne_a[0], m = nd.ne_a[1];
@@ -462,11 +508,48 @@ static int run_list(const b200_mul_mat_node * nodes, int64_t count, void * works
             int rc = flush();
             if (rc) return rc;
             if (dry) { plan[3 * i] = group++; plan[3 * i + 1] = -1; plan[3 * i + 2] = 0; continue; }
+            // a batched node that neither reads nor overwrites what the nodes in flight on the other lanes touch joins them
+            const int64_t cols_all = nd.ne_b[1] * nd.ne_b[2] * nd.ne_b[3];
+            const uintptr_t x0 = (uintptr_t) nd.b_dev, x1 = x0 + (size_t) nd.nb_b[3] * (size_t) nd.ne_b[3];
+            const uintptr_t d0 = (uintptr_t) nd.dst_dev, d1 = d0 + (size_t) m * (size_t) cols_all * 4;
+            const size_t lane_ws = (workspace_bytes / LIST_LANES) & ~(size_t) 255;
+            bool lane_ok = use_lanes && flat && ncols > B200_MMVQ_MAX_N && type_is_quant(nd.type_a) && !pg &&
+                           b200_mul_mat_workspace_size(nd.type_a, nd.ne_a, nd.ne_b) <= lane_ws;
+            if (lane_ok) {
+                for (int j = 0; j < n_inflight && lane_ok; j++) {
+                    const inflight & f = infl[j];
+                    if ((x0 < f.d1 && f.d0 < x1) || (d0 < f.d1 && f.d0 < d1) || (d0 < f.x1 && f.x0 < d1)) lane_ok = false;
+                }
+            }
+            if (!lane_ok || n_inflight == LIST_LANES) { rc = join_lanes(); if (rc) return rc; }
+            if (lane_ok) {
+                side_lanes & L = get_side_lanes();
+                if (!L.ok) lane_ok = false;
+                else {
+                    const int lane = n_inflight;
+                    cudaStream_t ls = st;
+                    if (lane > 0) {
+                        ls = L.s[lane - 1];
+                        const cudaError_t e = cudaStreamWaitEvent(ls, L.fork, 0);
+                        if (e != cudaSuccess) return -(int) e;
+                    } else {
+                        // lane 0 is the caller's stream: the fork point of the group is everything enqueued before this node
+                        const cudaError_t e = cudaEventRecord(L.fork, st);
+                        if (e != cudaSuccess) return -(int) e;
+                    }
+                    rc = b200_mul_mat_ex(nd.type_a, nd.a_dev, nd.ne_a, nd.nb_a, nd.b_dev, nd.ne_b, nd.nb_b, nd.dst_dev,
+                                         (uint8_t *) workspace_dev + (size_t) lane * lane_ws, lane_ws, nd.flags, ls);
+                    if (rc) return rc;
+                    infl[n_inflight++] = inflight{ x0, x1, d0, d1 };
+                    continue;
+                }
+            }
             rc = b200_mul_mat_ex(nd.type_a, nd.a_dev, nd.ne_a, nd.nb_a, nd.b_dev, nd.ne_b, nd.nb_b, nd.dst_dev,
                                  workspace_dev, workspace_bytes, nd.flags, stream);
             if (rc) return rc;
             continue;
         }
+        { const int rc = join_lanes(); if (rc) return rc; }      // list nodes follow on the caller's stream
         const uintptr_t x0 = (uintptr_t) nd.b_dev, x1 = x0 + (size_t) (ncols - 1) * nd.nb_b[1] + (size_t) k * 4;
         const uintptr_t d0 = (uintptr_t) nd.dst_dev, d1 = d0 + (size_t) m * ncols * 4;
         const int owner = to_cols ? 3 : batch_family(nd.type_a);
@@ -555,6 +638,7 @@ static int run_list(const b200_mul_mat_node * nodes, int64_t count, void * works
                              workspace_dev, workspace_bytes, nd.flags, stream);
         if (rc) return rc;
     }
+    { const int rc = join_lanes(); if (rc) return rc; }
     return flush();
 }
 

@@ -516,6 +516,45 @@ def test_mul_mat_batch_few_columns_padded_row_stride(kern, oracle):
         assert oracle.nmse(oracle.mul_mat(t, w_np, m, k, x_np, mode=mode), y.cpu().numpy()) <= NMSE_ORACLE, (t, m, k)
 
 
+def test_mul_mat_batch_prefill_nodes_share_lanes(kern, oracle):
+    """independent batched (n > 8) nodes of a list run side by side on up to three streams; a node that reads another's
+    output waits for it.  Every output equals the node computed alone, bit for bit -- eagerly and replayed from a CUDA graph
+    (the side streams are captured as parallel branches)."""
+    import b200
+    import torch
+    n = 48
+    specs = [("q4_K", 1024, 1024, "x"), ("q6_K", 512, 1024, "x"), ("q8_0", 300, 1024, "x"), ("q4_K", 640, 1024, 0),    # node 3 reads node 0
+             ("q5_K", 256, 512, "x2"), ("q4_0", 200, 640, 3)]                                                         # node 5 reads node 3
+    rng = np.random.default_rng(77)
+    xs = {"x": kern.to_device(rng.uniform(-1, 1, size=(n, 1024)).astype(np.float32)),
+          "x2": kern.to_device(rng.uniform(-1, 1, size=(n, 512)).astype(np.float32))}
+    ws = [dev_blocks(kern, random_blocks(t, m, k, seed=80 + i)) for i, (t, m, k, _) in enumerate(specs)]
+    ys = [torch.zeros((n, m), dtype=torch.float32, device=kern.device) for (_, m, _, _) in specs]
+    src = lambda i: xs[specs[i][3]] if isinstance(specs[i][3], str) else ys[specs[i][3]]
+    nodes = (b200.MulMatNode * len(specs))(*[b200.mul_mat_node(t, ws[i].data_ptr(), m, k, src(i).data_ptr(), n, ys[i].data_ptr())
+                                             for i, (t, m, k, _) in enumerate(specs)])
+    wsz = torch.empty(int(kern.lib.b200_mul_mat_batch_workspace_size(nodes, len(specs))) + 256, dtype=torch.uint8, device=kern.device)
+    kern.mul_mat_batch(nodes, ws=wsz)
+    torch.cuda.synchronize()
+    want = []
+    for i, (t, m, k, _) in enumerate(specs):
+        xin = src(i) if isinstance(specs[i][3], str) else want[specs[i][3]]
+        want.append(kern.mul_mat(t, ws[i], m, k, xin.contiguous()).reshape(n, m).clone())
+    for i in range(len(specs)):
+        assert torch.equal(ys[i].view(torch.int32), want[i].view(torch.int32)), i
+    # replay from a CUDA graph
+    for y in ys:
+        y.zero_()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        kern.mul_mat_batch(nodes, ws=wsz)
+    for _ in range(3):
+        g.replay()
+    torch.cuda.synchronize()
+    for i in range(len(specs)):
+        assert torch.equal(ys[i].view(torch.int32), want[i].view(torch.int32)), ("graph", i)
+
+
 def _batch_nodes(kern, mats, seed0=0, shared_x=False):
     import b200
     import torch
