@@ -170,7 +170,7 @@ template <bool HAS_QH> struct expander_k45 {
         if (HAS_QH) slab_words<4, 8>(s, qh);
     }
     // half: which 32 of the 64 elements this thread expands (two producer threads per row)
-    template <int SUB> __device__ __forceinline__ void expand64(const uint8_t * s, uint8_t * a_row, int row7, int half) {
+    template <int SUB> __device__ __forceinline__ void expand64(const uint8_t * s, uint8_t * a_row, int row7, int half, int ccm) {
         const float d = f16_bits_to_f32(hdr[0]), dmin = f16_bits_to_f32(hdr[0] >> 16);
         uint32_t q[8];
         slab_words<(HAS_QH ? 12 : 4) + 8 * SUB, 8>(s, q);
@@ -183,6 +183,7 @@ template <bool HAS_QH> struct expander_k45 {
             const wt2 m1 = f32_to_wt2(-(dmin * (float) mn));
 #pragma unroll
             for (int cc = 0; cc < 4; cc++) {
+                if (!((ccm >> cc) & 1)) continue;
                 wt2 v[4];
 #pragma unroll
                 for (int j = 0; j < 4; j++) {
@@ -223,22 +224,22 @@ template <> struct expander<T_Q6_K> {
             default: begin_slab_wo<3>(s); break;
         }
     }
-    template <int SUB> __device__ __forceinline__ void expand64(const uint8_t * s, uint8_t * a_row, int row7, int half) {
+    template <int SUB> __device__ __forceinline__ void expand64(const uint8_t * s, uint8_t * a_row, int row7, int half, int ccm) {
         switch (wo) {
-            case 0: expand64_wo<SUB, 0>(s, a_row, row7, half); break;
-            case 1: expand64_wo<SUB, 1>(s, a_row, row7, half); break;
-            case 2: expand64_wo<SUB, 2>(s, a_row, row7, half); break;
-            default: expand64_wo<SUB, 3>(s, a_row, row7, half); break;
+            case 0: expand64_wo<SUB, 0>(s, a_row, row7, half, ccm); break;
+            case 1: expand64_wo<SUB, 1>(s, a_row, row7, half, ccm); break;
+            case 2: expand64_wo<SUB, 2>(s, a_row, row7, half, ccm); break;
+            default: expand64_wo<SUB, 3>(s, a_row, row7, half, ccm); break;
         }
     }
-    template <int SUB, int WO> __device__ __forceinline__ void expand64_wo(const uint8_t * s, uint8_t * a_row, int row7, int half) {
+    template <int SUB, int WO> __device__ __forceinline__ void expand64_wo(const uint8_t * s, uint8_t * a_row, int row7, int half, int ccm) {
         constexpr int h = SUB >> 1, p = SUB & 1;
         uint32_t ql[16], qh[8];
         slab_words_sh<16 * h + WO, 16>(s, sh, ql);           // ql[64h .. 64h+64)
         slab_words_sh<32 + 8 * h + WO, 8>(s, sh, qh);        // qh[32h .. 32h+32)
 #pragma unroll
         for (int c = 0; c < 8; c++) {
-            if ((c >> 2) != half) continue;
+            if ((c >> 2) != half || !((ccm >> (c & 3)) & 1)) continue;
             const int st = 2 * p + (c >> 2);      // stream
             const int l0 = 8 * (c & 3);
             const int sidx = 8 * h + 2 * st + (l0 >> 4);
@@ -262,7 +263,7 @@ template <> struct expander<T_Q6_K> {
 template <> struct expander<T_Q4_0> {
     int nvalid;   // valid blocks in this slab (k tail)
     __device__ __forceinline__ void begin_slab(const uint8_t *, int nv) { nvalid = nv; }
-    template <int SUB> __device__ __forceinline__ void expand64(const uint8_t * s, uint8_t * a_row, int row7, int half) {
+    template <int SUB> __device__ __forceinline__ void expand64(const uint8_t * s, uint8_t * a_row, int row7, int half, int ccm) {
         uint32_t w[9];
         slab_words<9 * SUB, 9>(s, w);
 #pragma unroll
@@ -270,7 +271,7 @@ template <> struct expander<T_Q4_0> {
             if (b != half) continue;
             if (2 * SUB + b >= nvalid) {
 #pragma unroll
-                for (int cc = 0; cc < 4; cc++) store_zero_chunk(a_row, row7, 4 * b + cc);
+                for (int cc = 0; cc < 4; cc++) if ((ccm >> cc) & 1) store_zero_chunk(a_row, row7, 4 * b + cc);
                 continue;
             }
             uint32_t qs[4];
@@ -279,6 +280,7 @@ template <> struct expander<T_Q4_0> {
             const wt2 d = f32_to_wt2(f16_bits_to_f32(b == 0 ? w[0] : (w[4] >> 16)));
 #pragma unroll
             for (int cc = 0; cc < 4; cc++) {
+                if (!((ccm >> cc) & 1)) continue;
                 wt2 v[4];
 #pragma unroll
                 for (int j = 0; j < 4; j++) {
@@ -296,7 +298,7 @@ template <> struct expander<T_Q4_0> {
 template <> struct expander<T_Q8_0> {
     int nvalid;
     __device__ __forceinline__ void begin_slab(const uint8_t *, int nv) { nvalid = nv; }
-    template <int SUB> __device__ __forceinline__ void expand64(const uint8_t * s, uint8_t * a_row, int row7, int half) {
+    template <int SUB> __device__ __forceinline__ void expand64(const uint8_t * s, uint8_t * a_row, int row7, int half, int ccm) {
         uint32_t w[17];
         slab_words<17 * SUB, 17>(s, w);
 #pragma unroll
@@ -304,7 +306,7 @@ template <> struct expander<T_Q8_0> {
             if (b != half) continue;
             if (2 * SUB + b >= nvalid) {
 #pragma unroll
-                for (int cc = 0; cc < 4; cc++) store_zero_chunk(a_row, row7, 4 * b + cc);
+                for (int cc = 0; cc < 4; cc++) if ((ccm >> cc) & 1) store_zero_chunk(a_row, row7, 4 * b + cc);
                 continue;
             }
             // int8 q = (q & 127) - 128 * sign: bf16 holds 128 + (q & 127) exactly (the magic), the sign bit of the
@@ -314,6 +316,7 @@ template <> struct expander<T_Q8_0> {
             const wt2 dm64 = __hmul2(d, f32_to_wt2(-64.0f)), dm128 = __hmul2(d, f32_to_wt2(-128.0f));
 #pragma unroll
             for (int cc = 0; cc < 4; cc++) {
+                if (!((ccm >> cc) & 1)) continue;
                 wt2 v[4];
 #pragma unroll
                 for (int j = 0; j < 4; j++) {
@@ -352,7 +355,13 @@ constexpr int MMQ_BM = 128;
 constexpr int MMQ_BK = 64;           // K elements per MMA stage (one 128-byte swizzle row)
 constexpr int MMQ_RS = 3;            // raw slab ring depth (2 for the formats with slabs > 200 bytes: shared memory)
 template <int T, int BN = 256> struct mmq_rs { static constexpr int value = (slab<T>::bytes > 200 || BN > 256) ? 2 : MMQ_RS; };
-constexpr int MMQ_THREADS = 320;      // 8 weight-producer warps (two threads per row) + activation loader + MMA issuer
+#ifndef B200_MMQ_NP
+#define B200_MMQ_NP 2
+#endif
+constexpr int MMQ_NP = B200_MMQ_NP;   // producer threads per weight row: 2 (each expands 32 of every 64 elements) or 4 (16 each:
+                                      // -DB200_MMQ_NP=4, measured 5 % slower at 256-column tiles, profiles/r03u_prefill_16_producer_warps.txt)
+constexpr int MMQ_PW = 4 * MMQ_NP;    // weight-producer warps
+constexpr int MMQ_THREADS = (MMQ_PW + 2) * 32;      // + activation loader + MMA issuer
 #ifndef MMQ_STAGES_SMALL
 #define MMQ_STAGES_SMALL 4
 #endif
@@ -417,25 +426,28 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b, const __g
     const int nkt   = min((int) ((a.k + MMQ_BK - 1) / MMQ_BK) - kt0, 4 * nslab);      // 64-deep MMA stages
 
     if (tid == 0) {
-        for (int s = 0; s < ST; s++) { mbar_init(&full[s], 256 + 1); mbar_init(&empty[s], 1); }
+        for (int s = 0; s < ST; s++) { mbar_init(&full[s], 128 * MMQ_NP + 1); mbar_init(&empty[s], 1); }
         // ALIGNED: one 2-D TMA tile per raw slab (128 rows x slab bytes), issued by the loader thread;
         // otherwise one bulk copy per row, issued by that row's producer thread
         for (int s = 0; s < MMQ_RS * 4; s++) mbar_init(&raw_full[s], ALIGNED ? 1 : 32);
-        for (int s = 0; s < MMQ_RS; s++) mbar_init(&raw_empty[s], 256);
+        for (int s = 0; s < MMQ_RS; s++) mbar_init(&raw_empty[s], 128 * MMQ_NP);
         mbar_init(tmem_full, 1);
         mbar_fence_init();
     }
-    if (warp == 9) tmem_alloc(tmem_slot, CFG::tmem_cols);
+    if (warp == MMQ_PW + 1) tmem_alloc(tmem_slot, CFG::tmem_cols);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    if (warp < 8) {
+    if (warp < MMQ_PW) {
         // ===================================================== weight producers: thread pair (prow, half) per row.
         // The quant -> fp16 expansion is the bound of this kernel (one warp per scheduler cannot hide its own
         // latencies); warps w and w + 4 share rows 32 w .. 32 w + 31, each expanding 32 of every 64 elements.
-        const int prow = tid & 127, half = tid >> 7, pw = warp & 3;
+        // thread (prow, part): part = which 64 / MMQ_NP elements of every 64 it expands; the part-0 thread of a row also
+        // issues / realigns its raw bytes (unaligned rows) 
+        const int prow = tid & 127, part = tid >> 7, pw = warp & 3;
+        const int half = part / (MMQ_NP / 2), ccm = MMQ_NP == 4 ? ((part & 1) ? 0xC : 0x3) : 0xF;
         const int64_t row = (m0 + prow < a.m) ? (m0 + prow) : (a.m - 1);   // rows past m recompute the last row, never stored
         const uint8_t * wrow = a.w + row * a.w_row_stride;
         const int row7 = prow & 7;
@@ -458,7 +470,7 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b, const __g
             bulk_g2s(my_raw[r], src - off, cp, bar);
         };
 
-        if (!ALIGNED && half == 0) {
+        if (!ALIGNED && part == 0) {
             for (int s = 0; s < RS && s < nslab; s++) issue_raw(s);
         }
 
@@ -467,7 +479,7 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b, const __g
             const int r = s % RS;
             mbar_wait(&raw_full[r * 4 + (ALIGNED ? 0 : pw)], (uint32_t) ((s / RS) & 1));
             uint8_t * slab_ptr = my_raw[r];
-            if (!ALIGNED && half == 0) {
+            if (!ALIGNED && part == 0) {
                 // shift every row of this warp down to its 16-byte aligned slot start (2-byte granules,
                 // lanes side by side: conflict-free), in place
                 const uint8_t * src = wrow + (size_t) (s0 + s) * BLK_PER_SLAB * fmt<T>::bytes;
@@ -489,7 +501,7 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b, const __g
                 }
                 __syncwarp();
             }
-            if (!ALIGNED) named_bar_sync(1 + pw, 64);        // the pair's other warp reads the realigned rows
+            if (!ALIGNED) named_bar_sync(1 + pw, 32 * MMQ_NP);        // the pair's other warp reads the realigned rows
             if constexpr (T == T_Q6_K) ex.set_skew(ALIGNED ? slab_tma<T>::skew(s0 + s) : 0);
             ex.begin_slab(slab_ptr, slab_valid_blocks(s));
 #pragma unroll
@@ -499,10 +511,10 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b, const __g
                     const int st = kt % ST;
                     if (kt >= ST) mbar_wait(&empty[st], (uint32_t) (((kt / ST) - 1) & 1));
                     uint8_t * a_row = a_tiles + (size_t) st * CFG::a_bytes + prow * 128;
-                    if      (sub == 0) ex.template expand64<0>(slab_ptr, a_row, row7, half);
-                    else if (sub == 1) ex.template expand64<1>(slab_ptr, a_row, row7, half);
-                    else if (sub == 2) ex.template expand64<2>(slab_ptr, a_row, row7, half);
-                    else               ex.template expand64<3>(slab_ptr, a_row, row7, half);
+                    if      (sub == 0) ex.template expand64<0>(slab_ptr, a_row, row7, half, ccm);
+                    else if (sub == 1) ex.template expand64<1>(slab_ptr, a_row, row7, half, ccm);
+                    else if (sub == 2) ex.template expand64<2>(slab_ptr, a_row, row7, half, ccm);
+                    else               ex.template expand64<3>(slab_ptr, a_row, row7, half, ccm);
                     fence_proxy_async_smem();       // generic-proxy stores -> visible to the tensor core's async proxy
                     mbar_arrive(&full[st]);
                 }
@@ -510,8 +522,8 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b, const __g
             if (ALIGNED) {
                 mbar_arrive(&raw_empty[r]);          // the loader refills the slot when all 256 producers have left it
             } else {
-                named_bar_sync(1 + pw, 64);          // both warps of the pair are done with the raw slot
-                if (half == 0 && s + RS < nslab) issue_raw(s + RS);
+                named_bar_sync(1 + pw, 32 * MMQ_NP);          // both warps of the pair are done with the raw slot
+                if (part == 0 && s + RS < nslab) issue_raw(s + RS);
             }
         }
 
@@ -522,9 +534,9 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b, const __g
         float * out = a.ksplit > 1 ? a.part + (size_t) blockIdx.z * (size_t) a.n * (size_t) a.m : a.dst;
         const int64_t out_stride = a.ksplit > 1 ? a.m : a.dst_col_stride;
         const uint32_t taddr = tmem_base + ((uint32_t) (pw * 32) << 16);      // a warp reaches TMEM lanes 32 (warp % 4) ..
-        constexpr int CH = BN >= 16 ? BN / 2 : BN;                             // .. the pair splits the columns
+        constexpr int CH = BN / MMQ_NP >= 8 ? BN / MMQ_NP : 8;                  // .. the row's MMQ_NP threads split the columns
 #pragma unroll 1
-        for (int c0 = (BN >= 16 ? half * CH : 0); c0 < (BN >= 16 ? (half + 1) * CH : (half == 0 ? BN : 0)); c0 += 8) {
+        for (int c0 = part * CH; c0 < (part + 1) * CH && c0 < BN; c0 += 8) {
             if (n0 + c0 >= a.n) break;               // warp-uniform
             uint32_t v[8];
             tmem_ld8(taddr + (uint32_t) c0, v);
@@ -537,7 +549,7 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b, const __g
             }
         }
         tc_fence_before();
-    } else if (warp == 8) {
+    } else if (warp == MMQ_PW) {
         // ===================================================== activation loader (TMA)
         if (lane == 0) {
             int next_slab = 0;
@@ -588,7 +600,7 @@ k_mmq_tc(const mmq_args a, const __grid_constant__ CUtensorMap tmap_b, const __g
     }
 
     __syncthreads();
-    if (warp == 9) {
+    if (warp == MMQ_PW + 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, CFG::tmem_cols);
     }
