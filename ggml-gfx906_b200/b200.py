@@ -96,6 +96,7 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
     lib.b200_dequantize_4d.restype = i32
     lib.b200_dequantize_4d.argtypes = [i32, vp, A4i, A4s, vp, i32, A4i, A4s, vp]
     lib.b200_quantize_row_q8_1.restype = i32;    lib.b200_quantize_row_q8_1.argtypes = [vp, sz, i64, i64, vp, vp]
+    lib.b200_quantize_rows.restype = i32;        lib.b200_quantize_rows.argtypes = [i32, vp, sz, i64, i64, vp, sz, vp]
     lib.b200_get_rows.restype = i32
     lib.b200_get_rows.argtypes = [i32, vp, sz, i64, i64, vp, sz, i64, vp, i32, sz, vp]
     lib.b200_mul_mat_workspace_size.restype = sz
@@ -365,6 +366,15 @@ class Kernels:
         out = torch.empty((n, k // 32 * 36), dtype=torch.uint8, device=self.device)
         self._check(self.lib.b200_quantize_row_q8_1(x.data_ptr(), x.stride(0) * 4, k, n, out.data_ptr(), self._stream()),
                     "quantize_row_q8_1")
+        return out
+
+    def quantize_rows(self, t: str, x):
+        """x: f32 [n, k] -> uint8 [n, k/32 * block bytes] of Q8_0 / Q4_0 blocks (quantize_row_*_ref values)."""
+        torch = self.torch
+        n, k = x.shape
+        out = torch.empty((n, row_bytes(t, k)), dtype=torch.uint8, device=self.device)
+        self._check(self.lib.b200_quantize_rows(TYPE_ID[t], x.data_ptr(), x.stride(0) * 4, k, n, out.data_ptr(), out.stride(0), self._stream()),
+                    "quantize_rows")
         return out
 
     def quantize_acts_record(self, x):

@@ -62,12 +62,14 @@ struct cols_args {
 //   s32 uint2 [nsb][8 columns][2]  word pair t: .x = low bytes (sum & 63), .y = high bytes (sum >> 6) of the sums of the
 //                                  32-blocks 4t..4t+3 -- the B fragments of the m16n8k16 MMAs against the 6-bit mins
 //   s16 uint2 [nsb][8 columns][4]  the same for the sums of 16 (bsums), groups 4t..4t+3 -- against Q6_K's int8 scales
+//   n32 int32 [nsb][8 sub-blocks][8 columns]  -8 * (sum of the 32-block): the C input of Q4_0's MMAs (weights enter as q, not q - 8)
 struct cols_meta {
-    const float * d; const uint2 * s32; const uint2 * s16;
+    const float * d; const uint2 * s32; const uint2 * s16; const int * n32;
 };
 __device__ __host__ __forceinline__ cols_meta cols_meta_of(const uint8_t * ym, int k) {
     const size_t nsb = (size_t) (k >> 8);
-    return { reinterpret_cast<const float *>(ym), reinterpret_cast<const uint2 *>(ym + nsb * 32), reinterpret_cast<const uint2 *>(ym + nsb * 160) };
+    return { reinterpret_cast<const float *>(ym), reinterpret_cast<const uint2 *>(ym + nsb * 32), reinterpret_cast<const uint2 *>(ym + nsb * 160),
+             reinterpret_cast<const int *>(ym + nsb * 416) };
 }
 
 // ---------------------------------------------------------------- activations of the list: f32 -> Q8_K columns
@@ -84,10 +86,11 @@ __global__ void __launch_bounds__(256) k_quantize_cols(const __grid_constant__ c
     float  * dp  = const_cast<float *>(M.d) + sb * COLS_N + c;
     uint8_t * p32 = reinterpret_cast<uint8_t *>(const_cast<uint2 *>(M.s32) + (sb * COLS_N + c) * 2);
     uint8_t * p16 = reinterpret_cast<uint8_t *>(const_cast<uint2 *>(M.s16) + (sb * COLS_N + c) * 4);
+    int * pn = const_cast<int *>(M.n32) + (size_t) sb * 8 * COLS_N + c;         // + sub-block * COLS_N
     if (c >= nd.n) {                                      // padding columns: zero scale and sums, q never read as non-zero
         if (threadIdx.x == 0) *dp = 0.0f;
         if (threadIdx.x < 4)  reinterpret_cast<uint32_t *>(p32)[threadIdx.x] = 0u;
-        if (threadIdx.x < 8)  reinterpret_cast<uint32_t *>(p16)[threadIdx.x] = 0u;
+        if (threadIdx.x < 8)  { reinterpret_cast<uint32_t *>(p16)[threadIdx.x] = 0u; pn[threadIdx.x * COLS_N] = 0; }
         return;
     }
     const int j = threadIdx.x;
@@ -124,6 +127,7 @@ __global__ void __launch_bounds__(256) k_quantize_cols(const __grid_constant__ c
     if (lane == 0) {                                      // sum of the 32-block `warp`
         p32[(warp >> 2) * 8 + (warp & 3)]     = (uint8_t) (sum & 63);
         p32[(warp >> 2) * 8 + 4 + (warp & 3)] = (uint8_t) (sum >> 6);
+        pn[warp * COLS_N] = -8 * sum;
     }
     if (threadIdx.x == 0) *dp = d;
 }
@@ -132,6 +136,15 @@ __global__ void __launch_bounds__(256) k_quantize_cols(const __grid_constant__ c
 // m16n8k32, A = u8 weights (rows g / g + 8, k slots 4t.. and 16 + 4t..), B = s8 activations (column g)
 __device__ __forceinline__ void mma_u8s8_16x8x32(int (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
     asm("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%10, %10, %10, %10};"
+        : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "r"(0));
+}
+// the same with a C input (Q4_0: -8 * sum of the activations) and with signed weights (Q8_0)
+__device__ __forceinline__ void mma_u8s8_16x8x32_c(int (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1, int c01, int c11) {
+    asm("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%10, %11, %10, %11};"
+        : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "r"(c01), "r"(c11));
+}
+__device__ __forceinline__ void mma_s8s8_16x8x32(int (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm("mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%10, %10, %10, %10};"
         : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "r"(0));
 }
 // m16n8k16, A = u8 (mins, 6-bit weights) or s8 (Q6_K scales), B = s8
@@ -164,7 +177,8 @@ __device__ __forceinline__ uint4 ldg_stream128(const void * p) {
     return v;
 }
 
-__device__ __forceinline__ int cols_block_bytes(int type) { return type == T_Q6_K ? 210 : (type == T_Q5_K ? 176 : 144); }
+// bytes of 256 weights of a row (one super-block of the K-quants, eight blocks of Q4_0 / Q8_0)
+__device__ __host__ __forceinline__ int cols_block_bytes(int type) { return type == T_Q6_K ? 210 : (type == T_Q5_K ? 176 : (type == T_Q8_0 ? 272 : 144)); }
 
 // HBM -> L2 prefetch of a whole weight row (16-byte aligned, a multiple of 16 bytes): no registers, no completion
 __device__ __forceinline__ void l2_prefetch_bulk(const void * p, uint32_t bytes) {
@@ -490,19 +504,26 @@ constexpr int RING_STAGES   = 3;
 // fragment loads of the 8 row groups cover every bank twice), 1 = Q6_K (8 x 210 = 1680 = 16 mod 128: its 4-byte loads, 16
 // bytes per row group, cover every bank once).  A stage = the chunk's weights, then the matching slice of the activations:
 //   int8 [8 super-blocks][8 sub-blocks][8 columns][32] | f32 d [8][8 columns] | sums of 32 [8][8][2] uint2 or sums of 16 [8][8][4] uint2
+// Family 2 = Q8_0 (eight 34-byte blocks = 272 bytes per 256 weights, rows of 8 x 272 + 16 = 2192 = 16 mod 128; two stages);
+// Q4_0 (eight 18-byte blocks = 144 bytes) rides family 0 with Q4_K's geometry and the n32 plane in place of s32.
 template <int FAM> struct ring_geo {
-    static constexpr int pitch_max = FAM ? RING_CI * 210 : RING_CI * 176 + 32;
+    static constexpr int stages    = FAM == 2 ? 2 : RING_STAGES;
+    static constexpr int pitch_max = FAM == 1 ? RING_CI * 210 : (FAM == 2 ? RING_CI * 272 + 32 : RING_CI * 176 + 32);
     static constexpr int off_yq    = RING_ROWS * pitch_max;
     static constexpr int off_d     = off_yq + RING_CI * 8 * 32 * COLS_N;
     static constexpr int off_s     = off_d + RING_CI * COLS_N * 4;
-    static constexpr int s_bytes   = FAM ? COLS_N * 32 : COLS_N * 16;           // per super-block
-    static constexpr int stage     = off_s + RING_CI * s_bytes;                 // 63744 / 72448
-    static constexpr int off_red   = RING_STAGES * stage;                       // float red[RING_NWC][128]
+    static constexpr int s_bytes   = FAM == 2 ? 0 : COLS_N * 32;                // per super-block: s32 (128 B) or n32 (256 B) / s16 (256 B)
+    static constexpr int stage     = off_s + RING_CI * s_bytes;                 // 64768 / 72448 / 87296
+    static constexpr int off_red   = stages * stage;                            // float red[RING_NWC][128]
     static constexpr int off_bar   = off_red + RING_NWC * 128 * 4;
-    static constexpr int smem      = off_bar + 128;                             // 199552 / 225664
+    static constexpr int smem      = off_bar + 128;
 };
-static_assert(ring_geo<1>::smem <= 232448, "the Q6_K ring must fit the 227 KB of shared memory a CTA can have");
-__device__ __forceinline__ int ring_pitch(int type) { return type == T_Q6_K ? RING_CI * 210 : (type == T_Q5_K ? RING_CI * 176 + 32 : RING_CI * 144 + 32); }
+static_assert(ring_geo<1>::smem <= 232448 && ring_geo<0>::smem <= 232448 && ring_geo<2>::smem <= 232448, "the rings must fit the 227 KB of shared memory a CTA can have");
+__device__ __forceinline__ int ring_pitch(int type) {
+    // Q4_0 / Q8_0 fragments are 4-byte loads, 16 bytes per row group: pitch = 16 mod 128 spreads the 8 row groups over all banks
+    return type == T_Q6_K ? RING_CI * 210 : (type == T_Q5_K ? RING_CI * 176 + 32 :
+           (type == T_Q8_0 ? RING_CI * 272 + 16 : (type == T_Q4_0 ? RING_CI * 144 + 16 : RING_CI * 144 + 32)));
+}
 
 __device__ __forceinline__ uint2 lds64(const uint8_t * p) { return *reinterpret_cast<const uint2 *>(p); }
 
@@ -510,12 +531,12 @@ template <int FAM>
 __global__ void __launch_bounds__(RING_THREADS, 1) k_mmvq_cols_ring(const __grid_constant__ cols_args a) {
     using G = ring_geo<FAM>;
     extern __shared__ __align__(128) uint8_t smem[];
-    uint64_t * full = reinterpret_cast<uint64_t *>(smem + G::off_bar), * empty = full + RING_STAGES;
-    uint64_t * red_full = empty + RING_STAGES, * red_empty = red_full + 1;
+    uint64_t * full = reinterpret_cast<uint64_t *>(smem + G::off_bar), * empty = full + G::stages;
+    uint64_t * red_full = empty + G::stages, * red_empty = red_full + 1;
     float (*red)[128] = reinterpret_cast<float (*)[128]>(smem + G::off_red);     // one buffer: the epilogue is done with a tile long before the next one ends
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
-        for (int s = 0; s < RING_STAGES; s++) { mbar_init(&full[s], RING_NPROD); mbar_init(&empty[s], RING_NWC); }
+        for (int s = 0; s < G::stages; s++) { mbar_init(&full[s], RING_NPROD); mbar_init(&empty[s], RING_NWC); }
         mbar_init(red_full, RING_NWC); mbar_init(red_empty, 1);
         mbar_fence_init();
     }
@@ -538,17 +559,21 @@ __global__ void __launch_bounds__(RING_THREADS, 1) k_mmvq_cols_ring(const __grid
                 const uint32_t ci = (uint32_t) min(RING_CI, items - c0), bytes = ci * (uint32_t) bs;
                 uint8_t * st = smem + stage * G::stage;
                 mbar_wait(&empty[stage], phase ^ 1u);
-                const uint32_t abytes = ci * (pw == 0 ? 8 * 32 * COLS_N : (pw == 1 ? COLS_N * 4 : G::s_bytes));
+                // third plane: sums of 32 (Q4_K / Q5_K: 128 B per super-block), -8 * sums (Q4_0: 256 B), sums of 16 (Q6_K: 256 B), none (Q8_0)
+                const uint32_t sb3 = FAM == 2 ? 0u : (FAM == 1 || nd.type == T_Q4_0 ? COLS_N * 32u : COLS_N * 16u);
+                const uint32_t abytes = ci * (pw == 0 ? 8 * 32 * COLS_N : (pw == 1 ? COLS_N * 4 : sb3));
                 if (lane == 0) mbar_arrive_expect_tx(&full[stage], bytes * (uint32_t) my_rows + abytes);
                 __syncwarp();
                 if (lane < 11 && r < rows) bulk_g2s(st + r * pitch, src + (size_t) c0 * bs, bytes, &full[stage]);
                 if (lane == 11) {
                     if (pw == 0)      bulk_g2s(st + G::off_yq, nd.yq + (size_t) c0 * (8 * 32 * COLS_N), abytes, &full[stage]);
                     else if (pw == 1) bulk_g2s(st + G::off_d, M.d + (size_t) c0 * COLS_N, abytes, &full[stage]);
-                    else if (FAM)     bulk_g2s(st + G::off_s, M.s16 + (size_t) c0 * COLS_N * 4, abytes, &full[stage]);
-                    else              bulk_g2s(st + G::off_s, M.s32 + (size_t) c0 * COLS_N * 2, abytes, &full[stage]);
+                    else if (FAM == 1)          bulk_g2s(st + G::off_s, M.s16 + (size_t) c0 * COLS_N * 4, abytes, &full[stage]);
+                    else if (FAM == 2)          { }
+                    else if (nd.type == T_Q4_0) bulk_g2s(st + G::off_s, M.n32 + (size_t) c0 * 8 * COLS_N, abytes, &full[stage]);
+                    else                        bulk_g2s(st + G::off_s, M.s32 + (size_t) c0 * COLS_N * 2, abytes, &full[stage]);
                 }
-                if (++stage == RING_STAGES) { stage = 0; phase ^= 1u; }
+                if (++stage == G::stages) { stage = 0; phase ^= 1u; }
             }
         }
     } else if (warp == RING_NWC + RING_NPROD) {
@@ -591,7 +616,48 @@ __global__ void __launch_bounds__(RING_THREADS, 1) k_mmvq_cols_ring(const __grid
                     const uint2 dyb = lds64(st + G::off_d + slot * (COLS_N * 4) + 8 * t);                   // columns 2t, 2t + 1
                     const float2 dy = make_float2(__uint_as_float(dyb.x), __uint_as_float(dyb.y));
                     // (columns >= n hold whatever the workspace held: their results are never stored)
-                    if (FAM) {
+                    if (FAM == 2 || (FAM == 0 && nd.type == T_Q4_0)) {
+                        // Q4_0 / Q8_0: eight 32-weight blocks with an f16 scale each; lane (g, t) takes quant bytes 4t..4t+3 (k slots
+                        // 4t..) and, Q4_0: their high nibbles / Q8_0: bytes 16 + 4t.. (k slots 16 + 4t..) -- the activation
+                        // bytes of the same positions.  Blocks of even index sit 2 bytes off word alignment: funnel shifts.
+                        constexpr bool Q8 = FAM == 2;
+                        constexpr int BB = Q8 ? 34 : 18;
+                        const uint8_t * yqs = st + G::off_yq + (slot * 8) * (32 * COLS_N) + g * 32 + 4 * t;
+                        const int hsel = (g & 4) << 2;                      // 0 or 16
+                        auto blk = [&](auto Bc) {
+                            constexpr int b = decltype(Bc)::value;
+                            constexpr int o = BB * b + 2;                   // the block's quants; (o & 3) == 2 for even b
+                            uint32_t wa0, wb0, wa1 = 0, wb1 = 0;
+                            if (b & 1) {
+                                wa0 = lds32(ra + o + 4 * t); wb0 = lds32(rb + o + 4 * t);
+                                if (Q8) { wa1 = lds32(ra + o + 16 + 4 * t); wb1 = lds32(rb + o + 16 + 4 * t); }
+                            } else {
+                                wa0 = __funnelshift_r(lds32(ra + o - 2 + 4 * t), lds32(ra + o + 2 + 4 * t), 16);
+                                wb0 = __funnelshift_r(lds32(rb + o - 2 + 4 * t), lds32(rb + o + 2 + 4 * t), 16);
+                                if (Q8) {
+                                    wa1 = __funnelshift_r(lds32(ra + o + 14 + 4 * t), lds32(ra + o + 18 + 4 * t), 16);
+                                    wb1 = __funnelshift_r(lds32(rb + o + 14 + 4 * t), lds32(rb + o + 18 + 4 * t), 16);
+                                }
+                            }
+                            const float da = f16_bits_to_f32(lds16(ra + BB * b)), db = f16_bits_to_f32(lds16(rb + BB * b));
+                            // the two activation words are 16 bytes apart and columns 32: row groups g and g + 4 would share banks, so
+                            // groups 4..7 fetch them in the other order
+                            const uint32_t u0 = lds32(yqs + b * (32 * COLS_N) + hsel), u1 = lds32(yqs + b * (32 * COLS_N) + (hsel ^ 16));
+                            const uint32_t b0 = hsel ? u1 : u0, b1 = hsel ? u0 : u1;
+                            int c[4];
+                            if (Q8) mma_s8s8_16x8x32(c, wa0, wb0, wa1, wb1, b0, b1);
+                            else {
+                                const uint2 nn = lds64(st + G::off_s + ((slot * 8 + b) * COLS_N + 2 * t) * 4);      // -8 * sum32, columns 2t, 2t + 1
+                                mma_u8s8_16x8x32_c(c, wa0 & 0x0F0F0F0Fu, wb0 & 0x0F0F0F0Fu, (wa0 >> 4) & 0x0F0F0F0Fu, (wb0 >> 4) & 0x0F0F0F0Fu,
+                                                   b0, b1, (int) nn.x, (int) nn.y);
+                            }
+                            acc[0] += (da * dy.x) * (float) c[0]; acc[1] += (da * dy.y) * (float) c[1];
+                            acc[2] += (db * dy.x) * (float) c[2]; acc[3] += (db * dy.y) * (float) c[3];
+                        };
+                        blk(std::integral_constant<int, 0>()); blk(std::integral_constant<int, 1>()); blk(std::integral_constant<int, 2>());
+                        blk(std::integral_constant<int, 3>()); blk(std::integral_constant<int, 4>()); blk(std::integral_constant<int, 5>());
+                        blk(std::integral_constant<int, 6>()); blk(std::integral_constant<int, 7>());
+                    } else if (FAM == 1) {
                         const uint2 s16 = lds64(st + G::off_s + (slot * COLS_N + g) * 32 + 8 * t);          // column g, groups 4t..4t+3
                         const int8_t * yq = reinterpret_cast<const int8_t *>(st + G::off_yq) + g * 32;
                         cols_item6 ia, ib;
@@ -619,7 +685,7 @@ __global__ void __launch_bounds__(RING_THREADS, 1) k_mmvq_cols_ring(const __grid
                 }
                 __syncwarp();
                 if (lane == 0) mbar_arrive_cta(&empty[stage]);
-                if (++stage == RING_STAGES) { stage = 0; phase ^= 1u; }
+                if (++stage == G::stages) { stage = 0; phase ^= 1u; }
             }
             mbar_wait(red_empty, rphase ^ 1u);                   // the epilogue has read the previous tile
             *reinterpret_cast<float4 *>(&red[warp][lane * 4]) = make_float4(acc[0], acc[1], acc[2], acc[3]);
@@ -632,24 +698,27 @@ __global__ void __launch_bounds__(RING_THREADS, 1) k_mmvq_cols_ring(const __grid
 // ---------------------------------------------------------------- host side
 static inline bool cols_node_ok(int type, const uint8_t * w, int64_t row_stride, int64_t m, int64_t k, const float * x,
                                 int64_t x_stride_bytes, int64_t n) {
-    if (type != T_Q4_K && type != T_Q5_K && type != T_Q6_K) return false;
+    static const int ring_on = env_int("GGML_B200_COLS_RING", 1);
+    if (type != T_Q4_K && type != T_Q5_K && type != T_Q6_K && !((type == T_Q4_0 || type == T_Q8_0) && ring_on)) return false;
     if (n < 2 || n > COLS_N || m < 1 || k < 256 || k % 256 != 0) return false;
     if (m >= (int64_t) 1 << 31 || k >= (int64_t) 1 << 24) return false;
     if ((reinterpret_cast<uintptr_t>(w) & 15) || (row_stride & 15) || (reinterpret_cast<uintptr_t>(x) & 3) || (x_stride_bytes & 3)) return false;
     // Q6_K: the ring copies chunks of 8 super-blocks (8 x 210 = 1680 bytes, a multiple of 16); a shorter last chunk would not be one
     if (type == T_Q6_K && (k / 256) % 8 != 0) return false;
-    return row_stride >= k / 256 * (type == T_Q6_K ? 210 : (type == T_Q5_K ? 176 : 144));
+    return row_stride >= k / 256 * cols_block_bytes(type);
 }
 static inline size_t cols_ws_bytes(int64_t k, int64_t n) {
     (void) n;
     // int8 [k/32][8][32]  +  per super-block: f32 d [8], sums of 32 (2 x 8 bytes) [8], sums of 16 (4 x 8 bytes) [8] (cols_meta)
-    return (((size_t) COLS_N * k + 127) & ~(size_t) 127) + (((size_t) (k / 256) * COLS_N * (4 + 16 + 32) + 127) & ~(size_t) 127);
+    // + -8 * sums of 32 as int32 [8 sub-blocks][8]
+    return (((size_t) COLS_N * k + 127) & ~(size_t) 127) + (((size_t) (k / 256) * COLS_N * (4 + 16 + 32 + 32) + 127) & ~(size_t) 127);
 }
 
 struct cols_builder {
     cols_args args;       // tuning (GGML_B200_COLS_RING=0): k_mmvq_cols, 16-row tiles
     cols_args ring;       // Q4_K / Q5_K nodes: k_mmvq_cols_ring<0>, 32-row tiles
     cols_args ring6;      // Q6_K nodes: k_mmvq_cols_ring<1>
+    cols_args ring8;      // Q8_0 nodes: k_mmvq_cols_ring<2>  (Q4_0 nodes ride `ring`)
     // the activations quantized last (nodes of either list that read the same x share them: q/k/v, gate/up)
     const float * last_x; int64_t last_k, last_n, last_stride; int8_t * last_yq; uint8_t * last_ym;
     cols_builder() { reset(); }
@@ -657,15 +726,16 @@ struct cols_builder {
         args.count = 0; args.units = 0; args.kmax = 0; args.pad = 0;
         ring.count = 0; ring.units = 0; ring.kmax = 0; ring.pad = 0;
         ring6.count = 0; ring6.units = 0; ring6.kmax = 0; ring6.pad = 0;
+        ring8.count = 0; ring8.units = 0; ring8.kmax = 0; ring8.pad = 0;
         last_x = nullptr; last_k = last_n = last_stride = 0; last_yq = nullptr; last_ym = nullptr;
     }
-    bool full() const { return args.count >= COLS_MAX_NODES || ring.count >= COLS_MAX_NODES || ring6.count >= COLS_MAX_NODES; }
-    bool empty() const { return args.count == 0 && ring.count == 0 && ring6.count == 0; }
-    int  count() const { return args.count + ring.count + ring6.count; }
+    bool full() const { return args.count >= COLS_MAX_NODES || ring.count >= COLS_MAX_NODES || ring6.count >= COLS_MAX_NODES || ring8.count >= COLS_MAX_NODES; }
+    bool empty() const { return args.count == 0 && ring.count == 0 && ring6.count == 0 && ring8.count == 0; }
+    int  count() const { return args.count + ring.count + ring6.count + ring8.count; }
     bool add(int type, const uint8_t * w, int64_t row_stride, int64_t m, int64_t k, const float * x, int64_t x_stride_bytes,
              int64_t n, float * dst, ws_cursor & cur) {
         static const int use_ring = env_int("GGML_B200_COLS_RING", 1);
-        cols_args & A = !use_ring ? args : (type == T_Q6_K ? ring6 : ring);
+        cols_args & A = !use_ring ? args : (type == T_Q6_K ? ring6 : (type == T_Q8_0 ? ring8 : ring));
         const int tile = use_ring ? RING_ROWS : 16;
         cols_node & nd = A.nodes[A.count];
         if (last_x == x && last_k == k && last_n == n && last_stride == x_stride_bytes) {
@@ -692,7 +762,7 @@ static int cols_launch(cols_builder & cb, cudaStream_t st) {
     const dev_caps & caps = current_caps();
     static const int pdl = env_int("GGML_B200_FUSED_PDL", 1);
     // 1. the activations of both lists (a node that shares them with an earlier node of either list does nothing)
-    for (cols_args * A : { &cb.ring, &cb.ring6, &cb.args }) {
+    for (cols_args * A : { &cb.ring, &cb.ring6, &cb.ring8, &cb.args }) {
         if (A->count == 0) continue;
         const dim3 grid((unsigned) (A->kmax / 256), (unsigned) A->count, COLS_N);
         k_quantize_cols<<<grid, 256, 0, st>>>(*A);
@@ -713,9 +783,10 @@ static int cols_launch(cols_builder & cb, cudaStream_t st) {
         b200_count_launch(1);
         return B200_OK;
     };
-    static smem_limit lim0, lim1;
+    static smem_limit lim0, lim1, lim2;
     if (cb.ring.count)  { if (const int rc = ring_launch(k_mmvq_cols_ring<0>, ring_geo<0>::smem, cb.ring, lim0)) return rc; }
     if (cb.ring6.count) { if (const int rc = ring_launch(k_mmvq_cols_ring<1>, ring_geo<1>::smem, cb.ring6, lim1)) return rc; }
+    if (cb.ring8.count) { if (const int rc = ring_launch(k_mmvq_cols_ring<2>, ring_geo<2>::smem, cb.ring8, lim2)) return rc; }
     // 3. tuning fallback: per-lane loads behind L2 prefetches
     if (cb.args.count) {
         cols_args & a = cb.args;

@@ -103,6 +103,42 @@ __global__ void __launch_bounds__(256) k_quantize_acts(const uint8_t * __restric
     if (lane == 0) dd[row * (k / 32) + kb] = __half2float(__float2half_rn(r.d));
 }
 
+// ---------------------------------------------------------------- f32 -> Q8_0 / Q4_0 (CPY f32 -> quant)
+// replaces cpy_f32_q<cpy_blck_f32_q8_0 / _q4_0> (reference src/ggml-cuda/cpy.cu:66-92, cpy-utils.cuh) with the value contract of
+// the CPU definitions quantize_row_q8_0_ref / quantize_row_q4_0_ref (src/ggml-quants.c:199-222, 36-71), bit-exact:
+//   Q8_0: d = amax / 127, q = roundf(x / d)                         Q4_0: d = (the FIRST value of largest magnitude) / -8,
+//                                                                         q = min(15, (int8) (x / d + 8.5f))
+// One warp per 32-value block (lane = element); rows of k values x_row_stride bytes apart, blocks of a row contiguous.
+template <int T>
+__global__ void __launch_bounds__(256) k_quantize_blocks(const uint8_t * __restrict__ x, int64_t x_row_stride, int64_t k,
+                                                         uint8_t * __restrict__ y, int64_t y_row_stride) {
+    const int64_t kb = (int64_t) blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (kb * 32 >= k) return;
+    const int64_t row = blockIdx.y;
+    const float v = reinterpret_cast<const float *>(x + row * x_row_stride)[kb * 32 + lane];
+    uint8_t * b = y + row * y_row_stride + kb * fmt<T>::bytes;
+    if (T == T_Q8_0) {
+        const float amax = warp_max(fabsf(v));
+        const float d  = __fdiv_rn(amax, 127.0f);
+        const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+        b[2 + lane] = (uint8_t) (int8_t) roundf(__fmul_rn(v, id));
+        if (lane == 0) *reinterpret_cast<__half *>(b) = __float2half_rn(d);
+    } else {
+        // the first element of largest |v| (the reference's loop keeps the earlier one on ties): key = |v| bits : 31 - lane
+        unsigned long long key = ((unsigned long long) (__float_as_uint(v) & 0x7FFFFFFFu) << 5) | (unsigned) (31 - lane);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { const unsigned long long t = __shfl_xor_sync(0xFFFFFFFFu, key, o); key = t > key ? t : key; }
+        const float mx = (key >> 5) != 0ull ? __shfl_sync(0xFFFFFFFFu, v, 31 - (int) (key & 31u)) : 0.0f;
+        const float d  = __fdiv_rn(mx, -8.0f);
+        const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+        const int q = min(15, (int) (int8_t) (int) __fadd_rn(__fmul_rn(v, id), 8.5f));       // (int8_t) of a float in [0.5, 16.5]: truncation
+        const int hi = __shfl_down_sync(0xFFFFFFFFu, q, 16);
+        if (lane < 16) b[2 + lane] = (uint8_t) ((q & 0xFF) | (hi << 4));
+        if (lane == 0) *reinterpret_cast<__half *>(b) = __float2half_rn(d);
+    }
+}
+
 } // namespace b200
 
 using namespace b200;
@@ -150,4 +186,24 @@ extern "C" int b200_quantize_acts(const float * x_dev, size_t x_row_stride_bytes
     int8_t * q  = (int8_t *) scratch_dev;
     float  * dd = (float *) ((uint8_t *) scratch_dev + qbytes);
     return b200_quantize_acts_planes(x_dev, x_row_stride_bytes, k, n, q, dd, (cudaStream_t) stream);
+}
+
+// rows of f32 -> rows of Q8_0 / Q4_0 blocks (b200_quantize_rows, include/ggml_b200.h)
+extern "C" int b200_quantize_rows(int type, const float * x_dev, size_t x_row_stride_bytes, int64_t k, int64_t n,
+                                  void * y_dev, size_t y_row_stride_bytes, void * stream) {
+    if (type != T_Q8_0 && type != T_Q4_0) return B200_ERR_TYPE;
+    if (k < 0 || n < 0 || k % 32 != 0) return B200_ERR_SHAPE;
+    if (x_row_stride_bytes % 4 != 0 || y_row_stride_bytes % 2 != 0 || ((uintptr_t) y_dev & 1)) return B200_ERR_STRIDE;
+    if (k == 0 || n == 0) return B200_OK;
+    for (int64_t r0 = 0; r0 < n; r0 += 65535) {
+        const int64_t nr = n - r0 < 65535 ? n - r0 : 65535;
+        const dim3 grid((unsigned) ceil_div(k / 32, 8), (unsigned) nr);
+        const uint8_t * x = (const uint8_t *) x_dev + r0 * x_row_stride_bytes;
+        uint8_t * y = (uint8_t *) y_dev + r0 * y_row_stride_bytes;
+        if (type == T_Q8_0) k_quantize_blocks<T_Q8_0><<<grid, 256, 0, (cudaStream_t) stream>>>(x, (int64_t) x_row_stride_bytes, k, y, (int64_t) y_row_stride_bytes);
+        else                k_quantize_blocks<T_Q4_0><<<grid, 256, 0, (cudaStream_t) stream>>>(x, (int64_t) x_row_stride_bytes, k, y, (int64_t) y_row_stride_bytes);
+        b200_count_launch(1);
+    }
+    B200_RETURN_IF_LAUNCH_FAILED();
+    return B200_OK;
 }

@@ -124,6 +124,13 @@ B200_API int b200_dequantize_4d(int type, const void * x_dev, const int64_t ne_s
 B200_API int b200_quantize_row_q8_1(const float * x_dev, size_t x_row_stride_bytes, int64_t k, int64_t n,
                                     void * y_dev, void * stream);
 
+/* ---- quantize rows: f32 -> Q8_0 / Q4_0 (CPY f32 -> quant) ------------------------------------
+ * replaces ggml_cuda_cpy for f32 -> q8_0 / q4_0 (src/ggml-cuda/cpy.cu:66-92, 174-214) with the value contract of the CPU
+ * definitions quantize_row_q8_0_ref / quantize_row_q4_0_ref (src/ggml-quants.c:199-222, 36-71): bit-exact blocks.
+ * x_dev: n rows of k floats (k % 32 == 0); y_dev: n rows of k / 32 blocks, rows y_row_stride_bytes apart. */
+B200_API int b200_quantize_rows(int type, const float * x_dev, size_t x_row_stride_bytes, int64_t k, int64_t n,
+                                void * y_dev, size_t y_row_stride_bytes, void * stream);
+
 /* ---- GET_ROWS ------------------------------------------------------------------------------
  * replaces ggml_cuda_op_get_rows / get_rows_cuda_q (src/ggml-cuda/getrows.cu:93-124, 236-253) and
  * extends it to the K-quants, which the reference serves only on the CPU

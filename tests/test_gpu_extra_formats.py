@@ -94,3 +94,21 @@ def test_mul_mat_broadcast_channels(kern, oracle, t):
         for i12 in range(4):
             want = oracle.mul_mat(t, w_np[i12 // 2], m, k, x_np[i13, i12], mode=1)
             assert oracle.nmse(want, out[i13, i12]) <= NMSE_ORACLE, (t, i12, i13)
+
+
+@pytest.mark.parametrize("t", ("q8_0", "q4_0"))
+def test_quantize_rows_bit_exact(kern, oracle, golden, t):
+    """f32 -> Q8_0 / Q4_0 blocks (the CPY f32 -> quant direction): bit for bit quantize_row_*_ref -- the golden rows the
+    reference quantized without an importance matrix, random rows through the oracle, ties / zeros / one outlier, strided input"""
+    src = golden[f"{t}_src_f32"][:3]
+    got = kern.quantize_rows(t, kern.to_device(np.ascontiguousarray(src))).cpu().numpy()
+    assert np.array_equal(got, golden[f"{t}_blocks"][:3])
+    rng = np.random.default_rng(5)
+    x = rng.standard_normal((37, 1024 + 32)).astype(np.float32) * 3
+    x[1] = 0.0
+    x[2, :64] = np.tile(np.array([1.0, -1.0], dtype=np.float32), 32)      # |max| ties of opposite sign: the first one sets the scale
+    x[3, :32] = (np.arange(32) - 15.5).astype(np.float32)                 # x.5 ties after scaling
+    x[4, 7] = 1e6
+    big = kern.to_device(np.concatenate([x, x], axis=1))
+    got = kern.quantize_rows(t, big[:, :x.shape[1]]).cpu().numpy()        # row stride twice the row
+    assert np.array_equal(got, oracle.quantize(t, x))

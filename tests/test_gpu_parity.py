@@ -452,10 +452,10 @@ def test_mul_mat_batch_matches_single_calls(kern, oracle):
 
 @pytest.mark.parametrize("n", [2, 3, 4, 8])
 def test_mul_mat_batch_few_columns(kern, oracle, n):
-    """decode at batch n: Q4_K / Q5_K nodes with 2..8 columns go to the MMA list kernel (mmvq_cols.cuh); the other
-    formats ride the persistent launch as one entry per column (same weights, L2-resident for the later
-    columns), where each column equals the same column computed alone (n = 1 list) bit for bit.  All within
-    the NMSE bound of the oracle.  Column stride of x is padded (nb_b[1] > 4 k)."""
+    """decode at batch n: nodes with 2..8 columns go to the MMA list kernel (mmvq_cols.cuh: all five formats; Q6_K when its row
+    is a whole number of 8-super-block chunks); what does not qualify rides the persistent launch as one entry per column (same
+    weights, L2-resident for the later columns), where each column equals the same column computed alone (n = 1 list) bit
+    for bit.  All within the NMSE bound of the oracle.  Column stride of x is padded (nb_b[1] > 4 k)."""
     import b200
     import torch
     mats = [("q4_K", 300, 4096), ("q6_K", 130, 1024), ("q8_0", 96, 2048), ("q5_K", 4096, 1024), ("q4_0", 64, 4096),
@@ -471,7 +471,9 @@ def test_mul_mat_batch_few_columns(kern, oracle, n):
         nodes = (b200.MulMatNode * 1)(b200.mul_mat_node(t, w.data_ptr(), m, k, x.data_ptr(), n, y.data_ptr(), b_row_stride=4 * (k + pad)))
         kern.mul_mat_batch(nodes)
         got = y.cpu().numpy()
-        on_mma_kernel = t in ("q4_K", "q5_K") or (t == "q6_K" and k % 2048 == 0)     # Q6_K rows must be 16-byte multiples for the MMA path
+        # route 2 = the MMA list kernel (every format when k % 256 == 0; Q6_K: chunks of 8 super-blocks must be 16-byte multiples)
+        on_mma_kernel = b200.batch_plan(kern.lib, nodes)[0][2] == 2
+        assert on_mma_kernel or t in ("q6_K", "q4_0", "q8_0"), (t, m, k)
         # the MMA list kernel takes its activations through Q8_K like ggml-cpu (oracle mode 2), the others through q8_1
         want = oracle.mul_mat(t, w_np, m, k, np.ascontiguousarray(x_np[:, :k]), mode=2 if on_mma_kernel else 1)
         assert oracle.nmse(want, got) <= NMSE_ORACLE, (t, m, k, n)
@@ -553,6 +555,46 @@ def test_mul_mat_batch_prefill_nodes_share_lanes(kern, oracle):
     torch.cuda.synchronize()
     for i in range(len(specs)):
         assert torch.equal(ys[i].view(torch.int32), want[i].view(torch.int32)), ("graph", i)
+
+
+def test_mul_mat_batch_few_columns_long_mixed_list(kern, oracle):
+    """more 2..8-column nodes than one launch of the MMA list kernel takes (384 per family): Q4_K / Q5_K / Q6_K interleaved,
+    groups of three sharing their activations (q / k / v), row counts that are not multiples of the 32-row tile, k up to
+    28672 (14 chunks of the ring).  Sampled nodes against the oracle, all of them finite and reproducible."""
+    import b200
+    import torch
+    n = 5
+    rng = np.random.default_rng(123)
+    types = ("q4_K", "q6_K", "q5_K")
+    shapes = [(33, 2048), (70, 4096), (17, 2048), (129, 2048)]
+    nodes, keep = [], []
+    xs = {}
+    for i in range(1000):
+        t = types[i % 3]
+        m, k = (24, 28672) if i == 500 else shapes[(i // 3) % len(shapes)]
+        g = i // 3                                   # three consecutive nodes read the same x
+        if (g, k) not in xs:
+            xs[(g, k)] = kern.to_device(rng.uniform(-1, 1, size=(n, k)).astype(np.float32))
+        x = xs[(g, k)]
+        w_np = random_blocks(t, m, k, seed=1000 + i) if i % 97 == 0 or i == 500 else None
+        w = dev_blocks(kern, w_np) if w_np is not None else kern.to_device(random_blocks(t, m, k, seed=7).reshape(-1))
+        y = torch.zeros((n, m), dtype=torch.float32, device=kern.device)
+        nodes.append(b200.mul_mat_node(t, w.data_ptr(), m, k, x.data_ptr(), n, y.data_ptr()))
+        keep.append((t, m, k, w, w_np, x, y))
+    arr = (b200.MulMatNode * len(nodes))(*nodes)
+    wsz = torch.empty(int(kern.lib.b200_mul_mat_batch_workspace_size(arr, len(nodes))) + 256, dtype=torch.uint8, device=kern.device)
+    kern.mul_mat_batch(arr, ws=wsz)
+    first = [y.clone() for (_, _, _, _, _, _, y) in keep]
+    for (t, m, k, w, w_np, x, y) in keep:
+        assert torch.isfinite(y).all()
+        if w_np is not None:
+            want = oracle.mul_mat(t, w_np, m, k, x.cpu().numpy(), mode=2)
+            assert oracle.nmse(want, y.cpu().numpy()) <= NMSE_ORACLE, (t, m, k)
+    for (_, _, _, _, _, _, y) in keep:
+        y.zero_()
+    kern.mul_mat_batch(arr, ws=wsz)
+    for a, (_, _, _, _, _, _, y) in zip(first, keep):
+        assert torch.equal(a.view(torch.int32), y.view(torch.int32))
 
 
 def _batch_nodes(kern, mats, seed0=0, shared_x=False):
