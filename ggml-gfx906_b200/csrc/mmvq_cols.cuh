@@ -62,7 +62,11 @@ struct cols_args {
 //   s32 uint2 [nsb][8 columns][2]  word pair t: .x = low bytes (sum & 63), .y = high bytes (sum >> 6) of the sums of the
 //                                  32-blocks 4t..4t+3 -- the B fragments of the m16n8k16 MMAs against the 6-bit mins
 //   s16 uint2 [nsb][8 columns][4]  the same for the sums of 16 (bsums), groups 4t..4t+3 -- against Q6_K's int8 scales
-//   n32 int32 [nsb][8 sub-blocks][8 columns]  -8 * (sum of the 32-block): the C input of Q4_0's MMAs (weights enter as q, not q - 8)
+//   n32 int32 [nsb][8 sub-blocks][8 columns]  -8 * (sum of the 32-block) + COLS_I2F_BIAS: the C input of Q4_0's MMAs (weights enter as
+//                                  q, not q - 8); the bias makes the int32 result the bit pattern of the float 1.5 * 2^23 + result, so
+//                                  the int -> float conversion (I2F: a quarter-rate instruction, 4 per block) is one FADD
+constexpr int   COLS_I2F_BIAS  = 0x4B400000;       // bits of 12582912.0f = 1.5 * 2^23: exact for |result| < 2^22 (a block's dot is < 2^19)
+constexpr float COLS_I2F_BIASF = 12582912.0f;
 struct cols_meta {
     const float * d; const uint2 * s32; const uint2 * s16; const int * n32;
 };
@@ -90,7 +94,7 @@ __global__ void __launch_bounds__(256) k_quantize_cols(const __grid_constant__ c
     if (c >= nd.n) {                                      // padding columns: zero scale and sums, q never read as non-zero
         if (threadIdx.x == 0) *dp = 0.0f;
         if (threadIdx.x < 4)  reinterpret_cast<uint32_t *>(p32)[threadIdx.x] = 0u;
-        if (threadIdx.x < 8)  { reinterpret_cast<uint32_t *>(p16)[threadIdx.x] = 0u; pn[threadIdx.x * COLS_N] = 0; }
+        if (threadIdx.x < 8)  { reinterpret_cast<uint32_t *>(p16)[threadIdx.x] = 0u; pn[threadIdx.x * COLS_N] = COLS_I2F_BIAS; }
         return;
     }
     const int j = threadIdx.x;
@@ -127,7 +131,7 @@ __global__ void __launch_bounds__(256) k_quantize_cols(const __grid_constant__ c
     if (lane == 0) {                                      // sum of the 32-block `warp`
         p32[(warp >> 2) * 8 + (warp & 3)]     = (uint8_t) (sum & 63);
         p32[(warp >> 2) * 8 + 4 + (warp & 3)] = (uint8_t) (sum >> 6);
-        pn[warp * COLS_N] = -8 * sum;
+        pn[warp * COLS_N] = COLS_I2F_BIAS - 8 * sum;
     }
     if (threadIdx.x == 0) *dp = d;
 }
@@ -143,9 +147,9 @@ __device__ __forceinline__ void mma_u8s8_16x8x32_c(int (&d)[4], uint32_t a0, uin
     asm("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%10, %11, %10, %11};"
         : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "r"(c01), "r"(c11));
 }
-__device__ __forceinline__ void mma_s8s8_16x8x32(int (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+__device__ __forceinline__ void mma_s8s8_16x8x32(int (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1, int c) {
     asm("mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%10, %10, %10, %10};"
-        : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "r"(0));
+        : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "r"(c));
 }
 // m16n8k16, A = u8 (mins, 6-bit weights) or s8 (Q6_K scales), B = s8
 template <bool SIGNED_A>
@@ -505,24 +509,28 @@ constexpr int RING_STAGES   = 3;
 // bytes per row group, cover every bank once).  A stage = the chunk's weights, then the matching slice of the activations:
 //   int8 [8 super-blocks][8 sub-blocks][8 columns][32] | f32 d [8][8 columns] | sums of 32 [8][8][2] uint2 or sums of 16 [8][8][4] uint2
 // Family 2 = Q8_0 (eight 34-byte blocks = 272 bytes per 256 weights, rows of 8 x 272 + 16 = 2192 = 16 mod 128; two stages);
-// Q4_0 (eight 18-byte blocks = 144 bytes) rides family 0 with Q4_K's geometry and the n32 plane in place of s32.
+// family 3 = Q4_0 (eight 18-byte blocks = 144 bytes, rows of 8 x 144 + 16 = 1168 = 16 mod 128, the n32 plane in place of s32).  Its own
+// instantiation: folded into family 0 behind a run-time type test it cost Q4_K 7 % (0.720 -> 0.774 ms per Llama-2-7B pass at n = 8).
 template <int FAM> struct ring_geo {
     static constexpr int stages    = FAM == 2 ? 2 : RING_STAGES;
-    static constexpr int pitch_max = FAM == 1 ? RING_CI * 210 : (FAM == 2 ? RING_CI * 272 + 32 : RING_CI * 176 + 32);
+    static constexpr int pitch_max = FAM == 1 ? RING_CI * 210 : (FAM == 2 ? RING_CI * 272 + 16 : (FAM == 3 ? RING_CI * 144 + 16 : RING_CI * 176 + 32));
     static constexpr int off_yq    = RING_ROWS * pitch_max;
     static constexpr int off_d     = off_yq + RING_CI * 8 * 32 * COLS_N;
     static constexpr int off_s     = off_d + RING_CI * COLS_N * 4;
-    static constexpr int s_bytes   = FAM == 2 ? 0 : COLS_N * 32;                // per super-block: s32 (128 B) or n32 (256 B) / s16 (256 B)
-    static constexpr int stage     = off_s + RING_CI * s_bytes;                 // 64768 / 72448 / 87296
+    static constexpr int s_bytes   = FAM == 2 ? 0 : (FAM == 0 ? COLS_N * 16 : COLS_N * 32);     // per super-block: s32 (128 B), s16 / n32 (256 B), none
+    static constexpr int stage     = off_s + RING_CI * s_bytes;                 // 63744 / 72448 / 86784 / 56064
     static constexpr int off_red   = stages * stage;                            // float red[RING_NWC][128]
     static constexpr int off_bar   = off_red + RING_NWC * 128 * 4;
     static constexpr int smem      = off_bar + 128;
 };
-static_assert(ring_geo<1>::smem <= 232448 && ring_geo<0>::smem <= 232448 && ring_geo<2>::smem <= 232448, "the rings must fit the 227 KB of shared memory a CTA can have");
-__device__ __forceinline__ int ring_pitch(int type) {
-    // Q4_0 / Q8_0 fragments are 4-byte loads, 16 bytes per row group: pitch = 16 mod 128 spreads the 8 row groups over all banks
-    return type == T_Q6_K ? RING_CI * 210 : (type == T_Q5_K ? RING_CI * 176 + 32 :
-           (type == T_Q8_0 ? RING_CI * 272 + 16 : (type == T_Q4_0 ? RING_CI * 144 + 16 : RING_CI * 144 + 32)));
+static_assert(ring_geo<1>::smem <= 232448 && ring_geo<0>::smem <= 232448 && ring_geo<2>::smem <= 232448 && ring_geo<3>::smem <= 232448, "the rings must fit the 227 KB of shared memory a CTA can have");
+// row pitch and bytes per 256 weights of a node of family FAM (only family 0 holds two formats)
+// Q4_0 / Q8_0 fragments are 4-byte loads, 16 bytes per row group: pitch = 16 mod 128 spreads the 8 row groups over all banks
+template <int FAM> __device__ __forceinline__ int ring_pitch(int type) {
+    return FAM == 1 ? RING_CI * 210 : (FAM == 2 ? RING_CI * 272 + 16 : (FAM == 3 ? RING_CI * 144 + 16 : (type == T_Q5_K ? RING_CI * 176 + 32 : RING_CI * 144 + 32)));
+}
+template <int FAM> __device__ __forceinline__ int ring_block_bytes(int type) {
+    return FAM == 1 ? 210 : (FAM == 2 ? 272 : (FAM == 3 ? 144 : (type == T_Q5_K ? 176 : 144)));
 }
 
 __device__ __forceinline__ uint2 lds64(const uint8_t * p) { return *reinterpret_cast<const uint2 *>(p); }
@@ -550,8 +558,8 @@ __global__ void __launch_bounds__(RING_THREADS, 1) k_mmvq_cols_ring(const __grid
         for (int u = blockIdx.x; u < a.units; u += gridDim.x) {
             while (ni + 1 < a.count && u >= a.nodes[ni + 1].unit0) ni++;
             const cols_node & nd = a.nodes[ni];
-            const int row0 = (u - nd.unit0) * RING_ROWS, items = nd.k >> 8, bs = cols_block_bytes(nd.type);
-            const int rows = min(RING_ROWS, nd.m - row0), pitch = ring_pitch(nd.type);
+            const int row0 = (u - nd.unit0) * RING_ROWS, items = nd.k >> 8, bs = ring_block_bytes<FAM>(nd.type);
+            const int rows = min(RING_ROWS, nd.m - row0), pitch = ring_pitch<FAM>(nd.type);
             const int my_rows = max(0, min(rows, r_lo + 11) - r_lo);
             const uint8_t * src = nd.w + (size_t) (row0 + r) * nd.row_stride;
             const cols_meta M = cols_meta_of(nd.ym, nd.k);
@@ -560,8 +568,7 @@ __global__ void __launch_bounds__(RING_THREADS, 1) k_mmvq_cols_ring(const __grid
                 uint8_t * st = smem + stage * G::stage;
                 mbar_wait(&empty[stage], phase ^ 1u);
                 // third plane: sums of 32 (Q4_K / Q5_K: 128 B per super-block), -8 * sums (Q4_0: 256 B), sums of 16 (Q6_K: 256 B), none (Q8_0)
-                const uint32_t sb3 = FAM == 2 ? 0u : (FAM == 1 || nd.type == T_Q4_0 ? COLS_N * 32u : COLS_N * 16u);
-                const uint32_t abytes = ci * (pw == 0 ? 8 * 32 * COLS_N : (pw == 1 ? COLS_N * 4 : sb3));
+                const uint32_t abytes = ci * (pw == 0 ? 8 * 32 * COLS_N : (pw == 1 ? COLS_N * 4 : G::s_bytes));
                 if (lane == 0) mbar_arrive_expect_tx(&full[stage], bytes * (uint32_t) my_rows + abytes);
                 __syncwarp();
                 if (lane < 11 && r < rows) bulk_g2s(st + r * pitch, src + (size_t) c0 * bs, bytes, &full[stage]);
@@ -570,7 +577,7 @@ __global__ void __launch_bounds__(RING_THREADS, 1) k_mmvq_cols_ring(const __grid
                     else if (pw == 1) bulk_g2s(st + G::off_d, M.d + (size_t) c0 * COLS_N, abytes, &full[stage]);
                     else if (FAM == 1)          bulk_g2s(st + G::off_s, M.s16 + (size_t) c0 * COLS_N * 4, abytes, &full[stage]);
                     else if (FAM == 2)          { }
-                    else if (nd.type == T_Q4_0) bulk_g2s(st + G::off_s, M.n32 + (size_t) c0 * 8 * COLS_N, abytes, &full[stage]);
+                    else if (FAM == 3)          bulk_g2s(st + G::off_s, M.n32 + (size_t) c0 * 8 * COLS_N, abytes, &full[stage]);
                     else                        bulk_g2s(st + G::off_s, M.s32 + (size_t) c0 * COLS_N * 2, abytes, &full[stage]);
                 }
                 if (++stage == G::stages) { stage = 0; phase ^= 1u; }
@@ -606,7 +613,7 @@ __global__ void __launch_bounds__(RING_THREADS, 1) k_mmvq_cols_ring(const __grid
             const cols_node & nd = a.nodes[ni];
             const int items = nd.k >> 8;
             const bool q5 = nd.type == T_Q5_K;
-            const int bs = cols_block_bytes(nd.type), pitch = ring_pitch(nd.type);
+            const int bs = ring_block_bytes<FAM>(nd.type), pitch = ring_pitch<FAM>(nd.type);
             float acc[4] = { 0.0f, 0.0f, 0.0f, 0.0f };
             for (int c0 = 0; c0 < items; c0 += RING_CI) {
                 mbar_wait(&full[stage], phase);
@@ -616,7 +623,7 @@ __global__ void __launch_bounds__(RING_THREADS, 1) k_mmvq_cols_ring(const __grid
                     const uint2 dyb = lds64(st + G::off_d + slot * (COLS_N * 4) + 8 * t);                   // columns 2t, 2t + 1
                     const float2 dy = make_float2(__uint_as_float(dyb.x), __uint_as_float(dyb.y));
                     // (columns >= n hold whatever the workspace held: their results are never stored)
-                    if (FAM == 2 || (FAM == 0 && nd.type == T_Q4_0)) {
+                    if (FAM >= 2) {
                         // Q4_0 / Q8_0: eight 32-weight blocks with an f16 scale each; lane (g, t) takes quant bytes 4t..4t+3 (k slots
                         // 4t..) and, Q4_0: their high nibbles / Q8_0: bytes 16 + 4t.. (k slots 16 + 4t..) -- the activation
                         // bytes of the same positions.  Blocks of even index sit 2 bytes off word alignment: funnel shifts.
@@ -624,6 +631,7 @@ __global__ void __launch_bounds__(RING_THREADS, 1) k_mmvq_cols_ring(const __grid
                         constexpr int BB = Q8 ? 34 : 18;
                         const uint8_t * yqs = st + G::off_yq + (slot * 8) * (32 * COLS_N) + g * 32 + 4 * t;
                         const int hsel = (g & 4) << 2;                      // 0 or 16
+                        float sbs[4] = { 0.0f, 0.0f, 0.0f, 0.0f };          // the 256 weights' sums before the activations' scale (one per super-block)
                         auto blk = [&](auto Bc) {
                             constexpr int b = decltype(Bc)::value;
                             constexpr int o = BB * b + 2;                   // the block's quants; (o & 3) == 2 for even b
@@ -645,18 +653,21 @@ __global__ void __launch_bounds__(RING_THREADS, 1) k_mmvq_cols_ring(const __grid
                             const uint32_t u0 = lds32(yqs + b * (32 * COLS_N) + hsel), u1 = lds32(yqs + b * (32 * COLS_N) + (hsel ^ 16));
                             const uint32_t b0 = hsel ? u1 : u0, b1 = hsel ? u0 : u1;
                             int c[4];
-                            if (Q8) mma_s8s8_16x8x32(c, wa0, wb0, wa1, wb1, b0, b1);
+                            if (Q8) mma_s8s8_16x8x32(c, wa0, wb0, wa1, wb1, b0, b1, COLS_I2F_BIAS);
                             else {
                                 const uint2 nn = lds64(st + G::off_s + ((slot * 8 + b) * COLS_N + 2 * t) * 4);      // -8 * sum32, columns 2t, 2t + 1
                                 mma_u8s8_16x8x32_c(c, wa0 & 0x0F0F0F0Fu, wb0 & 0x0F0F0F0Fu, (wa0 >> 4) & 0x0F0F0F0Fu, (wb0 >> 4) & 0x0F0F0F0Fu,
                                                    b0, b1, (int) nn.x, (int) nn.y);
                             }
-                            acc[0] += (da * dy.x) * (float) c[0]; acc[1] += (da * dy.y) * (float) c[1];
-                            acc[2] += (db * dy.x) * (float) c[2]; acc[3] += (db * dy.y) * (float) c[3];
+                            // c = bias + the block's integer dot: its bits are the float 1.5 * 2^23 + dot, one exact FADD away from (float) dot
+                            sbs[0] = fmaf(da, __int_as_float(c[0]) - COLS_I2F_BIASF, sbs[0]); sbs[1] = fmaf(da, __int_as_float(c[1]) - COLS_I2F_BIASF, sbs[1]);
+                            sbs[2] = fmaf(db, __int_as_float(c[2]) - COLS_I2F_BIASF, sbs[2]); sbs[3] = fmaf(db, __int_as_float(c[3]) - COLS_I2F_BIASF, sbs[3]);
                         };
                         blk(std::integral_constant<int, 0>()); blk(std::integral_constant<int, 1>()); blk(std::integral_constant<int, 2>());
                         blk(std::integral_constant<int, 3>()); blk(std::integral_constant<int, 4>()); blk(std::integral_constant<int, 5>());
                         blk(std::integral_constant<int, 6>()); blk(std::integral_constant<int, 7>());
+                        acc[0] = fmaf(dy.x, sbs[0], acc[0]); acc[1] = fmaf(dy.y, sbs[1], acc[1]);
+                        acc[2] = fmaf(dy.x, sbs[2], acc[2]); acc[3] = fmaf(dy.y, sbs[3], acc[3]);
                     } else if (FAM == 1) {
                         const uint2 s16 = lds64(st + G::off_s + (slot * COLS_N + g) * 32 + 8 * t);          // column g, groups 4t..4t+3
                         const int8_t * yq = reinterpret_cast<const int8_t *>(st + G::off_yq) + g * 32;
@@ -718,7 +729,8 @@ struct cols_builder {
     cols_args args;       // tuning (GGML_B200_COLS_RING=0): k_mmvq_cols, 16-row tiles
     cols_args ring;       // Q4_K / Q5_K nodes: k_mmvq_cols_ring<0>, 32-row tiles
     cols_args ring6;      // Q6_K nodes: k_mmvq_cols_ring<1>
-    cols_args ring8;      // Q8_0 nodes: k_mmvq_cols_ring<2>  (Q4_0 nodes ride `ring`)
+    cols_args ring8;      // Q8_0 nodes: k_mmvq_cols_ring<2>
+    cols_args ring4;      // Q4_0 nodes: k_mmvq_cols_ring<3>
     // the activations quantized last (nodes of either list that read the same x share them: q/k/v, gate/up)
     const float * last_x; int64_t last_k, last_n, last_stride; int8_t * last_yq; uint8_t * last_ym;
     cols_builder() { reset(); }
@@ -727,15 +739,16 @@ struct cols_builder {
         ring.count = 0; ring.units = 0; ring.kmax = 0; ring.pad = 0;
         ring6.count = 0; ring6.units = 0; ring6.kmax = 0; ring6.pad = 0;
         ring8.count = 0; ring8.units = 0; ring8.kmax = 0; ring8.pad = 0;
+        ring4.count = 0; ring4.units = 0; ring4.kmax = 0; ring4.pad = 0;
         last_x = nullptr; last_k = last_n = last_stride = 0; last_yq = nullptr; last_ym = nullptr;
     }
-    bool full() const { return args.count >= COLS_MAX_NODES || ring.count >= COLS_MAX_NODES || ring6.count >= COLS_MAX_NODES || ring8.count >= COLS_MAX_NODES; }
-    bool empty() const { return args.count == 0 && ring.count == 0 && ring6.count == 0 && ring8.count == 0; }
-    int  count() const { return args.count + ring.count + ring6.count + ring8.count; }
+    bool full() const { return args.count >= COLS_MAX_NODES || ring.count >= COLS_MAX_NODES || ring6.count >= COLS_MAX_NODES || ring8.count >= COLS_MAX_NODES || ring4.count >= COLS_MAX_NODES; }
+    bool empty() const { return args.count == 0 && ring.count == 0 && ring6.count == 0 && ring8.count == 0 && ring4.count == 0; }
+    int  count() const { return args.count + ring.count + ring6.count + ring8.count + ring4.count; }
     bool add(int type, const uint8_t * w, int64_t row_stride, int64_t m, int64_t k, const float * x, int64_t x_stride_bytes,
              int64_t n, float * dst, ws_cursor & cur) {
         static const int use_ring = env_int("GGML_B200_COLS_RING", 1);
-        cols_args & A = !use_ring ? args : (type == T_Q6_K ? ring6 : (type == T_Q8_0 ? ring8 : ring));
+        cols_args & A = !use_ring ? args : (type == T_Q6_K ? ring6 : (type == T_Q8_0 ? ring8 : (type == T_Q4_0 ? ring4 : ring)));
         const int tile = use_ring ? RING_ROWS : 16;
         cols_node & nd = A.nodes[A.count];
         if (last_x == x && last_k == k && last_n == n && last_stride == x_stride_bytes) {
@@ -762,7 +775,7 @@ static int cols_launch(cols_builder & cb, cudaStream_t st) {
     const dev_caps & caps = current_caps();
     static const int pdl = env_int("GGML_B200_FUSED_PDL", 1);
     // 1. the activations of both lists (a node that shares them with an earlier node of either list does nothing)
-    for (cols_args * A : { &cb.ring, &cb.ring6, &cb.ring8, &cb.args }) {
+    for (cols_args * A : { &cb.ring, &cb.ring6, &cb.ring8, &cb.ring4, &cb.args }) {
         if (A->count == 0) continue;
         const dim3 grid((unsigned) (A->kmax / 256), (unsigned) A->count, COLS_N);
         k_quantize_cols<<<grid, 256, 0, st>>>(*A);
@@ -783,10 +796,11 @@ static int cols_launch(cols_builder & cb, cudaStream_t st) {
         b200_count_launch(1);
         return B200_OK;
     };
-    static smem_limit lim0, lim1, lim2;
+    static smem_limit lim0, lim1, lim2, lim3;
     if (cb.ring.count)  { if (const int rc = ring_launch(k_mmvq_cols_ring<0>, ring_geo<0>::smem, cb.ring, lim0)) return rc; }
     if (cb.ring6.count) { if (const int rc = ring_launch(k_mmvq_cols_ring<1>, ring_geo<1>::smem, cb.ring6, lim1)) return rc; }
     if (cb.ring8.count) { if (const int rc = ring_launch(k_mmvq_cols_ring<2>, ring_geo<2>::smem, cb.ring8, lim2)) return rc; }
+    if (cb.ring4.count) { if (const int rc = ring_launch(k_mmvq_cols_ring<3>, ring_geo<3>::smem, cb.ring4, lim3)) return rc; }
     // 3. tuning fallback: per-lane loads behind L2 prefetches
     if (cb.args.count) {
         cols_args & a = cb.args;
