@@ -697,13 +697,13 @@ extern "C" int b200_quantize_acts_columns(const float * x_dev, size_t x_row_stri
     if (((uintptr_t) x_dev & 3) || (x_row_stride_bytes & 3) || ((uintptr_t) columns_dev & 127)) return B200_ERR_STRIDE;
     static thread_local cols_args * a = nullptr;
     if (!a) a = new cols_args();
-    a->count = 1; a->units = 0; a->kmax = (int) k; a->pad = 0;
+    a->count = 1; a->units = 0; a->kmax = (int) k; a->nq = 1; a->qlist[0] = 0;
     cols_node & nd = a->nodes[0];
     memset(&nd, 0, sizeof(nd));
     nd.x = x_dev; nd.k = (int) k; nd.n = (int) n; nd.x_stride = (int) (x_row_stride_bytes / 4); nd.quantize = 1;
     nd.yq = (int8_t *) columns_dev;
     nd.ym = (uint8_t *) columns_dev + (((size_t) COLS_N * k + 127) & ~(size_t) 127);
-    const dim3 grid((unsigned) (k / 256), 1, COLS_N);
+    const dim3 grid((unsigned) ((k / 256 + 7) / 8), 1, COLS_N);
     k_quantize_cols<<<grid, 256, 0, (cudaStream_t) stream>>>(*a);
     b200_count_launch(1);
     B200_RETURN_IF_LAUNCH_FAILED();
