@@ -47,7 +47,8 @@ struct cols_node {
     uint8_t       * ym;       // workspace: per super-block f32 d [8 columns], then the activation sums (cols_meta below)
     int64_t row_stride;
     int   m, k, n, x_stride, unit0;     // unit0: index of this node's first 16-row tile in the launch
-    unsigned char type, quantize, pad[2];
+    unsigned char type, quantize, perm, unal;   // unal: Q6_K rows that are not 16-byte multiples (ring: aligned supersets per row);
+                                                // perm: the int8 of a 32-block sit as 0..3 16..19 4..7 20..23 .. (Q4_0 / Q8_0 B fragments: one 8-byte load)
 };
 static_assert(sizeof(cols_node) == 72, "cols_node is part of the kernel parameter block");
 static_assert(COLS_NW == 8, "k_mmvq_cols<8> splits K over the 8 warps of a CTA");
@@ -134,7 +135,13 @@ __global__ void __launch_bounds__(256) k_quantize_cols(const __grid_constant__ c
     pk.x = (uint32_t) (q[0] & 0xFF) | ((uint32_t) (q[1] & 0xFF) << 8) | ((uint32_t) (q[2] & 0xFF) << 16) | ((uint32_t) (q[3] & 0xFF) << 24);
     pk.y = (uint32_t) (q[4] & 0xFF) | ((uint32_t) (q[5] & 0xFF) << 8) | ((uint32_t) (q[6] & 0xFF) << 16) | ((uint32_t) (q[7] & 0xFF) << 24);
     // 32-block lane / 4, bytes 8 (lane & 3)..
-    *reinterpret_cast<uint2 *>(nd.yq + ((size_t) (sb * 8 + (lane >> 2)) * COLS_N + c) * 32 + (lane & 3) * 8) = pk;
+    int8_t * yb = nd.yq + ((size_t) (sb * 8 + (lane >> 2)) * COLS_N + c) * 32;
+    if (!nd.perm) *reinterpret_cast<uint2 *>(yb + (lane & 3) * 8) = pk;
+    else {
+        // elements j0 = 8 (lane & 3) .. j0 + 3 and j0 + 4 .. j0 + 7; four elements from j go to byte 2 j (j < 16) or 2 (j - 16) + 4
+        const int j0 = (lane & 3) * 8, p0 = j0 < 16 ? 2 * j0 : 2 * (j0 - 16) + 4;
+        *reinterpret_cast<uint32_t *>(yb + p0) = pk.x; *reinterpret_cast<uint32_t *>(yb + p0 + 8) = pk.y;
+    }
     int sum = q[0] + q[1] + q[2] + q[3] + q[4] + q[5] + q[6] + q[7];
     sum += __shfl_xor_sync(0xFFFFFFFFu, sum, 1);
     if ((lane & 1) == 0) {                                // sums of 16: group lane / 2
@@ -328,6 +335,26 @@ __device__ __forceinline__ void cols_load6(cols_item6 & it, const uint8_t * blk,
 #pragma unroll
         for (int i = 0; i < 4; i++) it.sc[i] = __funnelshift_r(w[i], w[i + 1], 16);
     }
+    it.d = *reinterpret_cast<const unsigned short *>(blk + 208);
+}
+// shared memory, block at any 2-byte alignment (known at run time only): every word is two aligned loads and a funnel shift
+__device__ __forceinline__ void cols_load6_var(cols_item6 & it, const uint8_t * blk, int t) {
+    const uint8_t * b4 = reinterpret_cast<const uint8_t *>(reinterpret_cast<uintptr_t>(blk) & ~(uintptr_t) 3);
+    const uint32_t sh = (uint32_t) (reinterpret_cast<uintptr_t>(blk) & 2) * 8;
+    auto ld = [&](int off) { return __funnelshift_r(*reinterpret_cast<const uint32_t *>(b4 + off), *reinterpret_cast<const uint32_t *>(b4 + off + 4), sh); };
+#pragma unroll
+    for (int h = 0; h < 2; h++)
+#pragma unroll
+        for (int s = 0; s < 2; s++) {
+            it.ql[h][0][s] = ld(64 * h + 16 * s + 4 * t);
+            it.ql[h][1][s] = ld(64 * h + 32 + 16 * s + 4 * t);
+            it.qh[h][s]    = ld(128 + 32 * h + 16 * s + 4 * t);
+        }
+    uint32_t w[5];
+#pragma unroll
+    for (int i = 0; i < 5; i++) w[i] = *reinterpret_cast<const uint32_t *>(b4 + 192 + 4 * i);
+#pragma unroll
+    for (int i = 0; i < 4; i++) it.sc[i] = __funnelshift_r(w[i], w[i + 1], sh);
     it.d = *reinterpret_cast<const unsigned short *>(blk + 208);
 }
 // yq_col: the column's int8 plane, [32-block][8 columns][32] from block 8 * item on (global memory, or the stage of the ring)
@@ -529,24 +556,25 @@ constexpr int RING_STAGES   = 3;
 // instantiation: folded into family 0 behind a run-time type test it cost Q4_K 7 % (0.720 -> 0.774 ms per Llama-2-7B pass at n = 8).
 template <int FAM> struct ring_geo {
     static constexpr int stages    = FAM == 2 ? 2 : RING_STAGES;
-    static constexpr int pitch_max = FAM == 1 ? RING_CI * 210 : (FAM == 2 ? RING_CI * 272 + 16 : (FAM == 3 ? RING_CI * 144 + 16 : RING_CI * 176 + 32));
+    static constexpr int pitch_max = FAM == 1 ? RING_CI * 210 : (FAM == 4 ? RING_CI * 210 + 32 : (FAM == 2 ? RING_CI * 272 + 16 : (FAM == 3 ? RING_CI * 144 + 16 : RING_CI * 176 + 32)));
     static constexpr int off_yq    = RING_ROWS * pitch_max;
     static constexpr int off_d     = off_yq + RING_CI * 8 * 32 * COLS_N;
     static constexpr int off_s     = off_d + RING_CI * COLS_N * 4;
-    static constexpr int s_bytes   = FAM == 2 ? 0 : (FAM == 0 ? COLS_N * 16 : COLS_N * 32);     // per super-block: s32 (128 B), s16 / n32 (256 B), none
+    static constexpr int s_bytes   = FAM == 2 ? 0 : (FAM == 0 ? COLS_N * 16 : COLS_N * 32);         // per super-block: s32 (128 B), s16 / n32 (256 B), none
     static constexpr int stage     = off_s + RING_CI * s_bytes;                 // 63744 / 72448 / 86784 / 56064
     static constexpr int off_red   = stages * stage;                            // float red[RING_NWC][128]
     static constexpr int off_bar   = off_red + RING_NWC * 128 * 4;
     static constexpr int smem      = off_bar + 128;
 };
-static_assert(ring_geo<1>::smem <= 232448 && ring_geo<0>::smem <= 232448 && ring_geo<2>::smem <= 232448 && ring_geo<3>::smem <= 232448, "the rings must fit the 227 KB of shared memory a CTA can have");
+static_assert(ring_geo<1>::smem <= 232448 && ring_geo<0>::smem <= 232448 && ring_geo<2>::smem <= 232448 && ring_geo<3>::smem <= 232448 && ring_geo<4>::smem <= 232448, "the rings must fit the 227 KB of shared memory a CTA can have");
 // row pitch and bytes per 256 weights of a node of family FAM (only family 0 holds two formats)
+// family 4 = Q6_K rows at 2-byte alignment: up to 14 bytes in front of a row's chunk, pitch 1712 = 48 mod 128 (eight distinct 16-byte bank groups)
 // Q4_0 / Q8_0 fragments are 4-byte loads, 16 bytes per row group: pitch = 16 mod 128 spreads the 8 row groups over all banks
 template <int FAM> __device__ __forceinline__ int ring_pitch(int type) {
-    return FAM == 1 ? RING_CI * 210 : (FAM == 2 ? RING_CI * 272 + 16 : (FAM == 3 ? RING_CI * 144 + 16 : (type == T_Q5_K ? RING_CI * 176 + 32 : RING_CI * 144 + 32)));
+    return FAM == 1 ? RING_CI * 210 : FAM == 4 ? RING_CI * 210 + 32 : (FAM == 2 ? RING_CI * 272 + 16 : (FAM == 3 ? RING_CI * 144 + 16 : (type == T_Q5_K ? RING_CI * 176 + 32 : RING_CI * 144 + 32)));
 }
 template <int FAM> __device__ __forceinline__ int ring_block_bytes(int type) {
-    return FAM == 1 ? 210 : (FAM == 2 ? 272 : (FAM == 3 ? 144 : (type == T_Q5_K ? 176 : 144)));
+    return FAM == 1 || FAM == 4 ? 210 : (FAM == 2 ? 272 : (FAM == 3 ? 144 : (type == T_Q5_K ? 176 : 144)));
 }
 
 __device__ __forceinline__ uint2 lds64(const uint8_t * p) { return *reinterpret_cast<const uint2 *>(p); }
@@ -585,13 +613,34 @@ __global__ void __launch_bounds__(RING_THREADS, 1) k_mmvq_cols_ring(const __grid
                 mbar_wait(&empty[stage], phase ^ 1u);
                 // third plane: sums of 32 (Q4_K / Q5_K: 128 B per super-block), -8 * sums (Q4_0: 256 B), sums of 16 (Q6_K: 256 B), none (Q8_0)
                 const uint32_t abytes = ci * (pw == 0 ? 8 * 32 * COLS_N : (pw == 1 ? COLS_N * 4 : G::s_bytes));
-                if (lane == 0) mbar_arrive_expect_tx(&full[stage], bytes * (uint32_t) my_rows + abytes);
-                __syncwarp();
-                if (lane < 11 && r < rows) bulk_g2s(st + r * pitch, src + (size_t) c0 * bs, bytes, &full[stage]);
+                if (FAM == 4) {
+                    // rows at 2-byte alignment (k / 256 not a multiple of 8): each row's chunk is copied as the 16-byte aligned range
+                    // around it (the consumers add the same offset); the last bytes of the tensor's last row are not over-read:
+                    // that one copy stops at the last whole 16 bytes and the lane stores the rest itself, before the arrive
+                    uint32_t cp = 0, tot = 0;
+                    const uint8_t * p0 = nullptr;
+                    if (lane < 11 && r < rows) {
+                        const uint8_t * p = src + (size_t) c0 * bs;
+                        const uint32_t mis = (uint32_t) (reinterpret_cast<uintptr_t>(p) & 15);
+                        p0 = p - mis; tot = mis + bytes;
+                        const bool last = row0 + r == nd.m - 1 && c0 + RING_CI >= items;
+                        cp = last ? (tot & ~15u) : ((tot + 15u) & ~15u);
+                        for (uint32_t o = cp; o < tot; o += 2)
+                            *reinterpret_cast<unsigned short *>(st + r * pitch + o) = __ldg(reinterpret_cast<const unsigned short *>(p0 + o));
+                    }
+                    const uint32_t total = __reduce_add_sync(0xFFFFFFFFu, cp);
+                    if (lane == 0) mbar_arrive_expect_tx(&full[stage], total + abytes);
+                    __syncwarp();
+                    if (cp) bulk_g2s(st + r * pitch, p0, cp, &full[stage]);
+                } else {
+                    if (lane == 0) mbar_arrive_expect_tx(&full[stage], bytes * (uint32_t) my_rows + abytes);
+                    __syncwarp();
+                    if (lane < 11 && r < rows) bulk_g2s(st + r * pitch, src + (size_t) c0 * bs, bytes, &full[stage]);
+                }
                 if (lane == 11) {
                     if (pw == 0)      bulk_g2s(st + G::off_yq, nd.yq + (size_t) c0 * (8 * 32 * COLS_N), abytes, &full[stage]);
                     else if (pw == 1) bulk_g2s(st + G::off_d, M.d + (size_t) c0 * COLS_N, abytes, &full[stage]);
-                    else if (FAM == 1)          bulk_g2s(st + G::off_s, M.s16 + (size_t) c0 * COLS_N * 4, abytes, &full[stage]);
+                    else if (FAM == 1 || FAM == 4) bulk_g2s(st + G::off_s, M.s16 + (size_t) c0 * COLS_N * 4, abytes, &full[stage]);
                     else if (FAM == 2)          { }
                     else if (FAM == 3)          bulk_g2s(st + G::off_s, M.n32 + (size_t) c0 * 8 * COLS_N, abytes, &full[stage]);
                     else                        bulk_g2s(st + G::off_s, M.s32 + (size_t) c0 * COLS_N * 2, abytes, &full[stage]);
@@ -639,14 +688,14 @@ __global__ void __launch_bounds__(RING_THREADS, 1) k_mmvq_cols_ring(const __grid
                     const uint2 dyb = lds64(st + G::off_d + slot * (COLS_N * 4) + 8 * t);                   // columns 2t, 2t + 1
                     const float2 dy = make_float2(__uint_as_float(dyb.x), __uint_as_float(dyb.y));
                     // (columns >= n hold whatever the workspace held: their results are never stored)
-                    if (FAM >= 2) {
+                    if (FAM == 2 || FAM == 3) {
                         // Q4_0 / Q8_0: eight 32-weight blocks with an f16 scale each; lane (g, t) takes quant bytes 4t..4t+3 (k slots
                         // 4t..) and, Q4_0: their high nibbles / Q8_0: bytes 16 + 4t.. (k slots 16 + 4t..) -- the activation
                         // bytes of the same positions.  Blocks of even index sit 2 bytes off word alignment: funnel shifts.
                         constexpr bool Q8 = FAM == 2;
                         constexpr int BB = Q8 ? 34 : 18;
-                        const uint8_t * yqs = st + G::off_yq + (slot * 8) * (32 * COLS_N) + g * 32 + 4 * t;
-                        const int hsel = (g & 4) << 2;                      // 0 or 16
+                        // (the list's quantizer stored them permuted -- cols_node::perm -- so that the two words are one 8-byte load)
+                        const uint8_t * yqs = st + G::off_yq + (slot * 8) * (32 * COLS_N) + g * 32 + 8 * t;
                         float sbs[4] = { 0.0f, 0.0f, 0.0f, 0.0f };          // the 256 weights' sums before the activations' scale (one per super-block)
                         auto blk = [&](auto Bc) {
                             constexpr int b = decltype(Bc)::value;
@@ -664,10 +713,8 @@ __global__ void __launch_bounds__(RING_THREADS, 1) k_mmvq_cols_ring(const __grid
                                 }
                             }
                             const float da = f16_bits_to_f32(lds16(ra + BB * b)), db = f16_bits_to_f32(lds16(rb + BB * b));
-                            // the two activation words are 16 bytes apart and columns 32: row groups g and g + 4 would share banks, so
-                            // groups 4..7 fetch them in the other order
-                            const uint32_t u0 = lds32(yqs + b * (32 * COLS_N) + hsel), u1 = lds32(yqs + b * (32 * COLS_N) + (hsel ^ 16));
-                            const uint32_t b0 = hsel ? u1 : u0, b1 = hsel ? u0 : u1;
+                            const uint2 bb = lds64(yqs + b * (32 * COLS_N));
+                            const uint32_t b0 = bb.x, b1 = bb.y;
                             int c[4];
                             if (Q8) mma_s8s8_16x8x32(c, wa0, wb0, wa1, wb1, b0, b1, COLS_I2F_BIAS);
                             else {
@@ -684,12 +731,19 @@ __global__ void __launch_bounds__(RING_THREADS, 1) k_mmvq_cols_ring(const __grid
                         blk(std::integral_constant<int, 6>()); blk(std::integral_constant<int, 7>());
                         acc[0] = fmaf(dy.x, sbs[0], acc[0]); acc[1] = fmaf(dy.y, sbs[1], acc[1]);
                         acc[2] = fmaf(dy.x, sbs[2], acc[2]); acc[3] = fmaf(dy.y, sbs[3], acc[3]);
-                    } else if (FAM == 1) {
+                    } else if (FAM == 1 || FAM == 4) {
                         const uint2 s16 = lds64(st + G::off_s + (slot * COLS_N + g) * 32 + 8 * t);          // column g, groups 4t..4t+3
                         const int8_t * yq = reinterpret_cast<const int8_t *>(st + G::off_yq) + g * 32;
                         cols_item6 ia, ib;
-                        if (slot & 1) { cols_load6<true, true>(ia, ra, t);  cols_load6<true, true>(ib, rb, t); }
-                        else          { cols_load6<false, true>(ia, ra, t); cols_load6<false, true>(ib, rb, t); }
+                        if (FAM == 4) {
+                            // the row's chunk sits `mis` bytes into its stage row (the producer copied the aligned range around it);
+                            // rows g and g + 8 are a multiple of 16 bytes apart
+                            const int row0 = (u - nd.unit0) * RING_ROWS;
+                            const uint32_t mis = (uint32_t) (reinterpret_cast<uintptr_t>(nd.w + (size_t) (row0 + 16 * half + g) * nd.row_stride + (size_t) c0 * bs) & 15);
+                            cols_load6_var(ia, ra + mis, t); cols_load6_var(ib, rb + mis, t);
+                        }
+                        else if (slot & 1) { cols_load6<true, true>(ia, ra, t);  cols_load6<true, true>(ib, rb, t); }
+                        else               { cols_load6<false, true>(ia, ra, t); cols_load6<false, true>(ib, rb, t); }
                         cols_item6_mma<true>(ia, ib, slot, t, yq, dy, s16, true, acc);
                     } else {
                         uint2 b[8];
@@ -729,9 +783,11 @@ static inline bool cols_node_ok(int type, const uint8_t * w, int64_t row_stride,
     if (type != T_Q4_K && type != T_Q5_K && type != T_Q6_K && !((type == T_Q4_0 || type == T_Q8_0) && ring_on)) return false;
     if (n < 2 || n > COLS_N || m < 1 || k < 256 || k % 256 != 0) return false;
     if (m >= (int64_t) 1 << 31 || k >= (int64_t) 1 << 24) return false;
-    if ((reinterpret_cast<uintptr_t>(w) & 15) || (row_stride & 15) || (reinterpret_cast<uintptr_t>(x) & 3) || (x_stride_bytes & 3)) return false;
-    // Q6_K: the ring copies chunks of 8 super-blocks (8 x 210 = 1680 bytes, a multiple of 16); a shorter last chunk would not be one
-    if (type == T_Q6_K && (k / 256) % 8 != 0) return false;
+    if ((reinterpret_cast<uintptr_t>(w) & 15) || (reinterpret_cast<uintptr_t>(x) & 3) || (x_stride_bytes & 3)) return false;
+    // rows that are multiples of 16 bytes; Q6_K (210-byte super-blocks: only when k / 256 is a multiple of 8) also at 2-byte alignment,
+    // where the ring copies the aligned range around each row's chunk (cols_node::unal) -- GGML_B200_COLS_UNAL=0: as one entry per column
+    static const int unal_on = env_int("GGML_B200_COLS_UNAL", 1);
+    if (type == T_Q6_K ? ((row_stride & 1) || (!(unal_on && ring_on) && ((row_stride & 15) || (k / 256) % 8 != 0))) : (row_stride & 15) != 0) return false;
     return row_stride >= k / 256 * cols_block_bytes(type);
 }
 static inline size_t cols_ws_bytes(int64_t k, int64_t n) {
@@ -747,8 +803,9 @@ struct cols_builder {
     cols_args ring6;      // Q6_K nodes: k_mmvq_cols_ring<1>
     cols_args ring8;      // Q8_0 nodes: k_mmvq_cols_ring<2>
     cols_args ring4;      // Q4_0 nodes: k_mmvq_cols_ring<3>
+    cols_args ring6u;     // Q6_K nodes whose rows are not 16-byte multiples: k_mmvq_cols_ring<4>
     // the activations quantized last (nodes of either list that read the same x share them: q/k/v, gate/up)
-    const float * last_x; int64_t last_k, last_n, last_stride; int8_t * last_yq; uint8_t * last_ym;
+    const float * last_x; int64_t last_k, last_n, last_stride; int8_t * last_yq; uint8_t * last_ym; int last_perm;
     cols_builder() { reset(); }
     void reset() {
         args.count = 0; args.units = 0; args.kmax = 0; args.nq = 0;
@@ -756,18 +813,21 @@ struct cols_builder {
         ring6.count = 0; ring6.units = 0; ring6.kmax = 0; ring6.nq = 0;
         ring8.count = 0; ring8.units = 0; ring8.kmax = 0; ring8.nq = 0;
         ring4.count = 0; ring4.units = 0; ring4.kmax = 0; ring4.nq = 0;
-        last_x = nullptr; last_k = last_n = last_stride = 0; last_yq = nullptr; last_ym = nullptr;
+        ring6u.count = 0; ring6u.units = 0; ring6u.kmax = 0; ring6u.nq = 0;
+        last_x = nullptr; last_k = last_n = last_stride = 0; last_yq = nullptr; last_ym = nullptr; last_perm = 0;
     }
-    bool full() const { return args.count >= COLS_MAX_NODES || ring.count >= COLS_MAX_NODES || ring6.count >= COLS_MAX_NODES || ring8.count >= COLS_MAX_NODES || ring4.count >= COLS_MAX_NODES; }
-    bool empty() const { return args.count == 0 && ring.count == 0 && ring6.count == 0 && ring8.count == 0 && ring4.count == 0; }
-    int  count() const { return args.count + ring.count + ring6.count + ring8.count + ring4.count; }
+    bool full() const { return args.count >= COLS_MAX_NODES || ring.count >= COLS_MAX_NODES || ring6.count >= COLS_MAX_NODES || ring8.count >= COLS_MAX_NODES || ring4.count >= COLS_MAX_NODES || ring6u.count >= COLS_MAX_NODES; }
+    bool empty() const { return args.count == 0 && ring.count == 0 && ring6.count == 0 && ring8.count == 0 && ring4.count == 0 && ring6u.count == 0; }
+    int  count() const { return args.count + ring.count + ring6.count + ring8.count + ring4.count + ring6u.count; }
     bool add(int type, const uint8_t * w, int64_t row_stride, int64_t m, int64_t k, const float * x, int64_t x_stride_bytes,
              int64_t n, float * dst, ws_cursor & cur) {
         static const int use_ring = env_int("GGML_B200_COLS_RING", 1);
-        cols_args & A = !use_ring ? args : (type == T_Q6_K ? ring6 : (type == T_Q8_0 ? ring8 : (type == T_Q4_0 ? ring4 : ring)));
+        const bool unal = type == T_Q6_K && ((row_stride & 15) || (k / 256) % 8 != 0);
+        cols_args & A = !use_ring ? args : (type == T_Q6_K ? (unal ? ring6u : ring6) : (type == T_Q8_0 ? ring8 : (type == T_Q4_0 ? ring4 : ring)));
         const int tile = use_ring ? RING_ROWS : 16;
         cols_node & nd = A.nodes[A.count];
-        if (last_x == x && last_k == k && last_n == n && last_stride == x_stride_bytes) {
+        const int perm = use_ring && (type == T_Q4_0 || type == T_Q8_0);
+        if (last_x == x && last_k == k && last_n == n && last_stride == x_stride_bytes && last_perm == perm) {
             nd.yq = last_yq; nd.ym = last_ym; nd.quantize = 0;     // same activations as the node before (gate/up, q/k/v)
         } else {
             const size_t need = cols_ws_bytes(k, n);
@@ -776,10 +836,11 @@ struct cols_builder {
             nd.ym = cur.p + (((size_t) COLS_N * k + 127) & ~(size_t) 127);
             nd.quantize = 1; cur.p += need; cur.left -= need;
             A.qlist[A.nq++] = (unsigned short) A.count;
-            last_x = x; last_k = k; last_n = n; last_stride = x_stride_bytes; last_yq = nd.yq; last_ym = nd.ym;
+            last_x = x; last_k = k; last_n = n; last_stride = x_stride_bytes; last_yq = nd.yq; last_ym = nd.ym; last_perm = perm;
         }
         nd.w = w; nd.x = x; nd.dst = dst; nd.row_stride = row_stride; nd.m = (int) m; nd.k = (int) k; nd.n = (int) n;
-        nd.x_stride = (int) (x_stride_bytes / 4); nd.unit0 = A.units; nd.type = (unsigned char) type; nd.pad[0] = nd.pad[1] = 0;
+        nd.x_stride = (int) (x_stride_bytes / 4); nd.unit0 = A.units; nd.type = (unsigned char) type; nd.perm = (unsigned char) perm;
+        nd.unal = (unsigned char) unal;
         A.units += (int) ((m + tile - 1) / tile);
         if (nd.k > A.kmax) A.kmax = nd.k;
         A.count++;
@@ -792,7 +853,7 @@ static int cols_launch(cols_builder & cb, cudaStream_t st) {
     const dev_caps & caps = current_caps();
     static const int pdl = env_int("GGML_B200_FUSED_PDL", 1);
     // 1. the activations of both lists (a node that shares them with an earlier node of either list does nothing)
-    for (cols_args * A : { &cb.ring, &cb.ring6, &cb.ring8, &cb.ring4, &cb.args }) {
+    for (cols_args * A : { &cb.ring, &cb.ring6, &cb.ring8, &cb.ring4, &cb.ring6u, &cb.args }) {
         if (A->nq == 0) continue;
         const dim3 grid((unsigned) ((A->kmax / 256 + 7) / 8), (unsigned) A->nq, COLS_N);
         k_quantize_cols<<<grid, 256, 0, st>>>(*A);
@@ -813,11 +874,12 @@ static int cols_launch(cols_builder & cb, cudaStream_t st) {
         b200_count_launch(1);
         return B200_OK;
     };
-    static smem_limit lim0, lim1, lim2, lim3;
+    static smem_limit lim0, lim1, lim2, lim3, lim4;
     if (cb.ring.count)  { if (const int rc = ring_launch(k_mmvq_cols_ring<0>, ring_geo<0>::smem, cb.ring, lim0)) return rc; }
     if (cb.ring6.count) { if (const int rc = ring_launch(k_mmvq_cols_ring<1>, ring_geo<1>::smem, cb.ring6, lim1)) return rc; }
     if (cb.ring8.count) { if (const int rc = ring_launch(k_mmvq_cols_ring<2>, ring_geo<2>::smem, cb.ring8, lim2)) return rc; }
     if (cb.ring4.count) { if (const int rc = ring_launch(k_mmvq_cols_ring<3>, ring_geo<3>::smem, cb.ring4, lim3)) return rc; }
+    if (cb.ring6u.count) { if (const int rc = ring_launch(k_mmvq_cols_ring<4>, ring_geo<4>::smem, cb.ring6u, lim4)) return rc; }
     // 3. tuning fallback: per-lane loads behind L2 prefetches
     if (cb.args.count) {
         cols_args & a = cb.args;

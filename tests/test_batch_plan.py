@@ -112,11 +112,13 @@ def test_few_column_nodes_take_the_mma_list_and_hazards_cut_it(lib):
     a = b200.mul_mat_node("q4_K", W0, 4096, 4096, xs("x"), 4, ys("a"))
     b = b200.mul_mat_node("q4_K", W0 + (1 << 26), 4096, 4096, ys("a"), 4, ys("b"))     # reads a: another launch
     c = b200.mul_mat_node("q8_0", W0 + (2 << 26), 4096, 4096, xs("x"), 4, ys("c"))     # Q8_0: the MMA list too (its own ring family)
-    d = b200.mul_mat_node("q6_K", W0 + (3 << 26), 64, 2304, xs("x2"), 4, ys("d"))      # Q6_K, 9 super-blocks: one persistent entry per column
-    p = plan(lib, [a, b, c, d])
+    d = b200.mul_mat_node("q6_K", W0 + (3 << 26), 64, 2304, xs("x2"), 4, ys("d"))      # Q6_K, 9 super-blocks (rows at 2-byte alignment): the MMA list
+    e = b200.mul_mat_node("q8_0", W0 + (4 << 26) + 8, 64, 4096, xs("x3"), 4, ys("e"))   # weights not 16-byte aligned: one persistent entry per column
+    p = plan(lib, [a, b, c, d, e])
     assert p[0] == (0, -1, 2) and p[1] == (1, -1, 2)
     assert p[2][2] == 2 and p[2][1] == -1
-    assert p[3][2] == 1 and p[3][1] == -1
+    assert p[3][2] == 2 and p[3][1] == -1
+    assert p[4][2] == 1 and p[4][1] == -1
 
 
 def test_shapes_outside_the_list_kernels_go_node_by_node(lib):

@@ -459,7 +459,8 @@ def test_mul_mat_batch_few_columns(kern, oracle, n):
     import b200
     import torch
     mats = [("q4_K", 300, 4096), ("q6_K", 130, 1024), ("q8_0", 96, 2048), ("q5_K", 4096, 1024), ("q4_0", 64, 4096),
-            ("q4_K", 17, 256), ("q5_K", 33, 11008), ("q4_K", 4096, 14336), ("q6_K", 200, 4096), ("q6_K", 49, 14336), ("q6_K", 1024, 2048)]
+            ("q4_K", 17, 256), ("q5_K", 33, 11008), ("q4_K", 4096, 14336), ("q6_K", 200, 4096), ("q6_K", 49, 14336), ("q6_K", 1024, 2048),
+            ("q6_K", 77, 11008), ("q6_K", 33, 2304), ("q6_K", 1, 256), ("q8_0", 40, 4128)]     # Q6_K rows at 2-byte alignment; k % 256 != 0
     c0 = kern.launch_count()
     for i, (t, m, k) in enumerate(mats):
         w_np = random_blocks(t, m, k, seed=40 + i)
@@ -499,12 +500,11 @@ def test_mul_mat_batch_few_columns(kern, oracle, n):
 
 
 def test_mul_mat_batch_few_columns_padded_row_stride(kern, oracle):
-    """weight rows padded to a 16-byte multiple: Q6_K with a super-block count that is not a multiple of 8 must stay off the
-    TMA ring (its chunks would not be multiples of 16 bytes) and take the one-column entries; Q4_K / Q6_K rows that do
-    qualify are read with the padded stride"""
+    """weight rows padded to a 16-byte multiple, read with the padded stride; Q6_K with a super-block count that is not a multiple
+    of 8 (its last chunk is not a multiple of 16 bytes) rides the ring family for rows at 2-byte alignment"""
     import b200
     import torch
-    for t, m, k, mode in (("q6_K", 70, 2304, 1), ("q6_K", 70, 2048, 2), ("q4_K", 70, 2304, 2), ("q5_K", 33, 768, 2)):
+    for t, m, k, mode in (("q6_K", 70, 2304, 2), ("q6_K", 70, 2048, 2), ("q4_K", 70, 2304, 2), ("q5_K", 33, 768, 2)):
         w_np = random_blocks(t, m, k, seed=91)
         rb = w_np.shape[1]
         stride = (rb + 15) // 16 * 16 + 32
@@ -514,7 +514,9 @@ def test_mul_mat_batch_few_columns_padded_row_stride(kern, oracle):
         x_np = np.random.default_rng(92).uniform(-1, 1, size=(4, k)).astype(np.float32)
         x = kern.to_device(x_np)
         y = torch.zeros((4, m), dtype=torch.float32, device=kern.device)
-        kern.mul_mat_batch((b200.MulMatNode * 1)(b200.mul_mat_node(t, w.data_ptr(), m, k, x.data_ptr(), 4, y.data_ptr(), a_row_stride=stride)))
+        nodes = (b200.MulMatNode * 1)(b200.mul_mat_node(t, w.data_ptr(), m, k, x.data_ptr(), 4, y.data_ptr(), a_row_stride=stride))
+        assert b200.batch_plan(kern.lib, nodes)[0][2] == 2
+        kern.mul_mat_batch(nodes)
         assert oracle.nmse(oracle.mul_mat(t, w_np, m, k, x_np, mode=mode), y.cpu().numpy()) <= NMSE_ORACLE, (t, m, k)
 
 
