@@ -1,4 +1,4 @@
-// mmvq_cols.cuh — decode at batch 2..8 (MUL_MAT with a few activation columns), Q4_K / Q5_K / Q6_K weights:
+// mmvq_cols.cuh — decode at batch 2..8 (MUL_MAT with a few activation columns), Q4_K / Q5_K / Q6_K / Q4_0 / Q8_0 weights:
 // ONE launch pair per list of independent nodes, int8 tensor-core MMA on the weight nibbles as they are.
 //
 // The reference sends n <= 8 through mul_mat_vec_q with ncols_dst template instances (src/ggml-cuda/mmvq.cu:139-226,
@@ -15,10 +15,12 @@
 //     (acc += sc * C, one IMAD per result instead of I2F + FMUL + FFMA), the -dmin * m * sum(q) term of Q4_K / Q5_K
 //     and the -32 offset of Q6_K become two tiny MMAs on the per-block activation sums (bsums, split into two
 //     bytes), and a super-block costs ~180 instructions per warp instead of 431 (round 1);
-//   * work unit = (node, 16-row tile), dealt round-robin to two CTAs per SM; the 8 warps of a CTA split K in
-//     256-weight super-blocks; whole tiles are requested into L2 two units ahead by bulk prefetches, the warps'
-//     own loads then hit L2; partial 16x8 tiles meet in shared memory and are added in fixed warp order: a row's
-//     value does not depend on the grid, a column's value does not depend on the other columns.
+//   * the shipped kernel is k_mmvq_cols_ring<family> further down (one persistent CTA per SM, 32-row tiles streamed through
+//     a TMA ring by three producer warps; one instantiation per format family, Q4_0 / Q8_0 and Q6_K rows at 2-byte
+//     alignment included); the k_mmvq_cols<KS> of this first part (work unit = (node, 16-row tile) dealt to two CTAs per
+//     SM, per-lane loads behind L2 prefetches, K-quants only) is the round-1 structure kept behind GGML_B200_COLS_RING=0;
+//     in both, partial 16x8 tiles meet in shared memory and are added in fixed warp order: a row's value does not
+//     depend on the grid, a column's value does not depend on the other columns.
 // Values: NMSE <= 1e-9 against the oracle's Q8_K arithmetic (mode 2), which is ggml-cpu's to 1e-10.
 #pragma once
 #include "mmvq_batch.cuh"
