@@ -97,6 +97,7 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
     lib.b200_dequantize_4d.argtypes = [i32, vp, A4i, A4s, vp, i32, A4i, A4s, vp]
     lib.b200_quantize_row_q8_1.restype = i32;    lib.b200_quantize_row_q8_1.argtypes = [vp, sz, i64, i64, vp, vp]
     lib.b200_quantize_rows.restype = i32;        lib.b200_quantize_rows.argtypes = [i32, vp, sz, i64, i64, vp, sz, vp]
+    lib.b200_quantize_rows_4d.restype = i32;     lib.b200_quantize_rows_4d.argtypes = [i32, vp, A4i, A4s, vp, A4s, vp]
     lib.b200_get_rows.restype = i32
     lib.b200_get_rows.argtypes = [i32, vp, sz, i64, i64, vp, sz, i64, vp, i32, sz, vp]
     lib.b200_mul_mat_workspace_size.restype = sz
@@ -375,6 +376,13 @@ class Kernels:
         out = torch.empty((n, row_bytes(t, k)), dtype=torch.uint8, device=self.device)
         self._check(self.lib.b200_quantize_rows(TYPE_ID[t], x.data_ptr(), x.stride(0) * 4, k, n, out.data_ptr(), out.stride(0), self._stream()),
                     "quantize_rows")
+        return out
+
+    def quantize_rows_4d(self, t: str, x, ne, nb_x, nb_y, out_bytes: int):
+        """strided form: x f32 device tensor (any view), ne / nb_x / nb_y in ggml order (dim 0 first, strides in bytes)."""
+        out = self.torch.zeros(out_bytes, dtype=self.torch.uint8, device=self.device)
+        self._check(self.lib.b200_quantize_rows_4d(TYPE_ID[t], x.data_ptr(), _a4i(ne), _a4s(nb_x), out.data_ptr(), _a4s(nb_y), self._stream()),
+                    "quantize_rows_4d")
         return out
 
     def quantize_acts_record(self, x):

@@ -49,8 +49,9 @@ struct cols_node {
     uint8_t       * ym;       // workspace: per super-block f32 d [8 columns], then the activation sums (cols_meta below)
     int64_t row_stride;
     int   m, k, n, x_stride, unit0;     // unit0: index of this node's first 16-row tile in the launch
-    unsigned char type, quantize, perm, unal;   // unal: Q6_K rows that are not 16-byte multiples (ring: aligned supersets per row);
-                                                // perm: the int8 of a 32-block sit as 0..3 16..19 4..7 20..23 .. (Q4_0 / Q8_0 B fragments: one 8-byte load)
+    unsigned char type, quantize, perm, unal;
+    // perm (Q4_0 / Q8_0 / Q6_K nodes of the ring kernel): the int8 of a 32-block sit as 0..3 16..19 4..7 20..23 .. so that the two B
+    //       words of a lane are one 8-byte load;  unal: Q6_K rows that are not 16-byte multiples (ring family 4)
 };
 static_assert(sizeof(cols_node) == 72, "cols_node is part of the kernel parameter block");
 static_assert(COLS_NW == 8, "k_mmvq_cols<8> splits K over the 8 warps of a CTA");
@@ -360,17 +361,22 @@ __device__ __forceinline__ void cols_load6_var(cols_item6 & it, const uint8_t * 
     it.d = *reinterpret_cast<const unsigned short *>(blk + 208);
 }
 // yq_col: the column's int8 plane, [32-block][8 columns][32] from block 8 * item on (global memory, or the stage of the ring)
-template <bool SMEM = false>
+// PERM (ring kernel): the int8 of a 32-block were stored as 0..3 16..19 4..7 20..23 .. (cols_node::perm), so the B words of the
+// two 16-weight groups of a block are one 8-byte load at 8 t (the 4-byte loads 16 bytes apart collided between row groups g, g + 4)
+template <bool SMEM = false, bool PERM = false>
 __device__ __forceinline__ void cols_item6_mma(const cols_item6 & ia, const cols_item6 & ib, int item, int t,
                                                const int8_t * yq_col, const float2 dy, const uint2 s16, bool col_ok, float (&acc)[4]) {
     int ai[4] = { 0, 0, 0, 0 };
+    uint2 bb = make_uint2(0u, 0u);
     auto group = [&](auto H, auto R, auto S) {
         constexpr int h = decltype(H)::value, r = decltype(R)::value, s = decltype(S)::value;
         const int B = item * 8 + 4 * h + r;                         // the 32-block of the activations
+        if (PERM && s == 0) bb = *reinterpret_cast<const uint2 *>(yq_col + B * (32 * COLS_N) + 8 * t);
         const uint32_t a0 = ((ia.ql[h][r & 1][s] >> (4 * (r >> 1))) & 0x0F0F0F0Fu) | (((ia.qh[h][s] >> (2 * r)) & 0x03030303u) << 4);
         const uint32_t a1 = ((ib.ql[h][r & 1][s] >> (4 * (r >> 1))) & 0x0F0F0F0Fu) | (((ib.qh[h][s] >> (2 * r)) & 0x03030303u) << 4);
         uint32_t b0 = 0u;
-        if (SMEM) b0 = *reinterpret_cast<const uint32_t *>(yq_col + B * (32 * COLS_N) + 16 * s + 4 * t);
+        if (PERM) b0 = s ? bb.y : bb.x;
+        else if (SMEM) b0 = *reinterpret_cast<const uint32_t *>(yq_col + B * (32 * COLS_N) + 16 * s + 4 * t);
         else if (col_ok) b0 = __ldg(reinterpret_cast<const uint32_t *>(yq_col + (size_t) B * (32 * COLS_N) + 16 * s + 4 * t));
         int c[4];
         mma_16x8x16<false>(c, a0, a1, b0);
@@ -746,7 +752,7 @@ __global__ void __launch_bounds__(RING_THREADS, 1) k_mmvq_cols_ring(const __grid
                         }
                         else if (slot & 1) { cols_load6<true, true>(ia, ra, t);  cols_load6<true, true>(ib, rb, t); }
                         else               { cols_load6<false, true>(ia, ra, t); cols_load6<false, true>(ib, rb, t); }
-                        cols_item6_mma<true>(ia, ib, slot, t, yq, dy, s16, true, acc);
+                        cols_item6_mma<true, true>(ia, ib, slot, t, yq, dy, s16, true, acc);
                     } else {
                         uint2 b[8];
 #pragma unroll
@@ -828,7 +834,7 @@ struct cols_builder {
         cols_args & A = !use_ring ? args : (type == T_Q6_K ? (unal ? ring6u : ring6) : (type == T_Q8_0 ? ring8 : (type == T_Q4_0 ? ring4 : ring)));
         const int tile = use_ring ? RING_ROWS : 16;
         cols_node & nd = A.nodes[A.count];
-        const int perm = use_ring && (type == T_Q4_0 || type == T_Q8_0);
+        const int perm = use_ring && (type == T_Q4_0 || type == T_Q8_0 || type == T_Q6_K);
         if (last_x == x && last_k == k && last_n == n && last_stride == x_stride_bytes && last_perm == perm) {
             nd.yq = last_yq; nd.ym = last_ym; nd.quantize = 0;     // same activations as the node before (gate/up, q/k/v)
         } else {

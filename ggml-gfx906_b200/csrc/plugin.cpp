@@ -304,9 +304,8 @@ static void b200_compute_node(b200_backend_ctx * ctx, struct ggml_tensor * node)
         case GGML_OP_DUP:
         case GGML_OP_CONT: {
             const struct ggml_tensor * dst = node->op == GGML_OP_CPY ? node->src[1] : node;
-            if (s0->type == GGML_TYPE_F32) {        // f32 -> Q8_0 / Q4_0, both contiguous and of one shape (supports_op)
-                B200_OK_OR_ABORT(b200_quantize_rows((int) dst->type, (const float *) s0->data, s0->nb[1], s0->ne[0], ggml_nrows(s0),
-                                                    dst->data, dst->nb[1], ctx->stream));
+            if (s0->type == GGML_TYPE_F32) {        // f32 -> Q8_0 / Q4_0 between tensors of one shape, dim 0 dense (supports_op)
+                B200_OK_OR_ABORT(b200_quantize_rows_4d((int) dst->type, (const float *) s0->data, s0->ne, s0->nb, dst->data, dst->nb, ctx->stream));
                 break;
             }
             const int out_type = dst->type == GGML_TYPE_F32 ? B200_TYPE_F32 : (dst->type == GGML_TYPE_F16 ? B200_TYPE_F16 : B200_TYPE_BF16);
@@ -634,7 +633,8 @@ static bool b200_dev_supports_op(ggml_backend_dev_t dev, const struct ggml_tenso
         case GGML_OP_CONT: {
             const struct ggml_tensor * dst = op->op == GGML_OP_CPY ? s1 : op;
             if (s0 && dst && s0->type == GGML_TYPE_F32 && (dst->type == GGML_TYPE_Q8_0 || dst->type == GGML_TYPE_Q4_0))
-                return op->op == GGML_OP_CPY && ggml_is_contiguous(s0) && ggml_is_contiguous(dst) && ggml_are_same_shape(s0, dst);
+                return op->op == GGML_OP_CPY && ggml_are_same_shape(s0, dst) && s0->nb[0] == sizeof(float) && dst->nb[0] == ggml_type_size(dst->type) &&
+                       s0->ne[0] % 32 == 0;
             return s0 && dst && is_block_quant(s0->type) && (dst->type == GGML_TYPE_F32 || dst->type == GGML_TYPE_F16 || dst->type == GGML_TYPE_BF16) &&
                    s0->nb[0] == ggml_type_size(s0->type) && ggml_nelements(s0) == ggml_nelements(dst);
         }

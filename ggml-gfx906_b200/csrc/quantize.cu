@@ -109,15 +109,16 @@ __global__ void __launch_bounds__(256) k_quantize_acts(const uint8_t * __restric
 //   Q8_0: d = amax / 127, q = roundf(x / d)                         Q4_0: d = (the FIRST value of largest magnitude) / -8,
 //                                                                         q = min(15, (int8) (x / d + 8.5f))
 // One warp per 32-value block (lane = element); rows of k values x_row_stride bytes apart, blocks of a row contiguous.
+// rows (i1, i2, i3) of a 4-D tensor: strides in bytes, dim 0 dense on both sides (ggml CPY between tensors of one shape)
+struct qrows_geo { int64_t k, ne1, ne2; int64_t xs[3], ys[3]; };
 template <int T>
-__global__ void __launch_bounds__(256) k_quantize_blocks(const uint8_t * __restrict__ x, int64_t x_row_stride, int64_t k,
-                                                         uint8_t * __restrict__ y, int64_t y_row_stride) {
+__global__ void __launch_bounds__(256) k_quantize_blocks(const uint8_t * __restrict__ x, uint8_t * __restrict__ y, const qrows_geo g, int64_t row0) {
     const int64_t kb = (int64_t) blockIdx.x * 8 + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
-    if (kb * 32 >= k) return;
-    const int64_t row = blockIdx.y;
-    const float v = reinterpret_cast<const float *>(x + row * x_row_stride)[kb * 32 + lane];
-    uint8_t * b = y + row * y_row_stride + kb * fmt<T>::bytes;
+    if (kb * 32 >= g.k) return;
+    const int64_t row = row0 + blockIdx.y, i1 = row % g.ne1, i2 = (row / g.ne1) % g.ne2, i3 = row / (g.ne1 * g.ne2);
+    const float v = reinterpret_cast<const float *>(x + i1 * g.xs[0] + i2 * g.xs[1] + i3 * g.xs[2])[kb * 32 + lane];
+    uint8_t * b = y + i1 * g.ys[0] + i2 * g.ys[1] + i3 * g.ys[2] + kb * fmt<T>::bytes;
     if (T == T_Q8_0) {
         const float amax = warp_max(fabsf(v));
         const float d  = __fdiv_rn(amax, 127.0f);
@@ -188,22 +189,39 @@ extern "C" int b200_quantize_acts(const float * x_dev, size_t x_row_stride_bytes
     return b200_quantize_acts_planes(x_dev, x_row_stride_bytes, k, n, q, dd, (cudaStream_t) stream);
 }
 
-// rows of f32 -> rows of Q8_0 / Q4_0 blocks (b200_quantize_rows, include/ggml_b200.h)
+// rows of f32 -> rows of Q8_0 / Q4_0 blocks (b200_quantize_rows / _4d, include/ggml_b200.h)
+static int quantize_rows_launch(int type, const void * x_dev, void * y_dev, const qrows_geo & g, int64_t n, cudaStream_t st) {
+    for (int64_t r0 = 0; r0 < n; r0 += 65535) {
+        const int64_t nr = n - r0 < 65535 ? n - r0 : 65535;
+        const dim3 grid((unsigned) ceil_div(g.k / 32, 8), (unsigned) nr);
+        if (type == T_Q8_0) k_quantize_blocks<T_Q8_0><<<grid, 256, 0, st>>>((const uint8_t *) x_dev, (uint8_t *) y_dev, g, r0);
+        else                k_quantize_blocks<T_Q4_0><<<grid, 256, 0, st>>>((const uint8_t *) x_dev, (uint8_t *) y_dev, g, r0);
+        b200_count_launch(1);
+    }
+    B200_RETURN_IF_LAUNCH_FAILED();
+    return B200_OK;
+}
 extern "C" int b200_quantize_rows(int type, const float * x_dev, size_t x_row_stride_bytes, int64_t k, int64_t n,
                                   void * y_dev, size_t y_row_stride_bytes, void * stream) {
     if (type != T_Q8_0 && type != T_Q4_0) return B200_ERR_TYPE;
     if (k < 0 || n < 0 || k % 32 != 0) return B200_ERR_SHAPE;
     if (x_row_stride_bytes % 4 != 0 || y_row_stride_bytes % 2 != 0 || ((uintptr_t) y_dev & 1)) return B200_ERR_STRIDE;
     if (k == 0 || n == 0) return B200_OK;
-    for (int64_t r0 = 0; r0 < n; r0 += 65535) {
-        const int64_t nr = n - r0 < 65535 ? n - r0 : 65535;
-        const dim3 grid((unsigned) ceil_div(k / 32, 8), (unsigned) nr);
-        const uint8_t * x = (const uint8_t *) x_dev + r0 * x_row_stride_bytes;
-        uint8_t * y = (uint8_t *) y_dev + r0 * y_row_stride_bytes;
-        if (type == T_Q8_0) k_quantize_blocks<T_Q8_0><<<grid, 256, 0, (cudaStream_t) stream>>>(x, (int64_t) x_row_stride_bytes, k, y, (int64_t) y_row_stride_bytes);
-        else                k_quantize_blocks<T_Q4_0><<<grid, 256, 0, (cudaStream_t) stream>>>(x, (int64_t) x_row_stride_bytes, k, y, (int64_t) y_row_stride_bytes);
-        b200_count_launch(1);
-    }
-    B200_RETURN_IF_LAUNCH_FAILED();
-    return B200_OK;
+    qrows_geo g;
+    g.k = k; g.ne1 = n; g.ne2 = 1;
+    g.xs[0] = (int64_t) x_row_stride_bytes; g.xs[1] = g.xs[2] = 0; g.ys[0] = (int64_t) y_row_stride_bytes; g.ys[1] = g.ys[2] = 0;
+    return quantize_rows_launch(type, x_dev, y_dev, g, n, (cudaStream_t) stream);
+}
+extern "C" int b200_quantize_rows_4d(int type, const float * x_dev, const int64_t ne[4], const size_t nb_x[4],
+                                     void * y_dev, const size_t nb_y[4], void * stream) {
+    if (type != T_Q8_0 && type != T_Q4_0) return B200_ERR_TYPE;
+    if (ne[0] < 0 || ne[1] < 0 || ne[2] < 0 || ne[3] < 0 || ne[0] % 32 != 0) return B200_ERR_SHAPE;
+    if (nb_x[0] != sizeof(float) || nb_y[0] != (size_t) type_bytes(type) || ((uintptr_t) x_dev & 3) || ((uintptr_t) y_dev & 1)) return B200_ERR_STRIDE;
+    for (int d = 1; d < 4; d++) if (nb_x[d] % 4 != 0 || nb_y[d] % 2 != 0) return B200_ERR_STRIDE;
+    const int64_t n = ne[1] * ne[2] * ne[3];
+    if (ne[0] == 0 || n == 0) return B200_OK;
+    qrows_geo g;
+    g.k = ne[0]; g.ne1 = ne[1]; g.ne2 = ne[2];
+    for (int d = 0; d < 3; d++) { g.xs[d] = (int64_t) nb_x[d + 1]; g.ys[d] = (int64_t) nb_y[d + 1]; }
+    return quantize_rows_launch(type, x_dev, y_dev, g, n, (cudaStream_t) stream);
 }

@@ -130,6 +130,10 @@ B200_API int b200_quantize_row_q8_1(const float * x_dev, size_t x_row_stride_byt
  * x_dev: n rows of k floats (k % 32 == 0); y_dev: n rows of k / 32 blocks, rows y_row_stride_bytes apart. */
 B200_API int b200_quantize_rows(int type, const float * x_dev, size_t x_row_stride_bytes, int64_t k, int64_t n,
                                 void * y_dev, size_t y_row_stride_bytes, void * stream);
+/* Strided 4-D form (ggml CPY between tensors of one shape, e.g. a permuted f32 source into a K/V-cache view): ne = the shape
+ * in elements, nb_x / nb_y = ggml byte strides; dim 0 dense on both sides (nb_x[0] == 4, nb_y[0] == block bytes). */
+B200_API int b200_quantize_rows_4d(int type, const float * x_dev, const int64_t ne[4], const size_t nb_x[4],
+                                   void * y_dev, const size_t nb_y[4], void * stream);
 
 /* ---- GET_ROWS ------------------------------------------------------------------------------
  * replaces ggml_cuda_op_get_rows / get_rows_cuda_q (src/ggml-cuda/getrows.cu:93-124, 236-253) and

@@ -112,3 +112,20 @@ def test_quantize_rows_bit_exact(kern, oracle, golden, t):
     big = kern.to_device(np.concatenate([x, x], axis=1))
     got = kern.quantize_rows(t, big[:, :x.shape[1]]).cpu().numpy()        # row stride twice the row
     assert np.array_equal(got, oracle.quantize(t, x))
+
+
+@pytest.mark.parametrize("t", ("q8_0", "q4_0"))
+def test_quantize_rows_4d_permuted_source(kern, oracle, t):
+    """CPY f32 -> quant from a permuted source (ggml permute 0,2,1,3: dims 1 and 2 swapped) into a dense destination: every row
+    (i1, i2, i3) bit for bit the quantized source row"""
+    from b200 import row_bytes
+    rng = np.random.default_rng(9)
+    k, a, b, c = 256, 2, 3, 4                       # the view has ne = [k, a, b, c]; its memory is [c][a][b][k]
+    mem = rng.standard_normal((c, a, b, k)).astype(np.float32)
+    view = np.ascontiguousarray(mem.transpose(0, 2, 1, 3))      # [c][b][a][k]: what the view reads in index order
+    rb = row_bytes(t, k)
+    nb_x = [4, 4 * k * b, 4 * k, 4 * k * b * a]     # strides of ne[1] = a, ne[2] = b, ne[3] = c in mem
+    nb_y = [rb // (k // 32), rb, rb * a, rb * a * b]
+    got = kern.quantize_rows_4d(t, kern.to_device(mem), [k, a, b, c], nb_x, nb_y, rb * a * b * c).cpu().numpy()
+    want = oracle.quantize(t, view.reshape(-1, k))
+    assert np.array_equal(got.reshape(-1, rb), want)

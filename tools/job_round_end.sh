@@ -15,5 +15,6 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:^
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:k_mmvq_batch -s 8 -c 1 -o gpurun_out/${T}_batch python bench.py --steps 3 --warmup 3 --no-extras > gpurun_out/${T}_ncu2.log 2>&1; echo full=$?
 timeout 300 python tools/bs_probe.py 1 2 4 8 > gpurun_out/${T}_bs_probe_l3mix.txt 2>&1
 BS_STACK=q4_K timeout 300 python tools/bs_probe.py 2 4 8 > gpurun_out/${T}_bs_probe_q4k.txt 2>&1
+for S in q5_K q6_K q4_0 q8_0; do BS_STACK=$S timeout 300 python tools/bs_probe.py 1 2 8 2>&1 | tail -3; done > gpurun_out/${T}_bs_probe_other_formats.txt
 timeout 600 python tools/prefill_l3_probe.py > gpurun_out/${T}_prefill_l3.txt 2>&1
 timeout 600 python tools/support_probe.py > gpurun_out/${T}_support_probe.txt 2>&1
