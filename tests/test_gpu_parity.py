@@ -460,7 +460,8 @@ def test_mul_mat_batch_few_columns(kern, oracle, n):
     import torch
     mats = [("q4_K", 300, 4096), ("q6_K", 130, 1024), ("q8_0", 96, 2048), ("q5_K", 4096, 1024), ("q4_0", 64, 4096),
             ("q4_K", 17, 256), ("q5_K", 33, 11008), ("q4_K", 4096, 14336), ("q6_K", 200, 4096), ("q6_K", 49, 14336), ("q6_K", 1024, 2048),
-            ("q6_K", 77, 11008), ("q6_K", 33, 2304), ("q6_K", 1, 256), ("q8_0", 40, 4128)]     # Q6_K rows at 2-byte alignment; k % 256 != 0
+            ("q6_K", 77, 11008), ("q6_K", 33, 2304), ("q6_K", 1, 256), ("q8_0", 40, 4128),     # Q6_K rows at 2-byte alignment; k % 256 != 0
+            ("q4_0", 33, 256), ("q8_0", 1, 11008), ("q4_0", 4097, 1024), ("q8_0", 300, 28672), ("q4_0", 31, 11008), ("q6_K", 4099, 768)]
     c0 = kern.launch_count()
     for i, (t, m, k) in enumerate(mats):
         w_np = random_blocks(t, m, k, seed=40 + i)
@@ -560,19 +561,19 @@ def test_mul_mat_batch_prefill_nodes_share_lanes(kern, oracle):
 
 
 def test_mul_mat_batch_few_columns_long_mixed_list(kern, oracle):
-    """more 2..8-column nodes than one launch of the MMA list kernel takes (384 per family): Q4_K / Q5_K / Q6_K interleaved,
+    """more 2..8-column nodes than one launch of the MMA list kernel takes (384 per family): all five formats interleaved,
     groups of three sharing their activations (q / k / v), row counts that are not multiples of the 32-row tile, k up to
     28672 (14 chunks of the ring).  Sampled nodes against the oracle, all of them finite and reproducible."""
     import b200
     import torch
     n = 5
     rng = np.random.default_rng(123)
-    types = ("q4_K", "q6_K", "q5_K")
-    shapes = [(33, 2048), (70, 4096), (17, 2048), (129, 2048)]
+    types = ("q4_K", "q6_K", "q5_K", "q4_0", "q8_0", "q6_K")
+    shapes = [(33, 2048), (70, 4096), (17, 2048), (129, 2048), (40, 1280)]     # k = 1280: Q6_K rows at 2-byte alignment (family 4)
     nodes, keep = [], []
     xs = {}
     for i in range(1000):
-        t = types[i % 3]
+        t = types[(i % 3) + 3 * ((i // 3) % 2)]
         m, k = (24, 28672) if i == 500 else shapes[(i // 3) % len(shapes)]
         g = i // 3                                   # three consecutive nodes read the same x
         if (g, k) not in xs:
