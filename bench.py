@@ -502,7 +502,7 @@ def measure_gguf_load(torch, kern, gib=1.0):
 
 def measure_decode_batches(torch, kern, stack, peak):
     """Secondary figure: the same stack (same resident weights) with n = 2, 4, 8 activation columns per MUL_MAT
-    (decode at batch n, BASELINE configs[3]): one b200_mul_mat_batch list per pass (Q4_K / Q5_K: the MMA list
+    (decode at batch n, BASELINE configs[3]): one b200_mul_mat_batch list per pass (the MMA list
     kernel of mmvq_cols.cuh), CUDA graph replay; GB/s on the weight bytes and tokens/s."""
     import b200
     out = {}
