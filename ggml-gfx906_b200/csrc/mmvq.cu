@@ -685,7 +685,7 @@ extern "C" int b200_quantize_acts_record(const float * x_dev, int64_t k, void * 
     batch_node & nd = a->nodes[0];
     memset(&nd, 0, sizeof(nd));
     nd.x = x_dev; nd.acts = (const uint8_t *) record_dev; nd.k = (int) k; nd.qflags = BATCH_Q_PRE | BATCH_Q_LOAD; nd.dep = -1;
-    const dim3 grid((unsigned) ceil_div(k / 32, 8), 1);
+    const dim3 grid((unsigned) ceil_div(k / 128, 8), 1);
     k_quantize_batch<<<grid, 256, 0, (cudaStream_t) stream>>>(*a);
     b200_count_launch(1);
     B200_RETURN_IF_LAUNCH_FAILED();

@@ -231,10 +231,12 @@ __device__ __forceinline__ void batch_slab(const node_r & nd, int & v, int & r_b
 }
 
 // ---------------------------------------------------------------- all activations of a list: f32 -> q8
-// grid (ceil(kmax / 32 / 8), count), block 256: one warp per 32 values (lane = element), as k_quantize_acts.
+// grid (ceil(kmax / 128 / 8), count), block 256: one warp per 128 values -- 8 lanes per 32-value block, 4 consecutive values per
+// lane (one 16-byte load), the arithmetic of k_quantize_acts.  (One warp per 32 values was 9 675 CTAs per Llama-2-7B list, half
+// of them past the end of a k = 4096 node: 9 us in front of every launch, every rank of a row split pays all of it.)
 __global__ void __launch_bounds__(256) k_quantize_batch(const __grid_constant__ batch_args a) {
     const batch_node & nd = a.nodes[blockIdx.y];
-    const int kb = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int item = blockIdx.x * 8 + (threadIdx.x >> 5);           // 128 values
     const int lane = threadIdx.x & 31;
     if (a.epoch) {
         // row split: this launch counts in set (epoch & 1); the other set is zeroed for the next launch (see the header)
@@ -248,20 +250,25 @@ __global__ void __launch_bounds__(256) k_quantize_batch(const __grid_constant__ 
     } else if (blockIdx.x == 0 && threadIdx.x == 0 && a.done) {
         a.done[blockIdx.y] = 0u;
     }
-    if (!(nd.qflags & BATCH_Q_PRE) || kb * 32 >= nd.k) return;
-    const float x = __ldg(nd.x + kb * 32 + lane);
-    const float amax = warp_max(fabsf(x));
+    if (!(nd.qflags & BATCH_Q_PRE) || item * 128 >= nd.k) return;    // k is a multiple of 256
+    const float4 x = __ldg(reinterpret_cast<const float4 *>(nd.x + item * 128) + lane);
+    float amax = fmaxf(fmaxf(fabsf(x.x), fabsf(x.y)), fmaxf(fabsf(x.z), fabsf(x.w)));
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xFFFFFFFFu, amax, o));
     const float d  = __fdiv_rn(amax, 127.0f);
     const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
     // float -> int8 as quantize.cu does it (cvttss2si semantics of the reference's x86 build)
-    const float v  = roundf(__fmul_rn(x, id));
-    const int   qi = fabsf(v) < 2147483648.0f ? (int) v : (int) 0x80000000;
+    auto q8 = [&](float xv) {
+        const float v = roundf(__fmul_rn(xv, id));
+        return (uint32_t) ((fabsf(v) < 2147483648.0f ? (int) v : (int) 0x80000000) & 0xFF);
+    };
+    const uint32_t pk = q8(x.x) | (q8(x.y) << 8) | (q8(x.z) << 16) | (q8(x.w) << 24);
     int8_t * q = reinterpret_cast<int8_t *>(const_cast<uint8_t *>(nd.acts));
     // 16-byte piece p of 128-value item idx is stored at piece (p + idx) % 8 of the item: the consumer lanes
     // (one item each, 128 B apart) then read piece p from eight different bank groups
-    const int e = kb * 32 + lane, idx = e >> 7, pc = (e >> 4) & 7;
-    q[idx * 128 + (((pc + idx) & 7) << 4) + (e & 15)] = (int8_t) (qi & 0xFF);
-    if (lane == 0) reinterpret_cast<float *>(q + nd.k)[kb] = __half2float(__float2half_rn(d));
+    const int pc = lane >> 2;                                        // elements 4 lane .. 4 lane + 3 of the item
+    *reinterpret_cast<uint32_t *>(q + item * 128 + (((pc + item) & 7) << 4) + (lane & 3) * 4) = pk;
+    if ((lane & 7) == 0) reinterpret_cast<float *>(q + nd.k)[item * 4 + (lane >> 3)] = __half2float(__float2half_rn(d));
 }
 
 // What the consumers need of a node; written to the head of the activation buffer by the activation
@@ -856,7 +863,7 @@ static int batch_launch(batch_builder & bb, cudaStream_t st) {
     if (const int rc = lim[bb.fam].ensure(kern, smem)) return rc;
     // 1. every activation vector of the list -> q8 (one launch)
     {
-        const dim3 grid((unsigned) ceil_div(a.kmax / 32, 8), (unsigned) a.count);
+        const dim3 grid((unsigned) ceil_div(a.kmax / 128, 8), (unsigned) a.count);
         k_quantize_batch<<<grid, 256, 0, st>>>(a);
         b200_count_launch(1);
     }
