@@ -98,6 +98,10 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
     lib.b200_quantize_row_q8_1.restype = i32;    lib.b200_quantize_row_q8_1.argtypes = [vp, sz, i64, i64, vp, vp]
     lib.b200_quantize_rows.restype = i32;        lib.b200_quantize_rows.argtypes = [i32, vp, sz, i64, i64, vp, sz, vp]
     lib.b200_quantize_rows_4d.restype = i32;     lib.b200_quantize_rows_4d.argtypes = [i32, vp, A4i, A4s, vp, A4s, vp]
+    lib.b200_mul_mat_id_workspace_size.restype = sz
+    lib.b200_mul_mat_id_workspace_size.argtypes = [i32, A4i, A4i]
+    lib.b200_mul_mat_id.restype = i32
+    lib.b200_mul_mat_id.argtypes = [i32, vp, A4i, A4s, vp, A4i, A4s, vp, C.POINTER(i64), C.POINTER(sz), vp, vp, sz, vp]
     lib.b200_get_rows.restype = i32
     lib.b200_get_rows.argtypes = [i32, vp, sz, i64, i64, vp, sz, i64, vp, i32, sz, vp]
     lib.b200_mul_mat_workspace_size.restype = sz
@@ -376,6 +380,22 @@ class Kernels:
         out = torch.empty((n, row_bytes(t, k)), dtype=torch.uint8, device=self.device)
         self._check(self.lib.b200_quantize_rows(TYPE_ID[t], x.data_ptr(), x.stride(0) * 4, k, n, out.data_ptr(), out.stride(0), self._stream()),
                     "quantize_rows")
+        return out
+
+    def mul_mat_id(self, t: str, experts, m: int, k: int, n_as: int, x, ids):
+        """MUL_MAT_ID: experts = n_as stacked matrices of m rows of k (block bytes, contiguous), x f32 [n_tok][ne11][k], ids int32
+        [n_tok][n_used] -> f32 [n_tok][n_used][m]; slot e of token t multiplies expert ids[t, e] with x[t, e % ne11]."""
+        torch = self.torch
+        n_tok, ne11, _ = x.shape
+        n_used = ids.shape[1]
+        rb = row_bytes(t, k)
+        ne_a, nb_a = _a4i([k, m, n_as, 1]), _a4s([BLOCK_BYTES[t], rb, rb * m, rb * m * n_as])
+        ne_b, nb_b = _a4i([k, ne11, n_tok, 1]), _a4s([4, 4 * k, 4 * k * ne11, 4 * k * ne11 * n_tok])
+        ne_i, nb_i = (C.c_int64 * 2)(n_used, n_tok), (C.c_size_t * 2)(4, 4 * n_used)
+        ws = torch.empty(int(self.lib.b200_mul_mat_id_workspace_size(TYPE_ID[t], ne_a, ne_b)) + 256, dtype=torch.uint8, device=self.device)
+        out = torch.empty((n_tok, n_used, m), dtype=torch.float32, device=self.device)
+        self._check(self.lib.b200_mul_mat_id(TYPE_ID[t], experts.data_ptr(), ne_a, nb_a, x.data_ptr(), ne_b, nb_b, ids.data_ptr(), ne_i, nb_i,
+                                             out.data_ptr(), ws.data_ptr(), ws.numel(), self._stream()), "mul_mat_id")
         return out
 
     def quantize_rows_4d(self, t: str, x, ne, nb_x, nb_y, out_bytes: int):

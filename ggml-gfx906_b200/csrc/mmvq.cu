@@ -279,6 +279,15 @@ extern "C" int b200_mul_mat_id(int type_a, const void * as_dev, const int64_t ne
     a.ids = (const uint8_t *) ids_dev; a.ids_nb0 = (int64_t) nb_ids[0]; a.ids_nb1 = (int64_t) nb_ids[1]; a.n_as = n_as; a.ne11 = ne11;
     a.bad = b200_error_word_dev();
     int rc;
+    // decode (and small batches): the K-stationary TMA-staged kernel, one grid plane per (slot, token), expert looked up on the device
+    // (the one-warp-per-row kernel below reached 25 % of the HBM peak on Mixtral-like experts)
+    static const int moe_stream = env_int("GGML_B200_MOE_STREAM", 1);
+    if (moe_stream && type_is_quant(type_a) && type_a != T_Q6_K && m >= 1) {          // Q6_K measured slower there (69 vs 52 us)
+        stream_moe mo = { (const uint8_t *) ids_dev, (int64_t) nb_ids[0], (int64_t) nb_ids[1], (int64_t) nb_a[2], n_as, ne11, n_used, n_tok, a.bad };
+        rc = mmvq_stream_try(type_a, (const uint8_t *) as_dev, (int64_t) nb_a[1], m, k, yq, yd, 1, dst_dev, m, st, &mo);
+        if (rc == B200_OK) return rc;
+        if (rc != B200_STREAM_NOT_APPLICABLE) return rc;
+    }
     switch (type_a) {
         case T_Q4_0: rc = launch_generic<T_Q4_0>(a, st); break;
         case T_Q8_0: rc = launch_generic<T_Q8_0>(a, st); break;

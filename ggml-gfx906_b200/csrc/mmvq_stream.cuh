@@ -344,6 +344,13 @@ struct stream_args {
     int     slots_off;        // byte offset of slot 0 in dynamic smem
     int     contiguous;       // rows back to back in memory -> one bulk copy per stage
     int     row_pitch;        // non-contiguous: bytes between rows inside a slot (multiple of 16)
+    // MUL_MAT_ID (grid y = slot e, grid z = token t): the weights are expert ids[e, t] of the stack (w_nb2 bytes apart), the
+    // activations column t * ne11 + e % ne11 of the planes, the results go to dst + e * dst_nb2 + t * dst_nb3; NULL: plain MUL_MAT
+    const uint8_t * ids;
+    int64_t ids_nb0, ids_nb1, w_nb2, dst_nb2, dst_nb3;
+    int     n_as, ne11;
+    unsigned * bad;           // sticky error word: an expert id outside [0, n_as)
+    int     n_tok_grid;       // MUL_MAT_ID: tokens (grid z); slots (grid y) = dst_nb3 / dst_nb2
 };
 
 template <int NCOLS, int IPL> struct stream_cfg {
@@ -366,11 +373,28 @@ k_mmvq_stream(const stream_args a) {
     const int64_t r_begin = (int64_t) blockIdx.x * a.rows_per_cta;
     const int nrows = (int) ((a.m - r_begin < a.rows_per_cta) ? (a.m - r_begin) : a.rows_per_cta);
     const int nbatch = (nrows + R - 1) / R;
+    const uint8_t * wbase = a.w;
+    const int8_t * yq = a.yq;
+    const float  * yd = a.yd;
+    float * dst = a.dst;
+    if (a.ids) {                                              // the same for the whole CTA
+        const int64_t i12 = blockIdx.y, i13 = blockIdx.z;
+        const int32_t e = *reinterpret_cast<const int32_t *>(a.ids + i12 * a.ids_nb0 + i13 * a.ids_nb1);
+        dst += i12 * a.dst_nb2 + i13 * a.dst_nb3;
+        if (e < 0 || e >= a.n_as) {                           // the reference asserts (src/ggml-cpu/ggml-cpu.c:1556): flag it, write zeros
+            if (tid == 0 && blockIdx.x == 0 && a.bad) atomicOr_system(a.bad, 1u);
+            for (int r = tid; r < nrows; r += blockDim.x) dst[r_begin + r] = 0.0f;
+            return;
+        }
+        wbase += (int64_t) e * a.w_nb2;
+        const int64_t col0 = i13 * a.ne11 + i12 % a.ne11;
+        yq += col0 * a.k; yd += col0 * (a.k / 32);
+    }
 
     auto issue = [&](int b) {
         const int s = b % S;
         const int rows_here = (nrows - b * R < R) ? (nrows - b * R) : R;
-        const uint8_t * src = a.w + (r_begin + (int64_t) b * R) * a.row_stride;
+        const uint8_t * src = wbase + (r_begin + (int64_t) b * R) * a.row_stride;
         uint8_t * slot = slots + (size_t) s * a.slot_stride;
         if (a.contiguous) {
             const uint32_t off = (uint32_t) (reinterpret_cast<uintptr_t>(src) & 15);
@@ -411,7 +435,7 @@ k_mmvq_stream(const stream_args a) {
 #pragma unroll
             for (int c = 0; c < NCOLS; c++) {
                 const int cc = c < a.n ? c : 0;     // padded columns recompute column 0 (never stored)
-                IT::load_acts(acts[c][i], a.yq + (int64_t) cc * a.k, a.yd + (int64_t) cc * (a.k / 32), idx);
+                IT::load_acts(acts[c][i], yq + (int64_t) cc * a.k, yd + (int64_t) cc * (a.k / 32), idx);
             }
         }
     }
@@ -421,7 +445,7 @@ k_mmvq_stream(const stream_args a) {
         mbar_wait(&full[s], (uint32_t) ((b / S) & 1));
         const int rows_here = (nrows - b * R < R) ? (nrows - b * R) : R;
         const uint8_t * slot = slots + (size_t) s * a.slot_stride;
-        const uint8_t * src0 = a.w + (r_begin + (int64_t) b * R) * a.row_stride;
+        const uint8_t * src0 = wbase + (r_begin + (int64_t) b * R) * a.row_stride;
         float * mypart = part + ((size_t) (b & 1) * NW + warp) * R * NCOLS;
 
         for (int r = 0; r < rows_here; r++) {
@@ -457,7 +481,7 @@ k_mmvq_stream(const stream_args a) {
                 const int r = o / NCOLS, c = o - r * NCOLS;
                 float v = 0.0f;
                 for (int w = 0; w < NW; w++) v += pb[(size_t) w * R * NCOLS + o];
-                if (c < a.n) a.dst[(int64_t) c * a.dst_col_stride + r_begin + (int64_t) b * R + r] = v;
+                if (c < a.n) dst[(int64_t) c * a.dst_col_stride + r_begin + (int64_t) b * R + r] = v;
             }
         }
     }
@@ -539,12 +563,14 @@ static int launch_stream(stream_args a, int nw, cudaStream_t st) {
     int cps = cps_env > 0 ? cps_env : (int) ((98304 + (size_t) a.S * a.slot_stride - 1) / ((size_t) a.S * a.slot_stride));
     if (cps < 2) cps = 2;
     if (cps > occ) cps = occ;
-    int64_t grid = (int64_t) caps.sm_count * cps;
+    const int64_t channels = a.ids ? a.dst_nb3 / a.dst_nb2 * a.n_tok_grid : 1;     // MUL_MAT_ID: one grid plane per (slot, token)
+    int64_t grid = ceil_div((int64_t) caps.sm_count * cps, channels);
     const int64_t max_grid = ceil_div(a.m, a.R);
     if (grid > max_grid) grid = max_grid;
     a.rows_per_cta = (int) ceil_div(a.m, grid);
     grid = ceil_div(a.m, a.rows_per_cta);
-    kern<<<(unsigned) grid, nw * 32, smem, st>>>(a);
+    if (a.ids) kern<<<dim3((unsigned) grid, (unsigned) (a.dst_nb3 / a.dst_nb2), (unsigned) a.n_tok_grid), nw * 32, smem, st>>>(a);
+    else       kern<<<(unsigned) grid, nw * 32, smem, st>>>(a);
     b200_count_launch(1);
     B200_RETURN_IF_LAUNCH_FAILED();
     return B200_OK;
@@ -576,9 +602,11 @@ static int launch_stream_t(stream_args a, cudaStream_t st) {
 
 // Returns B200_OK if the streaming kernel ran, B200_STREAM_NOT_APPLICABLE if the caller should use
 // the generic kernel, or an error.
+// moe != NULL: MUL_MAT_ID -- one column per (slot, token) channel, the expert looked up on the device
+struct stream_moe { const uint8_t * ids; int64_t ids_nb0, ids_nb1, w_nb2, n_as, ne11, n_used, n_tok; unsigned * bad; };
 static int mmvq_stream_try(int type, const uint8_t * w, int64_t row_stride, int64_t m, int64_t k,
                            const int8_t * yq, const float * yd, int64_t n, float * dst, int64_t dst_col_stride,
-                           cudaStream_t st) {
+                           cudaStream_t st, const stream_moe * moe = nullptr) {
     if (b200_option(B200_OPT_MMVQ_GENERIC)) return B200_STREAM_NOT_APPLICABLE;
     if (m < 1 || n < 1 || n > 8 || k < 256) return B200_STREAM_NOT_APPLICABLE;
     const int64_t row_bytes = k / type_qk(type) * type_bytes(type);
@@ -588,6 +616,12 @@ static int mmvq_stream_try(int type, const uint8_t * w, int64_t row_stride, int6
     a.yq = yq; a.yd = yd; a.k = k; a.n = (int) n; a.dst = dst; a.dst_col_stride = dst_col_stride;
     a.contiguous = row_stride == row_bytes ? 1 : 0;
     a.rows_per_cta = 0; a.R = 0; a.S = 0; a.slot_stride = 0; a.slots_off = 0; a.row_pitch = 0;
+    a.ids = nullptr; a.ids_nb0 = a.ids_nb1 = a.w_nb2 = a.dst_nb2 = a.dst_nb3 = 0; a.n_as = a.ne11 = 0; a.bad = nullptr; a.n_tok_grid = 0;
+    if (moe) {
+        if (n != 1 || (moe->w_nb2 & 15) || moe->n_used < 1 || moe->n_used > 65535 || moe->n_tok < 1 || moe->n_tok > 65535) return B200_STREAM_NOT_APPLICABLE;
+        a.ids = moe->ids; a.ids_nb0 = moe->ids_nb0; a.ids_nb1 = moe->ids_nb1; a.w_nb2 = moe->w_nb2; a.dst_nb2 = m; a.dst_nb3 = m * moe->n_used;
+        a.n_as = (int) moe->n_as; a.ne11 = (int) moe->ne11; a.bad = moe->bad; a.n_tok_grid = (int) moe->n_tok;
+    }
     switch (type) {
         case T_Q4_0: return launch_stream_t<T_Q4_0>(a, st);
         case T_Q8_0: return launch_stream_t<T_Q8_0>(a, st);

@@ -129,3 +129,33 @@ def test_quantize_rows_4d_permuted_source(kern, oracle, t):
     got = kern.quantize_rows_4d(t, kern.to_device(mem), [k, a, b, c], nb_x, nb_y, rb * a * b * c).cpu().numpy()
     want = oracle.quantize(t, view.reshape(-1, k))
     assert np.array_equal(got.reshape(-1, rb), want)
+
+
+@pytest.mark.parametrize("t", tuple(QUANT_TYPES) + ("q5_1",))
+@pytest.mark.parametrize("m,k,n_tok", [(300, 1024, 1), (33, 4096, 3), (4100, 512, 2)])
+def test_mul_mat_id_vs_oracle_and_bad_expert(kern, oracle, t, m, k, n_tok):
+    """MUL_MAT_ID through the C ABI (mixture of experts; ggml_mul_mat_id, src/ggml-cpu/ggml-cpu.c:1500-1620): every (slot, token)
+    channel is the one-column mat-vec of the expert its id names -- NMSE 1e-9 against the oracle's q8_1 arithmetic per channel,
+    whichever kernel serves it (TMA-staged stream kernel / one warp per row); an id outside the stack zero-fills its channel and
+    raises the sticky error flag (the reference asserts)."""
+    import b200
+    import torch
+    n_as, n_used = 4, 2
+    rng = np.random.default_rng(31)
+    w_np = [random_blocks(t, m, k, seed=60 + e) for e in range(n_as)]
+    experts = kern.to_device(np.concatenate([w.reshape(-1) for w in w_np]))
+    x_np = rng.uniform(-1, 1, size=(n_tok, 1, k)).astype(np.float32)
+    ids_np = np.stack([rng.permutation(n_as)[:n_used] for _ in range(n_tok)]).astype(np.int32)
+    assert kern.device_error_flags() == 0
+    got = kern.mul_mat_id(t, experts, m, k, n_as, kern.to_device(x_np), torch.from_numpy(ids_np).to(kern.device)).cpu().numpy()
+    assert kern.device_error_flags() == 0
+    for tok in range(n_tok):
+        for e in range(n_used):
+            want = oracle.mul_mat(t, w_np[ids_np[tok, e]], m, k, x_np[tok], mode=1)
+            assert oracle.nmse(want, got[tok, e].reshape(1, m)) <= NMSE_ORACLE, (t, tok, e)
+    bad = ids_np.copy()
+    bad[0, 1] = n_as
+    got2 = kern.mul_mat_id(t, experts, m, k, n_as, kern.to_device(x_np), torch.from_numpy(bad).to(kern.device)).cpu().numpy()
+    assert kern.device_error_flags() & b200.ERR_FLAG_INDEX
+    assert not got2[0, 1].any()
+    assert np.array_equal(got2[0, 0], got[0, 0])
