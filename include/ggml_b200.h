@@ -177,7 +177,9 @@ B200_API int    b200_mul_mat_ex(int type_a, const void * a_dev, const int64_t ne
  * t < ne_ids[1] = ne_b[2]; as_dev: the experts' weights [k, m, n_as] (quantized rows), ids_dev: int32 [n_used, n_tokens] with
  * byte strides nb_ids (may be a view).  replaces ggml_cuda_mul_mat_id (src/ggml-cuda/ggml-cuda.cu:2092-2233) and the ids
  * path of mul_mat_vec_q (src/ggml-cuda/mmvq.cu:163-166, 556-569); the ids never leave the device.  An id outside
- * [0, n_as) zero-fills its column and raises bit 0 of b200_device_error_flags. */
+ * [0, n_as) zero-fills its column and raises bit 0 of b200_device_error_flags.  Every (slot, token) pair is a one-column mat-vec
+ * on q8_1 activations: Q4_0 / Q8_0 / Q4_K / Q5_K on the TMA-staged kernel (one grid plane per pair, the expert looked up once per
+ * CTA), Q6_K and the extra formats on the one-warp-per-row kernel. */
 B200_API size_t b200_mul_mat_id_workspace_size(int type_a, const int64_t ne_a[4], const int64_t ne_b[4]);
 B200_API int    b200_mul_mat_id(int type_a, const void * as_dev, const int64_t ne_a[4], const size_t nb_a[4],
                                 const float * b_dev, const int64_t ne_b[4], const size_t nb_b[4],
