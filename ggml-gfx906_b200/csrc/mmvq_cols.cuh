@@ -637,6 +637,7 @@ __global__ void __launch_bounds__(RING_THREADS, 1) k_mmvq_cols_ring(const __grid
                             *reinterpret_cast<unsigned short *>(st + r * pitch + o) = __ldg(reinterpret_cast<const unsigned short *>(p0 + o));
                     }
                     const uint32_t total = __reduce_add_sync(0xFFFFFFFFu, cp);
+                    __syncwarp();                                 // the lanes' tail stores are ordered before lane 0's (release) arrive
                     if (lane == 0) mbar_arrive_expect_tx(&full[stage], total + abytes);
                     __syncwarp();
                     if (cp) bulk_g2s(st + r * pitch, p0, cp, &full[stage]);
