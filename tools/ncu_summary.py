@@ -1,9 +1,10 @@
 """Summarise an ncu report (read here, no GPU): headline raw metrics + stall reasons + hottest SASS lines.
-usage: ncu_summary.py REPORT.ncu-rep [top]"""
+usage: ncu_summary.py REPORT.ncu-rep [top] [result index in the report]"""
 import csv, subprocess, sys, io
 from collections import defaultdict
 rep = sys.argv[1]; top = int(sys.argv[2]) if len(sys.argv) > 2 else 25
-raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+sel = ["--launch-skip", sys.argv[3], "--launch-count", "1"] if len(sys.argv) > 3 else []
+raw = subprocess.run(["ncu", "-i", rep] + sel + ["--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
 h, u, v = rows[0], rows[1], rows[2]
 want = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "dram__bytes_read.sum.per_second",
@@ -16,7 +17,7 @@ want = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
 for i, k in enumerate(h):
     if k in want or "pipe_tensor" in k:
         print(f"{k:70s} {v[i]} {u[i]}")
-src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
+src = subprocess.run(["ncu", "-i", rep] + sel + ["--page", "source", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(src)))
 h, data = rows[1], rows[2:]
 ix = {k: i for i, k in enumerate(h)}
